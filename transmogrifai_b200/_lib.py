@@ -1,0 +1,90 @@
+"""ctypes binding of libtmog_b200.so -- the same C ABI a JNI shim binds (include/tmog_b200.h).
+
+There is no fallback: if the library has not been built (``python -c "import __graft_entry__ as g; g.build()"``) the
+import of anything that computes fails loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+from typing import Dict, List
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libtmog_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "tmog_b200.h")
+
+REAL_NSTAT = 8
+
+
+class TmogError(RuntimeError):
+    """A call into libtmog_b200 failed; ``code`` is the TMOG_E* status."""
+
+    def __init__(self, code: int, message: str):
+        super().__init__(f"libtmog_b200: {message} (status {code})")
+        self.code = code
+        self.message = message
+
+
+class TmogInvalidArgument(TmogError, ValueError):
+    """TMOG_EINVAL -- the reference would have thrown IllegalArgumentException (a failed ``require``)."""
+
+
+_lib = None
+
+_p = C.c_void_p
+_i64 = C.c_int64
+_int = C.c_int
+_dbl = C.c_double
+_sz = C.c_size_t
+
+# name -> argtypes; every function returns int except the two noted below
+_SIGNATURES: Dict[str, List] = {
+    "tmog_real_pilot_shift_dev": [_p, _i64, _p, _i64, _p, _i64, _int, _p, _p],
+    "tmog_real_fit_scratch_bytes": [_int, C.POINTER(_sz)],
+    "tmog_real_fit_partials_dev": [_p, _i64, _p, _i64, _p, _i64, _int, _p, _p, _sz, _p, _p],
+    "tmog_real_partials_merge": [_p, _p, _int],
+    "tmog_real_finish": [_p, _p, _int, _int, _dbl, _int, _p, _p, _p, _p, _p, _p, _p, _p],
+    "tmog_real_transform_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _int, _p, _i64, _i64, _p],
+    "tmog_binary_transform_dev": [_p, _i64, _p, _i64, _i64, _int, _int, _int, _p, _i64, _i64, _p],
+}
+
+
+def declared_symbols() -> List[str]:
+    """Every function the public header declares (used by the export test)."""
+    with open(HEADER_PATH) as f:
+        src = f.read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(tmog_[a-z0-9_]+)\s*\(", src)))
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.tmog_last_error.restype = C.c_char_p
+        L.tmog_last_error.argtypes = []
+        L.tmog_abi_version.restype = _int
+        L.tmog_abi_version.argtypes = []
+        for name, args in _SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = _int
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(status: int) -> None:
+    if status != 0:
+        msg = lib().tmog_last_error().decode("utf-8", "replace")
+        if status == -1:
+            raise TmogInvalidArgument(status, msg)
+        raise TmogError(status, msg)
+
+
+def call(name: str, *args) -> None:
+    check(getattr(lib(), name)(*args))

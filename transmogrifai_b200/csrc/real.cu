@@ -1,0 +1,432 @@
+// Real / RealNN / Binary vectorizers fused with the SanityChecker column scan (sm_100a).
+//
+// Path restated here (reference file:line in include/tmog_b200.h):
+//   fit        RealVectorizer.fitFn + MeanSeqNullNum, and for the emitted columns SanityChecker's colStats, label
+//              correlation and per-label null-indicator sums, all from ONE read of the raw columns
+//   transform  RealVectorizerModel / RealNNVectorizer / BinaryVectorizer transformFn into a row-major dense block
+//
+// HBM layout: column-major f64 values (stride ld), Arrow validity bitmaps (stride ldv words), f64 label.
+// Roofline: HBM.  fit reads ncols*8 + ncols/8 + 8 bytes per row once; transform reads the same minus the label and
+// writes 16 bytes per (row, column) when null indicators are tracked.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace tmog {
+
+constexpr int FIT_TILE = 2048;  // rows per tile = 32 lanes x 32 double2
+constexpr int FIT_THREADS = 256;
+constexpr int FIT_WARPS = FIT_THREADS / 32;
+constexpr int FIT_CTAS_PER_SM = 2;
+constexpr int NS = TMOG_REAL_NSTAT;
+constexpr int PILOT_ROWS = 4096;
+
+struct Acc {
+    double sd, sdd, sde, se, mn, mx;
+};
+
+__device__ __forceinline__ void acc_init(Acc& a) {
+    a.sd = a.sdd = a.sde = a.se = 0.0;
+    a.mn = INFINITY;
+    a.mx = -INFINITY;
+}
+
+__device__ __forceinline__ void acc_add(Acc& a, bool v, double x, double s, double e) {
+    const double d = v ? x - s : 0.0;
+    const double ev = v ? e : 0.0;
+    a.sd += d;
+    a.sdd = fma(d, d, a.sdd);
+    a.sde = fma(d, ev, a.sde);
+    a.se += ev;
+    a.mn = fmin(a.mn, v ? x : INFINITY);
+    a.mx = fmax(a.mx, v ? x : -INFINITY);
+}
+
+__device__ __forceinline__ void kahan_add(double& sum, double& comp, double v) {
+    const double y = v - comp;
+    const double t = sum + y;
+    comp = (t - sum) - y;
+    sum = t;
+}
+
+// One CTA walks row tiles (persistent, grid = SMs x FIT_CTAS_PER_SM).  Per tile the label is staged once in shared
+// memory as e = y - shift_y; each warp then streams whole columns of the tile with 128-bit loads (lane i holds rows
+// 2i, 2i+1 of every 64-row group, whose validity is one bitmap word broadcast by shuffle) and keeps six fp64
+// accumulators per lane.  A warp owns columns c = warp, warp + 8, ... so the per-CTA accumulators in shared memory
+// need no atomics; they are Kahan-compensated across tiles and written once per CTA to `scratch`.
+__global__ void __launch_bounds__(FIT_THREADS, FIT_CTAS_PER_SM)
+real_fit_kernel(const double* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid, int64_t ldv,
+                const double* __restrict__ label, int64_t n, int ncols, const double* __restrict__ shifts,
+                double* __restrict__ scratch) {
+    extern __shared__ __align__(16) double sm[];
+    double* e_tile = sm;                  // [FIT_TILE]
+    double* acc = sm + FIT_TILE;          // [(ncols+1) * NS]
+    double* comp = acc + (ncols + 1) * NS;  // [(ncols+1) * 4]  compensation of stats 1..4
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nacc = (ncols + 1) * NS;
+    for (int i = tid; i < nacc; i += FIT_THREADS) {
+        const int st = i % NS;
+        acc[i] = st == 5 ? INFINITY : (st == 6 ? -INFINITY : 0.0);
+    }
+    for (int i = tid; i < (ncols + 1) * 4; i += FIT_THREADS) comp[i] = 0.0;
+
+    const double sy = shifts[ncols];
+    const int64_t ntiles = (n + FIT_TILE - 1) / FIT_TILE;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int64_t r0 = tile * FIT_TILE;
+        const int rows = (int)min((int64_t)FIT_TILE, n - r0);
+        __syncthreads();  // readers of the previous tile are done (also orders the init above)
+        for (int i = tid; i < FIT_TILE; i += FIT_THREADS) e_tile[i] = i < rows ? label[r0 + i] - sy : 0.0;
+        __syncthreads();
+
+        for (int c = warp; c <= ncols; c += FIT_WARPS) {
+            const bool is_label = (c == ncols);
+            const double* col = is_label ? label : values + (int64_t)c * ld;
+            const uint64_t* vcol = (is_label || valid == nullptr) ? nullptr : valid + (int64_t)c * ldv;
+            const double s = shifts[c];
+            Acc a, b;
+            acc_init(a);
+            acc_init(b);
+            unsigned cnt = 0;
+            if (rows == FIT_TILE) {
+                const unsigned long long myw = vcol ? vcol[(r0 >> 6) + lane] : ~0ull;  // 32 words = this tile
+                cnt = __popcll(myw);
+                const double2* p = reinterpret_cast<const double2*>(col + r0) + lane;
+                const double2* ep = reinterpret_cast<const double2*>(e_tile) + lane;
+#pragma unroll 1
+                for (int i0 = 0; i0 < 32; i0 += 8) {
+                    double2 x[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) x[k] = ldg_stream(p + (i0 + k) * 32);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const unsigned long long w = __shfl_sync(FULL, myw, i0 + k);
+                        const unsigned bits = (unsigned)(w >> (2 * lane)) & 3u;
+                        const double2 e = ep[(i0 + k) * 32];
+                        acc_add(a, bits & 1u, x[k].x, s, e.x);
+                        acc_add(b, bits & 2u, x[k].y, s, e.y);
+                    }
+                }
+            } else {  // ragged last tile
+                for (int i = lane; i < rows; i += 32) {
+                    const int64_t r = r0 + i;
+                    const bool v = vcol ? ((vcol[r >> 6] >> (r & 63)) & 1ull) != 0 : true;
+                    cnt += v;
+                    acc_add(a, v, col[r], s, e_tile[i]);
+                }
+            }
+            const double sd = warp_sum(a.sd + b.sd);
+            const double sdd = warp_sum(a.sdd + b.sdd);
+            const double sde = warp_sum(a.sde + b.sde);
+            const double se = warp_sum(a.se + b.se);
+            const double mn = warp_min(fmin(a.mn, b.mn));
+            const double mx = warp_max(fmax(a.mx, b.mx));
+            const unsigned total = __reduce_add_sync(FULL, cnt);
+            if (lane == 0) {
+                double* q = acc + c * NS;
+                double* k = comp + c * 4;
+                q[0] += (double)total;
+                kahan_add(q[1], k[0], sd);
+                kahan_add(q[2], k[1], sdd);
+                kahan_add(q[3], k[2], sde);
+                kahan_add(q[4], k[3], se);
+                q[5] = fmin(q[5], mn);
+                q[6] = fmax(q[6], mx);
+            }
+        }
+    }
+    __syncthreads();
+    double* out = scratch + (int64_t)blockIdx.x * nacc;
+    for (int i = tid; i < nacc; i += FIT_THREADS) {
+        const int st = i % NS;
+        double v = acc[i];
+        if (st >= 1 && st <= 4) v -= comp[(i / NS) * 4 + (st - 1)];
+        out[i] = v;
+    }
+}
+
+// Reduce the per-CTA partials in a fixed order (deterministic for a given grid): one warp per column.
+__global__ void __launch_bounds__(32)
+real_fit_reduce_kernel(const double* __restrict__ scratch, int nblocks, int ncols, int64_t n,
+                       double* __restrict__ partials) {
+    const int c = blockIdx.x, lane = threadIdx.x;
+    const int nacc = (ncols + 1) * NS;
+    double s[5] = {0, 0, 0, 0, 0};
+    double mn = INFINITY, mx = -INFINITY;
+    for (int b = lane; b < nblocks; b += 32) {
+        const double* q = scratch + (int64_t)b * nacc + c * NS;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) s[k] += q[k];
+        mn = fmin(mn, q[5]);
+        mx = fmax(mx, q[6]);
+    }
+#pragma unroll
+    for (int k = 0; k < 5; ++k) s[k] = warp_sum(s[k]);
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    if (lane == 0) {
+        double* o = partials + c * NS;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) o[k] = s[k];
+        o[5] = mn;
+        o[6] = mx;
+        o[7] = (double)n;
+    }
+}
+
+__global__ void __launch_bounds__(128)
+real_pilot_shift_kernel(const double* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid, int64_t ldv,
+                        const double* __restrict__ label, int64_t n, int ncols, double* __restrict__ shifts) {
+    __shared__ double ssum[4];
+    __shared__ unsigned scnt[4];
+    const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool is_label = (c == ncols);
+    const double* col = is_label ? label : values + (int64_t)c * ld;
+    const uint64_t* vcol = (is_label || valid == nullptr) ? nullptr : valid + (int64_t)c * ldv;
+    const int rows = (int)min((int64_t)PILOT_ROWS, n);
+    double s = 0.0;
+    unsigned cnt = 0;
+    for (int r = tid; r < rows; r += 128) {
+        const bool v = vcol ? ((vcol[r >> 6] >> (r & 63)) & 1ull) != 0 : true;
+        const double x = col[r];
+        if (v && isfinite(x)) {
+            s += x;
+            ++cnt;
+        }
+    }
+    s = warp_sum(s);
+    cnt = __reduce_add_sync(FULL, cnt);
+    if (lane == 0) {
+        ssum[warp] = s;
+        scnt[warp] = cnt;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const double t = ssum[0] + ssum[1] + ssum[2] + ssum[3];
+        const unsigned k = scnt[0] + scnt[1] + scnt[2] + scnt[3];
+        shifts[c] = k > 0 ? t / (double)k : 0.0;
+    }
+}
+
+// Column-major -> row-major transposing writer.  Tile = 64 rows x 32 columns through padded shared memory: loads are
+// 256-byte row runs of one column per warp instruction, stores are one 512-byte run ([value, isNull] x 32 columns) of
+// one output row per warp instruction.
+template <typename T, bool TRACK>
+__global__ void __launch_bounds__(256)
+vec_transform_kernel(const T* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid, int64_t ldv,
+                     int64_t n, int ncols, const double* __restrict__ fills, double fill_const,
+                     double* __restrict__ out, int64_t out_ld, int64_t out_col0) {
+    __shared__ double tile[32][65];
+    __shared__ unsigned long long vbits[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int c0 = blockIdx.y * 32;
+    const int64_t r0 = (int64_t)blockIdx.x * 64;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int cl = warp + 8 * k;
+        const int c = c0 + cl;
+        if (c < ncols) {
+            const T* col = values + (int64_t)c * ld + r0;
+            const int64_t ra = r0 + lane, rb = r0 + lane + 32;
+            tile[cl][lane] = ra < n ? (double)col[lane] : 0.0;
+            tile[cl][lane + 32] = rb < n ? (double)col[lane + 32] : 0.0;
+            if (lane == 0) vbits[cl] = valid ? valid[(int64_t)c * ldv + (r0 >> 6)] : ~0ull;
+        }
+    }
+    __syncthreads();
+    const int c = c0 + lane;
+    if (c >= ncols) return;
+    const double fill = fills ? fills[c] : fill_const;
+    const unsigned long long vb = vbits[lane];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const int rl = warp + 8 * k;
+        const int64_t r = r0 + rl;
+        if (r < n) {
+            const bool v = (vb >> rl) & 1ull;
+            double x = tile[lane][rl];
+            if (sizeof(T) == 1) x = x != 0.0 ? 1.0 : 0.0;
+            x = v ? x : fill;
+            if (TRACK) {
+                stg_stream(reinterpret_cast<double2*>(out + r * out_ld + out_col0 + 2 * c),
+                           make_double2(x, v ? 0.0 : 1.0));
+            } else {
+                out[r * out_ld + out_col0 + c] = x;
+            }
+        }
+    }
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+static int fit_grid() { return sm_count() * FIT_CTAS_PER_SM; }
+
+static size_t fit_smem_bytes(int ncols) { return sizeof(double) * (size_t)(FIT_TILE + (ncols + 1) * (NS + 4)); }
+
+static int check_columns(const void* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n, int ncols,
+                         int elem_bytes) {
+    TMOG_REQUIRE(n >= 0 && ncols >= 0, "n (%lld) and ncols (%d) must be non-negative", (long long)n, ncols);
+    TMOG_REQUIRE(ncols == 0 || n == 0 || values != nullptr, "values is NULL");
+    TMOG_REQUIRE(ld >= n, "column stride ld (%lld) is smaller than n (%lld)", (long long)ld, (long long)n);
+    TMOG_REQUIRE(((ld * elem_bytes) & 15) == 0 && aligned16(values),
+                 "columns must be 16-byte aligned (base pointer and ld * %d bytes)", elem_bytes);
+    TMOG_REQUIRE(valid == nullptr || ldv >= (n + 63) / 64, "bitmap stride ldv (%lld) too small for n (%lld)",
+                 (long long)ldv, (long long)n);
+    return TMOG_OK;
+}
+
+}  // namespace tmog
+
+using namespace tmog;
+
+extern "C" int tmog_real_pilot_shift_dev(const double* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                         const double* label, int64_t n, int ncols, double* shifts, void* stream) {
+    if (int rc = check_columns(values, ld, valid, ldv, n, ncols, 8)) return rc;
+    TMOG_REQUIRE(shifts != nullptr && (label != nullptr || n == 0), "shifts / label is NULL");
+    real_pilot_shift_kernel<<<ncols + 1, 128, 0, (cudaStream_t)stream>>>(values, ld, valid, ldv, label, n, ncols,
+                                                                         shifts);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_real_fit_scratch_bytes(int ncols, size_t* bytes) {
+    TMOG_REQUIRE(ncols >= 0 && bytes != nullptr, "bad arguments");
+    *bytes = sizeof(double) * (size_t)fit_grid() * (size_t)(ncols + 1) * NS;
+    return TMOG_OK;
+}
+
+extern "C" int tmog_real_fit_partials_dev(const double* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                          const double* label, int64_t n, int ncols, const double* shifts,
+                                          void* scratch, size_t scratch_bytes, double* partials, void* stream) {
+    if (int rc = check_columns(values, ld, valid, ldv, n, ncols, 8)) return rc;
+    TMOG_REQUIRE(label != nullptr || n == 0, "label is NULL");
+    TMOG_REQUIRE(aligned16(label), "label must be 16-byte aligned");
+    TMOG_REQUIRE(shifts != nullptr && partials != nullptr, "shifts / partials is NULL");
+    const int grid = fit_grid();
+    const size_t need = sizeof(double) * (size_t)grid * (size_t)(ncols + 1) * NS;
+    if (scratch == nullptr || scratch_bytes < need) {
+        set_error("scratch too small: %zu bytes given, %zu needed (tmog_real_fit_scratch_bytes)", scratch_bytes, need);
+        return TMOG_ENOMEM;
+    }
+    const size_t smem = fit_smem_bytes(ncols);
+    TMOG_REQUIRE(smem <= 200 * 1024, "too many columns for one fit call (%d): split the column block", ncols);
+    if (smem > 48 * 1024) {
+        TMOG_CUDA(cudaFuncSetAttribute(real_fit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    real_fit_kernel<<<grid, FIT_THREADS, smem, st>>>(values, ld, valid, ldv, label, n, ncols, shifts,
+                                                     static_cast<double*>(scratch));
+    TMOG_LAUNCH_CHECK();
+    real_fit_reduce_kernel<<<ncols + 1, 32, 0, st>>>(static_cast<const double*>(scratch), grid, ncols, n, partials);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_real_partials_merge(double* acc, const double* other, int ncols) {
+    TMOG_REQUIRE(acc != nullptr && other != nullptr && ncols >= 0, "bad arguments");
+    for (int c = 0; c <= ncols; ++c) {
+        double* a = acc + c * NS;
+        const double* b = other + c * NS;
+        for (int k = 0; k < 5; ++k) a[k] += b[k];
+        a[5] = fmin(a[5], b[5]);
+        a[6] = fmax(a[6], b[6]);
+        a[7] += b[7];
+    }
+    return TMOG_OK;
+}
+
+extern "C" int tmog_real_finish(const double* partials, const double* shifts, int ncols, int fill_with_mean,
+                                double fill_const, int track_nulls, double* fills, double* mean, double* variance,
+                                double* mn, double* mx, double* cov_label, double* label_stats,
+                                double* null_label_sum) {
+    TMOG_REQUIRE(partials != nullptr && shifts != nullptr && ncols >= 0, "bad arguments");
+    const double* L = partials + ncols * NS;
+    const double n = L[7];
+    const double sy = shifts[ncols];
+    // label: e = y - sy over all rows
+    const double eps = n > 0 ? L[1] / n : 0.0;  // mean_y - sy
+    const double mean_y = sy + eps;
+    const double m2y = n > 0 ? L[2] - L[1] * L[1] / n : 0.0;
+    if (label_stats) {
+        label_stats[0] = n;
+        label_stats[1] = n > 0 ? mean_y : 0.0;
+        label_stats[2] = n > 1 ? fmax(m2y, 0.0) / (n - 1) : 0.0;
+        label_stats[3] = n > 0 ? L[5] : 0.0;
+        label_stats[4] = n > 0 ? L[6] : 0.0;
+    }
+    const int w = track_nulls ? 2 : 1;
+    for (int c = 0; c < ncols; ++c) {
+        const double* q = partials + c * NS;
+        const double v = q[0], sd = q[1], sdd = q[2], sde = q[3], sev = q[4];
+        const double z = n - v;
+        const double s = shifts[c];
+        // SequenceAggregators.scala:84 -- s / c if c > 0 else s (= 0.0)
+        const double fill = fill_with_mean ? (v > 0 ? s + sd / v : 0.0) : fill_const;
+        if (fills) fills[c] = fill;
+        // filled column f = x (valid) | fill (null)
+        const double mu = n > 0 ? (fill_with_mean ? fill : (v * s + sd + z * fill) / n) : 0.0;
+        const double delta = mu - s;  // x - mu = d - delta
+        double m2 = sdd - 2.0 * delta * sd + v * delta * delta + z * (fill - mu) * (fill - mu);
+        if (m2 < 0) m2 = 0;
+        const double se_null = L[1] - sev;  // sum of e over null rows
+        const double cov = (sde - eps * sd - delta * sev + v * delta * eps) + (fill - mu) * (se_null - z * eps);
+        const int o = c * w;
+        if (mean) mean[o] = mu;
+        if (variance) variance[o] = n > 1 ? m2 / (n - 1) : 0.0;
+        if (mn) mn[o] = n > 0 ? (z > 0 ? fmin(v > 0 ? q[5] : fill, fill) : q[5]) : 0.0;
+        if (mx) mx[o] = n > 0 ? (z > 0 ? fmax(v > 0 ? q[6] : fill, fill) : q[6]) : 0.0;
+        if (cov_label) cov_label[o] = cov;
+        if (null_label_sum) null_label_sum[c] = se_null + z * sy;
+        if (track_nulls) {
+            if (mean) mean[o + 1] = n > 0 ? z / n : 0.0;
+            if (variance) variance[o + 1] = n > 1 ? (z * (n - z) / n) / (n - 1) : 0.0;
+            if (mn) mn[o + 1] = (n > 0 && v == 0) ? 1.0 : 0.0;
+            if (mx) mx[o + 1] = z > 0 ? 1.0 : 0.0;
+            if (cov_label) cov_label[o + 1] = se_null - z * eps;
+        }
+    }
+    return TMOG_OK;
+}
+
+template <typename T>
+static int launch_transform(const T* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n, int ncols,
+                            const double* fills, double fill_const, int track_nulls, double* out, int64_t out_ld,
+                            int64_t out_col0, void* stream) {
+    if (int rc = check_columns(values, ld, valid, ldv, n, ncols, (int)sizeof(T))) return rc;
+    const int64_t width = (int64_t)ncols * (track_nulls ? 2 : 1);
+    TMOG_REQUIRE(out != nullptr || n == 0 || ncols == 0, "out is NULL");
+    TMOG_REQUIRE(out_col0 >= 0 && out_ld >= out_col0 + width, "output block [%lld, %lld) exceeds row stride %lld",
+                 (long long)out_col0, (long long)(out_col0 + width), (long long)out_ld);
+    if (track_nulls)
+        TMOG_REQUIRE(aligned16(out) && (out_ld & 1) == 0 && (out_col0 & 1) == 0,
+                     "tracked output needs a 16-byte aligned block: out pointer, even out_ld and even out_col0");
+    if (n == 0 || ncols == 0) return TMOG_OK;
+    const int64_t gx = (n + 63) / 64;
+    TMOG_REQUIRE(gx <= 0x7fffffffLL, "too many rows for one transform call (%lld): chunk the batch", (long long)n);
+    dim3 grid((unsigned)gx, (unsigned)((ncols + 31) / 32));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (track_nulls)
+        vec_transform_kernel<T, true><<<grid, 256, 0, st>>>(values, ld, valid, ldv, n, ncols, fills, fill_const, out,
+                                                             out_ld, out_col0);
+    else
+        vec_transform_kernel<T, false><<<grid, 256, 0, st>>>(values, ld, valid, ldv, n, ncols, fills, fill_const, out,
+                                                              out_ld, out_col0);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_real_transform_dev(const double* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                       int64_t n, int ncols, const double* fills, int track_nulls, double* out,
+                                       int64_t out_ld, int64_t out_col0, void* stream) {
+    TMOG_REQUIRE(fills != nullptr || valid == nullptr, "fills is NULL but the columns are nullable");
+    return launch_transform<double>(values, ld, valid, ldv, n, ncols, fills, 0.0, track_nulls, out, out_ld, out_col0,
+                                    stream);
+}
+
+extern "C" int tmog_binary_transform_dev(const uint8_t* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                         int64_t n, int ncols, int fill_value, int track_nulls, double* out,
+                                         int64_t out_ld, int64_t out_col0, void* stream) {
+    return launch_transform<uint8_t>(values, ld, valid, ldv, n, ncols, nullptr, fill_value ? 1.0 : 0.0, track_nulls,
+                                     out, out_ld, out_col0, stream);
+}
