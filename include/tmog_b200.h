@@ -105,6 +105,137 @@ int tmog_binary_transform_dev(const uint8_t* values, int64_t ld, const uint64_t*
                               int ncols, int fill_value, int track_nulls, double* out, int64_t out_ld,
                               int64_t out_col0, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------------------
+ * Label classes
+ * ------------------------------------------------------------------------------------------------------------------
+ * Replaces the keying of  C/stages/impl/preparators/SanityChecker.scala:265-281  (reduceByKey on the label value,
+ * distinct-label count, labels sorted ascending).  Distinctness follows java.lang.Double.equals (bit patterns, one
+ * NaN).  classes [max_classes] receives the sorted distinct values, *nclasses (DEVICE int) their number, or -1 when
+ * there are more than max_classes (<= 255): the label is then treated as continuous.  class_ids (may be NULL)
+ * receives one byte per row: the index of the row's label in classes; class_counts [max_classes] (may be NULL) the
+ * number of rows per class (the "contingency(d) = 1.0" slot of SanityChecker.scala:270). */
+int tmog_label_classes_scratch_bytes(size_t* bytes);
+int tmog_label_classes_dev(const double* label, int64_t n, int max_classes, double* classes, int* nclasses,
+                           uint8_t* class_ids, uint64_t* class_counts, void* scratch, size_t scratch_bytes,
+                           void* stream);
+
+/* counts[c * nclasses + k] = number of NULL rows of column c whose label class is k: the 2 x nLabels contingency
+ * table of a lone null indicator (SanityChecker.scala:306-322) for labels with any number of classes.
+ * accumulate != 0 adds to counts (row chunks), else counts is overwritten. */
+int tmog_null_class_counts_dev(const uint64_t* valid, int64_t ldv, const uint8_t* class_ids, int64_t n, int ncols,
+                               int nclasses, int accumulate, uint64_t* counts, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * SanityChecker over a materialised dense OPVector block (row-major f64, row stride ld, d feature columns)
+ * ------------------------------------------------------------------------------------------------------------------
+ * For vectors that did not come out of the fused vectorizer scans.  The label is treated as column d. */
+
+/* Pilot shifts [d+1]: column means over the first min(n, 4096) rows. */
+int tmog_dense_pilot_shift_dev(const double* x, int64_t ld, int64_t n, int d, const double* label, double* shifts,
+                               void* stream);
+int tmog_dense_stats_scratch_bytes(int64_t n, int d, size_t* bytes);
+
+/* Replaces Statistics.colStats (C/stages/impl/preparators/SanityChecker.scala:407), the label covariances of
+ * U/stats/OpStatistics.scala:86-90 and, for the columns flagged in cat_mask [d], the per-label column sums of
+ * SanityChecker.scala:265-272.  partials [(d+1) * TMOG_REAL_NSTAT] has the layout of tmog_real_fit_partials_dev
+ * (n_valid = n) and is finished by tmog_real_finish(track_nulls = 0); class_sums [nclasses * d] may be NULL. */
+int tmog_dense_stats_dev(const double* x, int64_t ld, int64_t n, int d, const double* label,
+                         const uint8_t* class_ids, int nclasses, const uint8_t* cat_mask, const double* shifts,
+                         void* scratch, size_t scratch_bytes, double* partials, double* class_sums, void* stream);
+
+/* Replaces SanityCheckerModel.transformFn -> removeFeatures
+ * (C/stages/impl/preparators/DerivedFeatureFilterUtils.scala:291-305) on a dense vector: out[r][j] = x[r][idx[j]]. */
+int tmog_dense_gather_dev(const double* x, int64_t ld, int64_t n, const int32_t* idx, int k, double* out,
+                          int64_t out_ld, void* stream);
+
+/* Replaces the Gramian pass of Statistics.corr (SanityChecker.scala:467-470; Spark RowMatrix.computeGramianMatrix):
+ * gram [(d+1)^2] += (X - s)^T (X - s), upper triangle (i <= j) only, label as column d.  The caller zeroes gram
+ * before the first row chunk; chunks / GPUs add. Fails for d + 1 > 65535 like the reference. */
+int tmog_dense_gram_dev(const double* x, int64_t ld, int64_t n, int d, const double* label, const double* shifts,
+                        double* gram, void* stream);
+
+/* Host: Pearson matrix [(D)^2] from the shifted Gramian and the shifted column sums (partials[.][1]) -- Spark's
+ * computeCovariance + computeCorrelationMatrixFromCovariance: NaN where |cov_ii| <= 1e-12, diagonal 1.0. */
+int tmog_pearson_from_gram(int D, double n, const double* gram, const double* sums, double* corr);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * SanityChecker driver-side finishing (host memory, tiny inputs)
+ * ------------------------------------------------------------------------------------------------------------------ */
+
+/* Replaces OpStatistics.contingencyStats  U/stats/OpStatistics.scala:300-326 (filterEmpties :141-175,
+ * chiSquaredTestOnFiltered :202-211 = Spark Statistics.chiSqTest without continuity correction, mutualInfo :234-271,
+ * maxConfidences :280-290).  matrix is rows x cols ROW-major: rows = feature choices, cols = label values.
+ * Outputs (any may be NULL): cramers_v, chi2, mutual_info scalars; pmi [rows*cols] row-major; max_conf, supports
+ * [rows].  Returns 1 (not an error) when the matrix is empty after filtering: the reference then yields NaN and empty
+ * maps, and every output is NaN. */
+int tmog_contingency_stats(const double* matrix, int rows, int cols, double* cramers_v, double* chi2,
+                           double* mutual_info, double* pmi, double* max_conf, double* supports);
+
+/* corr_i = cov_i / (sqrt(var_i) sqrt(var_y) (n - 1)), 0/0 kept as NaN  (U/stats/OpStatistics.scala:92-94). */
+int tmog_pearson_from_cov(int d, double n, const double* cov_label, const double* variance, double label_variance,
+                          double* corr);
+
+/* Replaces DerivedFeatureFilterUtils.makeColumnStatistics' parent-level maxima
+ * C/stages/impl/preparators/DerivedFeatureFilterUtils.scala:112-160, getFeaturesToDrop :234-281 and
+ * ColumnStatistics.reasonsToRemove :350-405 with column metadata reduced to integers by the caller:
+ *   d                 feature columns (label excluded)
+ *   variance[d]
+ *   corr_label        correlations with the label, indexed through corr_pos (NULL: none computed)
+ *   corr_matrix       corr_dim x corr_dim row-major Pearson matrix incl. the label as last row/col, or NULL
+ *                     (CorrelationLevel.Off)
+ *   corr_pos[d]       position of column i inside corr_label / corr_matrix, -1 if excluded (hashed text exclusion)
+ *   parent_offsets[d+1], parent_ids   CSR list of parent-feature ids per column (parentNamesWithMapKeys)
+ *   group_id[d]       feature-group id (featureGroup()) or -1
+ *   text_shared_hash[d]  isTextSharedHash :410-414
+ *   cramers_v[d], rule_count[d]  rule_count = -1: column is in no categorical group (cramersV = None); else the
+ *                     number (0..2) of (confidence, support) pairs in rule_conf / rule_support [2*d]
+ *   params[9]         minVariance, minCorrelation, maxCorrelation, maxFeatureCorr, maxCramersV, maxRuleConfidence,
+ *                     minRequiredRuleSupport, removeFeatureGroup, protectTextSharedHash
+ * Outputs: drop[d] (1 = remove); reasons[d] bit mask (1 variance, 2 minCorr, 4 maxCorr, 8 featureCorr, 16 cramersV,
+ * 32 ruleConfidence, 64 group flagged by rule confidence, 128 parent cramersV, 256 parent corr) or NULL;
+ * parent_corr / parent_cramers [d] (NaN = none) or NULL. */
+int tmog_sanity_decide(int d, const double* variance, const double* corr_label, const double* corr_matrix,
+                       int corr_dim, const int32_t* corr_pos, const int32_t* parent_offsets,
+                       const int32_t* parent_ids, const int32_t* group_id, const uint8_t* text_shared_hash,
+                       const double* cramers_v, const int32_t* rule_count, const double* rule_conf,
+                       const double* rule_support, const double* params, uint8_t* drop, uint32_t* reasons,
+                       double* parent_corr, double* parent_cramers);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Host-buffer entry points (what the JNI shim calls per exported Spark partition)
+ * ------------------------------------------------------------------------------------------------------------------
+ * A tmog_ctx is bound to one device and owns the staging buffers, streams and events that pipeline row chunks
+ * H2D -> kernel -> D2H.  One ctx per calling thread (FitStagesUtil runs one task thread per partition,
+ * C/utils/stages/FitStagesUtil.scala:96-119); a ctx itself is not thread-safe.  Inputs and outputs should live in
+ * pinned memory (tmog_pinned_alloc) so that the copies are asynchronous DMA. */
+typedef struct tmog_ctx tmog_ctx;
+int tmog_ctx_create(int device, tmog_ctx** ctx);
+int tmog_ctx_destroy(tmog_ctx* ctx);
+int tmog_pinned_alloc(size_t bytes, void** ptr);
+int tmog_pinned_free(void* ptr);
+
+/* tmog_real_fit_partials_dev over host columns, streamed in chunks of chunk_rows (<= 0: default 1 Mi rows).
+ *   keep_resident != 0 keeps the uploaded block on the device so that the following tmog_real_transform_host call on
+ *                      the same `values` pointer needs no second upload (SequenceEstimator.fit is always followed by
+ *                      the model's transform on the same data, C/utils/stages/FitStagesUtil.scala:251-290);
+ *   shifts_in          NULL: pilot shifts are taken from the first chunk; else the shifts another partition / rank
+ *                      already chose (partials only merge when they share shifts);
+ *   shifts_out         [ncols+1] the shifts used;  partials_out  [(ncols+1) * TMOG_REAL_NSTAT];
+ *   max_classes        0: skip; else (<= 255) also run tmog_label_classes_dev on the label: classes_out [max_classes],
+ *                      *nclasses_out (HOST int; -1 = continuous label), class_counts_out [max_classes] (may be NULL)
+ *                      and, when the label is categorical, null_class_counts_out [ncols * nclasses] (may be NULL) as
+ *                      tmog_null_class_counts_dev defines it. */
+int tmog_real_fit_host(tmog_ctx* ctx, const double* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                       const double* label, int64_t n, int ncols, int64_t chunk_rows, int keep_resident,
+                       const double* shifts_in, double* shifts_out, double* partials_out, int max_classes,
+                       double* classes_out, int* nclasses_out, uint64_t* class_counts_out,
+                       uint64_t* null_class_counts_out);
+
+/* tmog_real_transform_dev over host columns into a host row-major block (same out_ld / out_col0 meaning). */
+int tmog_real_transform_host(tmog_ctx* ctx, const double* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                             int64_t n, int ncols, const double* fills, int track_nulls, int64_t chunk_rows,
+                             double* out, int64_t out_ld, int64_t out_col0);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,179 @@
+"""GPU parity of the reference-facing stage API (setInput / fit / transform / getMetadata) against the oracle."""
+import math
+
+import numpy as np
+import pytest
+
+from oracle import sanity as S
+from oracle import vectorizers as V
+from oracle.metadata import ColumnMeta
+from tests.util_data import make_real_config
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+def _batch(cols, response=None, device=None):
+    from transmogrifai_b200.columnar import ColumnarBatch
+    b = ColumnarBatch.from_columns(cols, response=response)
+    return b.to(device) if device else b
+
+
+def _lists(x, valid):
+    return [[float(v) if ok else None for v, ok in zip(c, vc)] for c, vc in zip(x, valid)]
+
+
+@pytest.mark.parametrize("device", [None, "cuda"])
+def test_real_vectorizer_stage_reference_goldens(device):
+    # core/src/test/scala/com/salesforce/op/stages/impl/feature/RealVectorizerTest.scala:47-53,118-214
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.numeric import RealVectorizer
+    inA, inB, inC = (F.FeatureBuilder.Real(n).asPredictor() for n in ("inA", "inB", "inC"))
+    batch = _batch({"inA": (F.REAL, [4.0, None, 2.0]), "inB": (F.REAL, [2.0, 2.0, None]),
+                    "inC": (F.REAL, [None, None, None])}, device=device)
+    with pytest.raises(KeyError):
+        RealVectorizer().getOutput()                                         # :77-79
+    vec = RealVectorizer().setInput(inA, inB, inC)
+    out = vec.getOutput()
+    assert out.type_name == F.OPVECTOR and not out.is_response and out.parents == (inA, inB, inC)   # :81-89
+    m = vec.setFillWithMean().setTrackNulls(False).fit(batch)
+    assert m.fillValues == [3.0, 2.0, 0.0]
+    assert m.transform(batch).vectors[out.name].to_numpy().tolist() == [[4, 2, 0], [3, 2, 0], [2, 2, 0]]
+    m = vec.setFillWithConstant(4.2).setTrackNulls(False).fit(batch)
+    assert m.transform(batch).vectors[out.name].to_numpy().tolist() == [[4, 2, 4.2], [4.2, 2, 4.2], [2, 4.2, 4.2]]
+    m = vec.setFillWithMean().setTrackNulls(True).fit(batch)
+    assert m.transform(batch).vectors[out.name].to_numpy().tolist() == \
+        [[4, 0, 2, 0, 0, 1], [3, 1, 2, 0, 0, 1], [2, 0, 2, 1, 0, 1]]
+    meta = m.getMetadata()
+    assert [(c.grouping, c.indicatorValue) for c in meta.columns] == \
+        [(None, None), ("inA", "NullIndicatorValue"), (None, None), ("inB", "NullIndicatorValue"), (None, None),
+         ("inC", "NullIndicatorValue")]
+    assert meta.columnNames()[1] == "inA_inA_NullIndicatorValue_1"
+
+
+def test_binary_and_realnn_stages():
+    # BinaryVectorizerTest.scala:45-70, RealNNVectorizerTest.scala:45
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.numeric import BinaryVectorizer, RealNNVectorizer
+    f1 = [False, False, True, True, None, None, False, True, None]
+    f2 = [False, True, False, True, False, True, None, None, None]
+    batch = _batch({"f1": (F.BINARY, f1), "f2": (F.BINARY, f2), "r": (F.REALNN, [float(i) for i in range(9)])})
+    st = BinaryVectorizer().setInput(F.FeatureBuilder.Binary("f1").asPredictor(),
+                                     F.FeatureBuilder.Binary("f2").asPredictor())
+    got = st.transform(batch).vectors[st.getOutput().name].to_numpy()
+    assert np.array_equal(got, V.binary_vectorizer_transform([f1, f2]))
+    assert [c.indicatorValue for c in st.getMetadata().columns] == [None, "NullIndicatorValue"] * 2
+    rn = RealNNVectorizer().setInput(F.FeatureBuilder.RealNN("r").asPredictor())
+    assert rn.transform(batch).vectors[rn.getOutput().name].to_numpy()[:, 0].tolist() == [float(i) for i in range(9)]
+    with pytest.raises(ValueError):
+        _batch({"r": (F.REALNN, [1.0, None])})
+
+
+SC_ROWS = [(32, 5.0, 0, 1, 0.5, 0), (32, 4.0, 1, 0, 0, 0.1), (32, 6.0, 1, 1, 0.5, 0), (32, 5.5, 0, 1, 0.5, 0),
+           (32, 5.4, 1, 0, 0, 0.1), (32, 5.4, 1, 0, 0, 0.1)]
+SC_NAMES = ["age", "height", "height_null", "gender", "testFeatNegCor"]
+
+
+def _sc_batch():
+    """SanityCheckerTest.scala:100-128: a hand-made OPVector column with metadata but no statistics sidecar."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch, DensePart, NumericBlock, VectorColumn
+    from transmogrifai_b200.metadata import OpVectorColumnMetadata, OpVectorMetadata
+    x = np.array([[r[0], r[1], r[2], r[4], r[5]] for r in SC_ROWS], dtype=np.float64)
+    y = [float(r[3]) for r in SC_ROWS]
+    blk = NumericBlock.from_lists(["isBlueEye"], F.REALNN, [y])
+    meta = OpVectorMetadata("features", [OpVectorColumnMetadata((n,), (F.REAL,)) for n in SC_NAMES])
+    vec = VectorColumn("features", 6, meta, [DensePart(torch.from_numpy(x).cuda())])
+    batch = ColumnarBatch(6, [blk], {"features": vec}, response="isBlueEye")
+    label = F.Feature("isBlueEye", F.REALNN, True)
+    fv = F.Feature("features", F.OPVECTOR, False)
+    return batch, label, fv, x, y
+
+
+def test_sanity_checker_reference_drop_set():
+    # SanityCheckerTest.scala:133-164
+    batch, label, fv, x, y = _sc_batch()
+    checked = label.sanityCheck(fv, maxCorrelation=0.99, minVariance=0.0, checkSample=1.0, removeBadFeatures=True,
+                                sampleLowerLimit=0)
+    est = checked.origin_stage
+    model = est.fit(batch)
+    assert est.summary.dropped == ["age_0", "gender_3", "testFeatNegCor_4"]
+    assert model.indicesToKeep == [1, 2]
+    corr = dict(zip(est.summary.names, est.summary.correlationsWithLabel))
+    assert math.isnan(corr["age_0"]) and not any(math.isnan(corr[k]) for k in
+                                                 ("height_1", "height_null_2", "gender_3", "testFeatNegCor_4"))
+    assert est.summary.max[-1] == 1.0 and est.summary.mean[-1] == 0.5        # :659-660
+    out = model.transform(batch).vectors[checked.name]
+    assert np.array_equal(out.to_numpy(), x[:, [1, 2]])
+    assert out.metadata.columnNames() == ["height_0", "height_null_1"]
+    # oracle agreement on every statistic
+    metas = [ColumnMeta((n,), ("Real",), index=i) for i, n in enumerate(SC_NAMES)]
+    p = S.SanityParams(max_correlation=0.99, min_variance=0.0, remove_bad_features=True, sample_lower_limit=0)
+    ref = S.sanity_fit(y, x, metas, p)
+    np.testing.assert_allclose(est.summary.mean[:-1], ref.col_stats.mean[:-1], rtol=1e-12)
+    np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+    np.testing.assert_allclose(est.summary.featureFeatureCorr, ref.corr_matrix, rtol=1e-9, atol=1e-12, equal_nan=True)
+
+
+def test_sanity_checker_feature_feature_and_errors():
+    # SanityCheckerTest.scala:473-500 (later duplicate dropped), :349-357 (everything dropped -> error)
+    batch, label, fv, x, y = _sc_batch()
+    est = label.sanityCheck(fv, maxCorrelation=1.1, minVariance=-0.1, removeBadFeatures=True,
+                            removeFeatureGroup=False, sampleLowerLimit=0).origin_stage
+    est.setMinCorrelation(-0.1).setMaxFeatureCorrelation(0.9).setMaxCramersV(1.0).setCorrelationExclusion("HashedText")
+    est.fit(batch)
+    assert est.summary.dropped == ["testFeatNegCor_4"]
+    est.setFeatureFeatureCorrLevel("Off").fit(batch)
+    assert est.summary.dropped == []
+    bad = label.sanityCheck(fv, minVariance=1e9, removeBadFeatures=True, sampleLowerLimit=0).origin_stage
+    with pytest.raises(ValueError, match="dropped all of your features"):
+        bad.fit(batch)
+    from transmogrifai_b200.stages.sanity import SanityChecker
+    for v in (-1.0, 0.0, 2.0):                                              # :166-171
+        with pytest.raises(ValueError):
+            SanityChecker().setCheckSample(v)
+
+
+@pytest.mark.parametrize("device", [None, "cuda"])
+@pytest.mark.parametrize("n,ncols,corr_level", [(3000, 14, "Off"), (2500, 20, "Computed")])
+def test_transmogrify_sanity_check_real_matches_oracle(device, n, ncols, corr_level):
+    """Config-2 shape at oracle size: transmogrify(Real columns) + sanityCheck(removeBadFeatures) -- fused sidecar
+    path -- against oracle.sanity_fit on the oracle's own vectorized matrix."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+    x, valid, y = make_real_config(n, ncols, seed=77)
+    cols = _lists(x, valid)
+    names = [f"c{j:03d}" for j in range(ncols)]
+    data = {nm: (F.REAL, c) for nm, c in zip(names, cols)}
+    data["y"] = (F.REALNN, y.tolist())
+    batch = _batch(data, response="y", device=device)
+    feats = [F.FeatureBuilder.Real(nm).asPredictor() for nm in names]
+    label = F.FeatureBuilder.RealNN("y").asResponse()
+    vec = transmogrify(feats)
+    checked = label.sanityCheck(vec, removeBadFeatures=True, sampleLowerLimit=0, sampleUpperLimit=10 ** 9,
+                                featureFeatureCorrLevel=corr_level)
+    out_batch, fitted = fit_and_transform(batch, checked)
+    est = checked.origin_stage
+    # oracle
+    fills = V.real_vectorizer_fit(cols)
+    xo = V.real_vectorizer_transform(cols, fills, True)
+    metas = V.numeric_metadata(names, "Real", True)
+    p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                       feature_feature_corr_level=corr_level.lower())
+    ref = S.sanity_fit(y, xo, metas, p, label_name="y")
+    assert est.summary.dropped == ref.dropped                                  # removed-feature set: bit-exact
+    assert fitted[-1].indicesToKeep == ref.indices_to_keep
+    np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+    assert np.array_equal(est.summary.min, ref.col_stats.min) and np.array_equal(est.summary.max, ref.col_stats.max)
+    np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                               equal_nan=True)                                 # north_star: corr within 1e-9
+    got_v = {g.group: g.cramersV for g in est.summary.categoricalStats}
+    ref_v = {g.group: g.cramers_v for g in ref.cat_stats}
+    assert got_v.keys() == ref_v.keys()
+    for k in ref_v:
+        np.testing.assert_allclose(got_v[k], ref_v[k], rtol=1e-9, equal_nan=True)   # Cramer's V within 1e-9
+    got = out_batch.vectors[checked.name].to_numpy()
+    np.testing.assert_allclose(got, xo[:, ref.indices_to_keep], rtol=1e-12)
+    assert out_batch.vectors[checked.name].metadata.columnNames() == \
+        [f"{m.col_name().rsplit('_', 1)[0]}_{i}" for i, m in enumerate(metas[j] for j in ref.indices_to_keep)]

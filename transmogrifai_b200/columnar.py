@@ -1,0 +1,224 @@
+"""Columnar batches: the form in which Spark DataFrame partitions reach the library (SURVEY.md 8b "data at the
+boundary") -- Arrow-style column blocks in pinned host memory or, once uploaded, in HBM.
+
+* numeric block : several same-typed columns stored column-major, values [ncols, ld] (f64 for Real/RealNN, u8 for
+                  Binary), validity bitmaps [ncols, ldv] (bit r%64 of 64-bit word r/64, 1 = present) or None
+* vector column : an OPVector -- ordered parts (dense row-major blocks and CSR blocks) plus OpVectorMetadata, and an
+                  optional statistics sidecar filled by the fused vectorizer scans (see stages/sanity.py)
+
+torch tensors are the storage (CPU pinned or CUDA): plumbing only, every computation goes through libtmog_b200.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import features as F
+from .metadata import OpVectorMetadata
+
+
+def round_up(v: int, m: int) -> int:
+    return (v + m - 1) // m * m
+
+
+def pack_validity(valid: np.ndarray) -> np.ndarray:
+    """bool [ncols, n] -> bitmap words [ncols, ceil(n/64)] as int64 (bit pattern of uint64)."""
+    ncols, n = valid.shape
+    nw = max((n + 63) // 64, 1)
+    padded = np.zeros((ncols, nw * 64), dtype=np.uint8)
+    padded[:, :n] = valid
+    bits = np.packbits(padded.reshape(ncols, nw, 64), axis=2, bitorder="little")
+    return bits.reshape(ncols, nw * 8).view("<i8").reshape(ncols, nw).copy()
+
+
+def _pin(t: torch.Tensor) -> torch.Tensor:
+    if t.is_cuda or not torch.cuda.is_available():
+        return t
+    try:
+        return t.pin_memory()
+    except RuntimeError:
+        return t
+
+
+@dataclass
+class NumericBlock:
+    names: List[str]
+    type_name: str
+    values: torch.Tensor                 # [ncols, ld] float64 (Real, RealNN) or uint8 (Binary)
+    valid: Optional[torch.Tensor]        # [ncols, ldv] int64 bitmap words, or None (no nulls)
+    n: int
+
+    @property
+    def is_cuda(self) -> bool:
+        return self.values.is_cuda
+
+    @property
+    def ld(self) -> int:
+        return self.values.shape[1]
+
+    @property
+    def ldv(self) -> int:
+        return 0 if self.valid is None else self.valid.shape[1]
+
+    def rows(self, idx: Sequence[int]) -> "NumericBlock":
+        """Sub-block of the given columns: a view when they are a contiguous run, else a gathered copy."""
+        idx = list(idx)
+        if idx == list(range(idx[0], idx[0] + len(idx))):
+            v = self.values[idx[0]:idx[0] + len(idx)]
+            m = None if self.valid is None else self.valid[idx[0]:idx[0] + len(idx)]
+        else:
+            sel = torch.as_tensor(idx, device=self.values.device)
+            v = self.values.index_select(0, sel)
+            m = None if self.valid is None else self.valid.index_select(0, sel)
+        return NumericBlock([self.names[i] for i in idx], self.type_name, v, m, self.n)
+
+    def to(self, device) -> "NumericBlock":
+        return NumericBlock(self.names, self.type_name, self.values.to(device, non_blocking=True),
+                            None if self.valid is None else self.valid.to(device, non_blocking=True), self.n)
+
+    @staticmethod
+    def from_lists(names: Sequence[str], type_name: str, columns: Sequence[Sequence], pin: bool = True
+                   ) -> "NumericBlock":
+        n = len(columns[0]) if columns else 0
+        binary = type_name == F.BINARY
+        ld = round_up(max(n, 1), 16 if binary else 2)
+        vals = np.zeros((len(columns), ld), dtype=np.uint8 if binary else np.float64)
+        ok = np.zeros((len(columns), n), dtype=bool)
+        for j, col in enumerate(columns):
+            if len(col) != n:
+                raise ValueError("columns of one batch must have the same length")
+            for i, v in enumerate(col):
+                if v is not None:
+                    ok[j, i] = True
+                    vals[j, i] = (1 if v else 0) if binary else float(v)
+        if type_name == F.REALNN and not ok.all():
+            raise ValueError("None.get: a RealNN feature holds a null")   # RealNNVectorizer.scala:53
+        valid = None if ok.all() else torch.from_numpy(pack_validity(ok))
+        v = torch.from_numpy(vals)
+        if pin:
+            v, valid = _pin(v), (None if valid is None else _pin(valid))
+        return NumericBlock(list(names), type_name, v, valid, n)
+
+
+@dataclass
+class DensePart:
+    data: torch.Tensor                   # [n, width] float64 row-major (may be a column slice of a wider block)
+
+    @property
+    def width(self) -> int:
+        return self.data.shape[1]
+
+    def to_scipy(self):
+        import scipy.sparse as sp
+        return sp.csr_matrix(self.data.cpu().numpy())
+
+
+@dataclass
+class CsrPart:
+    indptr: torch.Tensor                 # [n+1] int64
+    indices: torch.Tensor                # [nnz] int32, sorted per row, local to this part
+    values: torch.Tensor                 # [nnz] float64
+    width: int
+
+    def to_scipy(self):
+        import scipy.sparse as sp
+        n = self.indptr.shape[0] - 1
+        m = sp.csr_matrix((self.values.cpu().numpy(), self.indices.cpu().numpy().astype(np.int64),
+                           self.indptr.cpu().numpy()), shape=(n, self.width))
+        m.eliminate_zeros()
+        return m
+
+
+@dataclass
+class VectorColumn:
+    name: str
+    n: int
+    metadata: OpVectorMetadata
+    parts: List[object]                  # DensePart | CsrPart, in output-column order
+    stats: Optional[object] = None       # stages.sanity.VectorStats sidecar
+
+    @property
+    def width(self) -> int:
+        return sum(p.width for p in self.parts)
+
+    def to_scipy(self):
+        import scipy.sparse as sp
+        if not self.parts:
+            return sp.csr_matrix((self.n, 0))
+        return sp.hstack([p.to_scipy() for p in self.parts], format="csr")
+
+    def to_numpy(self) -> np.ndarray:
+        return np.asarray(self.to_scipy().todense())
+
+
+@dataclass
+class ColumnarBatch:
+    n: int
+    blocks: List[NumericBlock] = field(default_factory=list)
+    vectors: Dict[str, VectorColumn] = field(default_factory=dict)
+    response: Optional[str] = None       # name of the response (label) column, a RealNN
+
+    def find(self, name: str) -> Tuple[NumericBlock, int]:
+        for b in self.blocks:
+            if name in b.names:
+                return b, b.names.index(name)
+        raise KeyError(f"no column named {name!r} in the batch")
+
+    def has(self, name: str) -> bool:
+        return name in self.vectors or any(name in b.names for b in self.blocks)
+
+    def numeric(self, names: Sequence[str]) -> NumericBlock:
+        """The block holding exactly these columns, in this order (zero-copy when they are a run of one block)."""
+        located = [self.find(nm) for nm in names]
+        first = located[0][0]
+        if all(b is first for b, _ in located):
+            return first.rows([i for _, i in located])
+        subs = [b.rows([i]) for b, i in located]
+        ld = max(s.ld for s in subs)
+        if any(s.ld != ld or s.type_name != subs[0].type_name for s in subs):
+            raise ValueError("columns of different layouts cannot form one block")
+        vals = torch.cat([s.values for s in subs], dim=0)
+        valid = None
+        if any(s.valid is not None for s in subs):
+            full = torch.full((1, (self.n + 63) // 64 or 1), -1, dtype=torch.int64, device=vals.device)
+            valid = torch.cat([s.valid if s.valid is not None else full for s in subs], dim=0)
+        return NumericBlock(list(names), subs[0].type_name, vals, valid, self.n)
+
+    def label(self, name: Optional[str] = None) -> torch.Tensor:
+        nm = name or self.response
+        if nm is None:
+            raise KeyError("the batch has no response column")
+        b, i = self.find(nm)
+        if b.type_name != F.REALNN or b.valid is not None:
+            raise ValueError("Sanity checker input missing label for row")   # SanityChecker.scala:391-393
+        return b.values[i]
+
+    def with_vector(self, v: VectorColumn) -> "ColumnarBatch":
+        out = ColumnarBatch(self.n, self.blocks, dict(self.vectors), self.response)
+        out.vectors[v.name] = v
+        return out
+
+    def to(self, device) -> "ColumnarBatch":
+        return ColumnarBatch(self.n, [b.to(device) for b in self.blocks], dict(self.vectors), self.response)
+
+    @staticmethod
+    def from_columns(columns: Dict[str, Tuple[str, Sequence]], response: Optional[str] = None, pin: bool = True
+                     ) -> "ColumnarBatch":
+        """{name: (type_name, python values with None for null)} -> one block per numeric type, in first-seen order
+        (the TestFeatureBuilder of this package)."""
+        n = None
+        groups: Dict[str, List[str]] = {}
+        for name, (tp, vals) in columns.items():
+            if n is None:
+                n = len(vals)
+            groups.setdefault(tp, []).append(name)
+        blocks = []
+        for tp, names in groups.items():
+            if tp in F.NUMERIC_TYPES:
+                blocks.append(NumericBlock.from_lists(names, tp, [columns[nm][1] for nm in names], pin))
+            else:
+                raise NotImplementedError(f"columns of type {tp} are not supported yet")
+        return ColumnarBatch(n or 0, blocks, {}, response)

@@ -1,0 +1,286 @@
+// SanityChecker over an already materialised dense OPVector block (row-major f64): column moments + label
+// covariance + per-label-class column sums, the full Gramian for CorrelationLevel.Computed, and the indicesToKeep
+// gather of SanityCheckerModel.  These serve vectors that did not come out of the fused vectorizer scans.
+#include <math.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+namespace tmog {
+
+constexpr int NS = TMOG_REAL_NSTAT;
+constexpr int DS_ROWS_PER_CTA = 4096;
+constexpr int PILOT_ROWS = 4096;
+
+// grid (ceil(D/32), row chunks); block (32 columns, 8 row lanes).  Column D-1 == d is the label.
+__global__ void __launch_bounds__(256)
+dense_pilot_kernel(const double* __restrict__ x, int64_t ld, int64_t n, int d, const double* __restrict__ label,
+                   double* __restrict__ shifts) {
+    __shared__ double red[8][33];
+    const int c = blockIdx.x * 32 + threadIdx.x;
+    const int rows = (int)min((int64_t)PILOT_ROWS, n);
+    double s = 0.0;
+    if (c <= d)
+        for (int r = threadIdx.y; r < rows; r += 8) {
+            const double v = c == d ? label[r] : x[(int64_t)r * ld + c];
+            s += isfinite(v) ? v : 0.0;
+        }
+    red[threadIdx.y][threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.y == 0 && c <= d) {
+        double t = 0.0;
+        for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
+        shifts[c] = rows > 0 ? t / rows : 0.0;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+dense_stats_kernel(const double* __restrict__ x, int64_t ld, int64_t n, int d, const double* __restrict__ label,
+                   const uint8_t* __restrict__ class_ids, int nclasses, const uint8_t* __restrict__ cat_mask,
+                   const double* __restrict__ shifts, double* __restrict__ scratch, double* __restrict__ class_sums) {
+    extern __shared__ double sm[];
+    double* red = sm;                    // [8][32][6]
+    double* cs = sm + 8 * 32 * 6;        // [nclasses][32] (only when class sums are requested)
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    const int c = blockIdx.x * 32 + tx;
+    const bool is_label = c == d;
+    const bool active = c <= d;
+    const bool track = class_sums != nullptr && active && !is_label && cat_mask != nullptr && cat_mask[c] != 0;
+    if (class_sums != nullptr)
+        for (int i = ty * 32 + tx; i < nclasses * 32; i += 256) cs[i] = 0.0;
+    __syncthreads();
+    const int64_t r0 = (int64_t)blockIdx.y * DS_ROWS_PER_CTA;
+    const int64_t r1 = min(n, r0 + DS_ROWS_PER_CTA);
+    const double s = active ? shifts[c] : 0.0;
+    const double sy = shifts[d];
+    double sd = 0, sdd = 0, sde = 0, se = 0, mn = INFINITY, mx = -INFINITY;
+    if (active)
+        for (int64_t r = r0 + ty; r < r1; r += 8) {
+            const double y = label[r];
+            const double v = is_label ? y : x[r * ld + c];
+            const double dv = v - s, e = y - sy;
+            sd += dv;
+            sdd = fma(dv, dv, sdd);
+            sde = fma(dv, e, sde);
+            se += e;
+            mn = fmin(mn, v);
+            mx = fmax(mx, v);
+            if (track && v != 0.0) atomicAdd(&cs[class_ids[r] * 32 + tx], v);
+        }
+    double* q = red + (ty * 32 + tx) * 6;
+    q[0] = sd; q[1] = sdd; q[2] = sde; q[3] = se; q[4] = mn; q[5] = mx;
+    __syncthreads();
+    if (ty == 0 && active) {
+        for (int k = 1; k < 8; ++k) {
+            const double* p = red + (k * 32 + tx) * 6;
+            sd += p[0]; sdd += p[1]; sde += p[2]; se += p[3];
+            mn = fmin(mn, p[4]);
+            mx = fmax(mx, p[5]);
+        }
+        double* o = scratch + ((int64_t)blockIdx.y * (d + 1) + c) * NS;
+        o[0] = (double)(r1 - r0); o[1] = sd; o[2] = sdd; o[3] = sde; o[4] = se; o[5] = mn; o[6] = mx;
+        o[7] = (double)(r1 - r0);
+    }
+    if (class_sums != nullptr && c < d) {
+        for (int k = ty; k < nclasses; k += 8) {
+            const double v = cs[k * 32 + tx];
+            if (v != 0.0) atomicAdd(&class_sums[(int64_t)k * d + c], v);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(32)
+dense_reduce_kernel(const double* __restrict__ scratch, int nchunks, int D, double* __restrict__ partials) {
+    const int c = blockIdx.x, lane = threadIdx.x;
+    double s[5] = {0, 0, 0, 0, 0}, mn = INFINITY, mx = -INFINITY, rows = 0;
+    for (int b = lane; b < nchunks; b += 32) {
+        const double* q = scratch + ((int64_t)b * D + c) * NS;
+        for (int k = 0; k < 5; ++k) s[k] += q[k];
+        mn = fmin(mn, q[5]);
+        mx = fmax(mx, q[6]);
+        rows += q[7];
+    }
+    for (int k = 0; k < 5; ++k) s[k] = warp_sum(s[k]);
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    rows = warp_sum(rows);
+    if (lane == 0) {
+        double* o = partials + c * NS;
+        for (int k = 0; k < 5; ++k) o[k] = s[k];
+        o[5] = mn; o[6] = mx; o[7] = rows;
+    }
+}
+
+// out[r][j] = x[r][idx[j]]   (DerivedFeatureFilterUtils.removeFeatures on a dense vector)
+__global__ void __launch_bounds__(256)
+dense_gather_kernel(const double* __restrict__ x, int64_t ld, int64_t n, const int32_t* __restrict__ idx, int k,
+                    double* __restrict__ out, int64_t out_ld) {
+    const int64_t total = n * (int64_t)k;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const int64_t r = i / k;
+        const int j = (int)(i - r * k);
+        out[r * out_ld + j] = x[r * ld + idx[j]];
+    }
+}
+
+// G[i][j] += sum_r (x[r][i] - s_i)(x[r][j] - s_j), label as column d.  32x32 output tile per CTA over one row chunk
+// (grid.z), upper-triangular tiles only; 16x16 threads, 2x2 outputs each; fp64 atomics merge the row chunks.
+constexpr int GR_ROWS = 64;
+__global__ void __launch_bounds__(256)
+dense_gram_kernel(const double* __restrict__ x, int64_t ld, int64_t n, int d, const double* __restrict__ label,
+                  const double* __restrict__ shifts, int64_t rows_per_cta, double* __restrict__ G) {
+    const int ti = blockIdx.x, tj = blockIdx.y;
+    if (tj < ti) return;
+    __shared__ double A[GR_ROWS][33], B[GR_ROWS][33];
+    const int D = d + 1;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const int64_t r0 = (int64_t)blockIdx.z * rows_per_cta;
+    const int64_t r1 = min(n, r0 + rows_per_cta);
+    double acc[2][2] = {{0, 0}, {0, 0}};
+    for (int64_t rb = r0; rb < r1; rb += GR_ROWS) {
+        for (int i = threadIdx.x; i < GR_ROWS * 32; i += 256) {
+            const int rr = i >> 5, cc = i & 31;
+            const int64_t r = rb + rr;
+            const int ca = ti * 32 + cc, cb = tj * 32 + cc;
+            double va = 0.0, vb = 0.0;
+            if (r < r1) {
+                if (ca < D) va = (ca == d ? label[r] : x[r * ld + ca]) - shifts[ca];
+                if (cb < D) vb = (cb == d ? label[r] : x[r * ld + cb]) - shifts[cb];
+            }
+            A[rr][cc] = va;
+            B[rr][cc] = vb;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int rr = 0; rr < GR_ROWS; ++rr) {
+            const double a0 = A[rr][ty], a1 = A[rr][ty + 16];
+            const double b0 = B[rr][tx], b1 = B[rr][tx + 16];
+            acc[0][0] = fma(a0, b0, acc[0][0]);
+            acc[0][1] = fma(a0, b1, acc[0][1]);
+            acc[1][0] = fma(a1, b0, acc[1][0]);
+            acc[1][1] = fma(a1, b1, acc[1][1]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            const int i = ti * 32 + ty + 16 * a, j = tj * 32 + tx + 16 * b;
+            if (i < D && j < D) atomicAdd(&G[(int64_t)i * D + j], acc[a][b]);
+        }
+}
+
+}  // namespace tmog
+
+using namespace tmog;
+
+static int dense_chunks(int64_t n) { return (int)std::max<int64_t>(1, (n + DS_ROWS_PER_CTA - 1) / DS_ROWS_PER_CTA); }
+
+extern "C" int tmog_dense_stats_scratch_bytes(int64_t n, int d, size_t* bytes) {
+    TMOG_REQUIRE(n >= 0 && d >= 0 && bytes != nullptr, "bad arguments");
+    *bytes = sizeof(double) * (size_t)dense_chunks(n) * (size_t)(d + 1) * NS;
+    return TMOG_OK;
+}
+
+extern "C" int tmog_dense_pilot_shift_dev(const double* x, int64_t ld, int64_t n, int d, const double* label,
+                                          double* shifts, void* stream) {
+    TMOG_REQUIRE(n >= 0 && d >= 0 && ld >= d && shifts != nullptr, "bad arguments");
+    TMOG_REQUIRE(n == 0 || ((x != nullptr || d == 0) && label != nullptr), "NULL input");
+    dense_pilot_kernel<<<(d + 1 + 31) / 32, dim3(32, 8), 0, (cudaStream_t)stream>>>(x, ld, n, d, label, shifts);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_dense_stats_dev(const double* x, int64_t ld, int64_t n, int d, const double* label,
+                                    const uint8_t* class_ids, int nclasses, const uint8_t* cat_mask,
+                                    const double* shifts, void* scratch, size_t scratch_bytes, double* partials,
+                                    double* class_sums, void* stream) {
+    TMOG_REQUIRE(n >= 0 && d >= 0 && ld >= d, "bad shape n=%lld d=%d ld=%lld", (long long)n, d, (long long)ld);
+    TMOG_REQUIRE(n == 0 || ((x != nullptr || d == 0) && label != nullptr), "NULL input");
+    TMOG_REQUIRE(shifts != nullptr && partials != nullptr, "shifts / partials is NULL");
+    TMOG_REQUIRE(class_sums == nullptr || (class_ids != nullptr && nclasses >= 1 && nclasses <= 255),
+                 "class sums need class ids and 1..255 classes");
+    const int chunks = dense_chunks(n);
+    const size_t need = sizeof(double) * (size_t)chunks * (size_t)(d + 1) * NS;
+    if (scratch == nullptr || scratch_bytes < need) {
+        set_error("scratch too small: %zu bytes given, %zu needed (tmog_dense_stats_scratch_bytes)", scratch_bytes,
+                  need);
+        return TMOG_ENOMEM;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (class_sums) TMOG_CUDA(cudaMemsetAsync(class_sums, 0, sizeof(double) * (size_t)nclasses * d, st));
+    const size_t smem = sizeof(double) * (8 * 32 * 6 + (class_sums ? (size_t)nclasses * 32 : 0));
+    if (smem > 48 * 1024)
+        TMOG_CUDA(cudaFuncSetAttribute(dense_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((d + 1 + 31) / 32, chunks);
+    TMOG_REQUIRE(chunks <= 65535, "too many rows for one dense stats call (%lld): chunk the batch", (long long)n);
+    dense_stats_kernel<<<grid, dim3(32, 8), smem, st>>>(x, ld, n, d, label, class_ids, nclasses, cat_mask, shifts,
+                                                        static_cast<double*>(scratch), class_sums);
+    TMOG_LAUNCH_CHECK();
+    dense_reduce_kernel<<<d + 1, 32, 0, st>>>(static_cast<const double*>(scratch), n > 0 ? chunks : 0, d + 1,
+                                              partials);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_dense_gather_dev(const double* x, int64_t ld, int64_t n, const int32_t* idx, int k, double* out,
+                                     int64_t out_ld, void* stream) {
+    TMOG_REQUIRE(n >= 0 && k >= 0 && out_ld >= k, "bad shape");
+    if (n == 0 || k == 0) return TMOG_OK;
+    TMOG_REQUIRE(x != nullptr && idx != nullptr && out != nullptr, "NULL argument");
+    const int64_t total = n * (int64_t)k;
+    const int grid = (int)std::min<int64_t>((total + 255) / 256, (int64_t)sm_count() * 16);
+    dense_gather_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, ld, n, idx, k, out, out_ld);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_dense_gram_dev(const double* x, int64_t ld, int64_t n, int d, const double* label,
+                                   const double* shifts, double* gram, void* stream) {
+    TMOG_REQUIRE(n >= 0 && d >= 0 && ld >= d && shifts != nullptr && gram != nullptr, "bad arguments");
+    TMOG_REQUIRE(d + 1 <= 65535, "Argument with more than 65535 cols: %d", d + 1);   // Spark RowMatrix limit
+    if (n == 0) return TMOG_OK;
+    TMOG_REQUIRE((x != nullptr || d == 0) && label != nullptr, "NULL input");
+    const int tiles = (d + 1 + 31) / 32;
+    const int64_t want_ctas = (int64_t)sm_count() * 8;
+    int64_t zc = std::max<int64_t>(1, want_ctas / std::max(1, tiles * (tiles + 1) / 2));
+    int64_t rows_per = std::max<int64_t>(GR_ROWS, (n + zc - 1) / zc);
+    rows_per = (rows_per + GR_ROWS - 1) / GR_ROWS * GR_ROWS;
+    zc = (n + rows_per - 1) / rows_per;
+    TMOG_REQUIRE(zc <= 65535 && tiles <= 65535, "grid too large");
+    dense_gram_kernel<<<dim3(tiles, tiles, (unsigned)zc), 256, 0, (cudaStream_t)stream>>>(x, ld, n, d, label, shifts,
+                                                                                          rows_per, gram);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+// Spark PearsonCorrelation.computeCorrelationMatrixFromCovariance on top of RowMatrix.computeCovariance, from the
+// shifted Gramian G (upper triangle valid) and the shifted column sums: cov_ij = (G_ij - n delta_i delta_j)/(n-1)
+// with delta = sum_d / n; sigma := 0 where |cov_ii| <= 1e-12 -> NaN row/col; diagonal 1.0.
+extern "C" int tmog_pearson_from_gram(int D, double n, const double* gram, const double* sums, double* corr) {
+    TMOG_REQUIRE(D >= 0 && gram != nullptr && sums != nullptr && corr != nullptr, "NULL argument");
+    TMOG_REQUIRE(n > 1, "Cannot compute the covariance of a RowMatrix with <= 1 row.");
+    std::vector<double> sigma(D);
+    auto cov = [&](int i, int j) {
+        const int a = std::min(i, j), b = std::max(i, j);
+        return (gram[(size_t)a * D + b] - sums[a] * sums[b] / n) / (n - 1.0);
+    };
+    for (int i = 0; i < D; ++i) {
+        const double c = cov(i, i);
+        sigma[i] = fabs(c) <= 1e-12 ? 0.0 : sqrt(c);
+    }
+    for (int i = 0; i < D; ++i)
+        for (int j = 0; j < D; ++j) {
+            if (i == j)
+                corr[(size_t)i * D + j] = 1.0;
+            else if (sigma[i] == 0.0 || sigma[j] == 0.0)
+                corr[(size_t)i * D + j] = NAN;
+            else
+                corr[(size_t)i * D + j] = cov(i, j) / (sigma[i] * sigma[j]);
+        }
+    return TMOG_OK;
+}

@@ -1,0 +1,206 @@
+// SanityChecker driver-side finishing steps (host code inside the library; tiny inputs):
+//   contingency statistics (Cramer's V, mutual information, rule confidence / support) and the removeBadFeatures
+//   decision.  Reference file:line for each function is given in include/tmog_b200.h.
+#include <math.h>
+
+#include <algorithm>
+#include <map>
+#include <vector>
+
+#include "common.cuh"
+
+using namespace tmog;
+
+namespace {
+
+// OpStatistics.filterEmpties: drop all-zero rows, then all-zero columns.  m is rows x cols, row-major.
+void filter_empties(const double* m, int rows, int cols, std::vector<double>& out, int& orows, int& ocols) {
+    std::vector<int> keep_r, keep_c;
+    for (int i = 0; i < rows; ++i) {
+        double s = 0.0;
+        for (int j = 0; j < cols; ++j) s += m[i * cols + j];
+        if (s != 0.0) keep_r.push_back(i);
+    }
+    for (int j = 0; j < cols; ++j) {
+        double s = 0.0;
+        for (int i : keep_r) s += m[i * cols + j];
+        if (s != 0.0) keep_c.push_back(j);
+    }
+    orows = (int)keep_r.size();
+    ocols = (int)keep_c.size();
+    out.assign((size_t)orows * ocols, 0.0);
+    for (int a = 0; a < orows; ++a)
+        for (int b = 0; b < ocols; ++b) out[(size_t)a * ocols + b] = m[keep_r[a] * cols + keep_c[b]];
+}
+
+}  // namespace
+
+extern "C" int tmog_contingency_stats(const double* matrix, int rows, int cols, double* cramers_v, double* chi2,
+                                      double* mutual_info, double* pmi, double* max_conf, double* supports) {
+    TMOG_REQUIRE(rows >= 0 && cols >= 0 && (matrix != nullptr || rows * cols == 0), "bad arguments");
+    const double nan = NAN;
+    std::vector<double> f;
+    int fr = 0, fc = 0;
+    if (rows * cols > 0) filter_empties(matrix, rows, cols, f, fr, fc);
+    if (fr * fc == 0) {  // contingencyStats: "filteredMatrix.numActives <= 0" -> all NaN / empty
+        if (cramers_v) *cramers_v = nan;
+        if (chi2) *chi2 = nan;
+        if (mutual_info) *mutual_info = nan;
+        if (pmi)
+            for (int i = 0; i < rows * cols; ++i) pmi[i] = nan;
+        if (max_conf)
+            for (int i = 0; i < rows; ++i) max_conf[i] = nan;
+        if (supports)
+            for (int i = 0; i < rows; ++i) supports[i] = nan;
+        return 1;  // "empty": the reference returns empty maps / arrays here
+    }
+    // chi-squared on the filtered matrix (Spark ChiSqTest.chiSquaredMatrix, no continuity correction)
+    double v = nan, stat = nan;
+    if (fr > 1 && fc > 1) {
+        std::vector<double> rs(fr, 0.0), cs(fc, 0.0);
+        double total = 0.0;
+        for (int i = 0; i < fr; ++i)
+            for (int j = 0; j < fc; ++j) {
+                const double x = f[(size_t)i * fc + j];
+                rs[i] += x;
+                cs[j] += x;
+                total += x;
+            }
+        stat = 0.0;
+        for (int j = 0; j < fc; ++j)
+            for (int i = 0; i < fr; ++i) {
+                const double e = rs[i] * cs[j] / total;
+                const double dlt = f[(size_t)i * fc + j] - e;
+                stat += dlt * dlt / e;
+            }
+        const double phi2 = stat / total;
+        v = sqrt(phi2 / (double)std::min(fr - 1, fc - 1));
+    }
+    if (cramers_v) *cramers_v = v;
+    if (chi2) *chi2 = stat;
+    // mutual information and rule confidences on the UNFILTERED matrix (OpStatistics.scala:314-316)
+    std::vector<double> rs(rows, 0.0), cs(cols, 0.0);
+    double total = 0.0;
+    for (int i = 0; i < rows; ++i)
+        for (int j = 0; j < cols; ++j) {
+            const double x = matrix[i * cols + j];
+            rs[i] += x;
+            cs[j] += x;
+            total += x;
+        }
+    double mi = 0.0;
+    for (int j = 0; j < cols; ++j)
+        for (int i = 0; i < rows; ++i) {
+            const double x = matrix[i * cols + j];
+            double p = 0.0;
+            if (!(x == 0.0 || rs[i] == 0.0 || cs[j] == 0.0))
+                p = log(std::max(x, 1e-99) * total / (rs[i] * cs[j])) / log(2.0);
+            if (pmi) pmi[i * cols + j] = p;
+            mi += p * x / total;
+        }
+    if (mutual_info) *mutual_info = mi;
+    for (int i = 0; i < rows; ++i) {
+        if (supports) supports[i] = rs[i] / total;
+        if (max_conf) {
+            double mx = matrix[i * cols];
+            for (int j = 1; j < cols; ++j) mx = std::max(mx, matrix[i * cols + j]);
+            max_conf[i] = rs[i] == 0.0 ? 0.0 : mx / rs[i];
+        }
+    }
+    return TMOG_OK;
+}
+
+extern "C" int tmog_sanity_decide(int d, const double* variance, const double* corr_label, const double* corr_matrix,
+                                  int corr_dim, const int32_t* corr_pos, const int32_t* parent_offsets,
+                                  const int32_t* parent_ids, const int32_t* group_id, const uint8_t* text_shared_hash,
+                                  const double* cramers_v, const int32_t* rule_count, const double* rule_conf,
+                                  const double* rule_support, const double* params, uint8_t* drop,
+                                  uint32_t* reasons, double* parent_corr_out, double* parent_cramers_out) {
+    TMOG_REQUIRE(d >= 0 && variance && corr_pos && parent_offsets && parent_ids && group_id && text_shared_hash &&
+                     cramers_v && rule_count && rule_conf && rule_support && params && drop,
+                 "NULL argument");
+    TMOG_REQUIRE(corr_matrix == nullptr || corr_dim > 0, "corr_dim must be positive with a correlation matrix");
+    const double min_variance = params[0], min_corr = params[1], max_corr = params[2], max_feature_corr = params[3],
+                 max_cramers = params[4], max_rule_conf = params[5], min_rule_support = params[6];
+    const bool remove_feature_group = params[7] != 0.0, protect_text_shared_hash = params[8] != 0.0;
+
+    // makeColumnStatistics: max |corr| and max Cramer's V per parent feature, NaNs skipped, folded from 0.0
+    std::map<int, double> corr_parent, cramers_parent;
+    for (int i = 0; i < d; ++i) {
+        if (corr_pos[i] >= 0 && corr_label) {
+            const double c = corr_label[corr_pos[i]];
+            for (int k = parent_offsets[i]; k < parent_offsets[i + 1]; ++k) {
+                double& slot = corr_parent.emplace(parent_ids[k], 0.0).first->second;
+                if (!isnan(c)) slot = std::max(slot, fabs(c));
+            }
+        }
+        // a column is in cramersVMap iff it belongs to a categorical group (rule_count >= 0); its V may be NaN.
+        // parentMap (.toMap) keeps the LAST parent of a multi-parent column.
+        if (rule_count[i] >= 0 && parent_offsets[i + 1] > parent_offsets[i]) {
+            const int last = parent_ids[parent_offsets[i + 1] - 1];
+            double& slot = cramers_parent.emplace(last, 0.0).first->second;
+            if (!isnan(cramers_v[i])) slot = std::max(slot, fabs(cramers_v[i]));
+        }
+    }
+    // getFeaturesToDrop: groups flagged by the association-rule check
+    std::vector<int> flagged_groups;
+    for (int i = 0; i < d; ++i) {
+        if (group_id[i] < 0) continue;
+        for (int k = 0; k < std::max(rule_count[i], 0); ++k)
+            if (rule_conf[2 * i + k] > max_rule_conf && rule_support[2 * i + k] > min_rule_support) {
+                flagged_groups.push_back(group_id[i]);
+                break;
+            }
+    }
+    for (int i = 0; i < d; ++i) {
+        uint32_t r = 0;
+        if (variance[i] <= min_variance) r |= 1u;
+        const bool has_corr = corr_pos[i] >= 0 && corr_label != nullptr;
+        const double c = has_corr ? corr_label[corr_pos[i]] : nan("");
+        if (has_corr && fabs(c) < min_corr) r |= 2u;
+        if (has_corr && fabs(c) > max_corr) r |= 4u;
+        if (corr_matrix && corr_pos[i] >= 0) {
+            // featureCorrs = column corr_pos[i] of the matrix without the label row; .take(index) -- index i itself
+            const int lim = std::min(i, corr_dim - 1);
+            for (int k = 0; k < lim; ++k)
+                if (fabs(corr_matrix[(size_t)k * corr_dim + corr_pos[i]]) > max_feature_corr) {
+                    r |= 8u;
+                    break;
+                }
+        }
+        if (rule_count[i] >= 0 && cramers_v[i] > max_cramers) r |= 16u;
+        for (int k = 0; k < std::max(rule_count[i], 0); ++k)
+            if (rule_conf[2 * i + k] > max_rule_conf && rule_support[2 * i + k] > min_rule_support) {
+                r |= 32u;
+                break;
+            }
+        if (group_id[i] >= 0 &&
+            std::find(flagged_groups.begin(), flagged_groups.end(), group_id[i]) != flagged_groups.end())
+            r |= 64u;
+        // parent-level values: max over the column's parents that have an entry
+        double pc = nan(""), pv = nan("");
+        for (int k = parent_offsets[i]; k < parent_offsets[i + 1]; ++k) {
+            auto a = corr_parent.find(parent_ids[k]);
+            if (a != corr_parent.end()) pc = isnan(pc) ? a->second : std::max(pc, a->second);
+            auto b = cramers_parent.find(parent_ids[k]);
+            if (b != cramers_parent.end()) pv = isnan(pv) ? b->second : std::max(pv, b->second);
+        }
+        if (parent_corr_out) parent_corr_out[i] = pc;
+        if (parent_cramers_out) parent_cramers_out[i] = pv;
+        if (remove_feature_group && (!text_shared_hash[i] || !protect_text_shared_hash)) {
+            if (!isnan(pv) && pv > max_cramers) r |= 128u;
+            if (!isnan(pc) && pc > max_corr) r |= 256u;
+        }
+        drop[i] = r != 0;
+        if (reasons) reasons[i] = r;
+    }
+    return TMOG_OK;
+}
+
+extern "C" int tmog_pearson_from_cov(int d, double n, const double* cov_label, const double* variance,
+                                     double label_variance, double* corr) {
+    TMOG_REQUIRE(d >= 0 && cov_label && variance && corr, "NULL argument");
+    const double sy = sqrt(label_variance);
+    for (int i = 0; i < d; ++i) corr[i] = cov_label[i] / (sqrt(variance[i]) * sy * (n - 1.0));  // 0/0 -> NaN kept
+    return TMOG_OK;
+}

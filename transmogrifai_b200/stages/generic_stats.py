@@ -1,0 +1,117 @@
+"""SanityChecker kernels over an already materialised OPVector (dense parts): used when the input vector carries no
+statistics sidecar (it was not produced by the fused vectorizer scans), for CorrelationLevel.Computed, and for the
+model's indicesToKeep gather."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from .. import _lib as L
+from .. import runtime as R
+from ..columnar import ColumnarBatch, CsrPart, DensePart, VectorColumn
+from ..stats import LabelInfo, VectorStats
+from .numeric import label_info_dev
+
+
+def _device_label(batch: ColumnarBatch, label_name: str) -> torch.Tensor:
+    cache = batch.__dict__.setdefault("_label_dev", {})
+    if label_name not in cache:
+        y = batch.label(label_name)[:batch.n]
+        cache[label_name] = y if y.is_cuda else y.cuda()
+    return cache[label_name]
+
+
+def _dense_block(vec: VectorColumn) -> torch.Tensor:
+    """All parts as one device row-major block (a copy only when there are several parts or host data)."""
+    for p in vec.parts:
+        if not isinstance(p, DensePart):
+            raise NotImplementedError("this operation needs a dense OPVector (sparse parts are handled by the fused "
+                                      "scans; set featureFeatureCorrLevel = Off for hashed / pivoted vectors)")
+    blocks = [p.data if p.data.is_cuda else p.data.cuda() for p in vec.parts]
+    return blocks[0] if len(blocks) == 1 else torch.cat(blocks, dim=1)
+
+
+def vector_stats(batch: ColumnarBatch, vec: VectorColumn, label_name: str) -> VectorStats:
+    R.require_cuda()
+    x = _dense_block(vec)
+    n, d = x.shape
+    y = _device_label(batch, label_name)
+    classes, counts, ids = label_info_dev(batch, y, label_name)
+    cat = np.array([c.grouping is not None and c.indicatorValue is not None for c in vec.metadata.columns],
+                   dtype=np.uint8)
+    d_cat = torch.from_numpy(cat).cuda()
+    nb = C.c_size_t()
+    L.call("tmog_dense_stats_scratch_bytes", n, d, C.byref(nb))
+    scratch = R.scratch("dense_stats", nb.value)
+    shifts = torch.zeros(d + 1, dtype=torch.float64, device="cuda")
+    partials = torch.zeros((d + 1) * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
+    ncls = 0 if classes is None else len(classes)
+    class_sums = torch.zeros((max(ncls, 1), d), dtype=torch.float64, device="cuda") if ncls else None
+    L.call("tmog_dense_pilot_shift_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), shifts.data_ptr(), R.stream())
+    L.call("tmog_dense_stats_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), ids.data_ptr() if ncls else None,
+           ncls, d_cat.data_ptr(), shifts.data_ptr(), scratch.data_ptr(), scratch.numel(), partials.data_ptr(),
+           R.ptr(class_sums), R.stream())
+    p = partials.cpu().numpy()
+    s = shifts.cpu().numpy()
+    mean, var, mn, mx, cov = (np.zeros(d) for _ in range(5))
+    lab = np.zeros(5)
+    L.call("tmog_real_finish", p.ctypes.data, s.ctypes.data, d, 1, 0.0, 0, None, mean.ctypes.data, var.ctypes.data,
+           mn.ctypes.data, mx.ctypes.data, cov.ctypes.data, lab.ctypes.data, None)
+    cs = None
+    if ncls:
+        cs = class_sums.cpu().numpy()
+        cs[:, cat == 0] = np.nan
+    st = VectorStats(LabelInfo(label_name, n, lab, classes, counts), mean, var, mn, mx, cov, cs)
+    st._shifted_sums = (s, p.reshape(d + 1, L.REAL_NSTAT)[:, 1].copy())
+    return st
+
+
+def pearson_matrix(batch: ColumnarBatch, vec: VectorColumn, label_name: str, corr_indices: Sequence[int],
+                   st: Optional[VectorStats]) -> np.ndarray:
+    """Statistics.corr(vectorRowsForCorr, "pearson") over the selected columns + label (SanityChecker.scala:467-470)."""
+    R.require_cuda()
+    x = _dense_block(vec)
+    n, d_all = x.shape
+    feat = [i for i in corr_indices if i < d_all]
+    if len(feat) + 1 > 65535:
+        raise ValueError(f"requirement failed: Argument with more than 65535 cols: {len(feat) + 1}")
+    if feat != list(range(d_all)):
+        idx = torch.tensor(feat, dtype=torch.int32, device="cuda")
+        sub = torch.empty((n, len(feat)), dtype=torch.float64, device="cuda")
+        L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), n, idx.data_ptr(), len(feat), sub.data_ptr(),
+               len(feat), R.stream())
+        x = sub
+    d = x.shape[1]
+    y = _device_label(batch, label_name)
+    D = d + 1
+    shifts = torch.zeros(D, dtype=torch.float64, device="cuda")
+    L.call("tmog_dense_pilot_shift_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), shifts.data_ptr(), R.stream())
+    nb = C.c_size_t()
+    L.call("tmog_dense_stats_scratch_bytes", n, d, C.byref(nb))
+    scratch = R.scratch("dense_stats", nb.value)
+    partials = torch.zeros(D * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
+    L.call("tmog_dense_stats_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), None, 0, None, shifts.data_ptr(),
+           scratch.data_ptr(), scratch.numel(), partials.data_ptr(), None, R.stream())
+    gram = torch.zeros((D, D), dtype=torch.float64, device="cuda")
+    L.call("tmog_dense_gram_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), shifts.data_ptr(), gram.data_ptr(),
+           R.stream())
+    g = gram.cpu().numpy()
+    sums = np.ascontiguousarray(partials.cpu().numpy().reshape(D, L.REAL_NSTAT)[:, 1])
+    corr = np.zeros((D, D))
+    L.call("tmog_pearson_from_gram", D, float(n), g.ctypes.data, sums.ctypes.data, corr.ctypes.data)
+    return corr
+
+
+def select_columns(vec: VectorColumn, keep: List[int]) -> list:
+    """removeFeatures: the kept columns, in order (DerivedFeatureFilterUtils.scala:291-305)."""
+    R.require_cuda()
+    x = _dense_block(vec)
+    n = x.shape[0]
+    idx = torch.tensor(keep, dtype=torch.int32, device="cuda")
+    out = torch.empty((n, len(keep)), dtype=torch.float64, device="cuda")
+    L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), n, idx.data_ptr(), len(keep), out.data_ptr(),
+           max(len(keep), 1), R.stream())
+    return [DensePart(out)]
