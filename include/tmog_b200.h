@@ -105,6 +105,17 @@ int tmog_binary_transform_dev(const uint8_t* values, int64_t ld, const uint64_t*
                               int ncols, int fill_value, int track_nulls, double* out, int64_t out_ld,
                               int64_t out_col0, void* stream);
 
+/* The two transforms above fused with SanityCheckerModel.transformFn -> removeFeatures
+ * (C/stages/impl/preparators/DerivedFeatureFilterUtils.scala:291-305): out_pos [ncols * (track_nulls ? 2 : 1)] (device)
+ * gives, for every column the vectorizer would emit, its position in the output row (any layout: the kept columns
+ * of the combined vector), or -1 when SanityChecker dropped it.  The dropped columns are never written. */
+int tmog_real_transform_select_dev(const double* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n,
+                                   int ncols, const double* fills, int track_nulls, const int32_t* out_pos,
+                                   double* out, int64_t out_ld, void* stream);
+int tmog_binary_transform_select_dev(const uint8_t* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                     int64_t n, int ncols, int fill_value, int track_nulls, const int32_t* out_pos,
+                                     double* out, int64_t out_ld, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------------
  * Label classes
  * ------------------------------------------------------------------------------------------------------------------
@@ -118,6 +129,12 @@ int tmog_label_classes_scratch_bytes(size_t* bytes);
 int tmog_label_classes_dev(const double* label, int64_t n, int max_classes, double* classes, int* nclasses,
                            uint8_t* class_ids, uint64_t* class_counts, void* scratch, size_t scratch_bytes,
                            void* stream);
+
+/* Class ids / counts against a GIVEN sorted class list (device arrays classes [*nclasses], *nclasses a device int):
+ * the second half of tmog_label_classes_dev, for row shards that must share one class list (multi-GPU: each rank
+ * discovers its classes, the union is broadcast, every rank maps its rows against the union). */
+int tmog_label_class_ids_dev(const double* label, int64_t n, const double* classes, const int* nclasses,
+                             int max_classes, uint8_t* class_ids, uint64_t* class_counts, void* stream);
 
 /* counts[c * nclasses + k] = number of NULL rows of column c whose label class is k: the 2 x nLabels contingency
  * table of a lone null indicator (SanityChecker.scala:306-322) for labels with any number of classes.
@@ -231,10 +248,12 @@ int tmog_real_fit_host(tmog_ctx* ctx, const double* values, int64_t ld, const ui
                        double* classes_out, int* nclasses_out, uint64_t* class_counts_out,
                        uint64_t* null_class_counts_out);
 
-/* tmog_real_transform_dev over host columns into a host row-major block (same out_ld / out_col0 meaning). */
+/* tmog_real_transform_dev over host columns into a host row-major block (same out_ld / out_col0 meaning).
+ * out_pos != NULL (HOST array, as tmog_real_transform_select_dev defines it) writes only the out_width columns that
+ * SanityChecker kept. */
 int tmog_real_transform_host(tmog_ctx* ctx, const double* values, int64_t ld, const uint64_t* valid, int64_t ldv,
                              int64_t n, int ncols, const double* fills, int track_nulls, int64_t chunk_rows,
-                             double* out, int64_t out_ld, int64_t out_col0);
+                             const int32_t* out_pos, int out_width, double* out, int64_t out_ld, int64_t out_col0);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,72 @@
+"""World-size-2 gloo tests (CPU) of the row-sharded multi-GPU plumbing: partial merge, shared shifts, label-class
+union, count-table reduction.  The data path needs no collective; these are the only exchanges."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+import torch.distributed as dist  # noqa: E402
+import torch.multiprocessing as mp  # noqa: E402
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, size, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=size)
+    try:
+        from transmogrifai_b200 import _lib as L
+        from transmogrifai_b200 import dist as D
+        assert D.world() == (rank, size)
+        # 1. partial merge == the library's own host merge
+        rng = np.random.default_rng(5)
+        parts = [rng.standard_normal((4, 8)) for _ in range(size)]
+        for p in parts:
+            p[:, 0] = rng.integers(0, 100, 4)
+            p[:, 7] = 100
+        merged = D.allreduce_real_partials(parts[rank].reshape(-1).copy())
+        ref = parts[0].reshape(-1).copy()
+        for p in parts[1:]:
+            L.call("tmog_real_partials_merge", ref.ctypes.data, p.reshape(-1).copy().ctypes.data, 3)
+        np.testing.assert_allclose(merged, ref, rtol=1e-15)
+        # 2. shifts come from rank 0
+        sh = D.broadcast(np.full(5, float(rank + 1)))
+        assert np.array_equal(sh, np.full(5, 1.0))
+        # 3. label-class union: sorted, distinct by bit pattern, -0.0 before 0.0; None if any rank is continuous
+        local = np.array([0.0, 2.0]) if rank == 0 else np.array([-0.0, 1.0, 2.0])
+        u = D.union_classes(local)
+        assert u.tolist() == [0.0, 0.0, 1.0, 2.0] and np.signbit(u[0]) and not np.signbit(u[1])
+        assert D.union_classes(None if rank == 1 else local) is None
+        # 4. count tables add
+        c = D.allreduce_sum(np.arange(6, dtype=np.int64).reshape(2, 3) * (rank + 1))
+        assert np.array_equal(c, np.arange(6).reshape(2, 3) * 3)
+        # 5. shards tile the rows, starts aligned
+        lo, hi = D.shard_rows(10_000, rank, size)
+        assert lo % 2048 == 0 and (lo, hi) == ((0, 6144) if rank == 0 else (6144, 10_000))
+        q.put((rank, "ok"))
+    except Exception as e:  # pragma: no cover
+        q.put((rank, repr(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_world_size_2():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, "ok"), (1, "ok")], res

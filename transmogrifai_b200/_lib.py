@@ -49,6 +49,7 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_binary_transform_dev": [_p, _i64, _p, _i64, _i64, _int, _int, _int, _p, _i64, _i64, _p],
     "tmog_label_classes_scratch_bytes": [C.POINTER(_sz)],
     "tmog_label_classes_dev": [_p, _i64, _int, _p, _p, _p, _p, _p, _sz, _p],
+    "tmog_label_class_ids_dev": [_p, _i64, _p, _p, _int, _p, _p, _p],
     "tmog_null_class_counts_dev": [_p, _i64, _p, _i64, _int, _int, _int, _p, _p],
     "tmog_dense_pilot_shift_dev": [_p, _i64, _i64, _int, _p, _p, _p],
     "tmog_dense_stats_scratch_bytes": [_i64, _int, C.POINTER(_sz)],
@@ -59,12 +60,14 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_contingency_stats": [_p, _int, _int, _p, _p, _p, _p, _p, _p],
     "tmog_pearson_from_cov": [_int, _dbl, _p, _p, _dbl, _p],
     "tmog_sanity_decide": [_int, _p, _p, _p, _int, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
+    "tmog_real_transform_select_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _int, _p, _p, _i64, _p],
+    "tmog_binary_transform_select_dev": [_p, _i64, _p, _i64, _i64, _int, _int, _int, _p, _p, _i64, _p],
     "tmog_ctx_create": [_int, C.POINTER(_p)],
     "tmog_ctx_destroy": [_p],
     "tmog_pinned_alloc": [_sz, C.POINTER(_p)],
     "tmog_pinned_free": [_p],
     "tmog_real_fit_host": [_p, _p, _i64, _p, _i64, _p, _i64, _int, _i64, _int, _p, _p, _p, _int, _p, _p, _p, _p],
-    "tmog_real_transform_host": [_p, _p, _i64, _p, _i64, _i64, _int, _p, _int, _i64, _p, _i64, _i64],
+    "tmog_real_transform_host": [_p, _p, _i64, _p, _i64, _i64, _int, _p, _int, _i64, _p, _int, _p, _i64, _i64],
 }
 
 

@@ -116,6 +116,35 @@ class DensePart:
         return sp.csr_matrix(self.data.cpu().numpy())
 
 
+class LazyDensePart:
+    """A dense block that is only written when somebody needs it.  The vectorizer models return these, so that
+    SanityChecker -- which fits from the statistics sidecar, not from the data -- can decide first and the transform
+    kernel then writes just the kept columns, once (``materialize(keep)``)."""
+
+    def __init__(self, width: int, materialize):
+        self.width = width
+        self._materialize = materialize      # (keep: Optional[List[int]]) -> tensor [n, len(keep) or width]
+        self._data = None
+
+    def materialize(self, keep=None) -> torch.Tensor:
+        if keep is None or list(keep) == list(range(self.width)):
+            return self.data
+        if self._data is not None:
+            idx = torch.as_tensor(list(keep), device=self._data.device)
+            return self._data.index_select(1, idx)
+        return self._materialize(list(keep))
+
+    @property
+    def data(self) -> torch.Tensor:
+        if self._data is None:
+            self._data = self._materialize(None)
+        return self._data
+
+    def to_scipy(self):
+        import scipy.sparse as sp
+        return sp.csr_matrix(self.data.cpu().numpy())
+
+
 @dataclass
 class CsrPart:
     indptr: torch.Tensor                 # [n+1] int64

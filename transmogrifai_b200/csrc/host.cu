@@ -43,7 +43,7 @@ struct tmog_ctx {
     bool r_has_valid = false;
     // streaming buffers
     DevBuf in_values[2], in_valid[2], out_block[2];
-    DevBuf scratch, shifts, partials, fills;
+    DevBuf scratch, shifts, partials, fills, pos;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_cmp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
     cudaEvent_t ev_lbl = nullptr;
 };
@@ -95,6 +95,7 @@ extern "C" int tmog_ctx_destroy(tmog_ctx* c) {
     c->shifts.release();
     c->partials.release();
     c->fills.release();
+    c->pos.release();
     if (c->s_h2d) cudaStreamDestroy(c->s_h2d);
     if (c->s_cmp) cudaStreamDestroy(c->s_cmp);
     if (c->s_d2h) cudaStreamDestroy(c->s_d2h);
@@ -273,15 +274,27 @@ extern "C" int tmog_real_fit_host(tmog_ctx* c, const double* values, int64_t ld,
 
 extern "C" int tmog_real_transform_host(tmog_ctx* c, const double* values, int64_t ld, const uint64_t* valid,
                                         int64_t ldv, int64_t n, int ncols, const double* fills, int track_nulls,
-                                        int64_t chunk_rows, double* out, int64_t out_ld, int64_t out_col0) {
+                                        int64_t chunk_rows, const int32_t* out_pos, int out_width, double* out,
+                                        int64_t out_ld, int64_t out_col0) {
     TMOG_REQUIRE(c != nullptr, "ctx is NULL");
     TMOG_REQUIRE(n >= 0 && ncols >= 0 && ld >= n, "bad shape");
     TMOG_REQUIRE((values != nullptr && out != nullptr) || n == 0 || ncols == 0, "NULL input / output");
     TMOG_REQUIRE(fills != nullptr || valid == nullptr, "fills is NULL but the columns are nullable");
-    const int64_t width = (int64_t)ncols * (track_nulls ? 2 : 1);
+    const int64_t full_width = (int64_t)ncols * (track_nulls ? 2 : 1);
+    TMOG_REQUIRE(out_pos == nullptr || (out_width >= 0 && out_width <= full_width), "bad out_width %d", out_width);
+    const int64_t width = out_pos ? out_width : full_width;
     TMOG_REQUIRE(out_col0 >= 0 && out_ld >= out_col0 + width, "output block exceeds the row stride");
-    if (n == 0 || ncols == 0) return TMOG_OK;
+    if (n == 0 || ncols == 0 || width == 0) return TMOG_OK;
     TMOG_CUDA(cudaSetDevice(c->device));
+    int32_t* d_pos = nullptr;
+    if (out_pos) {
+        for (int64_t i = 0; i < full_width; ++i)
+            TMOG_REQUIRE(out_pos[i] >= -1 && out_pos[i] < out_width, "out_pos[%lld] = %d outside [-1, %d)",
+                         (long long)i, out_pos[i], out_width);
+        if (int rc = c->pos.ensure(sizeof(int32_t) * full_width)) return rc;
+        d_pos = static_cast<int32_t*>(c->pos.p);
+        TMOG_CUDA(cudaMemcpyAsync(d_pos, out_pos, sizeof(int32_t) * full_width, cudaMemcpyHostToDevice, c->s_cmp));
+    }
     int64_t chunk;
     normalise_chunk(n, chunk_rows, &chunk);
     const int64_t nchunks = (n + chunk - 1) / chunk;
@@ -331,8 +344,12 @@ extern "C" int tmog_real_transform_host(tmog_ctx* c, const double* values, int64
         }
         if (k >= 2) TMOG_CUDA(cudaStreamWaitEvent(c->s_cmp, c->ev_out[b], 0));  // out_block[b] drained
         double* dout = static_cast<double*>(c->out_block[b].p);
-        if (int rc = tmog_real_transform_dev(dv, dld, dm, dldv, rows, ncols, d_fills, track_nulls, dout, dw, 0,
-                                             c->s_cmp))
+        if (d_pos) {
+            if (int rc = tmog_real_transform_select_dev(dv, dld, dm, dldv, rows, ncols, d_fills, track_nulls, d_pos,
+                                                        dout, dw, c->s_cmp))
+                return rc;
+        } else if (int rc = tmog_real_transform_dev(dv, dld, dm, dldv, rows, ncols, d_fills, track_nulls, dout, dw, 0,
+                                                    c->s_cmp))
             return rc;
         TMOG_CUDA(cudaEventRecord(c->ev_cmp[b], c->s_cmp));
         TMOG_CUDA(cudaStreamWaitEvent(c->s_d2h, c->ev_cmp[b], 0));

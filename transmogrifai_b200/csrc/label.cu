@@ -192,6 +192,21 @@ extern "C" int tmog_label_classes_dev(const double* label, int64_t n, int max_cl
     return TMOG_OK;
 }
 
+extern "C" int tmog_label_class_ids_dev(const double* label, int64_t n, const double* classes, const int* nclasses,
+                                       int max_classes, uint8_t* class_ids, uint64_t* class_counts, void* stream) {
+    TMOG_REQUIRE(n >= 0 && (label != nullptr || n == 0), "label is NULL");
+    TMOG_REQUIRE(classes != nullptr && nclasses != nullptr, "classes / nclasses is NULL");
+    TMOG_REQUIRE(max_classes >= 1 && max_classes <= 255, "max_classes must be in [1, 255]");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (class_counts != nullptr) TMOG_CUDA(cudaMemsetAsync(class_counts, 0, sizeof(uint64_t) * max_classes, st));
+    if (n == 0) return TMOG_OK;
+    const int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 8);
+    label_class_id_kernel<<<grid, 256, 0, st>>>(label, n, classes, nclasses, class_ids,
+                                                reinterpret_cast<unsigned long long*>(class_counts));
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
 extern "C" int tmog_null_class_counts_dev(const uint64_t* valid, int64_t ldv, const uint8_t* class_ids, int64_t n,
                                           int ncols, int nclasses, int accumulate, uint64_t* counts, void* stream) {
     TMOG_REQUIRE(n >= 0 && ncols >= 0 && nclasses >= 1 && nclasses <= 255, "bad shape");

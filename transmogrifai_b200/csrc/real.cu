@@ -216,7 +216,8 @@ template <typename T, bool TRACK>
 __global__ void __launch_bounds__(256)
 vec_transform_kernel(const T* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid, int64_t ldv,
                      int64_t n, int ncols, const double* __restrict__ fills, double fill_const,
-                     double* __restrict__ out, int64_t out_ld, int64_t out_col0) {
+                     double* __restrict__ out, int64_t out_ld, int64_t out_col0,
+                     const int32_t* __restrict__ out_pos) {
     __shared__ double tile[32][65];
     __shared__ unsigned long long vbits[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -248,7 +249,14 @@ vec_transform_kernel(const T* __restrict__ values, int64_t ld, const uint64_t* _
             double x = tile[lane][rl];
             if (sizeof(T) == 1) x = x != 0.0 ? 1.0 : 0.0;
             x = v ? x : fill;
-            if (TRACK) {
+            if (out_pos != nullptr) {  // column selection: every output column has its own position (or -1)
+                const int px = out_pos[TRACK ? 2 * c : c];
+                if (px >= 0) out[r * out_ld + px] = x;
+                if (TRACK) {
+                    const int pq = out_pos[2 * c + 1];
+                    if (pq >= 0) out[r * out_ld + pq] = v ? 0.0 : 1.0;
+                }
+            } else if (TRACK) {
                 stg_stream(reinterpret_cast<double2*>(out + r * out_ld + out_col0 + 2 * c),
                            make_double2(x, v ? 0.0 : 1.0));
             } else {
@@ -392,13 +400,14 @@ extern "C" int tmog_real_finish(const double* partials, const double* shifts, in
 template <typename T>
 static int launch_transform(const T* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n, int ncols,
                             const double* fills, double fill_const, int track_nulls, double* out, int64_t out_ld,
-                            int64_t out_col0, void* stream) {
+                            int64_t out_col0, void* stream, const int32_t* out_pos = nullptr) {
     if (int rc = check_columns(values, ld, valid, ldv, n, ncols, (int)sizeof(T))) return rc;
     const int64_t width = (int64_t)ncols * (track_nulls ? 2 : 1);
     TMOG_REQUIRE(out != nullptr || n == 0 || ncols == 0, "out is NULL");
-    TMOG_REQUIRE(out_col0 >= 0 && out_ld >= out_col0 + width, "output block [%lld, %lld) exceeds row stride %lld",
-                 (long long)out_col0, (long long)(out_col0 + width), (long long)out_ld);
-    if (track_nulls)
+    TMOG_REQUIRE(out_pos != nullptr || (out_col0 >= 0 && out_ld >= out_col0 + width),
+                 "output block [%lld, %lld) exceeds row stride %lld", (long long)out_col0,
+                 (long long)(out_col0 + width), (long long)out_ld);
+    if (track_nulls && out_pos == nullptr)
         TMOG_REQUIRE(aligned16(out) && (out_ld & 1) == 0 && (out_col0 & 1) == 0,
                      "tracked output needs a 16-byte aligned block: out pointer, even out_ld and even out_col0");
     if (n == 0 || ncols == 0) return TMOG_OK;
@@ -408,10 +417,10 @@ static int launch_transform(const T* values, int64_t ld, const uint64_t* valid, 
     cudaStream_t st = (cudaStream_t)stream;
     if (track_nulls)
         vec_transform_kernel<T, true><<<grid, 256, 0, st>>>(values, ld, valid, ldv, n, ncols, fills, fill_const, out,
-                                                             out_ld, out_col0);
+                                                             out_ld, out_col0, out_pos);
     else
         vec_transform_kernel<T, false><<<grid, 256, 0, st>>>(values, ld, valid, ldv, n, ncols, fills, fill_const, out,
-                                                              out_ld, out_col0);
+                                                              out_ld, out_col0, out_pos);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }
@@ -429,4 +438,21 @@ extern "C" int tmog_binary_transform_dev(const uint8_t* values, int64_t ld, cons
                                          int64_t out_ld, int64_t out_col0, void* stream) {
     return launch_transform<uint8_t>(values, ld, valid, ldv, n, ncols, nullptr, fill_value ? 1.0 : 0.0, track_nulls,
                                      out, out_ld, out_col0, stream);
+}
+
+extern "C" int tmog_real_transform_select_dev(const double* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                              int64_t n, int ncols, const double* fills, int track_nulls,
+                                              const int32_t* out_pos, double* out, int64_t out_ld, void* stream) {
+    TMOG_REQUIRE(fills != nullptr || valid == nullptr, "fills is NULL but the columns are nullable");
+    TMOG_REQUIRE(out_pos != nullptr, "out_pos is NULL");
+    return launch_transform<double>(values, ld, valid, ldv, n, ncols, fills, 0.0, track_nulls, out, out_ld, 0, stream,
+                                    out_pos);
+}
+
+extern "C" int tmog_binary_transform_select_dev(const uint8_t* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                                int64_t n, int ncols, int fill_value, int track_nulls,
+                                                const int32_t* out_pos, double* out, int64_t out_ld, void* stream) {
+    TMOG_REQUIRE(out_pos != nullptr, "out_pos is NULL");
+    return launch_transform<uint8_t>(values, ld, valid, ldv, n, ncols, nullptr, fill_value ? 1.0 : 0.0, track_nulls,
+                                     out, out_ld, 0, stream, out_pos);
 }

@@ -1,0 +1,93 @@
+"""Row-sharded multi-GPU support: one process per GPU, rows split contiguously across ranks, and only the small
+partial results cross NVLink -- the B200 counterpart of the reference's Spark aggregations (SURVEY.md section 2,
+"collective call sites"): Aggregator.merge / treeAggregate / reduceByKey become one NCCL all-reduce of
+[ncols] x {count, sums, min, max} (f64) and of the per-label-class count tables (i64).  No data-path collective.
+
+torch.distributed is the transport (NCCL on GPUs; gloo in the CPU tests)."""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ._lib import REAL_NSTAT
+
+
+def world() -> Tuple[int, int]:
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def _device() -> torch.device:
+    return torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+
+
+def allreduce_real_partials(partials: np.ndarray) -> np.ndarray:
+    """Merge [(ncols+1) * NSTAT] partial blocks of all ranks (they must share their shifts): sums and counts add,
+    [5] is a min, [6] a max -- tmog_real_partials_merge across ranks."""
+    if world()[1] == 1:
+        return partials
+    p = torch.from_numpy(partials.reshape(-1, REAL_NSTAT).copy()).to(_device())
+    sums = p[:, [0, 1, 2, 3, 4, 7]].contiguous()
+    ext = torch.stack([p[:, 5], -p[:, 6]], dim=1).contiguous()
+    dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+    dist.all_reduce(ext, op=dist.ReduceOp.MIN)
+    p[:, [0, 1, 2, 3, 4, 7]] = sums
+    p[:, 5] = ext[:, 0]
+    p[:, 6] = -ext[:, 1]
+    return p.cpu().numpy().reshape(-1)
+
+
+def broadcast(a: np.ndarray, src: int = 0) -> np.ndarray:
+    if world()[1] == 1:
+        return a
+    t = torch.from_numpy(np.ascontiguousarray(a)).to(_device())
+    dist.broadcast(t, src=src)
+    return t.cpu().numpy()
+
+
+def allreduce_sum(a: np.ndarray) -> np.ndarray:
+    if world()[1] == 1:
+        return a
+    t = torch.from_numpy(np.ascontiguousarray(a)).to(_device())
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return t.cpu().numpy()
+
+
+def union_classes(local: Optional[np.ndarray], cap: int = 255) -> Optional[np.ndarray]:
+    """Union of every rank's sorted distinct label values; None if any rank (or the union) exceeds `cap`."""
+    if world()[1] == 1:
+        return local
+    buf = np.full(cap + 1, np.nan)
+    k = -1 if local is None else len(local)
+    buf[0] = k
+    if k > 0:
+        buf[1:1 + k] = local
+    t = torch.from_numpy(buf).to(_device())
+    out = [torch.empty_like(t) for _ in range(world()[1])]
+    dist.all_gather(out, t)
+    vals = []
+    for o in out:
+        o = o.cpu().numpy()
+        kk = int(o[0])
+        if kk < 0:
+            return None
+        vals.append(o[1:1 + kk])
+    allv = np.concatenate(vals) if vals else np.zeros(0)
+    # distinct by bit pattern (java.lang.Double.equals), ascending by value with -0.0 < 0.0 and NaN last
+    bits = np.unique(allv.view(np.int64))
+    u = bits.view(np.float64)
+    key = np.where(bits < 0, ~bits.view(np.uint64), bits.view(np.uint64) | np.uint64(1 << 63))
+    u = u[np.argsort(key, kind="stable")]
+    return None if len(u) > cap else u
+
+
+def shard_rows(n: int, rank: int, size: int, align: int = 2048) -> Tuple[int, int]:
+    """Contiguous row range of `rank` (starts aligned so that bitmap words and 16-byte loads stay aligned)."""
+    per = (n + size - 1) // size
+    per = (per + align - 1) // align * align
+    lo = min(n, rank * per)
+    return lo, min(n, lo + per)

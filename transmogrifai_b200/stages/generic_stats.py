@@ -11,7 +11,7 @@ import torch
 
 from .. import _lib as L
 from .. import runtime as R
-from ..columnar import ColumnarBatch, CsrPart, DensePart, VectorColumn
+from ..columnar import ColumnarBatch, CsrPart, DensePart, LazyDensePart, VectorColumn
 from ..stats import LabelInfo, VectorStats
 from .numeric import label_info_dev
 
@@ -27,7 +27,7 @@ def _device_label(batch: ColumnarBatch, label_name: str) -> torch.Tensor:
 def _dense_block(vec: VectorColumn) -> torch.Tensor:
     """All parts as one device row-major block (a copy only when there are several parts or host data)."""
     for p in vec.parts:
-        if not isinstance(p, DensePart):
+        if not isinstance(p, (DensePart, LazyDensePart)):
             raise NotImplementedError("this operation needs a dense OPVector (sparse parts are handled by the fused "
                                       "scans; set featureFeatureCorrLevel = Off for hashed / pivoted vectors)")
     blocks = [p.data if p.data.is_cuda else p.data.cuda() for p in vec.parts]
@@ -106,12 +106,28 @@ def pearson_matrix(batch: ColumnarBatch, vec: VectorColumn, label_name: str, cor
 
 
 def select_columns(vec: VectorColumn, keep: List[int]) -> list:
-    """removeFeatures: the kept columns, in order (DerivedFeatureFilterUtils.scala:291-305)."""
+    """removeFeatures: the kept columns, in order (DerivedFeatureFilterUtils.scala:291-305).  Lazy parts are written
+    once with just their kept columns; materialised dense parts go through the gather kernel."""
     R.require_cuda()
-    x = _dense_block(vec)
-    n = x.shape[0]
-    idx = torch.tensor(keep, dtype=torch.int32, device="cuda")
-    out = torch.empty((n, len(keep)), dtype=torch.float64, device="cuda")
-    L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), n, idx.data_ptr(), len(keep), out.data_ptr(),
-           max(len(keep), 1), R.stream())
-    return [DensePart(out)]
+    out, off = [], 0
+    for p in vec.parts:
+        local = [i - off for i in keep if off <= i < off + p.width]
+        off += p.width
+        if not local:
+            continue
+        if isinstance(p, LazyDensePart):
+            out.append(DensePart(p.materialize(local)))
+        elif isinstance(p, DensePart):
+            if local == list(range(p.width)):
+                out.append(p)
+                continue
+            x = p.data if p.data.is_cuda else p.data.cuda()
+            n = x.shape[0]
+            idx = torch.tensor(local, dtype=torch.int32, device="cuda")
+            dst = torch.empty((n, len(local)), dtype=torch.float64, device="cuda")
+            L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), n, idx.data_ptr(), len(local),
+                   dst.data_ptr(), len(local), R.stream())
+            out.append(DensePart(dst))
+        else:
+            raise NotImplementedError("column selection on sparse parts")
+    return out

@@ -12,9 +12,10 @@ import numpy as np
 import torch
 
 from .. import _lib as L
+from .. import dist as D
 from .. import features as F
 from .. import runtime as R
-from ..columnar import ColumnarBatch, DensePart, NumericBlock, VectorColumn, round_up
+from ..columnar import ColumnarBatch, DensePart, LazyDensePart, NumericBlock, VectorColumn, round_up
 from ..metadata import OpVectorMetadata, feature_column
 from ..stats import LabelInfo, VectorStats
 from .base import OpEstimator, OpModel, OpTransformer
@@ -32,11 +33,13 @@ def _numeric_metadata(stage, track_nulls: bool) -> OpVectorMetadata:
 
 
 def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str):
-    """Distinct label classes + per-row class ids on the device (cached on the batch)."""
+    """Distinct label classes (global over all ranks), their global row counts, and per-row class ids of the local
+    rows on the device.  Cached on the batch."""
     cache = batch.__dict__.setdefault("_label_cache", {})
     if name in cache:
         return cache[name]
     n = batch.n
+    distributed = D.world()[1] > 1
     nb = C.c_size_t()
     L.call("tmog_label_classes_scratch_bytes", C.byref(nb))
     scratch = R.scratch("label", nb.value)
@@ -45,9 +48,22 @@ def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str):
     ncls = torch.zeros(1, dtype=torch.int32, device="cuda")
     ids = torch.empty(max(n, 1), dtype=torch.uint8, device="cuda")
     L.call("tmog_label_classes_dev", y.data_ptr(), n, MAX_LABEL_CLASSES, classes.data_ptr(), ncls.data_ptr(),
-           ids.data_ptr(), counts.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
+           None if distributed else ids.data_ptr(), None if distributed else counts.data_ptr(), scratch.data_ptr(),
+           scratch.numel(), R.stream())
     k = int(ncls.item())
-    out = (classes[:k].cpu().numpy() if k > 0 else None, counts[:k].cpu().numpy() if k > 0 else None, ids)
+    local = classes[:k].cpu().numpy() if k >= 0 else None
+    if distributed:
+        union = D.union_classes(local, MAX_LABEL_CLASSES)
+        if union is None or len(union) == 0:
+            out = (None, None, ids)
+        else:
+            classes[:len(union)] = torch.from_numpy(union).cuda()
+            ncls.fill_(len(union))
+            L.call("tmog_label_class_ids_dev", y.data_ptr(), n, classes.data_ptr(), ncls.data_ptr(),
+                   MAX_LABEL_CLASSES, ids.data_ptr(), counts.data_ptr(), R.stream())
+            out = (union, D.allreduce_sum(counts[:len(union)].cpu().numpy()), ids)
+    else:
+        out = (local, counts[:k].cpu().numpy(), ids) if k > 0 else (None, None, ids)
     cache[name] = out
     return out
 
@@ -100,6 +116,8 @@ class RealVectorizer(OpEstimator):
             d_part = torch.zeros((ncols + 1) * NS, dtype=torch.float64, device="cuda")
             L.call("tmog_real_pilot_shift_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
                    y.data_ptr(), n, ncols, d_shifts.data_ptr(), R.stream())
+            if D.world()[1] > 1:        # partials only merge when every rank uses rank 0's shifts
+                torch.distributed.broadcast(d_shifts, src=0)
             L.call("tmog_real_fit_partials_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
                    y.data_ptr(), n, ncols, d_shifts.data_ptr(), scratch.data_ptr(), scratch.numel(),
                    d_part.data_ptr(), R.stream())
@@ -109,8 +127,8 @@ class RealVectorizer(OpEstimator):
                     d_nc = torch.zeros((ncols, len(classes)), dtype=torch.int64, device="cuda")
                     L.call("tmog_null_class_counts_dev", R.ptr(block.valid), block.ldv, ids.data_ptr(), n, ncols,
                            len(classes), 0, d_nc.data_ptr(), R.stream())
-                    null_counts = d_nc.cpu().numpy()
-            partials = d_part.cpu().numpy()
+                    null_counts = D.allreduce_sum(d_nc.cpu().numpy())
+            partials = D.allreduce_real_partials(d_part.cpu().numpy())
             shifts = d_shifts.cpu().numpy()
         else:
             y = batch.label() if label_name else torch.zeros(max(n, 2), dtype=torch.float64)
@@ -118,8 +136,12 @@ class RealVectorizer(OpEstimator):
             cnt = np.zeros(256, dtype=np.uint64)
             ncls = C.c_int(0)
             nc = np.zeros((ncols, MAX_LABEL_CLASSES), dtype=np.uint64).reshape(-1)
+            shifts_in = None
+            if D.world()[1] > 1:
+                shifts_in = D.broadcast(_host_pilot_shifts(block, y, n, ncols))
             L.call("tmog_real_fit_host", R.ctx(), block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
-                   y.data_ptr(), n, ncols, self.chunkRows, 1, None, shifts.ctypes.data, partials.ctypes.data,
+                   y.data_ptr(), n, ncols, self.chunkRows, 1, None if shifts_in is None else shifts_in.ctypes.data,
+                   shifts.ctypes.data, partials.ctypes.data,
                    MAX_LABEL_CLASSES if label_name else 0, cls.ctypes.data, C.byref(ncls), cnt.ctypes.data,
                    nc.ctypes.data if self.trackNulls else None)
             if label_name and ncls.value > 0:
@@ -127,6 +149,23 @@ class RealVectorizer(OpEstimator):
                 classes, counts = cls[:k].copy(), cnt[:k].astype(np.int64)
                 if self.trackNulls:
                     null_counts = nc[:ncols * k].reshape(ncols, k).astype(np.int64)
+            if D.world()[1] > 1:
+                partials = D.allreduce_real_partials(partials)
+                union = D.union_classes(classes if label_name else np.zeros(0), MAX_LABEL_CLASSES)
+                if label_name and union is not None and len(union) > 0:
+                    ubits = union.view(np.int64)
+                    pos = np.array([int(np.nonzero(ubits == b)[0][0]) for b in classes.view(np.int64)],
+                                   dtype=np.int64) if classes is not None else np.zeros(0, dtype=np.int64)
+                    g_counts = np.zeros(len(union), dtype=np.int64)
+                    g_null = np.zeros((ncols, len(union)), dtype=np.int64)
+                    if classes is not None:
+                        g_counts[pos] = counts
+                        if null_counts is not None:
+                            g_null[:, pos] = null_counts
+                    classes, counts = union, D.allreduce_sum(g_counts)
+                    null_counts = D.allreduce_sum(g_null) if self.trackNulls else None
+                else:
+                    classes = counts = null_counts = None
         w = ncols * (2 if self.trackNulls else 1)
         fills = np.zeros(ncols)
         mean, var, mn, mx, cov = (np.zeros(w) for _ in range(5))
@@ -141,11 +180,27 @@ class RealVectorizer(OpEstimator):
                 class_sums = np.full((len(classes), w), np.nan)
                 if self.trackNulls and null_counts is not None:
                     class_sums[:, 1::2] = null_counts.T
-            stats = VectorStats(LabelInfo(label_name, n, lab, classes, counts), mean, var, mn, mx, cov, class_sums)
+            stats = VectorStats(LabelInfo(label_name, int(lab[0]), lab, classes, counts), mean, var, mn, mx, cov,
+                                class_sums)
         model = RealVectorizerModel(self, fills.tolist(), self.trackNulls)
         model._fit_stats = stats
         model._fit_key = (block.values.data_ptr(), n)
         return model
+
+
+def _host_pilot_shifts(block: NumericBlock, y: torch.Tensor, n: int, ncols: int) -> np.ndarray:
+    """Pilot shifts of a host block: upload its first rows and run the pilot kernel (rank 0's result is broadcast)."""
+    rows = min(n, 4096)
+    ld = round_up(max(rows, 1), 2)
+    v = torch.zeros((max(ncols, 1), ld), dtype=torch.float64)
+    v[:ncols, :rows] = block.values[:, :rows]
+    dv = v.cuda()
+    dm = None if block.valid is None else block.valid[:, :(rows + 63) // 64].contiguous().cuda()
+    dy = y[:max(rows, 1)].cuda()
+    sh = torch.zeros(ncols + 1, dtype=torch.float64, device="cuda")
+    L.call("tmog_real_pilot_shift_dev", dv.data_ptr(), ld, R.ptr(dm), 0 if dm is None else dm.shape[1], dy.data_ptr(),
+           rows, ncols, sh.data_ptr(), R.stream())
+    return sh.cpu().numpy()
 
 
 class RealVectorizerModel(OpModel):
@@ -161,37 +216,55 @@ class RealVectorizerModel(OpModel):
         R.require_cuda()
         names = [f.name for f in self.inN]
         block = batch.numeric(names)
-        out = _transform_numeric(block, np.asarray(self.fillValues), self.trackNulls, self.chunkRows)
+        fills, track, chunk = np.asarray(self.fillValues), self.trackNulls, self.chunkRows
+        part = LazyDensePart(len(names) * (2 if track else 1),
+                             lambda keep: _transform_numeric(block, fills, track, chunk, keep=keep))
         same = self._fit_key == (block.values.data_ptr(), batch.n)
-        return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [DensePart(out)],
+        return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part],
                             self._fit_stats if same else None)
 
 
 def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_nulls: bool, chunk_rows: int,
-                       fill_value: bool = False) -> torch.Tensor:
+                       fill_value: bool = False, keep: Optional[List[int]] = None) -> torch.Tensor:
+    """Run the transform kernel.  keep = the output columns wanted, in order (None = all): the kernel then writes
+    only those (SanityChecker's indicesToKeep fused into the vectorizer's transform)."""
     n, ncols = block.n, len(block.names)
-    w = ncols * (2 if track_nulls else 1)
+    w_full = ncols * (2 if track_nulls else 1)
     binary = block.values.dtype == torch.uint8
+    pos = None
+    w = w_full
+    if keep is not None:
+        pos = np.full(w_full, -1, dtype=np.int32)
+        pos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
+        w = len(keep)
     if block.is_cuda:
-        out = torch.empty((n, round_up(w, 2)), dtype=torch.float64, device="cuda")
+        out = torch.empty((n, round_up(max(w, 1), 2)), dtype=torch.float64, device="cuda")
+        d_pos = None if pos is None else torch.from_numpy(pos).cuda()
         if binary:
-            L.call("tmog_binary_transform_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv, n,
-                   ncols, int(fill_value), int(track_nulls), out.data_ptr(), out.shape[1], 0, R.stream())
+            if pos is None:
+                L.call("tmog_binary_transform_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
+                       n, ncols, int(fill_value), int(track_nulls), out.data_ptr(), out.shape[1], 0, R.stream())
+            else:
+                L.call("tmog_binary_transform_select_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid),
+                       block.ldv, n, ncols, int(fill_value), int(track_nulls), d_pos.data_ptr(), out.data_ptr(),
+                       out.shape[1], R.stream())
         else:
             d_fills = None if fills is None else torch.from_numpy(fills).cuda()
-            L.call("tmog_real_transform_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv, n,
-                   ncols, R.ptr(d_fills), int(track_nulls), out.data_ptr(), out.shape[1], 0, R.stream())
+            if pos is None:
+                L.call("tmog_real_transform_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
+                       n, ncols, R.ptr(d_fills), int(track_nulls), out.data_ptr(), out.shape[1], 0, R.stream())
+            else:
+                L.call("tmog_real_transform_select_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid),
+                       block.ldv, n, ncols, R.ptr(d_fills), int(track_nulls), d_pos.data_ptr(), out.data_ptr(),
+                       out.shape[1], R.stream())
         return out[:, :w]
     if binary:
         dev = block.to("cuda")
-        return _transform_numeric(dev, fills, track_nulls, chunk_rows, fill_value).cpu()
-    out = torch.empty((n, w), dtype=torch.float64)
-    try:
-        out = out.pin_memory()
-    except RuntimeError:
-        pass
+        return _transform_numeric(dev, fills, track_nulls, chunk_rows, fill_value, keep).cpu()
+    out = torch.empty((n, w), dtype=torch.float64, pin_memory=True)
     L.call("tmog_real_transform_host", R.ctx(), block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv, n,
-           ncols, None if fills is None else fills.ctypes.data, int(track_nulls), chunk_rows, out.data_ptr(), w, 0)
+           ncols, None if fills is None else fills.ctypes.data, int(track_nulls), chunk_rows,
+           None if pos is None else pos.ctypes.data, w, out.data_ptr(), w, 0)
     return out
 
 
@@ -212,8 +285,9 @@ class RealNNVectorizer(OpTransformer):
         block = batch.numeric([f.name for f in self.inN])
         if block.valid is not None:
             raise ValueError("None.get: a RealNN feature holds a null")
-        out = _transform_numeric(block, None, False, self.chunkRows)
-        return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [DensePart(out)], None)
+        chunk = self.chunkRows
+        part = LazyDensePart(len(block.names), lambda keep: _transform_numeric(block, None, False, chunk, keep=keep))
+        return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part], None)
 
 
 class BinaryVectorizer(OpTransformer):
@@ -244,5 +318,7 @@ class BinaryVectorizer(OpTransformer):
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
         R.require_cuda()
         block = batch.numeric([f.name for f in self.inN])
-        out = _transform_numeric(block, None, self.trackNulls, self.chunkRows, self.fillValue)
-        return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [DensePart(out)], None)
+        track, chunk, fv = self.trackNulls, self.chunkRows, self.fillValue
+        part = LazyDensePart(len(block.names) * (2 if track else 1),
+                             lambda keep: _transform_numeric(block, None, track, chunk, fv, keep=keep))
+        return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part], None)

@@ -16,6 +16,7 @@ import numpy as np
 import torch
 
 from .. import _lib as L
+from .. import dist as D
 from .. import features as F
 from ..columnar import ColumnarBatch, CsrPart, DensePart, VectorColumn
 from ..metadata import OpVectorMetadata
@@ -166,7 +167,7 @@ class SanityChecker(OpEstimator):
     def fit(self, batch: ColumnarBatch) -> "SanityCheckerModel":
         label_f, vec_f = self.inN
         vec = batch.vectors[vec_f.name]
-        n = batch.n
+        n = int(D.allreduce_sum(np.array([batch.n], dtype=np.int64))[0])    # rows over all ranks
         if n <= 0:
             raise ValueError("requirement failed: Sample size cannot be zero")
         frac = self.fraction(n)
