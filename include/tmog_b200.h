@@ -106,15 +106,17 @@ int tmog_binary_transform_dev(const uint8_t* values, int64_t ld, const uint64_t*
                               int64_t out_col0, void* stream);
 
 /* The two transforms above fused with SanityCheckerModel.transformFn -> removeFeatures
- * (C/stages/impl/preparators/DerivedFeatureFilterUtils.scala:291-305): out_pos [ncols * (track_nulls ? 2 : 1)] (device)
- * gives, for every column the vectorizer would emit, its position in the output row (any layout: the kept columns
- * of the combined vector), or -1 when SanityChecker dropped it.  The dropped columns are never written. */
+ * (C/stages/impl/preparators/DerivedFeatureFilterUtils.scala:291-305): keep_mask (device bitmap, bit i of word i/64)
+ * marks the columns the vectorizer would emit (0 .. ncols * (track_nulls ? 2 : 1) - 1) that SanityChecker kept, nkeep
+ * of them; they are written packed, in order, into columns [out_col0, out_col0 + nkeep) of the output rows.  Dropped
+ * columns are never written. */
 int tmog_real_transform_select_dev(const double* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n,
-                                   int ncols, const double* fills, int track_nulls, const int32_t* out_pos,
-                                   double* out, int64_t out_ld, void* stream);
+                                   int ncols, const double* fills, int track_nulls, const uint64_t* keep_mask,
+                                   int nkeep, double* out, int64_t out_ld, int64_t out_col0, void* stream);
 int tmog_binary_transform_select_dev(const uint8_t* values, int64_t ld, const uint64_t* valid, int64_t ldv,
-                                     int64_t n, int ncols, int fill_value, int track_nulls, const int32_t* out_pos,
-                                     double* out, int64_t out_ld, void* stream);
+                                     int64_t n, int ncols, int fill_value, int track_nulls,
+                                     const uint64_t* keep_mask, int nkeep, double* out, int64_t out_ld,
+                                     int64_t out_col0, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------------
  * Label classes
@@ -249,11 +251,11 @@ int tmog_real_fit_host(tmog_ctx* ctx, const double* values, int64_t ld, const ui
                        uint64_t* null_class_counts_out);
 
 /* tmog_real_transform_dev over host columns into a host row-major block (same out_ld / out_col0 meaning).
- * out_pos != NULL (HOST array, as tmog_real_transform_select_dev defines it) writes only the out_width columns that
- * SanityChecker kept. */
+ * keep != NULL (HOST array of nkeep ascending emitted-column indices) writes only the columns that SanityChecker
+ * kept, packed (tmog_real_transform_select_dev). */
 int tmog_real_transform_host(tmog_ctx* ctx, const double* values, int64_t ld, const uint64_t* valid, int64_t ldv,
                              int64_t n, int ncols, const double* fills, int track_nulls, int64_t chunk_rows,
-                             const int32_t* out_pos, int out_width, double* out, int64_t out_ld, int64_t out_col0);
+                             const int32_t* keep, int nkeep, double* out, int64_t out_ld, int64_t out_col0);
 
 #ifdef __cplusplus
 }

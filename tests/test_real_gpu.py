@@ -205,3 +205,28 @@ def test_real_full_size_properties():
            None, None, None, None, None)
     ref = (torch.where(bits, x, torch.zeros_like(x)).sum(dim=1) / bits.sum(dim=1)).cpu().numpy()
     np.testing.assert_allclose(fills, ref, rtol=1e-12)
+
+
+@pytest.mark.parametrize("track", [True, False])
+def test_real_transform_select_writes_only_kept_columns(track):
+    """tmog_real_transform_select_dev == transform followed by SanityCheckerModel's column gather."""
+    from transmogrifai_b200 import _lib as L
+    n, ncols = 3001, 37
+    x, valid, y = make_real_config(n, ncols, seed=9)
+    res = run_fit(x, valid, y, track_nulls=track)
+    full = V.real_vectorizer_transform(to_lists(x, valid), res["fills"], track)
+    rng = np.random.default_rng(1)
+    w = full.shape[1]
+    for keep in ([0], list(range(w)), sorted(rng.choice(w, size=w // 2, replace=False).tolist()), [w - 1],
+                 [i for i in range(w) if i != 14]):
+        bits = np.zeros((w + 63) // 64 * 64, dtype=np.uint8)
+        bits[keep] = 1
+        kd = torch.from_numpy(np.packbits(bits, bitorder="little").view("<i8").copy()).cuda()
+        out = torch.full((n, len(keep) + 3), -7.0, dtype=torch.float64, device="cuda")
+        fills = _dev(res["fills"])
+        L.call("tmog_real_transform_select_dev", res["xd"].data_ptr(), res["ld"], res["vptr"], res["ldv"], n, ncols,
+               fills.data_ptr(), int(track), kd.data_ptr(), len(keep), out.data_ptr(), len(keep) + 3, 2,
+               torch.cuda.current_stream().cuda_stream)
+        got = out.cpu().numpy()
+        assert np.array_equal(got[:, 2:2 + len(keep)], full[:, keep])
+        assert np.all(got[:, :2] == -7.0) and np.all(got[:, 2 + len(keep):] == -7.0)

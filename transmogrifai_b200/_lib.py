@@ -11,7 +11,7 @@ import re
 from typing import Dict, List
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtmog_b200.so")
+LIB_PATH = os.environ.get("TMOG_B200_LIB") or os.path.join(_HERE, "libtmog_b200.so")   # override: A/B kernel builds
 HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "tmog_b200.h")
 
 REAL_NSTAT = 8
@@ -60,8 +60,8 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_contingency_stats": [_p, _int, _int, _p, _p, _p, _p, _p, _p],
     "tmog_pearson_from_cov": [_int, _dbl, _p, _p, _dbl, _p],
     "tmog_sanity_decide": [_int, _p, _p, _p, _int, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
-    "tmog_real_transform_select_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _int, _p, _p, _i64, _p],
-    "tmog_binary_transform_select_dev": [_p, _i64, _p, _i64, _i64, _int, _int, _int, _p, _p, _i64, _p],
+    "tmog_real_transform_select_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _int, _p, _int, _p, _i64, _i64, _p],
+    "tmog_binary_transform_select_dev": [_p, _i64, _p, _i64, _i64, _int, _int, _int, _p, _int, _p, _i64, _i64, _p],
     "tmog_ctx_create": [_int, C.POINTER(_p)],
     "tmog_ctx_destroy": [_p],
     "tmog_pinned_alloc": [_sz, C.POINTER(_p)],

@@ -274,33 +274,36 @@ extern "C" int tmog_real_fit_host(tmog_ctx* c, const double* values, int64_t ld,
 
 extern "C" int tmog_real_transform_host(tmog_ctx* c, const double* values, int64_t ld, const uint64_t* valid,
                                         int64_t ldv, int64_t n, int ncols, const double* fills, int track_nulls,
-                                        int64_t chunk_rows, const int32_t* out_pos, int out_width, double* out,
+                                        int64_t chunk_rows, const int32_t* keep, int nkeep, double* out,
                                         int64_t out_ld, int64_t out_col0) {
     TMOG_REQUIRE(c != nullptr, "ctx is NULL");
     TMOG_REQUIRE(n >= 0 && ncols >= 0 && ld >= n, "bad shape");
     TMOG_REQUIRE((values != nullptr && out != nullptr) || n == 0 || ncols == 0, "NULL input / output");
     TMOG_REQUIRE(fills != nullptr || valid == nullptr, "fills is NULL but the columns are nullable");
     const int64_t full_width = (int64_t)ncols * (track_nulls ? 2 : 1);
-    TMOG_REQUIRE(out_pos == nullptr || (out_width >= 0 && out_width <= full_width), "bad out_width %d", out_width);
-    const int64_t width = out_pos ? out_width : full_width;
+    TMOG_REQUIRE(keep == nullptr || (nkeep >= 0 && nkeep <= full_width), "bad nkeep %d", nkeep);
+    const int64_t width = keep ? nkeep : full_width;
     TMOG_REQUIRE(out_col0 >= 0 && out_ld >= out_col0 + width, "output block exceeds the row stride");
     if (n == 0 || ncols == 0 || width == 0) return TMOG_OK;
     TMOG_CUDA(cudaSetDevice(c->device));
-    int32_t* d_pos = nullptr;
-    if (out_pos) {
-        for (int64_t i = 0; i < full_width; ++i)
-            TMOG_REQUIRE(out_pos[i] >= -1 && out_pos[i] < out_width, "out_pos[%lld] = %d outside [-1, %d)",
-                         (long long)i, out_pos[i], out_width);
-        if (int rc = c->pos.ensure(sizeof(int32_t) * full_width)) return rc;
-        d_pos = static_cast<int32_t*>(c->pos.p);
-        TMOG_CUDA(cudaMemcpyAsync(d_pos, out_pos, sizeof(int32_t) * full_width, cudaMemcpyHostToDevice, c->s_cmp));
+    uint64_t* d_keep = nullptr;
+    if (keep) {
+        std::vector<uint64_t> mask((size_t)(full_width + 63) / 64, 0ull);
+        for (int i = 0; i < nkeep; ++i) {
+            TMOG_REQUIRE(keep[i] >= 0 && keep[i] < full_width && (i == 0 || keep[i] > keep[i - 1]),
+                         "keep must be ascending indices in [0, %lld)", (long long)full_width);
+            mask[keep[i] >> 6] |= 1ull << (keep[i] & 63);
+        }
+        if (int rc = c->pos.ensure(sizeof(uint64_t) * mask.size())) return rc;
+        d_keep = static_cast<uint64_t*>(c->pos.p);
+        TMOG_CUDA(cudaMemcpy(d_keep, mask.data(), sizeof(uint64_t) * mask.size(), cudaMemcpyHostToDevice));
     }
     int64_t chunk;
     normalise_chunk(n, chunk_rows, &chunk);
     const int64_t nchunks = (n + chunk - 1) / chunk;
     const bool resident = c->r_key == values && c->r_n == n && c->r_ncols == ncols &&
                           c->r_has_valid == (valid != nullptr);
-    const int64_t dw = round_up(width, 2);  // device row stride (even, for the 16-byte stores)
+    const int64_t dw = round_up(width, 4);  // device row stride: rows start on 32-byte sector boundaries
     if (int rc = c->fills.ensure(sizeof(double) * std::max(ncols, 1))) return rc;
     double* d_fills = nullptr;
     if (fills) {
@@ -344,9 +347,9 @@ extern "C" int tmog_real_transform_host(tmog_ctx* c, const double* values, int64
         }
         if (k >= 2) TMOG_CUDA(cudaStreamWaitEvent(c->s_cmp, c->ev_out[b], 0));  // out_block[b] drained
         double* dout = static_cast<double*>(c->out_block[b].p);
-        if (d_pos) {
-            if (int rc = tmog_real_transform_select_dev(dv, dld, dm, dldv, rows, ncols, d_fills, track_nulls, d_pos,
-                                                        dout, dw, c->s_cmp))
+        if (d_keep) {
+            if (int rc = tmog_real_transform_select_dev(dv, dld, dm, dldv, rows, ncols, d_fills, track_nulls, d_keep,
+                                                        nkeep, dout, dw, 0, c->s_cmp))
                 return rc;
         } else if (int rc = tmog_real_transform_dev(dv, dld, dm, dldv, rows, ncols, d_fills, track_nulls, dout, dw, 0,
                                                     c->s_cmp))

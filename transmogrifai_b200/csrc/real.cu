@@ -209,60 +209,151 @@ real_pilot_shift_kernel(const double* __restrict__ values, int64_t ld, const uin
     }
 }
 
-// Column-major -> row-major transposing writer.  Tile = 64 rows x 32 columns through padded shared memory: loads are
-// 256-byte row runs of one column per warp instruction, stores are one 512-byte run ([value, isNull] x 32 columns) of
-// one output row per warp instruction.
+// Column-major -> row-major transposing writers.  A CTA owns 64 rows and walks the column tiles (32 input columns
+// each) of those rows, so one CTA writes whole output rows back to back.
+//
+// vec_transform_kernel: every emitted column is written (the vectorizer's own transformFn).  Per tile the loads are
+// 256-byte row runs of one column per warp instruction into a padded shared tile; the stores are contiguous 256-byte
+// runs of one output row per warp instruction (lane = emitted column).
 template <typename T, bool TRACK>
 __global__ void __launch_bounds__(256)
 vec_transform_kernel(const T* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid, int64_t ldv,
                      int64_t n, int ncols, const double* __restrict__ fills, double fill_const,
-                     double* __restrict__ out, int64_t out_ld, int64_t out_col0,
-                     const int32_t* __restrict__ out_pos) {
+                     double* __restrict__ out, int64_t out_ld, int64_t out_col0) {
     __shared__ double tile[32][65];
     __shared__ unsigned long long vbits[32];
+    constexpr int PER = TRACK ? 2 : 1;  // emitted columns per input column
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int c0 = blockIdx.y * 32;
     const int64_t r0 = (int64_t)blockIdx.x * 64;
+    const int rows_here = (int)min((int64_t)64, n - r0);
+    const int ntiles = (ncols + 31) / 32;
+    for (int t = 0; t < ntiles; ++t) {
+        const int c0 = t * 32;
+        const int tc = min(32, ncols - c0);
+        if (t > 0) __syncthreads();  // previous tile fully written before the shared tile is overwritten
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const int cl = warp + 8 * k;
-        const int c = c0 + cl;
-        if (c < ncols) {
-            const T* col = values + (int64_t)c * ld + r0;
-            const int64_t ra = r0 + lane, rb = r0 + lane + 32;
-            tile[cl][lane] = ra < n ? (double)col[lane] : 0.0;
-            tile[cl][lane + 32] = rb < n ? (double)col[lane + 32] : 0.0;
-            if (lane == 0) vbits[cl] = valid ? valid[(int64_t)c * ldv + (r0 >> 6)] : ~0ull;
-        }
-    }
-    __syncthreads();
-    const int c = c0 + lane;
-    if (c >= ncols) return;
-    const double fill = fills ? fills[c] : fill_const;
-    const unsigned long long vb = vbits[lane];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const int rl = warp + 8 * k;
-        const int64_t r = r0 + rl;
-        if (r < n) {
-            const bool v = (vb >> rl) & 1ull;
-            double x = tile[lane][rl];
-            if (sizeof(T) == 1) x = x != 0.0 ? 1.0 : 0.0;
-            x = v ? x : fill;
-            if (out_pos != nullptr) {  // column selection: every output column has its own position (or -1)
-                const int px = out_pos[TRACK ? 2 * c : c];
-                if (px >= 0) out[r * out_ld + px] = x;
-                if (TRACK) {
-                    const int pq = out_pos[2 * c + 1];
-                    if (pq >= 0) out[r * out_ld + pq] = v ? 0.0 : 1.0;
-                }
-            } else if (TRACK) {
-                stg_stream(reinterpret_cast<double2*>(out + r * out_ld + out_col0 + 2 * c),
-                           make_double2(x, v ? 0.0 : 1.0));
-            } else {
-                out[r * out_ld + out_col0 + c] = x;
+        for (int k = 0; k < 4; ++k) {
+            const int cl = warp + 8 * k;
+            if (cl < tc) {
+                const int c = c0 + cl;
+                const T* col = values + (int64_t)c * ld + r0;
+                tile[cl][lane] = lane < rows_here ? (double)col[lane] : 0.0;
+                tile[cl][lane + 32] = lane + 32 < rows_here ? (double)col[lane + 32] : 0.0;
+                if (lane == 0) vbits[cl] = valid ? valid[(int64_t)c * ldv + (r0 >> 6)] : ~0ull;
             }
         }
+        __syncthreads();
+#pragma unroll 1
+        for (int h = 0; h < PER; ++h) {
+            const int src = lane + 32 * h;      // emitted column of the tile served by this lane
+            if (src >= tc * PER) continue;
+            const int cl = TRACK ? (src >> 1) : src;
+            const bool is_ind = TRACK && (src & 1);
+            const double fill = fills ? fills[c0 + cl] : fill_const;
+            const unsigned long long vb = vbits[cl];
+            const double* trow = &tile[cl][warp];
+            double* optr = out + (r0 + warp) * out_ld + out_col0 + c0 * PER + src;
+            const int64_t ostep = 8 * out_ld;
+#pragma unroll 4
+            for (int k = 0; k < 8; ++k) {
+                const int rl = warp + 8 * k;
+                if (rl < rows_here) {
+                    const bool v = (vb >> rl) & 1ull;
+                    double x = trow[8 * k];
+                    if (sizeof(T) == 1) x = x != 0.0 ? 1.0 : 0.0;
+                    *optr = is_ind ? (v ? 0.0 : 1.0) : (v ? x : fill);
+                }
+                optr += ostep;
+            }
+        }
+    }
+}
+
+// vec_transform_select_kernel: only the columns that survive SanityChecker are written, packed (keep_mask: bit i set
+// <=> emitted column i is kept).  Lane = row on the load side; every value goes straight to its OUTPUT position in a
+// shared-memory ring of row buffers (the transpose); after each tile the warps flush whole 32-byte-aligned groups of
+// every row with contiguous 256-byte stores and carry the (< 4 values) tail to the next tile, so that DRAM only sees
+// full-sector writes although a dropped column shifts everything behind it by an odd number of slots.
+constexpr int TR_ROWS = 64;
+constexpr int TR_RING = 72;     // >= 3 carried + 64 new positions
+constexpr int TR_STRIDE = 73;   // odd row stride: lane = row accesses are bank-conflict free
+
+template <typename T, bool TRACK>
+__global__ void __launch_bounds__(256)
+vec_transform_select_kernel(const T* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid,
+                            int64_t ldv, int64_t n, int ncols, const double* __restrict__ fills, double fill_const,
+                            double* __restrict__ out, int64_t out_ld, int64_t out_col0,
+                            const unsigned long long* __restrict__ keep_mask) {
+    __shared__ double ring[TR_ROWS * TR_STRIDE];
+    constexpr int PER = TRACK ? 2 : 1;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t r0 = (int64_t)blockIdx.x * TR_ROWS;
+    const int rows_here = (int)min((int64_t)TR_ROWS, n - r0);
+    const int ntiles = (ncols + 31) / 32;
+    // the output block may start anywhere in the row; flush groups are aligned on the actual addresses
+    const int mis = (int)(((reinterpret_cast<uintptr_t>(out) >> 3) + (uintptr_t)out_col0) & 3u);
+    const bool rows_aligned = (out_ld & 3) == 0;
+    int plo = 0;    // packed output position of the tile's first kept column
+    int base = 0;   // first position not yet flushed
+    int ring0 = 0;  // multiple of TR_RING <= base: slot(p) = p - ring0, minus TR_RING once past the end
+    for (int t = 0; t < ntiles; ++t) {
+        const int c0 = t * 32;
+        const int tc = min(32, ncols - c0);
+        const int nbits = tc * PER;
+        unsigned long long m = nbits == 64 ? ~0ull : ((1ull << nbits) - 1ull);
+        const unsigned long long w = keep_mask[(c0 * PER) >> 6];
+        m &= TRACK ? w : (w >> ((c0 * PER) & 63));
+        const int cnt = __popcll(m);
+        // ---- load + transpose: warp w takes columns w, w+8, w+16, w+24 of the tile; lane = row (and row + 32)
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int cl = warp + 8 * k;
+            if (cl < tc) {
+                const int c = c0 + cl;
+                const unsigned long long mx = TRACK ? (m >> (2 * cl)) & 3ull : (m >> cl) & 1ull;
+                if (mx == 0) continue;  // the whole input column was dropped: never read it
+                const T* col = values + (int64_t)c * ld + r0;
+                const unsigned long long vb = valid ? valid[(int64_t)c * ldv + (r0 >> 6)] : ~0ull;
+                const double fill = fills ? fills[c] : fill_const;
+                int px = plo + __popcll(m & ((1ull << (PER * cl)) - 1ull)) - ring0;  // slot of the value column
+                int pq = px + (int)(mx & 1ull);                                       // slot of the null indicator
+                px -= px >= TR_RING ? TR_RING : 0;
+                pq -= pq >= TR_RING ? TR_RING : 0;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int rl = lane + 32 * h;
+                    double x = rl < rows_here ? (double)col[rl] : 0.0;
+                    if (sizeof(T) == 1) x = x != 0.0 ? 1.0 : 0.0;
+                    const bool v = (vb >> rl) & 1ull;
+                    if (mx & 1ull) ring[rl * TR_STRIDE + px] = v ? x : fill;
+                    if (TRACK && (mx & 2ull)) ring[rl * TR_STRIDE + pq] = v ? 0.0 : 1.0;
+                }
+            }
+        }
+        __syncthreads();
+        // ---- flush [base, hi): everything up to the last 32-byte boundary, or to the end on the last tile
+        const int end = plo + cnt;
+        int hi = end;
+        if (t + 1 < ntiles && rows_aligned) hi = ((end + mis) & ~3) - mis;
+        if (hi > base) {
+#pragma unroll 2
+            for (int k = 0; k < TR_ROWS / 8; ++k) {
+                const int rl = warp + 8 * k;
+                if (rl < rows_here) {
+                    double* orow = out + (r0 + rl) * out_ld + out_col0;
+                    const double* rrow = ring + rl * TR_STRIDE;
+                    for (int p = base + lane; p < hi; p += 32) {
+                        int sl = p - ring0;
+                        sl -= sl >= TR_RING ? TR_RING : 0;
+                        orow[p] = rrow[sl];
+                    }
+                }
+            }
+            base = hi;
+            if (base - ring0 >= TR_RING) ring0 += TR_RING;
+        }
+        plo = end;
+        if (t + 1 < ntiles) __syncthreads();  // ring slots of flushed positions are reused by the next tile
     }
 }
 
@@ -400,27 +491,32 @@ extern "C" int tmog_real_finish(const double* partials, const double* shifts, in
 template <typename T>
 static int launch_transform(const T* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n, int ncols,
                             const double* fills, double fill_const, int track_nulls, double* out, int64_t out_ld,
-                            int64_t out_col0, void* stream, const int32_t* out_pos = nullptr) {
+                            int64_t out_col0, void* stream, const uint64_t* keep = nullptr, int nkeep = 0) {
     if (int rc = check_columns(values, ld, valid, ldv, n, ncols, (int)sizeof(T))) return rc;
-    const int64_t width = (int64_t)ncols * (track_nulls ? 2 : 1);
-    TMOG_REQUIRE(out != nullptr || n == 0 || ncols == 0, "out is NULL");
-    TMOG_REQUIRE(out_pos != nullptr || (out_col0 >= 0 && out_ld >= out_col0 + width),
-                 "output block [%lld, %lld) exceeds row stride %lld", (long long)out_col0,
-                 (long long)(out_col0 + width), (long long)out_ld);
-    if (track_nulls && out_pos == nullptr)
-        TMOG_REQUIRE(aligned16(out) && (out_ld & 1) == 0 && (out_col0 & 1) == 0,
-                     "tracked output needs a 16-byte aligned block: out pointer, even out_ld and even out_col0");
-    if (n == 0 || ncols == 0) return TMOG_OK;
+    const int64_t width = keep ? nkeep : (int64_t)ncols * (track_nulls ? 2 : 1);
+    TMOG_REQUIRE(out != nullptr || n == 0 || width == 0, "out is NULL");
+    TMOG_REQUIRE(out_col0 >= 0 && out_ld >= out_col0 + width, "output block [%lld, %lld) exceeds row stride %lld",
+                 (long long)out_col0, (long long)(out_col0 + width), (long long)out_ld);
+    if (n == 0 || ncols == 0 || width == 0) return TMOG_OK;
     const int64_t gx = (n + 63) / 64;
     TMOG_REQUIRE(gx <= 0x7fffffffLL, "too many rows for one transform call (%lld): chunk the batch", (long long)n);
-    dim3 grid((unsigned)gx, (unsigned)((ncols + 31) / 32));
     cudaStream_t st = (cudaStream_t)stream;
-    if (track_nulls)
-        vec_transform_kernel<T, true><<<grid, 256, 0, st>>>(values, ld, valid, ldv, n, ncols, fills, fill_const, out,
-                                                             out_ld, out_col0, out_pos);
-    else
-        vec_transform_kernel<T, false><<<grid, 256, 0, st>>>(values, ld, valid, ldv, n, ncols, fills, fill_const, out,
-                                                              out_ld, out_col0, out_pos);
+    const unsigned long long* km = reinterpret_cast<const unsigned long long*>(keep);
+    if (km == nullptr) {
+        if (track_nulls)
+            vec_transform_kernel<T, true><<<(unsigned)gx, 256, 0, st>>>(values, ld, valid, ldv, n, ncols, fills,
+                                                                         fill_const, out, out_ld, out_col0);
+        else
+            vec_transform_kernel<T, false><<<(unsigned)gx, 256, 0, st>>>(values, ld, valid, ldv, n, ncols, fills,
+                                                                          fill_const, out, out_ld, out_col0);
+    } else {
+        if (track_nulls)
+            vec_transform_select_kernel<T, true><<<(unsigned)gx, 256, 0, st>>>(
+                values, ld, valid, ldv, n, ncols, fills, fill_const, out, out_ld, out_col0, km);
+        else
+            vec_transform_select_kernel<T, false><<<(unsigned)gx, 256, 0, st>>>(
+                values, ld, valid, ldv, n, ncols, fills, fill_const, out, out_ld, out_col0, km);
+    }
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }
@@ -442,17 +538,19 @@ extern "C" int tmog_binary_transform_dev(const uint8_t* values, int64_t ld, cons
 
 extern "C" int tmog_real_transform_select_dev(const double* values, int64_t ld, const uint64_t* valid, int64_t ldv,
                                               int64_t n, int ncols, const double* fills, int track_nulls,
-                                              const int32_t* out_pos, double* out, int64_t out_ld, void* stream) {
+                                              const uint64_t* keep_mask, int nkeep, double* out, int64_t out_ld,
+                                              int64_t out_col0, void* stream) {
     TMOG_REQUIRE(fills != nullptr || valid == nullptr, "fills is NULL but the columns are nullable");
-    TMOG_REQUIRE(out_pos != nullptr, "out_pos is NULL");
-    return launch_transform<double>(values, ld, valid, ldv, n, ncols, fills, 0.0, track_nulls, out, out_ld, 0, stream,
-                                    out_pos);
+    TMOG_REQUIRE(keep_mask != nullptr && nkeep >= 0, "keep_mask is NULL");
+    return launch_transform<double>(values, ld, valid, ldv, n, ncols, fills, 0.0, track_nulls, out, out_ld, out_col0,
+                                    stream, keep_mask, nkeep);
 }
 
 extern "C" int tmog_binary_transform_select_dev(const uint8_t* values, int64_t ld, const uint64_t* valid, int64_t ldv,
                                                 int64_t n, int ncols, int fill_value, int track_nulls,
-                                                const int32_t* out_pos, double* out, int64_t out_ld, void* stream) {
-    TMOG_REQUIRE(out_pos != nullptr, "out_pos is NULL");
+                                                const uint64_t* keep_mask, int nkeep, double* out,
+                                                int64_t out_ld, int64_t out_col0, void* stream) {
+    TMOG_REQUIRE(keep_mask != nullptr && nkeep >= 0, "keep_mask is NULL");
     return launch_transform<uint8_t>(values, ld, valid, ldv, n, ncols, nullptr, fill_value ? 1.0 : 0.0, track_nulls,
-                                     out, out_ld, 0, stream, out_pos);
+                                     out, out_ld, out_col0, stream, keep_mask, nkeep);
 }

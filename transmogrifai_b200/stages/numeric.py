@@ -231,32 +231,37 @@ def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_n
     n, ncols = block.n, len(block.names)
     w_full = ncols * (2 if track_nulls else 1)
     binary = block.values.dtype == torch.uint8
-    pos = None
+    kp = None
     w = w_full
     if keep is not None:
-        pos = np.full(w_full, -1, dtype=np.int32)
-        pos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
-        w = len(keep)
+        kp = np.asarray(keep, dtype=np.int32)
+        if len(kp) > 1 and not (np.diff(kp) > 0).all():
+            raise ValueError("kept columns must be ascending")
+        w = len(kp)
     if block.is_cuda:
-        out = torch.empty((n, round_up(max(w, 1), 2)), dtype=torch.float64, device="cuda")
-        d_pos = None if pos is None else torch.from_numpy(pos).cuda()
+        out = torch.empty((n, round_up(max(w, 1), 4)), dtype=torch.float64, device="cuda")   # 32-byte aligned rows
+        d_keep = None
+        if kp is not None:
+            bits = np.zeros(round_up(w_full, 64), dtype=np.uint8)
+            bits[kp] = 1
+            d_keep = torch.from_numpy(np.packbits(bits, bitorder="little").view("<i8").copy()).cuda()
         if binary:
-            if pos is None:
+            if kp is None:
                 L.call("tmog_binary_transform_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
                        n, ncols, int(fill_value), int(track_nulls), out.data_ptr(), out.shape[1], 0, R.stream())
             else:
                 L.call("tmog_binary_transform_select_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid),
-                       block.ldv, n, ncols, int(fill_value), int(track_nulls), d_pos.data_ptr(), out.data_ptr(),
-                       out.shape[1], R.stream())
+                       block.ldv, n, ncols, int(fill_value), int(track_nulls), d_keep.data_ptr(), w, out.data_ptr(),
+                       out.shape[1], 0, R.stream())
         else:
             d_fills = None if fills is None else torch.from_numpy(fills).cuda()
-            if pos is None:
+            if kp is None:
                 L.call("tmog_real_transform_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
                        n, ncols, R.ptr(d_fills), int(track_nulls), out.data_ptr(), out.shape[1], 0, R.stream())
             else:
                 L.call("tmog_real_transform_select_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid),
-                       block.ldv, n, ncols, R.ptr(d_fills), int(track_nulls), d_pos.data_ptr(), out.data_ptr(),
-                       out.shape[1], R.stream())
+                       block.ldv, n, ncols, R.ptr(d_fills), int(track_nulls), d_keep.data_ptr(), w, out.data_ptr(),
+                       out.shape[1], 0, R.stream())
         return out[:, :w]
     if binary:
         dev = block.to("cuda")
@@ -264,7 +269,7 @@ def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_n
     out = torch.empty((n, w), dtype=torch.float64, pin_memory=True)
     L.call("tmog_real_transform_host", R.ctx(), block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv, n,
            ncols, None if fills is None else fills.ctypes.data, int(track_nulls), chunk_rows,
-           None if pos is None else pos.ctypes.data, w, out.data_ptr(), w, 0)
+           None if kp is None else kp.ctypes.data, w, out.data_ptr(), w, 0)
     return out
 
 
