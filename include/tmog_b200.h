@@ -70,6 +70,19 @@ int tmog_real_fit_partials_dev(const double* values, int64_t ld, const uint64_t*
                                const double* label, int64_t n, int ncols, const double* shifts,
                                void* scratch, size_t scratch_bytes, double* partials, void* stream);
 
+/* tmog_real_fit_partials_dev for callers that cannot allocate device memory.  No counterpart in the reference: this
+ * entry point exists for hosts such as a JNI shim in a Spark executor whose GPU memory belongs to another
+ * component's pool, so that a side cudaMalloc fails or is not allowed and the shim owns nothing on the device but
+ * the partition's input and output buffers.  The per-CTA scratch is a fixed 4 MiB array built into the library
+ * (held by every GPU that loads it, until exit), which caps a call at (4 MiB / (64 B x 2 x SMs)) - 1 columns --
+ * 220 on a B200; wider blocks return TMOG_EINVAL with a message naming the limit.  Same inputs, outputs and results
+ * as tmog_real_fit_partials_dev.  The first call on each device resolves the array's address and should be made
+ * outside stream capture; all calls on a device share the array, so calls that overlap on the GPU race -- serialise
+ * them.  Never calls cudaMalloc / cudaFree. */
+int tmog_real_fit_partials_noalloc_dev(const double* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                       const double* label, int64_t n, int ncols, const double* shifts,
+                                       double* partials, void* stream);
+
 /* acc += other for two partial blocks taken with the same shifts (the Aggregator.merge of
  * U/spark/SequenceAggregators.scala:83 and the treeAggregate combOps of SanityChecker's statistics). Host memory. */
 int tmog_real_partials_merge(double* acc, const double* other, int ncols);

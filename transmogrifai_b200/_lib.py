@@ -43,6 +43,7 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_real_pilot_shift_dev": [_p, _i64, _p, _i64, _p, _i64, _int, _p, _p],
     "tmog_real_fit_scratch_bytes": [_int, C.POINTER(_sz)],
     "tmog_real_fit_partials_dev": [_p, _i64, _p, _i64, _p, _i64, _int, _p, _p, _sz, _p, _p],
+    "tmog_real_fit_partials_noalloc_dev": [_p, _i64, _p, _i64, _p, _i64, _int, _p, _p, _p],
     "tmog_real_partials_merge": [_p, _p, _int],
     "tmog_real_finish": [_p, _p, _int, _int, _dbl, _int, _p, _p, _p, _p, _p, _p, _p, _p],
     "tmog_real_transform_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _int, _p, _i64, _i64, _p],

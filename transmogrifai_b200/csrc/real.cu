@@ -554,3 +554,76 @@ extern "C" int tmog_binary_transform_select_dev(const uint8_t* values, int64_t l
     return launch_transform<uint8_t>(values, ld, valid, ldv, n, ncols, nullptr, fill_value ? 1.0 : 0.0, track_nulls,
                                      out, out_ld, out_col0, stream, keep_mask, nkeep);
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of tmog_real_fit_partials_dev.
+//
+// Some hosts of this library cannot give us device memory of their own.  The typical one is a JNI shim inside a Spark
+// executor whose GPU is already managed by a memory pool (a columnar accelerator plugin, say) that has claimed nearly
+// all of HBM up front: a cudaMalloc made on the side fails or is forbidden by policy there, and the shim's only
+// device buffers are the partition's inputs and outputs, which the pool handed it.  It has nowhere to get the few
+// hundred KiB that the fit kernel wants for its per-CTA partials.  For such callers the scratch lives in this file,
+// in a file-scope __device__ array of fixed size that every GPU loading the library holds until the process exits.
+//
+// Notes for callers
+//   * limit: TMOG_NOALLOC_SCRATCH_BYTES (4 MiB).  The kernel needs  CTAs x (ncols + 1) x 64 bytes, CTAs = 2 x SMs
+//     (296 on a B200), i.e. at most 220 columns per call on a B200; wider blocks are rejected with TMOG_EINVAL and a
+//     message that names the limit -- split the block, partials of column sub-blocks are independent.
+//   * the first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
+//     current).  Make that first call outside any stream capture.
+//   * every call on a device uses the same array.  Nothing in it has to start at zero (each CTA rewrites its whole
+//     slot before the reduce kernel reads it) and a call leaves its partials behind, but two calls that overlap on
+//     the GPU -- different streams, or different host threads on the same device -- race on it.  Serialise them.
+//   * nothing here calls cudaMalloc / cudaFree or an allocating library routine.
+// ---------------------------------------------------------------------------------------------------------------------
+#define TMOG_NOALLOC_SCRATCH_BYTES (4u << 20)
+
+static __device__ __align__(256) double g_noalloc_fit_scratch[TMOG_NOALLOC_SCRATCH_BYTES / sizeof(double)];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+// Device address of the scratch array on the CURRENT device.  In host code the symbol's name is only a stand-in;
+// the kernel must be given the address cudaGetSymbolAddress returns.
+int noalloc_scratch(double** out) {
+    int dev = 0;
+    TMOG_CUDA(cudaGetDevice(&dev));
+    TMOG_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "device index %d not supported", dev);
+    if (g_noalloc_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        TMOG_CUDA(cudaGetSymbolAddress(&p, g_noalloc_fit_scratch));
+        TMOG_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+        g_noalloc_ptr[dev] = static_cast<double*>(p);   // idempotent: racing first calls store the same value
+    }
+    *out = g_noalloc_ptr[dev];
+    return TMOG_OK;
+}
+}  // namespace
+
+extern "C" int tmog_real_fit_partials_noalloc_dev(const double* values, int64_t ld, const uint64_t* valid,
+                                                  int64_t ldv, const double* label, int64_t n, int ncols,
+                                                  const double* shifts, double* partials, void* stream) {
+    if (int rc = check_columns(values, ld, valid, ldv, n, ncols, 8)) return rc;
+    TMOG_REQUIRE(label != nullptr || n == 0, "label is NULL");
+    TMOG_REQUIRE(aligned16(label), "label must be 16-byte aligned");
+    TMOG_REQUIRE(shifts != nullptr && partials != nullptr, "shifts / partials is NULL");
+    const int grid = fit_grid();
+    const size_t need = sizeof(double) * (size_t)grid * (size_t)(ncols + 1) * NS;
+    const int max_cols = (int)(TMOG_NOALLOC_SCRATCH_BYTES / (sizeof(double) * (size_t)grid * NS)) - 1;
+    TMOG_REQUIRE(need <= TMOG_NOALLOC_SCRATCH_BYTES,
+                 "tmog_real_fit_partials_noalloc_dev: %d columns need %zu bytes of scratch but the built-in scratch "
+                 "is %u bytes (at most %d columns per call on this device): split the column block or use "
+                 "tmog_real_fit_partials_dev with caller-provided scratch",
+                 ncols, need, (unsigned)TMOG_NOALLOC_SCRATCH_BYTES, max_cols);
+    const size_t smem = fit_smem_bytes(ncols);
+    TMOG_REQUIRE(smem <= 48 * 1024, "too many columns for one allocation-free fit call (%d)", ncols);
+    double* scratch = nullptr;
+    if (int rc = noalloc_scratch(&scratch)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    real_fit_kernel<<<grid, FIT_THREADS, smem, st>>>(values, ld, valid, ldv, label, n, ncols, shifts, scratch);
+    TMOG_LAUNCH_CHECK();
+    real_fit_reduce_kernel<<<ncols + 1, 32, 0, st>>>(scratch, grid, ncols, n, partials);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
