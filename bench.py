@@ -132,6 +132,8 @@ def build_plan(feats, label):
 
 def run_step(batch, checked):
     from transmogrifai_b200.dsl import fit_and_transform
+    batch.__dict__.pop("_label_cache", None)   # label classes are part of the step: never reuse a previous step's
+    batch.__dict__.pop("_label_dev", None)
     out, fitted = fit_and_transform(batch, checked)
     vec = out.vectors[checked.name]
     for p in vec.parts:           # the transform is lazy until somebody reads the vector: read it

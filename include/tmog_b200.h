@@ -203,6 +203,14 @@ int tmog_pearson_from_gram(int D, double n, const double* gram, const double* su
 int tmog_contingency_stats(const double* matrix, int rows, int cols, double* cramers_v, double* chi2,
                            double* mutual_info, double* pmi, double* max_conf, double* supports);
 
+/* tmog_contingency_stats for every categorical feature group of a vector in one call: matrix g is rows[g] x cols[g]
+ * row-major at data + offsets[g]; pmi uses the layout of data; max_conf / supports are packed by row starting at
+ * row_offsets[g]; status[g] = 0, or 1 when group g is empty after filtering. */
+int tmog_contingency_stats_batch(int ngroups, const int32_t* rows, const int32_t* cols, const int64_t* offsets,
+                                 const int64_t* row_offsets, const double* data, double* cramers_v, double* chi2,
+                                 double* mutual_info, double* pmi, double* max_conf, double* supports,
+                                 int32_t* status);
+
 /* corr_i = cov_i / (sqrt(var_i) sqrt(var_y) (n - 1)), 0/0 kept as NaN  (U/stats/OpStatistics.scala:92-94). */
 int tmog_pearson_from_cov(int d, double n, const double* cov_label, const double* variance, double label_variance,
                           double* corr);

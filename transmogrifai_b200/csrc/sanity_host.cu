@@ -204,3 +204,23 @@ extern "C" int tmog_pearson_from_cov(int d, double n, const double* cov_label, c
     for (int i = 0; i < d; ++i) corr[i] = cov_label[i] / (sqrt(variance[i]) * sy * (n - 1.0));  // 0/0 -> NaN kept
     return TMOG_OK;
 }
+
+// Many contingency matrices in one call (one per categorical feature group): matrix g is rows[g] x cols[g] row-major at
+// data + offsets[g]; pmi has the layout of data; max_conf / supports are packed by row (row_offsets[g] = sum of rows
+// before g).  status[g] = the return value tmog_contingency_stats would give (0, or 1 for "empty after filtering").
+extern "C" int tmog_contingency_stats_batch(int ngroups, const int32_t* rows, const int32_t* cols,
+                                            const int64_t* offsets, const int64_t* row_offsets, const double* data,
+                                            double* cramers_v, double* chi2, double* mutual_info, double* pmi,
+                                            double* max_conf, double* supports, int32_t* status) {
+    TMOG_REQUIRE(ngroups >= 0 && (ngroups == 0 || (rows && cols && offsets && row_offsets && data)), "NULL argument");
+    for (int g = 0; g < ngroups; ++g) {
+        const int rc = tmog_contingency_stats(data + offsets[g], rows[g], cols[g], cramers_v ? cramers_v + g : nullptr,
+                                              chi2 ? chi2 + g : nullptr, mutual_info ? mutual_info + g : nullptr,
+                                              pmi ? pmi + offsets[g] : nullptr,
+                                              max_conf ? max_conf + row_offsets[g] : nullptr,
+                                              supports ? supports + row_offsets[g] : nullptr);
+        if (rc < 0) return rc;
+        if (status) status[g] = rc;
+    }
+    return TMOG_OK;
+}

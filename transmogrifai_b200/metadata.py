@@ -82,7 +82,7 @@ class OpVectorMetadata:
     def __init__(self, name: str, columns: Iterable[OpVectorColumnMetadata],
                  history: Optional[Dict[str, Sequence[str]]] = None):
         self.name = name
-        self.columns = [replace(c, index=i) for i, c in enumerate(columns)]   # OpVectorMetadata.scala:62
+        self.columns = [c if c.index == i else replace(c, index=i) for i, c in enumerate(columns)]  # :62
         self.history = {k: tuple(v) for k, v in (history or {}).items()}
 
     @property

@@ -23,7 +23,11 @@ class VectorsCombiner(OpEstimator):
 
     def fit(self, batch: ColumnarBatch) -> "VectorsCombinerModel":
         vecs = [batch.vectors[f.name] for f in self.inN]
-        self._metadata = OpVectorMetadata.flatten(self.getOutputFeatureName(), [v.metadata for v in vecs])
+        key = tuple(id(v.metadata) for v in vecs)
+        if getattr(self, "_flat_key", None) != key:      # same input metadata objects: same flattened metadata
+            self._flat = OpVectorMetadata.flatten(self.getOutputFeatureName(), [v.metadata for v in vecs])
+            self._flat_key, self._flat_src = key, [v.metadata for v in vecs]   # keep the sources alive (ids stay valid)
+        self._metadata = self._flat
         return VectorsCombinerModel(self)
 
 

@@ -24,6 +24,14 @@ MAX_LABEL_CLASSES = 100   # SanityChecker.scala:279 -- categorical iff distinct 
 
 
 def _numeric_metadata(stage, track_nulls: bool) -> OpVectorMetadata:
+    key = (tuple(f.name for f in stage.inN), track_nulls)
+    cache = stage.__dict__.setdefault("_meta_cache", {})
+    if key not in cache:
+        cache[key] = _build_numeric_metadata(stage, track_nulls)
+    return cache[key]
+
+
+def _build_numeric_metadata(stage, track_nulls: bool) -> OpVectorMetadata:
     cols = []
     for f in stage.inN:
         cols.append(feature_column(f.name, f.type_name))

@@ -220,11 +220,14 @@ class SanityChecker(OpEstimator):
             cat_stats = self._categorical_tests(meta, st)
         # decision ----------------------------------------------------------------------------------------------
         drop, reasons, pc, pv = self._decide(meta, st, corr, corr_indices, corr_matrix, cat_stats)
-        names = meta.columnNames()
+        names = self._plan(meta).names
         to_drop = [names[i] for i in range(d) if drop[i]] if self.removeBadFeatures else []
         keep = [i for i in range(d) if not (drop[i] and self.removeBadFeatures)]
-        out_meta = OpVectorMetadata(self.getOutputFeatureName(), [cols[i] for i in keep], meta.history)
-        self._metadata = out_meta
+        key = (id(meta), tuple(keep))
+        if getattr(self, "_out_meta_key", None) != key:     # same input metadata and keep set: same output metadata
+            self._out_meta = OpVectorMetadata(self.getOutputFeatureName(), [cols[i] for i in keep], meta.history)
+            self._out_meta_key = key
+        self._metadata = self._out_meta
         self.summary = SanityCheckerSummary(
             names=names + [label_f.name], count=n, mean=np.append(st.mean, lab.stats[1]),
             variance=np.append(st.variance, lab.stats[2]), min=np.append(st.min, lab.stats[3]),
@@ -238,85 +241,81 @@ class SanityChecker(OpEstimator):
                              "input data quality")
         return SanityCheckerModel(self, keep, self.removeBadFeatures)
 
+    @staticmethod
+    def _plan(meta: OpVectorMetadata) -> "_MetaPlan":
+        plan = meta.__dict__.get("_sanity_plan")
+        if plan is None:
+            plan = _MetaPlan(meta)
+            meta.__dict__["_sanity_plan"] = plan
+        return plan
+
     def _categorical_tests(self, meta: OpVectorMetadata, st: VectorStats) -> List[CategoricalGroupStats]:
+        """SanityChecker.categoricalTests :252-348 -- contingency matrices from the per-class column sums, then one
+        batched tmog_contingency_stats call."""
+        plan = self._plan(meta)
+        if not plan.groups:
+            return []
+        if plan.has_mpl:
+            raise NotImplementedError("MultiPickList contingency statistics are not on the GPU path yet")
         counts = st.label.class_counts.astype(np.float64)
-        groups: Dict[str, list] = {}
-        for c in meta.columns:
-            if c.grouping is not None and c.indicatorValue is not None:
-                groups.setdefault(c.featureGroup(), []).append(c)
+        L_ = len(counts)
+        sums = st.class_sums[:, plan.cat_cols]                    # [L, total categorical columns]
+        if np.isnan(sums).any():
+            raise ValueError("no per-label sums were tracked for some categorical group")
+        # rows of every group, packed: lone indicators contribute [indicator; complement]
+        data = np.empty(plan.total_rows * L_)
+        mats = data.reshape(plan.total_rows, L_)
+        mats[plan.row_of_col] = sums.T
+        if len(plan.lone_rows):
+            mats[plan.lone_rows + 1] = counts[None, :] - mats[plan.lone_rows]
+        ng = len(plan.groups)
+        cols = np.full(ng, L_, dtype=np.int32)
+        offsets = plan.row_offsets * L_
+        v, chi, mi = np.zeros(ng), np.zeros(ng), np.zeros(ng)
+        pmi = np.zeros(plan.total_rows * L_)
+        conf, sup = np.zeros(plan.total_rows), np.zeros(plan.total_rows)
+        status = np.zeros(ng, dtype=np.int32)
+        L.call("tmog_contingency_stats_batch", ng, plan.rows.ctypes.data, cols.ctypes.data, offsets.ctypes.data,
+               plan.row_offsets.ctypes.data, data.ctypes.data, v.ctypes.data, chi.ctypes.data, mi.ctypes.data,
+               pmi.ctypes.data, conf.ctypes.data, sup.ctypes.data, status.ctypes.data)
+        pm = pmi.reshape(plan.total_rows, L_)
         out = []
-        for g, cols in groups.items():
-            seen, cleaned = set(), []
-            for c in cols:                       # duplicate indicator values: only the first is used (:295-298)
-                if c.indicatorValue not in seen:
-                    seen.add(c.indicatorValue)
-                    cleaned.append(c)
-            idx = [c.index for c in cleaned]
-            sums = st.class_sums[:, idx]         # [L, k]
-            if np.isnan(sums).any():
-                raise ValueError(f"no per-label sums were tracked for categorical group {g}")
-            if any(c.isMultiPickList for c in cleaned):
-                raise NotImplementedError("MultiPickList contingency statistics are not on the GPU path yet")
-            if len(idx) == 1:
-                mat = np.stack([sums[:, 0], counts - sums[:, 0]])       # 2 x L
-            else:
-                mat = sums.T.copy()                                     # k x L
-            mat = np.ascontiguousarray(mat, dtype=np.float64)
-            r, c_ = mat.shape
-            v, chi, mi = (np.zeros(1) for _ in range(3))
-            pmi = np.zeros(r * c_)
-            conf, sup = np.zeros(r), np.zeros(r)
-            rc = L.lib().tmog_contingency_stats(mat.ctypes.data, r, c_, v.ctypes.data, chi.ctypes.data,
-                                                mi.ctypes.data, pmi.ctypes.data, conf.ctypes.data, sup.ctypes.data)
-            if rc < 0:
-                L.check(rc)
-            if rc == 1:
-                conf, sup = np.zeros(0), np.zeros(0)
-            out.append(CategoricalGroupStats(g, [c.makeColName() for c in cleaned], mat, float(v[0]), float(mi[0]),
-                                             pmi.reshape(r, c_), conf, sup))
+        for g, (name, col_names, _idx) in enumerate(plan.groups):
+            a, b = plan.row_offsets[g], plan.row_offsets[g] + plan.rows[g]
+            empty = status[g] == 1
+            out.append(CategoricalGroupStats(name, col_names, mats[a:b], float(v[g]), float(mi[g]), pm[a:b],
+                                             np.zeros(0) if empty else conf[a:b], np.zeros(0) if empty else sup[a:b]))
         return out
 
     def _decide(self, meta, st, corr, corr_indices, corr_matrix, cat_stats):
         d = meta.size
-        pos = {ci: k for k, ci in enumerate(corr_indices)}
-        corr_pos = np.array([pos.get(i, -1) for i in range(d)], dtype=np.int32)
-        parent_ids: Dict[str, int] = {}
-        group_ids: Dict[str, int] = {}
-        offs, pids = [0], []
-        gid = np.full(d, -1, dtype=np.int32)
-        tsh = np.zeros(d, dtype=np.uint8)
-        for c in meta.columns:
-            for pn in c.parentNamesWithMapKeys():
-                pids.append(parent_ids.setdefault(pn, len(parent_ids)))
-            offs.append(len(pids))
-            g = c.featureGroup()
-            if g is not None:
-                gid[c.index] = group_ids.setdefault(g, len(group_ids))
-            tsh[c.index] = c.isTextSharedHash
-        name_to_idx = {c.makeColName(): c.index for c in meta.columns}
+        plan = self._plan(meta)
+        if len(corr_indices) == d + 1:
+            corr_pos = plan.identity_pos
+        else:
+            pos = {ci: k for k, ci in enumerate(corr_indices)}
+            corr_pos = np.array([pos.get(i, -1) for i in range(d)], dtype=np.int32)
         cram = np.full(d, np.nan)
         rule_n = np.full(d, -1, dtype=np.int32)
         rconf, rsup = np.zeros(2 * d), np.zeros(2 * d)
-        for g in cat_stats:
-            lone = len(g.categoricalFeatures) == 1
-            for k, nm in enumerate(g.categoricalFeatures):
-                i = name_to_idx[nm]
-                cram[i] = g.cramersV
-                if lone:
-                    m = min(2, len(g.maxRuleConfidences))
-                    rule_n[i] = m
-                    rconf[2 * i:2 * i + m] = g.maxRuleConfidences[:m]
-                    rsup[2 * i:2 * i + m] = g.supports[:m]
-                else:
-                    has = k < len(g.maxRuleConfidences)
-                    rule_n[i] = 1 if has else 0
-                    if has:
-                        rconf[2 * i], rsup[2 * i] = g.maxRuleConfidences[k], g.supports[k]
+        for g, (_name, _cn, idx) in zip(cat_stats, plan.groups):
+            cram[idx] = g.cramersV
+            if len(idx) == 1:
+                i = idx[0]
+                m = min(2, len(g.maxRuleConfidences))
+                rule_n[i] = m
+                rconf[2 * i:2 * i + m] = g.maxRuleConfidences[:m]
+                rsup[2 * i:2 * i + m] = g.supports[:m]
+            else:
+                k = len(g.maxRuleConfidences)
+                ia = np.asarray(idx)
+                rule_n[ia] = 0
+                rule_n[ia[:k]] = 1
+                rconf[2 * ia[:k]] = g.maxRuleConfidences
+                rsup[2 * ia[:k]] = g.supports
         params = np.array([self.minVariance, self.minCorrelation, self.maxCorrelation, self.maxFeatureCorrelation,
                            self.maxCramersV, self.maxRuleConfidence, self.minRequiredRuleSupport,
                            float(self.removeFeatureGroup), float(self.protectTextSharedHash)])
-        offs = np.asarray(offs, dtype=np.int32)
-        pids = np.asarray(pids, dtype=np.int32)
         drop = np.zeros(d, dtype=np.uint8)
         reasons = np.zeros(d, dtype=np.uint32)
         pc, pv = np.zeros(d), np.zeros(d)
@@ -324,11 +323,67 @@ class SanityChecker(OpEstimator):
         corr = np.ascontiguousarray(corr, dtype=np.float64)
         cm = None if corr_matrix is None else np.ascontiguousarray(corr_matrix, dtype=np.float64)
         L.call("tmog_sanity_decide", d, var.ctypes.data, corr.ctypes.data, None if cm is None else cm.ctypes.data,
-               0 if cm is None else cm.shape[0], corr_pos.ctypes.data, offs.ctypes.data, pids.ctypes.data,
-               gid.ctypes.data, tsh.ctypes.data, cram.ctypes.data, rule_n.ctypes.data, rconf.ctypes.data,
+               0 if cm is None else cm.shape[0], corr_pos.ctypes.data, plan.offs.ctypes.data, plan.pids.ctypes.data,
+               plan.gid.ctypes.data, plan.tsh.ctypes.data, cram.ctypes.data, rule_n.ctypes.data, rconf.ctypes.data,
                rsup.ctypes.data, params.ctypes.data, drop.ctypes.data, reasons.ctypes.data, pc.ctypes.data,
                pv.ctypes.data)
         return drop, reasons, pc, pv
+
+
+class _MetaPlan:
+    """Column metadata of one vector reduced to the integer arrays the C ABI wants (built once per metadata object):
+    parent / group ids for tmog_sanity_decide, and the categorical groups of SanityChecker.categoricalTests."""
+
+    def __init__(self, meta: OpVectorMetadata):
+        d = meta.size
+        parent_ids: Dict[str, int] = {}
+        group_ids: Dict[str, int] = {}
+        offs, pids = [0], []
+        self.gid = np.full(d, -1, dtype=np.int32)
+        self.tsh = np.zeros(d, dtype=np.uint8)
+        groups: Dict[str, list] = {}
+        for c in meta.columns:
+            for pn in c.parentNamesWithMapKeys():
+                pids.append(parent_ids.setdefault(pn, len(parent_ids)))
+            offs.append(len(pids))
+            g = c.featureGroup()
+            if g is not None:
+                self.gid[c.index] = group_ids.setdefault(g, len(group_ids))
+                if c.indicatorValue is not None:
+                    groups.setdefault(g, []).append(c)
+            self.tsh[c.index] = c.isTextSharedHash
+        self.offs = np.asarray(offs, dtype=np.int32)
+        self.pids = np.asarray(pids, dtype=np.int32)
+        self.identity_pos = np.arange(d, dtype=np.int32)
+        self.names = meta.columnNames()
+        # categorical groups: duplicate indicator values inside a group -> only the first is used (:295-298)
+        self.groups = []
+        self.has_mpl = False
+        cat_cols, row_of_col, rows, lone_rows = [], [], [], []
+        r = 0
+        for g, cols in groups.items():
+            seen, cleaned = set(), []
+            for c in cols:
+                if c.indicatorValue not in seen:
+                    seen.add(c.indicatorValue)
+                    cleaned.append(c)
+            idx = [c.index for c in cleaned]
+            self.has_mpl = self.has_mpl or any(c.isMultiPickList for c in cleaned)
+            self.groups.append((g, [self.names[i] for i in idx], idx))
+            nrows = 2 if len(idx) == 1 else len(idx)
+            if len(idx) == 1:
+                lone_rows.append(r)
+            cat_cols.extend(idx)
+            row_of_col.extend(range(r, r + len(idx)))
+            rows.append(nrows)
+            r += nrows
+        self.cat_cols = np.asarray(cat_cols, dtype=np.int64)
+        self.row_of_col = np.asarray(row_of_col, dtype=np.int64)
+        self.lone_rows = np.asarray(lone_rows, dtype=np.int64)
+        self.rows = np.asarray(rows, dtype=np.int32)
+        self.row_offsets = np.concatenate([[0], np.cumsum(rows)[:-1]]).astype(np.int64) if rows else \
+            np.zeros(0, dtype=np.int64)
+        self.total_rows = r
 
 
 class SanityCheckerModel(OpModel):
