@@ -132,6 +132,54 @@ int tmog_binary_transform_select_dev(const uint8_t* values, int64_t ld, const ui
                                      int64_t out_col0, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------------
+ * Pivot vectorizers (OpTextPivotVectorizer on PickList / Text columns; the shared OpOneHotVectorizer logic)
+ * ------------------------------------------------------------------------------------------------------------------
+ * Columns arrive dictionary-encoded: codes[ncols][ld] int32 column-major (ld a multiple of 4; code < 0 = null) plus
+ * one utf8 dictionary per column.  String work happens once per DICTIONARY ENTRY on the host (the three functions
+ * below); the per-row work is integer only. */
+
+/* Replaces TextUtils.cleanString  U/text/TextUtils.scala:39-47  for a batch of strings (Arrow layout: utf8 bytes +
+ * int64 offsets [count+1]).  ASCII only: a byte >= 0x80 returns TMOG_EINVAL (Java's Unicode case mapping is not
+ * restated; such columns must run with cleanText = false). */
+int tmog_clean_strings(const uint8_t* data, const int64_t* offsets, int64_t count, uint8_t* out_data,
+                       int64_t out_capacity, int64_t* out_offsets);
+
+/* ids[i] = dense id (first-appearance order) of string i among the distinct strings: raw dictionary entries that
+ * clean to the same value share one count, as the Map[String, Int] keys of
+ * C/stages/impl/feature/OpOneHotVectorizer.scala:219-225 do. */
+int tmog_dedupe_strings(const uint8_t* data, const int64_t* offsets, int64_t count, int32_t* ids, int64_t* ndistinct);
+
+/* Replaces  countOccurrences.filter(_._2 >= minSup).sortBy(v => -v._2 -> v._1).take(topK)
+ * C/stages/impl/feature/OpOneHotVectorizer.scala:100-103: count descending, then java.lang.String.compareTo (UTF-16
+ * code-unit order).  Entries with count 0 never existed in the reference's map and are skipped.
+ * out_ids [top_k] receives the chosen entry indices in vocabulary order, *out_n their number. */
+int tmog_pivot_topk(const uint8_t* data, const int64_t* offsets, const int64_t* counts, int64_t count, int top_k,
+                    int64_t min_support, int32_t* out_ids, int* out_n);
+
+/* Replaces the value counting of OpOneHotVectorizer.fitFn (:95-97, the RDD.fold of per-row maps) and, in the same
+ * read, the per-label column sums SanityChecker.categoricalTests needs for the pivoted columns
+ * (C/stages/impl/preparators/SanityChecker.scala:265-272):  counts[count_offset_c + id * nclasses + class] += 1.
+ *   col_desc [ncols * 4] int64 (device): per column {nids, slot_offset, count_offset, ncodes};
+ *                        id = slots[slot_offset + code] for code >= 0, id = nids - 1 for a null;
+ *   slots                concatenated int32 code -> cleaned-id tables (device);
+ *   class_ids            one byte per row (tmog_label_classes_dev); ignored when nclasses == 1;
+ *   counts               uint64 (device), NOT cleared here: row chunks and ranks accumulate;
+ *   bad_code             device int set to 1 if a code >= ncodes was met. */
+int tmog_pivot_count_dev(const int32_t* codes, int64_t ld, int64_t n, int ncols, const uint8_t* class_ids,
+                         int nclasses, const int64_t* col_desc, const int32_t* slots, int64_t max_nids,
+                         uint64_t* counts, int* bad_code, void* stream);
+
+/* Replaces OneHotModelFun.pivotFn  C/stages/impl/feature/OpOneHotVectorizer.scala:416-437  for single-valued inputs
+ * (exactly one of {top value, OTHER, null indicator} is 1.0 per row and column) fused with reindex
+ * (Transmogrifier.scala:437-449) and SanityCheckerModel's removeFeatures:  out[r][out_col0 + c] = pos_c[code], the
+ * final column index of the 1.0 inside the output vector, or -1 if SanityChecker dropped that column.
+ *   pos                  concatenated int32 tables (device), table c has ncodes_c + 1 entries (the last is the null
+ *                        indicator's index) and starts at slot_offset_c + c;
+ *   out                  int32 row-major, row stride out_ld. */
+int tmog_pivot_transform_dev(const int32_t* codes, int64_t ld, int64_t n, int ncols, const int64_t* col_desc,
+                             const int32_t* pos, int32_t* out, int64_t out_ld, int64_t out_col0, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------------
  * Label classes
  * ------------------------------------------------------------------------------------------------------------------
  * Replaces the keying of  C/stages/impl/preparators/SanityChecker.scala:265-281  (reduceByKey on the label value,

@@ -48,6 +48,11 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_real_finish": [_p, _p, _int, _int, _dbl, _int, _p, _p, _p, _p, _p, _p, _p, _p],
     "tmog_real_transform_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _int, _p, _i64, _i64, _p],
     "tmog_binary_transform_dev": [_p, _i64, _p, _i64, _i64, _int, _int, _int, _p, _i64, _i64, _p],
+    "tmog_clean_strings": [_p, _p, _i64, _p, _i64, _p],
+    "tmog_dedupe_strings": [_p, _p, _i64, _p, _p],
+    "tmog_pivot_topk": [_p, _p, _p, _i64, _int, _i64, _p, _p],
+    "tmog_pivot_count_dev": [_p, _i64, _i64, _int, _p, _int, _p, _p, _i64, _p, _p, _p],
+    "tmog_pivot_transform_dev": [_p, _i64, _i64, _int, _p, _p, _p, _i64, _i64, _p],
     "tmog_label_classes_scratch_bytes": [C.POINTER(_sz)],
     "tmog_label_classes_dev": [_p, _i64, _int, _p, _p, _p, _p, _p, _sz, _p],
     "tmog_label_class_ids_dev": [_p, _i64, _p, _p, _int, _p, _p, _p],

@@ -103,6 +103,68 @@ class NumericBlock:
         return NumericBlock(list(names), type_name, v, valid, n)
 
 
+def encode_strings(strings: Sequence[str]) -> Tuple[np.ndarray, np.ndarray]:
+    """Arrow utf8 layout: (bytes uint8 [total], offsets int64 [count + 1])."""
+    enc = [t.encode("utf-8") for t in strings]
+    offsets = np.zeros(len(enc) + 1, dtype=np.int64)
+    if enc:
+        offsets[1:] = np.cumsum([len(e) for e in enc])
+    data = np.frombuffer(b"".join(enc), dtype=np.uint8).copy() if enc else np.zeros(0, dtype=np.uint8)
+    return data, offsets
+
+
+def decode_strings(data: np.ndarray, offsets: np.ndarray) -> List[str]:
+    b = data.tobytes()
+    return [b[offsets[i]:offsets[i + 1]].decode("utf-8") for i in range(len(offsets) - 1)]
+
+
+@dataclass
+class DictBlock:
+    """Dictionary-encoded string columns (PickList / Text): codes [ncols, ld] int32 column-major (code < 0 = null,
+    ld a multiple of 4) and one dictionary (list of distinct raw strings) per column -- the Arrow DictionaryArray the
+    columnar export produces."""
+    names: List[str]
+    type_name: str
+    codes: torch.Tensor
+    dicts: List[List[str]]
+    n: int
+
+    @property
+    def is_cuda(self) -> bool:
+        return self.codes.is_cuda
+
+    @property
+    def ld(self) -> int:
+        return self.codes.shape[1]
+
+    def rows(self, idx: Sequence[int]) -> "DictBlock":
+        idx = list(idx)
+        if idx == list(range(idx[0], idx[0] + len(idx))):
+            c = self.codes[idx[0]:idx[0] + len(idx)]
+        else:
+            c = self.codes.index_select(0, torch.as_tensor(idx, device=self.codes.device))
+        return DictBlock([self.names[i] for i in idx], self.type_name, c, [self.dicts[i] for i in idx], self.n)
+
+    def to(self, device) -> "DictBlock":
+        return DictBlock(self.names, self.type_name, self.codes.to(device, non_blocking=True), self.dicts, self.n)
+
+    @staticmethod
+    def from_lists(names: Sequence[str], type_name: str, columns: Sequence[Sequence[Optional[str]]],
+                   pin: bool = True) -> "DictBlock":
+        n = len(columns[0]) if columns else 0
+        ld = round_up(max(n, 1), 4)
+        codes = np.full((len(columns), ld), -1, dtype=np.int32)
+        dicts: List[List[str]] = []
+        for j, col in enumerate(columns):
+            seen: Dict[str, int] = {}
+            for i, v in enumerate(col):
+                if v is not None:
+                    codes[j, i] = seen.setdefault(v, len(seen))     # first-appearance order
+            dicts.append(list(seen))
+        t = torch.from_numpy(codes)
+        return DictBlock(list(names), type_name, _pin(t) if pin else t, dicts, n)
+
+
 @dataclass
 class DensePart:
     data: torch.Tensor                   # [n, width] float64 row-major (may be a column slice of a wider block)
@@ -162,6 +224,49 @@ class CsrPart:
 
 
 @dataclass
+class OneHotPart:
+    """Sparse block with at most `k` unit entries per row: indices [n, k] int32 are column positions local to the
+    part (-1 = no entry; the value 1.0 is implicit).  What the pivot vectorizers emit for single-valued columns."""
+    indices: torch.Tensor
+    width: int
+
+    def to_scipy(self):
+        import scipy.sparse as sp
+        idx = self.indices.cpu().numpy()
+        n, k = idx.shape
+        rows = np.repeat(np.arange(n), k)
+        flat = idx.reshape(-1)
+        ok = flat >= 0
+        m = sp.csr_matrix((np.ones(int(ok.sum())), (rows[ok], flat[ok].astype(np.int64))), shape=(n, self.width))
+        m.sum_duplicates()
+        return m
+
+
+class LazyOneHotPart:
+    """OneHotPart written on demand (see LazyDensePart): materialize(keep) emits indices renumbered to the kept
+    columns, -1 for dropped ones."""
+
+    def __init__(self, width: int, materialize):
+        self.width = width
+        self._materialize = materialize      # (keep: Optional[List[int]]) -> OneHotPart
+        self._part = None
+
+    def materialize(self, keep=None) -> OneHotPart:
+        if keep is None or list(keep) == list(range(self.width)):
+            if self._part is None:
+                self._part = self._materialize(None)
+            return self._part
+        return self._materialize(list(keep))
+
+    @property
+    def data(self):
+        return self.materialize(None).indices
+
+    def to_scipy(self):
+        return self.materialize(None).to_scipy()
+
+
+@dataclass
 class VectorColumn:
     name: str
     n: int
@@ -186,11 +291,11 @@ class VectorColumn:
 @dataclass
 class ColumnarBatch:
     n: int
-    blocks: List[NumericBlock] = field(default_factory=list)
+    blocks: List[object] = field(default_factory=list)     # NumericBlock | DictBlock
     vectors: Dict[str, VectorColumn] = field(default_factory=dict)
     response: Optional[str] = None       # name of the response (label) column, a RealNN
 
-    def find(self, name: str) -> Tuple[NumericBlock, int]:
+    def find(self, name: str):
         for b in self.blocks:
             if name in b.names:
                 return b, b.names.index(name)
@@ -198,6 +303,18 @@ class ColumnarBatch:
 
     def has(self, name: str) -> bool:
         return name in self.vectors or any(name in b.names for b in self.blocks)
+
+    def strings(self, names: Sequence[str]) -> "DictBlock":
+        """The dictionary-encoded block holding exactly these columns, in this order."""
+        located = [self.find(nm) for nm in names]
+        first = located[0][0]
+        if not all(isinstance(b, DictBlock) for b, _ in located):
+            raise ValueError("not string columns")
+        if all(b is first for b, _ in located):
+            return first.rows([i for _, i in located])
+        subs = [b.rows([i]) for b, i in located]
+        return DictBlock(list(names), subs[0].type_name, torch.cat([t.codes for t in subs], dim=0),
+                         [t.dicts[0] for t in subs], self.n)
 
     def numeric(self, names: Sequence[str]) -> NumericBlock:
         """The block holding exactly these columns, in this order (zero-copy when they are a run of one block)."""
@@ -248,6 +365,8 @@ class ColumnarBatch:
         for tp, names in groups.items():
             if tp in F.NUMERIC_TYPES:
                 blocks.append(NumericBlock.from_lists(names, tp, [columns[nm][1] for nm in names], pin))
+            elif tp in (F.PICKLIST, F.TEXT, F.TEXTAREA):
+                blocks.append(DictBlock.from_lists(names, tp, [columns[nm][1] for nm in names], pin))
             else:
                 raise NotImplementedError(f"columns of type {tp} are not supported yet")
         return ColumnarBatch(n or 0, blocks, {}, response)

@@ -11,7 +11,8 @@ import torch
 
 from .. import _lib as L
 from .. import runtime as R
-from ..columnar import ColumnarBatch, CsrPart, DensePart, LazyDensePart, VectorColumn
+from ..columnar import (ColumnarBatch, CsrPart, DensePart, LazyDensePart, LazyOneHotPart, OneHotPart,
+                        VectorColumn)
 from ..stats import LabelInfo, VectorStats
 from .numeric import label_info_dev
 
@@ -128,6 +129,17 @@ def select_columns(vec: VectorColumn, keep: List[int]) -> list:
             L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), n, idx.data_ptr(), len(local),
                    dst.data_ptr(), len(local), R.stream())
             out.append(DensePart(dst))
+        elif isinstance(p, LazyOneHotPart):
+            out.append(p.materialize(local))
+        elif isinstance(p, OneHotPart):
+            if local == list(range(p.width)):
+                out.append(p)
+                continue
+            newpos = torch.full((p.width + 1,), -1, dtype=torch.int32, device=p.indices.device)
+            newpos[torch.as_tensor(local, device=p.indices.device)] = torch.arange(
+                len(local), dtype=torch.int32, device=p.indices.device)
+            idx = p.indices.long()
+            out.append(OneHotPart(newpos[torch.where(idx < 0, torch.full_like(idx, p.width), idx)], len(local)))
         else:
-            raise NotImplementedError("column selection on sparse parts")
+            raise NotImplementedError("column selection on CSR parts")
     return out
