@@ -160,14 +160,17 @@ int tmog_pivot_topk(const uint8_t* data, const int64_t* offsets, const int64_t* 
  * read, the per-label column sums SanityChecker.categoricalTests needs for the pivoted columns
  * (C/stages/impl/preparators/SanityChecker.scala:265-272):  counts[count_offset_c + id * nclasses + class] += 1.
  *   col_desc [ncols * 4] int64 (device): per column {nids, slot_offset, count_offset, ncodes};
- *                        id = slots[slot_offset + code] for code >= 0, id = nids - 1 for a null;
- *   slots                concatenated int32 code -> cleaned-id tables (device);
+ *                        id = 1 + slots[slot_offset + code] for code >= 0, id = 0 for a null (nids = values + 1);
+ *   slots                concatenated int32 code -> id tables (device), or NULL: id = 1 + code (count per raw code and
+ *                        merge the codes that clean alike afterwards, on the host -- no gather in the kernel);
  *   class_ids            one byte per row (tmog_label_classes_dev); ignored when nclasses == 1;
- *   counts               uint64 (device), NOT cleared here: row chunks and ranks accumulate;
+ *   counts               uint32 bins (device; native 32-bit reductions), NOT cleared here, so a call adds to what
+ *                        is there; at most 2^32 - 1 rows may be accumulated into one table -- widen to int64 on
+ *                        the host when merging row chunks / ranks;
  *   bad_code             device int set to 1 if a code >= ncodes was met. */
 int tmog_pivot_count_dev(const int32_t* codes, int64_t ld, int64_t n, int ncols, const uint8_t* class_ids,
                          int nclasses, const int64_t* col_desc, const int32_t* slots, int64_t max_nids,
-                         uint64_t* counts, int* bad_code, void* stream);
+                         uint32_t* counts, int* bad_code, void* stream);
 
 /* Replaces OneHotModelFun.pivotFn  C/stages/impl/feature/OpOneHotVectorizer.scala:416-437  for single-valued inputs
  * (exactly one of {top value, OTHER, null indicator} is 1.0 per row and column) fused with reindex

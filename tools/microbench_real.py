@@ -43,9 +43,9 @@ print(f"fit: {tf:.3f} ms  {fit_b / tf / 1e6:.1f} GB/s   transform: {tt:.3f} ms  
 import numpy as np
 _bits = np.ones((2 * ncols + 63) // 64 * 64, dtype=np.uint8); _bits[14] = 0; _bits[2 * ncols:] = 0
 keep = torch.from_numpy(np.packbits(_bits, bitorder="little").view("<i8").copy()).cuda()
-out2 = torch.empty((n, 2 * ncols), dtype=torch.float64, device="cuda")
+out2 = torch.empty((n, 2 * ncols - 1), dtype=torch.float64, device="cuda")
 def trs():
     L.call("tmog_real_transform_select_dev", x.data_ptr(), n, vw.data_ptr(), vw.shape[1], n, ncols, fills.data_ptr(), 1,
-           keep.data_ptr(), 2 * ncols - 1, out2.data_ptr(), 2 * ncols, 0, st)
+           keep.data_ptr(), 2 * ncols - 1, out2.data_ptr(), 2 * ncols - 1, 0, st)
 ts = timeit(trs)
 print(f"transform-select(199): {ts:.3f} ms  {(tr_b - 8 * n) / ts / 1e6:.1f} GB/s", flush=True)

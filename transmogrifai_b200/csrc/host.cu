@@ -303,7 +303,7 @@ extern "C" int tmog_real_transform_host(tmog_ctx* c, const double* values, int64
     const int64_t nchunks = (n + chunk - 1) / chunk;
     const bool resident = c->r_key == values && c->r_n == n && c->r_ncols == ncols &&
                           c->r_has_valid == (valid != nullptr);
-    const int64_t dw = round_up(width, 4);  // device row stride: rows start on 32-byte sector boundaries
+    const int64_t dw = width;  // dense device rows: padding that is never written costs partial-sector fills
     if (int rc = c->fills.ensure(sizeof(double) * std::max(ncols, 1))) return rc;
     double* d_fills = nullptr;
     if (fills) {

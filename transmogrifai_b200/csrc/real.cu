@@ -290,12 +290,11 @@ vec_transform_select_kernel(const T* __restrict__ values, int64_t ld, const uint
     const int64_t r0 = (int64_t)blockIdx.x * TR_ROWS;
     const int rows_here = (int)min((int64_t)TR_ROWS, n - r0);
     const int ntiles = (ncols + 31) / 32;
-    // the output block may start anywhere in the row; flush groups are aligned on the actual addresses
-    const int mis = (int)(((reinterpret_cast<uintptr_t>(out) >> 3) + (uintptr_t)out_col0) & 3u);
-    const bool rows_aligned = (out_ld & 3) == 0;
-    int plo = 0;    // packed output position of the tile's first kept column
-    int base = 0;   // first position not yet flushed
-    int ring0 = 0;  // multiple of TR_RING <= base: slot(p) = p - ring0, minus TR_RING once past the end
+    // the output block may start anywhere and rows need not be 32-byte multiples: flush groups are aligned on the
+    // actual address of every row
+    const int mis0 = (int)(((reinterpret_cast<uintptr_t>(out) >> 3) + (uintptr_t)out_col0) & 3u);
+    int plo = 0;    // packed output position of the tile's first kept column (= end of the previous tile)
+    int ring0 = 0;  // multiple of TR_RING: slot(p) = p - ring0, minus TR_RING once past the end
     for (int t = 0; t < ntiles; ++t) {
         const int c0 = t * 32;
         const int tc = min(32, ncols - c0);
@@ -331,29 +330,29 @@ vec_transform_select_kernel(const T* __restrict__ values, int64_t ld, const uint
             }
         }
         __syncthreads();
-        // ---- flush [base, hi): everything up to the last 32-byte boundary, or to the end on the last tile
+        // ---- flush per row [lo, hi): from where the previous tile stopped up to the last 32-byte boundary of this
+        //      row (to the very end on the last tile); the < 4 values behind it wait in the ring for the next tile
         const int end = plo + cnt;
-        int hi = end;
-        if (t + 1 < ntiles && rows_aligned) hi = ((end + mis) & ~3) - mis;
-        if (hi > base) {
+        const bool last = t + 1 == ntiles;
 #pragma unroll 2
-            for (int k = 0; k < TR_ROWS / 8; ++k) {
-                const int rl = warp + 8 * k;
-                if (rl < rows_here) {
-                    double* orow = out + (r0 + rl) * out_ld + out_col0;
-                    const double* rrow = ring + rl * TR_STRIDE;
-                    for (int p = base + lane; p < hi; p += 32) {
-                        int sl = p - ring0;
-                        sl -= sl >= TR_RING ? TR_RING : 0;
-                        orow[p] = rrow[sl];
-                    }
+        for (int k = 0; k < TR_ROWS / 8; ++k) {
+            const int rl = warp + 8 * k;
+            if (rl < rows_here) {
+                const int mis = (mis0 + (int)(((r0 + rl) * out_ld) & 3)) & 3;
+                const int lo = t == 0 ? 0 : max(0, ((plo + mis) & ~3) - mis);
+                const int hi = last ? end : ((end + mis) & ~3) - mis;
+                double* orow = out + (r0 + rl) * out_ld + out_col0;
+                const double* rrow = ring + rl * TR_STRIDE;
+                for (int p = lo + lane; p < hi; p += 32) {
+                    int sl = p - ring0;
+                    sl -= sl >= TR_RING ? TR_RING : 0;
+                    orow[p] = rrow[sl];
                 }
             }
-            base = hi;
-            if (base - ring0 >= TR_RING) ring0 += TR_RING;
         }
         plo = end;
-        if (t + 1 < ntiles) __syncthreads();  // ring slots of flushed positions are reused by the next tile
+        ring0 = (max(end - 3, 0) / TR_RING) * TR_RING;  // every unflushed position is >= end - 3
+        if (!last) __syncthreads();  // ring slots of flushed positions are reused by the next tile
     }
 }
 

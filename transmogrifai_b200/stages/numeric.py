@@ -247,7 +247,7 @@ def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_n
             raise ValueError("kept columns must be ascending")
         w = len(kp)
     if block.is_cuda:
-        out = torch.empty((n, round_up(max(w, 1), 4)), dtype=torch.float64, device="cuda")   # 32-byte aligned rows
+        out = torch.empty((n, max(w, 1)), dtype=torch.float64, device="cuda")   # dense rows: no unwritten padding
         d_keep = None
         if kp is not None:
             bits = np.zeros(round_up(w_full, 64), dtype=np.uint8)

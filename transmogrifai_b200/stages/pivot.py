@@ -69,7 +69,7 @@ class _Plan:
             self.values.append(distinct)
         ncols = len(block.names)
         self.ncodes = np.array([len(d) for d in block.dicts], dtype=np.int64)
-        self.nids = np.array([len(v) + 1 for v in self.values], dtype=np.int64)       # + the null id
+        self.nids = self.ncodes + 1                                                    # raw codes + the null id 0
         self.slot_offset = np.concatenate([[0], np.cumsum(self.ncodes)[:-1]]).astype(np.int64) if ncols else \
             np.zeros(0, dtype=np.int64)
 
@@ -148,15 +148,12 @@ class OpTextPivotVectorizer(OpEstimator):
         desc = plan.desc(ncls)
         total_bins = int((plan.nids * ncls).sum())
         d_desc = torch.from_numpy(desc).cuda()
-        slots = np.concatenate(plan.ids).astype(np.int32) if ncols and sum(len(i) for i in plan.ids) else \
-            np.zeros(1, dtype=np.int32)
-        d_slots = torch.from_numpy(slots).cuda()
-        d_counts = torch.zeros(max(total_bins, 1), dtype=torch.int64, device="cuda")
+        d_counts = torch.zeros(max(total_bins, 1), dtype=torch.int32, device="cuda")     # uint32 bins
         d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
         L.call("tmog_pivot_count_dev", dev.codes.data_ptr(), dev.ld, n, ncols,
-               ids.data_ptr() if classes is not None else None, ncls, d_desc.data_ptr(), d_slots.data_ptr(),
+               ids.data_ptr() if classes is not None else None, ncls, d_desc.data_ptr(), None,
                int(plan.nids.max()) if ncols else 1, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
-        counts = D.allreduce_sum(d_counts.cpu().numpy())
+        counts = D.allreduce_sum(d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF)
         if int(d_bad.item()):
             raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
         n_global = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
@@ -164,15 +161,19 @@ class OpTextPivotVectorizer(OpEstimator):
         col_stats = []
         for c in range(ncols):
             k = int(plan.nids[c])
-            tab = counts[plan.count_offset[c]:plan.count_offset[c] + k * ncls].reshape(k, ncls)
+            raw = counts[plan.count_offset[c]:plan.count_offset[c] + k * ncls].reshape(k, ncls)
+            # bins are per RAW code (row 0 = null): merge the codes whose cleaned values coincide
+            tab = np.zeros((len(plan.values[c]), ncls), dtype=np.int64)
+            if len(plan.ids[c]):
+                np.add.at(tab, plan.ids[c], raw[1:])
             totals = tab.sum(axis=1)
-            chosen = top_k(plan.values[c], totals[:-1], self.topK, self.minSupport)
+            chosen = top_k(plan.values[c], totals, self.topK, self.minSupport)
             tops.append([plan.values[c][i] for i in chosen])
-            rest = np.ones(k - 1, dtype=bool)
+            rest = np.ones(len(tab), dtype=bool)
             rest[chosen] = False
-            rows = [tab[i] for i in chosen] + [tab[:-1][rest].sum(axis=0)]
+            rows = [tab[i] for i in chosen] + [tab[rest].sum(axis=0)]
             if self.trackNulls:
-                rows.append(tab[-1])
+                rows.append(raw[0])
             col_stats.append(np.stack(rows).astype(np.float64))            # [emitted columns, classes]
         self._metadata = self._metadata_for(tops)
         stats = None
@@ -254,7 +255,7 @@ class OpTextPivotVectorizerModel(OpModel):
         desc = plan.desc(1)
         d_desc = torch.from_numpy(desc).cuda()
         d_pos = torch.from_numpy(pos).cuda()
-        out = torch.empty((n, round_up(max(ncols, 1), 8)), dtype=torch.int32, device="cuda")   # 32-byte aligned rows
+        out = torch.empty((n, max(ncols, 1)), dtype=torch.int32, device="cuda")   # dense rows: no unwritten padding
         L.call("tmog_pivot_transform_dev", dev.codes.data_ptr(), dev.ld, n, ncols, d_desc.data_ptr(),
                d_pos.data_ptr(), out.data_ptr(), out.shape[1], 0, R.stream())
         return OneHotPart(out[:, :ncols], out_width)
