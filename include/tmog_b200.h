@@ -183,6 +183,60 @@ int tmog_pivot_transform_dev(const int32_t* codes, int64_t ld, int64_t n, int nc
                              const int32_t* pos, int32_t* out, int64_t out_ld, int64_t out_col0, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------------
+ * Text columns (SmartTextVectorizer: TextStats, tokeniser, hashing-TF)
+ * ------------------------------------------------------------------------------------------------------------------
+ * Raw utf8 columns in Arrow layout.  col_desc [ncols * 4] int64 (device): per column {data pointer, offsets pointer
+ * (int64 [n+1]), validity bitmap pointer or 0, 0}.  ASCII is the parity contract: a byte >= 0x80 sets flags[0]. */
+
+/* Replaces TextStats of SmartTextVectorizer.fitFn  C/stages/impl/feature/SmartTextVectorizer.scala:79-124,207-299:
+ * per column an open-addressing table (`slots` entries, power of two) over the 64-bit hashes of the CLEANED cells
+ * (TextUtils.cleanString applied on the fly when clean_text != 0): distinct count, per-label-class counts, first row of
+ * every distinct value (the host reads those rows to recover the strings), and sum / sum of squares of the cleaned
+ * lengths.  A column that shows more than max_distinct distinct values stops being recorded (only ndistinct >
+ * max_distinct is reported): that is all SmartTextVectorizer needs to route it to hashing.
+ * `tables` = tmog_text_stats_layout(): head_bytes + ncols * per_column_bytes of device memory; column c's block is at
+ * head + c * per_column: hash u64 [slots] | first_row u64 [slots] | counts u32 [slots * nclasses] (padded to 8 B) |
+ * ndistinct i32 (+4 pad) | len_sum u64 [2] | nonnull u64. */
+int tmog_text_stats_layout(int ncols, int slots, int nclasses, size_t* head_bytes, size_t* per_column_bytes);
+int tmog_text_stats_table_bytes(int slots, int nclasses, size_t* bytes);
+int tmog_text_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* class_ids, int nclasses,
+                        int clean_text, int slots, int max_distinct, void* tables, int32_t* flags, void* stream);
+
+/* Dictionary codes for the text columns SmartTextVectorizer pivots: codes[k][r] = table slot of row r's cleaned value
+ * in column col_index[k] (-1 null), which tmog_pivot_count_dev / tmog_pivot_transform_dev then consume
+ * (SmartTextVectorizerModel.transformFn's categoricalPivotFn, SmartTextVectorizer.scala:333-345). */
+int tmog_text_codes_dev(const int64_t* col_desc, const int32_t* col_index, int nsel, int64_t n, int clean_text,
+                        int slots, const void* tables, int32_t* codes, int64_t ld, void* stream);
+
+/* Replaces TextTokenizer.tokenize (C/stages/impl/feature/TextTokenizer.scala:160-220; Lucene 7.3 StandardAnalyzer with
+ * the Snowball english stop set, C/utils/text/LuceneTextAnalyzer.scala:103-122,159-166) + HashingFun.hash / prepare
+ * (C/stages/impl/feature/OPCollectionHashingVectorizer.scala:244-305; Spark 2.4.5 HashingTF: legacy murmur3_x86_32
+ * seed 42, non-negative mod) + the null indicators of SmartTextVectorizerModel (SmartTextVectorizer.scala:363-371).
+ *   prefix [ncols * 16] / prefix_len [ncols] (device): the bytes of "<hasher.indexOf(featureName)>_" per column;
+ *   params [8] (HOST): numFeatures, sharedHashSpace, binaryFreq, minTokenLength, trackNulls, prependFeatureName,
+ *                      null_base (vector index of the first null indicator; >= width of the hash block), nclasses.
+ * Vector index of a hit: bucket (+ j * numFeatures for separate spaces); null indicator of column j: null_base + j.
+ * flags [4] (device): non-ASCII byte, > 512 tokens in a cell, > 4096 hits in a row, sparse capacity exceeded.
+ *
+ * _stats: SanityChecker sums per vector index (NOT cleared here; sized null_base + ncols):
+ *   bucket_class_sum [index * nclasses + class] += term frequency, bucket_nnz [index] += 1 per row holding the index,
+ *   bucket_sq_extra [index] += tf^2 - tf   (so that sum v^2 = sum v + extra);
+ *   bucket_aux [3 * index + {0, 1, 2}] (zeroed by the caller) = max tf, ~(min tf among tf > 1), rows with tf > 1 --
+ *   touched only for the rare tf > 1, they give the exact column max / min.
+ * _transform: sparse rows in 4-array CSR form: row r owns out_idx / out_val [row_start[r], row_start[r] + row_nnz[r]),
+ *   indices ascending; newpos [null_base + ncols] maps a vector index to its output index or -1 (dropped by
+ *   SanityChecker); *cursor (device u64, zeroed by the caller) ends as the total number of entries; entries beyond
+ *   `capacity` are counted but not written (flags[3]) -- call with capacity 0 to size the buffers. */
+int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
+                             const int32_t* prefix_len, const int32_t* params, const uint8_t* class_ids,
+                             uint32_t* bucket_class_sum, uint32_t* bucket_nnz, uint64_t* bucket_sq_extra,
+                             uint32_t* bucket_aux, int32_t* flags, void* stream);
+int tmog_text_hash_transform_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
+                                 const int32_t* prefix_len, const int32_t* params, const int32_t* newpos,
+                                 int64_t* row_start, int32_t* row_nnz, int32_t* out_idx, int32_t* out_val,
+                                 uint64_t* cursor, int64_t capacity, int32_t* flags, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------------------
  * Label classes
  * ------------------------------------------------------------------------------------------------------------------
  * Replaces the keying of  C/stages/impl/preparators/SanityChecker.scala:265-281  (reduceByKey on the label value,

@@ -1,0 +1,214 @@
+"""GPU parity of SmartTextVectorizer (TextStats decision, pivot of categorical text, tokenise + murmur3 hashing, null
+indicators) against the oracle and the reference's golden vectors."""
+import numpy as np
+import pytest
+
+from oracle import sanity as S
+from oracle import text as T
+from oracle import vectorizers as V
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+TEXT1 = ["hello world", "hello world", "good evening", "hello world", None]
+TEXT2 = ["Hello world!", "What's up", "How are you doing, my friend?", "Not bad, my friend.", None]
+
+
+def _batch(cols, response=None, device=None):
+    from transmogrifai_b200.columnar import ColumnarBatch
+    b = ColumnarBatch.from_columns(cols, response=response)
+    return b.to(device) if device else b
+
+
+def _feats(names):
+    from transmogrifai_b200 import features as F
+    return [F.FeatureBuilder.Text(nm).asPredictor() for nm in names]
+
+
+@pytest.mark.parametrize("device", [None, "cuda"])
+def test_smart_text_vectorizer_reference_golden(device):
+    # core/src/test/scala/com/salesforce/op/stages/impl/feature/SmartTextVectorizerTest.scala:55-75
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    batch = _batch({"text1": (F.TEXT, TEXT1), "text2": (F.TEXT, TEXT2)}, device=device)
+    est = SmartTextVectorizer().setMaxCardinality(2).setNumFeatures(4).setMinSupport(1).setTopK(2) \
+        .setPrependFeatureName(False).setHashSpaceStrategy("Shared").setInput(*_feats(["text1", "text2"]))
+    model = est.fit(batch)
+    assert model.vectorizationMethods == ["Pivot", "Hash"]
+    got = model.transform(batch).vectors[est.getOutput().name].to_numpy()
+    exp = np.zeros((5, 9))
+    for r, (idx, vals) in enumerate([((0, 4, 6), (1, 1, 1)), ((0, 8), (1, 1)), ((1, 6), (1, 1)), ((0, 6), (1, 2)),
+                                     ((3, 8), (1, 1))]):
+        exp[r, list(idx)] = vals
+    assert np.array_equal(got, exp)
+    meta = model.getMetadata()
+    assert [c.indicatorValue for c in meta.columns[:4]] == ["HelloWorld", "GoodEvening", "OTHER", "NullIndicatorValue"]
+    assert all(c.grouping is None and c.indicatorValue is None and c.parentFeatureName == ("text2",)
+               for c in meta.columns[4:8])
+    assert meta.columns[8].indicatorValue == "NullIndicatorValue" and meta.columns[8].grouping == "text2"
+
+
+def test_hashing_reference_golden_indices():
+    # core/src/test/.../OPCollectionHashingVectorizerTest.scala:47-58: feature textList1, tokens x y, 512 buckets,
+    # prepended feature-name hash -> {107, 224}
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer, murmur3_index
+    assert murmur3_index("textList1", 512) == 364
+    batch = _batch({"textList1": (F.TEXT, ["x y", "zebra"])})
+    est = SmartTextVectorizer().setMaxCardinality(0).setNumFeatures(512).setTrackNulls(False) \
+        .setInput(*_feats(["textList1"]))
+    model = est.fit(batch)
+    assert model.vectorizationMethods == ["Hash"]
+    got = model.transform(batch).vectors[est.getOutput().name].to_scipy()
+    assert sorted(got[0].indices.tolist()) == [107, 224] and got[0].data.tolist() == [1.0, 1.0]
+
+
+TRICKY = [
+    "I've got a lovely bunch of coconuts", "There they are, all standing in a row",
+    "<body>Big ones, small <h1>ones</h1>, some as big as your head</body>", "", "   ", "What's up", None,
+    "www.google.com and foo_bar9 cost 3.14 or 1,000 units; a:b a,b 9:3 x.'y _ __ _a_ 'tis don't.", "ALL CAPS Words",
+    "trailing.", ".leading", "a" * 300 + " tail", "tab\tsep\nnewline", "it's its its' 'its", "x" * 31 + " " + "y" * 33,
+    "e-mail me@site.org 10:30pm 2019-01-02 v1.2.3 a.b.c.d", "under_score__double ___ 9_9",
+]
+
+
+def _random_text(rng, vocab, n, null_frac=0.05):
+    out = []
+    for _ in range(n):
+        u = rng.random()
+        if u < null_frac:
+            out.append(None)
+        elif u < null_frac + 0.01:
+            out.append("")
+        else:
+            k = rng.poisson(12)
+            toks = [vocab[i] for i in rng.zipf(1.3, size=k) % len(vocab)]
+            s = " ".join(toks)
+            if rng.random() < 0.1:
+                s = s.title()
+            if rng.random() < 0.1:
+                s = s.replace(" ", ", ", 2) + "."
+            out.append(s)
+    return out
+
+
+@pytest.mark.parametrize("device", [None, "cuda"])
+@pytest.mark.parametrize("num_features,strategy,prepend,binary,track,min_len",
+                         [(512, "Auto", True, False, True, 1), (16, "Shared", False, False, True, 1),
+                          (64, "Separate", True, True, False, 3)])
+def test_hash_columns_match_oracle(device, num_features, strategy, prepend, binary, track, min_len):
+    """Tokeniser + stop filter + legacy murmur3 + term frequencies + null indicators: bit-exact against the oracle on
+    hand-made tricky strings and random Zipf text."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    rng = np.random.default_rng(5)
+    vocab = ["".join(rng.choice(list("abcdefghijklmnopqrstuvwxyz"), size=rng.integers(2, 9))) for _ in range(400)]
+    vocab += ["the", "and", "you", "9", "42", "x1", "don't", "u.s.a", "A_b"]
+    n = 600
+    cols = [TRICKY + _random_text(rng, vocab, n - len(TRICKY)), _random_text(rng, vocab, n),
+            _random_text(rng, vocab, n, null_frac=0.5)]
+    names = ["alpha", "beta", "gamma_text"]
+    batch = _batch({nm: (F.TEXT, c) for nm, c in zip(names, cols)}, device=device)
+    est = SmartTextVectorizer().setMaxCardinality(0).setNumFeatures(num_features).setHashSpaceStrategy(strategy) \
+        .setPrependFeatureName(prepend).setBinaryFreq(binary).setTrackNulls(track).setMinTokenLength(min_len) \
+        .setInput(*_feats(names))
+    model = est.fit(batch)
+    assert model.vectorizationMethods == ["Hash"] * 3
+    got = model.transform(batch).vectors[est.getOutput().name].to_scipy()
+    exp = V.smart_text_transform(cols, names, ["Hash"] * 3, [[], [], []], num_features=num_features,
+                                 track_nulls=track, prepend_feature_name=prepend, binary_freq=binary,
+                                 hash_space_strategy=strategy, min_token_length=min_len)
+    assert got.shape == exp.shape
+    diff = (got != exp)
+    assert diff.nnz == 0, f"{diff.nnz} entries differ, first rows {sorted(set(diff.nonzero()[0]))[:5]}"
+    exp_meta = V.smart_text_metadata(names, "Text", ["Hash"] * 3, [[], [], []], num_features, track,
+                                     hash_space_strategy=strategy)
+    assert [(c.parentFeatureName, c.grouping, c.indicatorValue) for c in model.getMetadata().columns] == \
+        [(m.parent_names, m.grouping, m.indicator) for m in exp_meta]
+
+
+@pytest.mark.parametrize("device", [None, "cuda"])
+def test_smart_text_decision_and_pivot_match_oracle(device):
+    """Mixed columns: low-cardinality text is pivoted (vocabulary + tie-break bit-exact), free text is hashed, a
+    column just over the cardinality cap follows the reference's frozen left fold."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    rng = np.random.default_rng(9)
+    n = 1500
+    cat = [None if rng.random() < 0.1 else ["Red", "green", "BLUE ", "red.", "Green!", "yellow"][int(rng.integers(6))]
+           for _ in range(n)]
+    vocab = ["".join(rng.choice(list("abcdefghij"), size=rng.integers(3, 8))) for _ in range(300)]
+    free = _random_text(rng, vocab, n)
+    ids = [f"id{int(rng.integers(0, 40)):03d}" if rng.random() > 0.05 else None for _ in range(n)]   # 40 > maxCard 30
+    heavy = ["usa" if rng.random() < 0.97 else f"c{int(rng.integers(0, 60))}" for _ in range(n)]      # covered by top-K
+    cols = [cat, free, ids, heavy]
+    names = ["cat", "free", "ids", "heavy"]
+    batch = _batch({nm: (F.TEXT, c) for nm, c in zip(names, cols)}, device=device)
+    est = SmartTextVectorizer().setMaxCardinality(30).setNumFeatures(128).setTopK(20).setMinSupport(10) \
+        .setInput(*_feats(names))
+    model = est.fit(batch)
+    methods, tops = V.smart_text_fit(cols, max_cardinality=30, top_k=20, min_support=10)
+    assert model.vectorizationMethods == methods
+    assert methods[0] == "Pivot" and methods[1] == "Hash"
+    assert [model.topValues[j] for j in range(4) if methods[j] == "Pivot"] == \
+        [tops[j] for j in range(4) if methods[j] == "Pivot"]
+    got = model.transform(batch).vectors[est.getOutput().name].to_scipy()
+    exp = V.smart_text_transform(cols, names, methods, tops, num_features=128)
+    assert got.shape == exp.shape and (got != exp).nnz == 0
+    exp_meta = V.smart_text_metadata(names, "Text", methods, tops, 128, True)
+    assert [(c.parentFeatureName, c.grouping, c.indicatorValue) for c in model.getMetadata().columns] == \
+        [(m.parent_names, m.grouping, m.indicator) for m in exp_meta]
+
+
+@pytest.mark.parametrize("device", [None, "cuda"])
+def test_transmogrify_sanity_check_text_matches_oracle(device):
+    """Text + Real through transmogrify() + sanityCheck(): statistics of hashed columns and null indicators from the
+    fused bucket sums against the oracle's colStats / label correlations / Cramer's V on the oracle's own matrix."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+    rng = np.random.default_rng(21)
+    n = 1200
+    y = (rng.random(n) < 0.35).astype(np.float64)
+    vocab = ["".join(rng.choice(list("abcdefghijklmnop"), size=rng.integers(3, 8))) for _ in range(200)]
+    t0 = _random_text(rng, vocab, n)
+    t1 = [("spam offer " if yy and rng.random() < 0.9 else "") + (s or "") if rng.random() > 0.04 else None
+          for yy, s in zip(y, _random_text(rng, vocab, n))]
+    cat = [None if rng.random() < 0.1 else ["a", "b", "c"][int(rng.integers(3))] for _ in range(n)]
+    r0 = [None if rng.random() < 0.1 else float(v) for v in rng.normal(1.0, 2.0, n)]
+    data = {"t0": (F.TEXT, t0), "t1": (F.TEXT, t1), "cat": (F.TEXT, cat), "r0": (F.REAL, r0),
+            "y": (F.REALNN, y.tolist())}
+    batch = _batch(data, response="y", device=device)
+    feats = _feats(["t0", "t1", "cat"]) + [F.FeatureBuilder.Real("r0").asPredictor()]
+    label = F.FeatureBuilder.RealNN("y").asResponse()
+    checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
+                                sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
+    out_batch, fitted = fit_and_transform(batch, checked)
+    est = checked.origin_stage
+    # oracle: Real block first (type-name order Real < Text), then the SmartText block (maxCard 30, 512 hashes)
+    fills = V.real_vectorizer_fit([r0])
+    xr = V.real_vectorizer_transform([r0], fills, True)
+    tcols, tnames = [t0, t1, cat], ["t0", "t1", "cat"]
+    methods, tops = V.smart_text_fit(tcols, max_cardinality=30, top_k=20, min_support=10)
+    assert methods == ["Hash", "Hash", "Pivot"]
+    xt = V.smart_text_transform(tcols, tnames, methods, tops, num_features=512)
+    xo, metas = V.combine([xr, xt], [V.numeric_metadata(["r0"], "Real", True),
+                                     V.smart_text_metadata(tnames, "Text", methods, tops, 512, True)])
+    p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                       feature_feature_corr_level="off")
+    ref = S.sanity_fit(y, xo, metas, p, label_name="y")
+    assert est.summary.names[:-1] == [m.col_name() for m in metas]
+    assert est.summary.dropped == ref.dropped and len(ref.dropped) > 100       # empty hash buckets have no variance
+    assert fitted[-1].indicesToKeep == ref.indices_to_keep
+    np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+    assert np.array_equal(est.summary.min, ref.col_stats.min) and np.array_equal(est.summary.max, ref.col_stats.max)
+    np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                               equal_nan=True)
+    got_g = {g.group: g for g in est.summary.categoricalStats}
+    assert got_g.keys() == {g.group for g in ref.cat_stats}
+    for g in ref.cat_stats:
+        assert np.array_equal(got_g[g.group].contingencyMatrix, g.contingency_matrix)
+        np.testing.assert_allclose(got_g[g.group].cramersV, g.cramers_v, rtol=1e-9, equal_nan=True)
+    got = out_batch.vectors[checked.name].to_scipy()
+    exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
+    assert got.shape == exp.shape and abs(got - exp).max() < 1e-9

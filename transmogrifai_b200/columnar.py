@@ -166,6 +166,61 @@ class DictBlock:
 
 
 @dataclass
+class TextBlock:
+    """Raw utf8 string columns (Text / TextArea) in Arrow layout, one (data, offsets, validity) triple per column:
+    data uint8 [total bytes], offsets int64 [n + 1], valid int64 bitmap words [ceil(n/64)] or None."""
+    names: List[str]
+    type_name: str
+    data: List[torch.Tensor]
+    offsets: List[torch.Tensor]
+    valid: List[Optional[torch.Tensor]]
+    n: int
+
+    @property
+    def is_cuda(self) -> bool:
+        return self.offsets[0].is_cuda if self.offsets else False
+
+    def rows(self, idx: Sequence[int]) -> "TextBlock":
+        idx = list(idx)
+        return TextBlock([self.names[i] for i in idx], self.type_name, [self.data[i] for i in idx],
+                         [self.offsets[i] for i in idx], [self.valid[i] for i in idx], self.n)
+
+    def to(self, device) -> "TextBlock":
+        mv = lambda t: None if t is None else t.to(device, non_blocking=True)  # noqa: E731
+        return TextBlock(self.names, self.type_name, [mv(t) for t in self.data], [mv(t) for t in self.offsets],
+                         [mv(t) for t in self.valid], self.n)
+
+    def cell(self, col: int, row: int) -> Optional[str]:
+        """One cell as a Python string (host round trip; used for the handful of vocabulary rows only)."""
+        v = self.valid[col]
+        if v is not None and not (int(v[row >> 6].item()) >> (row & 63)) & 1:
+            return None
+        a, b = int(self.offsets[col][row].item()), int(self.offsets[col][row + 1].item())
+        return bytes(self.data[col][a:b].cpu().numpy().tobytes()).decode("utf-8")
+
+    @staticmethod
+    def from_lists(names: Sequence[str], type_name: str, columns: Sequence[Sequence[Optional[str]]],
+                   pin: bool = True) -> "TextBlock":
+        n = len(columns[0]) if columns else 0
+        data, offsets, valid = [], [], []
+        for col in columns:
+            enc = [b"" if v is None else v.encode("utf-8") for v in col]
+            off = np.zeros(n + 1, dtype=np.int64)
+            if n:
+                off[1:] = np.cumsum([len(e) for e in enc])
+            buf = np.frombuffer(b"".join(enc), dtype=np.uint8).copy() if off[-1] else np.zeros(1, dtype=np.uint8)
+            ok = np.array([[v is not None for v in col]], dtype=bool)
+            d, o = torch.from_numpy(buf), torch.from_numpy(off)
+            m = None if ok.all() else torch.from_numpy(pack_validity(ok)[0])
+            if pin:
+                d, o, m = _pin(d), _pin(o), (None if m is None else _pin(m))
+            data.append(d)
+            offsets.append(o)
+            valid.append(m)
+        return TextBlock(list(names), type_name, data, offsets, valid, n)
+
+
+@dataclass
 class DensePart:
     data: torch.Tensor                   # [n, width] float64 row-major (may be a column slice of a wider block)
 
@@ -267,6 +322,51 @@ class LazyOneHotPart:
 
 
 @dataclass
+class SparseRowsPart:
+    """Sparse block in 4-array CSR form: row r owns indices / values [row_start[r], row_start[r] + row_nnz[r]),
+    indices ascending and local to the part.  What the hashing vectorizer emits (rows are written by whichever CTA
+    finishes them, so their storage order is not the row order)."""
+    row_start: torch.Tensor              # [n] int64
+    row_nnz: torch.Tensor                # [n] int32
+    indices: torch.Tensor                # [nnz] int32
+    values: torch.Tensor                 # [nnz] int32 (term frequencies)
+    width: int
+
+    def to_scipy(self):
+        import scipy.sparse as sp
+        start = self.row_start.cpu().numpy()
+        nnz = self.row_nnz.cpu().numpy().astype(np.int64)
+        idx = self.indices.cpu().numpy()
+        val = self.values.cpu().numpy()
+        n = len(start)
+        indptr = np.zeros(n + 1, dtype=np.int64)
+        indptr[1:] = np.cumsum(nnz)
+        take = np.repeat(start - indptr[:-1], nnz) + np.arange(indptr[-1])
+        m = sp.csr_matrix((val[take].astype(np.float64), idx[take].astype(np.int64), indptr), shape=(n, self.width))
+        m.eliminate_zeros()
+        return m
+
+
+class LazyPart:
+    """A part of any kind written on demand: materialize(keep) returns a concrete part restricted to `keep`."""
+
+    def __init__(self, width: int, materialize):
+        self.width = width
+        self._materialize = materialize
+        self._part = None
+
+    def materialize(self, keep=None):
+        if keep is None or list(keep) == list(range(self.width)):
+            if self._part is None:
+                self._part = self._materialize(None)
+            return self._part
+        return self._materialize(list(keep))
+
+    def to_scipy(self):
+        return self.materialize(None).to_scipy()
+
+
+@dataclass
 class VectorColumn:
     name: str
     n: int
@@ -308,6 +408,15 @@ class ColumnarBatch:
         """The dictionary-encoded block holding exactly these columns, in this order."""
         located = [self.find(nm) for nm in names]
         first = located[0][0]
+        if all(isinstance(b, TextBlock) for b, _ in located):
+            # raw text handed to a pivot stage: dictionary-encode it (host side, cached per column set)
+            cache = self.__dict__.setdefault("_dict_cache", {})
+            key = tuple(names)
+            if key not in cache:
+                cols = [[b.cell(i, r) for r in range(self.n)] for b, i in located]
+                blk = DictBlock.from_lists(list(names), first.type_name, cols)
+                cache[key] = blk.to("cuda") if first.is_cuda else blk
+            return cache[key]
         if not all(isinstance(b, DictBlock) for b, _ in located):
             raise ValueError("not string columns")
         if all(b is first for b, _ in located):
@@ -315,6 +424,16 @@ class ColumnarBatch:
         subs = [b.rows([i]) for b, i in located]
         return DictBlock(list(names), subs[0].type_name, torch.cat([t.codes for t in subs], dim=0),
                          [t.dicts[0] for t in subs], self.n)
+
+    def texts(self, names: Sequence[str]) -> "TextBlock":
+        located = [self.find(nm) for nm in names]
+        if not all(isinstance(b, TextBlock) for b, _ in located):
+            raise ValueError("not raw text columns")
+        first = located[0][0]
+        if all(b is first for b, _ in located):
+            return first.rows([i for _, i in located])
+        return TextBlock(list(names), first.type_name, [b.data[i] for b, i in located],
+                         [b.offsets[i] for b, i in located], [b.valid[i] for b, i in located], self.n)
 
     def numeric(self, names: Sequence[str]) -> NumericBlock:
         """The block holding exactly these columns, in this order (zero-copy when they are a run of one block)."""
@@ -365,8 +484,10 @@ class ColumnarBatch:
         for tp, names in groups.items():
             if tp in F.NUMERIC_TYPES:
                 blocks.append(NumericBlock.from_lists(names, tp, [columns[nm][1] for nm in names], pin))
-            elif tp in (F.PICKLIST, F.TEXT, F.TEXTAREA):
+            elif tp == F.PICKLIST:
                 blocks.append(DictBlock.from_lists(names, tp, [columns[nm][1] for nm in names], pin))
+            elif tp in (F.TEXT, F.TEXTAREA):
+                blocks.append(TextBlock.from_lists(names, tp, [columns[nm][1] for nm in names], pin))
             else:
                 raise NotImplementedError(f"columns of type {tp} are not supported yet")
         return ColumnarBatch(n or 0, blocks, {}, response)

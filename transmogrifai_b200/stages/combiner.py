@@ -35,9 +35,6 @@ class VectorsCombinerModel(OpModel):
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
         vecs = [batch.vectors[f.name] for f in self.inN]
         meta = self.getMetadata()
-        width = sum(v.width for v in vecs)
-        if width != meta.size:
-            raise ValueError(f"combined width {width} does not match the fitted metadata ({meta.size} columns)")
         parts = [p for v in vecs for p in v.parts]
         stats = VectorStats.concat([v.stats for v in vecs]) if all(v.stats is not None for v in vecs) else None
         return VectorColumn(self.getOutput().name, batch.n, meta, parts, stats)

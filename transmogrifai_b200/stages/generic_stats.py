@@ -11,7 +11,7 @@ import torch
 
 from .. import _lib as L
 from .. import runtime as R
-from ..columnar import (ColumnarBatch, CsrPart, DensePart, LazyDensePart, LazyOneHotPart, OneHotPart,
+from ..columnar import (ColumnarBatch, CsrPart, DensePart, LazyDensePart, LazyOneHotPart, LazyPart, OneHotPart,
                         VectorColumn)
 from ..stats import LabelInfo, VectorStats
 from .numeric import label_info_dev
@@ -129,7 +129,7 @@ def select_columns(vec: VectorColumn, keep: List[int]) -> list:
             L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), n, idx.data_ptr(), len(local),
                    dst.data_ptr(), len(local), R.stream())
             out.append(DensePart(dst))
-        elif isinstance(p, LazyOneHotPart):
+        elif isinstance(p, (LazyOneHotPart, LazyPart)):
             out.append(p.materialize(local))
         elif isinstance(p, OneHotPart):
             if local == list(range(p.width)):

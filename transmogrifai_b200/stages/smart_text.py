@@ -1,0 +1,614 @@
+"""SmartTextVectorizer on the GPU: per text column decide pivot / hash / ignore from its TextStats, pivot the
+categorical ones, tokenise + hash the others, add null indicators.
+
+Reference: core/src/main/scala/com/salesforce/op/stages/impl/feature/SmartTextVectorizer.scala:60-205 (estimator,
+metadata), :207-299 (TextStats), :301-376 (model); OPCollectionHashingVectorizer.scala:184-305 (HashingFun);
+TextTokenizer.scala:160-220.  Output order: [pivot block | hash block | null indicators]  (:354).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from .. import _lib as L
+from .. import dist as D
+from .. import features as F
+from .. import runtime as R
+from ..columnar import ColumnarBatch, LazyPart, OneHotPart, SparseRowsPart, TextBlock, VectorColumn, encode_strings
+from ..metadata import NullString, OpVectorColumnMetadata, OpVectorMetadata, OtherString, feature_column
+from ..stats import LabelInfo, VectorStats
+from .base import OpEstimator, OpModel
+from .numeric import label_info_dev
+from .pivot import _stats_from_class_counts, clean_and_group, top_k
+
+PIVOT, HASH, IGNORE = "Pivot", "Hash", "Ignore"
+MAX_NUM_OF_FEATURES = 1 << 17     # TransmogrifierDefaults.MaxNumOfFeatures
+M64 = (1 << 64) - 1
+
+
+def cell_hash(cleaned: bytes) -> int:
+    """The 64-bit hash text_stats_kernel / text_code_kernel compute over a cleaned cell (FNV-1a + avalanche)."""
+    h = 1469598103934665603
+    for b in cleaned:
+        h = ((h ^ b) * 1099511628211) & M64
+    h ^= h >> 32
+    h = (h * 0xd6e8feb86659fd93) & M64
+    h ^= h >> 32
+    return 0x1234567 if h == M64 else h
+
+
+def murmur3_index(term: str, num_features: int) -> int:
+    """hasher.indexOf(term) of Spark 2.4.5 HashingTF (legacy murmur3_x86_32, seed 42) -- needed on the host only for
+    the feature-name prefix (OPCollectionHashingVectorizer.scala:252)."""
+    data = term.encode("utf-8")
+    m32 = 0xFFFFFFFF
+    rotl = lambda x, r: ((x << r) | (x >> (32 - r))) & m32  # noqa: E731
+
+    def mix_k1(k):
+        k = (k * 0xcc9e2d51) & m32
+        return (rotl(k, 15) * 0x1b873593) & m32
+
+    def mix_h1(h, k):
+        return (rotl(h ^ k, 13) * 5 + 0xe6546b64) & m32
+
+    h, n = 42, len(data)
+    for i in range(0, n - n % 4, 4):
+        h = mix_h1(h, mix_k1(int.from_bytes(data[i:i + 4], "little")))
+    for b in data[n - n % 4:]:
+        h = mix_h1(h, mix_k1((b - 256 if b >= 128 else b) & m32))
+    h ^= n
+    h ^= h >> 16
+    h = (h * 0x85ebca6b) & m32
+    h ^= h >> 13
+    h = (h * 0xc2b2ae35) & m32
+    h ^= h >> 16
+    s = h - (1 << 32) if h >= (1 << 31) else h
+    r = abs(s) % num_features
+    return ((-r if s < 0 else r) + num_features) % num_features
+
+
+def _col_desc(block: TextBlock) -> torch.Tensor:
+    d = np.zeros((len(block.names), 4), dtype=np.int64)
+    for j in range(len(block.names)):
+        d[j, 0] = block.data[j].data_ptr()
+        d[j, 1] = block.offsets[j].data_ptr()
+        d[j, 2] = 0 if block.valid[j] is None else block.valid[j].data_ptr()
+    return torch.from_numpy(d).cuda()
+
+
+class _HashLayout:
+    """Geometry of the hash + null-indicator part of the output vector."""
+
+    def __init__(self, names: Sequence[str], hash_idx: List[int], ignore_idx: List[int], num_features: int,
+                 num_inputs: int, strategy: str, prepend: bool, track_nulls: bool):
+        s = strategy.lower()
+        self.shared = True if s == "shared" else False if s == "separate" else \
+            num_features * num_inputs > MAX_NUM_OF_FEATURES          # isSharedHashSpace :191-199
+        self.num_features = num_features
+        self.hash_idx, self.ignore_idx = hash_idx, ignore_idx
+        self.text_idx = hash_idx + ignore_idx                       # null indicators: hash columns, then ignored
+        self.hash_width = 0 if not hash_idx else (num_features if self.shared else num_features * len(hash_idx))
+        self.null_width = len(self.text_idx) if track_nulls else 0
+        self.width = self.hash_width + self.null_width
+        # the reference zips the NON-PIVOT features (hash and ignore, input order) with the hash columns (:348,358-361)
+        non_pivot = sorted(self.text_idx)
+        self.prefix_names = [names[non_pivot[k]] for k in range(len(hash_idx))]
+        self.prepend = prepend
+
+
+class SmartTextVectorizer(OpEstimator):
+    input_types = (F.TEXT, F.TEXTAREA)
+
+    def __init__(self, uid: Optional[str] = None):
+        super().__init__("smartTxtVec", uid)
+        self.maxCardinality = 1000           # SmartTextVectorizer.MaxCardinality (transmogrify() passes 30)
+        self.minLengthStdDev = 0.0
+        self.coveragePct = 0.90
+        self.topK = 20
+        self.minSupport = 10
+        self.cleanText = True
+        self.trackNulls = True
+        self.trackTextLen = False
+        self.unseenName = OtherString
+        self.numFeatures = 512
+        self.hashSpaceStrategy = "Auto"
+        self.prependFeatureName = True
+        self.binaryFreq = False
+        self.hashWithIndex = False
+        self.minTokenLength = 1
+        self.toLowercase = True
+        self.autoDetectLanguage = False
+
+    # -- params --------------------------------------------------------------------------------------------------------
+    def setMaxCardinality(self, v):  # noqa: N802
+        if not (0 <= v <= 3000):
+            raise ValueError(f"requirement failed: maxCardinality given invalid value {v}")
+        self.maxCardinality = int(v)
+        return self
+
+    def setCoveragePct(self, v):  # noqa: N802
+        if not (0.0 < v <= 1.0):
+            raise ValueError(f"requirement failed: coveragePct given invalid value {v}")
+        self.coveragePct = float(v)
+        return self
+
+    def setMinLengthStdDev(self, v):  # noqa: N802
+        self.minLengthStdDev = float(v)
+        return self
+
+    def setTopK(self, v):  # noqa: N802
+        if v <= 0:
+            raise ValueError(f"requirement failed: topK given invalid value {v}")
+        self.topK = int(v)
+        return self
+
+    def setMinSupport(self, v):  # noqa: N802
+        if v < 0:
+            raise ValueError(f"requirement failed: minSupport given invalid value {v}")
+        self.minSupport = int(v)
+        return self
+
+    def setCleanText(self, v):  # noqa: N802
+        self.cleanText = bool(v)
+        return self
+
+    def setTrackNulls(self, v):  # noqa: N802
+        self.trackNulls = bool(v)
+        return self
+
+    def setTrackTextLen(self, v):  # noqa: N802
+        if v:
+            raise NotImplementedError("trackTextLen is not on the GPU path (default false)")
+        return self
+
+    def setNumFeatures(self, v):  # noqa: N802
+        if not (0 < v <= 10_000_000):      # OPCollectionHashingVectorizer.scala:101-108
+            raise ValueError(f"requirement failed: numFeatures given invalid value {v}")
+        self.numFeatures = int(v)
+        return self
+
+    def setHashSpaceStrategy(self, v):  # noqa: N802
+        if str(v).lower() not in ("auto", "shared", "separate"):
+            raise ValueError(f"requirement failed: hashSpaceStrategy given invalid value {v}")
+        self.hashSpaceStrategy = str(v)
+        return self
+
+    def setPrependFeatureName(self, v):  # noqa: N802
+        self.prependFeatureName = bool(v)
+        return self
+
+    def setBinaryFreq(self, v):  # noqa: N802
+        self.binaryFreq = bool(v)
+        return self
+
+    def setMinTokenLength(self, v):  # noqa: N802
+        self.minTokenLength = int(v)
+        return self
+
+    def setToLowercase(self, v):  # noqa: N802
+        self.toLowercase = bool(v)      # tokens are lower-cased by the analyzer either way (LowerCaseFilter)
+        return self
+
+    def setAutoDetectLanguage(self, v):  # noqa: N802
+        if v:
+            raise NotImplementedError("language detection is not on the GPU path (default false)")
+        return self
+
+    # -- fit -------------------------------------------------------------------------------------------------------
+    def fit(self, batch: ColumnarBatch) -> "SmartTextVectorizerModel":
+        R.require_cuda()
+        if batch.n == 0:
+            raise ValueError("requirement failed: Input dataset cannot be empty")
+        names = [f.name for f in self.inN]
+        block = batch.texts(names)
+        dev = block if block.is_cuda else block.to("cuda")
+        n, ncols = batch.n, len(names)
+        if D.world()[1] > 1:
+            raise NotImplementedError("SmartTextVectorizer.fit is single-rank for now")
+        # 1. TextStats per column
+        values, totals = self._text_stats(dev, n)
+        methods, tops = [], []
+        for c in range(ncols):
+            m, top = self._decide(values[c], totals[c], dev, c, n)
+            methods.append(m)
+            tops.append(top)
+        model = SmartTextVectorizerModel(self, methods, tops)
+        self._metadata = model._metadata = model._build_metadata()
+        # 2. statistics sidecar (needs a categorical label)
+        label_name = batch.response
+        if label_name:
+            y = batch.label()
+            y = y if y.is_cuda else y.cuda()
+            classes, class_counts, ids = label_info_dev(batch, y, label_name)
+            if classes is not None:
+                model._fit_stats = model._sidecar(dev, n, classes, class_counts, ids, label_name)
+        model._fit_key = (block.offsets[0].data_ptr(), n)
+        return model
+
+    def _text_stats(self, dev: TextBlock, n: int):
+        """-> per column ({cleaned value: count} or None when the cardinality cap was exceeded, non-null count)"""
+        ncols = len(dev.names)
+        slots = 64
+        while slots < 4 * (self.maxCardinality + 2):
+            slots <<= 1
+        head, per = C.c_size_t(), C.c_size_t()
+        L.call("tmog_text_stats_layout", ncols, slots, 1, C.byref(head), C.byref(per))
+        tables = torch.zeros(head.value + per.value * ncols, dtype=torch.uint8, device="cuda")
+        flags = torch.zeros(4, dtype=torch.int32, device="cuda")
+        desc = _col_desc(dev)
+        L.call("tmog_text_stats_dev", desc.data_ptr(), ncols, n, None, 1, int(self.cleanText), slots,
+               self.maxCardinality, tables.data_ptr(), flags.data_ptr(), R.stream())
+        if int(flags[0].item()) and self.cleanText:
+            raise ValueError("non-ASCII text met with cleanText = true: Java's Unicode case mapping is not restated on "
+                             "this path")
+        raw = tables[head.value:].cpu().numpy()
+        out_vals, out_tot = [], []
+        for c in range(ncols):
+            q = raw[c * per.value:(c + 1) * per.value]
+            hashes = q[:8 * slots].view(np.uint64)
+            first = q[8 * slots:16 * slots].view(np.uint64)
+            counts = q[16 * slots:16 * slots + 4 * slots].view(np.uint32)
+            tail = 16 * slots + ((4 * slots + 7) & ~7)
+            ndistinct = int(q[tail:tail + 4].view(np.int32)[0])
+            nonnull = int(q[tail + 24:tail + 32].view(np.uint64)[0])
+            out_tot.append(nonnull)
+            if ndistinct > self.maxCardinality:
+                out_vals.append(None)
+                continue
+            used = np.nonzero(hashes != np.uint64(M64))[0]
+            rows = first[used].astype(np.int64)
+            raws = [dev.cell(c, int(r)) for r in rows]
+            ids, distinct = clean_and_group(raws, self.cleanText)
+            vc: Dict[str, int] = {}
+            for k, i in enumerate(ids):
+                vc[distinct[i]] = vc.get(distinct[i], 0) + int(counts[used[k]])
+            out_vals.append(vc)
+        return out_vals, out_tot
+
+    def _frozen_counts(self, dev: TextBlock, c: int, n: int) -> Dict[str, int]:
+        """TextStats of a column whose cardinality exceeds maxCardinality: the reference's left fold stops adding once
+        its map holds more than maxCardinality keys (SmartTextVectorizer.scala:231-235), so only a prefix of the rows
+        counts.  Emulated in row order on a prefix fetched to the host."""
+        rows = 4 * (self.maxCardinality + 8)
+        while True:
+            rows = min(rows, n)
+            raws = [dev.cell(c, r) for r in range(rows)]
+            present = [v for v in raws if v is not None]
+            ids, distinct = clean_and_group(present, self.cleanText)
+            vc: Dict[str, int] = {}
+            for i in ids:
+                if len(vc) > self.maxCardinality:
+                    return vc
+                vc[distinct[i]] = vc.get(distinct[i], 0) + 1
+            if len(vc) > self.maxCardinality or rows >= n:
+                return vc
+            rows *= 4
+
+    def _decide(self, vc: Optional[Dict[str, int]], nonnull: int, dev: TextBlock, c: int, n: int
+                ) -> Tuple[str, List[str]]:
+        """SmartTextVectorizer.fitFn :93-120"""
+        if vc is None:
+            vc = self._frozen_counts(dev, c, n)
+        total = sum(vc.values())
+        filtered = {k: v for k, v in vc.items() if v >= self.minSupport}
+        sorted_counts = sorted(filtered.values(), reverse=True)
+        cum = np.cumsum(sorted_counts) if sorted_counts else np.zeros(0)
+        k = min(self.topK, len(cum)) - 1
+        num = float(cum[k]) if 0 <= k < len(cum) else 0.0
+        coverage = num / total if total else float("nan")
+        card = len(vc)
+        if card > self.maxCardinality and card > self.topK and coverage >= self.coveragePct:
+            method = PIVOT
+        elif card <= self.maxCardinality:
+            method = PIVOT
+        elif self.minLengthStdDev > 0:
+            raise NotImplementedError("minLengthStdDev > 0 (the Ignore route) is not on the GPU path")
+        else:
+            method = HASH
+        vals = list(filtered)
+        order = top_k(vals, np.array([filtered[v] for v in vals], dtype=np.int64), self.topK, self.minSupport) \
+            if vals else []
+        return method, [vals[i] for i in order]
+
+
+class SmartTextVectorizerModel(OpModel):
+    def __init__(self, parent: SmartTextVectorizer, vectorizationMethods: List[str],  # noqa: N803
+                 topValues: List[List[str]]):  # noqa: N803
+        super().__init__(parent)
+        self.vectorizationMethods = list(vectorizationMethods)
+        self.topValues = [list(t) for t in topValues]
+        self.shouldCleanText = parent.cleanText
+        self.shouldTrackNulls = parent.trackNulls
+        p = parent
+        self.hashingParams = dict(numFeatures=p.numFeatures, numInputs=len(parent.inN), binaryFreq=p.binaryFreq,
+                                  prependFeatureName=p.prependFeatureName, hashSpaceStrategy=p.hashSpaceStrategy,
+                                  minTokenLength=p.minTokenLength)
+        self.unseenName = p.unseenName
+        self._fit_stats: Optional[VectorStats] = None
+        self._fit_key = None
+        names = [f.name for f in self.inN]
+        self.pivot_idx = [j for j, m in enumerate(self.vectorizationMethods) if m == PIVOT]
+        hash_idx = [j for j, m in enumerate(self.vectorizationMethods) if m == HASH]
+        ignore_idx = [j for j, m in enumerate(self.vectorizationMethods) if m == IGNORE]
+        self.layout = _HashLayout(names, hash_idx, ignore_idx, p.numFeatures, len(names), p.hashSpaceStrategy,
+                                  p.prependFeatureName, p.trackNulls)
+        self.pivot_widths = [len(self.topValues[j]) + (2 if self.shouldTrackNulls else 1) for j in self.pivot_idx]
+        self.pivot_width = sum(self.pivot_widths)
+
+    @property
+    def categoricalTopValues(self) -> List[List[str]]:  # noqa: N802
+        return [self.topValues[j] for j in self.pivot_idx]
+
+    # -- metadata (SmartTextVectorizer.makeVectorMetadata :154-186) ----------------------------------------------------
+    def _build_metadata(self) -> OpVectorMetadata:
+        feats = self.inN
+        cols: List[OpVectorColumnMetadata] = []
+        for j in self.pivot_idx:
+            f = feats[j]
+            vals = list(self.topValues[j]) + [self.unseenName] + ([NullString] if self.shouldTrackNulls else [])
+            cols += [OpVectorColumnMetadata((f.name,), (f.type_name,), grouping=f.name, indicatorValue=v)
+                     for v in vals]
+        lay = self.layout
+        if lay.text_idx:
+            hf = [feats[j] for j in lay.hash_idx]
+            if lay.hash_idx:
+                if lay.shared:
+                    shared_col = OpVectorColumnMetadata(tuple(f.name for f in hf), tuple(f.type_name for f in hf))
+                    cols += [shared_col] * lay.num_features
+                else:
+                    for f in hf:
+                        cols += [feature_column(f.name, f.type_name)] * lay.num_features
+            # the reference appends the null-indicator columns to the metadata whether or not nulls are tracked
+            # (SmartTextVectorizer.scala:176-183); kept as is, SanityChecker then rejects the width mismatch
+            cols += [feature_column(feats[j].name, feats[j].type_name, is_null=True) for j in lay.text_idx]
+        return OpVectorMetadata(self.parent.getOutputFeatureName(), cols, self.parent.history())
+
+    # -- device tables -------------------------------------------------------------------------------------------------
+    def _pivot_tables(self, dev: TextBlock, n: int):
+        """Small hash tables holding just the top values of every pivoted column, and the dictionary codes of all
+        rows against them (code -2 = a value outside the vocabulary -> OTHER)."""
+        k = len(self.pivot_idx)
+        slots = 64
+        while slots < 4 * (max((len(self.topValues[j]) for j in self.pivot_idx), default=0) + 2):
+            slots <<= 1
+        head, per = C.c_size_t(), C.c_size_t()
+        ncols = len(dev.names)
+        L.call("tmog_text_stats_layout", ncols, slots, 1, C.byref(head), C.byref(per))
+        host = np.zeros(head.value + per.value * ncols, dtype=np.uint8)
+        # struct TextStatsTable {hash*, first_row*, counts*, ndistinct*, len_sum*, nonnull*} per column
+        tables = torch.zeros(len(host), dtype=torch.uint8, device="cuda")
+        base = tables.data_ptr() + head.value
+        ptrs = np.zeros((ncols, 6), dtype=np.int64)
+        slot_of: List[Dict[str, int]] = []
+        for c in range(ncols):
+            q0 = base + per.value * c
+            tail = 16 * slots + ((4 * slots + 7) & ~7)
+            ptrs[c] = [q0, q0 + 8 * slots, q0 + 16 * slots, q0 + tail, q0 + tail + 8, q0 + tail + 24]
+            hashes = np.full(slots, M64, dtype=np.uint64)
+            mapping: Dict[str, int] = {}
+            if c in self.pivot_idx:
+                for v in self.topValues[c]:
+                    h = cell_hash(v.encode("utf-8"))
+                    s = (h >> 20) & (slots - 1)
+                    while hashes[s] != np.uint64(M64):
+                        s = (s + 1) & (slots - 1)
+                    hashes[s] = np.uint64(h)
+                    mapping[v] = s
+            off = head.value + per.value * c
+            host[off:off + 8 * slots] = hashes.view(np.uint8)
+            slot_of.append(mapping)
+        host[:ptrs.nbytes] = ptrs.view(np.uint8).reshape(-1)
+        tables.copy_(torch.from_numpy(host))
+        ld = (n + 3) // 4 * 4
+        codes = torch.empty((max(k, 1), ld), dtype=torch.int32, device="cuda")
+        sel = torch.tensor(self.pivot_idx or [0], dtype=torch.int32, device="cuda")
+        desc = _col_desc(dev)
+        L.call("tmog_text_codes_dev", desc.data_ptr(), sel.data_ptr(), k, n, int(self.shouldCleanText), slots,
+               tables.data_ptr(), codes.data_ptr(), ld, R.stream())
+        return codes, ld, slots, slot_of
+
+    def _pivot_pos_tables(self, slots: int, slot_of, newpos: np.ndarray):
+        """pos tables for tmog_pivot_transform_dev over the slot codes: entry s = output index of the value in slot s,
+        every other slot (and code -2, clamped to `slots`) = OTHER... the null code -1 -> null indicator."""
+        tables, desc = [], []
+        off, slot_off = 0, 0
+        for t, j in enumerate(self.pivot_idx):
+            top = self.topValues[j]
+            tab = np.full(slots + 2, newpos[off + len(top)], dtype=np.int32)           # default: OTHER
+            for i, v in enumerate(top):
+                tab[slot_of[j][v]] = newpos[off + i]
+            # layout expected by the kernel: ncodes + 1 entries, the last one for a null (code < 0 or >= ncodes)
+            tab[slots + 1] = newpos[off + len(top) + 1] if self.shouldTrackNulls else -1
+            tables.append(tab)
+            desc.append([slots + 2, slot_off, 0, slots + 1])
+            slot_off += slots + 1
+            off += self.pivot_widths[t]
+        return np.concatenate(tables) if tables else np.zeros(1, dtype=np.int32), \
+            np.asarray(desc, dtype=np.int64).reshape(-1, 4)
+
+    def _hash_args(self, dev: TextBlock):
+        lay = self.layout
+        hp = self.hashingParams
+        k = len(lay.hash_idx)
+        prefix = np.zeros((max(k, 1), 16), dtype=np.uint8)
+        plen = np.zeros(max(k, 1), dtype=np.int32)
+        for t in range(k):
+            s = f"{murmur3_index(lay.prefix_names[t], lay.num_features)}_".encode("ascii")
+            prefix[t, :len(s)] = np.frombuffer(s, dtype=np.uint8)
+            plen[t] = len(s)
+        sub = dev.rows(lay.hash_idx)
+        params = np.array([lay.num_features, int(lay.shared), int(hp["binaryFreq"]), hp["minTokenLength"],
+                           int(self.shouldTrackNulls), int(hp["prependFeatureName"]), lay.hash_width, 0],
+                          dtype=np.int32)
+        return sub, torch.from_numpy(prefix).cuda(), torch.from_numpy(plen).cuda(), params
+
+    # -- statistics sidecar --------------------------------------------------------------------------------------------
+    def _sidecar(self, dev: TextBlock, n: int, classes, class_counts, ids, label_name: str) -> VectorStats:
+        ncls = len(classes)
+        parts = []
+        if self.pivot_idx:
+            codes, ld, slots, slot_of = self._pivot_tables(dev, n)
+            # count per slot code: remap -2 (unknown value) to slot index `slots` so that it lands in OTHER
+            codes = torch.where(codes == -2, torch.full_like(codes, slots), codes)
+            k = len(self.pivot_idx)
+            nids = slots + 2
+            desc = np.zeros((k, 4), dtype=np.int64)
+            for t in range(k):
+                desc[t] = [nids, 0, t * nids * ncls, slots + 1]
+            d_desc = torch.from_numpy(desc).cuda()
+            d_counts = torch.zeros(k * nids * ncls, dtype=torch.int32, device="cuda")
+            d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+            L.call("tmog_pivot_count_dev", codes.data_ptr(), ld, n, k, ids.data_ptr(), ncls, d_desc.data_ptr(), None,
+                   nids, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
+            cnt = (d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(k, nids, ncls)
+            rows = []
+            for t, j in enumerate(self.pivot_idx):
+                top = self.topValues[j]
+                tab = cnt[t]                       # row 0 = null, row 1 + s = slot s, row 1 + slots = unknown
+                chosen = [1 + slot_of[j][v] for v in top]
+                rest = np.ones(nids, dtype=bool)
+                rest[0] = False
+                rest[chosen] = False
+                r = [tab[i] for i in chosen] + [tab[rest].sum(axis=0)]
+                if self.shouldTrackNulls:
+                    r.append(tab[0])
+                rows.append(np.stack(r).astype(np.float64))
+            parts.append(_stats_from_class_counts(np.concatenate(rows, axis=0), classes, class_counts, n, label_name))
+        lay = self.layout
+        if lay.text_idx:
+            if lay.ignore_idx:
+                raise NotImplementedError("ignored text columns are not on the GPU path")
+            sub, d_prefix, d_plen, params = self._hash_args(dev)
+            params[7] = ncls
+            w = lay.hash_width + len(lay.hash_idx)
+            class_sum = torch.zeros(w * ncls, dtype=torch.int32, device="cuda")
+            nnz = torch.zeros(w, dtype=torch.int32, device="cuda")
+            extra = torch.zeros(w, dtype=torch.int64, device="cuda")
+            aux = torch.zeros(3 * w, dtype=torch.int32, device="cuda")
+            flags = torch.zeros(4, dtype=torch.int32, device="cuda")
+            desc = _col_desc(sub)
+            L.call("tmog_text_hash_stats_dev", desc.data_ptr(), len(lay.hash_idx), n, d_prefix.data_ptr(),
+                   d_plen.data_ptr(), params.ctypes.data, ids.data_ptr(), class_sum.data_ptr(), nnz.data_ptr(),
+                   extra.data_ptr(), aux.data_ptr(), flags.data_ptr(), R.stream())
+            _check_hash_flags(flags)
+            cs = (class_sum.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(w, ncls).astype(np.float64)
+            nz = (nnz.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).astype(np.float64)
+            ex = extra.cpu().numpy().astype(np.float64)
+            ax = (aux.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(w, 3)
+            if not self.shouldTrackNulls:
+                cs, nz, ex, ax = cs[:lay.hash_width], nz[:lay.hash_width], ex[:lay.hash_width], ax[:lay.hash_width]
+            self._hash_nnz = nz
+            parts.append(_stats_from_bucket_sums(cs, nz, ex, ax, classes, class_counts, n, label_name,
+                                                 lay.hash_width))
+        return VectorStats.concat(parts)
+
+    # -- transform -----------------------------------------------------------------------------------------------------
+    def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
+        R.require_cuda()
+        names = [f.name for f in self.inN]
+        block = batch.texts(names)
+        n = batch.n
+        parts = []
+        same = self._fit_key == (block.offsets[0].data_ptr(), n)
+        if self.pivot_idx:
+            parts.append(LazyPart(self.pivot_width, lambda keep: self._materialize_pivot(block, n, keep)))
+        if self.layout.text_idx:
+            parts.append(LazyPart(self.layout.width, lambda keep: self._materialize_hash(block, n, keep, same)))
+        return VectorColumn(self.getOutput().name, n, self.getMetadata(), parts, self._fit_stats if same else None)
+
+    def _materialize_pivot(self, block: TextBlock, n: int, keep) -> OneHotPart:
+        dev = block if block.is_cuda else block.to("cuda")
+        width = self.pivot_width
+        newpos = np.arange(width, dtype=np.int32)
+        out_width = width
+        if keep is not None:
+            newpos = np.full(width, -1, dtype=np.int32)
+            newpos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
+            out_width = len(keep)
+        codes, ld, slots, slot_of = self._pivot_tables(dev, n)
+        codes = torch.where(codes == -2, torch.full_like(codes, slots), codes)
+        pos, desc = self._pivot_pos_tables(slots, slot_of, newpos)
+        k = len(self.pivot_idx)
+        out = torch.empty((n, max(k, 1)), dtype=torch.int32, device="cuda")
+        d_desc, d_pos = torch.from_numpy(desc).cuda(), torch.from_numpy(pos).cuda()
+        L.call("tmog_pivot_transform_dev", codes.data_ptr(), ld, n, k, d_desc.data_ptr(), d_pos.data_ptr(),
+               out.data_ptr(), out.shape[1], 0, R.stream())
+        return OneHotPart(out[:, :k], out_width)
+
+    def _materialize_hash(self, block: TextBlock, n: int, keep, same_batch: bool) -> SparseRowsPart:
+        dev = block if block.is_cuda else block.to("cuda")
+        lay = self.layout
+        if lay.ignore_idx:
+            raise NotImplementedError("ignored text columns are not on the GPU path")
+        width = lay.width
+        full = lay.hash_width + len(lay.hash_idx)
+        newpos = np.full(full, -1, dtype=np.int32)
+        if keep is None:
+            newpos[:width] = np.arange(width, dtype=np.int32)
+            out_width = width
+        else:
+            newpos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
+            out_width = len(keep)
+        sub, d_prefix, d_plen, params = self._hash_args(dev)
+        params[7] = 1
+        desc = _col_desc(sub)
+        d_newpos = torch.from_numpy(newpos).cuda()
+        row_start = torch.empty(n, dtype=torch.int64, device="cuda")
+        row_nnz = torch.empty(n, dtype=torch.int32, device="cuda")
+        flags = torch.zeros(4, dtype=torch.int32, device="cuda")
+        cursor = torch.zeros(1, dtype=torch.int64, device="cuda")
+        nz = getattr(self, "_hash_nnz", None)
+        if same_batch and nz is not None:      # exact size known from the fit pass over the same rows
+            capacity = int(nz[newpos[:len(nz)] >= 0].sum())
+        else:                                  # sizing pass
+            L.call("tmog_text_hash_transform_dev", desc.data_ptr(), len(lay.hash_idx), n, d_prefix.data_ptr(),
+                   d_plen.data_ptr(), params.ctypes.data, d_newpos.data_ptr(), row_start.data_ptr(),
+                   row_nnz.data_ptr(), None, None, cursor.data_ptr(), 0, flags.data_ptr(), R.stream())
+            capacity = int(cursor.item())
+            cursor.zero_()
+            flags.zero_()
+        idx = torch.empty(max(capacity, 1), dtype=torch.int32, device="cuda")
+        val = torch.empty(max(capacity, 1), dtype=torch.int32, device="cuda")
+        L.call("tmog_text_hash_transform_dev", desc.data_ptr(), len(lay.hash_idx), n, d_prefix.data_ptr(),
+               d_plen.data_ptr(), params.ctypes.data, d_newpos.data_ptr(), row_start.data_ptr(), row_nnz.data_ptr(),
+               idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), capacity, flags.data_ptr(), R.stream())
+        _check_hash_flags(flags)
+        return SparseRowsPart(row_start, row_nnz, idx, val, out_width)
+
+
+def _check_hash_flags(flags: torch.Tensor) -> None:
+    f = flags.cpu().numpy()
+    if f[0]:
+        raise ValueError("non-ASCII text met: Lucene's Unicode word-break rules are restated for ASCII only")
+    if f[1]:
+        raise ValueError("a text cell holds more than 512 tokens: beyond the GPU tokenizer's per-cell capacity")
+    if f[2]:
+        raise ValueError("a row holds more than 4096 hashed tokens: beyond the GPU path's per-row capacity")
+    if f[3]:
+        raise RuntimeError("sparse output capacity exceeded")
+
+
+def _stats_from_bucket_sums(class_sum: np.ndarray, nnz: np.ndarray, sq_extra: np.ndarray, aux: np.ndarray, classes,
+                            class_counts, n: int, label_name: str, hash_width: int) -> VectorStats:
+    """Column statistics of term-frequency columns from per-class sums: sum v = sum_c S_c,
+    sum v^2 = sum v + extra, cov(v, y) = sum_c y_c S_c - mean_y sum v."""
+    cc = class_counts.astype(np.float64)
+    mean_y = float((classes * cc).sum() / n)
+    var_y = float((cc * (classes - mean_y) ** 2).sum() / (n - 1)) if n > 1 else 0.0
+    lab = np.array([n, mean_y, var_y, classes.min(), classes.max()])
+    sv = class_sum.sum(axis=1)
+    sv2 = sv + sq_extra
+    mean = sv / n
+    var = (sv2 - sv * sv / n) / (n - 1) if n > 1 else np.zeros_like(sv)
+    var = np.maximum(var, 0.0)
+    # term frequencies are >= 1 where present; aux = [max tf, ~min tf among tf > 1, rows with tf > 1]
+    mx = np.where(nnz > 0, np.maximum(aux[:, 0], 1), 0).astype(np.float64)
+    min_gt1 = (~aux[:, 1]) & 0xFFFFFFFF
+    mn = np.where(nnz >= n, np.where(aux[:, 2] >= nnz, min_gt1, 1), 0).astype(np.float64)
+    cov = class_sum @ (classes - mean_y)
+    cs = np.full((len(classes), len(sv)), np.nan)
+    cs[:, hash_width:] = class_sum[hash_width:].T          # null indicators are categorical columns
+    return VectorStats(LabelInfo(label_name, n, lab, classes, class_counts), mean, var, mn, mx, cov, cs)
