@@ -172,6 +172,12 @@ int tmog_pivot_count_dev(const int32_t* codes, int64_t ld, int64_t n, int ncols,
                          int nclasses, const int64_t* col_desc, const int32_t* slots, int64_t max_nids,
                          uint32_t* counts, int* bad_code, void* stream);
 
+/* Binary columns (u8 values + validity) as codes -1 null / 0 false / 1 true in codes[ncols][ldc] (ldc a multiple of 4),
+ * so that tmog_pivot_count_dev yields the SanityChecker sums of BinaryVectorizer's [value, isNull] columns
+ * (C/stages/impl/feature/BinaryVectorizer.scala:70-82) in the same pass as the pivoted columns. */
+int tmog_binary_codes_dev(const uint8_t* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n, int ncols,
+                          int32_t* codes, int64_t ldc, void* stream);
+
 /* Replaces OneHotModelFun.pivotFn  C/stages/impl/feature/OpOneHotVectorizer.scala:416-437  for single-valued inputs
  * (exactly one of {top value, OTHER, null indicator} is 1.0 per row and column) fused with reindex
  * (Transmogrifier.scala:437-449) and SanityCheckerModel's removeFeatures:  out[r][out_col0 + c] = pos_c[code], the

@@ -177,3 +177,68 @@ def test_transmogrify_sanity_check_real_matches_oracle(device, n, ncols, corr_le
     np.testing.assert_allclose(got, xo[:, ref.indices_to_keep], rtol=1e-12)
     assert out_batch.vectors[checked.name].metadata.columnNames() == \
         [f"{m.col_name().rsplit('_', 1)[0]}_{i}" for i, m in enumerate(metas[j] for j in ref.indices_to_keep)]
+
+
+@pytest.mark.parametrize("device", [None, "cuda"])
+def test_transmogrify_all_types_matches_oracle(device):
+    """Config-5 shape in miniature: Binary + PickList + Real + RealNN + Text through transmogrify() + sanityCheck();
+    type groups in type-name order; every statistic from the fused sidecars against the oracle."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+    rng = np.random.default_rng(31)
+    n = 2000
+    y = (rng.random(n) < 0.3).astype(np.float64)
+    opt = lambda v, p: None if rng.random() < p else v   # noqa: E731
+    b0 = [opt(bool(rng.random() < 0.4 + 0.3 * yy), 0.1) for yy in y]
+    b1 = [opt(bool(rng.random() < 0.5), 0.05) for _ in y]
+    p0 = [opt(["x", "y", "z", "X ", "w"][int(rng.integers(5))], 0.08) for _ in y]
+    r0 = [opt(float(rng.normal(2 + yy, 1)), 0.1) for yy in y]
+    r1 = [opt(float(rng.normal(0, 3)), 0.02) for _ in y]
+    nn = [float(v) for v in rng.normal(5, 2, n)]
+    words = ["".join(rng.choice(list("abcdefgh"), size=rng.integers(3, 7))) for _ in range(150)]
+    t0 = [opt(" ".join(words[i] for i in rng.integers(0, 150, rng.poisson(8))), 0.06) for _ in y]
+    data = {"b0": (F.BINARY, b0), "b1": (F.BINARY, b1), "p0": (F.PICKLIST, p0), "r0": (F.REAL, r0), "r1": (F.REAL, r1),
+            "nn": (F.REALNN, nn), "t0": (F.TEXT, t0), "y": (F.REALNN, y.tolist())}
+    batch = _batch(data, response="y", device=device)
+    FB = F.FeatureBuilder
+    feats = [FB.Text("t0").asPredictor(), FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(),
+             FB.RealNN("nn").asPredictor(), FB.PickList("p0").asPredictor(), FB.Real("r1").asPredictor(),
+             FB.Binary("b1").asPredictor()]
+    label = FB.RealNN("y").asResponse()
+    checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
+                                sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
+    out_batch, fitted = fit_and_transform(batch, checked)
+    est = checked.origin_stage
+    # oracle, Transmogrifier.scala:114 order: Binary < PickList < Real < RealNN < Text
+    xb = V.binary_vectorizer_transform([b0, b1])
+    tops = V.pivot_fit([p0], 20, 10, True)
+    xp = V.pivot_transform([p0], tops, True, True)
+    fills = V.real_vectorizer_fit([r0, r1])
+    xr = V.real_vectorizer_transform([r0, r1], fills, True)
+    xn = V.realnn_vectorizer_transform([nn])
+    methods, ttops = V.smart_text_fit([t0], max_cardinality=30, top_k=20, min_support=10)
+    xt = V.smart_text_transform([t0], ["t0"], methods, ttops, num_features=512)
+    xo, metas = V.combine(
+        [xb, xp, xr, xn, xt],
+        [V.numeric_metadata(["b0", "b1"], "Binary", True), V.pivot_metadata(["p0"], "PickList", tops, True),
+         V.numeric_metadata(["r0", "r1"], "Real", True), V.numeric_metadata(["nn"], "RealNN", False),
+         V.smart_text_metadata(["t0"], "Text", methods, ttops, 512, True)])
+    p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                       feature_feature_corr_level="off")
+    ref = S.sanity_fit(y, xo, metas, p, label_name="y")
+    assert est.summary.names[:-1] == [m.col_name() for m in metas]
+    assert est.summary.dropped == ref.dropped
+    assert fitted[-1].indicesToKeep == ref.indices_to_keep
+    np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+    assert np.array_equal(est.summary.min, ref.col_stats.min) and np.array_equal(est.summary.max, ref.col_stats.max)
+    np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                               equal_nan=True)
+    got_g = {g.group: g for g in est.summary.categoricalStats}
+    assert got_g.keys() == {g.group for g in ref.cat_stats}
+    for g in ref.cat_stats:
+        assert np.array_equal(got_g[g.group].contingencyMatrix, g.contingency_matrix)
+        np.testing.assert_allclose(got_g[g.group].cramersV, g.cramers_v, rtol=1e-9, equal_nan=True)
+    got = out_batch.vectors[checked.name].to_scipy()
+    exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
+    assert got.shape == exp.shape and abs(got - exp).max() < 1e-9

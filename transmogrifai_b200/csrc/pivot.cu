@@ -269,3 +269,33 @@ extern "C" int tmog_pivot_transform_dev(const int32_t* codes, int64_t ld, int64_
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }
+
+// Binary columns as dictionary codes (-1 null, 0 false, 1 true), so that their SanityChecker statistics come out of
+// the same count[code][class] table as the pivoted columns.
+namespace tmog {
+__global__ void __launch_bounds__(256)
+binary_codes_kernel(const uint8_t* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid, int64_t ldv,
+                    int64_t n, int32_t* __restrict__ codes, int64_t ldc) {
+    const int c = blockIdx.y;
+    const uint8_t* col = values + (int64_t)c * ld;
+    const uint64_t* vcol = valid ? valid + (int64_t)c * ldv : nullptr;
+    int32_t* out = codes + (int64_t)c * ldc;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += stride) {
+        const bool ok = vcol ? ((vcol[r >> 6] >> (r & 63)) & 1ull) != 0 : true;
+        out[r] = ok ? (col[r] != 0 ? 1 : 0) : -1;
+    }
+}
+}  // namespace tmog
+
+extern "C" int tmog_binary_codes_dev(const uint8_t* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n,
+                                     int ncols, int32_t* codes, int64_t ldc, void* stream) {
+    TMOG_REQUIRE(n >= 0 && ncols >= 0 && ld >= n && ldc >= n, "bad shape");
+    TMOG_REQUIRE(valid == nullptr || ldv >= (n + 63) / 64, "bitmap stride too small");
+    if (n == 0 || ncols == 0) return TMOG_OK;
+    TMOG_REQUIRE(values && codes, "NULL argument");
+    const int gx = (int)std::min<int64_t>((n + 255) / 256, (int64_t)tmog::sm_count() * 8);
+    tmog::binary_codes_kernel<<<dim3(gx, ncols), 256, 0, (cudaStream_t)stream>>>(values, ld, valid, ldv, n, codes, ldc);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}

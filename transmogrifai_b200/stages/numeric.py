@@ -300,7 +300,8 @@ class RealNNVectorizer(OpTransformer):
             raise ValueError("None.get: a RealNN feature holds a null")
         chunk = self.chunkRows
         part = LazyDensePart(len(block.names), lambda keep: _transform_numeric(block, None, False, chunk, keep=keep))
-        return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part], None)
+        stats = _realnn_stats(batch, block) if batch.response else None
+        return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part], stats)
 
 
 class BinaryVectorizer(OpTransformer):
@@ -334,4 +335,76 @@ class BinaryVectorizer(OpTransformer):
         track, chunk, fv = self.trackNulls, self.chunkRows, self.fillValue
         part = LazyDensePart(len(block.names) * (2 if track else 1),
                              lambda keep: _transform_numeric(block, None, track, chunk, fv, keep=keep))
-        return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part], None)
+        stats = _binary_stats(batch, block, track, fv) if batch.response else None
+        return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part], stats)
+
+
+def _realnn_stats(batch: ColumnarBatch, block: NumericBlock) -> Optional[VectorStats]:
+    """Statistics sidecar of a RealNN block: the fused fit scan without nulls (the vectorizer itself has no fit)."""
+    label_name = batch.response
+    dev = block if block.is_cuda else block.to("cuda")
+    y = batch.label()
+    y = y if y.is_cuda else y.cuda()
+    n, ncols = batch.n, len(block.names)
+    nb = C.c_size_t()
+    L.call("tmog_real_fit_scratch_bytes", ncols, C.byref(nb))
+    scratch = R.scratch("real_fit", nb.value)
+    d_shifts = torch.zeros(ncols + 1, dtype=torch.float64, device="cuda")
+    d_part = torch.zeros((ncols + 1) * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
+    L.call("tmog_real_pilot_shift_dev", dev.values.data_ptr(), dev.ld, None, 0, y.data_ptr(), n, ncols,
+           d_shifts.data_ptr(), R.stream())
+    if D.world()[1] > 1:
+        torch.distributed.broadcast(d_shifts, src=0)
+    L.call("tmog_real_fit_partials_dev", dev.values.data_ptr(), dev.ld, None, 0, y.data_ptr(), n, ncols,
+           d_shifts.data_ptr(), scratch.data_ptr(), scratch.numel(), d_part.data_ptr(), R.stream())
+    partials = D.allreduce_real_partials(d_part.cpu().numpy())
+    shifts = d_shifts.cpu().numpy()
+    classes, counts, _ids = label_info_dev(batch, y, label_name)
+    mean, var, mn, mx, cov = (np.zeros(ncols) for _ in range(5))
+    lab = np.zeros(5)
+    L.call("tmog_real_finish", partials.ctypes.data, shifts.ctypes.data, ncols, 1, 0.0, 0, None, mean.ctypes.data,
+           var.ctypes.data, mn.ctypes.data, mx.ctypes.data, cov.ctypes.data, lab.ctypes.data, None)
+    cs = None if classes is None else np.full((len(classes), ncols), np.nan)
+    return VectorStats(LabelInfo(label_name, int(lab[0]), lab, classes, counts), mean, var, mn, mx, cov, cs)
+
+
+def _binary_stats(batch: ColumnarBatch, block: NumericBlock, track_nulls: bool, fill_value: bool
+                  ) -> Optional[VectorStats]:
+    """Statistics sidecar of BinaryVectorizer's [value, isNull] columns from count[{null, false, true}][label class]
+    (needs a categorical label; otherwise SanityChecker scans the materialised block)."""
+    from .pivot import _stats_from_class_counts
+    label_name = batch.response
+    dev = block if block.is_cuda else block.to("cuda")
+    y = batch.label()
+    y = y if y.is_cuda else y.cuda()
+    classes, class_counts, ids = label_info_dev(batch, y, label_name)
+    if classes is None:
+        return None
+    n, ncols, ncls = batch.n, len(block.names), len(classes)
+    ldc = round_up(max(n, 1), 4)
+    codes = torch.empty((ncols, ldc), dtype=torch.int32, device="cuda")
+    L.call("tmog_binary_codes_dev", dev.values.data_ptr(), dev.ld, R.ptr(dev.valid), dev.ldv, n, ncols,
+           codes.data_ptr(), ldc, R.stream())
+    desc = np.zeros((ncols, 4), dtype=np.int64)
+    for c in range(ncols):
+        desc[c] = [3, 0, c * 3 * ncls, 2]          # ids: 0 null, 1 false, 2 true
+    d_desc = torch.from_numpy(desc).cuda()
+    d_counts = torch.zeros(ncols * 3 * ncls, dtype=torch.int32, device="cuda")
+    d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    L.call("tmog_pivot_count_dev", codes.data_ptr(), ldc, n, ncols, ids.data_ptr(), ncls, d_desc.data_ptr(), None, 3,
+           d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
+    cnt = D.allreduce_sum(d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(ncols, 3, ncls)
+    n_global = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
+    rows = []
+    for c in range(ncols):
+        ones = cnt[c, 2] + (cnt[c, 0] if fill_value else 0)
+        rows.append(ones)
+        if track_nulls:
+            rows.append(cnt[c, 0])
+    st = _stats_from_class_counts(np.stack(rows).astype(np.float64), classes, class_counts, n_global, label_name)
+    if st.class_sums is not None:                    # only the null indicators are categorical columns
+        keep = np.zeros(st.width, dtype=bool)
+        if track_nulls:
+            keep[1::2] = True
+        st.class_sums[:, ~keep] = np.nan
+    return st
