@@ -297,6 +297,15 @@ int tmog_dense_gather_dev(const double* x, int64_t ld, int64_t n, const int32_t*
 int tmog_dense_gram_dev(const double* x, int64_t ld, int64_t n, int d, const double* label, const double* shifts,
                         double* gram, void* stream);
 
+/* Sparse OPVector parts written into columns [out_col0, ...) of a dense row-major block that the caller has zeroed
+ * (input of tmog_dense_gram_dev for CorrelationLevel.Computed): the one-hot form of tmog_pivot_transform_dev
+ * (indices [n][idx_ld], -1 = no entry, value 1.0) and the 4-array sparse rows of tmog_text_hash_transform_dev. */
+int tmog_onehot_densify_dev(const int32_t* indices, int64_t idx_ld, int64_t n, int k, double* out, int64_t out_ld,
+                            int64_t out_col0, void* stream);
+int tmog_sparse_rows_densify_dev(const int64_t* row_start, const int32_t* row_nnz, const int32_t* indices,
+                                 const int32_t* values, int64_t n, double* out, int64_t out_ld, int64_t out_col0,
+                                 void* stream);
+
 /* Host: Pearson matrix [(D)^2] from the shifted Gramian and the shifted column sums (partials[.][1]) -- Spark's
  * computeCovariance + computeCorrelationMatrixFromCovariance: NaN where |cov_ii| <= 1e-12, diagonal 1.0. */
 int tmog_pearson_from_gram(int D, double n, const double* gram, const double* sums, double* corr);

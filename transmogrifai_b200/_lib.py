@@ -69,6 +69,8 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_dense_stats_dev": [_p, _i64, _i64, _int, _p, _p, _int, _p, _p, _p, _sz, _p, _p, _p],
     "tmog_dense_gather_dev": [_p, _i64, _i64, _p, _int, _p, _i64, _p],
     "tmog_dense_gram_dev": [_p, _i64, _i64, _int, _p, _p, _p, _p],
+    "tmog_onehot_densify_dev": [_p, _i64, _i64, _int, _p, _i64, _i64, _p],
+    "tmog_sparse_rows_densify_dev": [_p, _p, _p, _p, _i64, _p, _i64, _i64, _p],
     "tmog_pearson_from_gram": [_int, _dbl, _p, _p, _p],
     "tmog_contingency_stats": [_p, _int, _int, _p, _p, _p, _p, _p, _p],
     "tmog_contingency_stats_batch": [_int, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],

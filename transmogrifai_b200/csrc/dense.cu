@@ -284,3 +284,58 @@ extern "C" int tmog_pearson_from_gram(int D, double n, const double* gram, const
         }
     return TMOG_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Sparse OPVector parts -> columns of a dense row-major block (for CorrelationLevel.Computed, whose Gramian kernel
+// works on dense rows; Spark's RowMatrix densifies the same way through BLAS spr/dspr).  The caller zeroes the block.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace tmog {
+__global__ void __launch_bounds__(256)
+onehot_densify_kernel(const int32_t* __restrict__ idx, int64_t idx_ld, int64_t n, int k, double* __restrict__ out,
+                      int64_t out_ld, int64_t out_col0) {
+    const int64_t total = n * (int64_t)k;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / k;
+        const int v = idx[r * idx_ld + (i - r * k)];
+        if (v >= 0) out[r * out_ld + out_col0 + v] = 1.0;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+sparse_rows_densify_kernel(const int64_t* __restrict__ row_start, const int32_t* __restrict__ row_nnz,
+                           const int32_t* __restrict__ idx, const int32_t* __restrict__ val, int64_t n,
+                           double* __restrict__ out, int64_t out_ld, int64_t out_col0) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const int64_t s = row_start[r];
+        const int m = row_nnz[r];
+        for (int e = lane; e < m; e += 32) out[r * out_ld + out_col0 + idx[s + e]] = (double)val[s + e];
+    }
+}
+}  // namespace tmog
+
+extern "C" int tmog_onehot_densify_dev(const int32_t* indices, int64_t idx_ld, int64_t n, int k, double* out,
+                                       int64_t out_ld, int64_t out_col0, void* stream) {
+    TMOG_REQUIRE(n >= 0 && k >= 0 && idx_ld >= k && out_col0 >= 0, "bad shape");
+    if (n == 0 || k == 0) return TMOG_OK;
+    TMOG_REQUIRE(indices && out, "NULL argument");
+    const int grid = (int)std::min<int64_t>((n * (int64_t)k + 255) / 256, (int64_t)sm_count() * 16);
+    onehot_densify_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(indices, idx_ld, n, k, out, out_ld, out_col0);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_sparse_rows_densify_dev(const int64_t* row_start, const int32_t* row_nnz, const int32_t* indices,
+                                            const int32_t* values, int64_t n, double* out, int64_t out_ld,
+                                            int64_t out_col0, void* stream) {
+    TMOG_REQUIRE(n >= 0 && out_col0 >= 0, "bad shape");
+    if (n == 0) return TMOG_OK;
+    TMOG_REQUIRE(row_start && row_nnz && out, "NULL argument");
+    const int grid = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)sm_count() * 16);
+    sparse_rows_densify_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(row_start, row_nnz, indices, values, n, out, out_ld,
+                                                                       out_col0);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}

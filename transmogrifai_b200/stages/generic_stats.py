@@ -25,14 +25,38 @@ def _device_label(batch: ColumnarBatch, label_name: str) -> torch.Tensor:
     return cache[label_name]
 
 
+DENSIFY_LIMIT_BYTES = 64 << 30
+
+
 def _dense_block(vec: VectorColumn) -> torch.Tensor:
-    """All parts as one device row-major block (a copy only when there are several parts or host data)."""
-    for p in vec.parts:
-        if not isinstance(p, (DensePart, LazyDensePart)):
-            raise NotImplementedError("this operation needs a dense OPVector (sparse parts are handled by the fused "
-                                      "scans; set featureFeatureCorrLevel = Off for hashed / pivoted vectors)")
-    blocks = [p.data if p.data.is_cuda else p.data.cuda() for p in vec.parts]
-    return blocks[0] if len(blocks) == 1 else torch.cat(blocks, dim=1)
+    """All parts as one device row-major block: a view for a single dense part, else a copy in which sparse parts are
+    densified (what Spark's RowMatrix does for Statistics.corr)."""
+    from ..columnar import SparseRowsPart
+    parts = [p.materialize(None) if isinstance(p, (LazyPart, LazyOneHotPart)) else p for p in vec.parts]
+    if len(parts) == 1 and isinstance(parts[0], (DensePart, LazyDensePart)):
+        d = parts[0].data
+        return d if d.is_cuda else d.cuda()
+    n, w = vec.n, sum(p.width for p in parts)
+    if n * w * 8 > DENSIFY_LIMIT_BYTES:
+        raise ValueError(f"densifying a {n} x {w} vector needs {n * w * 8 >> 30} GiB: use featureFeatureCorrLevel = Off "
+                         "for wide hashed / pivoted vectors (the reference cannot exceed 65535 columns either)")
+    out = torch.zeros((n, w), dtype=torch.float64, device="cuda")
+    off = 0
+    for p in parts:
+        if isinstance(p, (DensePart, LazyDensePart)):
+            d = p.data
+            out[:, off:off + p.width] = d if d.is_cuda else d.cuda()
+        elif isinstance(p, OneHotPart):
+            idx = p.indices if p.indices.is_cuda else p.indices.cuda()
+            L.call("tmog_onehot_densify_dev", idx.data_ptr(), idx.stride(0), n, idx.shape[1], out.data_ptr(), w, off,
+                   R.stream())
+        elif isinstance(p, SparseRowsPart):
+            L.call("tmog_sparse_rows_densify_dev", p.row_start.data_ptr(), p.row_nnz.data_ptr(), p.indices.data_ptr(),
+                   p.values.data_ptr(), n, out.data_ptr(), w, off, R.stream())
+        else:
+            raise NotImplementedError(f"cannot densify a {type(p).__name__}")
+        off += p.width
+    return out
 
 
 def vector_stats(batch: ColumnarBatch, vec: VectorColumn, label_name: str) -> VectorStats:
