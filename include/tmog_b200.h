@@ -156,6 +156,23 @@ int tmog_dedupe_strings(const uint8_t* data, const int64_t* offsets, int64_t cou
 int tmog_pivot_topk(const uint8_t* data, const int64_t* offsets, const int64_t* counts, int64_t count, int top_k,
                     int64_t min_support, int32_t* out_ids, int* out_n);
 
+/* The driver-side finish of ONE pivoted column in one call (thread-safe; run the columns in parallel): cleans the
+ * dictionary (tmog_clean_strings), merges raw codes that clean alike (tmog_dedupe_strings), picks the vocabulary
+ * (tmog_pivot_topk) and sums the per-label-class counts of every emitted column.
+ *   raw_counts [(ncodes + 1) * nclasses]   this column's table from tmog_pivot_count_dev (row 0 = null), as int64
+ *   n_top, top_data / top_offsets [top_k+1] the vocabulary strings in order (Arrow layout)
+ *   code_to_out [ncodes]                    emitted-column index of every raw code: top position, or n_top = OTHER
+ *   out_class_counts [(top_k + 2) * nclasses] rows 0..n_top-1 = top values, n_top = OTHER, n_top + 1 = null */
+int tmog_pivot_column_finish(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes, int clean_text,
+                             const int64_t* raw_counts, int nclasses, int top_k, int64_t min_support, int* n_top,
+                             int32_t* code_to_out, int64_t* out_class_counts, uint8_t* top_data, int64_t top_capacity,
+                             int64_t* top_offsets);
+
+/* code_to_out for a dictionary other than the fitted one (transform of new data): position of each entry's cleaned
+ * value in the fitted vocabulary, or n_top (OTHER) -- OneHotModelFun.pivotFn :420-427. */
+int tmog_pivot_column_map(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes, int clean_text,
+                          const uint8_t* top_data, const int64_t* top_offsets, int n_top, int32_t* code_to_out);
+
 /* Replaces the value counting of OpOneHotVectorizer.fitFn (:95-97, the RDD.fold of per-row maps) and, in the same
  * read, the per-label column sums SanityChecker.categoricalTests needs for the pivoted columns
  * (C/stages/impl/preparators/SanityChecker.scala:265-272):  counts[count_offset_c + id * nclasses + class] += 1.

@@ -51,6 +51,8 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_clean_strings": [_p, _p, _i64, _p, _i64, _p],
     "tmog_dedupe_strings": [_p, _p, _i64, _p, _p],
     "tmog_pivot_topk": [_p, _p, _p, _i64, _int, _i64, _p, _p],
+    "tmog_pivot_column_finish": [_p, _p, _i64, _int, _p, _int, _int, _i64, _p, _p, _p, _p, _i64, _p],
+    "tmog_pivot_column_map": [_p, _p, _i64, _int, _p, _p, _int, _p],
     "tmog_pivot_count_dev": [_p, _i64, _i64, _int, _p, _int, _p, _p, _i64, _p, _p, _p],
     "tmog_binary_codes_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _i64, _p],
     "tmog_pivot_transform_dev": [_p, _i64, _i64, _int, _p, _p, _p, _i64, _i64, _p],

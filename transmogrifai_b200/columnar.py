@@ -118,6 +118,9 @@ def decode_strings(data: np.ndarray, offsets: np.ndarray) -> List[str]:
     return [b[offsets[i]:offsets[i + 1]].decode("utf-8") for i in range(len(offsets) - 1)]
 
 
+_DICT_ARRAYS: Dict[int, tuple] = {}     # id(dictionary list) -> (list, bytes, offsets)
+
+
 @dataclass
 class DictBlock:
     """Dictionary-encoded string columns (PickList / Text): codes [ncols, ld] int32 column-major (code < 0 = null,
@@ -136,6 +139,16 @@ class DictBlock:
     @property
     def ld(self) -> int:
         return self.codes.shape[1]
+
+    def dict_arrays(self, col: int) -> Tuple[np.ndarray, np.ndarray]:
+        """Column `col`'s dictionary in Arrow utf8 layout (bytes, int64 offsets) -- the form the columnar export
+        delivers; built once per dictionary object."""
+        d = self.dicts[col]
+        cache = _DICT_ARRAYS.get(id(d))
+        if cache is None or cache[0] is not d:
+            cache = (d,) + encode_strings(d)
+            _DICT_ARRAYS[id(d)] = cache
+        return cache[1], cache[2]
 
     def rows(self, idx: Sequence[int]) -> "DictBlock":
         idx = list(idx)

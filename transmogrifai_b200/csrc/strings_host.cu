@@ -151,3 +151,169 @@ extern "C" int tmog_pivot_topk(const uint8_t* data, const int64_t* offsets, cons
     *out_n = (int)k;
     return TMOG_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Whole driver-side finish of one pivoted column in one call (what OpOneHotVectorizer.fitFn does after its fold):
+// clean every dictionary entry, merge the raw codes whose cleaned values coincide, pick the top-K vocabulary, and
+// produce the per-label-class counts of every emitted column (top values, OTHER, null).  Thread-safe; callers run
+// the columns of a vectorizer in parallel.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+
+struct StrRef {
+    const char* p;
+    int64_t len;
+};
+
+inline uint64_t fnv64(const char* p, int64_t len) {
+    uint64_t h = 1469598103934665603ull;
+    for (int64_t i = 0; i < len; ++i) h = (h ^ (unsigned char)p[i]) * 1099511628211ull;
+    return h ^ (h >> 29);
+}
+
+// cleaned strings of a dictionary, stored back to back; returns false on non-ASCII input when cleaning
+bool clean_dictionary(const uint8_t* data, const int64_t* offsets, int64_t count, bool clean, std::string& pool,
+                      std::vector<int64_t>& pool_off, int64_t* bad_entry) {
+    pool.clear();
+    pool_off.assign(1, 0);
+    pool_off.reserve((size_t)count + 1);
+    std::string tmp;
+    for (int64_t i = 0; i < count; ++i) {
+        const int64_t len = offsets[i + 1] - offsets[i];
+        if (clean) {
+            if (!clean_ascii(data + offsets[i], len, tmp)) {
+                *bad_entry = i;
+                return false;
+            }
+            pool.append(tmp);
+        } else {
+            pool.append((const char*)data + offsets[i], (size_t)len);
+        }
+        pool_off.push_back((int64_t)pool.size());
+    }
+    return true;
+}
+
+// ids[i] = dense id of cleaned string i (first-appearance order); open addressing over (hash, id)
+int64_t group_strings(const std::string& pool, const std::vector<int64_t>& off, std::vector<int32_t>& ids,
+                      std::vector<int32_t>& first) {
+    const int64_t count = (int64_t)off.size() - 1;
+    size_t cap = 16;
+    while (cap < (size_t)count * 2 + 2) cap <<= 1;
+    std::vector<int32_t> slot(cap, -1);
+    ids.resize((size_t)count);
+    first.clear();
+    for (int64_t i = 0; i < count; ++i) {
+        const char* p = pool.data() + off[i];
+        const int64_t len = off[i + 1] - off[i];
+        size_t s = (size_t)fnv64(p, len) & (cap - 1);
+        for (;;) {
+            const int32_t id = slot[s];
+            if (id < 0) {
+                slot[s] = (int32_t)first.size();
+                ids[i] = (int32_t)first.size();
+                first.push_back((int32_t)i);
+                break;
+            }
+            const int32_t j = first[id];
+            if (off[j + 1] - off[j] == len && memcmp(pool.data() + off[j], p, (size_t)len) == 0) {
+                ids[i] = id;
+                break;
+            }
+            s = (s + 1) & (cap - 1);
+        }
+    }
+    return (int64_t)first.size();
+}
+
+}  // namespace
+
+extern "C" int tmog_pivot_column_finish(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes,
+                                        int clean_text, const int64_t* raw_counts, int nclasses, int top_k,
+                                        int64_t min_support, int* n_top, int32_t* code_to_out,
+                                        int64_t* out_class_counts, uint8_t* top_data, int64_t top_capacity,
+                                        int64_t* top_offsets) {
+    TMOG_REQUIRE(ncodes >= 0 && dict_offsets && raw_counts && n_top && code_to_out && out_class_counts && top_offsets,
+                 "NULL argument");
+    TMOG_REQUIRE(top_k > 0 && nclasses >= 1, "requirement failed: topK must be positive");
+    std::string pool;
+    std::vector<int64_t> off;
+    int64_t bad = -1;
+    if (!clean_dictionary(dict_data, dict_offsets, ncodes, clean_text != 0, pool, off, &bad)) {
+        set_error("cleanString: dictionary entry %lld holds non-ASCII text; Java's Unicode case mapping is not restated "
+                  "on this path (set cleanText = false)", (long long)bad);
+        return TMOG_EINVAL;
+    }
+    std::vector<int32_t> ids, first;
+    const int64_t nd = group_strings(pool, off, ids, first);
+    // merged counts per cleaned value and class (raw_counts row 0 is the null bin, row 1 + code the raw code)
+    std::vector<int64_t> merged((size_t)nd * nclasses, 0), total((size_t)nd, 0);
+    for (int64_t i = 0; i < ncodes; ++i)
+        for (int k = 0; k < nclasses; ++k) {
+            const int64_t v = raw_counts[(i + 1) * nclasses + k];
+            merged[(size_t)ids[i] * nclasses + k] += v;
+            total[ids[i]] += v;
+        }
+    // top-K: count >= minSupport (and > 0), sort by (-count, java string order)
+    std::vector<int32_t> cand;
+    for (int64_t v = 0; v < nd; ++v)
+        if (total[v] >= min_support && total[v] > 0) cand.push_back((int32_t)v);
+    auto str_of = [&](int32_t v) {
+        const int32_t i = first[v];
+        return std::string(pool.data() + off[i], (size_t)(off[i + 1] - off[i]));
+    };
+    auto less = [&](int32_t a, int32_t b) {
+        if (total[a] != total[b]) return total[a] > total[b];
+        return java_compare(str_of(a), str_of(b)) < 0;
+    };
+    const size_t k = std::min<size_t>((size_t)top_k, cand.size());
+    std::partial_sort(cand.begin(), cand.begin() + k, cand.end(), less);
+    std::vector<int32_t> pos((size_t)nd, (int32_t)k);  // OTHER = k
+    int64_t w = 0;
+    top_offsets[0] = 0;
+    for (size_t t = 0; t < k; ++t) {
+        pos[cand[t]] = (int32_t)t;
+        const std::string sv = str_of(cand[t]);
+        if (w + (int64_t)sv.size() > top_capacity) {
+            set_error("top_data too small");
+            return TMOG_ENOMEM;
+        }
+        if (!sv.empty()) memcpy(top_data + w, sv.data(), sv.size());
+        w += (int64_t)sv.size();
+        top_offsets[t + 1] = w;
+    }
+    *n_top = (int)k;
+    for (int64_t i = 0; i < ncodes; ++i) code_to_out[i] = pos[ids[i]];
+    // emitted columns: k top values, OTHER, null
+    for (size_t i = 0; i < (k + 2) * (size_t)nclasses; ++i) out_class_counts[i] = 0;
+    for (int64_t v = 0; v < nd; ++v)
+        for (int c = 0; c < nclasses; ++c) out_class_counts[(size_t)pos[v] * nclasses + c] += merged[(size_t)v * nclasses + c];
+    for (int c = 0; c < nclasses; ++c) out_class_counts[(k + 1) * nclasses + c] = raw_counts[c];
+    return TMOG_OK;
+}
+
+// code_to_out[i] = position of dictionary entry i's cleaned value in the fitted vocabulary `top` (n_top strings), or
+// n_top (OTHER): the table OneHotModelFun.pivotFn needs for a batch whose dictionary differs from the fitted one.
+extern "C" int tmog_pivot_column_map(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes,
+                                     int clean_text, const uint8_t* top_data, const int64_t* top_offsets, int n_top,
+                                     int32_t* code_to_out) {
+    TMOG_REQUIRE(ncodes >= 0 && dict_offsets && top_offsets && code_to_out && n_top >= 0, "NULL argument");
+    std::unordered_map<std::string, int32_t> top;
+    for (int t = 0; t < n_top; ++t)
+        top.emplace(std::string((const char*)top_data + top_offsets[t], (size_t)(top_offsets[t + 1] - top_offsets[t])), t);
+    std::string tmp;
+    for (int64_t i = 0; i < ncodes; ++i) {
+        const int64_t len = dict_offsets[i + 1] - dict_offsets[i];
+        if (clean_text) {
+            if (!clean_ascii(dict_data + dict_offsets[i], len, tmp)) {
+                set_error("cleanString: dictionary entry %lld holds non-ASCII text", (long long)i);
+                return TMOG_EINVAL;
+            }
+        } else {
+            tmp.assign((const char*)dict_data + dict_offsets[i], (size_t)len);
+        }
+        auto it = top.find(tmp);
+        code_to_out[i] = it == top.end() ? n_top : it->second;
+    }
+    return TMOG_OK;
+}

@@ -9,6 +9,7 @@ Per-row work is integer only (dictionary codes); strings are touched once per di
 """
 from __future__ import annotations
 
+import ctypes as C
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -55,28 +56,6 @@ def top_k(values: Sequence[str], counts: np.ndarray, k: int, min_support: int) -
     L.call("tmog_pivot_topk", data.ctypes.data, offs.ctypes.data, cnt.ctypes.data, len(values), int(k),
            int(min_support), out.ctypes.data, n_out.ctypes.data)
     return out[:int(n_out[0])].tolist()
-
-
-class _Plan:
-    """Device tables of one fit / transform call over a DictBlock."""
-
-    def __init__(self, block: DictBlock, clean: bool):
-        self.ids: List[np.ndarray] = []
-        self.values: List[List[str]] = []
-        for d in block.dicts:
-            ids, distinct = clean_and_group(d, clean)
-            self.ids.append(ids)
-            self.values.append(distinct)
-        ncols = len(block.names)
-        self.ncodes = np.array([len(d) for d in block.dicts], dtype=np.int64)
-        self.nids = self.ncodes + 1                                                    # raw codes + the null id 0
-        self.slot_offset = np.concatenate([[0], np.cumsum(self.ncodes)[:-1]]).astype(np.int64) if ncols else \
-            np.zeros(0, dtype=np.int64)
-
-    def desc(self, nclasses: int) -> np.ndarray:
-        count_offset = np.concatenate([[0], np.cumsum(self.nids * nclasses)[:-1]]).astype(np.int64)
-        self.count_offset = count_offset
-        return np.ascontiguousarray(np.stack([self.nids, self.slot_offset, count_offset, self.ncodes], axis=1))
 
 
 class OpTextPivotVectorizer(OpEstimator):
@@ -137,7 +116,6 @@ class OpTextPivotVectorizer(OpEstimator):
         block = batch.strings(names)
         dev = block if block.is_cuda else block.to("cuda")
         n, ncols = batch.n, len(names)
-        plan = _Plan(block, self.cleanText)
         label_name = batch.response
         classes = counts_per_class = ids = None
         if label_name:
@@ -145,45 +123,69 @@ class OpTextPivotVectorizer(OpEstimator):
             y = y if y.is_cuda else y.cuda()
             classes, counts_per_class, ids = label_info_dev(batch, y, label_name)
         ncls = len(classes) if classes is not None else 1
-        desc = plan.desc(ncls)
-        total_bins = int((plan.nids * ncls).sum())
+        ncodes = np.array([len(d) for d in block.dicts], dtype=np.int64)
+        nids = ncodes + 1                                   # raw codes + the null id 0
+        zeros = np.zeros(ncols, dtype=np.int64)
+        count_offset = np.concatenate([[0], np.cumsum(nids * ncls)[:-1]]).astype(np.int64) if ncols else zeros
+        desc = np.ascontiguousarray(np.stack([nids, zeros, count_offset, ncodes], axis=1)) if ncols else \
+            np.zeros((0, 4), dtype=np.int64)
+        total_bins = int((nids * ncls).sum())
         d_desc = torch.from_numpy(desc).cuda()
         d_counts = torch.zeros(max(total_bins, 1), dtype=torch.int32, device="cuda")     # uint32 bins
         d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
         L.call("tmog_pivot_count_dev", dev.codes.data_ptr(), dev.ld, n, ncols,
                ids.data_ptr() if classes is not None else None, ncls, d_desc.data_ptr(), None,
-               int(plan.nids.max()) if ncols else 1, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
+               int(nids.max()) if ncols else 1, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
         counts = D.allreduce_sum(d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF)
         if int(d_bad.item()):
             raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
         n_global = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
-        tops: List[List[str]] = []
-        col_stats = []
-        for c in range(ncols):
-            k = int(plan.nids[c])
-            raw = counts[plan.count_offset[c]:plan.count_offset[c] + k * ncls].reshape(k, ncls)
-            # bins are per RAW code (row 0 = null): merge the codes whose cleaned values coincide
-            tab = np.zeros((len(plan.values[c]), ncls), dtype=np.int64)
-            if len(plan.ids[c]):
-                np.add.at(tab, plan.ids[c], raw[1:])
-            totals = tab.sum(axis=1)
-            chosen = top_k(plan.values[c], totals, self.topK, self.minSupport)
-            tops.append([plan.values[c][i] for i in chosen])
-            rest = np.ones(len(tab), dtype=bool)
-            rest[chosen] = False
-            rows = [tab[i] for i in chosen] + [tab[rest].sum(axis=0)]
-            if self.trackNulls:
-                rows.append(raw[0])
-            col_stats.append(np.stack(rows).astype(np.float64))            # [emitted columns, classes]
+
+        def finish(c: int):
+            data, offs = block.dict_arrays(c)
+            raw = np.ascontiguousarray(counts[count_offset[c]:count_offset[c] + nids[c] * ncls])
+            k = self.topK
+            n_top = C.c_int(0)
+            code_to_out = np.zeros(max(int(ncodes[c]), 1), dtype=np.int32)
+            per_class = np.zeros((k + 2) * ncls, dtype=np.int64)
+            top_data = np.zeros(max(len(data), 1), dtype=np.uint8)
+            top_offs = np.zeros(k + 1, dtype=np.int64)
+            L.call("tmog_pivot_column_finish", data.ctypes.data, offs.ctypes.data, int(ncodes[c]),
+                   int(self.cleanText), raw.ctypes.data, ncls, k, self.minSupport, C.byref(n_top),
+                   code_to_out.ctypes.data, per_class.ctypes.data, top_data.ctypes.data, len(top_data),
+                   top_offs.ctypes.data)
+            t = n_top.value
+            top = decode_strings(top_data, top_offs[:t + 1])
+            rows = per_class.reshape(k + 2, ncls)[:t + 2]
+            if not self.trackNulls:
+                rows = rows[:t + 1]
+            return top, code_to_out[:int(ncodes[c])], rows.astype(np.float64)
+
+        results = list(_pool().map(finish, range(ncols))) if ncols > 1 else [finish(c) for c in range(ncols)]
+        tops = [r[0] for r in results]
         self._metadata = self._metadata_for(tops)
         stats = None
         if label_name and classes is not None:
-            stats = _stats_from_class_counts(np.concatenate(col_stats, axis=0), classes, counts_per_class, n_global,
-                                             label_name)
+            stats = _stats_from_class_counts(np.concatenate([r[2] for r in results], axis=0), classes,
+                                             counts_per_class, n_global, label_name)
         model = OpTextPivotVectorizerModel(self, tops, self.cleanText, self.trackNulls)
         model._fit_stats = stats
         model._fit_key = (block.codes.data_ptr(), n)
+        model._fit_tables = {id(block.dicts[c]): (block.dicts[c], results[c][1]) for c in range(ncols)}
         return model
+
+
+_POOL = None
+
+
+def _pool():
+    """Threads for the per-column driver-side finish (the C functions release the GIL)."""
+    global _POOL
+    if _POOL is None:
+        import os
+        from concurrent.futures import ThreadPoolExecutor
+        _POOL = ThreadPoolExecutor(max_workers=min(32, os.cpu_count() or 4))
+    return _POOL
 
 
 def _stats_from_class_counts(per_class: np.ndarray, classes: np.ndarray, class_counts: np.ndarray, n: int,
@@ -227,6 +229,19 @@ class OpTextPivotVectorizerModel(OpModel):
         return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part],
                             self._fit_stats if same else None)
 
+    def _code_to_out(self, block: DictBlock, c: int) -> np.ndarray:
+        """Emitted-column index (top position or OTHER) of every code of column c's dictionary."""
+        d = block.dicts[c]
+        hit = getattr(self, "_fit_tables", {}).get(id(d))
+        if hit is not None and hit[0] is d:              # the dictionary the model was fitted on
+            return hit[1]
+        data, offs = block.dict_arrays(c)
+        top_data, top_offs = encode_strings(self.topValues[c])
+        out = np.zeros(max(len(d), 1), dtype=np.int32)
+        L.call("tmog_pivot_column_map", data.ctypes.data, offs.ctypes.data, len(d), int(self.shouldCleanText),
+               top_data.ctypes.data, top_offs.ctypes.data, len(self.topValues[c]), out.ctypes.data)
+        return out[:len(d)]
+
     def _materialize(self, block: DictBlock, keep: Optional[List[int]]) -> OneHotPart:
         dev = block if block.is_cuda else block.to("cuda")
         n, ncols = block.n, len(block.names)
@@ -238,21 +253,21 @@ class OpTextPivotVectorizerModel(OpModel):
             newpos = np.full(width, -1, dtype=np.int32)
             newpos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
             out_width = len(keep)
-        plan = _Plan(block, self.shouldCleanText)
-        tables = []
-        off = 0
-        for c in range(ncols):
-            top = self.topValues[c]
-            index_of = {v: i for i, v in enumerate(top)}
-            local = np.array([index_of.get(v, len(top)) for v in plan.values[c]], dtype=np.int64)   # OTHER = len(top)
-            per_code = local[plan.ids[c]] if len(plan.ids[c]) else np.zeros(0, dtype=np.int64)
-            tab = np.empty(len(per_code) + 1, dtype=np.int32)
-            tab[:-1] = newpos[off + per_code]
-            tab[-1] = newpos[off + len(top) + 1] if self.shouldTrackNulls else -1   # null -> indicator (or nothing)
-            tables.append(tab)
-            off += widths[c]
+        offs = np.concatenate([[0], np.cumsum(widths)[:-1]]).astype(np.int64) if ncols else np.zeros(0, np.int64)
+
+        def table(c: int) -> np.ndarray:
+            local = self._code_to_out(block, c)
+            tab = np.empty(len(local) + 1, dtype=np.int32)
+            tab[:-1] = newpos[offs[c] + local]
+            top_n = len(self.topValues[c])
+            tab[-1] = newpos[offs[c] + top_n + 1] if self.shouldTrackNulls else -1   # null -> indicator (or nothing)
+            return tab
+
+        tables = list(_pool().map(table, range(ncols))) if ncols > 1 else [table(c) for c in range(ncols)]
         pos = np.concatenate(tables) if tables else np.zeros(1, dtype=np.int32)
-        desc = plan.desc(1)
+        ncodes = np.array([len(d) for d in block.dicts], dtype=np.int64)
+        slot_off = np.concatenate([[0], np.cumsum(ncodes)[:-1]]).astype(np.int64) if ncols else ncodes
+        desc = np.ascontiguousarray(np.stack([ncodes + 1, slot_off, np.zeros_like(ncodes), ncodes], axis=1))
         d_desc = torch.from_numpy(desc).cuda()
         d_pos = torch.from_numpy(pos).cuda()
         out = torch.empty((n, max(ncols, 1)), dtype=torch.int32, device="cuda")   # dense rows: no unwritten padding
