@@ -1,7 +1,10 @@
 #!/usr/bin/env python
 """bench.py -- rows/sec of transmogrify() + sanityCheck() fit + transform on synthetic data (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--rows R] [--impl tmog|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4|c5] [--rows R] [--impl tmog|reference]
+
+The default workload is config 2 of BASELINE.json (the configuration it names for one B200); c3 / c4 / c5 run the
+PickList, Text and mixed configurations (c4 and c5 scaled to the rows that fit, see benchdata.py).
 
 One process per GPU (torchrun for N > 1); rows are sharded across ranks (weak scaling: R rows per GPU) and the only
 exchange is the NCCL all-reduce of the per-column partial sums / count tables.  A "step" is one full pass of the hot
@@ -23,16 +26,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-WORKLOAD = ("C2: synthetic {rows} rows x {ncols} Real columns (5% nulls) per GPU: RealVectorizer mean-fill + null "
-            "indicators fused with SanityChecker (column moments, label correlations, Cramer's V of the null "
-            "indicators, removeBadFeatures decision, featureFeatureCorrLevel=Off), then the transform writing the "
-            "kept columns")
-NCOLS = 100
 SEED = 20260001
-# algorithmic bytes per row: fit = one read of values + bitmaps + label; transform = the same read
-# without the label + 16 bytes per (row, input column) written
-FIT_BYTES_PER_ROW = NCOLS * 8 + NCOLS / 8 + 8
-TRANSFORM_BYTES_PER_ROW = NCOLS * 8 + NCOLS / 8 + NCOLS * 16
+METRIC = "rows/sec transmogrify+sanityCheck fit+transform"
 
 
 def peaks():
@@ -78,118 +73,146 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def make_device_batch(rows: int, seed: int):
-    """Config-2 data generated on the device (torch RNG, seeded): N(j, 1 + j/10) columns, 5 % nulls, Bernoulli(0.3)
-    label, 5 label-shifted columns, one constant column, one duplicated column."""
-    import torch
-    from transmogrifai_b200 import features as F
-    from transmogrifai_b200.columnar import ColumnarBatch, NumericBlock
-    g = torch.Generator(device="cuda").manual_seed(seed)
-    ld = (rows + 2047) // 2048 * 2048
-    nw = ld // 64
-    y = (torch.rand(ld, device="cuda", generator=g) < 0.3).double()
-    vals = torch.empty((NCOLS, ld), dtype=torch.float64, device="cuda")
-    valid = torch.empty((NCOLS, nw), dtype=torch.int64, device="cuda")
-    w = (torch.ones(64, dtype=torch.int64, device="cuda") << torch.arange(64, device="cuda")).view(1, 64)
-    for j in range(NCOLS):
-        vals[j].normal_(float(j), 1.0 + j / 10.0, generator=g)
-        ok = (torch.rand(ld, device="cuda", generator=g) >= 0.05).view(nw, 64).long()
-        valid[j] = (ok * w).sum(dim=1)
-    for j in range(0, 50, 10):
-        vals[j] += 0.5 * y
-    vals[7] = 3.25
-    vals[12] = vals[11]
-    valid[12] = valid[11]
-    names = [f"c{j:03d}" for j in range(NCOLS)]
-    blocks = [NumericBlock(names, F.REAL, vals, valid, rows),
-              NumericBlock(["label"], F.REALNN, y.view(1, ld), None, rows)]
-    feats = [F.FeatureBuilder.Real(nm).asPredictor() for nm in names]
-    label = F.FeatureBuilder.RealNN("label").asResponse()
-    return ColumnarBatch(rows, blocks, {}, response="label"), feats, label
 
 
-def host_copy(batch):
-    import torch
-    from transmogrifai_b200.columnar import ColumnarBatch, NumericBlock
-    blocks = []
-    for b in batch.blocks:
-        v = torch.empty(b.values.shape, dtype=b.values.dtype, pin_memory=True)
-        v.copy_(b.values)
-        m = None
-        if b.valid is not None:
-            m = torch.empty(b.valid.shape, dtype=b.valid.dtype, pin_memory=True)
-            m.copy_(b.valid)
-        blocks.append(NumericBlock(b.names, b.type_name, v, m, b.n))
-    return ColumnarBatch(batch.n, blocks, {}, batch.response)
+def build_plan(feats, label, info):
+    from transmogrifai_b200.dsl import TransmogrifierDefaults, transmogrify
 
+    class Defaults(TransmogrifierDefaults):
+        DefaultNumOfFeatures = info["num_features"]
 
-def build_plan(feats, label):
-    from transmogrifai_b200.dsl import transmogrify
-    vec = transmogrify(feats)
+    vec = transmogrify(feats, defaults=Defaults)
     return label.sanityCheck(vec, removeBadFeatures=True, checkSample=1.0, sampleLowerLimit=0,
                              sampleUpperLimit=2 ** 31 - 1, featureFeatureCorrLevel="Off")
 
 
 def run_step(batch, checked):
+    """One step: fit every stage (fused vectorizer + SanityChecker scans, label classes, decision) and materialise
+    the kept columns of the output vector.  Nothing is reused from a previous step."""
     from transmogrifai_b200.dsl import fit_and_transform
-    batch.__dict__.pop("_label_cache", None)   # label classes are part of the step: never reuse a previous step's
-    batch.__dict__.pop("_label_dev", None)
+    for k in ("_label_cache", "_label_dev", "_dict_cache"):
+        batch.__dict__.pop(k, None)
     out, fitted = fit_and_transform(batch, checked)
     vec = out.vectors[checked.name]
-    for p in vec.parts:           # the transform is lazy until somebody reads the vector: read it
-        _ = p.data
-    return vec, fitted
+    parts = [p.materialize(None) if hasattr(p, "materialize") else p for p in vec.parts]   # lazy until read: read it
+    for p in parts:
+        if hasattr(p, "data") and not hasattr(p, "materialize"):
+            _ = p.data
+    return vec, fitted, parts
 
 
-def kernel_times(batch, reps: int = 5):
-    """Average device time of the two dominant kernels at this batch size (CUDA events on the launch stream)."""
+def output_bytes(parts) -> int:
+    tot = 0
+    for p in parts:
+        for name in ("data", "indices", "values", "row_start", "row_nnz"):
+            t = getattr(p, name, None)
+            if t is not None and hasattr(t, "numel"):
+                tot += t.numel() * t.element_size()
+    return tot
+
+
+def _time(f, reps):
+    import torch
+    for _ in range(2):
+        f()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        f()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def kernel_times(workload, batch, fitted, info, reps: int = 5):
+    """Device time of the dominant kernels of the step on this very batch (CUDA events on the launch stream), with the
+    algorithmic bytes each one moves per row.  -> list of dicts, the slowest first."""
     import ctypes as C
     import torch
     from transmogrifai_b200 import _lib as L
     from transmogrifai_b200 import runtime as R
-    blk = batch.numeric(batch.blocks[0].names)
-    y = batch.label()
-    n, ncols = batch.n, len(blk.names)
-    nb = C.c_size_t()
-    L.call("tmog_real_fit_scratch_bytes", ncols, C.byref(nb))
-    scratch = R.scratch("real_fit", nb.value)
-    shifts = torch.zeros(ncols + 1, dtype=torch.float64, device="cuda")
-    part = torch.zeros((ncols + 1) * 8, dtype=torch.float64, device="cuda")
-    fills = torch.zeros(ncols, dtype=torch.float64, device="cuda")
-    out = torch.empty((n, 2 * ncols), dtype=torch.float64, device="cuda")
+    from transmogrifai_b200.columnar import DictBlock, NumericBlock, TextBlock
     st = R.stream()
-    L.call("tmog_real_pilot_shift_dev", blk.values.data_ptr(), blk.ld, blk.valid.data_ptr(), blk.ldv, y.data_ptr(), n,
-           ncols, shifts.data_ptr(), st)
+    n = batch.n
+    out = []
+    for blk in batch.blocks:
+        if isinstance(blk, NumericBlock) and blk.type_name == "Real":
+            ncols = len(blk.names)
+            y = batch.label()
+            nb = C.c_size_t()
+            L.call("tmog_real_fit_scratch_bytes", ncols, C.byref(nb))
+            scratch = R.scratch("real_fit", nb.value)
+            shifts = torch.zeros(ncols + 1, dtype=torch.float64, device="cuda")
+            part = torch.zeros((ncols + 1) * 8, dtype=torch.float64, device="cuda")
+            fills = torch.zeros(ncols, dtype=torch.float64, device="cuda")
+            keep_local = [i for i in range(2 * ncols) if i != 14]          # what SanityChecker keeps of this block
+            bits = np.zeros((2 * ncols + 63) // 64 * 64, dtype=np.uint8)
+            bits[keep_local] = 1
+            mask = torch.from_numpy(np.packbits(bits, bitorder="little").view("<i8").copy()).cuda()
+            dst = torch.empty((n, len(keep_local)), dtype=torch.float64, device="cuda")
+            L.call("tmog_real_pilot_shift_dev", blk.values.data_ptr(), blk.ld, blk.valid.data_ptr(), blk.ldv,
+                   y.data_ptr(), n, ncols, shifts.data_ptr(), st)
+            t_fit = _time(lambda: L.call("tmog_real_fit_partials_dev", blk.values.data_ptr(), blk.ld,
+                                         blk.valid.data_ptr(), blk.ldv, y.data_ptr(), n, ncols, shifts.data_ptr(),
+                                         scratch.data_ptr(), scratch.numel(), part.data_ptr(), st), reps)
+            t_tr = _time(lambda: L.call("tmog_real_transform_select_dev", blk.values.data_ptr(), blk.ld,
+                                        blk.valid.data_ptr(), blk.ldv, n, ncols, fills.data_ptr(), 1, mask.data_ptr(),
+                                        len(keep_local), dst.data_ptr(), len(keep_local), 0, st), reps)
+            out.append({"kernel": "vec_transform_select_kernel<double, true>", "ms": t_tr,
+                        "bytes_per_row": ncols * 8 + ncols / 8 + len(keep_local) * 8})
+            out.append({"kernel": "real_fit_kernel", "ms": t_fit, "bytes_per_row": ncols * 8 + ncols / 8 + 8})
+            del dst
+        elif isinstance(blk, DictBlock):
+            ncols = len(blk.names)
+            ncodes = np.array([len(d) for d in blk.dicts], dtype=np.int64)
+            nids, ncls = ncodes + 1, 2
+            zeros = np.zeros(ncols, dtype=np.int64)
+            coff = np.concatenate([[0], np.cumsum(nids * ncls)[:-1]]).astype(np.int64)
+            soff = np.concatenate([[0], np.cumsum(ncodes)[:-1]]).astype(np.int64)
+            desc = torch.from_numpy(np.ascontiguousarray(np.stack([nids, soff, coff, ncodes], axis=1))).cuda()
+            counts = torch.zeros(int((nids * ncls).sum()), dtype=torch.int32, device="cuda")
+            bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+            ids = (batch.label()[:max(n, 4)] > 0).to(torch.uint8)
+            pos = torch.zeros(int(ncodes.sum()) + ncols, dtype=torch.int32, device="cuda")
+            dst = torch.empty((n, ncols), dtype=torch.int32, device="cuda")
+            t_cnt = _time(lambda: L.call("tmog_pivot_count_dev", blk.codes.data_ptr(), blk.ld, n, ncols, ids.data_ptr(),
+                                         ncls, desc.data_ptr(), None, int(nids.max()), counts.data_ptr(),
+                                         bad.data_ptr(), st), reps)
+            t_tr = _time(lambda: L.call("tmog_pivot_transform_dev", blk.codes.data_ptr(), blk.ld, n, ncols,
+                                        desc.data_ptr(), pos.data_ptr(), dst.data_ptr(), ncols, 0, st), reps)
+            out.append({"kernel": "pivot_transform_kernel", "ms": t_tr, "bytes_per_row": ncols * 8})
+            out.append({"kernel": "pivot_count_kernel", "ms": t_cnt, "bytes_per_row": ncols * 4 + 1})
+            del dst
+        elif isinstance(blk, TextBlock):
+            model = [m for m in fitted if hasattr(m, "vectorizationMethods")][0]
+            sub, d_prefix, d_plen, params = model._hash_args(blk)
+            from transmogrifai_b200.stages.smart_text import _col_desc
+            lay = model.layout
+            k = len(lay.hash_idx)
+            params[7] = 2
+            w = lay.hash_width + k
+            cs = torch.zeros(w * 2, dtype=torch.int32, device="cuda")
+            nz = torch.zeros(w, dtype=torch.int32, device="cuda")
+            ex = torch.zeros(w, dtype=torch.int64, device="cuda")
+            ax = torch.zeros(3 * w, dtype=torch.int32, device="cuda")
+            fl = torch.zeros(4, dtype=torch.int32, device="cuda")
+            ids = (batch.label()[:max(n, 4)] > 0).to(torch.uint8)
+            desc = _col_desc(sub)
+            t_h = _time(lambda: L.call("tmog_text_hash_stats_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(),
+                                       d_plen.data_ptr(), params.ctypes.data, ids.data_ptr(), cs.data_ptr(),
+                                       nz.data_ptr(), ex.data_ptr(), ax.data_ptr(), fl.data_ptr(), st), max(reps // 2, 1))
+            bpr = sum(int(sub.offsets[j][-1].item()) for j in range(k)) / max(n, 1)
+            out.append({"kernel": "text_hash_kernel<false>", "ms": t_h, "bytes_per_row": bpr + k * 8 + k / 8 + 1,
+                        "note": "instruction-bound (tokenise + murmur3 + per-row sort), reported against HBM anyway"})
+    return sorted(out, key=lambda d: -d["ms"])
 
-    def fit():
-        L.call("tmog_real_fit_partials_dev", blk.values.data_ptr(), blk.ld, blk.valid.data_ptr(), blk.ldv,
-               y.data_ptr(), n, ncols, shifts.data_ptr(), scratch.data_ptr(), scratch.numel(), part.data_ptr(), st)
 
-    def tr():
-        L.call("tmog_real_transform_dev", blk.values.data_ptr(), blk.ld, blk.valid.data_ptr(), blk.ldv, n, ncols,
-               fills.data_ptr(), 1, out.data_ptr(), 2 * ncols, 0, st)
-
-    res = {}
-    for name, f in (("fit", fit), ("transform", tr)):
-        for _ in range(2):
-            f()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        e0.record()
-        for _ in range(reps):
-            f()
-        e1.record()
-        torch.cuda.synchronize()
-        res[name] = e0.elapsed_time(e1) / reps
-    del out
-    return res
-
-
-def cpu_reference(rows: int, threads: int):
-    """The reference's CPU job sequence for this workload (oracle/c port, OpenMP) on `rows` rows: returns seconds."""
+def cpu_reference_c2(rows: int, threads: int):
+    """The reference's CPU job sequence for config 2 (oracle/c: C + OpenMP) on `rows` rows -> seconds."""
     from oracle import c_port as CP
     from tests.util_data import make_real_config, pack_validity
-    x, valid, y = make_real_config(rows, NCOLS, seed=SEED)
+    x, valid, y = make_real_config(rows, 100, seed=SEED)
     vw = pack_validity(valid)
     x = np.ascontiguousarray(x)
     CP.real_pipeline(x[:, :2048].copy(), pack_validity(valid[:, :2048]), y[:2048].copy(), threads)   # page in
@@ -199,41 +222,120 @@ def cpu_reference(rows: int, threads: int):
     return time.perf_counter() - t0
 
 
+def cpu_reference_generic(workload: str, rows: int):
+    """The oracle (pure Python / numpy restatement, one core) on a small sample of the same synthetic workload:
+    vectorizer fit + transform per type group, combine, SanityChecker statistics.  -> seconds."""
+    import torch
+    import scipy.sparse as sp
+    import benchdata
+    from oracle import vectorizers as V
+    from transmogrifai_b200.columnar import DictBlock, NumericBlock, TextBlock
+    batch, feats, label, info = benchdata.make_workload(workload, rows, SEED)
+    y = batch.label()[:rows].cpu().numpy()
+    cols = {}
+    for b in batch.blocks:
+        if isinstance(b, NumericBlock):
+            v = b.values[:, :rows].cpu().numpy()
+            ok = np.ones_like(v, dtype=bool) if b.valid is None else np.unpackbits(
+                b.valid.cpu().numpy().view(np.uint8), axis=1, bitorder="little")[:, :rows].astype(bool)
+            for j, nm in enumerate(b.names):
+                cols[nm] = [(bool(x) if b.type_name == "Binary" else float(x)) if o else None
+                            for x, o in zip(v[j], ok[j])]
+        elif isinstance(b, DictBlock):
+            c = b.codes[:, :rows].cpu().numpy()
+            for j, nm in enumerate(b.names):
+                d = b.dicts[j]
+                cols[nm] = [None if k < 0 else d[k] for k in c[j]]
+        elif isinstance(b, TextBlock):
+            for j, nm in enumerate(b.names):
+                cols[nm] = [b.cell(j, r) for r in range(rows)]
+    del batch
+    torch.cuda.empty_cache()
+    by_type = {}
+    for f in feats:
+        by_type.setdefault(f.type_name, []).append(f.name)
+    t0 = time.perf_counter()
+    mats = []
+    for tp in sorted(by_type):
+        names = by_type[tp]
+        data = [cols[nm] for nm in names]
+        if tp == "Binary":
+            mats.append(sp.csr_matrix(V.binary_vectorizer_transform(data)))
+        elif tp == "Real":
+            mats.append(sp.csr_matrix(V.real_vectorizer_transform(data, V.real_vectorizer_fit(data), True)))
+        elif tp == "PickList":
+            tops = V.pivot_fit(data, 20, 10, True)
+            mats.append(V.pivot_transform(data, tops, True, True))
+        elif tp == "Text":
+            methods, tops = V.smart_text_fit(data, max_cardinality=30, top_k=20, min_support=10)
+            mats.append(V.smart_text_transform(data, names, methods, tops, num_features=info["num_features"]))
+    x = sp.hstack(mats, format="csr")
+    # SanityChecker statistics, sparse-aware (the reference's Off route loops densely over every column of every
+    # row, U/stats/OpStatistics.scala:86-90; this is the cheaper equivalent)
+    n = x.shape[0]
+    s1 = np.asarray(x.sum(axis=0)).ravel()
+    s2 = np.asarray(x.multiply(x).sum(axis=0)).ravel()
+    sxy = np.asarray(x.T @ y).ravel()
+    mean = s1 / n
+    var = (s2 - n * mean * mean) / (n - 1)
+    cov = sxy - mean * y.sum()
+    _ = cov / np.sqrt(np.maximum(var, 1e-300) * y.var(ddof=1)) / (n - 1)
+    _ = [np.asarray(x[y == k].sum(axis=0)) for k in (0.0, 1.0)]
+    return time.perf_counter() - t0
+
+
+def cpu_baseline(workload: str, cores: int, cpu_rows: int):
+    if workload == "c2":
+        secs = cpu_reference_c2(cpu_rows, cores)
+        return secs, cpu_rows, cores, (f"{cpu_rows} rows x 100 Real columns of the same workload; the reference's job "
+                                       f"sequence (fit, transform, colStats, label correlations, per-label sums) as "
+                                       f"oracle/c (C + OpenMP) on {cores} threads")
+    rows = {"c3": 20_000, "c4": 1_000, "c5": 1_000}[workload]
+    secs = cpu_reference_generic(workload, rows)
+    return secs, rows, 1, (f"{rows} rows of the same workload through the oracle (pure Python / numpy restatement of "
+                           "the reference, one core; no compiled port of the string paths yet)")
+
+
 def main():
+    import benchdata
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--rows", type=int, default=10_000_000, help="rows per GPU")
+    ap.add_argument("--workload", default="c2", choices=list(benchdata.WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="rows per GPU (0 = the workload's default)")
     ap.add_argument("--impl", default="tmog", choices=["tmog", "reference"])
-    ap.add_argument("--cpu-rows", type=int, default=1_000_000, help="rows of the bounded CPU-baseline sample")
+    ap.add_argument("--cpu-rows", type=int, default=1_000_000, help="rows of the bounded CPU-baseline sample (c2)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     steps, warmup = max(args.steps, 1), max(args.warmup, 3 if args.impl == "tmog" else 1)
     cores = os.cpu_count() or 1
+    wl = args.workload
+    rows = args.rows or benchdata.DEFAULT_ROWS[wl]
 
     if args.impl == "reference":
         if rank != 0:
             return
-        secs = []
+        import torch
+        if wl != "c2":
+            torch.cuda.set_device(0)      # the sample of the string workloads is drawn by the device generator
+        secs, used = [], 1
         for i in range(warmup + steps):
-            t = cpu_reference(args.cpu_rows, cores)
+            t, srows, used, sample = cpu_baseline(wl, cores, args.cpu_rows)
             if i >= warmup:
                 secs.append(t)
-        v = args.cpu_rows * len(secs) / sum(secs)
-        sample = (f"{args.cpu_rows} rows x {NCOLS} Real columns of the same workload per step; the reference's job "
-                  f"sequence (fit, transform, colStats, label correlations, per-label sums) as oracle/c "
-                  f"(C + OpenMP) on {cores} threads; the JVM reference cannot run on this box")
+        v = srows * len(secs) / sum(secs)
         print(json.dumps({
-            "impl": "reference", "metric": "rows/sec transmogrify+sanityCheck fit+transform", "value": v,
-            "unit": "rows/s", "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
-            "ms_per_step": 1e3 * sum(secs) / len(secs), "higher_is_better": True, "scaling": "weak",
+            "impl": "reference", "metric": METRIC, "value": v, "unit": "rows/s", "n_gpus": args.gpus, "steps": steps,
+            "warmup": warmup, "ms_per_step": 1e3 * sum(secs) / len(secs), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD.format(rows=args.cpu_rows, ncols=NCOLS)},
-            "cpu_baseline": {"value": v, "unit": "rows/s", "cores": cores, "kind": "port", "sample": sample},
+            "config": {"workload": f"{wl}: bounded CPU sample of the tmog arm's workload", "rows_per_step": srows},
+            "cpu_baseline": {"value": v, "unit": "rows/s", "cores": used, "kind": "port",
+                             "sample": sample + "; the JVM reference cannot run on this box (no JVM)"},
             "e2e": {"value": v, "unit": "rows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
         return
 
@@ -251,13 +353,18 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    rows = args.rows
-    batch, feats, label = make_device_batch(rows, SEED + rank)
-    checked = build_plan(feats, label)
+    def max_over_ranks(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
+    batch, feats, label, info = benchdata.make_workload(wl, rows, SEED + rank)
+    checked = build_plan(feats, label, info)
     for _ in range(warmup):
-        vec, fitted = run_step(batch, checked)
-        del vec
+        vec, fitted, parts = run_step(batch, checked)
+        del vec, parts
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -265,74 +372,75 @@ def main():
     barrier()
     e0.record()
     for _ in range(steps):
-        vec, fitted = run_step(batch, checked)
-        del vec
+        vec, fitted, parts = run_step(batch, checked)
+        del vec, parts
     e1.record()
     barrier()
-    ms = e0.elapsed_time(e1) / steps
+    ms = max_over_ranks(e0.elapsed_time(e1) / steps)
     clocks = sampler.stop()
-    if world > 1:
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
     value = rows * world / (ms * 1e-3)
 
-    # dominant kernels, measured live on this batch
-    kt = kernel_times(batch)
+    kt = kernel_times(wl, batch, fitted, info)
     peak, peak_src = peaks()
-    tr_gbs = rows * TRANSFORM_BYTES_PER_ROW / (kt["transform"] * 1e-3) / 1e9
-    fit_gbs = rows * FIT_BYTES_PER_ROW / (kt["fit"] * 1e-3) / 1e9
+    for k in kt:
+        k["achieved"] = rows * k["bytes_per_row"] / (k["ms"] * 1e-3) / 1e9
+        k["frac"] = k["achieved"] / peak
 
-    # end to end through the stage API with pinned host buffers (H2D of the raw columns, D2H of the kept columns)
+    # end to end through the stage API with pinned host buffers: H2D of every raw block, D2H of the kept columns
     e2e = None
     if not args.no_e2e:
-        hbatch = host_copy(batch)
-        est = checked.origin_stage
+        hbatch = benchdata.host_copy(batch)
+        h2d = benchdata.input_bytes(hbatch)
+        del batch
+        torch.cuda.empty_cache()
+
+        def e2e_step():
+            vec, _f, parts = run_step(hbatch, checked)
+            host = []
+            for p in parts:                                  # results that are still on the device go back to the host
+                for name in ("data", "indices", "values", "row_start", "row_nnz"):
+                    t = getattr(p, name, None)
+                    if t is not None and hasattr(t, "is_cuda"):
+                        host.append(t.cpu() if t.is_cuda else t)
+            return parts, host
+
         for _ in range(2):
-            vec, _f = run_step(hbatch, checked)
+            parts, host = e2e_step()
         barrier()
         t0 = time.perf_counter()
         k_e2e = max(2, min(steps, 5))
         for _ in range(k_e2e):
-            vec, _f = run_step(hbatch, checked)
+            parts, host = e2e_step()
         barrier()
-        dt = (time.perf_counter() - t0) / k_e2e
-        if world > 1:
-            t = torch.tensor([dt], dtype=torch.float64, device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt = float(t.item())
-        h2d = sum(b.values.numel() * b.values.element_size() + (0 if b.valid is None else b.valid.numel() * 8)
-                  for b in hbatch.blocks)
-        d2h = sum(p.data.numel() * 8 for p in vec.parts)
+        dt = max_over_ranks((time.perf_counter() - t0) / k_e2e)
         e2e = {"value": rows * world / dt, "unit": "rows/s", "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h), "ms_per_step": dt * 1e3, "steps": k_e2e,
-               "api": "fit_and_transform(host ColumnarBatch, label.sanityCheck(transmogrify(features))) -> "
-                      "tmog_real_fit_host / tmog_real_transform_host"}
-        del hbatch, vec
+               "d2h_bytes_per_step": int(sum(t.numel() * t.element_size() for t in host)), "ms_per_step": dt * 1e3,
+               "steps": k_e2e,
+               "api": "fit_and_transform(pinned host ColumnarBatch, label.sanityCheck(transmogrify(features)))"}
+        del hbatch, parts, host
 
     cpu = None
-    if rank == 0 and world == 1:
-        secs = cpu_reference(args.cpu_rows, cores)
-        cpu = {"value": args.cpu_rows / secs, "unit": "rows/s", "cores": cores, "kind": "port",
-               "sample": f"{args.cpu_rows} rows x {NCOLS} columns of the same workload, oracle/c (C + OpenMP) on "
-                         f"{cores} threads, {secs:.2f} s"}
+    if rank == 0 and world == 1 and not args.no_cpu:
+        secs, srows, used, sample = cpu_baseline(wl, cores, args.cpu_rows)
+        cpu = {"value": srows / secs, "unit": "rows/s", "cores": used, "kind": "port",
+               "sample": f"{sample}, {secs:.2f} s"}
     if rank == 0:
         est = checked.origin_stage
-        launches_per_step = 9   # pilot, fit, fit-reduce, label init/distinct/sort/class-id, null-class-count, transform
+        launches = {"c2": 9, "c3": 8, "c4": 12, "c5": 30}[wl]
+        top = kt[0]
         print(json.dumps({
-            "metric": "rows/sec transmogrify+sanityCheck fit+transform", "value": value, "unit": "rows/s",
-            "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD.format(rows=rows, ncols=NCOLS), "rows_per_gpu": rows,
-                       "l2": "inputs (8.1 GB per GPU) exceed the 126 MB L2; no flush needed",
-                       "kept_columns": len(fitted[-1].indicesToKeep), "dropped": est.summary.dropped},
-            "roofline": {"bound": "hbm", "kernel": "vec_transform_kernel<double, true>", "achieved": tr_gbs,
-                         "peak": peak, "unit": "GB/s", "frac": tr_gbs / peak, "traffic": None,
-                         "peak_source": peak_src, "ms": kt["transform"],
-                         "bytes_per_row": TRANSFORM_BYTES_PER_ROW,
-                         "other": {"kernel": "real_fit_kernel", "achieved": fit_gbs, "frac": fit_gbs / peak,
-                                   "ms": kt["fit"], "bytes_per_row": FIT_BYTES_PER_ROW}},
-            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_per_step * steps, "clocks": clocks}))
+            "metric": METRIC, "value": value, "unit": "rows/s", "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": info["desc"], "rows_per_gpu": rows,
+                       "l2": "inputs exceed the 126 MB L2 many times over; no flush needed",
+                       "vector_width": est.summary.count and len(est.summary.names) - 1,
+                       "kept_columns": len(fitted[-1].indicesToKeep), "dropped_columns": len(est.summary.dropped),
+                       "algorithmic_bytes_per_row": {"fit": info["fit_bytes"], "transform": info["transform_bytes"]}},
+            "roofline": {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved"], "peak": peak,
+                         "unit": "GB/s", "frac": top["frac"], "traffic": None, "peak_source": peak_src,
+                         "ms": top["ms"], "bytes_per_row": top["bytes_per_row"], "other": kt[1:]},
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches * steps, "clocks": clocks}))
     if world > 1:
         dist.destroy_process_group()
 

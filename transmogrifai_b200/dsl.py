@@ -52,7 +52,8 @@ def _vectorizer_for(type_name: str, feats: List[F.Feature], d=TransmogrifierDefa
     raise NotImplementedError(f"transmogrify(): no default vectorizer for feature type {type_name} on this path")
 
 
-def transmogrify(features: Sequence[F.Feature], label: Optional[F.Feature] = None) -> F.Feature:
+def transmogrify(features: Sequence[F.Feature], label: Optional[F.Feature] = None,
+                 defaults=TransmogrifierDefaults) -> F.Feature:
     """Seq(features).transmogrify(): one vectorizer per feature TYPE (types visited in type-name order, members in
     input order), then VectorsCombiner."""
     if not features:
@@ -60,7 +61,7 @@ def transmogrify(features: Sequence[F.Feature], label: Optional[F.Feature] = Non
     groups: Dict[str, List[F.Feature]] = {}
     for f in features:
         groups.setdefault(f.type_name, []).append(f)
-    vectors = [f for tp in sorted(groups) for f in ([_vectorizer_for(tp, groups[tp])] if tp != F.OPVECTOR
+    vectors = [f for tp in sorted(groups) for f in ([_vectorizer_for(tp, groups[tp], defaults)] if tp != F.OPVECTOR
                                                      else groups[tp])]
     return VectorsCombiner().setInput(*vectors).getOutput()
 
