@@ -211,6 +211,34 @@ class TextBlock:
         a, b = int(self.offsets[col][row].item()), int(self.offsets[col][row + 1].item())
         return bytes(self.data[col][a:b].cpu().numpy().tobytes()).decode("utf-8")
 
+    def prefix_cells(self, col: int, rows: int) -> List[Optional[str]]:
+        """The first `rows` cells of a column with three host round trips in all (offsets, bytes, validity)."""
+        rows = min(rows, self.n)
+        off = self.offsets[col][:rows + 1].cpu().numpy()
+        raw = self.data[col][int(off[0]):int(off[-1])].cpu().numpy().tobytes() if rows else b""
+        v = self.valid[col]
+        ok = np.ones(rows, dtype=bool) if v is None else np.unpackbits(
+            v[:(rows + 63) // 64].cpu().numpy().view(np.uint8), bitorder="little")[:rows].astype(bool)
+        base = int(off[0])
+        return [raw[int(off[r]) - base:int(off[r + 1]) - base].decode("utf-8") if ok[r] else None
+                for r in range(rows)]
+
+    def cells(self, col: int, rows: Sequence[int]) -> List[Optional[str]]:
+        """Arbitrary cells of a column: one round trip for their offsets, one per cell for the bytes."""
+        if not len(rows):
+            return []
+        idx = torch.as_tensor(np.asarray(rows, dtype=np.int64), device=self.offsets[col].device)
+        a = self.offsets[col].index_select(0, idx).cpu().numpy()
+        b = self.offsets[col].index_select(0, idx + 1).cpu().numpy()
+        out = []
+        for r, lo, hi in zip(rows, a, b):
+            v = self.valid[col]
+            if v is not None and not (int(v[int(r) >> 6].item()) >> (int(r) & 63)) & 1:
+                out.append(None)
+            else:
+                out.append(self.data[col][int(lo):int(hi)].cpu().numpy().tobytes().decode("utf-8"))
+        return out
+
     @staticmethod
     def from_lists(names: Sequence[str], type_name: str, columns: Sequence[Sequence[Optional[str]]],
                    pin: bool = True) -> "TextBlock":

@@ -9,6 +9,8 @@ from __future__ import annotations
 from dataclasses import dataclass, replace
 from typing import Dict, Iterable, List, Optional, Sequence, Tuple
 
+import numpy as np
+
 from .features import MULTIPICKLIST, TEXT_TYPES
 
 NullString = "NullIndicatorValue"
@@ -73,31 +75,85 @@ def feature_column(name: str, type_name: str, is_null: bool = False) -> OpVector
                                   indicatorValue=NullString if is_null else None)
 
 
-@dataclass
 class OpVectorMetadata:
-    name: str
-    columns: List[OpVectorColumnMetadata]
-    history: Dict[str, Tuple[str, ...]]
+    """Metadata of an OPVector: one OpVectorColumnMetadata per column, re-indexed 0..size-1 (OpVectorMetadata.scala:62).
 
-    def __init__(self, name: str, columns: Iterable[OpVectorColumnMetadata],
-                 history: Optional[Dict[str, Sequence[str]]] = None):
+    Hashed text blocks repeat one column description hundreds of thousands of times, so the columns are held as runs
+    (description, count) and only expanded on demand; everything SanityChecker needs is computed per run."""
+
+    def __init__(self, name: str, columns: Optional[Iterable[OpVectorColumnMetadata]] = None,
+                 history: Optional[Dict[str, Sequence[str]]] = None,
+                 runs: Optional[Sequence[Tuple[OpVectorColumnMetadata, int]]] = None):
         self.name = name
-        self.columns = [c if c.index == i else replace(c, index=i) for i, c in enumerate(columns)]  # :62
         self.history = {k: tuple(v) for k, v in (history or {}).items()}
+        merged: List[List] = []
+        source = runs if runs is not None else ((c, 1) for c in (columns or ()))
+        for c, k in source:
+            if k <= 0:
+                continue
+            if merged and merged[-1][0] is c:
+                merged[-1][1] += k
+            else:
+                merged.append([c, k])
+        self.runs: List[Tuple[OpVectorColumnMetadata, int]] = [(c, k) for c, k in merged]
+        self.run_starts = np.concatenate([[0], np.cumsum([k for _, k in self.runs])]).astype(np.int64)
+        self._columns: Optional[List[OpVectorColumnMetadata]] = None
+        self._names: Optional[List[str]] = None
 
     @property
     def size(self) -> int:
-        return len(self.columns)
+        return int(self.run_starts[-1])
+
+    @property
+    def columns(self) -> List[OpVectorColumnMetadata]:
+        if self._columns is None:
+            out: List[OpVectorColumnMetadata] = []
+            for (c, k), s0 in zip(self.runs, self.run_starts[:-1]):
+                s0 = int(s0)
+                out.extend(c if (k == 1 and c.index == s0) else replace(c, index=s0 + i) for i in range(k))
+            self._columns = out
+        return self._columns
+
+    def column(self, i: int) -> OpVectorColumnMetadata:
+        r = int(np.searchsorted(self.run_starts, i, side="right")) - 1
+        return replace(self.runs[r][0], index=int(i))
 
     def columnNames(self) -> List[str]:  # noqa: N802
-        return [c.makeColName() for c in self.columns]
+        if self._names is None:
+            out: List[str] = []
+            for (c, k), s0 in zip(self.runs, self.run_starts[:-1]):
+                stem = c.makeColName().rsplit("_", 1)[0]
+                out.extend(f"{stem}_{int(s0) + i}" for i in range(k))
+            self._names = out
+        return self._names
+
+    def names_of(self, indices: Sequence[int]) -> List[str]:
+        if self._names is not None:
+            return [self._names[int(i)] for i in indices]
+        out = []
+        for i in indices:
+            r = int(np.searchsorted(self.run_starts, i, side="right")) - 1
+            out.append(f"{self.runs[r][0].makeColName().rsplit('_', 1)[0]}_{int(i)}")
+        return out
+
+    def select(self, name: str, keep: Sequence[int]) -> "OpVectorMetadata":
+        """Metadata of the vector restricted to the columns `keep` (ascending), runs preserved."""
+        keep = np.asarray(keep, dtype=np.int64)
+        lo = np.searchsorted(keep, self.run_starts[:-1], side="left")
+        hi = np.searchsorted(keep, self.run_starts[1:], side="left")
+        return OpVectorMetadata(name, history=self.history,
+                                runs=[(c, int(h - l)) for (c, _), l, h in zip(self.runs, lo, hi) if h > l])
+
+    def __eq__(self, other) -> bool:
+        return isinstance(other, OpVectorMetadata) and self.name == other.name and self.size == other.size and \
+            [(replace(c, index=0), k) for c, k in self.runs] == [(replace(c, index=0), k) for c, k in other.runs]
 
     @staticmethod
     def flatten(name: str, vectors: Sequence["OpVectorMetadata"]) -> "OpVectorMetadata":
         """OpVectorMetadata.scala:270-275"""
-        cols: List[OpVectorColumnMetadata] = []
+        runs: List[Tuple[OpVectorColumnMetadata, int]] = []
         hist: Dict[str, Tuple[str, ...]] = {}
         for v in vectors:
-            cols.extend(v.columns)
+            runs.extend(v.runs)
             hist.update(v.history)
-        return OpVectorMetadata(name, cols, hist)
+        return OpVectorMetadata(name, history=hist, runs=runs)

@@ -45,7 +45,8 @@ class CategoricalGroupStats:
 
 @dataclass
 class SanityCheckerSummary:
-    names: List[str]
+    meta: OpVectorMetadata               # metadata of the checked vector (column names are expanded on demand)
+    labelName: str
     count: int
     mean: np.ndarray
     variance: np.ndarray
@@ -58,6 +59,11 @@ class SanityCheckerSummary:
     reasons: Dict[str, List[str]]
     sampleFraction: float
     featureFeatureCorr: Optional[np.ndarray] = None
+
+    @property
+    def names(self) -> List[str]:
+        """featureNames :+ label name (SanityChecker.scala:519)"""
+        return self.meta.columnNames() + [self.labelName]
 
 
 class SanityChecker(OpEstimator):
@@ -187,15 +193,13 @@ class SanityChecker(OpEstimator):
             from .generic_stats import vector_stats
             st = vector_stats(batch, vec, label_f.name)
         lab = st.label
-        cols = meta.columns
+        plan = self._plan(meta)
         # correlations with the label ---------------------------------------------------------------------------
         if self.correlationExclusion == "HashedText":
-            hashed = {c.index for c in cols if c.grouping is None and c.indicatorValue is None
-                      and c.hasParentOfType(F.TEXT, F.TEXTAREA, "TextMap", "TextAreaMap")}
-            corr_indices = [i for i in range(d + 1) if i not in hashed]
+            corr_indices = np.concatenate([np.nonzero(~plan.hashed_text)[0], [d]]).astype(np.int64)
         else:
-            corr_indices = list(range(d + 1))
-        feat_idx = [i for i in corr_indices if i < d]
+            corr_indices = np.arange(d + 1, dtype=np.int64)
+        feat_idx = corr_indices[:-1]
         corr = np.zeros(len(corr_indices))
         if n <= 1:
             raise ValueError(f"requirement failed: computeCorrelationsWithLabel called on matrix with only {n} rows.")
@@ -209,7 +213,7 @@ class SanityChecker(OpEstimator):
         corr_matrix = None
         if self.featureFeatureCorrLevel == "Computed":
             from .generic_stats import pearson_matrix
-            corr_matrix = pearson_matrix(batch, vec, label_f.name, corr_indices, st)
+            corr_matrix = pearson_matrix(batch, vec, label_f.name, [int(i) for i in corr_indices], st)
             corr = corr_matrix[:, -1].copy()
         # categorical tests -------------------------------------------------------------------------------------
         cat_stats: List[CategoricalGroupStats] = []
@@ -220,21 +224,24 @@ class SanityChecker(OpEstimator):
             cat_stats = self._categorical_tests(meta, st)
         # decision ----------------------------------------------------------------------------------------------
         drop, reasons, pc, pv = self._decide(meta, st, corr, corr_indices, corr_matrix, cat_stats)
-        names = self._plan(meta).names
-        to_drop = [names[i] for i in range(d) if drop[i]] if self.removeBadFeatures else []
-        keep = [i for i in range(d) if not (drop[i] and self.removeBadFeatures)]
-        key = (id(meta), tuple(keep))
+        drop_idx = np.nonzero(drop)[0] if self.removeBadFeatures else np.zeros(0, dtype=np.int64)
+        to_drop = meta.names_of(drop_idx)
+        keep = np.nonzero(drop == 0)[0] if self.removeBadFeatures else np.arange(d)
+        key = (id(meta), keep.tobytes())
         if getattr(self, "_out_meta_key", None) != key:     # same input metadata and keep set: same output metadata
-            self._out_meta = OpVectorMetadata(self.getOutputFeatureName(), [cols[i] for i in keep], meta.history)
+            self._out_meta = meta.select(self.getOutputFeatureName(), keep)
             self._out_meta_key = key
         self._metadata = self._out_meta
+        flagged = np.nonzero(reasons)[0]
         self.summary = SanityCheckerSummary(
-            names=names + [label_f.name], count=n, mean=np.append(st.mean, lab.stats[1]),
+            meta=meta, labelName=label_f.name, count=n, mean=np.append(st.mean, lab.stats[1]),
             variance=np.append(st.variance, lab.stats[2]), min=np.append(st.min, lab.stats[3]),
-            max=np.append(st.max, lab.stats[4]), correlationsWithLabel=corr, corrIndices=corr_indices,
-            categoricalStats=cat_stats, dropped=to_drop,
-            reasons={names[i]: [t for b, t in REASONS.items() if reasons[i] & b] for i in range(d) if reasons[i]},
+            max=np.append(st.max, lab.stats[4]), correlationsWithLabel=corr,
+            corrIndices=corr_indices, categoricalStats=cat_stats, dropped=to_drop,
+            reasons={nm: [t for b, t in REASONS.items() if reasons[i] & b]
+                     for nm, i in zip(meta.names_of(flagged), flagged)},
             sampleFraction=frac, featureFeatureCorr=corr_matrix)
+        keep = [int(i) for i in keep]
         self.parentCorr, self.parentCramersV = pc, pv
         if not keep:
             raise ValueError("requirement failed: The sanity checker has dropped all of your features, check your "
@@ -293,8 +300,8 @@ class SanityChecker(OpEstimator):
         if len(corr_indices) == d + 1:
             corr_pos = plan.identity_pos
         else:
-            pos = {ci: k for k, ci in enumerate(corr_indices)}
-            corr_pos = np.array([pos.get(i, -1) for i in range(d)], dtype=np.int32)
+            corr_pos = np.full(d, -1, dtype=np.int32)
+            corr_pos[corr_indices[:-1]] = np.arange(len(corr_indices) - 1, dtype=np.int32)
         cram = np.full(d, np.nan)
         rule_n = np.full(d, -1, dtype=np.int32)
         rconf, rsup = np.zeros(2 * d), np.zeros(2 * d)
@@ -331,31 +338,36 @@ class SanityChecker(OpEstimator):
 
 
 class _MetaPlan:
-    """Column metadata of one vector reduced to the integer arrays the C ABI wants (built once per metadata object):
-    parent / group ids for tmog_sanity_decide, and the categorical groups of SanityChecker.categoricalTests."""
+    """Column metadata of one vector reduced to the integer arrays the C ABI wants (built once per metadata object,
+    run by run): parent / group ids for tmog_sanity_decide, and the categorical groups of categoricalTests."""
 
     def __init__(self, meta: OpVectorMetadata):
         d = meta.size
         parent_ids: Dict[str, int] = {}
         group_ids: Dict[str, int] = {}
-        offs, pids = [0], []
-        self.gid = np.full(d, -1, dtype=np.int32)
-        self.tsh = np.zeros(d, dtype=np.uint8)
+        run_np, run_gid, run_tsh, run_hashed = [], [], [], []
+        pid_chunks = []
         groups: Dict[str, list] = {}
-        for c in meta.columns:
-            for pn in c.parentNamesWithMapKeys():
-                pids.append(parent_ids.setdefault(pn, len(parent_ids)))
-            offs.append(len(pids))
+        counts = np.array([k for _, k in meta.runs], dtype=np.int64)
+        for (c, k), s0 in zip(meta.runs, meta.run_starts[:-1]):
+            pids = [parent_ids.setdefault(pn, len(parent_ids)) for pn in c.parentNamesWithMapKeys()]
+            run_np.append(len(pids))
+            pid_chunks.append(np.tile(np.asarray(pids, dtype=np.int32), k))
             g = c.featureGroup()
-            if g is not None:
-                self.gid[c.index] = group_ids.setdefault(g, len(group_ids))
-                if c.indicatorValue is not None:
-                    groups.setdefault(g, []).append(c)
-            self.tsh[c.index] = c.isTextSharedHash
-        self.offs = np.asarray(offs, dtype=np.int32)
-        self.pids = np.asarray(pids, dtype=np.int32)
+            run_gid.append(group_ids.setdefault(g, len(group_ids)) if g is not None else -1)
+            run_tsh.append(c.isTextSharedHash)
+            run_hashed.append(c.grouping is None and c.indicatorValue is None
+                              and c.hasParentOfType(F.TEXT, F.TEXTAREA, "TextMap", "TextAreaMap"))
+            if g is not None and c.indicatorValue is not None:
+                for i in range(k):
+                    groups.setdefault(g, []).append((c, int(s0) + i))
+        per_col_np = np.repeat(np.asarray(run_np, dtype=np.int64), counts)
+        self.offs = np.concatenate([[0], np.cumsum(per_col_np)]).astype(np.int32)
+        self.pids = np.concatenate(pid_chunks).astype(np.int32) if pid_chunks else np.zeros(0, dtype=np.int32)
+        self.gid = np.repeat(np.asarray(run_gid, dtype=np.int32), counts)
+        self.tsh = np.repeat(np.asarray(run_tsh, dtype=np.uint8), counts)
+        self.hashed_text = np.repeat(np.asarray(run_hashed, dtype=bool), counts)
         self.identity_pos = np.arange(d, dtype=np.int32)
-        self.names = meta.columnNames()
         # categorical groups: duplicate indicator values inside a group -> only the first is used (:295-298)
         self.groups = []
         self.has_mpl = False
@@ -363,13 +375,13 @@ class _MetaPlan:
         r = 0
         for g, cols in groups.items():
             seen, cleaned = set(), []
-            for c in cols:
+            for c, i in cols:
                 if c.indicatorValue not in seen:
                     seen.add(c.indicatorValue)
-                    cleaned.append(c)
-            idx = [c.index for c in cleaned]
-            self.has_mpl = self.has_mpl or any(c.isMultiPickList for c in cleaned)
-            self.groups.append((g, [self.names[i] for i in idx], idx))
+                    cleaned.append((c, i))
+            idx = [i for _, i in cleaned]
+            self.has_mpl = self.has_mpl or any(c.isMultiPickList for c, _ in cleaned)
+            self.groups.append((g, meta.names_of(idx), idx))
             nrows = 2 if len(idx) == 1 else len(idx)
             if len(idx) == 1:
                 lone_rows.append(r)

@@ -260,7 +260,7 @@ class SmartTextVectorizer(OpEstimator):
                 continue
             used = np.nonzero(hashes != np.uint64(M64))[0]
             rows = first[used].astype(np.int64)
-            raws = [dev.cell(c, int(r)) for r in rows]
+            raws = dev.cells(c, rows)
             ids, distinct = clean_and_group(raws, self.cleanText)
             vc: Dict[str, int] = {}
             for k, i in enumerate(ids):
@@ -275,7 +275,7 @@ class SmartTextVectorizer(OpEstimator):
         rows = 4 * (self.maxCardinality + 8)
         while True:
             rows = min(rows, n)
-            raws = [dev.cell(c, r) for r in range(rows)]
+            raws = dev.prefix_cells(c, rows)
             present = [v for v in raws if v is not None]
             ids, distinct = clean_and_group(present, self.cleanText)
             vc: Dict[str, int] = {}
@@ -345,26 +345,25 @@ class SmartTextVectorizerModel(OpModel):
     # -- metadata (SmartTextVectorizer.makeVectorMetadata :154-186) ----------------------------------------------------
     def _build_metadata(self) -> OpVectorMetadata:
         feats = self.inN
-        cols: List[OpVectorColumnMetadata] = []
+        runs: List[Tuple[OpVectorColumnMetadata, int]] = []
         for j in self.pivot_idx:
             f = feats[j]
             vals = list(self.topValues[j]) + [self.unseenName] + ([NullString] if self.shouldTrackNulls else [])
-            cols += [OpVectorColumnMetadata((f.name,), (f.type_name,), grouping=f.name, indicatorValue=v)
+            runs += [(OpVectorColumnMetadata((f.name,), (f.type_name,), grouping=f.name, indicatorValue=v), 1)
                      for v in vals]
         lay = self.layout
         if lay.text_idx:
             hf = [feats[j] for j in lay.hash_idx]
             if lay.hash_idx:
                 if lay.shared:
-                    shared_col = OpVectorColumnMetadata(tuple(f.name for f in hf), tuple(f.type_name for f in hf))
-                    cols += [shared_col] * lay.num_features
+                    runs.append((OpVectorColumnMetadata(tuple(f.name for f in hf), tuple(f.type_name for f in hf)),
+                                 lay.num_features))
                 else:
-                    for f in hf:
-                        cols += [feature_column(f.name, f.type_name)] * lay.num_features
+                    runs += [(feature_column(f.name, f.type_name), lay.num_features) for f in hf]
             # the reference appends the null-indicator columns to the metadata whether or not nulls are tracked
             # (SmartTextVectorizer.scala:176-183); kept as is, SanityChecker then rejects the width mismatch
-            cols += [feature_column(feats[j].name, feats[j].type_name, is_null=True) for j in lay.text_idx]
-        return OpVectorMetadata(self.parent.getOutputFeatureName(), cols, self.parent.history())
+            runs += [(feature_column(feats[j].name, feats[j].type_name, is_null=True), 1) for j in lay.text_idx]
+        return OpVectorMetadata(self.parent.getOutputFeatureName(), history=self.parent.history(), runs=runs)
 
     # -- device tables -------------------------------------------------------------------------------------------------
     def _pivot_tables(self, dev: TextBlock, n: int):
