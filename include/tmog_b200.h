@@ -239,25 +239,33 @@ int tmog_text_codes_dev(const int64_t* col_desc, const int32_t* col_index, int n
  *   params [8] (HOST): numFeatures, sharedHashSpace, binaryFreq, minTokenLength, trackNulls, prependFeatureName,
  *                      null_base (vector index of the first null indicator; >= width of the hash block), nclasses.
  * Vector index of a hit: bucket (+ j * numFeatures for separate spaces); null indicator of column j: null_base + j.
- * flags [4] (device): non-ASCII byte, > 512 tokens in a cell, > 4096 hits in a row, sparse capacity exceeded.
+ * text bytes are read with aligned 16-byte loads, so every column's `data` must lie in an allocation whose bounds are
+ * 16-byte aligned (true of anything cudaMalloc returns).
+ * scratch: tmog_text_hash_scratch_bytes(n) bytes of device memory, 8-byte aligned, contents irrelevant (row counters and
+ *   the list of rows with too many distinct buckets for the fast table, which a second launch redoes).
+ * flags [4] (device): [0] non-ASCII byte met (unsupported), [1] a run of token characters longer than ~4000 bytes,
+ *   [2] a row with more than ~12000 distinct buckets, [3] sparse capacity exceeded.
  *
  * _stats: SanityChecker sums per vector index (NOT cleared here; sized null_base + ncols):
- *   bucket_class_sum [index * nclasses + class] += term frequency, bucket_nnz [index] += 1 per row holding the index,
- *   bucket_sq_extra [index] += tf^2 - tf   (so that sum v^2 = sum v + extra);
+ *   bucket_class_sum [index * nclasses + class] += term frequency tf of every row holding the index;
+ *   for the rare tf > 1 only: bucket_dup [index] += tf - 1 (rows holding the index = sum of class sums - dup),
+ *   bucket_sq_extra [index] += tf^2 - tf   (so that sum v^2 = sum v + extra), and
  *   bucket_aux [3 * index + {0, 1, 2}] (zeroed by the caller) = max tf, ~(min tf among tf > 1), rows with tf > 1 --
- *   touched only for the rare tf > 1, they give the exact column max / min.
+ *   they give the exact column max / min.
  * _transform: sparse rows in 4-array CSR form: row r owns out_idx / out_val [row_start[r], row_start[r] + row_nnz[r]),
  *   indices ascending; newpos [null_base + ncols] maps a vector index to its output index or -1 (dropped by
  *   SanityChecker); *cursor (device u64, zeroed by the caller) ends as the total number of entries; entries beyond
  *   `capacity` are counted but not written (flags[3]) -- call with capacity 0 to size the buffers. */
+int tmog_text_hash_scratch_bytes(int64_t n, size_t* bytes);
 int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
                              const int32_t* prefix_len, const int32_t* params, const uint8_t* class_ids,
-                             uint32_t* bucket_class_sum, uint32_t* bucket_nnz, uint64_t* bucket_sq_extra,
-                             uint32_t* bucket_aux, int32_t* flags, void* stream);
+                             uint32_t* bucket_class_sum, uint32_t* bucket_dup, uint64_t* bucket_sq_extra,
+                             uint32_t* bucket_aux, int32_t* flags, void* scratch, size_t scratch_bytes, void* stream);
 int tmog_text_hash_transform_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
                                  const int32_t* prefix_len, const int32_t* params, const int32_t* newpos,
                                  int64_t* row_start, int32_t* row_nnz, int32_t* out_idx, int32_t* out_val,
-                                 uint64_t* cursor, int64_t capacity, int32_t* flags, void* stream);
+                                 uint64_t* cursor, int64_t capacity, int32_t* flags, void* scratch,
+                                 size_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------------
  * Label classes

@@ -212,3 +212,57 @@ def test_transmogrify_sanity_check_text_matches_oracle(device):
     got = out_batch.vectors[checked.name].to_scipy()
     exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
     assert got.shape == exp.shape and abs(got - exp).max() < 1e-9
+
+
+def _hash_case(cols, names, num_features, strategy, **kw):
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    batch = _batch({nm: (F.TEXT, c) for nm, c in zip(names, cols)}, device="cuda")
+    est = SmartTextVectorizer().setMaxCardinality(0).setNumFeatures(num_features).setHashSpaceStrategy(strategy) \
+        .setInput(*_feats(names))
+    model = est.fit(batch)
+    got = model.transform(batch).vectors[est.getOutput().name].to_scipy()
+    exp = V.smart_text_transform(cols, names, ["Hash"] * len(names), [[] for _ in names], num_features=num_features,
+                                 track_nulls=True, prepend_feature_name=True, binary_freq=False,
+                                 hash_space_strategy=strategy, min_token_length=1)
+    assert got.shape == exp.shape
+    diff = (got != exp)
+    assert diff.nnz == 0, f"{diff.nnz} entries differ, first rows {sorted(set(diff.nonzero()[0]))[:5]}"
+    return got
+
+
+def test_hash_long_cells_and_crowded_rows():
+    """Cells longer than the kernel's text buffer (staged in pieces cut at a word break), rows with more distinct
+    buckets than the fast table holds (redone by the second launch), runs longer than maxTokenLength, '_' runs."""
+    rng = np.random.default_rng(11)
+    words = ["".join(rng.choice(list("abcdefghijklmnopqrstuvwxyz0123456789"), size=rng.integers(1, 12)))
+             for _ in range(6000)]
+    long_cell = " ".join(words[i] for i in rng.integers(0, 6000, size=2500))          # ~16 KB, ~2000 distinct
+    seps = [" ", ", ", ".", "'", ":", ";", "_", " - ", "\n"]
+    messy = "".join(words[i] + seps[i % len(seps)] for i in rng.integers(0, 300, size=1500))
+    col_a = [long_cell, "short one", None, messy, "b" * 255 + " " + "c" * 256 + " " + "d" * 700 + " end",
+             "_" * 10 + " " + "_" * 300 + "z" + " _x_ __", " ".join(words[:4000]), "", "z" * 2046, "y" * 2015 + " q"]
+    col_b = [" ".join(words[i] for i in rng.integers(0, 6000, size=rng.integers(0, 900))) for _ in col_a]
+    col_b[2] = None
+    for strategy in ("Shared", "Separate"):
+        _hash_case([col_a, col_b], ["long_a", "long_b"], 1 << 12, strategy)
+
+
+def test_hash_token_run_longer_than_buffer_is_refused():
+    with pytest.raises(ValueError, match="longer than"):
+        _hash_case([["ok text", "a" * 9000 + " tail"]], ["t"], 64, "Shared")
+
+
+def test_hash_many_columns_wide_keys_and_count_overflow():
+    """More than 32 (several cell passes) and more than 64 columns (prefix state not cached) with separate spaces wide
+    enough for the 64-bit table; and a bucket met > 255 times in one row with 2^23 buckets, where the packed 32-bit
+    slot overflows and the row is redone with 64-bit slots."""
+    rng = np.random.default_rng(13)
+    vocab = ["".join(rng.choice(list("abcdefghijklmnopqrstuvwxyz"), size=rng.integers(2, 9))) for _ in range(300)]
+    names = [f"col{j}" for j in range(70)]
+    cols = [_random_text(rng, vocab, 40, null_frac=0.2) for _ in names]
+    _hash_case(cols, names, 1 << 18, "Separate")
+    _hash_case(cols[:40], names[:40], 1 << 10, "Separate")
+    rep = [" ".join(["repeat"] * 700 + ["other"] * 3), "repeat once", " ".join(["w%d" % (i % 7) for i in range(2000)])]
+    got = _hash_case([rep], ["rep"], 1 << 23, "Shared")
+    assert got[0].data.max() == 700

@@ -65,9 +65,12 @@ class_sum = torch.zeros(w_all * ncls, dtype=torch.int32, device="cuda"); nnz = t
 extra = torch.zeros(w_all, dtype=torch.int64, device="cuda"); aux = torch.zeros(3 * w_all, dtype=torch.int32, device="cuda")
 flags = torch.zeros(4, dtype=torch.int32, device="cuda")
 st = torch.cuda.current_stream().cuda_stream
+import ctypes
+_need = ctypes.c_size_t(0); L.call("tmog_text_hash_scratch_bytes", n, ctypes.byref(_need))
+scratch = torch.empty(_need.value, dtype=torch.uint8, device="cuda")
 def stats():
     L.call("tmog_text_hash_stats_dev", d_desc.data_ptr(), ncols, n, d_prefix.data_ptr(), d_plen.data_ptr(), params.ctypes.data,
-           cls.data_ptr(), class_sum.data_ptr(), nnz.data_ptr(), extra.data_ptr(), aux.data_ptr(), flags.data_ptr(), st)
+           cls.data_ptr(), class_sum.data_ptr(), nnz.data_ptr(), extra.data_ptr(), aux.data_ptr(), flags.data_ptr(), scratch.data_ptr(), scratch.numel(), st)
 def timeit(f, reps=3):
     f(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -81,12 +84,13 @@ print(f"hash-stats: {t:.2f} ms  {n / t * 1e3 / 1e6:.2f} M rows/s  {tot_bytes / t
 params2 = params.copy(); params2[7] = 1
 newpos = torch.arange(w_all, dtype=torch.int32, device="cuda")
 row_start = torch.empty(n, dtype=torch.int64, device="cuda"); row_nnz = torch.empty(n, dtype=torch.int32, device="cuda")
-cap = int(nnz.long().sum().item()) // 4 + 16
+cap = int(class_sum.long().sum().item()) // 4 + 16   # upper bound: every hit distinct
 idx = torch.empty(cap, dtype=torch.int32, device="cuda"); val = torch.empty(cap, dtype=torch.int32, device="cuda")
 cursor = torch.zeros(1, dtype=torch.int64, device="cuda")
 def tr():
     cursor.zero_()
     L.call("tmog_text_hash_transform_dev", d_desc.data_ptr(), ncols, n, d_prefix.data_ptr(), d_plen.data_ptr(), params2.ctypes.data,
-           newpos.data_ptr(), row_start.data_ptr(), row_nnz.data_ptr(), idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), cap, flags.data_ptr(), st)
+           newpos.data_ptr(), row_start.data_ptr(), row_nnz.data_ptr(), idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), cap, flags.data_ptr(), scratch.data_ptr(), scratch.numel(), st)
 t2 = timeit(tr)
+print("deferred rows:", int(scratch[16:20].view(torch.int32).item()))
 print(f"hash-transform: {t2:.2f} ms  {n / t2 * 1e3 / 1e6:.2f} M rows/s  nnz {int(cursor.item())} cap {cap} flags {flags.cpu().tolist()}")

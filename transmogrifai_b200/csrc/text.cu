@@ -12,9 +12,8 @@
 //                       null indicators; either accumulated into per-bucket statistics for SanityChecker (fit) or
 //                       written as sorted sparse rows (transform)
 //
-// One CTA (4 warps) works on one row at a time: warps take columns, lanes take tokens; the row's bucket indices are
-// collected in shared memory, bitonic-sorted and run-length encoded.  This path is instruction-bound, not HBM-bound
-// (~100 instructions per token); see DESIGN.md.
+// The tokenise + hash kernel is instruction-bound, not HBM-bound; its design is described above the kernel and in
+// DESIGN.md.
 #include <string.h>
 
 #include <algorithm>
@@ -95,12 +94,6 @@ struct StopEntry {
     char w[STOP_MAXLEN];
 };
 __constant__ StopEntry c_stop[STOP_SLOTS];
-
-__host__ __device__ inline unsigned stop_hash(const unsigned char* s, int len) {
-    unsigned h = 2166136261u;
-    for (int i = 0; i < len; ++i) h = (h ^ s[i]) * 16777619u;
-    return h;
-}
 
 // ------------------------------------------------------------------------------------------------------------------
 // column descriptors
@@ -259,11 +252,28 @@ text_code_kernel(const TextColumn* __restrict__ cols, const int* __restrict__ co
 // ------------------------------------------------------------------------------------------------------------------
 // tokenise + hash
 // ------------------------------------------------------------------------------------------------------------------
-constexpr int TH_THREADS = 128;
-constexpr int TH_WARPS = TH_THREADS / 32;
-constexpr int TH_TOK_CAP = 512;    // tokens per cell handled per warp
-constexpr int TH_LIST_CAP = 4096;  // bucket hits per row
-constexpr int TH_PREFIX = 16;      // bytes reserved for "<nameHash>_"
+// One warp owns one row at a time (rows are handed out through a global counter).  The work on a row is split into
+// phases that each keep all 32 lanes busy:
+//
+//   stage     the bytes of a cell are copied to the warp's text buffer in shared memory with 16-byte loads (lower-cased
+//             four bytes at a time, bytes outside the cell zeroed); cells are packed back to back on 32-byte boundaries
+//             with the same alignment (mod 32) as in global memory
+//   classify  one lane per byte: a byte belongs to a token if it is a letter, a digit, '_' or a Mid* character between
+//             two letters / two digits (UAX#29 WB6/7, WB11/12 for ASCII -- the decision only needs the two
+//             neighbours); __ballot_sync gives 32 bits of the token mask, token starts (a set bit after a clear one)
+//             are compacted into a list
+//   hash      one lane per TOKEN of the list: its end is found in the mask, the stop-word probe and murmur3 (continued
+//             from the state after the "<nameHash>_" prefix of its column) read the staged bytes as unaligned words,
+//             and the bucket goes into the row's open-addressing table (key | count in one slot) in shared memory
+//   flush     at the end of the row the table is emitted: per-bucket statistics with global atomics (fit) or compacted,
+//             bitonic-sorted and written as a sparse row (transform)
+//
+// Rows that do not fit the table of the fast variant (too many distinct buckets, or a count that overflows the packed
+// slot) are put on a list and redone by a second launch whose table is 64-bit slots in nearly all of shared memory.
+constexpr int TH_PREFIX = 16;        // bytes reserved for "<nameHash>_"
+constexpr int TH_COLCACHE = 64;      // columns whose murmur3 prefix state is cached in shared memory
+constexpr int TH_GRAB = 4;           // rows taken from the counter at once
+constexpr int TH_MAX_TOKEN = 255;    // StandardAnalyzer.DEFAULT_MAX_TOKEN_LENGTH
 
 struct TextHashParams {
     int num_features;      // hash buckets per space
@@ -275,231 +285,486 @@ struct TextHashParams {
     int hash_width;        // total width of the hash block (num_features or ncols * num_features)
     int null_base;         // index of the first null-indicator column (= hash_width + length columns)
     int nclasses;
+    int pow2_mask;         // num_features - 1 if it is a power of two, else -1
+    int count_bits;        // low bits of a table slot that hold the count (the key sits above)
 };
 
-// flags: [0] non-ASCII byte met, [1] a cell had more than TH_TOK_CAP tokens, [2] a row had more than TH_LIST_CAP hits,
-//        [3] sparse output capacity exceeded
-template <bool SPARSE_OUT>
-__global__ void __launch_bounds__(TH_THREADS)
+struct StopSlot {          // stop-word table in shared memory: length + the word packed little-endian in 3 words
+    unsigned len, w0, w1, w2;
+};
+
+__host__ __device__ inline unsigned stop_slot_hash(unsigned w0, unsigned w1, unsigned w2) {
+    return ((w0 * 0x9E3779B1u) ^ (w1 * 0x85EBCA6Bu) ^ (w2 * 0xC2B2AE35u)) >> 23;   // 9 bits: STOP_SLOTS == 512
+}
+
+template <typename Slot> struct SlotTraits;
+template <> struct SlotTraits<unsigned> { static constexpr unsigned EMPTY = 0xffffffffu; };
+template <> struct SlotTraits<unsigned long long> { static constexpr unsigned long long EMPTY = ~0ull; };
+
+// lower-case four ASCII bytes at once
+__device__ __forceinline__ unsigned lower4(unsigned w) {
+    const unsigned h = w & 0x7f7f7f7fu;
+    const unsigned ge_a = h + 0x3f3f3f3fu;      // bit 7 of a byte set iff it is >= 'A'
+    const unsigned gt_z = h + 0x25252525u;      // bit 7 set iff > 'Z'
+    return w | ((ge_a & ~gt_z & ~w & 0x80808080u) >> 2);
+}
+// bytes [lo, hi) of a word kept (lo, hi relative to the word, any range)
+__device__ __forceinline__ unsigned byte_range_mask(int lo, int hi) {
+    lo = max(lo, 0);
+    hi = min(hi, 4);
+    if (hi <= lo) return 0u;
+    const unsigned upto_hi = hi == 4 ? 0xffffffffu : (1u << (8 * hi)) - 1u;
+    return upto_hi & ~((1u << (8 * lo)) - 1u);
+}
+
+// bytes of one warp's working set in shared memory
+template <typename Slot, int T, int TB>
+struct ThLayout {
+    static constexpr int BUF = 0;                               // 16 slack + TB text + 32 slack
+    static constexpr int MASK = BUF + 16 + TB + 32;             // (TB / 32 + 1) words, the last one stays zero
+    static constexpr int TOKS = MASK + ((TB / 32 + 1) * 4 + 15) / 16 * 16;   // TB / 2 token starts (u16)
+    static constexpr int WCELL = TOKS + TB;                     // cell of every 32-byte window (u8)
+    static constexpr int TABLE = WCELL + (TB / 32 + 15) / 16 * 16;
+    static constexpr int BYTES = TABLE + T * (int)sizeof(Slot);
+};
+
+// flags: [0] non-ASCII byte met, [1] a run of token characters longer than the text buffer, [2] a row has more
+//        distinct buckets than the large table holds, [3] sparse output capacity exceeded
+template <typename Slot, int T, int TB, int WARPS, bool SPARSE_OUT>
+__global__ void __launch_bounds__(WARPS * 32)
 text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, const uint8_t* __restrict__ prefix,
                  const int* __restrict__ prefix_len, TextHashParams p, const uint8_t* __restrict__ class_ids,
+                 // rows to work on: all of [0, n), or row_list[0 .. *row_list_n) (rows deferred by the fast variant)
+                 const int32_t* __restrict__ row_list, const unsigned* __restrict__ row_list_n,
+                 unsigned long long* __restrict__ row_counter,
+                 // rows this launch cannot hold are appended here (NULL: set flags[2] instead)
+                 int32_t* __restrict__ defer_list, unsigned* __restrict__ defer_n,
                  // statistics mode
-                 unsigned int* __restrict__ bucket_class_sum, unsigned int* __restrict__ bucket_nnz,
+                 unsigned int* __restrict__ bucket_class_sum, unsigned int* __restrict__ bucket_dup,
                  unsigned long long* __restrict__ bucket_sq_extra, unsigned int* __restrict__ bucket_aux,
                  // sparse-output mode
                  const int32_t* __restrict__ newpos, int64_t* __restrict__ row_start, int32_t* __restrict__ row_nnz,
                  int32_t* __restrict__ out_idx, int32_t* __restrict__ out_val, unsigned long long* __restrict__ cursor,
                  int64_t capacity, int* __restrict__ flags) {
-    __shared__ int list[TH_LIST_CAP];
-    __shared__ int tok_start[TH_WARPS][TH_TOK_CAP];
-    __shared__ int tok_end[TH_WARPS][TH_TOK_CAP];
-    __shared__ int list_len;
-    __shared__ unsigned long long out_base;
-    __shared__ int scan_tmp[TH_WARPS];
+    using L = ThLayout<Slot, T, TB>;
+    constexpr Slot EMPTY = SlotTraits<Slot>::EMPTY;
+    extern __shared__ __align__(16) unsigned char th_smem[];
+    StopSlot* stop = reinterpret_cast<StopSlot*>(th_smem);                                   // [STOP_SLOTS]
+    unsigned* colstate = reinterpret_cast<unsigned*>(th_smem + STOP_SLOTS * sizeof(StopSlot));  // [TH_COLCACHE][3]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const unsigned lt_mask = (1u << lane) - 1u;
+    static_assert(L::BYTES % 16 == 0 && (TH_COLCACHE * 12) % 16 == 0, "per-warp regions must stay 16-byte aligned");
+    unsigned char* wbase = th_smem + STOP_SLOTS * sizeof(StopSlot) + TH_COLCACHE * 12 + (size_t)warp * L::BYTES;
+    unsigned char* buf = wbase + L::BUF + 16;                      // text; buf[-16 ..) and (.. TB + 32) are slack
+    const unsigned* bufw = reinterpret_cast<const unsigned*>(wbase + L::BUF);
+    unsigned* mask = reinterpret_cast<unsigned*>(wbase + L::MASK);
+    unsigned short* toks = reinterpret_cast<unsigned short*>(wbase + L::TOKS);
+    unsigned char* wcell = wbase + L::WCELL;
+    Slot* table = reinterpret_cast<Slot*>(wbase + L::TABLE);
 
-    for (int64_t row = blockIdx.x; row < n; row += gridDim.x) {
-        if (tid == 0) list_len = 0;
-        __syncthreads();
-        for (int j = warp; j < ncols; j += TH_WARPS) {
-            const TextColumn tc = cols[j];
-            int emitted = 0;
-            if (cell_valid(tc, row)) {
-                const int64_t a = tc.offsets[row];
-                const int len = (int)(tc.offsets[row + 1] - a);
-                const uint8_t* s = tc.data + a;
-                // ---- pass 1: token boundaries, 32 bytes per step
-                int ntok = 0, nend = 0;
-                unsigned carry_t = 0;                 // previous byte was a token character
-                bool carry_l = false, carry_d = false;  // previous byte was a letter / digit
-                for (int base = 0; base < len; base += 32) {
-                    const int pos = base + lane;
-                    const unsigned b = pos < len ? s[pos] : ' ';
-                    const unsigned nb = pos + 1 < len ? s[pos + 1] : ' ';
-                    if (b >= 0x80u) flags[0] = 1;
-                    const bool L = is_letter(b), D = is_digit(b);
-                    bool pl = __shfl_up_sync(FULL, L, 1), pd = __shfl_up_sync(FULL, D, 1);
-                    if (lane == 0) { pl = carry_l; pd = carry_d; }
-                    const bool nl = is_letter(nb), nd = is_digit(nb);
-                    const bool mid_letter = b == ':' || b == '.' || b == '\'';   // MidLetter | MidNumLet | SingleQuote
-                    const bool mid_num = b == ',' || b == ';' || b == '.' || b == '\'';  // MidNum | MidNumLet | SQ
-                    const bool tokc = L || D || b == '_' || (mid_letter && pl && nl) || (mid_num && pd && nd);
-                    const unsigned T = __ballot_sync(FULL, tokc);
-                    const unsigned prevT = (T << 1) | carry_t;
-                    const unsigned S = T & ~prevT, E = ~T & prevT;
-                    if ((S >> lane) & 1u) {
-                        const int ord = ntok + __popc(S & lt_mask);
-                        if (ord < TH_TOK_CAP) tok_start[warp][ord] = pos;
-                    }
-                    if ((E >> lane) & 1u) {
-                        const int ord = nend + __popc(E & lt_mask);
-                        if (ord < TH_TOK_CAP) tok_end[warp][ord] = pos;
-                    }
-                    ntok += __popc(S);
-                    nend += __popc(E);
-                    carry_t = T >> 31;
-                    carry_l = __shfl_sync(FULL, L, 31);
-                    carry_d = __shfl_sync(FULL, D, 31);
+    for (int i = tid; i < STOP_SLOTS; i += WARPS * 32) {
+        const StopEntry e = c_stop[i];
+        StopSlot sl = {e.len, 0u, 0u, 0u};
+        for (int q = 0; q < e.len; ++q) {
+            const unsigned c = (unsigned char)e.w[q];
+            if (q < 4) sl.w0 |= c << (8 * q);
+            else if (q < 8) sl.w1 |= c << (8 * (q - 4));
+            else sl.w2 |= c << (8 * (q - 8));
+        }
+        stop[i] = sl;
+    }
+    for (int j = tid; j < min(ncols, TH_COLCACHE); j += WARPS * 32) {
+        Murmur pm;
+        pm.init();
+        const int plen = p.prepend ? prefix_len[j] : 0;
+        for (int q = 0; q < plen; ++q) pm.push(prefix[j * TH_PREFIX + q]);
+        colstate[3 * j] = pm.h;
+        colstate[3 * j + 1] = pm.word;
+        colstate[3 * j + 2] = pm.n;
+    }
+    for (int i = lane; i < T; i += 32) table[i] = EMPTY;
+    for (int i = lane; i < (L::TOKS - L::BUF) / 4; i += 32) reinterpret_cast<unsigned*>(wbase)[i] = 0u;
+    __syncthreads();
+
+    const int cb = p.count_bits;
+    const Slot cmask = (Slot(1) << cb) - Slot(1);
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int64_t nrows = row_list ? (int64_t)*row_list_n : n;
+
+    for (;;) {
+        unsigned long long grab = 0;
+        if (lane == 0) grab = atomicAdd(row_counter, (unsigned long long)TH_GRAB);
+        grab = __shfl_sync(FULL, grab, 0);
+        if ((int64_t)grab >= nrows) break;
+        const int64_t grab_end = min((int64_t)grab + TH_GRAB, nrows);
+        for (int64_t ri = (int64_t)grab; ri < grab_end; ++ri) {
+            const int64_t row = row_list ? (int64_t)row_list[ri] : ri;
+
+            // ---- size of the table for this row: a power of two >= 2 x (upper bound of the hits), at most T
+            int64_t bytes_bound = 0;
+            for (int c0 = 0; c0 < ncols; c0 += 32) {
+                const int j = c0 + lane;
+                if (j < ncols) {
+                    const TextColumn tc = cols[j];
+                    if (cell_valid(tc, row)) bytes_bound += (tc.offsets[row + 1] - tc.offsets[row] + 1) >> 1;
                 }
-                if (carry_t && lane == 0 && nend < TH_TOK_CAP) tok_end[warp][nend] = len;
-                if (ntok > TH_TOK_CAP) {
-                    if (lane == 0) flags[1] = 1;
-                    ntok = TH_TOK_CAP;
+            }
+            for (int o = 16; o > 0; o >>= 1) bytes_bound += __shfl_xor_sync(FULL, bytes_bound, o);
+            bytes_bound += ncols;
+            int tbits = 6;
+            while (tbits < 31 && (1ll << tbits) < 2 * bytes_bound && (1 << tbits) < T) ++tbits;
+            const int tsize = 1 << tbits;
+            const int dist_limit = tsize - (tsize >> 2);        // the table never gets fuller than 3/4 (+ 32)
+            int ndist = 0;
+            bool row_bad = false;
+
+            for (int c0 = 0; c0 < ncols && !row_bad; c0 += 32) {
+                // ---- lane k holds cell k of this pass
+                const int ncells = min(32, ncols - c0);
+                const uint8_t* my_ptr = nullptr;
+                int64_t my_len = 0;
+                if (lane < ncells) {
+                    const TextColumn tc = cols[c0 + lane];
+                    if (cell_valid(tc, row)) {
+                        const int64_t a = tc.offsets[row];
+                        my_len = tc.offsets[row + 1] - a;
+                        my_ptr = tc.data + a;
+                    }
                 }
-                __syncwarp();
-                // ---- pass 2: one token per lane: lower-case, filters, murmur3 of prefix + token
-                const int plen = p.prepend ? prefix_len[j] : 0;
-                const uint8_t* pre = prefix + j * TH_PREFIX;
-                const int space_off = p.shared ? 0 : j * p.num_features;
-                for (int k0 = 0; k0 < ntok; k0 += 32) {
-                    const int k = k0 + lane;
-                    int hits = 0;
-                    if (k < ntok) {
-                        const int ts = tok_start[warp][k], te = tok_end[warp][k];
-                        // tokens longer than 255 characters are chopped into 255-character pieces (Lucene >= 6.5)
-                        for (int ps = ts; ps < te; ps += 255) {
-                            const int pe = min(te, ps + 255);
-                            const int tl = pe - ps;
-                            bool alnum = false;
-                            unsigned char low[STOP_MAXLEN];
-                            Murmur mm;
-                            mm.init();
-                            for (int q = 0; q < plen; ++q) mm.push(pre[q]);
-                            for (int q = 0; q < tl; ++q) {
-                                const unsigned c = to_lower(s[ps + q]);
-                                alnum |= is_letter(c) || is_digit(c);
-                                if (q < STOP_MAXLEN) low[q] = (unsigned char)c;
-                                mm.push(c);
+                unsigned emitted = 0u;       // bit k: a token of cell k survived (per lane, OR-reduced below)
+                int k = 0;
+                int64_t off = 0;             // bytes of cell k already consumed (cells longer than the buffer)
+                for (;;) {
+                    int fill = 0, ntok = 0;
+                    // ---- stage + classify as many cells as the buffer holds
+                    while (k < ncells) {
+                        const int64_t len = __shfl_sync(FULL, my_len, k);
+                        const int64_t rem = len - off;
+                        if (rem <= 0) {
+                            ++k;
+                            off = 0;
+                            continue;
+                        }
+                        const uint8_t* g = reinterpret_cast<const uint8_t*>(
+                                               __shfl_sync(FULL, reinterpret_cast<unsigned long long>(my_ptr), k)) + off;
+                        const int a32 = (int)(reinterpret_cast<uintptr_t>(g) & 31u);
+                        bool final = true;
+                        int cnt;
+                        if (fill + a32 + rem + 1 <= TB) {
+                            cnt = (int)rem;
+                        } else if (fill > 0) {
+                            break;                       // hash what is staged, then come back with an empty buffer
+                        } else {
+                            cnt = TB - 33;               // a piece of a long cell
+                            final = false;
+                        }
+                        // stage: 16-byte chunks, global and shared addresses congruent mod 32
+                        const int sh16 = a32 & 15;
+                        const int pos0 = fill + a32;
+                        const uint8_t* gal = g - sh16;
+                        unsigned char* sb = buf + pos0 - sh16;
+                        const int nchunk = (sh16 + cnt + 15) >> 4;
+                        unsigned na = 0u;
+                        for (int c = lane; c < nchunk; c += 32) {
+                            uint4 v = __ldg(reinterpret_cast<const uint4*>(gal + 16 * c));
+                            const int lo = c == 0 ? sh16 : 0;
+                            const int hi = min(16, sh16 + cnt - 16 * c);
+                            if (lo != 0 || hi != 16) {
+                                v.x &= byte_range_mask(lo, hi);
+                                v.y &= byte_range_mask(lo - 4, hi - 4);
+                                v.z &= byte_range_mask(lo - 8, hi - 8);
+                                v.w &= byte_range_mask(lo - 12, hi - 12);
                             }
-                            if (!alnum || tl < p.min_token_length) continue;
-                            bool stop = false;
-                            if (tl <= STOP_MAXLEN) {
-                                unsigned sl = stop_hash(low, tl) & (STOP_SLOTS - 1);
-                                for (int probe = 0; probe < STOP_SLOTS; ++probe) {
-                                    const int el = c_stop[sl].len;
-                                    if (el == 0) break;
-                                    if (el == tl) {
-                                        bool eq = true;
-                                        for (int q = 0; q < tl; ++q) eq &= c_stop[sl].w[q] == (char)low[q];
-                                        if (eq) { stop = true; break; }
+                            na |= (v.x | v.y | v.z | v.w) & 0x80808080u;
+                            v.x = lower4(v.x);
+                            v.y = lower4(v.y);
+                            v.z = lower4(v.z);
+                            v.w = lower4(v.w);
+                            *reinterpret_cast<uint4*>(sb + 16 * c) = v;
+                        }
+                        if (na) flags[0] = 1;
+                        __syncwarp();
+                        // classify: one lane per byte, 32 mask bits per step
+                        const int end = pos0 + cnt;
+                        int zpos = -1;
+                        unsigned carry = 0u;
+                        for (int w = pos0 >> 5; w <= (end >> 5); ++w) {
+                            const int i = (w << 5) + lane;
+                            const bool in = i >= pos0 && i < end;
+                            const unsigned c = in ? buf[i] : 0u;
+                            unsigned pc = __shfl_up_sync(FULL, c, 1), nc = __shfl_down_sync(FULL, c, 1);
+                            if (lane == 0) pc = (i - 1 >= pos0) ? buf[i - 1] : 0u;
+                            if (lane == 31) nc = (i + 1 < end) ? buf[i + 1] : 0u;
+                            const bool cl = (c - 'a') < 26u, cd = (c - '0') < 10u;
+                            bool tc = cl || cd || c == '_';
+                            if (!tc && (c - 0x27u) <= 0x14u) {      // '\'' .. ';' holds all the Mid* characters
+                                const bool pl = (pc - 'a') < 26u, pd = (pc - '0') < 10u;
+                                const bool nl = (nc - 'a') < 26u, nd = (nc - '0') < 10u;
+                                const bool both = c == '.' || c == '\'';
+                                tc = ((both || c == ':') && pl && nl) || ((both || c == ',' || c == ';') && pd && nd);
+                            }
+                            const unsigned m = __ballot_sync(FULL, tc);
+                            const unsigned S = m & ~((m << 1) | carry);
+                            carry = m >> 31;
+                            if (lane == 0) {
+                                mask[w] = m;
+                                wcell[w] = (unsigned char)k;
+                            }
+                            if ((S >> lane) & 1u) toks[ntok + __popc(S & lt_mask)] = (unsigned short)i;
+                            ntok += __popc(S);
+                            if (!final) {
+                                const unsigned z = __ballot_sync(FULL, in && !tc && i < end - 1);
+                                if (z) zpos = (w << 5) + 31 - __clz(z);
+                            }
+                        }
+                        fill = ((end >> 5) + 1) << 5;
+                        __syncwarp();
+                        if (final) {
+                            ++k;
+                            off = 0;
+                        } else {
+                            if (zpos < 0) {              // no break in the whole piece: the variant with the larger
+                                if (defer_list) row_bad = true;          // buffer redoes the row, or gives up
+                                else if (lane == 0) flags[1] = 1;
+                                off += cnt;
+                            } else {                     // the token after the last break is redone with the next piece
+                                if (ntok > 0 && (int)toks[ntok - 1] > zpos) --ntok;
+                                off += zpos - pos0 + 1;
+                            }
+                            break;
+                        }
+                    }
+                    // ---- hash: one lane per token
+                    for (int t0 = 0; t0 < ntok && !row_bad; t0 += 32) {
+                        const int t = t0 + lane;
+                        bool newd = false, ovf = false;
+                        if (t < ntok) {
+                            const int s = toks[t];
+                            int w = s >> 5;
+                            const int kc = wcell[w];
+                            unsigned inv = ~mask[w] >> (s & 31);
+                            int e;
+                            if (inv) {
+                                e = s + __ffs(inv) - 1;
+                            } else {
+                                do inv = ~mask[++w]; while (!inv);
+                                e = (w << 5) + __ffs(inv) - 1;
+                            }
+                            const int j = c0 + kc;
+                            unsigned ph, pw, pn;
+                            if (j < TH_COLCACHE) {
+                                ph = colstate[3 * j];
+                                pw = colstate[3 * j + 1];
+                                pn = colstate[3 * j + 2];
+                            } else {
+                                Murmur pm;
+                                pm.init();
+                                const int plen = p.prepend ? prefix_len[j] : 0;
+                                for (int q = 0; q < plen; ++q) pm.push(prefix[j * TH_PREFIX + q]);
+                                ph = pm.h;
+                                pw = pm.word;
+                                pn = pm.n;
+                            }
+                            const int space_off = p.shared ? 0 : j * p.num_features;
+                            bool has_alnum = true;      // a run of '_' only is not a token
+                            if (e - s > TH_MAX_TOKEN || buf[s] == '_') {
+                                has_alnum = false;
+                                for (int q = s; q < e; ++q) has_alnum |= buf[q] != '_';
+                            }
+                            // a run longer than maxTokenLength is emitted in pieces of maxTokenLength
+                            for (int ps = s; has_alnum && ps < e; ps += TH_MAX_TOKEN) {
+                                const int plen = min(TH_MAX_TOKEN, e - ps);
+                                if (plen < p.min_token_length) continue;
+                                if (plen <= STOP_MAXLEN) {
+                                    const int q0 = ps + 16;
+                                    unsigned l0 = __funnelshift_r(bufw[q0 >> 2], bufw[(q0 >> 2) + 1], (q0 & 3) * 8);
+                                    unsigned l1 = __funnelshift_r(bufw[(q0 >> 2) + 1], bufw[(q0 >> 2) + 2], (q0 & 3) * 8);
+                                    unsigned l2 = __funnelshift_r(bufw[(q0 >> 2) + 2], bufw[(q0 >> 2) + 3], (q0 & 3) * 8);
+                                    l0 &= byte_range_mask(0, plen);
+                                    l1 &= byte_range_mask(0, plen - 4);
+                                    l2 &= byte_range_mask(0, plen - 8);
+                                    unsigned sl = stop_slot_hash(l0, l1, l2);
+                                    bool is_stop = false;
+                                    for (int probe = 0; probe < STOP_SLOTS; ++probe) {
+                                        const StopSlot se = stop[sl];
+                                        if (se.len == 0u) break;
+                                        if (se.len == (unsigned)plen && se.w0 == l0 && se.w1 == l1 && se.w2 == l2) {
+                                            is_stop = true;
+                                            break;
+                                        }
+                                        sl = (sl + 1) & (STOP_SLOTS - 1);
                                     }
-                                    sl = (sl + 1) & (STOP_SLOTS - 1);
+                                    if (is_stop) continue;
+                                }
+                                // murmur3 continued from the prefix state: the r bytes the prefix left pending are the
+                                // low bytes of the first word
+                                const int r = (int)(pn & 3u);
+                                const unsigned keep_hi = ~((1u << (8 * r)) - 1u);
+                                const int tot = r + plen, nfull = tot >> 2, tail = tot & 3;
+                                const int q0 = ps - r + 16;
+                                const int sh = (q0 & 3) * 8;
+                                const unsigned* bw = bufw + (q0 >> 2);
+                                unsigned h = ph;
+                                unsigned nxt = bw[0];
+                                for (int q = 0; q <= nfull; ++q) {
+                                    const unsigned cur = nxt;
+                                    nxt = bw[q + 1];
+                                    unsigned wd = __funnelshift_r(cur, nxt, sh);
+                                    if (q == 0) wd = (wd & keep_hi) | pw;
+                                    if (q < nfull) {
+                                        h = mix_h1(h, mix_k1(wd));
+                                    } else {
+                                        for (int b = 0; b < tail; ++b)
+                                            h = mix_h1(h, mix_k1((unsigned)(int)(signed char)((wd >> (8 * b)) & 0xffu)));
+                                    }
+                                }
+                                const unsigned hv = fmix32(h, pn + (unsigned)plen);
+                                const int bucket = p.pow2_mask >= 0 ? (int)(hv & (unsigned)p.pow2_mask)
+                                                                    : non_negative_mod(hv, p.num_features);
+                                const unsigned key = (unsigned)(space_off + bucket);
+                                emitted |= 1u << kc;
+                                // insert / count
+                                unsigned slot = (key * 0x9E3779B1u) >> (32 - tbits);
+                                for (;;) {
+                                    Slot cur = table[slot];
+                                    if (cur == EMPTY) {
+                                        cur = atomicCAS(&table[slot], EMPTY, (Slot(key) << cb) | Slot(1));
+                                        if (cur == EMPTY) {
+                                            newd = true;
+                                            break;
+                                        }
+                                    }
+                                    if ((unsigned)(cur >> cb) == key) {
+                                        const Slot old = atomicAdd(&table[slot], Slot(1));
+                                        if ((old & cmask) == cmask) ovf = true;   // the count ran into the key
+                                        break;
+                                    }
+                                    slot = (slot + 1) & (tsize - 1);
                                 }
                             }
-                            if (stop) continue;
-                            const int idx = space_off + non_negative_mod(mm.finish(), p.num_features);
-                            const int at = atomicAdd(&list_len, 1);
-                            if (at < TH_LIST_CAP) list[at] = idx;
-                            ++hits;
+                        }
+                        ndist += __popc(__ballot_sync(FULL, newd));
+                        if (__any_sync(FULL, ovf) || ndist > dist_limit) row_bad = true;
+                    }
+                    __syncwarp();
+                    if (k >= ncells || row_bad) break;
+                }
+                // ---- null indicators of this pass: no token of the cell survived (null, empty or all stop words)
+                emitted = __reduce_or_sync(FULL, emitted);
+                if (p.track_nulls && !row_bad) {
+                    bool newd = false;
+                    if (lane < ncells && !((emitted >> lane) & 1u)) {
+                        const unsigned key = (unsigned)(p.null_base + c0 + lane);
+                        unsigned slot = (key * 0x9E3779B1u) >> (32 - tbits);
+                        for (;;) {
+                            const Slot cur = atomicCAS(&table[slot], EMPTY, (Slot(key) << cb) | Slot(1));
+                            if (cur == EMPTY) {
+                                newd = true;
+                                break;
+                            }
+                            slot = (slot + 1) & (tsize - 1);
                         }
                     }
-                    emitted += __reduce_add_sync(FULL, hits);
+                    ndist += __popc(__ballot_sync(FULL, newd));
+                    if (ndist > dist_limit) row_bad = true;
                 }
+                __syncwarp();
             }
-            // null indicator of this text column: no token survived (null, empty or all stop words)
-            if (p.track_nulls && emitted == 0 && lane == 0) {
-                const int at = atomicAdd(&list_len, 1);
-                if (at < TH_LIST_CAP) list[at] = p.null_base + j;
-            }
-        }
-        __syncthreads();
-        int len = list_len;
-        if (len > TH_LIST_CAP) {
-            if (tid == 0) flags[2] = 1;
-            len = TH_LIST_CAP;
-        }
-        // ---- sort the row's hits (bitonic, padded to a power of two with INT_MAX)
-        int m = 32;
-        while (m < len) m <<= 1;
-        for (int i = len + tid; i < m; i += TH_THREADS) list[i] = 0x7fffffff;
-        __syncthreads();
-        for (int k2 = 2; k2 <= m; k2 <<= 1) {
-            for (int jj = k2 >> 1; jj > 0; jj >>= 1) {
-                for (int i = tid; i < m; i += TH_THREADS) {
-                    const int ixj = i ^ jj;
-                    if (ixj > i) {
-                        const int x = list[i], y = list[ixj];
-                        const bool up = (i & k2) == 0;
-                        if ((x > y) == up) {
-                            list[i] = y;
-                            list[ixj] = x;
-                        }
+
+            // ---- flush the row's table
+            if (row_bad) {
+                for (int i = lane; i < tsize; i += 32) table[i] = EMPTY;
+                if (lane == 0) {
+                    if (defer_list) defer_list[atomicAdd(defer_n, 1u)] = (int32_t)row;
+                    else flags[2] = 1;
+                    if (SPARSE_OUT && !defer_list) {
+                        row_start[row] = 0;
+                        row_nnz[row] = 0;
                     }
                 }
-                __syncthreads();
+                __syncwarp();
+                continue;
             }
-        }
-        // ---- run-length encode: a thread owning a run head emits (index, count)
-        const int cls = (p.nclasses > 1 && class_ids) ? class_ids[row] : 0;
-        if (!SPARSE_OUT) {
-            for (int i = tid; i < len; i += TH_THREADS) {
-                const int v = list[i];
-                if (i == 0 || list[i - 1] != v) {
-                    int e = i + 1;
-                    while (e < len && list[e] == v) ++e;
-                    const unsigned cnt = p.binary_freq && v < p.hash_width ? 1u : (unsigned)(e - i);
+            if (!SPARSE_OUT) {
+                const int cls = (p.nclasses > 1 && class_ids) ? class_ids[row] : 0;
+                for (int i = lane; i < tsize; i += 32) {
+                    const Slot sv = table[i];
+                    if (sv == EMPTY) continue;
+                    table[i] = EMPTY;
+                    const unsigned v = (unsigned)(sv >> cb);
+                    const unsigned cnt = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
                     atomicAdd(&bucket_class_sum[(int64_t)v * p.nclasses + cls], cnt);
-                    atomicAdd(&bucket_nnz[v], 1u);
                     if (cnt > 1u) {   // rare: everything beyond "present once" goes to the auxiliary arrays
+                        atomicAdd(&bucket_dup[v], cnt - 1u);
                         atomicAdd(&bucket_sq_extra[v], (unsigned long long)cnt * cnt - cnt);
-                        atomicMax(&bucket_aux[3 * (int64_t)v], cnt);          // largest frequency
-                        atomicMin(&bucket_aux[3 * (int64_t)v + 1], ~cnt);     // smallest frequency > 1, stored negated
-                        atomicAdd(&bucket_aux[3 * (int64_t)v + 2], 1u);       // rows with a frequency > 1
+                        atomicMax(&bucket_aux[3 * (int64_t)v], cnt);
+                        atomicMin(&bucket_aux[3 * (int64_t)v + 1], ~cnt);
+                        atomicAdd(&bucket_aux[3 * (int64_t)v + 2], 1u);
+                    }
+                }
+            } else {
+                // compact the kept buckets to the front of the table as (new position | value) ...
+                int kept = 0;
+                for (int i0 = 0; i0 < tsize; i0 += 32) {
+                    const Slot sv = table[i0 + lane];
+                    int np = -1;
+                    unsigned val = 0u;
+                    if (sv != EMPTY) {
+                        const unsigned v = (unsigned)(sv >> cb);
+                        np = newpos[v];
+                        val = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
+                    }
+                    const unsigned kb = __ballot_sync(FULL, np >= 0);
+                    table[i0 + lane] = EMPTY;
+                    __syncwarp();
+                    if (np >= 0) table[kept + __popc(kb & lt_mask)] = (Slot((unsigned)np) << cb) | Slot(val);
+                    kept += __popc(kb);
+                    __syncwarp();
+                }
+                // ... sort them (bitonic, the padding EMPTY sorts last) ...
+                int m = 32;
+                while (m < kept) m <<= 1;
+                for (int k2 = 2; k2 <= m; k2 <<= 1) {
+                    for (int jj = k2 >> 1; jj > 0; jj >>= 1) {
+                        for (int t = lane; t < (m >> 1); t += 32) {
+                            const int i = ((t & ~(jj - 1)) << 1) | (t & (jj - 1));
+                            const int ixj = i | jj;
+                            const Slot x = table[i], y = table[ixj];
+                            const bool up = (i & k2) == 0;
+                            if ((x > y) == up) {
+                                table[i] = y;
+                                table[ixj] = x;
+                            }
+                        }
+                        __syncwarp();
+                    }
+                }
+                // ... and write the sparse row
+                unsigned long long base = 0;
+                if (lane == 0) {
+                    base = atomicAdd(cursor, (unsigned long long)kept);
+                    row_start[row] = (int64_t)base;
+                    row_nnz[row] = kept;
+                    if ((int64_t)base + kept > capacity) flags[3] = 1;
+                }
+                base = __shfl_sync(FULL, base, 0);
+                for (int i = lane; i < kept; i += 32) {
+                    const Slot sv = table[i];
+                    table[i] = EMPTY;
+                    const int64_t at = (int64_t)base + i;
+                    if (at < capacity) {
+                        out_idx[at] = (int32_t)(sv >> cb);
+                        out_val[at] = (int32_t)(sv & cmask);
                     }
                 }
             }
-        } else {
-            // heads per thread -> block exclusive scan -> packed output (kept columns only, renumbered)
-            // contiguous chunk of the sorted list per thread, so that the packed output keeps the order
-            const int per = (len + TH_THREADS - 1) / TH_THREADS;
-            const int lo = min(len, tid * per), hi = min(len, lo + per);
-            int heads = 0;
-            for (int i = lo; i < hi; ++i) {
-                const int v = list[i];
-                if ((i == 0 || list[i - 1] != v) && newpos[v] >= 0) ++heads;
-            }
-            int incl = heads;
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t2 = __shfl_up_sync(FULL, incl, o);
-                if (lane >= o) incl += t2;
-            }
-            if (lane == 31) scan_tmp[warp] = incl;
-            __syncthreads();
-            int warp_off = 0, total = 0;
-            for (int w = 0; w < TH_WARPS; ++w) {
-                if (w < warp) warp_off += scan_tmp[w];
-                total += scan_tmp[w];
-            }
-            if (tid == 0) {
-                out_base = atomicAdd(cursor, (unsigned long long)total);
-                row_start[row] = (int64_t)out_base;
-                row_nnz[row] = total;
-                if ((int64_t)out_base + total > capacity) flags[3] = 1;
-            }
-            __syncthreads();
-            int64_t w0 = (int64_t)out_base + warp_off + incl - heads;
-            for (int i = lo; i < hi; ++i) {
-                const int v = list[i];
-                if ((i == 0 || list[i - 1] != v) && newpos[v] >= 0) {
-                    int e = i + 1;
-                    while (e < len && list[e] == v) ++e;
-                    if (w0 < capacity) {
-                        out_idx[w0] = newpos[v];
-                        out_val[w0] = p.binary_freq && v < p.hash_width ? 1 : e - i;
-                    }
-                    ++w0;
-                }
-            }
+            __syncwarp();
         }
-        __syncthreads();
     }
 }
 
 }  // namespace tmog
 
 using namespace tmog;
-
 // Snowball english_stop.txt (174 words) as loaded by Lucene's StandardAnalyzer in the reference
 // (core/src/main/scala/com/salesforce/op/utils/text/LuceneTextAnalyzer.scala:159-161)
 static const char* const kStopWords[] = {
@@ -527,7 +792,9 @@ static int upload_stop_words() {
     const int nwords = (int)(sizeof(kStopWords) / sizeof(kStopWords[0]));
     for (int i = 0; i < nwords; ++i) {
         const int len = (int)strlen(kStopWords[i]);
-        unsigned s = stop_hash((const unsigned char*)kStopWords[i], len) & (STOP_SLOTS - 1);
+        unsigned pw[3] = {0u, 0u, 0u};
+        for (int q = 0; q < len; ++q) pw[q >> 2] |= (unsigned)(unsigned char)kStopWords[i][q] << (8 * (q & 3));
+        unsigned s = stop_slot_hash(pw[0], pw[1], pw[2]) & (STOP_SLOTS - 1);
         while (table[s].len != 0) s = (s + 1) & (STOP_SLOTS - 1);
         table[s].len = (unsigned char)len;
         memcpy(table[s].w, kStopWords[i], len);
@@ -627,38 +894,157 @@ static int text_hash_common(const int64_t* col_desc, int ncols, int64_t n, const
     return upload_stop_words();
 }
 
-extern "C" int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
-                                        const int32_t* prefix_len, const int32_t* params, const uint8_t* class_ids,
-                                        uint32_t* bucket_class_sum, uint32_t* bucket_nnz, uint64_t* bucket_sq_extra,
-                                        uint32_t* bucket_aux, int32_t* flags, void* stream) {
+// scratch of the tokenise + hash entry points: two row counters, the number of deferred rows, the deferred rows
+struct ThScratch {
+    unsigned long long row_counter;
+    unsigned long long defer_counter;
+    unsigned defer_n;
+    unsigned pad[3];
+};
+
+extern "C" int tmog_text_hash_scratch_bytes(int64_t n, size_t* bytes) {
+    TMOG_REQUIRE(bytes != nullptr && n >= 0 && n < 0x7fffffffLL, "bad arguments");
+    *bytes = sizeof(ThScratch) + sizeof(int32_t) * (size_t)n;
+    return TMOG_OK;
+}
+
+struct ThArgs {
+    const TextColumn* cols;
+    int ncols;
+    int64_t n;
+    const uint8_t* prefix;
+    const int32_t* prefix_len;
     TextHashParams p;
-    if (int rc = text_hash_common(col_desc, ncols, n, prefix, prefix_len, params, &p)) return rc;
-    TMOG_REQUIRE(bucket_class_sum && bucket_nnz && bucket_sq_extra && bucket_aux && flags, "NULL output");
-    TMOG_REQUIRE(p.nclasses == 1 || class_ids != nullptr, "class_ids is NULL");
-    if (n == 0 || ncols == 0) return TMOG_OK;
-    const int grid = (int)std::min<int64_t>(n, (int64_t)sm_count() * 8);
-    text_hash_kernel<false><<<grid, TH_THREADS, 0, (cudaStream_t)stream>>>(
-        reinterpret_cast<const TextColumn*>(col_desc), ncols, n, prefix, prefix_len, p, class_ids, bucket_class_sum,
-        bucket_nnz, reinterpret_cast<unsigned long long*>(bucket_sq_extra), bucket_aux, nullptr, nullptr, nullptr, nullptr,
-        nullptr, nullptr, 0, flags);
+    const uint8_t* class_ids;
+    uint32_t *class_sum, *dup;
+    unsigned long long* sq_extra;
+    uint32_t* aux;
+    const int32_t* newpos;
+    int64_t* row_start;
+    int32_t *row_nnz, *out_idx, *out_val;
+    unsigned long long* cursor;
+    int64_t capacity;
+    int32_t* flags;
+    ThScratch* scratch;
+    cudaStream_t stream;
+};
+
+template <typename Slot, int T, int TB, int WARPS, bool SPARSE_OUT>
+static int th_launch(const ThArgs& a, bool deferred_pass) {
+    auto kernel = text_hash_kernel<Slot, T, TB, WARPS, SPARSE_OUT>;
+    const size_t smem = STOP_SLOTS * sizeof(StopSlot) + TH_COLCACHE * 12 + 32 + (size_t)WARPS * ThLayout<Slot, T, TB>::BYTES;
+    TMOG_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, WARPS * 32, smem));
+    TMOG_REQUIRE(per_sm >= 1, "text hash kernel does not fit an SM");
+    int64_t grid = (int64_t)sm_count() * per_sm;
+    if (!deferred_pass) grid = std::max<int64_t>(1, std::min<int64_t>(grid, (a.n + WARPS - 1) / WARPS));
+    int32_t* list = reinterpret_cast<int32_t*>(a.scratch + 1);
+    kernel<<<(int)grid, WARPS * 32, smem, a.stream>>>(
+        a.cols, a.ncols, a.n, a.prefix, a.prefix_len, a.p, a.class_ids,
+        deferred_pass ? list : nullptr, deferred_pass ? &a.scratch->defer_n : nullptr,
+        deferred_pass ? &a.scratch->defer_counter : &a.scratch->row_counter,
+        deferred_pass ? nullptr : list, deferred_pass ? nullptr : &a.scratch->defer_n,
+        a.class_sum, a.dup, a.sq_extra, a.aux, a.newpos, a.row_start, a.row_nnz, a.out_idx, a.out_val, a.cursor,
+        a.capacity, a.flags);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
+}
+
+// fast variant with packed 32-bit slots when the key leaves >= 8 bits for the count, else 64-bit slots; then the rows
+// either of them deferred, with a table that takes most of the shared memory of an SM
+template <bool SPARSE_OUT>
+static int th_run(ThArgs& a) {
+    TMOG_CUDA(cudaMemsetAsync(a.scratch, 0, sizeof(ThScratch), a.stream));
+    const int64_t max_key = (int64_t)a.p.null_base + a.ncols;      // keys (and new positions) are < max_key
+    int key_bits = 1;
+    while ((1ll << key_bits) - 1 <= max_key) ++key_bits;
+    if (key_bits <= 24) {
+        a.p.count_bits = 32 - key_bits;
+        if (int rc = th_launch<unsigned, 2048, 2048, 8, SPARSE_OUT>(a, false)) return rc;
+    } else {
+        a.p.count_bits = 32;
+        if (int rc = th_launch<unsigned long long, 1024, 2048, 8, SPARSE_OUT>(a, false)) return rc;
+    }
+    a.p.count_bits = 32;
+    return th_launch<unsigned long long, 16384, 4096, 1, SPARSE_OUT>(a, true);
+}
+
+static int text_hash_common(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
+                            const int32_t* prefix_len, const int32_t* params, void* scratch, size_t scratch_bytes,
+                            ThArgs* a) {
+    TMOG_REQUIRE(ncols >= 0 && n >= 0 && n < 0x7fffffffLL, "bad shape");
+    TMOG_REQUIRE(col_desc && prefix && prefix_len && params, "NULL argument");
+    TextHashParams& p = a->p;
+    p.num_features = params[0];
+    p.shared = params[1];
+    p.binary_freq = params[2];
+    p.min_token_length = params[3];
+    p.track_nulls = params[4];
+    p.prepend = params[5];
+    p.null_base = params[6];
+    p.nclasses = params[7];
+    TMOG_REQUIRE(p.num_features > 0 && p.num_features <= 10000000,
+                 "requirement failed: numFeatures must be in (0, 10000000], got %d", p.num_features);
+    TMOG_REQUIRE(p.nclasses >= 1 && p.nclasses <= 255, "nclasses must be in [1, 255]");
+    const int64_t hw = p.shared ? p.num_features : (int64_t)p.num_features * ncols;
+    TMOG_REQUIRE(hw + ncols < 0x7fffffffLL, "hash block too wide");
+    p.hash_width = (int)hw;
+    TMOG_REQUIRE(p.null_base >= p.hash_width && (int64_t)p.null_base + ncols < 0x7fffffffLL,
+                 "null_base must not overlap the hash block");
+    p.pow2_mask = (p.num_features & (p.num_features - 1)) == 0 ? p.num_features - 1 : -1;
+    p.count_bits = 32;
+    size_t need = 0;
+    if (int rc = tmog_text_hash_scratch_bytes(n, &need)) return rc;
+    TMOG_REQUIRE(scratch != nullptr && scratch_bytes >= need, "scratch too small: %zu bytes needed", need);
+    TMOG_REQUIRE((reinterpret_cast<uintptr_t>(scratch) & 7u) == 0, "scratch must be 8-byte aligned");
+    a->cols = reinterpret_cast<const TextColumn*>(col_desc);
+    a->ncols = ncols;
+    a->n = n;
+    a->prefix = prefix;
+    a->prefix_len = prefix_len;
+    a->scratch = reinterpret_cast<ThScratch*>(scratch);
+    return upload_stop_words();
+}
+
+extern "C" int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
+                                        const int32_t* prefix_len, const int32_t* params, const uint8_t* class_ids,
+                                        uint32_t* bucket_class_sum, uint32_t* bucket_dup, uint64_t* bucket_sq_extra,
+                                        uint32_t* bucket_aux, int32_t* flags, void* scratch, size_t scratch_bytes,
+                                        void* stream) {
+    ThArgs a = {};
+    if (int rc = text_hash_common(col_desc, ncols, n, prefix, prefix_len, params, scratch, scratch_bytes, &a)) return rc;
+    TMOG_REQUIRE(bucket_class_sum && bucket_dup && bucket_sq_extra && bucket_aux && flags, "NULL output");
+    TMOG_REQUIRE(a.p.nclasses == 1 || class_ids != nullptr, "class_ids is NULL");
+    if (n == 0 || ncols == 0) return TMOG_OK;
+    a.class_ids = class_ids;
+    a.class_sum = bucket_class_sum;
+    a.dup = bucket_dup;
+    a.sq_extra = reinterpret_cast<unsigned long long*>(bucket_sq_extra);
+    a.aux = bucket_aux;
+    a.flags = flags;
+    a.stream = (cudaStream_t)stream;
+    return th_run<false>(a);
 }
 
 extern "C" int tmog_text_hash_transform_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
                                             const int32_t* prefix_len, const int32_t* params, const int32_t* newpos,
                                             int64_t* row_start, int32_t* row_nnz, int32_t* out_idx, int32_t* out_val,
-                                            uint64_t* cursor, int64_t capacity, int32_t* flags, void* stream) {
-    TextHashParams p;
-    if (int rc = text_hash_common(col_desc, ncols, n, prefix, prefix_len, params, &p)) return rc;
+                                            uint64_t* cursor, int64_t capacity, int32_t* flags, void* scratch,
+                                            size_t scratch_bytes, void* stream) {
+    ThArgs a = {};
+    if (int rc = text_hash_common(col_desc, ncols, n, prefix, prefix_len, params, scratch, scratch_bytes, &a)) return rc;
     TMOG_REQUIRE(newpos && row_start && row_nnz && cursor && flags, "NULL argument");
     TMOG_REQUIRE(capacity >= 0 && (capacity == 0 || (out_idx && out_val)), "NULL output");
     if (n == 0 || ncols == 0) return TMOG_OK;
-    const int grid = (int)std::min<int64_t>(n, (int64_t)sm_count() * 8);
-    text_hash_kernel<true><<<grid, TH_THREADS, 0, (cudaStream_t)stream>>>(
-        reinterpret_cast<const TextColumn*>(col_desc), ncols, n, prefix, prefix_len, p, nullptr, nullptr, nullptr,
-        nullptr, nullptr, newpos, row_start, row_nnz, out_idx, out_val, reinterpret_cast<unsigned long long*>(cursor), capacity,
-        flags);
-    TMOG_LAUNCH_CHECK();
-    return TMOG_OK;
+    a.newpos = newpos;
+    a.row_start = row_start;
+    a.row_nnz = row_nnz;
+    a.out_idx = out_idx;
+    a.out_val = out_val;
+    a.cursor = reinterpret_cast<unsigned long long*>(cursor);
+    a.capacity = capacity;
+    a.flags = flags;
+    a.stream = (cudaStream_t)stream;
+    return th_run<true>(a);
 }

@@ -484,17 +484,19 @@ class SmartTextVectorizerModel(OpModel):
             params[7] = ncls
             w = lay.hash_width + len(lay.hash_idx)
             class_sum = torch.zeros(w * ncls, dtype=torch.int32, device="cuda")
-            nnz = torch.zeros(w, dtype=torch.int32, device="cuda")
+            dup = torch.zeros(w, dtype=torch.int32, device="cuda")
             extra = torch.zeros(w, dtype=torch.int64, device="cuda")
+            scratch = _hash_scratch(n)
             aux = torch.zeros(3 * w, dtype=torch.int32, device="cuda")
             flags = torch.zeros(4, dtype=torch.int32, device="cuda")
             desc = _col_desc(sub)
             L.call("tmog_text_hash_stats_dev", desc.data_ptr(), len(lay.hash_idx), n, d_prefix.data_ptr(),
-                   d_plen.data_ptr(), params.ctypes.data, ids.data_ptr(), class_sum.data_ptr(), nnz.data_ptr(),
-                   extra.data_ptr(), aux.data_ptr(), flags.data_ptr(), R.stream())
+                   d_plen.data_ptr(), params.ctypes.data, ids.data_ptr(), class_sum.data_ptr(), dup.data_ptr(),
+                   extra.data_ptr(), aux.data_ptr(), flags.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
             _check_hash_flags(flags)
             cs = (class_sum.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(w, ncls).astype(np.float64)
-            nz = (nnz.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).astype(np.float64)
+            # rows holding an index = sum of its term frequencies - (tf - 1) of the rows with tf > 1
+            nz = cs.sum(axis=1) - (dup.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).astype(np.float64)
             ex = extra.cpu().numpy().astype(np.float64)
             ax = (aux.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(w, 3)
             if not self.shouldTrackNulls:
@@ -559,13 +561,15 @@ class SmartTextVectorizerModel(OpModel):
         row_nnz = torch.empty(n, dtype=torch.int32, device="cuda")
         flags = torch.zeros(4, dtype=torch.int32, device="cuda")
         cursor = torch.zeros(1, dtype=torch.int64, device="cuda")
+        scratch = _hash_scratch(n)
         nz = getattr(self, "_hash_nnz", None)
         if same_batch and nz is not None:      # exact size known from the fit pass over the same rows
             capacity = int(nz[newpos[:len(nz)] >= 0].sum())
         else:                                  # sizing pass
             L.call("tmog_text_hash_transform_dev", desc.data_ptr(), len(lay.hash_idx), n, d_prefix.data_ptr(),
                    d_plen.data_ptr(), params.ctypes.data, d_newpos.data_ptr(), row_start.data_ptr(),
-                   row_nnz.data_ptr(), None, None, cursor.data_ptr(), 0, flags.data_ptr(), R.stream())
+                   row_nnz.data_ptr(), None, None, cursor.data_ptr(), 0, flags.data_ptr(), scratch.data_ptr(),
+                   scratch.numel(), R.stream())
             capacity = int(cursor.item())
             cursor.zero_()
             flags.zero_()
@@ -573,9 +577,17 @@ class SmartTextVectorizerModel(OpModel):
         val = torch.empty(max(capacity, 1), dtype=torch.int32, device="cuda")
         L.call("tmog_text_hash_transform_dev", desc.data_ptr(), len(lay.hash_idx), n, d_prefix.data_ptr(),
                d_plen.data_ptr(), params.ctypes.data, d_newpos.data_ptr(), row_start.data_ptr(), row_nnz.data_ptr(),
-               idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), capacity, flags.data_ptr(), R.stream())
+               idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), capacity, flags.data_ptr(), scratch.data_ptr(),
+               scratch.numel(), R.stream())
         _check_hash_flags(flags)
         return SparseRowsPart(row_start, row_nnz, idx, val, out_width)
+
+
+def _hash_scratch(n: int) -> torch.Tensor:
+    import ctypes
+    need = ctypes.c_size_t(0)
+    L.call("tmog_text_hash_scratch_bytes", n, ctypes.byref(need))
+    return torch.empty(max(need.value, 8), dtype=torch.uint8, device="cuda")
 
 
 def _check_hash_flags(flags: torch.Tensor) -> None:
@@ -583,9 +595,9 @@ def _check_hash_flags(flags: torch.Tensor) -> None:
     if f[0]:
         raise ValueError("non-ASCII text met: Lucene's Unicode word-break rules are restated for ASCII only")
     if f[1]:
-        raise ValueError("a text cell holds more than 512 tokens: beyond the GPU tokenizer's per-cell capacity")
+        raise ValueError("a run of letters / digits longer than ~4000 bytes: beyond the GPU tokenizer's text buffer")
     if f[2]:
-        raise ValueError("a row holds more than 4096 hashed tokens: beyond the GPU path's per-row capacity")
+        raise ValueError("a row holds more than ~12000 distinct hashed tokens: beyond the GPU path's per-row table")
     if f[3]:
         raise RuntimeError("sparse output capacity exceeded")
 
