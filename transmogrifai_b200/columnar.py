@@ -261,6 +261,11 @@ class TextBlock:
         return TextBlock(list(names), type_name, data, offsets, valid, n)
 
 
+def _is_identity(keep, width: int) -> bool:
+    k = np.asarray(keep)
+    return len(k) == width and bool((k == np.arange(width)).all())
+
+
 @dataclass
 class DensePart:
     data: torch.Tensor                   # [n, width] float64 row-major (may be a column slice of a wider block)
@@ -285,12 +290,12 @@ class LazyDensePart:
         self._data = None
 
     def materialize(self, keep=None) -> torch.Tensor:
-        if keep is None or list(keep) == list(range(self.width)):
+        if keep is None or _is_identity(keep, self.width):
             return self.data
         if self._data is not None:
-            idx = torch.as_tensor(list(keep), device=self._data.device)
+            idx = torch.as_tensor(np.asarray(keep, dtype=np.int64), device=self._data.device)
             return self._data.index_select(1, idx)
-        return self._materialize(list(keep))
+        return self._materialize(np.asarray(keep, dtype=np.int64))
 
     @property
     def data(self) -> torch.Tensor:
@@ -348,11 +353,11 @@ class LazyOneHotPart:
         self._part = None
 
     def materialize(self, keep=None) -> OneHotPart:
-        if keep is None or list(keep) == list(range(self.width)):
+        if keep is None or _is_identity(keep, self.width):
             if self._part is None:
                 self._part = self._materialize(None)
             return self._part
-        return self._materialize(list(keep))
+        return self._materialize(np.asarray(keep, dtype=np.int64))
 
     @property
     def data(self):
@@ -397,11 +402,11 @@ class LazyPart:
         self._part = None
 
     def materialize(self, keep=None):
-        if keep is None or list(keep) == list(range(self.width)):
+        if keep is None or _is_identity(keep, self.width):
             if self._part is None:
                 self._part = self._materialize(None)
             return self._part
-        return self._materialize(list(keep))
+        return self._materialize(np.asarray(keep, dtype=np.int64))
 
     def to_scipy(self):
         return self.materialize(None).to_scipy()

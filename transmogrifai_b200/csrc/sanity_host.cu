@@ -124,31 +124,41 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
                  max_cramers = params[4], max_rule_conf = params[5], min_rule_support = params[6];
     const bool remove_feature_group = params[7] != 0.0, protect_text_shared_hash = params[8] != 0.0;
 
-    // makeColumnStatistics: max |corr| and max Cramer's V per parent feature, NaNs skipped, folded from 0.0
-    std::map<int, double> corr_parent, cramers_parent;
+    // makeColumnStatistics: max |corr| and max Cramer's V per parent feature, NaNs skipped, folded from 0.0.  Parent and
+    // group ids are small dense integers, so the two maps are arrays (NaN = no entry).
+    int max_parent = -1, max_group = -1;
+    for (int k = 0; k < parent_offsets[d]; ++k) {
+        TMOG_REQUIRE(parent_ids[k] >= 0, "negative parent id");
+        max_parent = std::max(max_parent, parent_ids[k]);
+    }
+    for (int i = 0; i < d; ++i) max_group = std::max(max_group, group_id[i]);
+    const double none = nan("");
+    std::vector<double> corr_parent((size_t)max_parent + 1, none), cramers_parent((size_t)max_parent + 1, none);
     for (int i = 0; i < d; ++i) {
         if (corr_pos[i] >= 0 && corr_label) {
             const double c = corr_label[corr_pos[i]];
+            const double ac = isnan(c) ? 0.0 : fabs(c);
             for (int k = parent_offsets[i]; k < parent_offsets[i + 1]; ++k) {
-                double& slot = corr_parent.emplace(parent_ids[k], 0.0).first->second;
-                if (!isnan(c)) slot = std::max(slot, fabs(c));
+                double& slot = corr_parent[parent_ids[k]];
+                slot = isnan(slot) ? ac : std::max(slot, ac);
             }
         }
         // a column is in cramersVMap iff it belongs to a categorical group (rule_count >= 0); its V may be NaN.
         // parentMap (.toMap) keeps the LAST parent of a multi-parent column.
         if (rule_count[i] >= 0 && parent_offsets[i + 1] > parent_offsets[i]) {
             const int last = parent_ids[parent_offsets[i + 1] - 1];
-            double& slot = cramers_parent.emplace(last, 0.0).first->second;
-            if (!isnan(cramers_v[i])) slot = std::max(slot, fabs(cramers_v[i]));
+            const double av = isnan(cramers_v[i]) ? 0.0 : fabs(cramers_v[i]);
+            double& slot = cramers_parent[last];
+            slot = isnan(slot) ? av : std::max(slot, av);
         }
     }
     // getFeaturesToDrop: groups flagged by the association-rule check
-    std::vector<int> flagged_groups;
+    std::vector<char> group_flagged((size_t)max_group + 1, 0);
     for (int i = 0; i < d; ++i) {
         if (group_id[i] < 0) continue;
         for (int k = 0; k < std::max(rule_count[i], 0); ++k)
             if (rule_conf[2 * i + k] > max_rule_conf && rule_support[2 * i + k] > min_rule_support) {
-                flagged_groups.push_back(group_id[i]);
+                group_flagged[group_id[i]] = 1;
                 break;
             }
     }
@@ -174,16 +184,13 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
                 r |= 32u;
                 break;
             }
-        if (group_id[i] >= 0 &&
-            std::find(flagged_groups.begin(), flagged_groups.end(), group_id[i]) != flagged_groups.end())
-            r |= 64u;
+        if (group_id[i] >= 0 && group_flagged[group_id[i]]) r |= 64u;
         // parent-level values: max over the column's parents that have an entry
         double pc = nan(""), pv = nan("");
         for (int k = parent_offsets[i]; k < parent_offsets[i + 1]; ++k) {
-            auto a = corr_parent.find(parent_ids[k]);
-            if (a != corr_parent.end()) pc = isnan(pc) ? a->second : std::max(pc, a->second);
-            auto b = cramers_parent.find(parent_ids[k]);
-            if (b != cramers_parent.end()) pv = isnan(pv) ? b->second : std::max(pv, b->second);
+            const double a = corr_parent[parent_ids[k]], b = cramers_parent[parent_ids[k]];
+            if (!isnan(a)) pc = isnan(pc) ? a : std::max(pc, a);
+            if (!isnan(b)) pv = isnan(pv) ? b : std::max(pv, b);
         }
         if (parent_corr_out) parent_corr_out[i] = pc;
         if (parent_cramers_out) parent_cramers_out[i] = pv;

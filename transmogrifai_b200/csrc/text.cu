@@ -17,6 +17,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <type_traits>
 #include <vector>
 
 #include "common.cuh"
@@ -320,13 +321,101 @@ __device__ __forceinline__ unsigned byte_range_mask(int lo, int hi) {
 // bytes of one warp's working set in shared memory
 template <typename Slot, int T, int TB>
 struct ThLayout {
+    using Tok = typename std::conditional<(TB <= 2048), unsigned short, unsigned>::type;
     static constexpr int BUF = 0;                               // 16 slack + TB text + 32 slack
-    static constexpr int MASK = BUF + 16 + TB + 32;             // (TB / 32 + 1) words, the last one stays zero
-    static constexpr int TOKS = MASK + ((TB / 32 + 1) * 4 + 15) / 16 * 16;   // TB / 2 token starts (u16)
-    static constexpr int WCELL = TOKS + TB;                     // cell of every 32-byte window (u8)
-    static constexpr int TABLE = WCELL + (TB / 32 + 15) / 16 * 16;
+    static constexpr int MASK = BUF + 16 + TB + 32;             // TB / 32 words: bit b of word w = byte 32 w + b
+    static constexpr int TOKS = MASK + (TB / 32 * 4 + 15) / 16 * 16;         // TB / 2 token records
+    static constexpr int WCELL = TOKS + TB / 2 * (int)sizeof(Tok);           // cell of every 16 bytes (u8)
+    static constexpr int TABLE = WCELL + (TB / 16 + 15) / 16 * 16;
     static constexpr int BYTES = TABLE + T * (int)sizeof(Slot);
 };
+
+// stop-word probe of the staged (lower-cased) token [ps, ps + plen), plen <= STOP_MAXLEN
+__device__ __forceinline__ bool th_is_stop(const StopSlot* stop, const unsigned* bufw, int ps, int plen) {
+    const int q0 = ps + 16, sh = (q0 & 3) * 8;
+    const unsigned* bw = bufw + (q0 >> 2);
+    const unsigned a = bw[0], b = bw[1], c = bw[2], d = bw[3];
+    const unsigned l0 = __funnelshift_r(a, b, sh) & byte_range_mask(0, plen);
+    const unsigned l1 = __funnelshift_r(b, c, sh) & byte_range_mask(0, plen - 4);
+    const unsigned l2 = __funnelshift_r(c, d, sh) & byte_range_mask(0, plen - 8);
+    unsigned sl = stop_slot_hash(l0, l1, l2);
+    for (int probe = 0; probe < STOP_SLOTS; ++probe) {
+        const StopSlot se = stop[sl];
+        if (se.len == 0u) return false;
+        if (se.len == (unsigned)plen && se.w0 == l0 && se.w1 == l1 && se.w2 == l2) return true;
+        sl = (sl + 1) & (STOP_SLOTS - 1);
+    }
+    return false;
+}
+
+// murmur3 of "<prefix><token>" continued from the state (ph, pw, pn) after the prefix: the r = pn & 3 bytes the prefix
+// left pending are the low bytes of the first word; the token is read from the staged text as unaligned words
+__device__ __forceinline__ unsigned th_hash_piece(const unsigned* bufw, int ps, int plen, unsigned ph, unsigned pw,
+                                                  unsigned pn) {
+    const int r = (int)(pn & 3u);
+    const unsigned keep_hi = ~((1u << (8 * r)) - 1u);
+    const int tot = r + plen, nfull = tot >> 2, tail = tot & 3;
+    const int q0 = ps - r + 16, sh = (q0 & 3) * 8;
+    const unsigned* bw = bufw + (q0 >> 2);
+    unsigned h = ph, nxt = bw[0];
+    for (int q = 0; q < nfull; ++q) {
+        const unsigned cur = nxt;
+        nxt = bw[q + 1];
+        unsigned wd = __funnelshift_r(cur, nxt, sh);
+        if (q == 0) wd = (wd & keep_hi) | pw;
+        h = mix_h1(h, mix_k1(wd));
+    }
+    unsigned wd = __funnelshift_r(nxt, bw[nfull + 1], sh);
+    if (nfull == 0) wd = (wd & keep_hi) | pw;
+    // the (< 4) bytes left are mixed one by one, sign-extended (Spark's legacy hashUnsafeBytes)
+    if (tail > 0) h = mix_h1(h, mix_k1((unsigned)(int)(signed char)(wd & 0xffu)));
+    if (tail > 1) h = mix_h1(h, mix_k1((unsigned)(int)(signed char)((wd >> 8) & 0xffu)));
+    if (tail > 2) h = mix_h1(h, mix_k1((unsigned)(int)(signed char)((wd >> 16) & 0xffu)));
+    return fmix32(h, pn + (unsigned)plen);
+}
+
+__device__ __forceinline__ void th_col_state(const unsigned* colstate, const uint8_t* prefix, const int* prefix_len,
+                                             const TextHashParams& p, int j, unsigned& ph, unsigned& pw, unsigned& pn) {
+    if (j < TH_COLCACHE) {
+        ph = colstate[3 * j];
+        pw = colstate[3 * j + 1];
+        pn = colstate[3 * j + 2];
+    } else {
+        Murmur pm;
+        pm.init();
+        const int plen = p.prepend ? prefix_len[j] : 0;
+        for (int q = 0; q < plen; ++q) pm.push(prefix[j * TH_PREFIX + q]);
+        ph = pm.h;
+        pw = pm.word;
+        pn = pm.n;
+    }
+}
+
+// count `key` in the row's table (1 << tbits slots in use, the count in the low cb bits of a slot)
+template <typename Slot>
+__device__ __forceinline__ void th_insert(Slot* table, int tbits, int cb, unsigned key, bool& newd, bool& ovf) {
+    constexpr Slot EMPTY = SlotTraits<Slot>::EMPTY;
+    const Slot cmask = (Slot(1) << cb) - Slot(1);
+    const unsigned tmask = (1u << tbits) - 1u;
+    unsigned slot = (key * 0x9E3779B1u) >> (32 - tbits);
+    for (unsigned probe = 0; probe <= tmask; ++probe) {
+        Slot cur = table[slot];
+        if (cur == EMPTY) {
+            cur = atomicCAS(&table[slot], EMPTY, (Slot(key) << cb) | Slot(1));
+            if (cur == EMPTY) {
+                newd = true;
+                return;
+            }
+        }
+        if ((unsigned)(cur >> cb) == key) {
+            const Slot old = atomicAdd(&table[slot], Slot(1));
+            if ((old & cmask) == cmask) ovf = true;       // the count ran into the key
+            return;
+        }
+        slot = (slot + 1) & tmask;
+    }
+    ovf = true;                                           // table full
+}
 
 // flags: [0] non-ASCII byte met, [1] a run of token characters longer than the text buffer, [2] a row has more
 //        distinct buckets than the large table holds, [3] sparse output capacity exceeded
@@ -357,7 +446,10 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
     unsigned char* buf = wbase + L::BUF + 16;                      // text; buf[-16 ..) and (.. TB + 32) are slack
     const unsigned* bufw = reinterpret_cast<const unsigned*>(wbase + L::BUF);
     unsigned* mask = reinterpret_cast<unsigned*>(wbase + L::MASK);
-    unsigned short* toks = reinterpret_cast<unsigned short*>(wbase + L::TOKS);
+    using Tok = typename L::Tok;
+    constexpr int SB = TB <= 2048 ? 11 : 12;            // bits of a buffer position in a token record
+    static_assert(TB == 2048 || TB == 4096, "token records are packed for these two buffer sizes");
+    Tok* toks = reinterpret_cast<Tok*>(wbase + L::TOKS);
     unsigned char* wcell = wbase + L::WCELL;
     Slot* table = reinterpret_cast<Slot*>(wbase + L::TABLE);
 
@@ -434,8 +526,10 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 int k = 0;
                 int64_t off = 0;             // bytes of cell k already consumed (cells longer than the buffer)
                 for (;;) {
-                    int fill = 0, ntok = 0;
-                    // ---- stage + classify as many cells as the buffer holds
+                    // ---- stage as many cells as the buffer holds: 16-byte chunks, global and shared addresses
+                    //      congruent mod 16; every byte of [0, fill) that is not a cell byte is zero
+                    int fill = 0;
+                    int piece_pos0 = -1, piece_cnt = 0;      // set when the buffer holds one piece of a long cell
                     while (k < ncells) {
                         const int64_t len = __shfl_sync(FULL, my_len, k);
                         const int64_t rem = len - off;
@@ -446,101 +540,148 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                         }
                         const uint8_t* g = reinterpret_cast<const uint8_t*>(
                                                __shfl_sync(FULL, reinterpret_cast<unsigned long long>(my_ptr), k)) + off;
-                        const int a32 = (int)(reinterpret_cast<uintptr_t>(g) & 31u);
-                        bool final = true;
+                        const int sh16 = (int)(reinterpret_cast<uintptr_t>(g) & 15u);
                         int cnt;
-                        if (fill + a32 + rem + 1 <= TB) {
+                        if (fill + sh16 + rem + 1 <= TB) {
                             cnt = (int)rem;
                         } else if (fill > 0) {
                             break;                       // hash what is staged, then come back with an empty buffer
                         } else {
-                            cnt = TB - 33;               // a piece of a long cell
-                            final = false;
+                            cnt = TB - 17;               // a piece of a long cell
+                            piece_pos0 = sh16;
+                            piece_cnt = cnt;
                         }
-                        // stage: 16-byte chunks, global and shared addresses congruent mod 32
-                        const int sh16 = a32 & 15;
-                        const int pos0 = fill + a32;
                         const uint8_t* gal = g - sh16;
-                        unsigned char* sb = buf + pos0 - sh16;
-                        const int nchunk = (sh16 + cnt + 15) >> 4;
+                        unsigned char* sb = buf + fill;
+                        const int nchunk = (sh16 + cnt + 16) >> 4;       // through the zero byte after the cell
                         unsigned na = 0u;
                         for (int c = lane; c < nchunk; c += 32) {
-                            uint4 v = __ldg(reinterpret_cast<const uint4*>(gal + 16 * c));
                             const int lo = c == 0 ? sh16 : 0;
                             const int hi = min(16, sh16 + cnt - 16 * c);
-                            if (lo != 0 || hi != 16) {
-                                v.x &= byte_range_mask(lo, hi);
-                                v.y &= byte_range_mask(lo - 4, hi - 4);
-                                v.z &= byte_range_mask(lo - 8, hi - 8);
-                                v.w &= byte_range_mask(lo - 12, hi - 12);
+                            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                            if (hi > 0) {
+                                v = __ldg(reinterpret_cast<const uint4*>(gal + 16 * c));
+                                if (lo != 0 || hi != 16) {
+                                    v.x &= byte_range_mask(lo, hi);
+                                    v.y &= byte_range_mask(lo - 4, hi - 4);
+                                    v.z &= byte_range_mask(lo - 8, hi - 8);
+                                    v.w &= byte_range_mask(lo - 12, hi - 12);
+                                }
+                                na |= (v.x | v.y | v.z | v.w) & 0x80808080u;
+                                v.x = lower4(v.x);
+                                v.y = lower4(v.y);
+                                v.z = lower4(v.z);
+                                v.w = lower4(v.w);
                             }
-                            na |= (v.x | v.y | v.z | v.w) & 0x80808080u;
-                            v.x = lower4(v.x);
-                            v.y = lower4(v.y);
-                            v.z = lower4(v.z);
-                            v.w = lower4(v.w);
                             *reinterpret_cast<uint4*>(sb + 16 * c) = v;
+                            wcell[(fill >> 4) + c] = (unsigned char)k;
                         }
                         if (na) flags[0] = 1;
-                        __syncwarp();
-                        // classify: one lane per byte, 32 mask bits per step
-                        const int end = pos0 + cnt;
-                        int zpos = -1;
-                        unsigned carry = 0u;
-                        for (int w = pos0 >> 5; w <= (end >> 5); ++w) {
-                            const int i = (w << 5) + lane;
-                            const bool in = i >= pos0 && i < end;
-                            const unsigned c = in ? buf[i] : 0u;
-                            unsigned pc = __shfl_up_sync(FULL, c, 1), nc = __shfl_down_sync(FULL, c, 1);
-                            if (lane == 0) pc = (i - 1 >= pos0) ? buf[i - 1] : 0u;
-                            if (lane == 31) nc = (i + 1 < end) ? buf[i + 1] : 0u;
-                            const bool cl = (c - 'a') < 26u, cd = (c - '0') < 10u;
-                            bool tc = cl || cd || c == '_';
-                            if (!tc && (c - 0x27u) <= 0x14u) {      // '\'' .. ';' holds all the Mid* characters
-                                const bool pl = (pc - 'a') < 26u, pd = (pc - '0') < 10u;
-                                const bool nl = (nc - 'a') < 26u, nd = (nc - '0') < 10u;
-                                const bool both = c == '.' || c == '\'';
-                                tc = ((both || c == ':') && pl && nl) || ((both || c == ',' || c == ';') && pd && nd);
-                            }
-                            const unsigned m = __ballot_sync(FULL, tc);
-                            const unsigned S = m & ~((m << 1) | carry);
-                            carry = m >> 31;
-                            if (lane == 0) {
-                                mask[w] = m;
-                                wcell[w] = (unsigned char)k;
-                            }
-                            if ((S >> lane) & 1u) toks[ntok + __popc(S & lt_mask)] = (unsigned short)i;
+                        fill += nchunk << 4;
+                        if (piece_pos0 >= 0) break;
+                        ++k;
+                        off = 0;
+                    }
+                    __syncwarp();
+
+                    // ---- classify: four bytes per lane (SWAR), 128 mask bits per step; token starts are listed
+                    int ntok = 0;
+                    {
+                        unsigned carry = 0u;         // token bit of the byte before the window
+                        const int nwin = (fill + 127) >> 7;
+                        for (int w = 0; w < nwin; ++w) {
+                            const unsigned* bp = bufw + 4 + (w << 5) + lane;
+                            const unsigned W = bp[0];
+                            const unsigned plast = bp[-1] >> 24, nfirst = bp[1] & 0xffu;
+                            const unsigned h7 = W & 0x7f7f7f7fu, ascii = ~W & 0x80808080u;
+                            // bit 7 of (h7 + (0x80 - x) * 0x01010101) is set iff the byte is >= x
+                            const unsigned fl = (h7 + 0x1f1f1f1fu) & ~(h7 + 0x05050505u) & ascii;     // 'a' .. 'z'
+                            const unsigned fd = (h7 + 0x50505050u) & ~(h7 + 0x46464646u) & ascii;     // '0' .. '9'
+                            // bit 7 of ((h7 ^ c) + 0x7f) is set iff the byte differs from c
+                            const unsigned ne_us = (h7 ^ 0x5f5f5f5fu) + 0x7f7f7f7fu;
+                            const unsigned ne_dot = (h7 ^ 0x2e2e2e2eu) + 0x7f7f7f7fu;
+                            const unsigned ne_apo = (h7 ^ 0x27272727u) + 0x7f7f7f7fu;
+                            const unsigned ne_col = (h7 ^ 0x3a3a3a3au) + 0x7f7f7f7fu;
+                            const unsigned ne_com = (h7 ^ 0x2c2c2c2cu) + 0x7f7f7f7fu;
+                            const unsigned ne_sem = (h7 ^ 0x3b3b3b3bu) + 0x7f7f7f7fu;
+                            const unsigned mid_l = ~(ne_dot & ne_apo & ne_col);              // MidLetter | MidNumLet | '
+                            const unsigned mid_n = ~(ne_dot & ne_apo & ne_com & ne_sem);     // MidNum | MidNumLet | '
+                            const unsigned pl = (plast - 'a') < 26u ? 0x80u : 0u, pd = (plast - '0') < 10u ? 0x80u : 0u;
+                            const unsigned nl = (nfirst - 'a') < 26u ? 0x80000000u : 0u;
+                            const unsigned nd = (nfirst - '0') < 10u ? 0x80000000u : 0u;
+                            const unsigned joined = (mid_l & ((fl << 8) | pl) & ((fl >> 8) | nl)) |
+                                                    (mid_n & ((fd << 8) | pd) & ((fd >> 8) | nd));
+                            unsigned tcf = (fl | fd | ((~ne_us | joined) & ascii)) & 0x80808080u;
+                            if ((((w << 5) + lane) << 2) >= fill) tcf = 0u;
+                            // bits 7, 15, 23, 31 -> a nibble, placed by lane; eight lanes make a mask word
+                            const unsigned nib = (((tcf >> 7) * 0x00204081u) >> 21) & 0xfu;
+                            const unsigned mine = nib << ((lane & 7) << 2);
+                            const int q = lane >> 3;
+                            uint4 m;
+                            m.x = __reduce_or_sync(FULL, q == 0 ? mine : 0u);
+                            m.y = __reduce_or_sync(FULL, q == 1 ? mine : 0u);
+                            m.z = __reduce_or_sync(FULL, q == 2 ? mine : 0u);
+                            m.w = __reduce_or_sync(FULL, q == 3 ? mine : 0u);
+                            if (lane == 0) reinterpret_cast<uint4*>(mask)[w] = m;
+                            const int base = w << 7;
+                            unsigned S = m.x & ~((m.x << 1) | carry);
+                            if ((S >> lane) & 1u) toks[ntok + __popc(S & lt_mask)] = (Tok)(base + lane);
                             ntok += __popc(S);
-                            if (!final) {
-                                const unsigned z = __ballot_sync(FULL, in && !tc && i < end - 1);
-                                if (z) zpos = (w << 5) + 31 - __clz(z);
-                            }
-                        }
-                        fill = ((end >> 5) + 1) << 5;
-                        __syncwarp();
-                        if (final) {
-                            ++k;
-                            off = 0;
-                        } else {
-                            if (zpos < 0) {              // no break in the whole piece: the variant with the larger
-                                if (defer_list) row_bad = true;          // buffer redoes the row, or gives up
-                                else if (lane == 0) flags[1] = 1;
-                                off += cnt;
-                            } else {                     // the token after the last break is redone with the next piece
-                                if (ntok > 0 && (int)toks[ntok - 1] > zpos) --ntok;
-                                off += zpos - pos0 + 1;
-                            }
-                            break;
+                            S = m.y & ~((m.y << 1) | (m.x >> 31));
+                            if ((S >> lane) & 1u) toks[ntok + __popc(S & lt_mask)] = (Tok)(base + 32 + lane);
+                            ntok += __popc(S);
+                            S = m.z & ~((m.z << 1) | (m.y >> 31));
+                            if ((S >> lane) & 1u) toks[ntok + __popc(S & lt_mask)] = (Tok)(base + 64 + lane);
+                            ntok += __popc(S);
+                            S = m.w & ~((m.w << 1) | (m.z >> 31));
+                            if ((S >> lane) & 1u) toks[ntok + __popc(S & lt_mask)] = (Tok)(base + 96 + lane);
+                            ntok += __popc(S);
+                            carry = m.w >> 31;
                         }
                     }
-                    // ---- hash: one lane per token
-                    for (int t0 = 0; t0 < ntok && !row_bad; t0 += 32) {
+                    __syncwarp();
+                    if (piece_pos0 >= 0) {
+                        // a piece of a long cell: everything after its last break is redone with the next piece.  The
+                        // last byte does not count as a break (its right neighbour is not staged).
+                        const int end = piece_pos0 + piece_cnt;
+                        int zpos = -1;
+                        for (int wb = ((end - 2) >> 5) & ~31; wb >= 0 && zpos < 0; wb -= 32) {
+                            const int wi = wb + lane;
+                            unsigned inv = 0u;
+                            if ((wi << 5) < end - 1) {
+                                inv = ~mask[wi];
+                                const int lo = piece_pos0 - (wi << 5), hi = end - 1 - (wi << 5);
+                                if (lo > 0) inv &= lo >= 32 ? 0u : ~((1u << lo) - 1u);
+                                if (hi < 32) inv &= (1u << hi) - 1u;
+                            }
+                            const unsigned any = __ballot_sync(FULL, inv != 0u);
+                            if (any) {
+                                const int src = 31 - __clz(any);
+                                const unsigned iv = __shfl_sync(FULL, inv, src);
+                                zpos = ((wb + src) << 5) + 31 - __clz(iv);
+                            }
+                        }
+                        if (zpos < 0) {                  // no break in the whole piece: the variant with the larger
+                            if (defer_list) row_bad = true;              // buffer redoes the row, or gives up
+                            else if (lane == 0) flags[1] = 1;
+                            off += piece_cnt;
+                        } else {
+                            if (ntok > 0 && (int)toks[ntok - 1] > zpos) --ntok;
+                            off += zpos - piece_pos0 + 1;
+                        }
+                    }
+
+                    // ---- pass 1, one lane per token: find its end, drop stop words and short tokens; the survivors of
+                    //      at most 32 bytes are compacted to the front of the list as start | (length - 1) << SB, the
+                    //      rare longer runs to its back
+                    int nsurv = 0, nlong = 0;
+                    for (int t0 = 0; t0 < ntok; t0 += 32) {
                         const int t = t0 + lane;
-                        bool newd = false, ovf = false;
+                        int kind = 0;
+                        unsigned rec = 0u;
                         if (t < ntok) {
                             const int s = toks[t];
                             int w = s >> 5;
-                            const int kc = wcell[w];
                             unsigned inv = ~mask[w] >> (s & 31);
                             int e;
                             if (inv) {
@@ -549,100 +690,88 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                                 do inv = ~mask[++w]; while (!inv);
                                 e = (w << 5) + __ffs(inv) - 1;
                             }
-                            const int j = c0 + kc;
-                            unsigned ph, pw, pn;
-                            if (j < TH_COLCACHE) {
-                                ph = colstate[3 * j];
-                                pw = colstate[3 * j + 1];
-                                pn = colstate[3 * j + 2];
-                            } else {
-                                Murmur pm;
-                                pm.init();
-                                const int plen = p.prepend ? prefix_len[j] : 0;
-                                for (int q = 0; q < plen; ++q) pm.push(prefix[j * TH_PREFIX + q]);
-                                ph = pm.h;
-                                pw = pm.word;
-                                pn = pm.n;
-                            }
-                            const int space_off = p.shared ? 0 : j * p.num_features;
-                            bool has_alnum = true;      // a run of '_' only is not a token
-                            if (e - s > TH_MAX_TOKEN || buf[s] == '_') {
-                                has_alnum = false;
-                                for (int q = s; q < e; ++q) has_alnum |= buf[q] != '_';
-                            }
-                            // a run longer than maxTokenLength is emitted in pieces of maxTokenLength
-                            for (int ps = s; has_alnum && ps < e; ps += TH_MAX_TOKEN) {
-                                const int plen = min(TH_MAX_TOKEN, e - ps);
-                                if (plen < p.min_token_length) continue;
-                                if (plen <= STOP_MAXLEN) {
-                                    const int q0 = ps + 16;
-                                    unsigned l0 = __funnelshift_r(bufw[q0 >> 2], bufw[(q0 >> 2) + 1], (q0 & 3) * 8);
-                                    unsigned l1 = __funnelshift_r(bufw[(q0 >> 2) + 1], bufw[(q0 >> 2) + 2], (q0 & 3) * 8);
-                                    unsigned l2 = __funnelshift_r(bufw[(q0 >> 2) + 2], bufw[(q0 >> 2) + 3], (q0 & 3) * 8);
-                                    l0 &= byte_range_mask(0, plen);
-                                    l1 &= byte_range_mask(0, plen - 4);
-                                    l2 &= byte_range_mask(0, plen - 8);
-                                    unsigned sl = stop_slot_hash(l0, l1, l2);
-                                    bool is_stop = false;
-                                    for (int probe = 0; probe < STOP_SLOTS; ++probe) {
-                                        const StopSlot se = stop[sl];
-                                        if (se.len == 0u) break;
-                                        if (se.len == (unsigned)plen && se.w0 == l0 && se.w1 == l1 && se.w2 == l2) {
-                                            is_stop = true;
-                                            break;
-                                        }
-                                        sl = (sl + 1) & (STOP_SLOTS - 1);
-                                    }
-                                    if (is_stop) continue;
+                            const int len = e - s;
+                            if (len > 32) {
+                                kind = 2;
+                                rec = (unsigned)s;
+                            } else if (len >= p.min_token_length) {
+                                bool keep = true;
+                                if (buf[s] == '_') {          // a run of '_' only is not a token
+                                    keep = false;
+                                    for (int q = s; q < e; ++q) keep |= buf[q] != '_';
                                 }
-                                // murmur3 continued from the prefix state: the r bytes the prefix left pending are the
-                                // low bytes of the first word
-                                const int r = (int)(pn & 3u);
-                                const unsigned keep_hi = ~((1u << (8 * r)) - 1u);
-                                const int tot = r + plen, nfull = tot >> 2, tail = tot & 3;
-                                const int q0 = ps - r + 16;
-                                const int sh = (q0 & 3) * 8;
-                                const unsigned* bw = bufw + (q0 >> 2);
-                                unsigned h = ph;
-                                unsigned nxt = bw[0];
-                                for (int q = 0; q <= nfull; ++q) {
-                                    const unsigned cur = nxt;
-                                    nxt = bw[q + 1];
-                                    unsigned wd = __funnelshift_r(cur, nxt, sh);
-                                    if (q == 0) wd = (wd & keep_hi) | pw;
-                                    if (q < nfull) {
-                                        h = mix_h1(h, mix_k1(wd));
-                                    } else {
-                                        for (int b = 0; b < tail; ++b)
-                                            h = mix_h1(h, mix_k1((unsigned)(int)(signed char)((wd >> (8 * b)) & 0xffu)));
-                                    }
-                                }
-                                const unsigned hv = fmix32(h, pn + (unsigned)plen);
-                                const int bucket = p.pow2_mask >= 0 ? (int)(hv & (unsigned)p.pow2_mask)
-                                                                    : non_negative_mod(hv, p.num_features);
-                                const unsigned key = (unsigned)(space_off + bucket);
-                                emitted |= 1u << kc;
-                                // insert / count
-                                unsigned slot = (key * 0x9E3779B1u) >> (32 - tbits);
-                                for (;;) {
-                                    Slot cur = table[slot];
-                                    if (cur == EMPTY) {
-                                        cur = atomicCAS(&table[slot], EMPTY, (Slot(key) << cb) | Slot(1));
-                                        if (cur == EMPTY) {
-                                            newd = true;
-                                            break;
-                                        }
-                                    }
-                                    if ((unsigned)(cur >> cb) == key) {
-                                        const Slot old = atomicAdd(&table[slot], Slot(1));
-                                        if ((old & cmask) == cmask) ovf = true;   // the count ran into the key
-                                        break;
-                                    }
-                                    slot = (slot + 1) & (tsize - 1);
+                                if (keep && len <= STOP_MAXLEN) keep = !th_is_stop(stop, bufw, s, len);
+                                if (keep) {
+                                    kind = 1;
+                                    rec = (unsigned)s | ((unsigned)(len - 1) << SB);
+                                    emitted |= 1u << wcell[s >> 4];
                                 }
                             }
                         }
+                        const unsigned b1 = __ballot_sync(FULL, kind == 1), b2 = __ballot_sync(FULL, kind == 2);
+                        __syncwarp();
+                        if (kind == 1) toks[nsurv + __popc(b1 & lt_mask)] = (Tok)rec;
+                        if (kind == 2) toks[TB / 2 - 1 - (nlong + __popc(b2 & lt_mask))] = (Tok)rec;
+                        nsurv += __popc(b1);
+                        nlong += __popc(b2);
+                    }
+                    __syncwarp();
+                    // ---- pass 2, one lane per surviving token: murmur3 and the table
+                    for (int t0 = 0; t0 < nsurv && !row_bad; t0 += 32) {
+                        const int t = t0 + lane;
+                        bool newd = false, ovf = false;
+                        if (t < nsurv) {
+                            const unsigned rec = toks[t];
+                            const int s = (int)(rec & (unsigned)(TB - 1)), len = (int)(rec >> SB) + 1;
+                            const int j = c0 + wcell[s >> 4];
+                            unsigned ph, pw, pn;
+                            th_col_state(colstate, prefix, prefix_len, p, j, ph, pw, pn);
+                            const unsigned hv = th_hash_piece(bufw, s, len, ph, pw, pn);
+                            const int bucket = p.pow2_mask >= 0 ? (int)(hv & (unsigned)p.pow2_mask)
+                                                                : non_negative_mod(hv, p.num_features);
+                            const unsigned key = (unsigned)((p.shared ? 0 : j * p.num_features) + bucket);
+                            th_insert<Slot>(table, tbits, cb, key, newd, ovf);
+                        }
                         ndist += __popc(__ballot_sync(FULL, newd));
+                        if (__any_sync(FULL, ovf) || ndist > dist_limit) row_bad = true;
+                    }
+                    // ---- runs longer than 32 bytes: emitted in pieces of maxTokenLength
+                    for (int t0 = 0; t0 < nlong && !row_bad; t0 += 32) {
+                        const int t = t0 + lane;
+                        bool ovf = false;
+                        int nnew = 0;
+                        if (t < nlong) {
+                            const int s = toks[TB / 2 - 1 - t];
+                            int w = s >> 5;
+                            unsigned inv = ~mask[w] >> (s & 31);
+                            int e;
+                            if (inv) {
+                                e = s + __ffs(inv) - 1;
+                            } else {
+                                do inv = ~mask[++w]; while (!inv);
+                                e = (w << 5) + __ffs(inv) - 1;
+                            }
+                            const int kc = wcell[s >> 4];
+                            const int j = c0 + kc;
+                            unsigned ph, pw, pn;
+                            th_col_state(colstate, prefix, prefix_len, p, j, ph, pw, pn);
+                            bool has_alnum = false;
+                            for (int q = s; q < e; ++q) has_alnum |= buf[q] != '_';
+                            for (int ps = s; has_alnum && ps < e; ps += TH_MAX_TOKEN) {
+                                const int plen = min(TH_MAX_TOKEN, e - ps);
+                                if (plen < p.min_token_length) continue;
+                                if (plen <= STOP_MAXLEN && th_is_stop(stop, bufw, ps, plen)) continue;
+                                const unsigned hv = th_hash_piece(bufw, ps, plen, ph, pw, pn);
+                                const int bucket = p.pow2_mask >= 0 ? (int)(hv & (unsigned)p.pow2_mask)
+                                                                    : non_negative_mod(hv, p.num_features);
+                                const unsigned key = (unsigned)((p.shared ? 0 : j * p.num_features) + bucket);
+                                emitted |= 1u << kc;
+                                bool nd1 = false;
+                                th_insert<Slot>(table, tbits, cb, key, nd1, ovf);
+                                nnew += nd1 ? 1 : 0;
+                            }
+                        }
+                        ndist += __reduce_add_sync(FULL, nnew);
                         if (__any_sync(FULL, ovf) || ndist > dist_limit) row_bad = true;
                     }
                     __syncwarp();
@@ -686,19 +815,28 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
             }
             if (!SPARSE_OUT) {
                 const int cls = (p.nclasses > 1 && class_ids) ? class_ids[row] : 0;
-                for (int i = lane; i < tsize; i += 32) {
-                    const Slot sv = table[i];
-                    if (sv == EMPTY) continue;
-                    table[i] = EMPTY;
-                    const unsigned v = (unsigned)(sv >> cb);
-                    const unsigned cnt = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
-                    atomicAdd(&bucket_class_sum[(int64_t)v * p.nclasses + cls], cnt);
-                    if (cnt > 1u) {   // rare: everything beyond "present once" goes to the auxiliary arrays
-                        atomicAdd(&bucket_dup[v], cnt - 1u);
-                        atomicAdd(&bucket_sq_extra[v], (unsigned long long)cnt * cnt - cnt);
-                        atomicMax(&bucket_aux[3 * (int64_t)v], cnt);
-                        atomicMin(&bucket_aux[3 * (int64_t)v + 1], ~cnt);
-                        atomicAdd(&bucket_aux[3 * (int64_t)v + 2], 1u);
+                // every lane looks at slots lane, lane + 32, ... and remembers the occupied ones in a bitmap, so that the
+                // emitting loop below runs with most lanes busy
+                for (int i0 = 0; i0 < tsize; i0 += 1024) {
+                    const int lim = min(32, (tsize - i0) >> 5);
+                    unsigned occ = 0u;
+                    for (int b = 0; b < lim; ++b)
+                        if (table[i0 + (b << 5) + lane] != EMPTY) occ |= 1u << b;
+                    while (occ) {
+                        const int i = i0 + ((__ffs(occ) - 1) << 5) + lane;
+                        occ &= occ - 1u;
+                        const Slot sv = table[i];
+                        table[i] = EMPTY;
+                        const unsigned v = (unsigned)(sv >> cb);
+                        const unsigned cnt = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
+                        atomicAdd(&bucket_class_sum[(int64_t)v * p.nclasses + cls], cnt);
+                        if (cnt > 1u) {   // rare: everything beyond "present once" goes to the auxiliary arrays
+                            atomicAdd(&bucket_dup[v], cnt - 1u);
+                            atomicAdd(&bucket_sq_extra[v], (unsigned long long)cnt * cnt - cnt);
+                            atomicMax(&bucket_aux[3 * (int64_t)v], cnt);
+                            atomicMin(&bucket_aux[3 * (int64_t)v + 1], ~cnt);
+                            atomicAdd(&bucket_aux[3 * (int64_t)v + 2], 1u);
+                        }
                     }
                 }
             } else {

@@ -135,20 +135,22 @@ def select_columns(vec: VectorColumn, keep: List[int]) -> list:
     once with just their kept columns; materialised dense parts go through the gather kernel."""
     R.require_cuda()
     out, off = [], 0
+    keep = np.asarray(keep, dtype=np.int64)
     for p in vec.parts:
-        local = [i - off for i in keep if off <= i < off + p.width]
+        local = keep[(keep >= off) & (keep < off + p.width)] - off
         off += p.width
-        if not local:
+        if len(local) == 0:
             continue
+        whole = len(local) == p.width and bool((local == np.arange(p.width)).all())
         if isinstance(p, LazyDensePart):
             out.append(DensePart(p.materialize(local)))
         elif isinstance(p, DensePart):
-            if local == list(range(p.width)):
+            if whole:
                 out.append(p)
                 continue
             x = p.data if p.data.is_cuda else p.data.cuda()
             n = x.shape[0]
-            idx = torch.tensor(local, dtype=torch.int32, device="cuda")
+            idx = torch.from_numpy(local.astype(np.int32)).cuda()
             dst = torch.empty((n, len(local)), dtype=torch.float64, device="cuda")
             L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), n, idx.data_ptr(), len(local),
                    dst.data_ptr(), len(local), R.stream())
@@ -156,11 +158,11 @@ def select_columns(vec: VectorColumn, keep: List[int]) -> list:
         elif isinstance(p, (LazyOneHotPart, LazyPart)):
             out.append(p.materialize(local))
         elif isinstance(p, OneHotPart):
-            if local == list(range(p.width)):
+            if whole:
                 out.append(p)
                 continue
             newpos = torch.full((p.width + 1,), -1, dtype=torch.int32, device=p.indices.device)
-            newpos[torch.as_tensor(local, device=p.indices.device)] = torch.arange(
+            newpos[torch.from_numpy(local).to(p.indices.device)] = torch.arange(
                 len(local), dtype=torch.int32, device=p.indices.device)
             idx = p.indices.long()
             out.append(OneHotPart(newpos[torch.where(idx < 0, torch.full_like(idx, p.width), idx)], len(local)))

@@ -241,9 +241,8 @@ class SanityChecker(OpEstimator):
             reasons={nm: [t for b, t in REASONS.items() if reasons[i] & b]
                      for nm, i in zip(meta.names_of(flagged), flagged)},
             sampleFraction=frac, featureFeatureCorr=corr_matrix)
-        keep = [int(i) for i in keep]
         self.parentCorr, self.parentCramersV = pc, pv
-        if not keep:
+        if len(keep) == 0:
             raise ValueError("requirement failed: The sanity checker has dropped all of your features, check your "
                              "input data quality")
         return SanityCheckerModel(self, keep, self.removeBadFeatures)
@@ -401,7 +400,8 @@ class _MetaPlan:
 class SanityCheckerModel(OpModel):
     def __init__(self, parent: SanityChecker, indicesToKeep: List[int], removeBadFeatures: bool):  # noqa: N803
         super().__init__(parent)
-        self.indicesToKeep = list(indicesToKeep)
+        self._keep = np.asarray(indicesToKeep, dtype=np.int64)
+        self.indicesToKeep = self._keep.tolist()
         self.removeBadFeatures = removeBadFeatures
 
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
@@ -410,6 +410,6 @@ class SanityCheckerModel(OpModel):
         if not self.removeBadFeatures:
             return VectorColumn(name, batch.n, self.getMetadata(), vec.parts, vec.stats)
         from .generic_stats import select_columns
-        parts = select_columns(vec, self.indicesToKeep)
-        stats = None if vec.stats is None else vec.stats.select(self.indicesToKeep)
+        parts = select_columns(vec, self._keep)
+        stats = None if vec.stats is None else vec.stats.select(self._keep)
         return VectorColumn(name, batch.n, self.getMetadata(), parts, stats)

@@ -49,6 +49,9 @@ class VectorStats:
         return VectorStats(first.label, cat("mean"), cat("variance"), cat("min"), cat("max"), cat("cov_label"), cs)
 
     def select(self, idx: List[int]) -> "VectorStats":
+        idx = np.asarray(idx, dtype=np.int64)
+        if len(idx) == self.width and bool((idx == np.arange(self.width)).all()):
+            return self
         cs = None if self.class_sums is None else self.class_sums[:, idx]
         return VectorStats(self.label, self.mean[idx], self.variance[idx], self.min[idx], self.max[idx],
                            self.cov_label[idx], cs)
