@@ -294,8 +294,12 @@ struct StopSlot {          // stop-word table in shared memory: length + the wor
     unsigned len, w0, w1, w2;
 };
 
+// two slot choices per word (cuckoo hashing): a probe is two loads, no loop
 __host__ __device__ inline unsigned stop_slot_hash(unsigned w0, unsigned w1, unsigned w2) {
     return ((w0 * 0x9E3779B1u) ^ (w1 * 0x85EBCA6Bu) ^ (w2 * 0xC2B2AE35u)) >> 23;   // 9 bits: STOP_SLOTS == 512
+}
+__host__ __device__ inline unsigned stop_slot_hash2(unsigned w0, unsigned w1, unsigned w2) {
+    return ((w0 * 0x85EBCA6Bu) ^ (w1 * 0xC2B2AE35u) ^ (w2 * 0x27D4EB2Fu) ^ 0x165667B1u) >> 23;
 }
 
 template <typename Slot> struct SlotTraits;
@@ -338,14 +342,11 @@ __device__ __forceinline__ bool th_is_stop(const StopSlot* stop, const unsigned*
     const unsigned l0 = __funnelshift_r(a, b, sh) & byte_range_mask(0, plen);
     const unsigned l1 = __funnelshift_r(b, c, sh) & byte_range_mask(0, plen - 4);
     const unsigned l2 = __funnelshift_r(c, d, sh) & byte_range_mask(0, plen - 8);
-    unsigned sl = stop_slot_hash(l0, l1, l2);
-    for (int probe = 0; probe < STOP_SLOTS; ++probe) {
-        const StopSlot se = stop[sl];
-        if (se.len == 0u) return false;
-        if (se.len == (unsigned)plen && se.w0 == l0 && se.w1 == l1 && se.w2 == l2) return true;
-        sl = (sl + 1) & (STOP_SLOTS - 1);
-    }
-    return false;
+    const uint4 e1 = reinterpret_cast<const uint4*>(stop)[stop_slot_hash(l0, l1, l2)];
+    const uint4 e2 = reinterpret_cast<const uint4*>(stop)[stop_slot_hash2(l0, l1, l2)];
+    const unsigned d1 = (e1.x ^ (unsigned)plen) | (e1.y ^ l0) | (e1.z ^ l1) | (e1.w ^ l2);
+    const unsigned d2 = (e2.x ^ (unsigned)plen) | (e2.y ^ l0) | (e2.z ^ l1) | (e2.w ^ l2);
+    return d1 == 0u || d2 == 0u;
 }
 
 // murmur3 of "<prefix><token>" continued from the state (ph, pw, pn) after the prefix: the r = pn & 3 bytes the prefix
@@ -391,6 +392,17 @@ __device__ __forceinline__ void th_col_state(const unsigned* colstate, const uin
     }
 }
 
+// a bucket met cnt > 1 times in a row: everything beyond "present once" goes to the auxiliary arrays
+__device__ __forceinline__ void th_rare_update(uint2 e, unsigned* bucket_dup, unsigned long long* bucket_sq_extra,
+                                               unsigned* bucket_aux) {
+    const unsigned v = e.x, cnt = e.y;
+    atomicAdd(&bucket_dup[v], cnt - 1u);
+    atomicAdd(&bucket_sq_extra[v], (unsigned long long)cnt * cnt - cnt);
+    atomicMax(&bucket_aux[3 * (int64_t)v], cnt);
+    atomicMin(&bucket_aux[3 * (int64_t)v + 1], ~cnt);
+    atomicAdd(&bucket_aux[3 * (int64_t)v + 2], 1u);
+}
+
 // count `key` in the row's table (1 << tbits slots in use, the count in the low cb bits of a slot)
 template <typename Slot>
 __device__ __forceinline__ void th_insert(Slot* table, int tbits, int cb, unsigned key, bool& newd, bool& ovf) {
@@ -420,7 +432,7 @@ __device__ __forceinline__ void th_insert(Slot* table, int tbits, int cb, unsign
 // flags: [0] non-ASCII byte met, [1] a run of token characters longer than the text buffer, [2] a row has more
 //        distinct buckets than the large table holds, [3] sparse output capacity exceeded
 template <typename Slot, int T, int TB, int WARPS, bool SPARSE_OUT>
-__global__ void __launch_bounds__(WARPS * 32)
+__global__ void __launch_bounds__(WARPS * 32, WARPS >= 8 ? 2 : 1)
 text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, const uint8_t* __restrict__ prefix,
                  const int* __restrict__ prefix_len, TextHashParams p, const uint8_t* __restrict__ class_ids,
                  // rows to work on: all of [0, n), or row_list[0 .. *row_list_n) (rows deferred by the fast variant)
@@ -527,60 +539,99 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 int64_t off = 0;             // bytes of cell k already consumed (cells longer than the buffer)
                 for (;;) {
                     // ---- stage as many cells as the buffer holds: 16-byte chunks, global and shared addresses
-                    //      congruent mod 16; every byte of [0, fill) that is not a cell byte is zero
+                    //      congruent mod 16; every byte of [0, fill) that is not a cell byte is zero.  The chunks of all
+                    //      the cells of the batch are numbered through and taken one per lane.
                     int fill = 0;
                     int piece_pos0 = -1, piece_cnt = 0;      // set when the buffer holds one piece of a long cell
-                    while (k < ncells) {
-                        const int64_t len = __shfl_sync(FULL, my_len, k);
-                        const int64_t rem = len - off;
-                        if (rem <= 0) {
-                            ++k;
-                            off = 0;
-                            continue;
+                    {
+                        const uint8_t* cptr = my_ptr + (lane == k ? off : 0);
+                        const int64_t crem = my_len - (lane == k ? off : 0);
+                        const int csh = (int)(reinterpret_cast<uintptr_t>(cptr) & 15u);
+                        const bool mine = lane >= k && lane < ncells && crem > 0;
+                        // chunks through the zero byte after the cell (a cell longer than the buffer: more than fit)
+                        const int need = !mine ? 0 : (crem > TB ? TB : (int)((csh + crem + 16) >> 4));
+                        int incl = need;
+                        for (int o = 1; o < 32; o <<= 1) {
+                            const int up = __shfl_up_sync(FULL, incl, o);
+                            if (lane >= o) incl += up;
                         }
-                        const uint8_t* g = reinterpret_cast<const uint8_t*>(
-                                               __shfl_sync(FULL, reinterpret_cast<unsigned long long>(my_ptr), k)) + off;
-                        const int sh16 = (int)(reinterpret_cast<uintptr_t>(g) & 15u);
-                        int cnt;
-                        if (fill + sh16 + rem + 1 <= TB) {
-                            cnt = (int)rem;
-                        } else if (fill > 0) {
-                            break;                       // hash what is staged, then come back with an empty buffer
+                        const int cstart = incl - need;          // first chunk of this lane's cell
+                        // incl is monotone, so the cells that fit are a run starting at k
+                        const int kend = min(ncells, k + __popc(__ballot_sync(FULL, lane >= k && (incl << 4) <= TB)));
+                        unsigned na = 0u;
+                        if (kend > k) {
+                            const int nchunks = __shfl_sync(FULL, incl, kend - 1);
+                            for (int f0 = 0; f0 < nchunks; f0 += 32) {
+                                const int f = min(f0 + lane, nchunks - 1);
+                                int lo_c = k, hi_c = kend - 1;       // the last cell whose first chunk is <= f
+#pragma unroll
+                                for (int it = 0; it < 5; ++it) {
+                                    const int mid = (lo_c + hi_c + 1) >> 1;
+                                    const int cs = __shfl_sync(FULL, cstart, mid);
+                                    if (cs <= f) lo_c = mid;
+                                    else hi_c = mid - 1;
+                                }
+                                const int c = f - __shfl_sync(FULL, cstart, lo_c);
+                                const uint8_t* g = reinterpret_cast<const uint8_t*>(
+                                    __shfl_sync(FULL, reinterpret_cast<unsigned long long>(cptr), lo_c));
+                                const int cnt = (int)__shfl_sync(FULL, (int)min(crem, (int64_t)TB), lo_c);
+                                if (f0 + lane < nchunks) {
+                                    const int sh16 = (int)(reinterpret_cast<uintptr_t>(g) & 15u);
+                                    const int lo = c == 0 ? sh16 : 0;
+                                    const int hi = min(16, sh16 + cnt - 16 * c);
+                                    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                                    if (hi > 0) {
+                                        v = __ldg(reinterpret_cast<const uint4*>(g - sh16 + 16 * c));
+                                        if (lo != 0 || hi != 16) {
+                                            v.x &= byte_range_mask(lo, hi);
+                                            v.y &= byte_range_mask(lo - 4, hi - 4);
+                                            v.z &= byte_range_mask(lo - 8, hi - 8);
+                                            v.w &= byte_range_mask(lo - 12, hi - 12);
+                                        }
+                                        na |= (v.x | v.y | v.z | v.w) & 0x80808080u;
+                                        v.x = lower4(v.x);
+                                        v.y = lower4(v.y);
+                                        v.z = lower4(v.z);
+                                        v.w = lower4(v.w);
+                                    }
+                                    *reinterpret_cast<uint4*>(buf + 16 * f) = v;
+                                    wcell[f] = (unsigned char)lo_c;
+                                }
+                            }
+                            fill = nchunks << 4;
+                            k = kend;
+                            off = 0;
                         } else {
-                            cnt = TB - 17;               // a piece of a long cell
+                            // cell k alone is longer than the buffer: stage a piece of it
+                            const uint8_t* g = reinterpret_cast<const uint8_t*>(
+                                __shfl_sync(FULL, reinterpret_cast<unsigned long long>(cptr), k));
+                            const int sh16 = (int)(reinterpret_cast<uintptr_t>(g) & 15u);
+                            const int cnt = TB - 17;
                             piece_pos0 = sh16;
                             piece_cnt = cnt;
-                        }
-                        const uint8_t* gal = g - sh16;
-                        unsigned char* sb = buf + fill;
-                        const int nchunk = (sh16 + cnt + 16) >> 4;       // through the zero byte after the cell
-                        unsigned na = 0u;
-                        for (int c = lane; c < nchunk; c += 32) {
-                            const int lo = c == 0 ? sh16 : 0;
-                            const int hi = min(16, sh16 + cnt - 16 * c);
-                            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-                            if (hi > 0) {
-                                v = __ldg(reinterpret_cast<const uint4*>(gal + 16 * c));
-                                if (lo != 0 || hi != 16) {
+                            const int nchunks = (sh16 + cnt + 16) >> 4;
+                            for (int c = lane; c < nchunks; c += 32) {
+                                const int lo = c == 0 ? sh16 : 0;
+                                const int hi = min(16, sh16 + cnt - 16 * c);
+                                uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                                if (hi > 0) {
+                                    v = __ldg(reinterpret_cast<const uint4*>(g - sh16 + 16 * c));
                                     v.x &= byte_range_mask(lo, hi);
                                     v.y &= byte_range_mask(lo - 4, hi - 4);
                                     v.z &= byte_range_mask(lo - 8, hi - 8);
                                     v.w &= byte_range_mask(lo - 12, hi - 12);
+                                    na |= (v.x | v.y | v.z | v.w) & 0x80808080u;
+                                    v.x = lower4(v.x);
+                                    v.y = lower4(v.y);
+                                    v.z = lower4(v.z);
+                                    v.w = lower4(v.w);
                                 }
-                                na |= (v.x | v.y | v.z | v.w) & 0x80808080u;
-                                v.x = lower4(v.x);
-                                v.y = lower4(v.y);
-                                v.z = lower4(v.z);
-                                v.w = lower4(v.w);
+                                *reinterpret_cast<uint4*>(buf + 16 * c) = v;
+                                wcell[c] = (unsigned char)k;
                             }
-                            *reinterpret_cast<uint4*>(sb + 16 * c) = v;
-                            wcell[(fill >> 4) + c] = (unsigned char)k;
+                            fill = nchunks << 4;
                         }
                         if (na) flags[0] = 1;
-                        fill += nchunk << 4;
-                        if (piece_pos0 >= 0) break;
-                        ++k;
-                        off = 0;
                     }
                     __syncwarp();
 
@@ -817,28 +868,41 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 const int cls = (p.nclasses > 1 && class_ids) ? class_ids[row] : 0;
                 // every lane looks at slots lane, lane + 32, ... and remembers the occupied ones in a bitmap, so that the
                 // emitting loop below runs with most lanes busy
+                // the rare term frequencies > 1 are set aside (in the token list, free by now) and handled afterwards
+                // with all lanes busy
+                uint2* rare = reinterpret_cast<uint2*>(toks);
+                constexpr int RARE_CAP = TB / 2 * (int)sizeof(Tok) / (int)sizeof(uint2);
+                int nrare = 0;
                 for (int i0 = 0; i0 < tsize; i0 += 1024) {
                     const int lim = min(32, (tsize - i0) >> 5);
                     unsigned occ = 0u;
-                    for (int b = 0; b < lim; ++b)
-                        if (table[i0 + (b << 5) + lane] != EMPTY) occ |= 1u << b;
-                    while (occ) {
-                        const int i = i0 + ((__ffs(occ) - 1) << 5) + lane;
-                        occ &= occ - 1u;
-                        const Slot sv = table[i];
-                        table[i] = EMPTY;
-                        const unsigned v = (unsigned)(sv >> cb);
-                        const unsigned cnt = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
-                        atomicAdd(&bucket_class_sum[(int64_t)v * p.nclasses + cls], cnt);
-                        if (cnt > 1u) {   // rare: everything beyond "present once" goes to the auxiliary arrays
-                            atomicAdd(&bucket_dup[v], cnt - 1u);
-                            atomicAdd(&bucket_sq_extra[v], (unsigned long long)cnt * cnt - cnt);
-                            atomicMax(&bucket_aux[3 * (int64_t)v], cnt);
-                            atomicMin(&bucket_aux[3 * (int64_t)v + 1], ~cnt);
-                            atomicAdd(&bucket_aux[3 * (int64_t)v + 2], 1u);
+                    for (int b = 0; b < lim; ++b) occ |= (table[i0 + (b << 5) + lane] != EMPTY ? 1u : 0u) << b;
+                    while (__any_sync(FULL, occ != 0u)) {
+                        unsigned v = 0u, cnt = 0u;
+                        if (occ) {
+                            const int i = i0 + ((__ffs(occ) - 1) << 5) + lane;
+                            occ &= occ - 1u;
+                            const Slot sv = table[i];
+                            table[i] = EMPTY;
+                            v = (unsigned)(sv >> cb);
+                            cnt = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
+                            atomicAdd(&bucket_class_sum[(int64_t)v * p.nclasses + cls], cnt);
+                        }
+                        const unsigned rb = __ballot_sync(FULL, cnt > 1u);
+                        if (rb) {
+                            if (nrare + 32 > RARE_CAP) {          // no room (never with the shipped sizes): drain first
+                                __syncwarp();
+                                for (int i = lane; i < nrare; i += 32) th_rare_update(rare[i], bucket_dup, bucket_sq_extra, bucket_aux);
+                                nrare = 0;
+                                __syncwarp();
+                            }
+                            if (cnt > 1u) rare[nrare + __popc(rb & lt_mask)] = make_uint2(v, cnt);
+                            nrare += __popc(rb);
                         }
                     }
                 }
+                __syncwarp();
+                for (int i = lane; i < nrare; i += 32) th_rare_update(rare[i], bucket_dup, bucket_sq_extra, bucket_aux);
             } else {
                 // compact the kept buckets to the front of the table as (new position | value) ...
                 int kept = 0;
@@ -928,14 +992,26 @@ static int upload_stop_words() {
     static StopEntry table[STOP_SLOTS];
     memset(table, 0, sizeof(table));
     const int nwords = (int)(sizeof(kStopWords) / sizeof(kStopWords[0]));
-    for (int i = 0; i < nwords; ++i) {
-        const int len = (int)strlen(kStopWords[i]);
-        unsigned pw[3] = {0u, 0u, 0u};
-        for (int q = 0; q < len; ++q) pw[q >> 2] |= (unsigned)(unsigned char)kStopWords[i][q] << (8 * (q & 3));
-        unsigned s = stop_slot_hash(pw[0], pw[1], pw[2]) & (STOP_SLOTS - 1);
-        while (table[s].len != 0) s = (s + 1) & (STOP_SLOTS - 1);
-        table[s].len = (unsigned char)len;
-        memcpy(table[s].w, kStopWords[i], len);
+    for (int i = 0; i < nwords; ++i) {      // cuckoo insertion: every word ends in one of its two slots
+        StopEntry cur;
+        memset(&cur, 0, sizeof(cur));
+        cur.len = (unsigned char)strlen(kStopWords[i]);
+        memcpy(cur.w, kStopWords[i], cur.len);
+        unsigned pos = ~0u;
+        bool placed = false;
+        for (int kick = 0; kick < 256 && !placed; ++kick) {
+            unsigned pw[3] = {0u, 0u, 0u};
+            for (int q = 0; q < cur.len; ++q) pw[q >> 2] |= (unsigned)(unsigned char)cur.w[q] << (8 * (q & 3));
+            const unsigned a = stop_slot_hash(pw[0], pw[1], pw[2]), b = stop_slot_hash2(pw[0], pw[1], pw[2]);
+            pos = (pos == a) ? b : a;
+            if (table[pos].len == 0) {
+                table[pos] = cur;
+                placed = true;
+            } else {
+                std::swap(table[pos], cur);
+            }
+        }
+        TMOG_REQUIRE(placed, "stop-word table: cuckoo insertion failed");
     }
     TMOG_CUDA(cudaMemcpyToSymbol(c_stop, table, sizeof(table)));
     if (dev >= 0 && dev < 64) done[dev] = true;
