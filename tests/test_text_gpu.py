@@ -214,6 +214,19 @@ def test_transmogrify_sanity_check_text_matches_oracle(device):
     assert got.shape == exp.shape and abs(got - exp).max() < 1e-9
 
 
+def _assert_rows_sorted(vec):
+    """Sparse rows come out with strictly increasing indices (what Spark's SparseVector requires)."""
+    from transmogrifai_b200.columnar import SparseRowsPart
+    for part in vec.parts:
+        part = part.materialize(None) if hasattr(part, "materialize") else part
+        if not isinstance(part, SparseRowsPart):
+            continue
+        start, nnz, idx = part.row_start.cpu().numpy(), part.row_nnz.cpu().numpy(), part.indices.cpu().numpy()
+        for r in range(len(start)):
+            row = idx[start[r]:start[r] + nnz[r]]
+            assert (np.diff(row) > 0).all(), f"row {r} is not sorted"
+
+
 def _hash_case(cols, names, num_features, strategy, **kw):
     from transmogrifai_b200 import features as F
     from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
@@ -221,7 +234,9 @@ def _hash_case(cols, names, num_features, strategy, **kw):
     est = SmartTextVectorizer().setMaxCardinality(0).setNumFeatures(num_features).setHashSpaceStrategy(strategy) \
         .setInput(*_feats(names))
     model = est.fit(batch)
-    got = model.transform(batch).vectors[est.getOutput().name].to_scipy()
+    vec = model.transform(batch).vectors[est.getOutput().name]
+    _assert_rows_sorted(vec)
+    got = vec.to_scipy()
     exp = V.smart_text_transform(cols, names, ["Hash"] * len(names), [[] for _ in names], num_features=num_features,
                                  track_nulls=True, prepend_feature_name=True, binary_freq=False,
                                  hash_space_strategy=strategy, min_token_length=1)

@@ -322,15 +322,23 @@ __device__ __forceinline__ unsigned byte_range_mask(int lo, int hi) {
     return upto_hi & ~((1u << (8 * lo)) - 1u);
 }
 
+constexpr int th_pow2_floor(int x) {
+    int p = 1;
+    while (2 * p <= x) p *= 2;
+    return p;
+}
+
 // bytes of one warp's working set in shared memory
 template <typename Slot, int T, int TB>
 struct ThLayout {
     using Tok = typename std::conditional<(TB <= 2048), unsigned short, unsigned>::type;
     static constexpr int BUF = 0;                               // 16 slack + TB text + 32 slack
-    static constexpr int MASK = BUF + 16 + TB + 32;             // TB / 32 words: bit b of word w = byte 32 w + b
-    static constexpr int TOKS = MASK + (TB / 32 * 4 + 15) / 16 * 16;         // TB / 2 token records
-    static constexpr int WCELL = TOKS + TB / 2 * (int)sizeof(Tok);           // cell of every 16 bytes (u8)
+    static constexpr int TOKS = BUF + 16 + TB + 32;             // TB / 2 token records
+    static constexpr int MASK = TOKS + TB / 2 * (int)sizeof(Tok);            // TB / 32 words: bit b of word w = byte 32 w + b
+    static constexpr int WCELL = MASK + (TB / 32 * 4 + 15) / 16 * 16;        // cell of every 16 bytes (u8)
     static constexpr int TABLE = WCELL + (TB / 16 + 15) / 16 * 16;
+    // text + token list double as the ordered scatter table of the sparse-row flush
+    static constexpr int T2 = th_pow2_floor((MASK - BUF) / (int)sizeof(Slot));
     static constexpr int BYTES = TABLE + T * (int)sizeof(Slot);
 };
 
@@ -486,7 +494,7 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
         colstate[3 * j + 2] = pm.n;
     }
     for (int i = lane; i < T; i += 32) table[i] = EMPTY;
-    for (int i = lane; i < (L::TOKS - L::BUF) / 4; i += 32) reinterpret_cast<unsigned*>(wbase)[i] = 0u;
+    for (int i = lane; i < (L::TABLE - L::BUF) / 4; i += 32) reinterpret_cast<unsigned*>(wbase)[i] = 0u;
     __syncthreads();
 
     const int cb = p.count_bits;
@@ -904,58 +912,132 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 __syncwarp();
                 for (int i = lane; i < nrare; i += 32) th_rare_update(rare[i], bucket_dup, bucket_sq_extra, bucket_aux);
             } else {
-                // compact the kept buckets to the front of the table as (new position | value) ...
+                // The kept buckets go out in ascending order of their new position.  Fast way: an ordered scatter --
+                // (new position | value) is pushed into a second table at a slot proportional to the bucket index,
+                // every slot keeping the smaller of what it holds and what arrives and passing the larger on, so that
+                // reading that table front to back gives the sorted row.  It lives in the text buffer and the token
+                // list (free by now); when the row is too crowded for it, or the scatter runs off its end, the table is
+                // compacted and bitonic-sorted in place instead.
+                Slot* t2 = reinterpret_cast<Slot*>(wbase + L::BUF);
+                constexpr int T2 = L::T2;
                 int kept = 0;
-                for (int i0 = 0; i0 < tsize; i0 += 32) {
-                    const Slot sv = table[i0 + lane];
-                    int np = -1;
-                    unsigned val = 0u;
-                    if (sv != EMPTY) {
-                        const unsigned v = (unsigned)(sv >> cb);
-                        np = newpos[v];
-                        val = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
-                    }
-                    const unsigned kb = __ballot_sync(FULL, np >= 0);
-                    table[i0 + lane] = EMPTY;
+                bool ordered = ndist <= T2 / 2 + T2 / 8;
+                if (ordered) {
+                    for (int i = lane; i < T2; i += 32) t2[i] = EMPTY;
                     __syncwarp();
-                    if (np >= 0) table[kept + __popc(kb & lt_mask)] = (Slot((unsigned)np) << cb) | Slot(val);
-                    kept += __popc(kb);
-                    __syncwarp();
-                }
-                // ... sort them (bitonic, the padding EMPTY sorts last) ...
-                int m = 32;
-                while (m < kept) m <<= 1;
-                for (int k2 = 2; k2 <= m; k2 <<= 1) {
-                    for (int jj = k2 >> 1; jj > 0; jj >>= 1) {
-                        for (int t = lane; t < (m >> 1); t += 32) {
-                            const int i = ((t & ~(jj - 1)) << 1) | (t & (jj - 1));
-                            const int ixj = i | jj;
-                            const Slot x = table[i], y = table[ixj];
-                            const bool up = (i & k2) == 0;
-                            if ((x > y) == up) {
-                                table[i] = y;
-                                table[ixj] = x;
+                    const float scale = (float)(T2 - 64) / (float)(p.null_base + ncols);
+                    bool fail = false;
+                    for (int i0 = 0; i0 < tsize; i0 += 1024) {
+                        const int lim = min(32, (tsize - i0) >> 5);
+                        unsigned occ = 0u;
+                        for (int b = 0; b < lim; ++b) occ |= (table[i0 + (b << 5) + lane] != EMPTY ? 1u : 0u) << b;
+                        while (__any_sync(FULL, occ != 0u)) {
+                            int np = -1;
+                            if (occ) {
+                                const Slot sv = table[i0 + ((__ffs(occ) - 1) << 5) + lane];
+                                occ &= occ - 1u;
+                                const unsigned v = (unsigned)(sv >> cb);
+                                np = newpos[v];
+                                if (np >= 0) {
+                                    const unsigned val =
+                                        (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
+                                    Slot x = (Slot((unsigned)np) << cb) | Slot(val);
+                                    int slot = min((int)((float)v * scale), T2 - 64);
+                                    for (;;) {
+                                        const Slot old = atomicMin(&t2[slot], x);
+                                        if (old == EMPTY) break;
+                                        x = old > x ? old : x;
+                                        if (++slot >= T2) {
+                                            fail = true;
+                                            break;
+                                        }
+                                    }
+                                }
                             }
+                            kept += __popc(__ballot_sync(FULL, np >= 0));
                         }
+                    }
+                    __syncwarp();
+                    ordered = !__any_sync(FULL, fail);
+                    if (ordered) {
+                        unsigned long long base = 0;
+                        if (lane == 0) {
+                            base = atomicAdd(cursor, (unsigned long long)kept);
+                            row_start[row] = (int64_t)base;
+                            row_nnz[row] = kept;
+                            if ((int64_t)base + kept > capacity) flags[3] = 1;
+                        }
+                        base = __shfl_sync(FULL, base, 0);
+                        int done = 0;
+                        for (int i0 = 0; i0 < T2 && done < kept; i0 += 32) {
+                            const Slot sv = t2[i0 + lane];
+                            const unsigned ob = __ballot_sync(FULL, sv != EMPTY);
+                            const int64_t at = (int64_t)base + done + __popc(ob & lt_mask);
+                            if (sv != EMPTY && at < capacity) {
+                                out_idx[at] = (int32_t)(sv >> cb);
+                                out_val[at] = (int32_t)(sv & cmask);
+                            }
+                            done += __popc(ob);
+                        }
+                        for (int i = lane; i < tsize; i += 32) table[i] = EMPTY;
+                    }
+                    __syncwarp();
+                    if (lane < 4) reinterpret_cast<unsigned*>(wbase + L::BUF)[lane] = 0u;   // the slack before the text
+                }
+                if (!ordered) {
+                    // compact the kept buckets to the front of the table as (new position | value) ...
+                    kept = 0;
+                    for (int i0 = 0; i0 < tsize; i0 += 32) {
+                        const Slot sv = table[i0 + lane];
+                        int np = -1;
+                        unsigned val = 0u;
+                        if (sv != EMPTY) {
+                            const unsigned v = (unsigned)(sv >> cb);
+                            np = newpos[v];
+                            val = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
+                        }
+                        const unsigned kb = __ballot_sync(FULL, np >= 0);
+                        table[i0 + lane] = EMPTY;
+                        __syncwarp();
+                        if (np >= 0) table[kept + __popc(kb & lt_mask)] = (Slot((unsigned)np) << cb) | Slot(val);
+                        kept += __popc(kb);
                         __syncwarp();
                     }
-                }
-                // ... and write the sparse row
-                unsigned long long base = 0;
-                if (lane == 0) {
-                    base = atomicAdd(cursor, (unsigned long long)kept);
-                    row_start[row] = (int64_t)base;
-                    row_nnz[row] = kept;
-                    if ((int64_t)base + kept > capacity) flags[3] = 1;
-                }
-                base = __shfl_sync(FULL, base, 0);
-                for (int i = lane; i < kept; i += 32) {
-                    const Slot sv = table[i];
-                    table[i] = EMPTY;
-                    const int64_t at = (int64_t)base + i;
-                    if (at < capacity) {
-                        out_idx[at] = (int32_t)(sv >> cb);
-                        out_val[at] = (int32_t)(sv & cmask);
+                    // ... sort them (bitonic, the padding EMPTY sorts last) ...
+                    int m = 32;
+                    while (m < kept) m <<= 1;
+                    for (int k2 = 2; k2 <= m; k2 <<= 1) {
+                        for (int jj = k2 >> 1; jj > 0; jj >>= 1) {
+                            for (int t = lane; t < (m >> 1); t += 32) {
+                                const int i = ((t & ~(jj - 1)) << 1) | (t & (jj - 1));
+                                const int ixj = i | jj;
+                                const Slot x = table[i], y = table[ixj];
+                                const bool up = (i & k2) == 0;
+                                if ((x > y) == up) {
+                                    table[i] = y;
+                                    table[ixj] = x;
+                                }
+                            }
+                            __syncwarp();
+                        }
+                    }
+                    // ... and write the sparse row
+                    unsigned long long base = 0;
+                    if (lane == 0) {
+                        base = atomicAdd(cursor, (unsigned long long)kept);
+                        row_start[row] = (int64_t)base;
+                        row_nnz[row] = kept;
+                        if ((int64_t)base + kept > capacity) flags[3] = 1;
+                    }
+                    base = __shfl_sync(FULL, base, 0);
+                    for (int i = lane; i < kept; i += 32) {
+                        const Slot sv = table[i];
+                        table[i] = EMPTY;
+                        const int64_t at = (int64_t)base + i;
+                        if (at < capacity) {
+                            out_idx[at] = (int32_t)(sv >> cb);
+                            out_val[at] = (int32_t)(sv & cmask);
+                        }
                     }
                 }
             }
