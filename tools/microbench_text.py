@@ -92,5 +92,5 @@ def tr():
     L.call("tmog_text_hash_transform_dev", d_desc.data_ptr(), ncols, n, d_prefix.data_ptr(), d_plen.data_ptr(), params2.ctypes.data,
            newpos.data_ptr(), row_start.data_ptr(), row_nnz.data_ptr(), idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), cap, flags.data_ptr(), scratch.data_ptr(), scratch.numel(), st)
 t2 = timeit(tr)
-print("deferred rows:", int(scratch[16:20].view(torch.int32).item()))
+print("deferred rows:", scratch[24:32].view(torch.int32).tolist())
 print(f"hash-transform: {t2:.2f} ms  {n / t2 * 1e3 / 1e6:.2f} M rows/s  nnz {int(cursor.item())} cap {cap} flags {flags.cpu().tolist()}")

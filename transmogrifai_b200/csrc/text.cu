@@ -288,6 +288,7 @@ struct TextHashParams {
     int nclasses;
     int pow2_mask;         // num_features - 1 if it is a power of two, else -1
     int count_bits;        // low bits of a table slot that hold the count (the key sits above)
+    int max_token_bound;   // rows with more possible tokens (bytes / 2) than this go to the next level right away
 };
 
 struct StopSlot {          // stop-word table in shared memory: length + the word packed little-endian in 3 words
@@ -522,6 +523,10 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
             }
             for (int o = 16; o > 0; o >>= 1) bytes_bound += __shfl_xor_sync(FULL, bytes_bound, o);
             bytes_bound += ncols;
+            if (defer_list && bytes_bound > p.max_token_bound) {      // too long for this level's table
+                if (lane == 0) defer_list[atomicAdd(defer_n, 1u)] = (int32_t)row;
+                continue;
+            }
             int tbits = 6;
             while (tbits < 31 && (1ll << tbits) < 2 * bytes_bound && (1 << tbits) < T) ++tbits;
             const int tsize = 1 << tbits;
@@ -1168,39 +1173,16 @@ extern "C" int tmog_text_codes_dev(const int64_t* col_desc, const int32_t* col_i
     return TMOG_OK;
 }
 
-static int text_hash_common(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
-                            const int32_t* prefix_len, const int32_t* params, TextHashParams* p) {
-    TMOG_REQUIRE(ncols >= 0 && n >= 0, "bad shape");
-    TMOG_REQUIRE(col_desc && prefix && prefix_len && params, "NULL argument");
-    p->num_features = params[0];
-    p->shared = params[1];
-    p->binary_freq = params[2];
-    p->min_token_length = params[3];
-    p->track_nulls = params[4];
-    p->prepend = params[5];
-    p->null_base = params[6];
-    p->nclasses = params[7];
-    TMOG_REQUIRE(p->num_features > 0 && p->num_features <= 10000000,
-                 "requirement failed: numFeatures must be in (0, 10000000], got %d", p->num_features);
-    TMOG_REQUIRE(p->nclasses >= 1 && p->nclasses <= 255, "nclasses must be in [1, 255]");
-    const int64_t hw = p->shared ? p->num_features : (int64_t)p->num_features * ncols;
-    TMOG_REQUIRE(hw + ncols < 0x7fffffffLL, "hash block too wide");
-    p->hash_width = (int)hw;
-    TMOG_REQUIRE(p->null_base >= p->hash_width, "null_base must not overlap the hash block");
-    return upload_stop_words();
-}
-
-// scratch of the tokenise + hash entry points: two row counters, the number of deferred rows, the deferred rows
+// scratch of the tokenise + hash entry points: a row counter per level, the lengths of the two lists of deferred rows,
+// the lists
 struct ThScratch {
-    unsigned long long row_counter;
-    unsigned long long defer_counter;
-    unsigned defer_n;
-    unsigned pad[3];
+    unsigned long long row_counter[3];
+    unsigned defer_n[2];
 };
 
 extern "C" int tmog_text_hash_scratch_bytes(int64_t n, size_t* bytes) {
     TMOG_REQUIRE(bytes != nullptr && n >= 0 && n < 0x7fffffffLL, "bad arguments");
-    *bytes = sizeof(ThScratch) + sizeof(int32_t) * (size_t)n;
+    *bytes = sizeof(ThScratch) + 2 * sizeof(int32_t) * (size_t)n;
     return TMOG_OK;
 }
 
@@ -1225,8 +1207,9 @@ struct ThArgs {
     cudaStream_t stream;
 };
 
+// level 0 reads all rows, level 1 the rows level 0 deferred, level 2 the rows level 1 deferred
 template <typename Slot, int T, int TB, int WARPS, bool SPARSE_OUT>
-static int th_launch(const ThArgs& a, bool deferred_pass) {
+static int th_launch(const ThArgs& a, int level, int max_token_bound) {
     auto kernel = text_hash_kernel<Slot, T, TB, WARPS, SPARSE_OUT>;
     const size_t smem = STOP_SLOTS * sizeof(StopSlot) + TH_COLCACHE * 12 + 32 + (size_t)WARPS * ThLayout<Slot, T, TB>::BYTES;
     TMOG_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -1234,21 +1217,24 @@ static int th_launch(const ThArgs& a, bool deferred_pass) {
     TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, WARPS * 32, smem));
     TMOG_REQUIRE(per_sm >= 1, "text hash kernel does not fit an SM");
     int64_t grid = (int64_t)sm_count() * per_sm;
-    if (!deferred_pass) grid = std::max<int64_t>(1, std::min<int64_t>(grid, (a.n + WARPS - 1) / WARPS));
-    int32_t* list = reinterpret_cast<int32_t*>(a.scratch + 1);
+    if (level == 0) grid = std::max<int64_t>(1, std::min<int64_t>(grid, (a.n + WARPS - 1) / WARPS));
+    int32_t* lists = reinterpret_cast<int32_t*>(a.scratch + 1);
+    TextHashParams p = a.p;
+    p.max_token_bound = max_token_bound;
     kernel<<<(int)grid, WARPS * 32, smem, a.stream>>>(
-        a.cols, a.ncols, a.n, a.prefix, a.prefix_len, a.p, a.class_ids,
-        deferred_pass ? list : nullptr, deferred_pass ? &a.scratch->defer_n : nullptr,
-        deferred_pass ? &a.scratch->defer_counter : &a.scratch->row_counter,
-        deferred_pass ? nullptr : list, deferred_pass ? nullptr : &a.scratch->defer_n,
+        a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, a.class_ids,
+        level == 0 ? nullptr : lists + (size_t)(level - 1) * a.n, level == 0 ? nullptr : &a.scratch->defer_n[level - 1],
+        &a.scratch->row_counter[level],
+        level == 2 ? nullptr : lists + (size_t)level * a.n, level == 2 ? nullptr : &a.scratch->defer_n[level],
         a.class_sum, a.dup, a.sq_extra, a.aux, a.newpos, a.row_start, a.row_nnz, a.out_idx, a.out_val, a.cursor,
         a.capacity, a.flags);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }
 
-// fast variant with packed 32-bit slots when the key leaves >= 8 bits for the count, else 64-bit slots; then the rows
-// either of them deferred, with a table that takes most of the shared memory of an SM
+// Three launches, by the size of the row's table: rows whose text is short enough for about 768 distinct buckets run
+// with 24 warps per SM, rows up to about 1536 with 16 warps per SM, the rest (and whatever overflowed a smaller table)
+// with 64-bit slots in most of the shared memory of an SM.  Packed 32-bit slots need >= 8 bits left for the count.
 template <bool SPARSE_OUT>
 static int th_run(ThArgs& a) {
     TMOG_CUDA(cudaMemsetAsync(a.scratch, 0, sizeof(ThScratch), a.stream));
@@ -1257,13 +1243,15 @@ static int th_run(ThArgs& a) {
     while ((1ll << key_bits) - 1 <= max_key) ++key_bits;
     if (key_bits <= 24) {
         a.p.count_bits = 32 - key_bits;
-        if (int rc = th_launch<unsigned, 2048, 2048, 8, SPARSE_OUT>(a, false)) return rc;
+        if (int rc = th_launch<unsigned, 1024, 2048, 12, SPARSE_OUT>(a, 0, 3072)) return rc;
+        if (int rc = th_launch<unsigned, 2048, 2048, 8, SPARSE_OUT>(a, 1, 6144)) return rc;
     } else {
         a.p.count_bits = 32;
-        if (int rc = th_launch<unsigned long long, 1024, 2048, 8, SPARSE_OUT>(a, false)) return rc;
+        if (int rc = th_launch<unsigned long long, 512, 2048, 12, SPARSE_OUT>(a, 0, 1536)) return rc;
+        if (int rc = th_launch<unsigned long long, 1024, 2048, 8, SPARSE_OUT>(a, 1, 3072)) return rc;
     }
     a.p.count_bits = 32;
-    return th_launch<unsigned long long, 16384, 4096, 1, SPARSE_OUT>(a, true);
+    return th_launch<unsigned long long, 16384, 4096, 1, SPARSE_OUT>(a, 2, 0x7fffffff);
 }
 
 static int text_hash_common(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
