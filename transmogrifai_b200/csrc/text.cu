@@ -917,63 +917,78 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 __syncwarp();
                 for (int i = lane; i < nrare; i += 32) th_rare_update(rare[i], bucket_dup, bucket_sq_extra, bucket_aux);
             } else {
-                // The kept buckets go out in ascending order of their new position.  Fast way: an ordered scatter --
-                // (new position | value) is pushed into a second table at a slot proportional to the bucket index,
-                // every slot keeping the smaller of what it holds and what arrives and passing the larger on, so that
-                // reading that table front to back gives the sorted row.  It lives in the text buffer and the token
-                // list (free by now); when the row is too crowded for it, or the scatter runs off its end, the table is
-                // compacted and bitonic-sorted in place instead.
+                // The kept buckets go out in ascending order of their new position.  They are first compacted to the
+                // front of the table as (new position | value).  Fast way to order them: an ordered scatter -- every
+                // entry is pushed into a second table at a slot proportional to its new position, each slot keeping
+                // the smaller of what it holds and what arrives and passing the larger on, so that reading that table
+                // front to back gives the sorted row.  It lives in the text buffer and the token list (free by now); a
+                // crowded row takes several phases, each over a slice of the positions.  When the scatter runs off the
+                // end of its table (skewed positions) the compacted list is bitonic-sorted in place instead.
                 Slot* t2 = reinterpret_cast<Slot*>(wbase + L::BUF);
                 constexpr int T2 = L::T2;
-                int kept = 0;
-                bool ordered = ndist <= T2 / 2 + T2 / 8;
-                if (ordered) {
-                    for (int i = lane; i < T2; i += 32) t2[i] = EMPTY;
+                int kept = 0, np_min = 0x7fffffff, np_max = -1;
+                for (int i0 = 0; i0 < tsize; i0 += 32) {
+                    const Slot sv = table[i0 + lane];
+                    int np = -1;
+                    unsigned val = 0u;
+                    if (sv != EMPTY) {
+                        const unsigned v = (unsigned)(sv >> cb);
+                        np = newpos[v];
+                        val = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
+                    }
+                    const unsigned kb = __ballot_sync(FULL, np >= 0);
+                    table[i0 + lane] = EMPTY;
                     __syncwarp();
-                    const float scale = (float)(T2 - 64) / (float)(p.null_base + ncols);
-                    bool fail = false;
-                    for (int i0 = 0; i0 < tsize; i0 += 1024) {
-                        const int lim = min(32, (tsize - i0) >> 5);
-                        unsigned occ = 0u;
-                        for (int b = 0; b < lim; ++b) occ |= (table[i0 + (b << 5) + lane] != EMPTY ? 1u : 0u) << b;
-                        while (__any_sync(FULL, occ != 0u)) {
-                            int np = -1;
-                            if (occ) {
-                                const Slot sv = table[i0 + ((__ffs(occ) - 1) << 5) + lane];
-                                occ &= occ - 1u;
-                                const unsigned v = (unsigned)(sv >> cb);
-                                np = newpos[v];
-                                if (np >= 0) {
-                                    const unsigned val =
-                                        (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
-                                    Slot x = (Slot((unsigned)np) << cb) | Slot(val);
-                                    int slot = min((int)((float)v * scale), T2 - 64);
-                                    for (;;) {
-                                        const Slot old = atomicMin(&t2[slot], x);
-                                        if (old == EMPTY) break;
-                                        x = old > x ? old : x;
-                                        if (++slot >= T2) {
-                                            fail = true;
-                                            break;
-                                        }
-                                    }
+                    if (np >= 0) {
+                        table[kept + __popc(kb & lt_mask)] = (Slot((unsigned)np) << cb) | Slot(val);
+                        np_min = min(np_min, np);
+                        np_max = max(np_max, np);
+                    }
+                    kept += __popc(kb);
+                    __syncwarp();
+                }
+                np_min = __reduce_min_sync(FULL, np_min);
+                np_max = __reduce_max_sync(FULL, np_max);
+                unsigned long long base = 0;
+                if (lane == 0) {
+                    base = atomicAdd(cursor, (unsigned long long)kept);
+                    row_start[row] = (int64_t)base;
+                    row_nnz[row] = kept;
+                    if ((int64_t)base + kept > capacity) flags[3] = 1;
+                }
+                base = __shfl_sync(FULL, base, 0);
+                const int phases = max(1, (kept + T2 / 2 - 1) / (T2 / 2));
+                bool ordered = kept > 0 && phases <= 8;
+                if (ordered) {
+                    const unsigned long long span = (unsigned long long)(np_max - np_min) + 1ull;
+                    int done = 0;
+                    for (int ph = 0; ph < phases; ++ph) {
+                        const int lo_p = np_min + (int)(span * ph / phases);
+                        const int hi_p = np_min + (int)(span * (ph + 1) / phases);
+                        const float scale = (float)(T2 - 64) / (float)(hi_p - lo_p);
+                        for (int i = lane; i < T2; i += 32) t2[i] = EMPTY;
+                        __syncwarp();
+                        bool fail = false;
+                        for (int i = lane; i < kept; i += 32) {
+                            Slot x = table[i];
+                            const int np = (int)(x >> cb);
+                            if (np < lo_p || np >= hi_p) continue;
+                            int slot = min((int)((float)(np - lo_p) * scale), T2 - 64);
+                            for (;;) {
+                                const Slot old = atomicMin(&t2[slot], x);
+                                if (old == EMPTY) break;
+                                x = old > x ? old : x;
+                                if (++slot >= T2) {
+                                    fail = true;
+                                    break;
                                 }
                             }
-                            kept += __popc(__ballot_sync(FULL, np >= 0));
                         }
-                    }
-                    __syncwarp();
-                    ordered = !__any_sync(FULL, fail);
-                    if (ordered) {
-                        unsigned long long base = 0;
-                        if (lane == 0) {
-                            base = atomicAdd(cursor, (unsigned long long)kept);
-                            row_start[row] = (int64_t)base;
-                            row_nnz[row] = kept;
-                            if ((int64_t)base + kept > capacity) flags[3] = 1;
+                        __syncwarp();
+                        if (__any_sync(FULL, fail)) {
+                            ordered = false;
+                            break;
                         }
-                        base = __shfl_sync(FULL, base, 0);
-                        int done = 0;
                         for (int i0 = 0; i0 < T2 && done < kept; i0 += 32) {
                             const Slot sv = t2[i0 + lane];
                             const unsigned ob = __ballot_sync(FULL, sv != EMPTY);
@@ -984,31 +999,14 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                             }
                             done += __popc(ob);
                         }
-                        for (int i = lane; i < tsize; i += 32) table[i] = EMPTY;
+                        __syncwarp();
                     }
-                    __syncwarp();
-                    if (lane < 4) reinterpret_cast<unsigned*>(wbase + L::BUF)[lane] = 0u;   // the slack before the text
+                    if (ordered)
+                        for (int i = lane; i < kept; i += 32) table[i] = EMPTY;
                 }
+                __syncwarp();
+                if (lane < 4) reinterpret_cast<unsigned*>(wbase + L::BUF)[lane] = 0u;       // the slack before the text
                 if (!ordered) {
-                    // compact the kept buckets to the front of the table as (new position | value) ...
-                    kept = 0;
-                    for (int i0 = 0; i0 < tsize; i0 += 32) {
-                        const Slot sv = table[i0 + lane];
-                        int np = -1;
-                        unsigned val = 0u;
-                        if (sv != EMPTY) {
-                            const unsigned v = (unsigned)(sv >> cb);
-                            np = newpos[v];
-                            val = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
-                        }
-                        const unsigned kb = __ballot_sync(FULL, np >= 0);
-                        table[i0 + lane] = EMPTY;
-                        __syncwarp();
-                        if (np >= 0) table[kept + __popc(kb & lt_mask)] = (Slot((unsigned)np) << cb) | Slot(val);
-                        kept += __popc(kb);
-                        __syncwarp();
-                    }
-                    // ... sort them (bitonic, the padding EMPTY sorts last) ...
                     int m = 32;
                     while (m < kept) m <<= 1;
                     for (int k2 = 2; k2 <= m; k2 <<= 1) {
@@ -1026,15 +1024,6 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                             __syncwarp();
                         }
                     }
-                    // ... and write the sparse row
-                    unsigned long long base = 0;
-                    if (lane == 0) {
-                        base = atomicAdd(cursor, (unsigned long long)kept);
-                        row_start[row] = (int64_t)base;
-                        row_nnz[row] = kept;
-                        if ((int64_t)base + kept > capacity) flags[3] = 1;
-                    }
-                    base = __shfl_sync(FULL, base, 0);
                     for (int i = lane; i < kept; i += 32) {
                         const Slot sv = table[i];
                         table[i] = EMPTY;
