@@ -34,6 +34,15 @@ __device__ __forceinline__ bool is_punct(unsigned c) {  // java \p{Punct}: the 3
 }
 __device__ __forceinline__ unsigned to_lower(unsigned c) { return (c - 'A') < 26u ? c + 32u : c; }
 
+// bytes [lo, hi) of a word kept (lo, hi relative to the word, any range)
+__device__ __forceinline__ unsigned byte_range_mask(int lo, int hi) {
+    lo = max(lo, 0);
+    hi = min(hi, 4);
+    if (hi <= lo) return 0u;
+    const unsigned upto_hi = hi == 4 ? 0xffffffffu : (1u << (8 * hi)) - 1u;
+    return upto_hi & ~((1u << (8 * lo)) - 1u);
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // Spark 2.4.5 mllib HashingTF: Murmur3_x86_32.hashUnsafeBytes (legacy tail handling), seed 42
 // ------------------------------------------------------------------------------------------------------------------
@@ -143,6 +152,41 @@ __device__ __forceinline__ void clean_hash_cell(const uint8_t* s, int64_t len, b
     out_len = m;
 }
 
+// Length of the cleaned cell only (what TextStats still needs once the column is past the cardinality cap): the bytes
+// that are neither ' ' nor punctuation, counted 16 bytes per load, four bytes per step
+__device__ __forceinline__ int clean_length_cell(const uint8_t* s, int64_t len, bool clean, bool& non_ascii) {
+    if (!clean) {
+        // no cleaning: every byte counts; only the non-ASCII check needs the bytes, and it is not needed either
+        return (int)len;
+    }
+    const int sh = (int)(reinterpret_cast<uintptr_t>(s) & 15u);
+    const uint8_t* base = s - sh;
+    const int64_t nchunk = (sh + len + 15) >> 4;
+    int kept = 0;
+    unsigned na = 0u;
+    for (int64_t c = 0; c < nchunk; ++c) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(base + 16 * c));
+        const int lo = c == 0 ? sh : 0;
+        const int hi = (int)min((int64_t)16, sh + len - 16 * c);
+        const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            unsigned in = 0x80808080u;                       // bit 7 of the bytes that belong to the cell
+            if (lo != 0 || hi != 16) in &= byte_range_mask(lo - 4 * q, hi - 4 * q);
+            const unsigned h7 = w[q] & 0x7f7f7f7fu;
+            // bit 7 of (h7 + (0x80 - x) * 0x01010101) is set iff the byte is >= x
+            const unsigned drop = ((h7 + 0x60606060u) & ~(h7 + 0x50505050u)) |      // ' ' and 0x21 .. 0x2f
+                                  ((h7 + 0x46464646u) & ~(h7 + 0x3f3f3f3fu)) |      // ':' .. '@'
+                                  ((h7 + 0x25252525u) & ~(h7 + 0x1f1f1f1fu)) |      // '[' .. '`'
+                                  ((h7 + 0x05050505u) & ~(h7 + 0x01010101u));       // '{' .. '~'
+            na |= w[q] & in;
+            kept += __popc(in & ~(drop & ~w[q]));
+        }
+    }
+    if (na) non_ascii = true;
+    return kept;
+}
+
 constexpr unsigned long long TS_EMPTY = 0xFFFFFFFFFFFFFFFFull;
 
 // per column: table of `slots` entries {hash, first_row}, counts [slots][nclasses] u32, ndistinct, overflow flag
@@ -197,10 +241,15 @@ text_stats_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
     for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
         if (!cell_valid(tc, r)) continue;
         const int64_t a = tc.offsets[r], b = tc.offsets[r + 1];
-        unsigned long long h;
         int m;
-        clean_hash_cell(tc.data + a, b - a, clean != 0, h, m, non_ascii);
-        ts_insert(t, slots, max_distinct, h, r, nclasses > 1 ? class_ids[r] : 0, nclasses);
+        if (*t.ndistinct > max_distinct) {
+            // past the cardinality cap nothing more is recorded for the column but the lengths
+            m = clean_length_cell(tc.data + a, b - a, clean != 0, non_ascii);
+        } else {
+            unsigned long long h;
+            clean_hash_cell(tc.data + a, b - a, clean != 0, h, m, non_ascii);
+            ts_insert(t, slots, max_distinct, h, r, nclasses > 1 ? class_ids[r] : 0, nclasses);
+        }
         lsum += (unsigned long long)m;
         lsq += (unsigned long long)m * (unsigned long long)m;
         ++nn;
@@ -313,14 +362,6 @@ __device__ __forceinline__ unsigned lower4(unsigned w) {
     const unsigned ge_a = h + 0x3f3f3f3fu;      // bit 7 of a byte set iff it is >= 'A'
     const unsigned gt_z = h + 0x25252525u;      // bit 7 set iff > 'Z'
     return w | ((ge_a & ~gt_z & ~w & 0x80808080u) >> 2);
-}
-// bytes [lo, hi) of a word kept (lo, hi relative to the word, any range)
-__device__ __forceinline__ unsigned byte_range_mask(int lo, int hi) {
-    lo = max(lo, 0);
-    hi = min(hi, 4);
-    if (hi <= lo) return 0u;
-    const unsigned upto_hi = hi == 4 ? 0xffffffffu : (1u << (8 * hi)) - 1u;
-    return upto_hi & ~((1u << (8 * lo)) - 1u);
 }
 
 constexpr int th_pow2_floor(int x) {
