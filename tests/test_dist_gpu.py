@@ -1,0 +1,132 @@
+"""Two ranks on one GPU (gloo for the small host-side exchanges, both processes computing on cuda:0): the row-sharded
+fit of every vectorizer + SanityChecker gives the statistics, vocabularies, decisions and dropped set of the whole
+dataset, and each rank's transform gives its own rows."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+import torch.distributed as dist  # noqa: E402
+import torch.multiprocessing as mp  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _make_data(n):
+    from transmogrifai_b200 import features as F
+    rng = np.random.default_rng(77)
+    y = (rng.random(n) < 0.3).astype(np.float64)
+    opt = lambda v, p: None if rng.random() < p else v   # noqa: E731
+    b0 = [opt(bool(rng.random() < 0.4 + 0.3 * yy), 0.1) for yy in y]
+    p0 = [opt(["x", "y", "z", "X ", "w"][int(rng.integers(5))], 0.08) for _ in y]
+    r0 = [opt(float(rng.normal(2 + yy, 1)), 0.1) for yy in y]
+    nn = [float(v) for v in rng.normal(5, 2, n)]
+    words = ["".join(rng.choice(list("abcdefgh"), size=rng.integers(3, 7))) for _ in range(150)]
+    t0 = [opt(" ".join(words[i] for i in rng.integers(0, 150, rng.poisson(8))), 0.06) for _ in y]
+    # low-cardinality text: pivoted; its values arrive in a different order on the two shards
+    t1 = [opt(["red", "Green", "blue", "blue!", "teal"][int(rng.integers(5 if i > n // 2 else 3))], 0.05)
+          for i in range(n)]
+    # "the the ..." in every row: a hashed bucket met twice or more in all rows (column minimum 2)
+    t2 = ["zq zq " * int(rng.integers(1, 3)) + words[int(rng.integers(150))] for _ in y]
+    return {"b0": (F.BINARY, b0), "p0": (F.PICKLIST, p0), "r0": (F.REAL, r0), "nn": (F.REALNN, nn), "t0": (F.TEXT, t0),
+            "t1": (F.TEXT, t1), "t2": (F.TEXT, t2), "y": (F.REALNN, y.tolist())}, y
+
+
+def _worker(rank, size, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=size)
+    try:
+        from oracle import sanity as S
+        from oracle import vectorizers as V
+        from transmogrifai_b200 import dist as D
+        from transmogrifai_b200 import features as F
+        from transmogrifai_b200.columnar import ColumnarBatch
+        from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+        n = 5000
+        data, y = _make_data(n)
+        lo, hi = D.shard_rows(n, rank, size)
+        assert hi > lo
+        shard = {k: (t, v[lo:hi]) for k, (t, v) in data.items()}
+        batch = ColumnarBatch.from_columns(shard, response="y").to("cuda")
+        FB = F.FeatureBuilder
+        feats = [FB.Text("t0").asPredictor(), FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(),
+                 FB.RealNN("nn").asPredictor(), FB.PickList("p0").asPredictor(), FB.Text("t1").asPredictor(),
+                 FB.Text("t2").asPredictor()]
+        label = FB.RealNN("y").asResponse()
+        checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
+                                    sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
+        out_batch, fitted = fit_and_transform(batch, checked)
+        est = checked.origin_stage
+        # oracle on the whole dataset
+        col = lambda k: data[k][1]   # noqa: E731
+        xb = V.binary_vectorizer_transform([col("b0")])
+        tops = V.pivot_fit([col("p0")], 20, 10, True)
+        xp = V.pivot_transform([col("p0")], tops, True, True)
+        fills = V.real_vectorizer_fit([col("r0")])
+        xr = V.real_vectorizer_transform([col("r0")], fills, True)
+        xn = V.realnn_vectorizer_transform([col("nn")])
+        tcols, tnames = [col("t0"), col("t1"), col("t2")], ["t0", "t1", "t2"]
+        methods, ttops = V.smart_text_fit(tcols, max_cardinality=30, top_k=20, min_support=10)
+        assert methods == ["Hash", "Pivot", "Hash"]
+        xt = V.smart_text_transform(tcols, tnames, methods, ttops, num_features=512)
+        xo, metas = V.combine(
+            [xb, xp, xr, xn, xt],
+            [V.numeric_metadata(["b0"], "Binary", True), V.pivot_metadata(["p0"], "PickList", tops, True),
+             V.numeric_metadata(["r0"], "Real", True), V.numeric_metadata(["nn"], "RealNN", False),
+             V.smart_text_metadata(tnames, "Text", methods, ttops, 512, True)])
+        p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                           feature_feature_corr_level="off")
+        ref = S.sanity_fit(y, xo, metas, p, label_name="y")
+        exp_names = [m.col_name() for m in metas]
+        got_names = est.summary.names[:-1]
+        assert got_names == exp_names, [(i, a, b) for i, (a, b) in enumerate(zip(got_names, exp_names)) if a != b][:6] + \
+            [len(got_names), len(exp_names)]
+        assert est.summary.dropped == ref.dropped
+        assert fitted[-1].indicesToKeep == ref.indices_to_keep
+        bad = np.nonzero(~np.isclose(est.summary.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300))[0]
+        assert len(bad) == 0, [(int(i), (exp_names + ["y"])[i], est.summary.mean[i], ref.col_stats.mean[i]) for i in bad[:6]]
+        np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+        assert np.array_equal(est.summary.min, ref.col_stats.min) and np.array_equal(est.summary.max, ref.col_stats.max)
+        assert ref.col_stats.min.max() >= 2.0          # the "zq zq" bucket: met at least twice in every row
+        np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                                   equal_nan=True)
+        got_g = {g.group: g for g in est.summary.categoricalStats}
+        assert got_g.keys() == {g.group for g in ref.cat_stats}
+        for g in ref.cat_stats:
+            assert np.array_equal(got_g[g.group].contingencyMatrix, g.contingency_matrix)
+            np.testing.assert_allclose(got_g[g.group].cramersV, g.cramers_v, rtol=1e-9, equal_nan=True)
+        got = out_batch.vectors[checked.name].to_scipy()
+        exp = xo[lo:hi][:, ref.indices_to_keep]
+        assert got.shape == exp.shape
+        np.testing.assert_allclose(np.asarray(got.todense()), np.asarray(exp.todense()) if hasattr(exp, "todense") else exp,
+                                   rtol=1e-12)
+        q.put((rank, "ok"))
+    except Exception:  # pragma: no cover
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_all_types_match_oracle():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, "ok"), (1, "ok")], "\n".join(str(r[1]) for r in res)

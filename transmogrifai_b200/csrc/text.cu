@@ -449,7 +449,7 @@ __device__ __forceinline__ void th_rare_update(uint2 e, unsigned* bucket_dup, un
     atomicAdd(&bucket_dup[v], cnt - 1u);
     atomicAdd(&bucket_sq_extra[v], (unsigned long long)cnt * cnt - cnt);
     atomicMax(&bucket_aux[3 * (int64_t)v], cnt);
-    atomicMin(&bucket_aux[3 * (int64_t)v + 1], ~cnt);
+    atomicMax(&bucket_aux[3 * (int64_t)v + 1], ~cnt);      // the largest complement = the smallest count
     atomicAdd(&bucket_aux[3 * (int64_t)v + 2], 1u);
 }
 

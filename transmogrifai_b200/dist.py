@@ -57,6 +57,31 @@ def allreduce_sum(a: np.ndarray) -> np.ndarray:
     return t.cpu().numpy()
 
 
+def allreduce_max(a: np.ndarray) -> np.ndarray:
+    if world()[1] == 1:
+        return a
+    t = torch.from_numpy(np.ascontiguousarray(a)).to(_device())
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.cpu().numpy()
+
+
+def all_gather_object(obj) -> list:
+    """Small driver-side objects of every rank, in rank order (TextStats maps: what Spark's reduce would merge)."""
+    if world()[1] == 1:
+        return [obj]
+    out = [None] * world()[1]
+    dist.all_gather_object(out, obj)
+    return out
+
+
+def broadcast_object(obj, src: int = 0):
+    if world()[1] == 1:
+        return obj
+    box = [obj if world()[0] == src else None]
+    dist.broadcast_object_list(box, src=src, device=_device())
+    return box[0]
+
+
 def union_classes(local: Optional[np.ndarray], cap: int = 255) -> Optional[np.ndarray]:
     """Union of every rank's sorted distinct label values; None if any rank (or the union) exceeds `cap`."""
     if world()[1] == 1:

@@ -110,6 +110,27 @@ class OpTextPivotVectorizer(OpEstimator):
                      for v in vals]
         return OpVectorMetadata(self.getOutputFeatureName(), cols, self.history())
 
+    @staticmethod
+    def _union_dictionaries(block):
+        """-> (dictionary per column valid on every rank, per column the map local code -> code in it, or None where
+        all ranks already share one dictionary)."""
+        ncols = len(block.dicts)
+        if D.world()[1] == 1:
+            return block.dicts, [None] * ncols
+        sigs = D.all_gather_object([_dict_signature(d) for d in block.dicts])
+        differ = [c for c in range(ncols) if any(s[c] != sigs[0][c] for s in sigs)]
+        dicts, maps = list(block.dicts), [None] * ncols
+        if differ:
+            gathered = D.all_gather_object([block.dicts[c] for c in differ])
+            for t, c in enumerate(differ):
+                index = {}
+                for per_rank in gathered:
+                    for v in per_rank[t]:
+                        index.setdefault(v, len(index))
+                dicts[c] = list(index)
+                maps[c] = np.array([index[v] for v in block.dicts[c]], dtype=np.int64)
+        return dicts, maps
+
     def fit(self, batch: ColumnarBatch) -> "OpTextPivotVectorizerModel":
         R.require_cuda()
         names = [f.name for f in self.inN]
@@ -136,21 +157,42 @@ class OpTextPivotVectorizer(OpEstimator):
         L.call("tmog_pivot_count_dev", dev.codes.data_ptr(), dev.ld, n, ncols,
                ids.data_ptr() if classes is not None else None, ncls, d_desc.data_ptr(), None,
                int(nids.max()) if ncols else 1, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
-        counts = D.allreduce_sum(d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF)
+        counts = d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF
         if int(d_bad.item()):
             raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
         n_global = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
+        # Ranks may have encoded their rows against different dictionaries (one per exported partition): the count
+        # tables are then re-indexed against the union dictionary (rank order) before they are summed.
+        g_dicts, g_maps = self._union_dictionaries(block)
+        g_ncodes = np.array([len(d) for d in g_dicts], dtype=np.int64)
+        g_offset = np.concatenate([[0], np.cumsum((g_ncodes + 1) * ncls)[:-1]]).astype(np.int64) if ncols else zeros
+        if any(m is not None for m in g_maps):
+            g_counts = np.zeros(int(((g_ncodes + 1) * ncls).sum()), dtype=np.int64)
+            for c in range(ncols):
+                loc = counts[count_offset[c]:count_offset[c] + nids[c] * ncls].reshape(int(nids[c]), ncls)
+                dst = g_counts[g_offset[c]:g_offset[c] + (g_ncodes[c] + 1) * ncls].reshape(int(g_ncodes[c]) + 1, ncls)
+                if g_maps[c] is None:
+                    dst[:] = loc
+                else:
+                    dst[0] = loc[0]                                   # the null id
+                    dst[1 + g_maps[c]] = loc[1:]
+            counts = g_counts
+        counts = D.allreduce_sum(counts)
 
         def finish(c: int):
-            data, offs = block.dict_arrays(c)
-            raw = np.ascontiguousarray(counts[count_offset[c]:count_offset[c] + nids[c] * ncls])
+            if g_maps[c] is None:
+                data, offs = block.dict_arrays(c)
+            else:
+                data, offs = encode_strings(g_dicts[c])
+            nc = int(g_ncodes[c])
+            raw = np.ascontiguousarray(counts[g_offset[c]:g_offset[c] + (nc + 1) * ncls])
             k = self.topK
             n_top = C.c_int(0)
-            code_to_out = np.zeros(max(int(ncodes[c]), 1), dtype=np.int32)
+            code_to_out = np.zeros(max(nc, 1), dtype=np.int32)
             per_class = np.zeros((k + 2) * ncls, dtype=np.int64)
             top_data = np.zeros(max(len(data), 1), dtype=np.uint8)
             top_offs = np.zeros(k + 1, dtype=np.int64)
-            L.call("tmog_pivot_column_finish", data.ctypes.data, offs.ctypes.data, int(ncodes[c]),
+            L.call("tmog_pivot_column_finish", data.ctypes.data, offs.ctypes.data, nc,
                    int(self.cleanText), raw.ctypes.data, ncls, k, self.minSupport, C.byref(n_top),
                    code_to_out.ctypes.data, per_class.ctypes.data, top_data.ctypes.data, len(top_data),
                    top_offs.ctypes.data)
@@ -159,7 +201,8 @@ class OpTextPivotVectorizer(OpEstimator):
             rows = per_class.reshape(k + 2, ncls)[:t + 2]
             if not self.trackNulls:
                 rows = rows[:t + 1]
-            return top, code_to_out[:int(ncodes[c])], rows.astype(np.float64)
+            local = code_to_out[:nc] if g_maps[c] is None else code_to_out[:nc][g_maps[c]]
+            return top, local, rows.astype(np.float64)
 
         results = list(_pool().map(finish, range(ncols))) if ncols > 1 else [finish(c) for c in range(ncols)]
         tops = [r[0] for r in results]
@@ -176,6 +219,15 @@ class OpTextPivotVectorizer(OpEstimator):
 
 
 _POOL = None
+
+
+def _dict_signature(d: List[str]) -> str:
+    import hashlib
+    h = hashlib.sha1()
+    for v in d:
+        h.update(v.encode("utf-8", "surrogatepass"))
+        h.update(b"\x00")
+    return h.hexdigest()
 
 
 def _pool():

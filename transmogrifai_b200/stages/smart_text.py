@@ -206,10 +206,9 @@ class SmartTextVectorizer(OpEstimator):
         block = batch.texts(names)
         dev = block if block.is_cuda else block.to("cuda")
         n, ncols = batch.n, len(names)
-        if D.world()[1] > 1:
-            raise NotImplementedError("SmartTextVectorizer.fit is single-rank for now")
-        # 1. TextStats per column
+        # 1. TextStats per column (merged over the ranks like the reference's reduce over partitions)
         values, totals = self._text_stats(dev, n)
+        values = self._merge_text_stats(values, dev, n)
         methods, tops = [], []
         for c in range(ncols):
             m, top = self._decide(values[c], totals[c], dev, c, n)
@@ -224,7 +223,8 @@ class SmartTextVectorizer(OpEstimator):
             y = y if y.is_cuda else y.cuda()
             classes, class_counts, ids = label_info_dev(batch, y, label_name)
             if classes is not None:
-                model._fit_stats = model._sidecar(dev, n, classes, class_counts, ids, label_name)
+                n_all = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
+                model._fit_stats = model._sidecar(dev, n, n_all, classes, class_counts, ids, label_name)
         model._fit_key = (block.offsets[0].data_ptr(), n)
         return model
 
@@ -268,17 +268,44 @@ class SmartTextVectorizer(OpEstimator):
             out_vals.append(vc)
         return out_vals, out_tot
 
-    def _frozen_counts(self, dev: TextBlock, c: int, n: int) -> Dict[str, int]:
+    def _merge_text_stats(self, values, dev: TextBlock, n: int):
+        """Row shards are the partitions of one dataset in rank order.  The value counts of a column add up over the
+        ranks as long as the merged map stays within maxCardinality; the rank in whose rows it would grow past the cap
+        continues the fold over its own rows in row order (that is where the reference's left fold freezes) and
+        tells the others."""
+        rank, size = D.world()
+        if size == 1:
+            return values
+        gathered = D.all_gather_object(values)
+        merged = []
+        for c in range(len(values)):
+            acc: Dict[str, int] = {}
+            freezer = None
+            for r in range(size):
+                vc = gathered[r][c]
+                if vc is not None and len(set(acc) | set(vc)) <= self.maxCardinality:
+                    for k, v in vc.items():
+                        acc[k] = acc.get(k, 0) + v
+                else:
+                    freezer = r
+                    break
+            if freezer is not None:
+                res = self._frozen_counts(dev, c, n, seed=acc) if rank == freezer else None
+                acc = D.broadcast_object(res, src=freezer)
+            merged.append(acc)
+        return merged
+
+    def _frozen_counts(self, dev: TextBlock, c: int, n: int, seed: Optional[Dict[str, int]] = None) -> Dict[str, int]:
         """TextStats of a column whose cardinality exceeds maxCardinality: the reference's left fold stops adding once
         its map holds more than maxCardinality keys (SmartTextVectorizer.scala:231-235), so only a prefix of the rows
-        counts.  Emulated in row order on a prefix fetched to the host."""
+        counts.  Emulated in row order on a prefix fetched to the host (`seed`: the map of the ranks before)."""
         rows = 4 * (self.maxCardinality + 8)
         while True:
             rows = min(rows, n)
             raws = dev.prefix_cells(c, rows)
             present = [v for v in raws if v is not None]
             ids, distinct = clean_and_group(present, self.cleanText)
-            vc: Dict[str, int] = {}
+            vc: Dict[str, int] = dict(seed or {})
             for i in ids:
                 if len(vc) > self.maxCardinality:
                     return vc
@@ -445,7 +472,8 @@ class SmartTextVectorizerModel(OpModel):
         return sub, torch.from_numpy(prefix).cuda(), torch.from_numpy(plen).cuda(), params
 
     # -- statistics sidecar --------------------------------------------------------------------------------------------
-    def _sidecar(self, dev: TextBlock, n: int, classes, class_counts, ids, label_name: str) -> VectorStats:
+    def _sidecar(self, dev: TextBlock, n: int, n_all: int, classes, class_counts, ids, label_name: str) -> VectorStats:
+        """n = local rows, n_all = rows of all ranks; the count tables and bucket sums are all-reduced."""
         ncls = len(classes)
         parts = []
         if self.pivot_idx:
@@ -462,7 +490,7 @@ class SmartTextVectorizerModel(OpModel):
             d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
             L.call("tmog_pivot_count_dev", codes.data_ptr(), ld, n, k, ids.data_ptr(), ncls, d_desc.data_ptr(), None,
                    nids, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
-            cnt = (d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(k, nids, ncls)
+            cnt = D.allreduce_sum(d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(k, nids, ncls)
             rows = []
             for t, j in enumerate(self.pivot_idx):
                 top = self.topValues[j]
@@ -475,7 +503,8 @@ class SmartTextVectorizerModel(OpModel):
                 if self.shouldTrackNulls:
                     r.append(tab[0])
                 rows.append(np.stack(r).astype(np.float64))
-            parts.append(_stats_from_class_counts(np.concatenate(rows, axis=0), classes, class_counts, n, label_name))
+            parts.append(_stats_from_class_counts(np.concatenate(rows, axis=0), classes, class_counts, n_all,
+                                                  label_name))
         lay = self.layout
         if lay.text_idx:
             if lay.ignore_idx:
@@ -501,8 +530,12 @@ class SmartTextVectorizerModel(OpModel):
             ax = (aux.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(w, 3)
             if not self.shouldTrackNulls:
                 cs, nz, ex, ax = cs[:lay.hash_width], nz[:lay.hash_width], ex[:lay.hash_width], ax[:lay.hash_width]
-            self._hash_nnz = nz
-            parts.append(_stats_from_bucket_sums(cs, nz, ex, ax, classes, class_counts, n, label_name,
+            self._hash_nnz = nz                      # of the local rows: sizes the sparse output of the same batch
+            if D.world()[1] > 1:
+                cs, nz, ex = D.allreduce_sum(cs), D.allreduce_sum(nz), D.allreduce_sum(ex)
+                ax = np.stack([D.allreduce_max(ax[:, 0].copy()), D.allreduce_max(ax[:, 1].copy()),
+                               D.allreduce_sum(ax[:, 2].copy())], axis=1)
+            parts.append(_stats_from_bucket_sums(cs, nz, ex, ax, classes, class_counts, n_all, label_name,
                                                  lay.hash_width))
         return VectorStats.concat(parts)
 
