@@ -117,7 +117,7 @@ class OpTextPivotVectorizer(OpEstimator):
         ncols = len(block.dicts)
         if D.world()[1] == 1:
             return block.dicts, [None] * ncols
-        sigs = D.all_gather_object([_dict_signature(d) for d in block.dicts])
+        sigs = D.all_gather_object([_dict_signature(*block.dict_arrays(c)) for c in range(ncols)])
         differ = [c for c in range(ncols) if any(s[c] != sigs[0][c] for s in sigs)]
         dicts, maps = list(block.dicts), [None] * ncols
         if differ:
@@ -221,12 +221,11 @@ class OpTextPivotVectorizer(OpEstimator):
 _POOL = None
 
 
-def _dict_signature(d: List[str]) -> str:
+def _dict_signature(data: np.ndarray, offs: np.ndarray) -> str:
+    """Digest of a dictionary in Arrow utf8 layout."""
     import hashlib
-    h = hashlib.sha1()
-    for v in d:
-        h.update(v.encode("utf-8", "surrogatepass"))
-        h.update(b"\x00")
+    h = hashlib.sha1(data.tobytes())
+    h.update(offs.tobytes())
     return h.hexdigest()
 
 
