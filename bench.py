@@ -159,7 +159,7 @@ def kernel_times(workload, batch, fitted, info, reps: int = 5):
             t_tr = _time(lambda: L.call("tmog_real_transform_select_dev", blk.values.data_ptr(), blk.ld,
                                         blk.valid.data_ptr(), blk.ldv, n, ncols, fills.data_ptr(), 1, mask.data_ptr(),
                                         len(keep_local), dst.data_ptr(), len(keep_local), 0, st), reps)
-            out.append({"kernel": "vec_transform_select_kernel<double, true>", "ms": t_tr,
+            out.append({"kernel": "vec_transform_pack_kernel<double, true>", "ms": t_tr,
                         "bytes_per_row": ncols * 8 + ncols / 8 + len(keep_local) * 8})
             out.append({"kernel": "real_fit_kernel", "ms": t_fit, "bytes_per_row": ncols * 8 + ncols / 8 + 8})
             del dst

@@ -356,6 +356,87 @@ vec_transform_select_kernel(const T* __restrict__ values, int64_t ld, const uint
     }
 }
 
+// vec_transform_pack_kernel: the select transform for the common case of dense output rows (out_ld == kept columns,
+// no column offset).  A CTA takes 32 rows and ALL columns: every value goes straight to its packed position in a
+// shared-memory image of the CTA's stretch of the output (row stride padded to an odd number of doubles, so that
+// lane = row accesses are conflict free), and after one barrier the image is copied out as one contiguous run of
+// 32 * nkeep doubles -- the stretch starts on a 256-byte multiple, so DRAM sees full sectors only and no row needs
+// its own alignment handling.
+constexpr int TP_ROWS = 32;
+constexpr int TP_THREADS = 384;
+constexpr int TP_BATCH = 4;       // loads a warp keeps in flight
+
+template <typename T, bool TRACK>
+__global__ void __launch_bounds__(TP_THREADS)
+vec_transform_pack_kernel(const T* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid, int64_t ldv,
+                          int64_t n, int ncols, const double* __restrict__ fills, double fill_const,
+                          double* __restrict__ out, int nkeep, int stride,
+                          const unsigned long long* __restrict__ keep_mask) {
+    extern __shared__ double tp_tile[];        // [TP_ROWS][stride], then the packed position of every input column
+    int* pos_of = reinterpret_cast<int*>(tp_tile + TP_ROWS * stride);     // -1: the whole column was dropped
+    constexpr int PER = TRACK ? 2 : 1;
+    constexpr int NW = TP_THREADS / 32;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t r0 = (int64_t)blockIdx.x * TP_ROWS;
+    const int rows_here = (int)min((int64_t)TP_ROWS, n - r0);
+    for (int c = tid; c < ncols; c += TP_THREADS) {
+        const int bit = c * PER;
+        const unsigned long long w = keep_mask[bit >> 6];
+        const unsigned mx = (unsigned)(w >> (bit & 63)) & (TRACK ? 3u : 1u);
+        int pos = __popcll(w & ((1ull << (bit & 63)) - 1ull));
+        for (int q = 0; q < (bit >> 6); ++q) pos += __popcll(keep_mask[q]);
+        pos_of[c] = mx ? (pos << 2) | (int)mx : -1;
+    }
+    __syncthreads();
+    const int64_t r = r0 + lane;
+    const bool row_ok = lane < rows_here;
+    const int vshift = (int)(r0 & 63) + lane;
+    double* trow = tp_tile + lane * stride;
+    for (int cb = warp; cb < ncols; cb += NW * TP_BATCH) {
+        double x[TP_BATCH];
+        unsigned long long vb[TP_BATCH];
+        int pm[TP_BATCH];
+#pragma unroll
+        for (int k = 0; k < TP_BATCH; ++k) {
+            const int c = cb + k * NW;
+            pm[k] = c < ncols ? pos_of[c] : -1;
+            x[k] = 0.0;
+            vb[k] = ~0ull;
+            if (pm[k] >= 0) {
+                if (row_ok) x[k] = (double)values[(int64_t)c * ld + r];
+                if (valid) vb[k] = valid[(int64_t)c * ldv + (r0 >> 6)];
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < TP_BATCH; ++k) {
+            if (pm[k] < 0) continue;
+            const int c = cb + k * NW;
+            const int pos = pm[k] >> 2;
+            const unsigned mx = (unsigned)pm[k] & 3u;
+            double xv = x[k];
+            if (sizeof(T) == 1) xv = xv != 0.0 ? 1.0 : 0.0;
+            const bool v = (vb[k] >> vshift) & 1ull;
+            const double fill = fills ? fills[c] : fill_const;
+            if (mx & 1u) trow[pos] = v ? xv : fill;
+            if (TRACK && (mx & 2u)) trow[pos + (int)(mx & 1u)] = v ? 0.0 : 1.0;
+        }
+    }
+    __syncthreads();
+    double* dst = out + r0 * nkeep;
+    const int total = rows_here * nkeep;
+    int rl = tid / nkeep, cl = tid - rl * nkeep;           // position of this thread's element; advanced by 512
+    const int dr = TP_THREADS / nkeep, dc = TP_THREADS - dr * nkeep;
+    for (int q = tid; q < total; q += TP_THREADS) {
+        dst[q] = tp_tile[rl * stride + cl];
+        rl += dr;
+        cl += dc;
+        if (cl >= nkeep) {
+            cl -= nkeep;
+            ++rl;
+        }
+    }
+}
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 static int fit_grid() { return sm_count() * FIT_CTAS_PER_SM; }
@@ -508,6 +589,24 @@ static int launch_transform(const T* values, int64_t ld, const uint64_t* valid, 
         else
             vec_transform_kernel<T, false><<<(unsigned)gx, 256, 0, st>>>(values, ld, valid, ldv, n, ncols, fills,
                                                                           fill_const, out, out_ld, out_col0);
+    } else if (out_col0 == 0 && out_ld == width && (reinterpret_cast<uintptr_t>(out) & 31u) == 0 &&
+               (size_t)TP_ROWS * (size_t)(width | 1) * sizeof(double) + 4 * (size_t)ncols <= 100 * 1024) {
+        // dense output rows: the packing kernel
+        const int stride = (int)width | 1;
+        const size_t smem = (size_t)TP_ROWS * stride * sizeof(double) + 4 * (size_t)ncols;
+        const int64_t gp = (n + TP_ROWS - 1) / TP_ROWS;
+        TMOG_REQUIRE(gp <= 0x7fffffffLL, "too many rows for one transform call (%lld): chunk the batch", (long long)n);
+        if (track_nulls) {
+            TMOG_CUDA(cudaFuncSetAttribute(vec_transform_pack_kernel<T, true>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            vec_transform_pack_kernel<T, true><<<(unsigned)gp, TP_THREADS, smem, st>>>(
+                values, ld, valid, ldv, n, ncols, fills, fill_const, out, (int)width, stride, km);
+        } else {
+            TMOG_CUDA(cudaFuncSetAttribute(vec_transform_pack_kernel<T, false>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            vec_transform_pack_kernel<T, false><<<(unsigned)gp, TP_THREADS, smem, st>>>(
+                values, ld, valid, ldv, n, ncols, fills, fill_const, out, (int)width, stride, km);
+        }
     } else {
         if (track_nulls)
             vec_transform_select_kernel<T, true><<<(unsigned)gx, 256, 0, st>>>(
