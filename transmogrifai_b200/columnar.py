@@ -442,10 +442,18 @@ class ColumnarBatch:
     response: Optional[str] = None       # name of the response (label) column, a RealNN
 
     def find(self, name: str):
-        for b in self.blocks:
-            if name in b.names:
-                return b, b.names.index(name)
-        raise KeyError(f"no column named {name!r} in the batch")
+        index = self.__dict__.get("_name_index")
+        if index is None or index[0] != len(self.blocks):
+            table = {}
+            for b in self.blocks:
+                for i, nm in enumerate(b.names):
+                    table.setdefault(nm, (b, i))
+            index = (len(self.blocks), table)
+            self.__dict__["_name_index"] = index
+        try:
+            return index[1][name]
+        except KeyError:
+            raise KeyError(f"no column named {name!r} in the batch") from None
 
     def has(self, name: str) -> bool:
         return name in self.vectors or any(name in b.names for b in self.blocks)

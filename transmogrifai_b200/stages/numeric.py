@@ -40,11 +40,14 @@ def _build_numeric_metadata(stage, track_nulls: bool) -> OpVectorMetadata:
     return OpVectorMetadata(stage.getOutputFeatureName(), cols, stage.history())
 
 
-def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str):
+def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str, after_launch=None):
     """Distinct label classes (global over all ranks), their global row counts, and per-row class ids of the local
-    rows on the device.  Cached on the batch."""
+    rows on the device.  Cached on the batch.  `after_launch(ids)` is called once the class ids are queued on the
+    stream and before the host waits for the classes, so that kernels consuming the ids run back to back with them."""
     cache = batch.__dict__.setdefault("_label_cache", {})
     if name in cache:
+        if after_launch is not None:
+            after_launch(cache[name][2])
         return cache[name]
     n = batch.n
     distributed = D.world()[1] > 1
@@ -58,6 +61,8 @@ def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str):
     L.call("tmog_label_classes_dev", y.data_ptr(), n, MAX_LABEL_CLASSES, classes.data_ptr(), ncls.data_ptr(),
            None if distributed else ids.data_ptr(), None if distributed else counts.data_ptr(), scratch.data_ptr(),
            scratch.numel(), R.stream())
+    if not distributed and after_launch is not None:
+        after_launch(ids)
     k = int(ncls.item())
     local = classes[:k].cpu().numpy() if k >= 0 else None
     if distributed:
@@ -69,6 +74,8 @@ def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str):
             ncls.fill_(len(union))
             L.call("tmog_label_class_ids_dev", y.data_ptr(), n, classes.data_ptr(), ncls.data_ptr(),
                    MAX_LABEL_CLASSES, ids.data_ptr(), counts.data_ptr(), R.stream())
+            if after_launch is not None:
+                after_launch(ids)
             out = (union, D.allreduce_sum(counts[:len(union)].cpu().numpy()), ids)
     else:
         out = (local, counts[:k].cpu().numpy(), ids) if k > 0 else (None, None, ids)
@@ -130,12 +137,18 @@ class RealVectorizer(OpEstimator):
                    y.data_ptr(), n, ncols, d_shifts.data_ptr(), scratch.data_ptr(), scratch.numel(),
                    d_part.data_ptr(), R.stream())
             if label_name:
-                classes, counts, ids = label_info_dev(batch, y, label_name)
-                if classes is not None and self.trackNulls:
-                    d_nc = torch.zeros((ncols, len(classes)), dtype=torch.int64, device="cuda")
-                    L.call("tmog_null_class_counts_dev", R.ptr(block.valid), block.ldv, ids.data_ptr(), n, ncols,
-                           len(classes), 0, d_nc.data_ptr(), R.stream())
-                    null_counts = D.allreduce_sum(d_nc.cpu().numpy())
+                d_nc = None
+
+                def count_nulls(ids):       # queued right behind the class-id kernel, counted against 255 classes
+                    nonlocal d_nc
+                    if self.trackNulls:
+                        d_nc = torch.zeros((ncols, MAX_LABEL_CLASSES), dtype=torch.int64, device="cuda")
+                        L.call("tmog_null_class_counts_dev", R.ptr(block.valid), block.ldv, ids.data_ptr(), n, ncols,
+                               MAX_LABEL_CLASSES, 0, d_nc.data_ptr(), R.stream())
+
+                classes, counts, ids = label_info_dev(batch, y, label_name, after_launch=count_nulls)
+                if classes is not None and d_nc is not None:
+                    null_counts = D.allreduce_sum(d_nc[:, :len(classes)].cpu().numpy())
             partials = D.allreduce_real_partials(d_part.cpu().numpy())
             shifts = d_shifts.cpu().numpy()
         else:

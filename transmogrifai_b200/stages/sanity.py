@@ -43,6 +43,41 @@ class CategoricalGroupStats:
     supports: np.ndarray
 
 
+class _GroupStatsList:
+    """categoricalStats as a read-only sequence over the packed arrays of tmog_contingency_stats_batch; the per-group
+    objects are only built when somebody looks at them (a wide vector has thousands of lone null-indicator groups)."""
+
+    def __init__(self, plan, mats, v, mi, pm, conf, sup, status):
+        self.plan, self.mats, self.v, self.mi, self.pm, self.conf, self.sup, self.status = \
+            plan, mats, v, mi, pm, conf, sup, status
+        self._built: Dict[int, CategoricalGroupStats] = {}
+
+    def __len__(self) -> int:
+        return len(self.plan.groups)
+
+    def __getitem__(self, g):
+        if isinstance(g, slice):
+            return [self[i] for i in range(*g.indices(len(self)))]
+        if g < 0:
+            g += len(self)
+        got = self._built.get(g)
+        if got is None:
+            name, col_names, _idx = self.plan.groups[g]
+            a, b = self.plan.row_offsets[g], self.plan.row_offsets[g] + self.plan.rows[g]
+            empty = self.status[g] == 1
+            got = CategoricalGroupStats(name, col_names, self.mats[a:b], float(self.v[g]), float(self.mi[g]),
+                                        self.pm[a:b], np.zeros(0) if empty else self.conf[a:b],
+                                        np.zeros(0) if empty else self.sup[a:b])
+            self._built[g] = got
+        return got
+
+    def __iter__(self):
+        return (self[g] for g in range(len(self)))
+
+    def __eq__(self, other):
+        return list(self) == list(other)
+
+
 @dataclass
 class SanityCheckerSummary:
     meta: OpVectorMetadata               # metadata of the checked vector (column names are expanded on demand)
@@ -284,14 +319,7 @@ class SanityChecker(OpEstimator):
         L.call("tmog_contingency_stats_batch", ng, plan.rows.ctypes.data, cols.ctypes.data, offsets.ctypes.data,
                plan.row_offsets.ctypes.data, data.ctypes.data, v.ctypes.data, chi.ctypes.data, mi.ctypes.data,
                pmi.ctypes.data, conf.ctypes.data, sup.ctypes.data, status.ctypes.data)
-        pm = pmi.reshape(plan.total_rows, L_)
-        out = []
-        for g, (name, col_names, _idx) in enumerate(plan.groups):
-            a, b = plan.row_offsets[g], plan.row_offsets[g] + plan.rows[g]
-            empty = status[g] == 1
-            out.append(CategoricalGroupStats(name, col_names, mats[a:b], float(v[g]), float(mi[g]), pm[a:b],
-                                             np.zeros(0) if empty else conf[a:b], np.zeros(0) if empty else sup[a:b]))
-        return out
+        return _GroupStatsList(plan, mats, v, mi, pmi.reshape(plan.total_rows, L_), conf, sup, status)
 
     def _decide(self, meta, st, corr, corr_indices, corr_matrix, cat_stats):
         d = meta.size
@@ -304,21 +332,23 @@ class SanityChecker(OpEstimator):
         cram = np.full(d, np.nan)
         rule_n = np.full(d, -1, dtype=np.int32)
         rconf, rsup = np.zeros(2 * d), np.zeros(2 * d)
-        for g, (_name, _cn, idx) in zip(cat_stats, plan.groups):
-            cram[idx] = g.cramersV
-            if len(idx) == 1:
-                i = idx[0]
-                m = min(2, len(g.maxRuleConfidences))
-                rule_n[i] = m
-                rconf[2 * i:2 * i + m] = g.maxRuleConfidences[:m]
-                rsup[2 * i:2 * i + m] = g.supports[:m]
-            else:
-                k = len(g.maxRuleConfidences)
-                ia = np.asarray(idx)
+        if len(cat_stats):
+            cs = cat_stats
+            cram[plan.cat_cols] = cs.v[plan.group_of_col]
+            # lone indicators (one column, two rows: indicator and complement): both rule confidences count
+            ok = cs.status[plan.lone_groups] != 1
+            lc, lr = plan.lone_cols, plan.lone_rows
+            rule_n[lc] = np.where(ok, 2, 0)
+            rconf[2 * lc], rconf[2 * lc + 1] = np.where(ok, cs.conf[lr], 0.0), np.where(ok, cs.conf[lr + 1], 0.0)
+            rsup[2 * lc], rsup[2 * lc + 1] = np.where(ok, cs.sup[lr], 0.0), np.where(ok, cs.sup[lr + 1], 0.0)
+            for g in plan.multi_groups:
+                ia = np.asarray(plan.groups[g][2])
+                a = plan.row_offsets[g]
+                k = 0 if cs.status[g] == 1 else int(plan.rows[g])
                 rule_n[ia] = 0
                 rule_n[ia[:k]] = 1
-                rconf[2 * ia[:k]] = g.maxRuleConfidences
-                rsup[2 * ia[:k]] = g.supports
+                rconf[2 * ia[:k]] = cs.conf[a:a + k]
+                rsup[2 * ia[:k]] = cs.sup[a:a + k]
         params = np.array([self.minVariance, self.minCorrelation, self.maxCorrelation, self.maxFeatureCorrelation,
                            self.maxCramersV, self.maxRuleConfidence, self.minRequiredRuleSupport,
                            float(self.removeFeatureGroup), float(self.protectTextSharedHash)])
@@ -388,6 +418,11 @@ class _MetaPlan:
             row_of_col.extend(range(r, r + len(idx)))
             rows.append(nrows)
             r += nrows
+        self.group_of_col = np.repeat(np.arange(len(self.groups), dtype=np.int64),
+                                      [len(g[2]) for g in self.groups]) if self.groups else np.zeros(0, dtype=np.int64)
+        self.lone_groups = np.asarray([g for g, grp in enumerate(self.groups) if len(grp[2]) == 1], dtype=np.int64)
+        self.lone_cols = np.asarray([self.groups[g][2][0] for g in self.lone_groups], dtype=np.int64)
+        self.multi_groups = [g for g, grp in enumerate(self.groups) if len(grp[2]) != 1]
         self.cat_cols = np.asarray(cat_cols, dtype=np.int64)
         self.row_of_col = np.asarray(row_of_col, dtype=np.int64)
         self.lone_rows = np.asarray(lone_rows, dtype=np.int64)
