@@ -231,6 +231,34 @@ int tmog_text_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uin
 int tmog_text_codes_dev(const int64_t* col_desc, const int32_t* col_index, int nsel, int64_t n, int clean_text,
                         int slots, const void* tables, int32_t* codes, int64_t ld, void* stream);
 
+/* ---- OpSetVectorizer (MultiPickList) ------------------------------------------------------------------------------
+ * Set columns in Arrow List<dictionary> layout (device): int64 offsets [n + 1], int32 codes [offsets[n]]; row r holds
+ * the codes [offsets[r], offsets[r + 1]) without duplicates, an empty range is the empty set.  The dictionary strings
+ * stay on the host; tmog_clean_strings / tmog_dedupe_strings give the cleaned value (group) of every code.
+ *
+ * tmog_set_count_dev replaces OpSetVectorizer.convertToSeqOfMaps + the count fold of OpOneHotVectorizer.fitFn
+ * (C/stages/impl/feature/OpOneHotVectorizer.scala:75-124,171-177): counts [(1 + ngroups) * nclasses] (u32, NOT cleared
+ * here) += rows of each label class holding the cleaned value gid[code] (raw values of a row that clean alike count
+ * once); entry 0 counts the empty sets.  *bad is set if a code is outside [0, ncodes). */
+int tmog_set_count_dev(const int64_t* offsets, const int32_t* codes, int64_t n, const int32_t* gid, int ncodes,
+                       int ngroups, const uint8_t* class_ids, int nclasses, uint32_t* counts, int32_t* bad,
+                       void* stream);
+
+/* OneHotModelFun.pivotFn for sets (OpOneHotVectorizer.scala:416-437): with pos [ncodes] = output slot of every code
+ * (0 .. k-1 the top values, k = OTHER) row r has the entries (slot, number of its raw values with that slot) and, for an
+ * empty set with track_nulls, (k + 1, 1).
+ * _stats: SanityChecker sums over k + 2 slots (NOT cleared here): class_sum [slot * nclasses + class] += value,
+ *   present [slot * nclasses + class] += 1 (the column clipped to <= 1, SanityChecker.scala:258-268), and for the rare
+ *   value > 1: sq_extra [slot] += v^2 - v, aux [3 * slot + {0, 1, 2}] = max v, max ~v, rows with v > 1.
+ * _transform: the entries whose newpos [slot] >= 0, as (newpos, value) in slot order.  Call once with row_start = NULL
+ *   to get row_nnz [n], prefix-sum it into row_start [n], call again to write out_idx / out_val. */
+int tmog_set_stats_dev(const int64_t* offsets, const int32_t* codes, int64_t n, const int32_t* pos, int ncodes, int k,
+                       int track_nulls, const uint8_t* class_ids, int nclasses, uint32_t* class_sum, uint32_t* present,
+                       uint64_t* sq_extra, uint32_t* aux, int32_t* bad, void* stream);
+int tmog_set_transform_dev(const int64_t* offsets, const int32_t* codes, int64_t n, const int32_t* pos, int ncodes,
+                           int k, int track_nulls, const int32_t* newpos, const int64_t* row_start, int32_t* row_nnz,
+                           int32_t* out_idx, int32_t* out_val, int32_t* bad, void* stream);
+
 /* Replaces TextTokenizer.tokenize (C/stages/impl/feature/TextTokenizer.scala:160-220; Lucene 7.3 StandardAnalyzer with
  * the Snowball english stop set, C/utils/text/LuceneTextAnalyzer.scala:103-122,159-166) + HashingFun.hash / prepare
  * (C/stages/impl/feature/OPCollectionHashingVectorizer.scala:244-305; Spark 2.4.5 HashingTF: legacy murmur3_x86_32

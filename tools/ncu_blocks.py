@@ -49,9 +49,10 @@ while i < len(data):
     smp = sum(d[3] for d in data[i:j + 1])
     blocks.append((data[i][0] - base, n, data[i][1] / units, thr / max(ins, 1), ins / tot * 100, smp, line_of.get(data[i][0] - base)))
     i = j + 1
-print(f"total {tot:.4g} warp instructions = {tot / units:.1f} per unit")
+tsmp = sum(d[3] for d in data)
+print(f"total {tot:.4g} warp instructions = {tot / units:.1f} per unit; {tsmp:.0f} stall samples")
 for a, n, cnt, act, share, smp, ln in blocks:
-    if share < 0.25:
+    if share < 0.25 and smp / tsmp < 0.004:
         continue
     text = src[ln - 1].strip()[:70] if ln and ln <= len(src) else ""
-    print(f"{a:05x} n={n:3d} x{cnt:8.1f} act {act:4.1f} {share:5.1f}%  {n * cnt:8.0f}/unit | {ln}: {text}")
+    print(f"{a:05x} n={n:3d} x{cnt:8.1f} act {act:4.1f} ins {share:5.1f}% smp {smp / tsmp * 100:5.1f}%  {n * cnt:8.0f}/unit | {ln}: {text}")

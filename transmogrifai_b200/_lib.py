@@ -56,6 +56,9 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_pivot_count_dev": [_p, _i64, _i64, _int, _p, _int, _p, _p, _i64, _p, _p, _p],
     "tmog_binary_codes_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _i64, _p],
     "tmog_pivot_transform_dev": [_p, _i64, _i64, _int, _p, _p, _p, _i64, _i64, _p],
+    "tmog_set_count_dev": [_p, _p, _i64, _p, _int, _int, _p, _int, _p, _p, _p],
+    "tmog_set_stats_dev": [_p, _p, _i64, _p, _int, _int, _int, _p, _int, _p, _p, _p, _p, _p, _p],
+    "tmog_set_transform_dev": [_p, _p, _i64, _p, _int, _int, _int, _p, _p, _p, _p, _p, _p, _p],
     "tmog_text_stats_layout": [_int, _int, _int, C.POINTER(_sz), C.POINTER(_sz)],
     "tmog_text_stats_table_bytes": [_int, _int, C.POINTER(_sz)],
     "tmog_text_stats_dev": [_p, _int, _i64, _p, _int, _int, _int, _int, _p, _p, _p],

@@ -179,6 +179,62 @@ class DictBlock:
 
 
 @dataclass
+class SetBlock:
+    """Set-valued string columns (MultiPickList) in Arrow List<dictionary> layout, per column: offsets int64 [n + 1],
+    codes int32 [offsets[n]] (row r holds codes[offsets[r]:offsets[r + 1]], no duplicates; an empty range is the empty
+    set, which is also what a null becomes), and the dictionary of distinct raw strings."""
+    names: List[str]
+    type_name: str
+    offsets: List[torch.Tensor]
+    codes: List[torch.Tensor]
+    dicts: List[List[str]]
+    n: int
+
+    @property
+    def is_cuda(self) -> bool:
+        return bool(self.offsets) and self.offsets[0].is_cuda
+
+    def dict_arrays(self, col: int) -> Tuple[np.ndarray, np.ndarray]:
+        d = self.dicts[col]
+        cache = _DICT_ARRAYS.get(id(d))
+        if cache is None or cache[0] is not d:
+            cache = (d,) + encode_strings(d)
+            _DICT_ARRAYS[id(d)] = cache
+        return cache[1], cache[2]
+
+    def rows(self, idx: Sequence[int]) -> "SetBlock":
+        idx = list(idx)
+        return SetBlock([self.names[i] for i in idx], self.type_name, [self.offsets[i] for i in idx],
+                        [self.codes[i] for i in idx], [self.dicts[i] for i in idx], self.n)
+
+    def to(self, device) -> "SetBlock":
+        mv = lambda t: t.to(device, non_blocking=True)  # noqa: E731
+        return SetBlock(self.names, self.type_name, [mv(t) for t in self.offsets], [mv(t) for t in self.codes],
+                        self.dicts, self.n)
+
+    @staticmethod
+    def from_lists(names: Sequence[str], type_name: str, columns: Sequence[Sequence], pin: bool = True) -> "SetBlock":
+        """Cells: None, or any iterable of strings (duplicates collapse, first-seen order kept: a Scala Set)."""
+        n = len(columns[0]) if columns else 0
+        offsets, codes, dicts = [], [], []
+        for col in columns:
+            seen: Dict[str, int] = {}
+            offs = np.zeros(n + 1, dtype=np.int64)
+            flat: List[int] = []
+            for i, cell in enumerate(col):
+                if cell is not None:
+                    for v in dict.fromkeys(cell):
+                        flat.append(seen.setdefault(v, len(seen)))
+                offs[i + 1] = len(flat)
+            to = torch.from_numpy(offs)
+            tc = torch.from_numpy(np.asarray(flat if flat else [0], dtype=np.int32)[:max(len(flat), 1)])
+            offsets.append(_pin(to) if pin else to)
+            codes.append(_pin(tc) if pin else tc)
+            dicts.append(list(seen))
+        return SetBlock(list(names), type_name, offsets, codes, dicts, n)
+
+
+@dataclass
 class TextBlock:
     """Raw utf8 string columns (Text / TextArea) in Arrow layout, one (data, offsets, validity) triple per column:
     data uint8 [total bytes], offsets int64 [n + 1], valid int64 bitmap words [ceil(n/64)] or None."""
@@ -479,6 +535,14 @@ class ColumnarBatch:
         return DictBlock(list(names), subs[0].type_name, torch.cat([t.codes for t in subs], dim=0),
                          [t.dicts[0] for t in subs], self.n)
 
+    def sets(self, names: Sequence[str]) -> "SetBlock":
+        located = [self.find(nm) for nm in names]
+        if not all(isinstance(b, SetBlock) for b, _ in located):
+            raise ValueError("not set-valued columns")
+        first = located[0][0]
+        return SetBlock(list(names), first.type_name, [b.offsets[i] for b, i in located],
+                        [b.codes[i] for b, i in located], [b.dicts[i] for b, i in located], self.n)
+
     def texts(self, names: Sequence[str]) -> "TextBlock":
         located = [self.find(nm) for nm in names]
         if not all(isinstance(b, TextBlock) for b, _ in located):
@@ -542,6 +606,8 @@ class ColumnarBatch:
                 blocks.append(DictBlock.from_lists(names, tp, [columns[nm][1] for nm in names], pin))
             elif tp in (F.TEXT, F.TEXTAREA):
                 blocks.append(TextBlock.from_lists(names, tp, [columns[nm][1] for nm in names], pin))
+            elif tp == F.MULTIPICKLIST:
+                blocks.append(SetBlock.from_lists(names, tp, [columns[nm][1] for nm in names], pin))
             else:
                 raise NotImplementedError(f"columns of type {tp} are not supported yet")
         return ColumnarBatch(n or 0, blocks, {}, response)

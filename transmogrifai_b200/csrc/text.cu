@@ -728,19 +728,17 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                             m.z = __reduce_or_sync(FULL, q == 2 ? mine : 0u);
                             m.w = __reduce_or_sync(FULL, q == 3 ? mine : 0u);
                             if (lane == 0) reinterpret_cast<uint4*>(mask)[w] = m;
-                            const int base = w << 7;
-                            unsigned S = m.x & ~((m.x << 1) | carry);
-                            if ((S >> lane) & 1u) toks[ntok + __popc(S & lt_mask)] = (Tok)(base + lane);
-                            ntok += __popc(S);
-                            S = m.y & ~((m.y << 1) | (m.x >> 31));
-                            if ((S >> lane) & 1u) toks[ntok + __popc(S & lt_mask)] = (Tok)(base + 32 + lane);
-                            ntok += __popc(S);
-                            S = m.z & ~((m.z << 1) | (m.y >> 31));
-                            if ((S >> lane) & 1u) toks[ntok + __popc(S & lt_mask)] = (Tok)(base + 64 + lane);
-                            ntok += __popc(S);
-                            S = m.w & ~((m.w << 1) | (m.z >> 31));
-                            if ((S >> lane) & 1u) toks[ntok + __popc(S & lt_mask)] = (Tok)(base + 96 + lane);
-                            ntok += __popc(S);
+                            // token starts (a token byte after a non-token byte): at most two per lane
+                            const unsigned up = __shfl_up_sync(FULL, nib, 1);
+                            const unsigned before = ((nib << 1) | (lane == 0 ? carry : (up >> 3))) & 0xfu;
+                            const unsigned sn = nib & ~before;
+                            const int sc = __popc(sn);
+                            const unsigned s1 = __ballot_sync(FULL, sc >= 1), s2 = __ballot_sync(FULL, sc == 2);
+                            const int at = ntok + __popc(s1 & lt_mask) + __popc(s2 & lt_mask);
+                            const int pos4 = (w << 7) + (lane << 2);
+                            if (sc >= 1) toks[at] = (Tok)(pos4 + __ffs(sn) - 1);
+                            if (sc == 2) toks[at + 1] = (Tok)(pos4 + 31 - __clz(sn));
+                            ntok += __popc(s1) + __popc(s2);
                             carry = m.w >> 31;
                         }
                     }

@@ -61,8 +61,8 @@ def top_k(values: Sequence[str], counts: np.ndarray, k: int, min_support: int) -
 class OpTextPivotVectorizer(OpEstimator):
     input_types = (F.PICKLIST, F.TEXT, F.TEXTAREA)
 
-    def __init__(self, uid: Optional[str] = None):
-        super().__init__("pivotText", uid)
+    def __init__(self, uid: Optional[str] = None, operationName: str = "pivotText"):  # noqa: N803
+        super().__init__(operationName, uid)
         self.topK = 20                  # TransmogrifierDefaults.TopK
         self.minSupport = 10            # TransmogrifierDefaults.MinSupport
         self.cleanText = True

@@ -296,8 +296,6 @@ class SanityChecker(OpEstimator):
         plan = self._plan(meta)
         if not plan.groups:
             return []
-        if plan.has_mpl:
-            raise NotImplementedError("MultiPickList contingency statistics are not on the GPU path yet")
         counts = st.label.class_counts.astype(np.float64)
         L_ = len(counts)
         sums = st.class_sums[:, plan.cat_cols]                    # [L, total categorical columns]
@@ -319,6 +317,23 @@ class SanityChecker(OpEstimator):
         L.call("tmog_contingency_stats_batch", ng, plan.rows.ctypes.data, cols.ctypes.data, offsets.ctypes.data,
                plan.row_offsets.ctypes.data, data.ctypes.data, v.ctypes.data, chi.ctypes.data, mi.ctypes.data,
                pmi.ctypes.data, conf.ctypes.data, sup.ctypes.data, status.ctypes.data)
+        # MultiPickList groups (OpStatistics.contingencyStatsFromMultiPickList :346-382): Cramer's V is the largest V of
+        # the 2 x nLabels tables [choice; rest] over the non-empty choices; everything else stays the full table's
+        for g in plan.mpl_groups:
+            a, b = plan.row_offsets[g], plan.row_offsets[g] + plan.rows[g]
+            m = mats[a:b]
+            m = m[m.sum(axis=1) != 0.0]
+            m = m[:, m.sum(axis=0) != 0.0] if len(m) else m
+            best = None
+            for row in m:
+                two = np.ascontiguousarray(np.stack([row, counts[:len(row)] - row]))
+                v1, chi1, mi1 = np.zeros(1), np.zeros(1), np.zeros(1)
+                L.call("tmog_contingency_stats", two.ctypes.data, 2, two.shape[1], v1.ctypes.data, chi1.ctypes.data,
+                       mi1.ctypes.data, None, None, None)
+                if best is None or v1[0] > best:          # maxBy keeps the first maximum; NaN never compares greater
+                    best = float(v1[0])
+            if best is not None:
+                v[g] = best
         return _GroupStatsList(plan, mats, v, mi, pmi.reshape(plan.total_rows, L_), conf, sup, status)
 
     def _decide(self, meta, st, corr, corr_indices, corr_matrix, cat_stats):
@@ -399,7 +414,7 @@ class _MetaPlan:
         self.identity_pos = np.arange(d, dtype=np.int32)
         # categorical groups: duplicate indicator values inside a group -> only the first is used (:295-298)
         self.groups = []
-        self.has_mpl = False
+        self.mpl_groups: List[int] = []
         cat_cols, row_of_col, rows, lone_rows = [], [], [], []
         r = 0
         for g, cols in groups.items():
@@ -409,7 +424,8 @@ class _MetaPlan:
                     seen.add(c.indicatorValue)
                     cleaned.append((c, i))
             idx = [i for _, i in cleaned]
-            self.has_mpl = self.has_mpl or any(c.isMultiPickList for c, _ in cleaned)
+            if any(c.isMultiPickList for c, _ in cleaned):
+                self.mpl_groups.append(len(self.groups))
             self.groups.append((g, meta.names_of(idx), idx))
             nrows = 2 if len(idx) == 1 else len(idx)
             if len(idx) == 1:

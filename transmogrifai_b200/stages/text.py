@@ -1,5 +1,5 @@
 """Default vectorizers of the string-typed features (Transmogrifier.scala:275-317): PickList -> pivot,
-Text / TextArea -> SmartTextVectorizer."""
+MultiPickList -> OpSetVectorizer, Text / TextArea -> SmartTextVectorizer."""
 from __future__ import annotations
 
 from typing import List
@@ -11,6 +11,10 @@ from .pivot import OpTextPivotVectorizer
 def vectorizer_for_text_type(type_name: str, feats: List[F.Feature], d) -> F.Feature:
     if type_name == F.PICKLIST:
         return OpTextPivotVectorizer().setInput(*feats).setTopK(d.TopK).setMinSupport(d.MinSupport) \
+            .setCleanText(d.CleanText).setTrackNulls(d.TrackNulls).getOutput()
+    if type_name == F.MULTIPICKLIST:
+        from .sets import OpSetVectorizer
+        return OpSetVectorizer().setInput(*feats).setTopK(d.TopK).setMinSupport(d.MinSupport) \
             .setCleanText(d.CleanText).setTrackNulls(d.TrackNulls).getOutput()
     if type_name in (F.TEXT, F.TEXTAREA):
         from .smart_text import SmartTextVectorizer
