@@ -58,6 +58,9 @@ def top_k(values: Sequence[str], counts: np.ndarray, k: int, min_support: int) -
     return out[:int(n_out[0])].tolist()
 
 
+_COLUMN_DESCRIPTIONS: Dict[tuple, OpVectorColumnMetadata] = {}
+
+
 class OpTextPivotVectorizer(OpEstimator):
     input_types = (F.PICKLIST, F.TEXT, F.TEXTAREA)
 
@@ -106,8 +109,15 @@ class OpTextPivotVectorizer(OpEstimator):
         cols = []
         for f, top in zip(self.inN, tops):
             vals = list(top) + [self.unseenName] + ([NullString] if self.trackNulls else [])
-            cols += [OpVectorColumnMetadata((f.name,), (f.type_name,), grouping=f.name, indicatorValue=v)
-                     for v in vals]
+            for v in vals:
+                key = (f.name, f.type_name, v)
+                col = _COLUMN_DESCRIPTIONS.get(key)
+                if col is None:                 # immutable descriptions, shared between fits
+                    if len(_COLUMN_DESCRIPTIONS) > 1_000_000:
+                        _COLUMN_DESCRIPTIONS.clear()
+                    col = OpVectorColumnMetadata((f.name,), (f.type_name,), grouping=f.name, indicatorValue=v)
+                    _COLUMN_DESCRIPTIONS[key] = col
+                cols.append(col)
         return OpVectorMetadata(self.getOutputFeatureName(), cols, self.history())
 
     @staticmethod

@@ -62,7 +62,8 @@ class _GroupStatsList:
             g += len(self)
         got = self._built.get(g)
         if got is None:
-            name, col_names, _idx = self.plan.groups[g]
+            name, _names, idx = self.plan.groups[g]
+            col_names = self.plan.meta.names_of(idx)
             a, b = self.plan.row_offsets[g], self.plan.row_offsets[g] + self.plan.rows[g]
             empty = self.status[g] == 1
             got = CategoricalGroupStats(name, col_names, self.mats[a:b], float(self.v[g]), float(self.mi[g]),
@@ -387,16 +388,21 @@ class _MetaPlan:
 
     def __init__(self, meta: OpVectorMetadata):
         d = meta.size
+        self.meta = meta
         parent_ids: Dict[str, int] = {}
         group_ids: Dict[str, int] = {}
         run_np, run_gid, run_tsh, run_hashed = [], [], [], []
-        pid_chunks = []
+        pid_list: List[int] = []
+        long_runs = []                      # (position in pid_list, parent ids, repeat) of runs longer than one column
         groups: Dict[str, list] = {}
         counts = np.array([k for _, k in meta.runs], dtype=np.int64)
         for (c, k), s0 in zip(meta.runs, meta.run_starts[:-1]):
             pids = [parent_ids.setdefault(pn, len(parent_ids)) for pn in c.parentNamesWithMapKeys()]
             run_np.append(len(pids))
-            pid_chunks.append(np.tile(np.asarray(pids, dtype=np.int32), k))
+            if k == 1:
+                pid_list.extend(pids)
+            else:                           # a hashed block: hundreds of thousands of identical columns
+                long_runs.append((len(pid_list), pids, k))
             g = c.featureGroup()
             run_gid.append(group_ids.setdefault(g, len(group_ids)) if g is not None else -1)
             run_tsh.append(c.isTextSharedHash)
@@ -407,7 +413,13 @@ class _MetaPlan:
                     groups.setdefault(g, []).append((c, int(s0) + i))
         per_col_np = np.repeat(np.asarray(run_np, dtype=np.int64), counts)
         self.offs = np.concatenate([[0], np.cumsum(per_col_np)]).astype(np.int32)
-        self.pids = np.concatenate(pid_chunks).astype(np.int32) if pid_chunks else np.zeros(0, dtype=np.int32)
+        pieces, at = [], 0
+        for where, pids, k in long_runs:
+            pieces.append(np.asarray(pid_list[at:where], dtype=np.int32))
+            pieces.append(np.tile(np.asarray(pids, dtype=np.int32), k))
+            at = where
+        pieces.append(np.asarray(pid_list[at:], dtype=np.int32))
+        self.pids = np.concatenate(pieces)
         self.gid = np.repeat(np.asarray(run_gid, dtype=np.int32), counts)
         self.tsh = np.repeat(np.asarray(run_tsh, dtype=np.uint8), counts)
         self.hashed_text = np.repeat(np.asarray(run_hashed, dtype=bool), counts)
@@ -426,7 +438,7 @@ class _MetaPlan:
             idx = [i for _, i in cleaned]
             if any(c.isMultiPickList for c, _ in cleaned):
                 self.mpl_groups.append(len(self.groups))
-            self.groups.append((g, meta.names_of(idx), idx))
+            self.groups.append((g, None, idx))        # the column names are looked up when somebody asks
             nrows = 2 if len(idx) == 1 else len(idx)
             if len(idx) == 1:
                 lone_rows.append(r)
