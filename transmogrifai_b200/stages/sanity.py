@@ -19,7 +19,7 @@ from .. import _lib as L
 from .. import dist as D
 from .. import features as F
 from ..columnar import ColumnarBatch, CsrPart, DensePart, VectorColumn
-from ..metadata import OpVectorMetadata
+from ..metadata import OpVectorColumnMetadata, OpVectorMetadata
 from ..stats import VectorStats
 from .base import OpEstimator, OpModel
 
@@ -382,6 +382,9 @@ class SanityChecker(OpEstimator):
         return drop, reasons, pc, pv
 
 
+_RUN_INFO: Dict[OpVectorColumnMetadata, tuple] = {}
+
+
 class _MetaPlan:
     """Column metadata of one vector reduced to the integer arrays the C ABI wants (built once per metadata object,
     run by run): parent / group ids for tmog_sanity_decide, and the categorical groups of categoricalTests."""
@@ -397,17 +400,24 @@ class _MetaPlan:
         groups: Dict[str, list] = {}
         counts = np.array([k for _, k in meta.runs], dtype=np.int64)
         for (c, k), s0 in zip(meta.runs, meta.run_starts[:-1]):
-            pids = [parent_ids.setdefault(pn, len(parent_ids)) for pn in c.parentNamesWithMapKeys()]
+            info = _RUN_INFO.get(c)
+            if info is None:                # per column description (immutable, shared between fits)
+                if len(_RUN_INFO) > 1_000_000:
+                    _RUN_INFO.clear()
+                info = (tuple(c.parentNamesWithMapKeys()), c.featureGroup(), c.isTextSharedHash,
+                        c.grouping is None and c.indicatorValue is None
+                        and c.hasParentOfType(F.TEXT, F.TEXTAREA, "TextMap", "TextAreaMap"))
+                _RUN_INFO[c] = info
+            parents, g, tsh, hashed = info
+            pids = [parent_ids.setdefault(pn, len(parent_ids)) for pn in parents]
             run_np.append(len(pids))
             if k == 1:
                 pid_list.extend(pids)
             else:                           # a hashed block: hundreds of thousands of identical columns
                 long_runs.append((len(pid_list), pids, k))
-            g = c.featureGroup()
             run_gid.append(group_ids.setdefault(g, len(group_ids)) if g is not None else -1)
-            run_tsh.append(c.isTextSharedHash)
-            run_hashed.append(c.grouping is None and c.indicatorValue is None
-                              and c.hasParentOfType(F.TEXT, F.TEXTAREA, "TextMap", "TextAreaMap"))
+            run_tsh.append(tsh)
+            run_hashed.append(hashed)
             if g is not None and c.indicatorValue is not None:
                 for i in range(k):
                     groups.setdefault(g, []).append((c, int(s0) + i))
