@@ -214,7 +214,12 @@ class OpTextPivotVectorizer(OpEstimator):
             local = code_to_out[:nc] if g_maps[c] is None else code_to_out[:nc][g_maps[c]]
             return top, local, rows.astype(np.float64)
 
-        results = list(_pool().map(finish, range(ncols))) if ncols > 1 else [finish(c) for c in range(ncols)]
+        if ncols > 1:                  # the largest dictionaries first: they are the critical path
+            order = sorted(range(ncols), key=lambda c: -int(g_ncodes[c]))
+            done = dict(zip(order, _pool().map(finish, order)))
+            results = [done[c] for c in range(ncols)]
+        else:
+            results = [finish(c) for c in range(ncols)]
         tops = [r[0] for r in results]
         self._metadata = self._metadata_for(tops)
         stats = None
