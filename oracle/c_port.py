@@ -97,3 +97,123 @@ def real_pipeline(values: np.ndarray, valid_words: Optional[np.ndarray], y: np.n
     with np.errstate(divide="ignore", invalid="ignore"):
         corr = cov / (sd * sd[-1] * (n - 1))
     return fills, rows, mean, var, mn, mx, corr
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# string paths (oracle/c/oracle_text.c)
+# ---------------------------------------------------------------------------------------------------------------------
+def encode_text_columns(columns):
+    """Python columns (str / None cells) -> per column (bytes uint8, offsets int64 [n+1], validity uint64 words)."""
+    out = []
+    for col in columns:
+        n = len(col)
+        enc = [b"" if v is None else v.encode("utf-8") for v in col]
+        offs = np.zeros(n + 1, dtype=np.int64)
+        offs[1:] = np.cumsum([len(e) for e in enc])
+        data = np.frombuffer(b"".join(enc) or b"\0", dtype=np.uint8).copy()
+        bits = np.zeros((n + 63) // 64 * 64, dtype=np.uint8)
+        bits[:n] = [v is not None for v in col]
+        valid = np.packbits(bits, bitorder="little").view(np.uint64).copy()
+        out.append((data, offs, valid))
+    return out
+
+
+def _ptr_arrays(cols):
+    data = np.array([c[0].ctypes.data for c in cols], dtype=np.uintp)
+    offs = np.array([c[1].ctypes.data for c in cols], dtype=np.uintp)
+    valid = np.array([0 if c[2] is None else c[2].ctypes.data for c in cols], dtype=np.uintp)
+    return data, offs, valid
+
+
+def text_hash(cols, n: int, prefixes, num_features: int, shared: bool, binary_freq: bool = False,
+              min_token_length: int = 1, track_nulls: bool = True, class_ids: Optional[np.ndarray] = None,
+              nclasses: int = 1, threads: int = 1, want_stats: bool = True, want_rows: bool = True):
+    """cols: [(data, offsets, valid)] per hashed column; prefixes: the "<nameHash>_" bytes per column ("" = none).
+    -> dict(class_sum [width, nclasses], sq_sum, nnz, vmax, vmin, row_start, row_nnz, idx, val)"""
+    ncols = len(cols)
+    hash_width = num_features if shared else num_features * ncols
+    null_base = hash_width
+    width = null_base + ncols
+    pre = np.zeros((max(ncols, 1), 16), dtype=np.uint8)
+    plen = np.zeros(max(ncols, 1), dtype=np.int32)
+    for j, p in enumerate(prefixes):
+        b = p.encode("ascii")
+        pre[j, :len(b)] = np.frombuffer(b, dtype=np.uint8)
+        plen[j] = len(b)
+    dp, op, vp = _ptr_arrays(cols)
+    res = {}
+    cs = sq = nz = mx = mn = None
+    if want_stats:
+        cs = np.zeros((width, nclasses), dtype=np.int64)
+        sq, nz = np.zeros(width, dtype=np.int64), np.zeros(width, dtype=np.int64)
+        mx = np.zeros(width, dtype=np.int32)
+        mn = np.full(width, np.iinfo(np.int32).max, dtype=np.int32)
+    rs = np.zeros(max(n, 1), dtype=np.int64)
+    rn = np.zeros(max(n, 1), dtype=np.int32)
+    oi, ov, tot = C.c_void_p(), C.c_void_p(), C.c_int64(0)
+    f = lib().orc_text_hash
+    f.restype = C.c_int
+    rc = f(_p(dp), _p(op), _p(vp), C.c_int(ncols), C.c_int64(n), _p(pre), _p(plen), C.c_int(num_features),
+           C.c_int(int(shared)), C.c_int(int(binary_freq)), C.c_int(min_token_length), C.c_int(int(track_nulls)),
+           C.c_int(null_base), _p(class_ids), C.c_int(nclasses), C.c_int(threads), _p(cs), _p(sq), _p(nz), _p(mx),
+           _p(mn), C.c_int(int(want_rows)), _p(rs), _p(rn), C.byref(oi), C.byref(ov), C.byref(tot))
+    if rc != 0:
+        raise MemoryError("orc_text_hash ran out of memory")
+    res.update(class_sum=cs, sq_sum=sq, nnz=nz, vmax=mx, vmin=mn, width=width)
+    if want_rows:
+        t = tot.value
+        res["row_start"], res["row_nnz"] = rs[:n], rn[:n]
+        res["idx"] = np.ctypeslib.as_array(C.cast(oi, C.POINTER(C.c_int32)), shape=(max(t, 1),))[:t].copy()
+        res["val"] = np.ctypeslib.as_array(C.cast(ov, C.POINTER(C.c_int32)), shape=(max(t, 1),))[:t].copy()
+        lib().orc_free(oi)
+        lib().orc_free(ov)
+    return res
+
+
+def text_stats(cols, n: int, clean: bool, max_card: int, threads: int = 1):
+    ncols = len(cols)
+    dp, op, vp = _ptr_arrays(cols)
+    distinct = np.zeros(ncols, dtype=np.int32)
+    nonnull, ls, lq = (np.zeros(ncols, dtype=np.int64) for _ in range(3))
+    f = lib().orc_text_stats
+    f.restype = C.c_int
+    if f(_p(dp), _p(op), _p(vp), C.c_int(ncols), C.c_int64(n), C.c_int(int(clean)), C.c_int(max_card),
+         C.c_int(threads), _p(distinct), _p(nonnull), _p(ls), _p(lq)) != 0:
+        raise MemoryError("orc_text_stats ran out of memory")
+    return distinct, nonnull, ls, lq
+
+
+def clean_string(s: str) -> str:
+    b = np.frombuffer(s.encode("ascii") or b"\0", dtype=np.uint8).copy()
+    out = np.zeros(max(len(b), 1), dtype=np.uint8)
+    f = lib().orc_clean_string
+    f.restype = C.c_int64
+    m = f(_p(b), C.c_int64(len(s)), _p(out))
+    return out[:m].tobytes().decode("ascii")
+
+
+def pivot_counts(codes: np.ndarray, n: int, ncodes: np.ndarray, class_ids: Optional[np.ndarray], nclasses: int,
+                 threads: int = 1):
+    """codes [ncols, ld] int32 -> list per column of counts [(1 + ncodes_c), nclasses] (row 0 = nulls)"""
+    ncols, ld = codes.shape
+    sizes = (np.asarray(ncodes, dtype=np.int64) + 1) * nclasses
+    off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    counts = np.zeros(int(off[-1]), dtype=np.int64)
+    f = lib().orc_pivot_counts
+    f.restype = C.c_int
+    if f(_p(codes), C.c_int64(ld), C.c_int64(n), C.c_int(ncols), _p(off), C.c_int64(int(off[-1])), _p(class_ids),
+         C.c_int(nclasses), C.c_int(threads), _p(counts)) != 0:
+        raise MemoryError("orc_pivot_counts ran out of memory")
+    return [counts[off[c]:off[c + 1]].reshape(-1, nclasses) for c in range(ncols)]
+
+
+def pivot_transform(codes: np.ndarray, n: int, pos_tables, threads: int = 1) -> np.ndarray:
+    """pos_tables[c]: int32 [ncodes_c + 1] (last entry = the null indicator's index) -> out [n, ncols] int32"""
+    ncols, ld = codes.shape
+    ncodes = np.array([len(t) - 1 for t in pos_tables], dtype=np.int32)
+    off = np.concatenate([[0], np.cumsum([len(t) for t in pos_tables])]).astype(np.int64)
+    pos = np.ascontiguousarray(np.concatenate(pos_tables), dtype=np.int32)
+    out = np.zeros((n, ncols), dtype=np.int32)
+    lib().orc_pivot_transform(_p(codes), C.c_int64(ld), C.c_int64(n), C.c_int(ncols), _p(pos), _p(off), _p(ncodes),
+                              C.c_int(threads), _p(out))
+    return out
