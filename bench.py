@@ -225,65 +225,78 @@ def cpu_reference_c2(rows: int, threads: int):
     return time.perf_counter() - t0
 
 
-def cpu_reference_generic(workload: str, rows: int):
-    """The oracle (pure Python / numpy restatement, one core) on a small sample of the same synthetic workload:
-    vectorizer fit + transform per type group, combine, SanityChecker statistics.  -> seconds."""
+def cpu_reference_generic(workload: str, rows: int, threads: int):
+    """The reference's job sequence on a sample of the same synthetic workload, as oracle/c (C + OpenMP, row
+    partitions like Spark local[N]): per type group the vectorizer's fit and transform, then SanityChecker's sums
+    (column moments, label covariance, per-label column sums).  The string work is done once per dictionary entry and
+    the hashed columns' statistics are taken in the hashing pass -- both cheaper than what the reference does per
+    row, so this baseline errs on the fast side.  -> seconds (the sample is drawn before the clock starts)."""
     import torch
-    import scipy.sparse as sp
     import benchdata
+    from oracle import c_port as CP
     from oracle import vectorizers as V
     from transmogrifai_b200.columnar import DictBlock, NumericBlock, TextBlock
+    from transmogrifai_b200.stages.smart_text import murmur3_index
     batch, feats, label, info = benchdata.make_workload(workload, rows, SEED)
-    y = batch.label()[:rows].cpu().numpy()
-    cols = {}
+    y = np.ascontiguousarray(batch.label()[:rows].cpu().numpy())
+    cls = (y > 0).astype(np.uint8)
+    work = []
     for b in batch.blocks:
         if isinstance(b, NumericBlock):
-            v = b.values[:, :rows].cpu().numpy()
-            ok = np.ones_like(v, dtype=bool) if b.valid is None else np.unpackbits(
-                b.valid.cpu().numpy().view(np.uint8), axis=1, bitorder="little")[:, :rows].astype(bool)
-            for j, nm in enumerate(b.names):
-                cols[nm] = [(bool(x) if b.type_name == "Binary" else float(x)) if o else None
-                            for x, o in zip(v[j], ok[j])]
+            v = np.ascontiguousarray(b.values[:, :rows].cpu().numpy().astype(np.float64))
+            vw = None if b.valid is None else np.ascontiguousarray(
+                b.valid[:, :(rows + 63) // 64].cpu().numpy().view(np.uint64))
+            work.append(("num", b.type_name, v, vw))
         elif isinstance(b, DictBlock):
-            c = b.codes[:, :rows].cpu().numpy()
-            for j, nm in enumerate(b.names):
-                d = b.dicts[j]
-                cols[nm] = [None if k < 0 else d[k] for k in c[j]]
+            work.append(("dict", np.ascontiguousarray(b.codes[:, :rows].cpu().numpy()), b.dicts))
         elif isinstance(b, TextBlock):
-            for j, nm in enumerate(b.names):
-                cols[nm] = [b.cell(j, r) for r in range(rows)]
+            cols = []
+            for j in range(len(b.names)):
+                offs = b.offsets[j][:rows + 1].cpu().numpy().astype(np.int64)
+                data = b.data[j][:max(int(offs[-1]), 1)].cpu().numpy()
+                valid = None if b.valid[j] is None else b.valid[j][:(rows + 63) // 64].cpu().numpy().view(np.uint64)
+                cols.append((np.ascontiguousarray(data), np.ascontiguousarray(offs),
+                             None if valid is None else np.ascontiguousarray(valid)))
+            work.append(("text", list(b.names), cols))
     del batch
     torch.cuda.empty_cache()
-    by_type = {}
-    for f in feats:
-        by_type.setdefault(f.type_name, []).append(f.name)
+    labels = np.array([0.0, 1.0])
     t0 = time.perf_counter()
-    mats = []
-    for tp in sorted(by_type):
-        names = by_type[tp]
-        data = [cols[nm] for nm in names]
-        if tp == "Binary":
-            mats.append(sp.csr_matrix(V.binary_vectorizer_transform(data)))
-        elif tp == "Real":
-            mats.append(sp.csr_matrix(V.real_vectorizer_transform(data, V.real_vectorizer_fit(data), True)))
-        elif tp == "PickList":
-            tops = V.pivot_fit(data, 20, 10, True)
-            mats.append(V.pivot_transform(data, tops, True, True))
-        elif tp == "Text":
-            methods, tops = V.smart_text_fit(data, max_cardinality=30, top_k=20, min_support=10)
-            mats.append(V.smart_text_transform(data, names, methods, tops, num_features=info["num_features"]))
-    x = sp.hstack(mats, format="csr")
-    # SanityChecker statistics, sparse-aware (the reference's Off route loops densely over every column of every
-    # row, U/stats/OpStatistics.scala:86-90; this is the cheaper equivalent)
-    n = x.shape[0]
-    s1 = np.asarray(x.sum(axis=0)).ravel()
-    s2 = np.asarray(x.multiply(x).sum(axis=0)).ravel()
-    sxy = np.asarray(x.T @ y).ravel()
-    mean = s1 / n
-    var = (s2 - n * mean * mean) / (n - 1)
-    cov = sxy - mean * y.sum()
-    _ = cov / np.sqrt(np.maximum(var, 1e-300) * y.var(ddof=1)) / (n - 1)
-    _ = [np.asarray(x[y == k].sum(axis=0)) for k in (0.0, 1.0)]
+    for item in work:
+        if item[0] == "num":
+            _, tp, v, vw = item
+            if tp == "Real":
+                _, rows_m, _, _, _, _, _ = CP.real_pipeline(v, vw, y, threads)
+            else:                                           # Binary / RealNN: constant fill, then the same passes
+                rows_m = CP.real_transform(v, vw, np.zeros(v.shape[0]), tp == "Binary", threads, extra_cols=1)
+                rows_m[:, -1] = y
+                mean, _, _, _ = CP.col_stats(rows_m, threads)
+                CP.label_cov(rows_m, mean, threads)
+            CP.label_sums(rows_m[:, :-1], y, labels, threads)
+        elif item[0] == "dict":
+            _, codes, dicts = item
+            ncodes = np.array([len(d) for d in dicts])
+            counts = CP.pivot_counts(codes, rows, ncodes, cls, 2, threads)
+            tables, off = [], 0
+            for c, d in enumerate(dicts):
+                merged = {}
+                cleaned = CP.clean_strings(d)
+                tot = counts[c][1:].sum(axis=1)
+                for k, cv in enumerate(cleaned):
+                    merged[cv] = merged.get(cv, 0) + int(tot[k])
+                top = V.top_values(merged, 20, 10)
+                index = {v: i for i, v in enumerate(top)}
+                tab = np.array([off + index.get(cv, len(top)) for cv in cleaned] + [off + len(top) + 1], dtype=np.int32)
+                tables.append(tab)
+                off += len(top) + 2
+            CP.pivot_transform(codes, rows, tables, threads)     # one-hot rows; their sums are the counts above
+        else:
+            _, names, cols = item
+            CP.text_stats(cols, rows, True, 30, threads)
+            nf = info["num_features"]
+            shared = nf * len(names) > (1 << 17)
+            prefixes = [f"{murmur3_index(nm, nf)}_" for nm in names]
+            CP.text_hash(cols, rows, prefixes, nf, shared, class_ids=cls, nclasses=2, threads=threads)
     return time.perf_counter() - t0
 
 
@@ -293,10 +306,11 @@ def cpu_baseline(workload: str, cores: int, cpu_rows: int):
         return secs, cpu_rows, cores, (f"{cpu_rows} rows x 100 Real columns of the same workload; the reference's job "
                                        f"sequence (fit, transform, colStats, label correlations, per-label sums) as "
                                        f"oracle/c (C + OpenMP) on {cores} threads")
-    rows = {"c3": 20_000, "c4": 1_000, "c5": 1_000}[workload]
-    secs = cpu_reference_generic(workload, rows)
-    return secs, rows, 1, (f"{rows} rows of the same workload through the oracle (pure Python / numpy restatement of "
-                           "the reference, one core; no compiled port of the string paths yet)")
+    rows = {"c3": 5_000_000, "c4": 500_000, "c5": 200_000}[workload]
+    secs = cpu_reference_generic(workload, rows, cores)
+    return secs, rows, cores, (f"{rows} rows of the same workload; the reference's job sequence per type group (fit, "
+                               f"transform, SanityChecker sums) as oracle/c (C + OpenMP) on {cores} threads, string "
+                               "work per dictionary entry")
 
 
 def main():

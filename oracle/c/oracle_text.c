@@ -479,3 +479,14 @@ void orc_pivot_transform(const int32_t* codes, int64_t ld, int64_t n, int ncols,
             out[r * ncols + c] = pos[pos_off[c] + (code < 0 ? ncodes[c] : code)];
         }
 }
+
+/* cleanString over a whole dictionary (Arrow utf8 in, Arrow utf8 out; out_data needs offsets[count] bytes). */
+void orc_clean_strings(const uint8_t* data, const int64_t* offsets, int64_t count, uint8_t* out_data,
+                       int64_t* out_offsets) {
+    int64_t w = 0;
+    out_offsets[0] = 0;
+    for (int64_t i = 0; i < count; ++i) {
+        w += orc_clean_string(data + offsets[i], offsets[i + 1] - offsets[i], out_data + w);
+        out_offsets[i + 1] = w;
+    }
+}

@@ -217,3 +217,16 @@ def pivot_transform(codes: np.ndarray, n: int, pos_tables, threads: int = 1) -> 
     lib().orc_pivot_transform(_p(codes), C.c_int64(ld), C.c_int64(n), C.c_int(ncols), _p(pos), _p(off), _p(ncodes),
                               C.c_int(threads), _p(out))
     return out
+
+
+def clean_strings(values):
+    """cleanString of every entry of a list of ASCII strings."""
+    enc = [v.encode("ascii") for v in values]
+    offs = np.zeros(len(enc) + 1, dtype=np.int64)
+    offs[1:] = np.cumsum([len(e) for e in enc])
+    data = np.frombuffer(b"".join(enc) or b"\0", dtype=np.uint8).copy()
+    out = np.zeros(max(int(offs[-1]), 1), dtype=np.uint8)
+    ooffs = np.zeros(len(enc) + 1, dtype=np.int64)
+    lib().orc_clean_strings(_p(data), _p(offs), C.c_int64(len(enc)), _p(out), _p(ooffs))
+    raw = out.tobytes()
+    return [raw[ooffs[i]:ooffs[i + 1]].decode("ascii") for i in range(len(enc))]
