@@ -203,7 +203,8 @@ def kernel_times(workload, batch, fitted, info, reps: int = 5):
             desc = _col_desc(sub)
             t_h = _time(lambda: L.call("tmog_text_hash_stats_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(),
                                        d_plen.data_ptr(), params.ctypes.data, ids.data_ptr(), cs.data_ptr(),
-                                       nz.data_ptr(), ex.data_ptr(), ax.data_ptr(), fl.data_ptr(), scr.data_ptr(), scr.numel(), st),
+                                       nz.data_ptr(), ex.data_ptr(), ax.data_ptr(), None, 0.0, None, fl.data_ptr(),
+                                       scr.data_ptr(), scr.numel(), st),
                         max(reps // 2, 1))
             bpr = sum(int(sub.offsets[j][-1].item()) for j in range(k)) / max(n, 1)
             out.append({"kernel": "text_hash_kernel", "ms": t_h, "bytes_per_row": bpr + k * 8 + k / 8 + 1,

@@ -195,6 +195,14 @@ int tmog_pivot_count_dev(const int32_t* codes, int64_t ld, int64_t n, int ncols,
 int tmog_binary_codes_dev(const uint8_t* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n, int ncols,
                           int32_t* codes, int64_t ldc, void* stream);
 
+/* The label side of the covariance of one-hot / null-indicator columns with a CONTINUOUS label
+ * (U/stats/OpStatistics.scala:86-90), next to the plain counts of tmog_pivot_count_dev (nclasses = 1):
+ * wsum [wsum_offset[c] + id] += label[r] - shift for the row's id in column c (0 = null, 1 + slot(code); col_desc and
+ * slots as in tmog_pivot_count_dev; wsum is f64 with nids_c entries per column, NOT cleared here). */
+int tmog_pivot_label_sum_dev(const int32_t* codes, int64_t ld, int64_t n, int ncols, const int64_t* col_desc,
+                             const int32_t* slots, const int64_t* wsum_offset, const double* label, double shift,
+                             double* wsum, void* stream);
+
 /* Replaces OneHotModelFun.pivotFn  C/stages/impl/feature/OpOneHotVectorizer.scala:416-437  for single-valued inputs
  * (exactly one of {top value, OTHER, null indicator} is 1.0 per row and column) fused with reindex
  * (Transmogrifier.scala:437-449) and SanityCheckerModel's removeFeatures:  out[r][out_col0 + c] = pos_c[code], the
@@ -254,7 +262,8 @@ int tmog_set_count_dev(const int64_t* offsets, const int32_t* codes, int64_t n, 
  *   to get row_nnz [n], prefix-sum it into row_start [n], call again to write out_idx / out_val. */
 int tmog_set_stats_dev(const int64_t* offsets, const int32_t* codes, int64_t n, const int32_t* pos, int ncodes, int k,
                        int track_nulls, const uint8_t* class_ids, int nclasses, uint32_t* class_sum, uint32_t* present,
-                       uint64_t* sq_extra, uint32_t* aux, int32_t* bad, void* stream);
+                       uint64_t* sq_extra, uint32_t* aux, const double* label, double label_shift, double* wsum,
+                       int32_t* bad, void* stream);
 int tmog_set_transform_dev(const int64_t* offsets, const int32_t* codes, int64_t n, const int32_t* pos, int ncodes,
                            int k, int track_nulls, const int32_t* newpos, const int64_t* row_start, int32_t* row_nnz,
                            int32_t* out_idx, int32_t* out_val, int32_t* bad, void* stream);
@@ -280,6 +289,10 @@ int tmog_set_transform_dev(const int64_t* offsets, const int32_t* codes, int64_t
  *   bucket_sq_extra [index] += tf^2 - tf   (so that sum v^2 = sum v + extra), and
  *   bucket_aux [3 * index + {0, 1, 2}] (zeroed by the caller) = max tf, ~(min tf among tf > 1), rows with tf > 1 --
  *   they give the exact column max / min.
+ *   Continuous label (more distinct values than label classes are tracked; nclasses = 1): with label (device f64 [n])
+ *   and bucket_wsum (f64 per index) given, bucket_wsum [index] += tf * (label[row] - label_shift), which with the sums
+ *   above gives the covariance of every column with the label (U/stats/OpStatistics.scala:86-90); both NULL otherwise.
+ *   tmog_set_stats_dev's label / wsum [k + 2] and tmog_pivot_label_sum_dev do the same for their columns.
  * _transform: sparse rows in 4-array CSR form: row r owns out_idx / out_val [row_start[r], row_start[r] + row_nnz[r]),
  *   indices ascending; newpos [null_base + ncols] maps a vector index to its output index or -1 (dropped by
  *   SanityChecker); *cursor (device u64, zeroed by the caller) ends as the total number of entries; entries beyond
@@ -288,7 +301,8 @@ int tmog_text_hash_scratch_bytes(int64_t n, size_t* bytes);
 int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
                              const int32_t* prefix_len, const int32_t* params, const uint8_t* class_ids,
                              uint32_t* bucket_class_sum, uint32_t* bucket_dup, uint64_t* bucket_sq_extra,
-                             uint32_t* bucket_aux, int32_t* flags, void* scratch, size_t scratch_bytes, void* stream);
+                             uint32_t* bucket_aux, const double* label, double label_shift, double* bucket_wsum,
+                             int32_t* flags, void* scratch, size_t scratch_bytes, void* stream);
 int tmog_text_hash_transform_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
                                  const int32_t* prefix_len, const int32_t* params, const int32_t* newpos,
                                  int64_t* row_start, int32_t* row_nnz, int32_t* out_idx, int32_t* out_val,

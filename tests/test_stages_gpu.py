@@ -242,3 +242,70 @@ def test_transmogrify_all_types_matches_oracle(device):
     got = out_batch.vectors[checked.name].to_scipy()
     exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
     assert got.shape == exp.shape and abs(got - exp).max() < 1e-9
+
+
+def test_transmogrify_all_types_continuous_label_matches_oracle():
+    """A regression label (every value distinct): no categorical tests, and the label correlations of the one-hot,
+    multiplicity, null-indicator and hashed columns come from per-column label sums taken in the fused scans."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+    rng = np.random.default_rng(41)
+    n = 2000
+    z = rng.normal(0, 1, n)
+    y = 100.0 + 3.0 * z + rng.normal(0, 0.5, n)
+    opt = lambda v, p: None if rng.random() < p else v   # noqa: E731
+    b0 = [opt(bool(zz + rng.normal(0, 1) > 0), 0.1) for zz in z]
+    p0 = [opt(["x", "y", "z", "X ", "w"][int(np.clip(round(zz + 2), 0, 4))], 0.08) for zz in z]
+    r0 = [opt(float(zz * 2 + rng.normal(0, 1)), 0.1) for zz in z]
+    nn = [float(v) for v in rng.normal(5, 2, n)]
+    words = ["".join(rng.choice(list("abcdefgh"), size=rng.integers(3, 7))) for _ in range(150)]
+    t0 = [opt(" ".join([words[i] for i in rng.integers(0, 150, rng.poisson(8))] + (["zq zq"] if zz > 0.5 else [])), 0.06)
+          for zz in z]
+    t1 = [opt(["red", "Green", "blue", "blue!"][int(rng.integers(4))], 0.05) for _ in z]
+    s0 = [opt([["a", "A "], ["b"], ["a", "c", "d"], []][int(rng.integers(4))] + (["hi"] if zz > 0 else []), 0.07)
+          for zz in z]
+    data = {"b0": (F.BINARY, b0), "p0": (F.PICKLIST, p0), "r0": (F.REAL, r0), "nn": (F.REALNN, nn), "t0": (F.TEXT, t0),
+            "t1": (F.TEXT, t1), "s0": (F.MULTIPICKLIST, s0), "y": (F.REALNN, y.tolist())}
+    batch = _batch(data, response="y", device="cuda")
+    FB = F.FeatureBuilder
+    feats = [FB.Text("t0").asPredictor(), FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(),
+             FB.RealNN("nn").asPredictor(), FB.PickList("p0").asPredictor(), FB.Text("t1").asPredictor(),
+             FB.MultiPickList("s0").asPredictor()]
+    label = FB.RealNN("y").asResponse()
+    checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
+                                sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
+    out_batch, fitted = fit_and_transform(batch, checked)
+    est = checked.origin_stage
+    # oracle; Transmogrifier.scala:114 order: Binary < MultiPickList < PickList < Real < RealNN < Text
+    xb = V.binary_vectorizer_transform([b0])
+    stops = V.pivot_fit([s0], 20, 10, True)
+    xs = V.pivot_transform([s0], stops, True, True)
+    tops = V.pivot_fit([p0], 20, 10, True)
+    xp = V.pivot_transform([p0], tops, True, True)
+    fills = V.real_vectorizer_fit([r0])
+    xr = V.real_vectorizer_transform([r0], fills, True)
+    xn = V.realnn_vectorizer_transform([nn])
+    methods, ttops = V.smart_text_fit([t0, t1], max_cardinality=30, top_k=20, min_support=10)
+    assert methods == ["Hash", "Pivot"]
+    xt = V.smart_text_transform([t0, t1], ["t0", "t1"], methods, ttops, num_features=512)
+    xo, metas = V.combine(
+        [xb, xs, xp, xr, xn, xt],
+        [V.numeric_metadata(["b0"], "Binary", True), V.pivot_metadata(["s0"], "MultiPickList", stops, True),
+         V.pivot_metadata(["p0"], "PickList", tops, True), V.numeric_metadata(["r0"], "Real", True),
+         V.numeric_metadata(["nn"], "RealNN", False), V.smart_text_metadata(["t0", "t1"], "Text", methods, ttops, 512, True)])
+    p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                       feature_feature_corr_level="off")
+    ref = S.sanity_fit(y, xo, metas, p, label_name="y")
+    assert not ref.cat_stats and not list(est.summary.categoricalStats)
+    assert est.summary.names[:-1] == [m.col_name() for m in metas]
+    assert est.summary.dropped == ref.dropped
+    assert fitted[-1].indicesToKeep == ref.indices_to_keep
+    np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+    assert np.array_equal(est.summary.min, ref.col_stats.min) and np.array_equal(est.summary.max, ref.col_stats.max)
+    np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                               equal_nan=True)
+    got = out_batch.vectors[checked.name].to_scipy()
+    import scipy.sparse as sp
+    exp = sp.csr_matrix(xo)[:, ref.indices_to_keep]
+    assert got.shape == exp.shape and abs(got - exp).max() < 1e-12

@@ -70,7 +70,7 @@ _need = ctypes.c_size_t(0); L.call("tmog_text_hash_scratch_bytes", n, ctypes.byr
 scratch = torch.empty(_need.value, dtype=torch.uint8, device="cuda")
 def stats():
     L.call("tmog_text_hash_stats_dev", d_desc.data_ptr(), ncols, n, d_prefix.data_ptr(), d_plen.data_ptr(), params.ctypes.data,
-           cls.data_ptr(), class_sum.data_ptr(), nnz.data_ptr(), extra.data_ptr(), aux.data_ptr(), flags.data_ptr(), scratch.data_ptr(), scratch.numel(), st)
+           cls.data_ptr(), class_sum.data_ptr(), nnz.data_ptr(), extra.data_ptr(), aux.data_ptr(), None, 0.0, None, flags.data_ptr(), scratch.data_ptr(), scratch.numel(), st)
 def timeit(f, reps=3):
     f(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -57,14 +57,15 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_binary_codes_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _i64, _p],
     "tmog_pivot_transform_dev": [_p, _i64, _i64, _int, _p, _p, _p, _i64, _i64, _p],
     "tmog_set_count_dev": [_p, _p, _i64, _p, _int, _int, _p, _int, _p, _p, _p],
-    "tmog_set_stats_dev": [_p, _p, _i64, _p, _int, _int, _int, _p, _int, _p, _p, _p, _p, _p, _p],
+    "tmog_set_stats_dev": [_p, _p, _i64, _p, _int, _int, _int, _p, _int, _p, _p, _p, _p, _p, _dbl, _p, _p, _p],
+    "tmog_pivot_label_sum_dev": [_p, _i64, _i64, _int, _p, _p, _p, _p, _dbl, _p, _p],
     "tmog_set_transform_dev": [_p, _p, _i64, _p, _int, _int, _int, _p, _p, _p, _p, _p, _p, _p],
     "tmog_text_stats_layout": [_int, _int, _int, C.POINTER(_sz), C.POINTER(_sz)],
     "tmog_text_stats_table_bytes": [_int, _int, C.POINTER(_sz)],
     "tmog_text_stats_dev": [_p, _int, _i64, _p, _int, _int, _int, _int, _p, _p, _p],
     "tmog_text_codes_dev": [_p, _p, _int, _i64, _int, _int, _p, _p, _i64, _p],
     "tmog_text_hash_scratch_bytes": [_i64, C.POINTER(_sz)],
-    "tmog_text_hash_stats_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p],
+    "tmog_text_hash_stats_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _dbl, _p, _p, _p, _sz, _p],
     "tmog_text_hash_transform_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _p, _p, _sz, _p],
     "tmog_label_classes_scratch_bytes": [C.POINTER(_sz)],
     "tmog_label_classes_dev": [_p, _i64, _int, _p, _p, _p, _p, _p, _sz, _p],

@@ -210,6 +210,58 @@ pivot_transform_kernel(const int32_t* __restrict__ codes, int64_t ld, int64_t n,
     }
 }
 
+
+// Continuous label (more distinct values than label classes are tracked): one f64 sum per id,
+//   wsum [wsum_offset_c + id] += label[r] - shift   for the row's id (0 = null, 1 + slot(code)),
+// which together with the plain counts gives the covariance of every one-hot / null-indicator column with the label
+// (U/stats/OpStatistics.scala:86-90: sum (x - mean_x)(y - mean_y) = sum_x (y - s) - count (mean_y - s)).
+// A CTA takes a stretch of rows of one column; the first PL_HOT ids live in shared memory, the rest go to global
+// memory aggregated over the lanes that hit the same id.
+constexpr int PL_THREADS = 256;
+constexpr int PL_HOT = 4096;
+constexpr int PL_ROWS = 1 << 16;
+
+__global__ void __launch_bounds__(PL_THREADS)
+pivot_label_sum_kernel(const int32_t* __restrict__ codes, int64_t ld, int64_t n, const PivotColumn* __restrict__ cols,
+                       const int32_t* __restrict__ slots, const int64_t* __restrict__ wsum_offset,
+                       const double* __restrict__ label, double shift, double* __restrict__ wsum) {
+    __shared__ double hot[PL_HOT];
+    const int c = blockIdx.y;
+    const PivotColumn pc = cols[c];
+    const int32_t* col = codes + (int64_t)c * ld;
+    const int32_t* sl = slots ? slots + pc.slot_offset : nullptr;
+    double* g = wsum + wsum_offset[c];
+    const int nhot = (int)min((int64_t)PL_HOT, pc.nids);
+    for (int i = threadIdx.x; i < nhot; i += PL_THREADS) hot[i] = 0.0;
+    __syncthreads();
+    const int64_t r0 = (int64_t)blockIdx.x * PL_ROWS, r1 = min(n, r0 + PL_ROWS);
+    for (int64_t rb = r0; rb < r1; rb += PL_THREADS) {
+        const int64_t r = rb + threadIdx.x;
+        int id = -1;
+        double e = 0.0;
+        if (r < r1) {
+            const int code = col[r];
+            if (code < 0) id = 0;
+            else if (code < pc.ncodes) id = 1 + (sl ? sl[code] : code);
+            e = label[r] - shift;
+        }
+        if (id >= 0 && id < nhot) {
+            atomicAdd(&hot[id], e);
+        } else {
+            // cold ids: one global atomic per distinct id of the warp
+            const unsigned peers = __match_any_sync(__activemask(), id);
+            if (id >= 0) {
+                double sum = 0.0;
+                for (unsigned m = peers; m; m &= m - 1) sum += __shfl_sync(peers, e, __ffs(m) - 1);
+                if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&g[id], sum);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < nhot; i += PL_THREADS)
+        if (hot[i] != 0.0) atomicAdd(&g[i], hot[i]);
+}
+
 }  // namespace tmog
 
 using namespace tmog;
@@ -296,6 +348,20 @@ extern "C" int tmog_binary_codes_dev(const uint8_t* values, int64_t ld, const ui
     TMOG_REQUIRE(values && codes, "NULL argument");
     const int gx = (int)std::min<int64_t>((n + 255) / 256, (int64_t)tmog::sm_count() * 8);
     tmog::binary_codes_kernel<<<dim3(gx, ncols), 256, 0, (cudaStream_t)stream>>>(values, ld, valid, ldv, n, codes, ldc);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_pivot_label_sum_dev(const int32_t* codes, int64_t ld, int64_t n, int ncols, const int64_t* col_desc,
+                                        const int32_t* slots, const int64_t* wsum_offset, const double* label,
+                                        double shift, double* wsum, void* stream) {
+    TMOG_REQUIRE(n >= 0 && ncols >= 0 && ld >= n, "bad shape");
+    TMOG_REQUIRE(ncols == 0 || n == 0 || (codes && col_desc && wsum_offset && label && wsum), "NULL argument");
+    if (n == 0 || ncols == 0) return TMOG_OK;
+    const int64_t gx = (n + PL_ROWS - 1) / PL_ROWS;
+    TMOG_REQUIRE(gx <= 0x7fffffffLL && ncols <= 65535, "too many rows or columns for one call");
+    pivot_label_sum_kernel<<<dim3((unsigned)gx, (unsigned)ncols), PL_THREADS, 0, (cudaStream_t)stream>>>(
+        codes, ld, n, reinterpret_cast<const PivotColumn*>(col_desc), slots, wsum_offset, label, shift, wsum);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }

@@ -57,6 +57,7 @@ set_rows_kernel(const int64_t* __restrict__ offsets, const int32_t* __restrict__
                 // statistics (width = k + 2 slots: top values, OTHER, null)
                 unsigned int* __restrict__ class_sum, unsigned int* __restrict__ present,
                 unsigned long long* __restrict__ sq_extra, unsigned int* __restrict__ aux,
+                const double* __restrict__ label, double label_shift, double* __restrict__ wsum,
                 // sparse rows
                 const int32_t* __restrict__ newpos, const int64_t* __restrict__ row_start, int32_t* __restrict__ row_nnz,
                 int32_t* __restrict__ out_idx, int32_t* __restrict__ out_val, int* __restrict__ bad) {
@@ -69,6 +70,7 @@ set_rows_kernel(const int64_t* __restrict__ offsets, const int32_t* __restrict__
             if (MODE == 0) {
                 atomicAdd(&class_sum[(int64_t)slot * nclasses + cls], v);
                 atomicAdd(&present[(int64_t)slot * nclasses + cls], 1u);
+                if (label) atomicAdd(&wsum[slot], (double)v * (label[r] - label_shift));
                 if (v > 1u) {
                     atomicAdd(&sq_extra[slot], (unsigned long long)v * v - v);
                     atomicMax(&aux[3 * slot], v);
@@ -130,15 +132,17 @@ extern "C" int tmog_set_count_dev(const int64_t* offsets, const int32_t* codes, 
 extern "C" int tmog_set_stats_dev(const int64_t* offsets, const int32_t* codes, int64_t n, const int32_t* pos,
                                   int ncodes, int k, int track_nulls, const uint8_t* class_ids, int nclasses,
                                   uint32_t* class_sum, uint32_t* present, uint64_t* sq_extra, uint32_t* aux,
-                                  int32_t* bad, void* stream) {
+                                  const double* label, double label_shift, double* wsum, int32_t* bad, void* stream) {
     TMOG_REQUIRE(n >= 0 && ncodes >= 0 && k >= 0 && nclasses >= 1 && nclasses <= 255, "bad shape");
     TMOG_REQUIRE(class_sum && present && sq_extra && aux && bad && (n == 0 || offsets != nullptr), "NULL argument");
     TMOG_REQUIRE(nclasses == 1 || class_ids != nullptr || n == 0, "class_ids is NULL");
+    TMOG_REQUIRE((label == nullptr) == (wsum == nullptr), "label and wsum go together");
     if (n == 0) return TMOG_OK;
     TMOG_REQUIRE(ncodes == 0 || pos != nullptr, "pos is NULL");
     set_rows_kernel<0><<<set_grid(n), SET_THREADS, 0, (cudaStream_t)stream>>>(
         offsets, codes, n, pos, ncodes, k, track_nulls, class_ids, nclasses, class_sum, present,
-        reinterpret_cast<unsigned long long*>(sq_extra), aux, nullptr, nullptr, nullptr, nullptr, nullptr, bad);
+        reinterpret_cast<unsigned long long*>(sq_extra), aux, label, label_shift, wsum, nullptr, nullptr, nullptr,
+        nullptr, nullptr, bad);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }
@@ -156,12 +160,14 @@ extern "C" int tmog_set_transform_dev(const int64_t* offsets, const int32_t* cod
     cudaStream_t st = (cudaStream_t)stream;
     if (row_start == nullptr)
         set_rows_kernel<1><<<set_grid(n), SET_THREADS, 0, st>>>(offsets, codes, n, pos, ncodes, k, track_nulls, nullptr, 1,
-                                                                nullptr, nullptr, nullptr, nullptr, newpos, nullptr,
-                                                                row_nnz, nullptr, nullptr, bad);
+                                                                nullptr, nullptr, nullptr, nullptr, nullptr, 0.0,
+                                                                nullptr, newpos, nullptr, row_nnz, nullptr, nullptr,
+                                                                bad);
     else
         set_rows_kernel<2><<<set_grid(n), SET_THREADS, 0, st>>>(offsets, codes, n, pos, ncodes, k, track_nulls, nullptr, 1,
-                                                                nullptr, nullptr, nullptr, nullptr, newpos, row_start,
-                                                                row_nnz, out_idx, out_val, bad);
+                                                                nullptr, nullptr, nullptr, nullptr, nullptr, 0.0,
+                                                                nullptr, newpos, row_start, row_nnz, out_idx, out_val,
+                                                                bad);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }

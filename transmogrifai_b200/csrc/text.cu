@@ -493,6 +493,8 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                  // statistics mode
                  unsigned int* __restrict__ bucket_class_sum, unsigned int* __restrict__ bucket_dup,
                  unsigned long long* __restrict__ bucket_sq_extra, unsigned int* __restrict__ bucket_aux,
+                 // continuous label (or NULL): bucket_wsum [index] += tf * (label[row] - label_shift)
+                 const double* __restrict__ label, double label_shift, double* __restrict__ bucket_wsum,
                  // sparse-output mode
                  const int32_t* __restrict__ newpos, int64_t* __restrict__ row_start, int32_t* __restrict__ row_nnz,
                  int32_t* __restrict__ out_idx, int32_t* __restrict__ out_val, unsigned long long* __restrict__ cursor,
@@ -918,6 +920,7 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
             }
             if (!SPARSE_OUT) {
                 const int cls = (p.nclasses > 1 && class_ids) ? class_ids[row] : 0;
+                const double e_row = label ? label[row] - label_shift : 0.0;
                 // every lane looks at slots lane, lane + 32, ... and remembers the occupied ones in a bitmap, so that the
                 // emitting loop below runs with most lanes busy
                 // the rare term frequencies > 1 are set aside (in the token list, free by now) and handled afterwards
@@ -939,6 +942,7 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                             v = (unsigned)(sv >> cb);
                             cnt = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
                             atomicAdd(&bucket_class_sum[(int64_t)v * p.nclasses + cls], cnt);
+                            if (label) atomicAdd(&bucket_wsum[v], (double)cnt * e_row);
                         }
                         const unsigned rb = __ballot_sync(FULL, cnt > 1u);
                         if (rb) {
@@ -1225,6 +1229,9 @@ struct ThArgs {
     uint32_t *class_sum, *dup;
     unsigned long long* sq_extra;
     uint32_t* aux;
+    const double* label;
+    double label_shift;
+    double* wsum;
     const int32_t* newpos;
     int64_t* row_start;
     int32_t *row_nnz, *out_idx, *out_val;
@@ -1254,7 +1261,7 @@ static int th_launch(const ThArgs& a, int level, int max_token_bound) {
         level == 0 ? nullptr : lists + (size_t)(level - 1) * a.n, level == 0 ? nullptr : &a.scratch->defer_n[level - 1],
         &a.scratch->row_counter[level],
         level == 2 ? nullptr : lists + (size_t)level * a.n, level == 2 ? nullptr : &a.scratch->defer_n[level],
-        a.class_sum, a.dup, a.sq_extra, a.aux, a.newpos, a.row_start, a.row_nnz, a.out_idx, a.out_val, a.cursor,
+        a.class_sum, a.dup, a.sq_extra, a.aux, a.label, a.label_shift, a.wsum, a.newpos, a.row_start, a.row_nnz, a.out_idx, a.out_val, a.cursor,
         a.capacity, a.flags);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
@@ -1322,7 +1329,8 @@ static int text_hash_common(const int64_t* col_desc, int ncols, int64_t n, const
 extern "C" int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
                                         const int32_t* prefix_len, const int32_t* params, const uint8_t* class_ids,
                                         uint32_t* bucket_class_sum, uint32_t* bucket_dup, uint64_t* bucket_sq_extra,
-                                        uint32_t* bucket_aux, int32_t* flags, void* scratch, size_t scratch_bytes,
+                                        uint32_t* bucket_aux, const double* label, double label_shift,
+                                        double* bucket_wsum, int32_t* flags, void* scratch, size_t scratch_bytes,
                                         void* stream) {
     ThArgs a = {};
     if (int rc = text_hash_common(col_desc, ncols, n, prefix, prefix_len, params, scratch, scratch_bytes, &a)) return rc;
@@ -1334,6 +1342,10 @@ extern "C" int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int6
     a.dup = bucket_dup;
     a.sq_extra = reinterpret_cast<unsigned long long*>(bucket_sq_extra);
     a.aux = bucket_aux;
+    TMOG_REQUIRE((label == nullptr) == (bucket_wsum == nullptr), "label and bucket_wsum go together");
+    a.label = label;
+    a.label_shift = label_shift;
+    a.wsum = bucket_wsum;
     a.flags = flags;
     a.stream = (cudaStream_t)stream;
     return th_run<false>(a);

@@ -83,6 +83,49 @@ def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str, after_launc
     return out
 
 
+def label_moments_dev(batch: ColumnarBatch, y: torch.Tensor, name: str):
+    """A continuous label (more distinct values than label classes are tracked): its count, mean, variance, min, max
+    over all ranks, and the shift every label-sum kernel subtracts (rank 0's pilot mean).  Cached on the batch."""
+    cache = batch.__dict__.setdefault("_label_cache", {})
+    key = (name, "moments")
+    if key in cache:
+        return cache[key]
+    n = batch.n
+    nb = C.c_size_t()
+    L.call("tmog_real_fit_scratch_bytes", 0, C.byref(nb))
+    scratch = R.scratch("real_fit", nb.value)
+    d_shift = torch.zeros(1, dtype=torch.float64, device="cuda")
+    d_part = torch.zeros(L.REAL_NSTAT, dtype=torch.float64, device="cuda")
+    ld = round_up(max(n, 1), 2)
+    L.call("tmog_real_pilot_shift_dev", None, ld, None, 0, y.data_ptr(), n, 0, d_shift.data_ptr(), R.stream())
+    if D.world()[1] > 1:
+        torch.distributed.broadcast(d_shift, src=0)
+    L.call("tmog_real_fit_partials_dev", None, ld, None, 0, y.data_ptr(), n, 0, d_shift.data_ptr(),
+           scratch.data_ptr(), scratch.numel(), d_part.data_ptr(), R.stream())
+    partials = D.allreduce_real_partials(d_part.cpu().numpy())
+    shift = d_shift.cpu().numpy()
+    lab = np.zeros(5)
+    L.call("tmog_real_finish", partials.ctypes.data, shift.ctypes.data, 0, 1, 0.0, 0, None, None, None, None, None,
+           None, lab.ctypes.data, None)
+    out = (lab, float(shift[0]))
+    cache[key] = out
+    return out
+
+
+def stats_from_sums_continuous(sv: np.ndarray, sv2: np.ndarray, nnz: np.ndarray, vmax: np.ndarray, vmin: np.ndarray,
+                               wsum: np.ndarray, lab: np.ndarray, shift: float, label_name: str) -> VectorStats:
+    """Statistics of non-negative integer-valued columns (indicators, term frequencies) against a continuous label:
+    sv = sum v, sv2 = sum v^2, nnz = rows with v > 0, vmax / vmin = max / min of v over those rows,
+    wsum = sum v (y - shift); cov(v, y) = wsum - sv (mean_y - shift)   (U/stats/OpStatistics.scala:86-90)."""
+    n = int(lab[0])
+    mean = sv / n if n else np.zeros_like(sv)
+    var = np.maximum((sv2 - sv * sv / n) / (n - 1), 0.0) if n > 1 else np.zeros_like(sv)
+    mx = np.where(nnz > 0, vmax, 0.0).astype(np.float64)
+    mn = np.where(nnz >= n, vmin, 0.0).astype(np.float64)
+    cov = wsum - sv * (lab[1] - shift)
+    return VectorStats(LabelInfo(label_name, n, lab, None, None), mean, var, mn, mx, cov, None)
+
+
 class RealVectorizer(OpEstimator):
     """Fill nulls with the mean (or a constant) and optionally emit a null indicator per input."""
 
@@ -391,9 +434,7 @@ def _binary_stats(batch: ColumnarBatch, block: NumericBlock, track_nulls: bool, 
     y = batch.label()
     y = y if y.is_cuda else y.cuda()
     classes, class_counts, ids = label_info_dev(batch, y, label_name)
-    if classes is None:
-        return None
-    n, ncols, ncls = batch.n, len(block.names), len(classes)
+    n, ncols, ncls = batch.n, len(block.names), (len(classes) if classes is not None else 1)
     ldc = round_up(max(n, 1), 4)
     codes = torch.empty((ncols, ldc), dtype=torch.int32, device="cuda")
     L.call("tmog_binary_codes_dev", dev.values.data_ptr(), dev.ld, R.ptr(dev.valid), dev.ldv, n, ncols,
@@ -404,10 +445,27 @@ def _binary_stats(batch: ColumnarBatch, block: NumericBlock, track_nulls: bool, 
     d_desc = torch.from_numpy(desc).cuda()
     d_counts = torch.zeros(ncols * 3 * ncls, dtype=torch.int32, device="cuda")
     d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
-    L.call("tmog_pivot_count_dev", codes.data_ptr(), ldc, n, ncols, ids.data_ptr(), ncls, d_desc.data_ptr(), None, 3,
-           d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
+    L.call("tmog_pivot_count_dev", codes.data_ptr(), ldc, n, ncols, ids.data_ptr() if classes is not None else None,
+           ncls, d_desc.data_ptr(), None, 3, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
     cnt = D.allreduce_sum(d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(ncols, 3, ncls)
     n_global = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
+    if classes is None:                              # continuous label: counts + label sums per {null, false, true}
+        lab, shift = label_moments_dev(batch, y, label_name)
+        d_ws = torch.zeros(ncols * 3, dtype=torch.float64, device="cuda")
+        d_off = torch.arange(0, ncols * 3, 3, dtype=torch.int64, device="cuda")
+        L.call("tmog_pivot_label_sum_dev", codes.data_ptr(), ldc, n, ncols, d_desc.data_ptr(), None, d_off.data_ptr(),
+               y.data_ptr(), shift, d_ws.data_ptr(), R.stream())
+        ws = D.allreduce_sum(d_ws.cpu().numpy()).reshape(ncols, 3)
+        c1, w1 = [], []
+        for c in range(ncols):
+            c1.append(cnt[c, 2, 0] + (cnt[c, 0, 0] if fill_value else 0))
+            w1.append(ws[c, 2] + (ws[c, 0] if fill_value else 0.0))
+            if track_nulls:
+                c1.append(cnt[c, 0, 0])
+                w1.append(ws[c, 0])
+        sv = np.asarray(c1, dtype=np.float64)
+        ones = np.ones_like(sv)
+        return stats_from_sums_continuous(sv, sv, sv, ones, ones, np.asarray(w1), lab, shift, label_name)
     rows = []
     for c in range(ncols):
         ones = cnt[c, 2] + (cnt[c, 0] if fill_value else 0)

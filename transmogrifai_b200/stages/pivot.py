@@ -24,7 +24,7 @@ from ..columnar import (ColumnarBatch, DictBlock, LazyOneHotPart, OneHotPart, Ve
 from ..metadata import NullString, OpVectorColumnMetadata, OpVectorMetadata, OtherString
 from ..stats import LabelInfo, VectorStats
 from .base import OpEstimator, OpModel
-from .numeric import label_info_dev
+from .numeric import label_info_dev, label_moments_dev, stats_from_sums_continuous
 
 
 def clean_and_group(strings: Sequence[str], clean: bool) -> Tuple[np.ndarray, List[str]]:
@@ -226,6 +226,28 @@ class OpTextPivotVectorizer(OpEstimator):
         if label_name and classes is not None:
             stats = _stats_from_class_counts(np.concatenate([r[2] for r in results], axis=0), classes,
                                              counts_per_class, n_global, label_name)
+        elif label_name:
+            # continuous label: the plain counts above (one class) + the label sums of every raw code, folded into the
+            # emitted columns (top values, OTHER, null) with the code -> column table of the finish
+            lab, shift = label_moments_dev(batch, y, label_name)
+            w_off = np.concatenate([[0], np.cumsum(nids)[:-1]]).astype(np.int64) if ncols else zeros
+            d_ws = torch.zeros(max(int(nids.sum()), 1), dtype=torch.float64, device="cuda")
+            d_woff = torch.from_numpy(w_off).cuda()
+            L.call("tmog_pivot_label_sum_dev", dev.codes.data_ptr(), dev.ld, n, ncols, d_desc.data_ptr(), None,
+                   d_woff.data_ptr(), y.data_ptr(), shift, d_ws.data_ptr(), R.stream())
+            ws = d_ws.cpu().numpy()
+            cnt_cols, ws_cols = [], []
+            for c in range(ncols):
+                k = len(tops[c])
+                w = ws[w_off[c]:w_off[c] + nids[c]]
+                folded = np.bincount(results[c][1], weights=w[1:], minlength=k + 1)[:k + 1]
+                folded = np.append(folded, w[0])                       # the null indicator
+                ws_cols.append(folded[:results[c][2].shape[0]])
+                cnt_cols.append(results[c][2][:, 0])
+            sv = np.concatenate(cnt_cols)
+            ones = np.ones_like(sv)
+            stats = stats_from_sums_continuous(sv, sv, sv, ones, ones, D.allreduce_sum(np.concatenate(ws_cols)), lab,
+                                               shift, label_name)
         model = OpTextPivotVectorizerModel(self, tops, self.cleanText, self.trackNulls)
         model._fit_stats = stats
         model._fit_key = (block.codes.data_ptr(), n)

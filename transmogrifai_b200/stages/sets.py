@@ -23,7 +23,7 @@ from .. import runtime as R
 from ..columnar import ColumnarBatch, LazyPart, SetBlock, SparseRowsPart, VectorColumn
 from ..stats import LabelInfo, VectorStats
 from .base import OpModel
-from .numeric import label_info_dev
+from .numeric import label_info_dev, label_moments_dev, stats_from_sums_continuous
 from .pivot import OpTextPivotVectorizer, clean_and_group, top_k
 
 
@@ -81,8 +81,9 @@ class OpSetVectorizer(OpTextPivotVectorizer):
         model = OpSetVectorizerModel(self, tops, self.cleanText, self.trackNulls)
         model._pos_cache = {id(block.dicts[c]): (block.dicts[c], pos_tables[c]) for c in range(ncols)}
         model._fit_key = (dev.offsets[0].data_ptr(), n) if ncols else None
-        if label_name and classes is not None:
-            model._fit_stats = model._sidecar(dev, n, n_all, classes, class_counts, ids, label_name)
+        if label_name:
+            cont = None if classes is not None else label_moments_dev(batch, y, label_name) + (y,)
+            model._fit_stats = model._sidecar(dev, n, n_all, classes, class_counts, ids, label_name, cont)
         return model
 
 
@@ -113,9 +114,11 @@ class OpSetVectorizerModel(OpModel):
         self._pos_cache[id(d)] = (d, table)
         return table
 
-    def _sidecar(self, dev: SetBlock, n: int, n_all: int, classes, class_counts, ids, label_name: str) -> VectorStats:
-        ncls = len(classes)
-        cs_all, pr_all, ex_all, ax_all = [], [], [], []
+    def _sidecar(self, dev: SetBlock, n: int, n_all: int, classes, class_counts, ids, label_name: str,
+                 cont=None) -> VectorStats:
+        """cont = (label moments, shift, label on the device) for a continuous label (then classes is None)."""
+        ncls = len(classes) if classes is not None else 1
+        cs_all, pr_all, ex_all, ax_all, ws_all = [], [], [], [], []
         d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
         for c in range(len(dev.names)):
             k = len(self.topValues[c])
@@ -125,15 +128,20 @@ class OpSetVectorizerModel(OpModel):
             pr = torch.zeros(w * ncls, dtype=torch.int32, device="cuda")
             ex = torch.zeros(w, dtype=torch.int64, device="cuda")
             ax = torch.zeros(3 * w, dtype=torch.int32, device="cuda")
+            ws = torch.zeros(w, dtype=torch.float64, device="cuda") if cont is not None else None
             L.call("tmog_set_stats_dev", dev.offsets[c].data_ptr(), dev.codes[c].data_ptr(), n, pos.data_ptr(),
-                   len(dev.dicts[c]), k, int(self.shouldTrackNulls), ids.data_ptr(), ncls, cs.data_ptr(),
-                   pr.data_ptr(), ex.data_ptr(), ax.data_ptr(), d_bad.data_ptr(), R.stream())
+                   len(dev.dicts[c]), k, int(self.shouldTrackNulls), ids.data_ptr() if classes is not None else None,
+                   ncls, cs.data_ptr(), pr.data_ptr(), ex.data_ptr(), ax.data_ptr(),
+                   cont[2].data_ptr() if cont is not None else None, cont[1] if cont is not None else 0.0,
+                   ws.data_ptr() if cont is not None else None, d_bad.data_ptr(), R.stream())
             u32 = lambda t: t.cpu().numpy().astype(np.int64) & 0xFFFFFFFF   # noqa: E731
             keep = self.widths[c]                      # without the null slot when nulls are not tracked
             cs_all.append(u32(cs).reshape(w, ncls)[:keep])
             pr_all.append(u32(pr).reshape(w, ncls)[:keep])
             ex_all.append(ex.cpu().numpy()[:keep])
             ax_all.append(u32(ax).reshape(w, 3)[:keep])
+            if cont is not None:
+                ws_all.append(ws.cpu().numpy()[:keep])
         cs = D.allreduce_sum(np.concatenate(cs_all)).astype(np.float64)
         pr = D.allreduce_sum(np.concatenate(pr_all)).astype(np.float64)
         ex = D.allreduce_sum(np.concatenate(ex_all)).astype(np.float64)
@@ -143,6 +151,12 @@ class OpSetVectorizerModel(OpModel):
                            D.allreduce_sum(ax[:, 2].copy())], axis=1)
         if int(d_bad.item()):
             raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
+        if cont is not None:
+            sv, nnz = cs[:, 0], pr[:, 0]
+            vmax = np.maximum(ax[:, 0], 1).astype(np.float64)
+            vmin = np.where(ax[:, 2] >= nnz, (~ax[:, 1]) & 0xFFFFFFFF, 1).astype(np.float64)
+            return stats_from_sums_continuous(sv, sv + ex, nnz, vmax, vmin, D.allreduce_sum(np.concatenate(ws_all)),
+                                              cont[0], cont[1], label_name)
         cc = class_counts.astype(np.float64)
         mean_y = float((classes * cc).sum() / n_all)
         var_y = float((cc * (classes - mean_y) ** 2).sum() / (n_all - 1)) if n_all > 1 else 0.0

@@ -21,7 +21,7 @@ from ..columnar import ColumnarBatch, LazyPart, OneHotPart, SparseRowsPart, Text
 from ..metadata import NullString, OpVectorColumnMetadata, OpVectorMetadata, OtherString, feature_column
 from ..stats import LabelInfo, VectorStats
 from .base import OpEstimator, OpModel
-from .numeric import label_info_dev
+from .numeric import label_info_dev, label_moments_dev, stats_from_sums_continuous
 from .pivot import _stats_from_class_counts, clean_and_group, top_k
 
 PIVOT, HASH, IGNORE = "Pivot", "Hash", "Ignore"
@@ -222,9 +222,9 @@ class SmartTextVectorizer(OpEstimator):
             y = batch.label()
             y = y if y.is_cuda else y.cuda()
             classes, class_counts, ids = label_info_dev(batch, y, label_name)
-            if classes is not None:
-                n_all = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
-                model._fit_stats = model._sidecar(dev, n, n_all, classes, class_counts, ids, label_name)
+            n_all = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
+            cont = None if classes is not None else label_moments_dev(batch, y, label_name) + (y,)
+            model._fit_stats = model._sidecar(dev, n, n_all, classes, class_counts, ids, label_name, cont)
         model._fit_key = (block.offsets[0].data_ptr(), n)
         return model
 
@@ -472,9 +472,12 @@ class SmartTextVectorizerModel(OpModel):
         return sub, torch.from_numpy(prefix).cuda(), torch.from_numpy(plen).cuda(), params
 
     # -- statistics sidecar --------------------------------------------------------------------------------------------
-    def _sidecar(self, dev: TextBlock, n: int, n_all: int, classes, class_counts, ids, label_name: str) -> VectorStats:
-        """n = local rows, n_all = rows of all ranks; the count tables and bucket sums are all-reduced."""
-        ncls = len(classes)
+    def _sidecar(self, dev: TextBlock, n: int, n_all: int, classes, class_counts, ids, label_name: str,
+                 cont=None) -> VectorStats:
+        """n = local rows, n_all = rows of all ranks; the count tables and bucket sums are all-reduced.
+        cont = (label moments, shift, label on the device) for a continuous label (then classes is None)."""
+        ncls = len(classes) if classes is not None else 1
+        ids_ptr = ids.data_ptr() if classes is not None else None
         parts = []
         if self.pivot_idx:
             codes, ld, slots, slot_of = self._pivot_tables(dev, n)
@@ -488,10 +491,17 @@ class SmartTextVectorizerModel(OpModel):
             d_desc = torch.from_numpy(desc).cuda()
             d_counts = torch.zeros(k * nids * ncls, dtype=torch.int32, device="cuda")
             d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
-            L.call("tmog_pivot_count_dev", codes.data_ptr(), ld, n, k, ids.data_ptr(), ncls, d_desc.data_ptr(), None,
+            L.call("tmog_pivot_count_dev", codes.data_ptr(), ld, n, k, ids_ptr, ncls, d_desc.data_ptr(), None,
                    nids, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
             cnt = D.allreduce_sum(d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(k, nids, ncls)
-            rows = []
+            ws = None
+            if cont is not None:
+                d_ws = torch.zeros(k * nids, dtype=torch.float64, device="cuda")
+                d_woff = torch.arange(0, k * nids, nids, dtype=torch.int64, device="cuda")
+                L.call("tmog_pivot_label_sum_dev", codes.data_ptr(), ld, n, k, d_desc.data_ptr(), None,
+                       d_woff.data_ptr(), cont[2].data_ptr(), cont[1], d_ws.data_ptr(), R.stream())
+                ws = D.allreduce_sum(d_ws.cpu().numpy()).reshape(k, nids)
+            rows, wrows = [], []
             for t, j in enumerate(self.pivot_idx):
                 top = self.topValues[j]
                 tab = cnt[t]                       # row 0 = null, row 1 + s = slot s, row 1 + slots = unknown
@@ -503,8 +513,19 @@ class SmartTextVectorizerModel(OpModel):
                 if self.shouldTrackNulls:
                     r.append(tab[0])
                 rows.append(np.stack(r).astype(np.float64))
-            parts.append(_stats_from_class_counts(np.concatenate(rows, axis=0), classes, class_counts, n_all,
-                                                  label_name))
+                if ws is not None:
+                    wr = [ws[t][i] for i in chosen] + [ws[t][rest].sum()]
+                    if self.shouldTrackNulls:
+                        wr.append(ws[t][0])
+                    wrows.append(np.asarray(wr))
+            if cont is None:
+                parts.append(_stats_from_class_counts(np.concatenate(rows, axis=0), classes, class_counts, n_all,
+                                                      label_name))
+            else:
+                sv = np.concatenate(rows, axis=0)[:, 0]
+                ones = np.ones_like(sv)
+                parts.append(stats_from_sums_continuous(sv, sv, sv, ones, ones, np.concatenate(wrows), cont[0], cont[1],
+                                                        label_name))
         lay = self.layout
         if lay.text_idx:
             if lay.ignore_idx:
@@ -519,9 +540,12 @@ class SmartTextVectorizerModel(OpModel):
             aux = torch.zeros(3 * w, dtype=torch.int32, device="cuda")
             flags = torch.zeros(4, dtype=torch.int32, device="cuda")
             desc = _col_desc(sub)
+            wsum = torch.zeros(w, dtype=torch.float64, device="cuda") if cont is not None else None
             L.call("tmog_text_hash_stats_dev", desc.data_ptr(), len(lay.hash_idx), n, d_prefix.data_ptr(),
-                   d_plen.data_ptr(), params.ctypes.data, ids.data_ptr(), class_sum.data_ptr(), dup.data_ptr(),
-                   extra.data_ptr(), aux.data_ptr(), flags.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
+                   d_plen.data_ptr(), params.ctypes.data, ids_ptr, class_sum.data_ptr(), dup.data_ptr(),
+                   extra.data_ptr(), aux.data_ptr(), cont[2].data_ptr() if cont is not None else None,
+                   cont[1] if cont is not None else 0.0, wsum.data_ptr() if cont is not None else None,
+                   flags.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
             _check_hash_flags(flags)
             cs = (class_sum.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(w, ncls).astype(np.float64)
             # rows holding an index = sum of its term frequencies - (tf - 1) of the rows with tf > 1
@@ -535,8 +559,15 @@ class SmartTextVectorizerModel(OpModel):
                 cs, nz, ex = D.allreduce_sum(cs), D.allreduce_sum(nz), D.allreduce_sum(ex)
                 ax = np.stack([D.allreduce_max(ax[:, 0].copy()), D.allreduce_max(ax[:, 1].copy()),
                                D.allreduce_sum(ax[:, 2].copy())], axis=1)
-            parts.append(_stats_from_bucket_sums(cs, nz, ex, ax, classes, class_counts, n_all, label_name,
-                                                 lay.hash_width))
+            if cont is None:
+                parts.append(_stats_from_bucket_sums(cs, nz, ex, ax, classes, class_counts, n_all, label_name,
+                                                     lay.hash_width))
+            else:
+                wv = D.allreduce_sum(wsum.cpu().numpy()[:len(nz)])
+                sv = cs[:, 0]
+                vmax = np.maximum(ax[:, 0], 1).astype(np.float64)
+                vmin = np.where(ax[:, 2] >= nz, ((~ax[:, 1]) & 0xFFFFFFFF), 1).astype(np.float64)
+                parts.append(stats_from_sums_continuous(sv, sv + ex, nz, vmax, vmin, wv, cont[0], cont[1], label_name))
         return VectorStats.concat(parts)
 
     # -- transform -----------------------------------------------------------------------------------------------------
