@@ -126,52 +126,118 @@ dense_gather_kernel(const double* __restrict__ x, int64_t ld, int64_t n, const i
     }
 }
 
-// G[i][j] += sum_r (x[r][i] - s_i)(x[r][j] - s_j), label as column d.  32x32 output tile per CTA over one row chunk
-// (grid.z), upper-triangular tiles only; 16x16 threads, 2x2 outputs each; fp64 atomics merge the row chunks.
-constexpr int GR_ROWS = 64;
-__global__ void __launch_bounds__(256)
-dense_gram_kernel(const double* __restrict__ x, int64_t ld, int64_t n, int d, const double* __restrict__ label,
-                  const double* __restrict__ shifts, int64_t rows_per_cta, double* __restrict__ G) {
+// G[i][j] += sum_r (x[r][i] - s_i)(x[r][j] - s_j), label as column d; fp64 atomics merge the row stretches.
+// On the fp64 tensor cores (mma.sync m8n8k4, DMMA): G = sum over row chunks of X_c^T X_c.  A CTA of
+// four warps owns a 64 x 64 output tile (upper-triangular tiles only) over one stretch of rows (grid.z); 32 shifted
+// rows at a time are staged in shared memory (row stride 68 doubles: the fragment loads of a half-warp hit 16 distinct
+// banks), every warp keeps a 32 x 32 block of the tile in 4 x 4 accumulator fragments and issues 16 DMMAs per 8
+// fragment loads.  Fragment layout of m8n8k4 (PTX ISA): A[m][k] and B[k][n] are held by lane (m or n) * 4 + k, which for
+// X^T X is the same shared-memory index pattern on both sides; C[m][n] by lane m * 4 + n / 2, two values each.
+constexpr int GM_TILE = 64;
+constexpr int GM_KC = 32;
+constexpr int GM_LD = 68;
+
+__device__ __forceinline__ void dmma_m8n8k4(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0, %1}, {%2}, {%3}, {%0, %1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gmem_src) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N)); }
+
+// Raw values are staged with cp.async into two buffers (the copy of the next 32 rows overlaps the DMMAs of the current
+// ones); the shifts are subtracted when the fragments are read.  Positions outside the matrix are staged as the
+// shift itself, so that they contribute zero.
+constexpr int GM_STAGE = GM_KC * GM_LD;          // doubles per staged tile
+
+__global__ void __launch_bounds__(128)
+dense_gram_dmma_kernel(const double* __restrict__ x, int64_t ld, int64_t n, int d, const double* __restrict__ label,
+                       const double* __restrict__ shifts, int64_t rows_per_cta, double* __restrict__ G) {
     const int ti = blockIdx.x, tj = blockIdx.y;
     if (tj < ti) return;
-    __shared__ double A[GR_ROWS][33], B[GR_ROWS][33];
+    extern __shared__ double gm_smem[];          // [2 stages][A | B][GM_KC][GM_LD]
+    const bool diag = ti == tj;
     const int D = d + 1;
-    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wi = warp >> 1, wj = warp & 1;
     const int64_t r0 = (int64_t)blockIdx.z * rows_per_cta;
     const int64_t r1 = min(n, r0 + rows_per_cta);
-    double acc[2][2] = {{0, 0}, {0, 0}};
-    for (int64_t rb = r0; rb < r1; rb += GR_ROWS) {
-        for (int i = threadIdx.x; i < GR_ROWS * 32; i += 256) {
-            const int rr = i >> 5, cc = i & 31;
+    double acc[4][4][2];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+    // loader: this thread's column of the staged tiles
+    const int cc = tid & 63, rhalf = tid >> 6;           // 2 rows of 64 columns per pass of the CTA
+    const int ca = ti * GM_TILE + cc, cb = tj * GM_TILE + cc;
+    const double sa = ca < D ? shifts[ca] : 0.0, sb = cb < D ? shifts[cb] : 0.0;
+    auto stage = [&](int64_t rb, int buf) {
+        double* As = gm_smem + buf * 2 * GM_STAGE;
+        double* Bs = As + GM_STAGE;
+#pragma unroll 4
+        for (int rr = rhalf; rr < GM_KC; rr += 2) {
             const int64_t r = rb + rr;
-            const int ca = ti * 32 + cc, cb = tj * 32 + cc;
-            double va = 0.0, vb = 0.0;
-            if (r < r1) {
-                if (ca < D) va = (ca == d ? label[r] : x[r * ld + ca]) - shifts[ca];
-                if (cb < D) vb = (cb == d ? label[r] : x[r * ld + cb]) - shifts[cb];
+            if (r < r1 && ca < D) cp_async8(&As[rr * GM_LD + cc], ca == d ? label + r : x + r * ld + ca);
+            else As[rr * GM_LD + cc] = sa;
+            if (!diag) {
+                if (r < r1 && cb < D) cp_async8(&Bs[rr * GM_LD + cc], cb == d ? label + r : x + r * ld + cb);
+                else Bs[rr * GM_LD + cc] = sb;
             }
-            A[rr][cc] = va;
-            B[rr][cc] = vb;
+        }
+        cp_async_commit();
+    };
+    // fragments: [k = lane & 3][column = lane >> 2]; shifts of the 4 + 4 fragment columns of this lane
+    const int frag = (lane & 3) * GM_LD + (lane >> 2);
+    double sha[4], shb[4];
+#pragma unroll
+    for (int m = 0; m < 4; ++m) {
+        const int ia = ti * GM_TILE + wi * 32 + m * 8 + (lane >> 2), ib = tj * GM_TILE + wj * 32 + m * 8 + (lane >> 2);
+        sha[m] = ia < D ? shifts[ia] : 0.0;
+        shb[m] = ib < D ? shifts[ib] : 0.0;
+    }
+    int buf = 0;
+    if (r0 < r1) stage(r0, 0);
+    for (int64_t rb = r0; rb < r1; rb += GM_KC) {
+        if (rb + GM_KC < r1) {
+            stage(rb + GM_KC, buf ^ 1);
+            cp_async_wait<1>();
+        } else {
+            cp_async_wait<0>();
         }
         __syncthreads();
-#pragma unroll 8
-        for (int rr = 0; rr < GR_ROWS; ++rr) {
-            const double a0 = A[rr][ty], a1 = A[rr][ty + 16];
-            const double b0 = B[rr][tx], b1 = B[rr][tx + 16];
-            acc[0][0] = fma(a0, b0, acc[0][0]);
-            acc[0][1] = fma(a0, b1, acc[0][1]);
-            acc[1][0] = fma(a1, b0, acc[1][0]);
-            acc[1][1] = fma(a1, b1, acc[1][1]);
+        const double* As = gm_smem + buf * 2 * GM_STAGE;
+        const double* Bt = diag ? As : As + GM_STAGE;
+#pragma unroll
+        for (int kk = 0; kk < GM_KC / 4; ++kk) {
+            double a[4], b[4];
+#pragma unroll
+            for (int m = 0; m < 4; ++m) a[m] = As[kk * 4 * GM_LD + frag + wi * 32 + m * 8] - sha[m];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) b[q] = Bt[kk * 4 * GM_LD + frag + wj * 32 + q * 8] - shb[q];
+#pragma unroll
+            for (int m = 0; m < 4; ++m)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) dmma_m8n8k4(acc[m][q][0], acc[m][q][1], a[m], b[q]);
         }
         __syncthreads();
+        buf ^= 1;
     }
 #pragma unroll
-    for (int a = 0; a < 2; ++a)
+    for (int m = 0; m < 4; ++m)
 #pragma unroll
-        for (int b = 0; b < 2; ++b) {
-            const int i = ti * 32 + ty + 16 * a, j = tj * 32 + tx + 16 * b;
-            if (i < D && j < D) atomicAdd(&G[(int64_t)i * D + j], acc[a][b]);
-        }
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int i = ti * GM_TILE + wi * 32 + m * 8 + (lane >> 2);
+                const int j = tj * GM_TILE + wj * 32 + q * 8 + (lane & 3) * 2 + h;
+                if (i < D && j < D && i <= j) atomicAdd(&G[(int64_t)i * D + j], acc[m][q][h]);
+            }
 }
 
 }  // namespace tmog
@@ -245,15 +311,17 @@ extern "C" int tmog_dense_gram_dev(const double* x, int64_t ld, int64_t n, int d
     TMOG_REQUIRE(d + 1 <= 65535, "Argument with more than 65535 cols: %d", d + 1);   // Spark RowMatrix limit
     if (n == 0) return TMOG_OK;
     TMOG_REQUIRE((x != nullptr || d == 0) && label != nullptr, "NULL input");
-    const int tiles = (d + 1 + 31) / 32;
-    const int64_t want_ctas = (int64_t)sm_count() * 8;
+    const int tiles = (d + 1 + GM_TILE - 1) / GM_TILE;
+    const int64_t want_ctas = (int64_t)sm_count() * 6;
     int64_t zc = std::max<int64_t>(1, want_ctas / std::max(1, tiles * (tiles + 1) / 2));
-    int64_t rows_per = std::max<int64_t>(GR_ROWS, (n + zc - 1) / zc);
-    rows_per = (rows_per + GR_ROWS - 1) / GR_ROWS * GR_ROWS;
+    int64_t rows_per = std::max<int64_t>(GM_KC, (n + zc - 1) / zc);
+    rows_per = (rows_per + GM_KC - 1) / GM_KC * GM_KC;
     zc = (n + rows_per - 1) / rows_per;
     TMOG_REQUIRE(zc <= 65535 && tiles <= 65535, "grid too large");
-    dense_gram_kernel<<<dim3(tiles, tiles, (unsigned)zc), 256, 0, (cudaStream_t)stream>>>(x, ld, n, d, label, shifts,
-                                                                                          rows_per, gram);
+    const size_t smem = sizeof(double) * 4 * GM_STAGE;
+    TMOG_CUDA(cudaFuncSetAttribute(dense_gram_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dense_gram_dmma_kernel<<<dim3(tiles, tiles, (unsigned)zc), 128, smem, (cudaStream_t)stream>>>(x, ld, n, d, label,
+                                                                                                 shifts, rows_per, gram);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }
