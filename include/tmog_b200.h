@@ -309,6 +309,28 @@ int tmog_text_hash_transform_dev(const int64_t* col_desc, int ncols, int64_t n, 
                                  uint64_t* cursor, int64_t capacity, int32_t* flags, void* scratch,
                                  size_t scratch_bytes, void* stream);
 
+/* Fit and transform of the hashed text columns in ONE pass over the text (what an OpWorkflow does on its training
+ * data: SmartTextVectorizer's model transforms the rows it was just fitted on, FitStagesUtil.scala:261-269): the
+ * statistics of tmog_text_hash_stats_dev over all vector indices and the sparse rows of
+ * tmog_text_hash_transform_dev (normally with newpos = identity, since SanityChecker has not decided yet).  The
+ * rows are then cut down to SanityChecker's kept columns by tmog_sparse_rows_select_dev instead of a second
+ * tokenise + hash pass.  Arguments as in the two functions above. */
+int tmog_text_hash_fit_transform_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
+                                     const int32_t* prefix_len, const int32_t* params, const uint8_t* class_ids,
+                                     uint32_t* bucket_class_sum, uint32_t* bucket_dup, uint64_t* bucket_sq_extra,
+                                     uint32_t* bucket_aux, const double* label, double label_shift,
+                                     double* bucket_wsum, const int32_t* newpos, int64_t* row_start, int32_t* row_nnz,
+                                     int32_t* out_idx, int32_t* out_val, uint64_t* cursor, int64_t capacity,
+                                     int32_t* flags, void* scratch, size_t scratch_bytes, void* stream);
+
+/* Replaces SanityCheckerModel.transformFn -> removeFeatures (C/stages/impl/preparators/DerivedFeatureFilterUtils.scala:
+ * 291-305) on sparse rows in 4-array CSR form: row r keeps the entries whose newpos [index] >= 0, as (newpos, value),
+ * in order.  Call once with out_start = NULL to get out_nnz [n], prefix-sum it into out_start [n], call again to write
+ * out_idx / out_val. */
+int tmog_sparse_rows_select_dev(const int64_t* row_start, const int32_t* row_nnz, const int32_t* idx,
+                                const int32_t* val, int64_t n, const int32_t* newpos, const int64_t* out_start,
+                                int32_t* out_nnz, int32_t* out_idx, int32_t* out_val, void* stream);
+
 /* ------------------------------------------------------------------------------------------------------------------
  * Label classes
  * ------------------------------------------------------------------------------------------------------------------

@@ -67,6 +67,9 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_text_hash_scratch_bytes": [_i64, C.POINTER(_sz)],
     "tmog_text_hash_stats_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _dbl, _p, _p, _p, _sz, _p],
     "tmog_text_hash_transform_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _p, _p, _sz, _p],
+    "tmog_text_hash_fit_transform_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _dbl, _p, _p, _p, _p, _p, _p,
+                                         _p, _i64, _p, _p, _sz, _p],
+    "tmog_sparse_rows_select_dev": [_p, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p],
     "tmog_label_classes_scratch_bytes": [C.POINTER(_sz)],
     "tmog_label_classes_dev": [_p, _i64, _int, _p, _p, _p, _p, _p, _sz, _p],
     "tmog_label_class_ids_dev": [_p, _i64, _p, _p, _int, _p, _p, _p],

@@ -970,6 +970,10 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 Slot* t2 = reinterpret_cast<Slot*>(wbase + L::BUF);
                 constexpr int T2 = L::T2;
                 int kept = 0, np_min = 0x7fffffff, np_max = -1;
+                // fit + transform in one pass: with bucket_class_sum given, the statistics of ALL buckets (kept or
+                // not) are taken here as well
+                const int cls_s = (bucket_class_sum && p.nclasses > 1 && class_ids) ? class_ids[row] : 0;
+                const double e_s = (bucket_class_sum && label) ? label[row] - label_shift : 0.0;
                 for (int i0 = 0; i0 < tsize; i0 += 32) {
                     const Slot sv = table[i0 + lane];
                     int np = -1;
@@ -978,6 +982,11 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                         const unsigned v = (unsigned)(sv >> cb);
                         np = newpos[v];
                         val = (p.binary_freq && v < (unsigned)p.hash_width) ? 1u : (unsigned)(sv & cmask);
+                        if (bucket_class_sum) {
+                            atomicAdd(&bucket_class_sum[(int64_t)v * p.nclasses + cls_s], val);
+                            if (label) atomicAdd(&bucket_wsum[v], (double)val * e_s);
+                            if (val > 1u) th_rare_update(make_uint2(v, val), bucket_dup, bucket_sq_extra, bucket_aux);
+                        }
                     }
                     const unsigned kb = __ballot_sync(FULL, np >= 0);
                     table[i0 + lane] = EMPTY;
@@ -1080,6 +1089,38 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
             }
             __syncwarp();
         }
+    }
+}
+
+
+// Column selection on sparse rows (SanityCheckerModel's removeFeatures on the rows the fit pass already wrote): a warp
+// per row keeps the entries whose new position is >= 0, in order.  WRITE = false only counts them.
+template <bool WRITE>
+__global__ void __launch_bounds__(256)
+sparse_rows_select_kernel(const int64_t* __restrict__ row_start, const int32_t* __restrict__ row_nnz,
+                          const int32_t* __restrict__ idx, const int32_t* __restrict__ val, int64_t n,
+                          const int32_t* __restrict__ newpos, const int64_t* __restrict__ out_start,
+                          int32_t* __restrict__ out_nnz, int32_t* __restrict__ out_idx, int32_t* __restrict__ out_val) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n; r += warps) {
+        const int64_t a = row_start[r];
+        const int m = row_nnz[r];
+        const int64_t o = WRITE ? out_start[r] : 0;
+        int kept = 0;
+        for (int i0 = 0; i0 < m; i0 += 32) {
+            const int i = i0 + lane;
+            const int np = i < m ? newpos[idx[a + i]] : -1;
+            const unsigned k = __ballot_sync(FULL, np >= 0);
+            if (WRITE && np >= 0) {
+                const int64_t at = o + kept + __popc(k & lt);
+                out_idx[at] = np;
+                out_val[at] = val[a + i];
+            }
+            kept += __popc(k);
+        }
+        if (!WRITE && lane == 0) out_nnz[r] = kept;
     }
 }
 
@@ -1371,4 +1412,59 @@ extern "C" int tmog_text_hash_transform_dev(const int64_t* col_desc, int ncols, 
     a.flags = flags;
     a.stream = (cudaStream_t)stream;
     return th_run<true>(a);
+}
+
+extern "C" int tmog_text_hash_fit_transform_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
+                                                const int32_t* prefix_len, const int32_t* params,
+                                                const uint8_t* class_ids, uint32_t* bucket_class_sum,
+                                                uint32_t* bucket_dup, uint64_t* bucket_sq_extra, uint32_t* bucket_aux,
+                                                const double* label, double label_shift, double* bucket_wsum,
+                                                const int32_t* newpos, int64_t* row_start, int32_t* row_nnz,
+                                                int32_t* out_idx, int32_t* out_val, uint64_t* cursor, int64_t capacity,
+                                                int32_t* flags, void* scratch, size_t scratch_bytes, void* stream) {
+    ThArgs a = {};
+    if (int rc = text_hash_common(col_desc, ncols, n, prefix, prefix_len, params, scratch, scratch_bytes, &a)) return rc;
+    TMOG_REQUIRE(bucket_class_sum && bucket_dup && bucket_sq_extra && bucket_aux, "NULL statistics output");
+    TMOG_REQUIRE(a.p.nclasses == 1 || class_ids != nullptr, "class_ids is NULL");
+    TMOG_REQUIRE((label == nullptr) == (bucket_wsum == nullptr), "label and bucket_wsum go together");
+    TMOG_REQUIRE(newpos && row_start && row_nnz && cursor && flags, "NULL argument");
+    TMOG_REQUIRE(capacity >= 0 && (capacity == 0 || (out_idx && out_val)), "NULL output");
+    if (n == 0 || ncols == 0) return TMOG_OK;
+    a.class_ids = class_ids;
+    a.class_sum = bucket_class_sum;
+    a.dup = bucket_dup;
+    a.sq_extra = reinterpret_cast<unsigned long long*>(bucket_sq_extra);
+    a.aux = bucket_aux;
+    a.label = label;
+    a.label_shift = label_shift;
+    a.wsum = bucket_wsum;
+    a.newpos = newpos;
+    a.row_start = row_start;
+    a.row_nnz = row_nnz;
+    a.out_idx = out_idx;
+    a.out_val = out_val;
+    a.cursor = reinterpret_cast<unsigned long long*>(cursor);
+    a.capacity = capacity;
+    a.flags = flags;
+    a.stream = (cudaStream_t)stream;
+    return th_run<true>(a);
+}
+
+extern "C" int tmog_sparse_rows_select_dev(const int64_t* row_start, const int32_t* row_nnz, const int32_t* idx,
+                                           const int32_t* val, int64_t n, const int32_t* newpos,
+                                           const int64_t* out_start, int32_t* out_nnz, int32_t* out_idx,
+                                           int32_t* out_val, void* stream) {
+    TMOG_REQUIRE(n >= 0 && (n == 0 || (row_start && row_nnz && newpos)), "NULL argument");
+    TMOG_REQUIRE(out_start != nullptr ? (out_idx && out_val) : out_nnz != nullptr,
+                 "pass out_nnz to size the rows, or out_start with out_idx / out_val to write them");
+    if (n == 0) return TMOG_OK;
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 7) / 8, (int64_t)sm_count() * 16));
+    if (out_start == nullptr)
+        sparse_rows_select_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(row_start, row_nnz, idx, val, n, newpos,
+                                                                                 nullptr, out_nnz, nullptr, nullptr);
+    else
+        sparse_rows_select_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(row_start, row_nnz, idx, val, n, newpos,
+                                                                                out_start, out_nnz, out_idx, out_val);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
 }

@@ -541,12 +541,35 @@ class SmartTextVectorizerModel(OpModel):
             flags = torch.zeros(4, dtype=torch.int32, device="cuda")
             desc = _col_desc(sub)
             wsum = torch.zeros(w, dtype=torch.float64, device="cuda") if cont is not None else None
-            L.call("tmog_text_hash_stats_dev", desc.data_ptr(), len(lay.hash_idx), n, d_prefix.data_ptr(),
-                   d_plen.data_ptr(), params.ctypes.data, ids_ptr, class_sum.data_ptr(), dup.data_ptr(),
-                   extra.data_ptr(), aux.data_ptr(), cont[2].data_ptr() if cont is not None else None,
-                   cont[1] if cont is not None else 0.0, wsum.data_ptr() if cont is not None else None,
-                   flags.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
+            # One pass over the text gives the statistics AND the sparse rows of this batch (the workflow transforms
+            # its training rows right after the fit): the output is sized from a sample of the first rows; if the
+            # estimate turns out too small the rows are dropped and the transform tokenises again.
+            k = len(lay.hash_idx)
+            ident = torch.arange(w, dtype=torch.int32, device="cuda")
+            row_start = torch.empty(max(n, 1), dtype=torch.int64, device="cuda")
+            row_nnz = torch.empty(max(n, 1), dtype=torch.int32, device="cuda")
+            cursor = torch.zeros(1, dtype=torch.int64, device="cuda")
+            m = min(n, 16384)
+            params1 = params.copy()
+            params1[7] = 1
+            L.call("tmog_text_hash_transform_dev", desc.data_ptr(), k, m, d_prefix.data_ptr(), d_plen.data_ptr(),
+                   params1.ctypes.data, ident.data_ptr(), row_start.data_ptr(), row_nnz.data_ptr(), None, None,
+                   cursor.data_ptr(), 0, flags.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
+            capacity = int(int(cursor.item()) / max(m, 1) * n * 1.1) + 65536
+            cursor.zero_()
+            flags.zero_()
+            idx = torch.empty(capacity, dtype=torch.int32, device="cuda")
+            val = torch.empty(capacity, dtype=torch.int32, device="cuda")
+            L.call("tmog_text_hash_fit_transform_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(), d_plen.data_ptr(),
+                   params.ctypes.data, ids_ptr, class_sum.data_ptr(), dup.data_ptr(), extra.data_ptr(), aux.data_ptr(),
+                   cont[2].data_ptr() if cont is not None else None, cont[1] if cont is not None else 0.0,
+                   wsum.data_ptr() if cont is not None else None, ident.data_ptr(), row_start.data_ptr(),
+                   row_nnz.data_ptr(), idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), capacity, flags.data_ptr(),
+                   scratch.data_ptr(), scratch.numel(), R.stream())
+            too_small = int(flags[3].item()) != 0
+            flags[3] = 0
             _check_hash_flags(flags)
+            self._fit_rows = None if too_small else SparseRowsPart(row_start[:n], row_nnz[:n], idx, val, w)
             cs = (class_sum.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(w, ncls).astype(np.float64)
             # rows holding an index = sum of its term frequencies - (tf - 1) of the rows with tf > 1
             nz = cs.sum(axis=1) - (dup.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).astype(np.float64)
@@ -617,10 +640,27 @@ class SmartTextVectorizerModel(OpModel):
         else:
             newpos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
             out_width = len(keep)
+        d_newpos = torch.from_numpy(newpos).cuda()
+        rows = getattr(self, "_fit_rows", None)
+        if same_batch and rows is not None:
+            # the fit pass wrote the rows of this batch: keep the wanted columns of them
+            if keep is None or (len(keep) == width and bool((np.asarray(keep) == np.arange(width)).all())):
+                return SparseRowsPart(rows.row_start, rows.row_nnz, rows.indices, rows.values, width)
+            out_nnz = torch.empty(max(n, 1), dtype=torch.int32, device="cuda")
+            args = (rows.row_start.data_ptr(), rows.row_nnz.data_ptr(), rows.indices.data_ptr(),
+                    rows.values.data_ptr(), n, d_newpos.data_ptr())
+            L.call("tmog_sparse_rows_select_dev", *args, None, out_nnz.data_ptr(), None, None, R.stream())
+            incl = torch.cumsum(out_nnz.to(torch.int64), 0)
+            out_start = (incl - out_nnz).contiguous()
+            total = int(incl[n - 1].item()) if n else 0
+            oi = torch.empty(max(total, 1), dtype=torch.int32, device="cuda")
+            ov = torch.empty(max(total, 1), dtype=torch.int32, device="cuda")
+            L.call("tmog_sparse_rows_select_dev", *args, out_start.data_ptr(), out_nnz.data_ptr(), oi.data_ptr(),
+                   ov.data_ptr(), R.stream())
+            return SparseRowsPart(out_start[:n], out_nnz[:n], oi, ov, out_width)
         sub, d_prefix, d_plen, params = self._hash_args(dev)
         params[7] = 1
         desc = _col_desc(sub)
-        d_newpos = torch.from_numpy(newpos).cuda()
         row_start = torch.empty(n, dtype=torch.int64, device="cuda")
         row_nnz = torch.empty(n, dtype=torch.int32, device="cuda")
         flags = torch.zeros(4, dtype=torch.int32, device="cuda")
