@@ -279,6 +279,30 @@ class TextBlock:
         return [raw[int(off[r]) - base:int(off[r + 1]) - base].decode("utf-8") if ok[r] else None
                 for r in range(rows)]
 
+    def prefix_cells_many(self, cols: Sequence[int], rows: int) -> Dict[int, List[Optional[str]]]:
+        """prefix_cells of several columns with three host round trips in all."""
+        rows = min(rows, self.n)
+        cols = list(cols)
+        if not cols or rows == 0:
+            return {c: [] for c in cols}
+        offs = torch.stack([self.offsets[c][:rows + 1] for c in cols]).cpu().numpy()
+        raw = torch.cat([self.data[c][int(o[0]):int(o[-1])] for c, o in zip(cols, offs)]).cpu().numpy().tobytes()
+        words = (rows + 63) // 64
+        with_valid = [c for c in cols if self.valid[c] is not None]
+        bits = {}
+        if with_valid:
+            vw = torch.stack([self.valid[c][:words] for c in with_valid]).cpu().numpy()
+            for c, w in zip(with_valid, vw):
+                bits[c] = np.unpackbits(w.view(np.uint8), bitorder="little")[:rows].astype(bool)
+        out, at = {}, 0
+        for c, o in zip(cols, offs):
+            ok = bits.get(c)
+            base = int(o[0]) - at
+            out[c] = [raw[int(o[r]) - base:int(o[r + 1]) - base].decode("utf-8") if (ok is None or ok[r]) else None
+                      for r in range(rows)]
+            at += int(o[-1]) - int(o[0])
+        return out
+
     def cells(self, col: int, rows: Sequence[int]) -> List[Optional[str]]:
         """Arbitrary cells of a column: one round trip for their offsets, one per cell for the bytes."""
         if not len(rows):

@@ -210,6 +210,20 @@ class SmartTextVectorizer(OpEstimator):
         values, totals = self._text_stats(dev, n)
         values = self._merge_text_stats(values, dev, n)
         methods, tops = [], []
+        # columns past the cardinality cap need the first rows on the host (the reference's fold freezes there): fetch
+        # them for all such columns at once
+        over = [c for c in range(ncols) if values[c] is None]
+        self._prefix = {}
+        if over:                                  # one fetch and one cleaning call for all of them
+            rows0 = min(4 * (self.maxCardinality + 8), n)
+            fetched = dev.prefix_cells_many(over, rows0)
+            flat = [v for c in over for v in fetched[c] if v is not None]
+            ids, distinct = clean_and_group(flat, self.cleanText)
+            at = 0
+            for c in over:
+                k = sum(v is not None for v in fetched[c])
+                self._prefix[c] = (rows0, [distinct[i] for i in ids[at:at + k]])
+                at += k
         for c in range(ncols):
             m, top = self._decide(values[c], totals[c], dev, c, n)
             methods.append(m)
@@ -300,16 +314,22 @@ class SmartTextVectorizer(OpEstimator):
         its map holds more than maxCardinality keys (SmartTextVectorizer.scala:231-235), so only a prefix of the rows
         counts.  Emulated in row order on a prefix fetched to the host (`seed`: the map of the ranks before)."""
         rows = 4 * (self.maxCardinality + 8)
+        first = True
         while True:
             rows = min(rows, n)
-            raws = dev.prefix_cells(c, rows)
-            present = [v for v in raws if v is not None]
-            ids, distinct = clean_and_group(present, self.cleanText)
+            pre = getattr(self, "_prefix", {}).get(c) if first else None
+            first = False
+            if pre is not None and pre[0] == rows:
+                cleaned = pre[1]                     # the cleaned values of the first rows, fetched with the others
+            else:
+                present = [v for v in dev.prefix_cells(c, rows) if v is not None]
+                ids, distinct = clean_and_group(present, self.cleanText)
+                cleaned = [distinct[i] for i in ids]
             vc: Dict[str, int] = dict(seed or {})
-            for i in ids:
+            for v in cleaned:
                 if len(vc) > self.maxCardinality:
                     return vc
-                vc[distinct[i]] = vc.get(distinct[i], 0) + 1
+                vc[v] = vc.get(v, 0) + 1
             if len(vc) > self.maxCardinality or rows >= n:
                 return vc
             rows *= 4
