@@ -149,7 +149,7 @@ def text_bytes_per_row(block: TextBlock) -> float:
 
 
 WORKLOADS = ("c2", "c3", "c4", "c5")
-DEFAULT_ROWS = {"c2": 10_000_000, "c3": 50_000_000, "c4": 2_000_000, "c5": 1_000_000}
+DEFAULT_ROWS = {"c2": 10_000_000, "c3": 50_000_000, "c4": 5_000_000, "c5": 4_000_000}
 
 
 def make_workload(name: str, rows: int, seed: int):
