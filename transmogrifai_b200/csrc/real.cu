@@ -421,9 +421,24 @@ vec_transform_pack_kernel(const T* __restrict__ values, int64_t ld, const uint64
             if (TRACK && (mx & 2u)) trow[pos + (int)(mx & 1u)] = v ? 0.0 : 1.0;
         }
     }
+    // the image is read by the bulk-copy engine below: order the generic-proxy writes before its async-proxy reads
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncthreads();
     double* dst = out + r0 * nkeep;
     const int total = rows_here * nkeep;
+    if (stride == nkeep && ((total * (int)sizeof(double)) & 15) == 0) {
+        // unpadded image (odd nkeep is conflict free as it is): one TMA bulk store of the whole stretch, issued by one
+        // thread -- no per-element instructions, the SM's issue slots go to the other CTAs' loads
+        if (tid == 0) {
+            const unsigned src = (unsigned)__cvta_generic_to_shared(tp_tile);
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src),
+                         "r"(total * (int)sizeof(double))
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        }
+        return;
+    }
     int rl = tid / nkeep, cl = tid - rl * nkeep;           // position of this thread's element; advanced by 512
     const int dr = TP_THREADS / nkeep, dc = TP_THREADS - dr * nkeep;
     for (int q = tid; q < total; q += TP_THREADS) {
