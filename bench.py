@@ -421,6 +421,7 @@ def main():
     # end to end through the stage API with pinned host buffers: H2D of every raw block, D2H of the kept columns
     e2e = None
     if not args.no_e2e:
+        from transmogrifai_b200.columnar import to_host
         hbatch = benchdata.host_copy(batch)
         h2d = benchdata.input_bytes(hbatch)
         del batch
@@ -428,13 +429,13 @@ def main():
 
         def e2e_step():
             vec, _f, parts = run_step(hbatch, checked)
-            host = []
+            dev = []
             for p in parts:                                  # results that are still on the device go back to the host
                 for name in ("data", "indices", "values", "row_start", "row_nnz"):
                     t = getattr(p, name, None)
                     if t is not None and hasattr(t, "is_cuda"):
-                        host.append(t.cpu() if t.is_cuda else t)
-            return parts, host
+                        dev.append(t)
+            return parts, to_host(dev, piece_bytes=1 << 30)  # pinned destinations, one wait
 
         for _ in range(2):
             parts, host = e2e_step()
@@ -446,7 +447,9 @@ def main():
         barrier()
         dt = max_over_ranks((time.perf_counter() - t0) / k_e2e)
         e2e = {"value": rows * world / dt, "unit": "rows/s", "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(sum(t.numel() * t.element_size() for t in host)), "ms_per_step": dt * 1e3,
+               "d2h_bytes_per_step": int(sum(t.numel() * t.element_size() for h in host
+                                             for t in (h if isinstance(h, list) else [h]))),
+               "ms_per_step": dt * 1e3,
                "steps": k_e2e,
                "api": "fit_and_transform(pinned host ColumnarBatch, label.sanityCheck(transmogrify(features)))"}
         del hbatch, parts, host

@@ -43,6 +43,36 @@ def _pin(t: torch.Tensor) -> torch.Tensor:
         return t
 
 
+def to_host(tensors, piece_bytes: Optional[int] = None) -> list:
+    """Device tensors -> pinned host tensors: every copy is queued asynchronously on the current stream and the
+    stream is waited for once (what a reader of the transformed partition does with the kept columns).  Pinned
+    buffers come from torch's caching host allocator, so repeated reads of same-sized results reuse them; a
+    pageable destination would halve the PCIe rate and fault in fresh pages on every call.  With `piece_bytes` a
+    tensor larger than that comes back as a list of flat pinned pieces in order (the allocator rounds a request up
+    to a power of two, which a 13 GB array cannot afford)."""
+    out, pending = [], False
+
+    def pull(t):
+        h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        h.copy_(t, non_blocking=True)
+        return h
+
+    for t in tensors:
+        if t is None or not t.is_cuda:
+            out.append(t)
+            continue
+        pending = True
+        nbytes = t.numel() * t.element_size()
+        if piece_bytes is None or nbytes <= piece_bytes or not t.is_contiguous():
+            out.append(pull(t))
+        else:
+            flat, step = t.reshape(-1), max(piece_bytes // t.element_size(), 1)
+            out.append([pull(flat[i:i + step]) for i in range(0, flat.numel(), step)])
+    if pending:
+        torch.cuda.current_stream().synchronize()
+    return out
+
+
 @dataclass
 class NumericBlock:
     names: List[str]
