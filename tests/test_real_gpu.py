@@ -103,6 +103,46 @@ def test_real_fit_transform_matches_oracle(n, ncols):
         np.testing.assert_allclose(res["cov"], cov, rtol=1e-9, atol=1e-9 * max(scale.max(), 1e-300))
 
 
+@pytest.mark.parametrize("n,ncols,nulls", [(148 * 4096 * 2 + 4096 * 5 + 2 * 1024 + 77, 11, True),
+                                           (4096 * 300 + 1024, 3, True), (1024 * 7, 17, False), (1023, 9, True)])
+def test_real_fit_partials_over_many_super_tiles(n, ncols, nulls):
+    """Raw partials of the fit scan when every CTA walks several super-tiles (the label ring wraps, both column
+    buffers of a warp are reused) plus a ragged tail, against numpy on the same shifted sums."""
+    from transmogrifai_b200 import _lib as L
+    rng = np.random.default_rng(n + ncols)
+    x = rng.normal(3.0, 2.0, size=(ncols, n))
+    valid = rng.random((ncols, n)) > 0.2 if nulls else None
+    y = (rng.random(n) < 0.3).astype(np.float64)
+    res = run_fit(x, valid, y)
+    xd, vd, yd = res["xd"], res["keep"][0], res["keep"][1]
+    shifts = torch.zeros(ncols + 1, dtype=torch.float64, device="cuda")
+    partials = torch.zeros((ncols + 1) * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
+    nb = C.c_size_t()
+    L.call("tmog_real_fit_scratch_bytes", ncols, C.byref(nb))
+    scratch = torch.empty(nb.value, dtype=torch.uint8, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    L.call("tmog_real_pilot_shift_dev", xd.data_ptr(), res["ld"], res["vptr"], res["ldv"], yd.data_ptr(), n, ncols,
+           shifts.data_ptr(), st)
+    L.call("tmog_real_fit_partials_dev", xd.data_ptr(), res["ld"], res["vptr"], res["ldv"], yd.data_ptr(), n, ncols,
+           shifts.data_ptr(), scratch.data_ptr(), nb.value, partials.data_ptr(), st)
+    torch.cuda.synchronize()
+    got = partials.cpu().numpy().reshape(ncols + 1, L.REAL_NSTAT)
+    s = shifts.cpu().numpy()
+    e = y - s[ncols]
+    cols = np.concatenate([x, y[None, :]], axis=0)
+    ok = np.ones((ncols + 1, n), dtype=bool)
+    if valid is not None:
+        ok[:ncols] = valid
+    d = np.where(ok, cols - s[:, None], 0.0)
+    exp = np.stack([ok.sum(axis=1), d.sum(axis=1), (d * d).sum(axis=1), (d * e).sum(axis=1),
+                    np.where(ok, e, 0.0).sum(axis=1), np.where(ok, cols, np.inf).min(axis=1),
+                    np.where(ok, cols, -np.inf).max(axis=1), np.full(ncols + 1, n)], axis=1)
+    assert np.array_equal(got[:, [0, 5, 6, 7]], exp[:, [0, 5, 6, 7]])      # counts, min, max: exact
+    scale = np.sqrt(n) * 10.0
+    np.testing.assert_allclose(got[:, 1:5], exp[:, 1:5], rtol=1e-11, atol=1e-12 * scale * scale)
+    del vd
+
+
 def test_real_reference_golden_vectors():
     # core/src/test/scala/com/salesforce/op/stages/impl/feature/RealVectorizerTest.scala:118-145,182-214
     x = np.array([[4.0, 0.0, 2.0], [2.0, 2.0, 0.0], [0.0, 0.0, 0.0]])

@@ -146,6 +146,266 @@ real_fit_kernel(const double* __restrict__ values, int64_t ld, const uint64_t* _
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// real_fit_tma_kernel: the same scan with the columns brought in by the bulk-copy engine (cp.async.bulk + mbarrier).
+//
+// A CTA (one per SM) walks super-tiles of FT_SUPER rows.  Work unit = (super-tile, column), owned by consumer warp
+// c % FT_WARPS, cut into sub-tiles of FT_SUB = 1024 rows.  Every consumer warp has its own two 8 KB buffers: while it
+// works on one sub-tile out of shared memory, the bulk copy of its next one (next sub-tile, next column or next
+// super-tile) is in flight, so each SM always has >= 64 KB of loads outstanding without holding them in registers.
+// Inside a sub-tile lane L owns rows 32L .. 32L+31: their validity is the lane's own 32-bit bitmap word (one coalesced
+// load, no shuffles; rotated once so that every bit test is an immediate mask), and the lane reads its rows as
+// 128-bit pairs in the rotated order p = (k + L) mod 16, which is bank-conflict free.  The label of a super-tile is
+// staged once (a ninth warp issues the copy into a two-deep ring; consumers release a slot through an mbarrier that
+// counts units).  A column's accumulators stay in registers over the unit's sub-tiles and are reduced across lanes
+// once per unit; per-CTA accumulators, the scratch layout and the fixed-order reduce are those of real_fit_kernel, so
+// the result is deterministic for a given grid.  Rows past the last full sub-tile (< 1024) are read directly by the
+// last CTA.
+constexpr int FT_SUB = 1024;
+constexpr int FT_SUBS = 4;
+constexpr int FT_SUPER = FT_SUB * FT_SUBS;
+constexpr int FT_WARPS = 8;
+constexpr int FT_THREADS = (FT_WARPS + 1) * 32;
+constexpr int FT_STAGES = 2;
+constexpr int FT_NBAR = FT_WARPS * FT_STAGES + 4;
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned ok = 0;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+// global -> shared bulk copy (16-byte aligned, size a multiple of 16) that completes on an mbarrier of this CTA
+__device__ __forceinline__ void bulk_load(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
+__device__ __forceinline__ void acc_add_lean(Acc& a, bool v, double x, double s, double e) {
+    const double d = v ? x - s : 0.0;
+    a.sd += d;
+    a.sdd = fma(d, d, a.sdd);
+    a.sde = fma(d, e, a.sde);  // d == 0 on a null row
+    a.se += v ? e : 0.0;
+    a.mn = (v & (x < a.mn)) ? x : a.mn;  // branch-free: one predicated compare + select
+    a.mx = (v & (x > a.mx)) ? x : a.mx;
+}
+
+struct FitChunkIt {  // the sub-tiles of one consumer warp, in the order it works through them
+    int64_t st;      // super-tile
+    int i;           // ordinal of the super-tile within this CTA
+    int c;           // column (ncols = the label)
+    int j;           // sub-tile within the super-tile
+    int nfull;       // sub-tiles of this super-tile
+};
+
+__global__ void __launch_bounds__(FT_THREADS, 1)
+real_fit_tma_kernel(const double* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid, int64_t ldv,
+                    const double* __restrict__ label, int64_t n, int ncols, const double* __restrict__ shifts,
+                    double* __restrict__ scratch) {
+    extern __shared__ __align__(128) unsigned char ft_smem[];
+    double* colbuf = reinterpret_cast<double*>(ft_smem);        // [FT_WARPS][FT_STAGES][FT_SUB]
+    double* ybuf = colbuf + FT_WARPS * FT_STAGES * FT_SUB;      // [2][FT_SUPER]
+    double* acc = ybuf + 2 * FT_SUPER;                          // [(ncols+1) * NS]
+    double* comp = acc + (ncols + 1) * NS;                      // [(ncols+1) * 4]
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(comp + (ncols + 1) * 4);
+    const unsigned bar0 = smem_u32(bars);
+    // bars: [w * FT_STAGES + stage] column buffer full | [16 + slot] label full | [18 + slot] label empty
+    const unsigned bar_yfull = bar0 + 8u * (FT_WARPS * FT_STAGES), bar_yempty = bar_yfull + 16u;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nacc = (ncols + 1) * NS;
+    for (int i = tid; i < nacc; i += FT_THREADS) {
+        const int st = i % NS;
+        acc[i] = st == 5 ? INFINITY : (st == 6 ? -INFINITY : 0.0);
+    }
+    for (int i = tid; i < (ncols + 1) * 4; i += FT_THREADS) comp[i] = 0.0;
+    if (tid == 0) {
+        for (int b = 0; b < FT_WARPS * FT_STAGES + 2; ++b) mbar_init(bar0 + 8u * b, 1);
+        mbar_init(bar_yempty, (unsigned)(ncols + 1));
+        mbar_init(bar_yempty + 8u, (unsigned)(ncols + 1));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int64_t rows_full = (n / FT_SUB) * FT_SUB;
+    const int64_t nsuper = (rows_full + FT_SUPER - 1) / FT_SUPER;
+    const double sy = shifts[ncols];
+
+    if (warp == FT_WARPS) {
+        // label producer: one copy per super-tile into a two-deep ring
+        if (lane == 0) {
+            int i = 0;
+            for (int64_t st = blockIdx.x; st < nsuper; st += gridDim.x, ++i) {
+                const unsigned slot = i & 1;
+                if (i >= 2) mbar_wait(bar_yempty + 8u * slot, ((i >> 1) & 1) ^ 1);
+                const int64_t r0 = st * FT_SUPER;
+                const unsigned bytes = (unsigned)min((int64_t)FT_SUPER, rows_full - r0) * 8u;
+                mbar_expect_tx(bar_yfull + 8u * slot, bytes);
+                bulk_load(smem_u32(ybuf + slot * FT_SUPER), label + r0, bytes, bar_yfull + 8u * slot);
+            }
+        }
+    } else {
+        const unsigned my_bar = bar0 + 8u * (warp * FT_STAGES);
+        double* my_buf = colbuf + warp * FT_STAGES * FT_SUB;
+        auto nfull_of = [&](int64_t st) {
+            return (int)min((int64_t)FT_SUBS, (rows_full - st * FT_SUPER) / FT_SUB);
+        };
+        auto it_valid = [&](const FitChunkIt& it) { return it.st < nsuper && it.c <= ncols; };
+        auto it_next = [&](FitChunkIt& it) {
+            if (++it.j < it.nfull) return;
+            it.j = 0;
+            it.c += FT_WARPS;
+            if (it.c <= ncols) return;
+            it.c = warp;
+            it.st += gridDim.x;
+            ++it.i;
+            it.nfull = it.st < nsuper ? nfull_of(it.st) : 0;
+        };
+        // issue the bulk copy of chunk `it` into stage q & 1 and fetch the lane's validity word for it
+        auto issue = [&](const FitChunkIt& it, unsigned q) -> unsigned {
+            const bool is_label = it.c == ncols;
+            const int64_t r0 = it.st * FT_SUPER + (int64_t)it.j * FT_SUB;
+            const double* src = (is_label ? label : values + (int64_t)it.c * ld) + r0;
+            if (lane == 0) {
+                const unsigned bar = my_bar + 8u * (q & 1u);
+                mbar_expect_tx(bar, FT_SUB * 8u);
+                bulk_load(smem_u32(my_buf + (q & 1u) * FT_SUB), src, FT_SUB * 8u, bar);
+            }
+            if (is_label || valid == nullptr) return 0xffffffffu;
+            const unsigned* v32 = reinterpret_cast<const unsigned*>(valid + (int64_t)it.c * ldv);
+            return __ldg(v32 + (r0 >> 5) + lane);
+        };
+
+        FitChunkIt cur{(int64_t)blockIdx.x, 0, warp, 0, 0};
+        cur.nfull = cur.st < nsuper ? nfull_of(cur.st) : 0;
+        FitChunkIt nxt = cur;
+        unsigned q = 0, w_cur = 0, w_nxt = 0;
+        if (it_valid(nxt)) {
+            w_cur = issue(nxt, 0);
+            it_next(nxt);
+        }
+        Acc a, b;
+        unsigned cnt = 0;
+        double s = 0.0;
+        while (it_valid(cur)) {
+            if (it_valid(nxt)) {  // stage (q + 1) & 1 was released by the __syncwarp that ended chunk q - 1
+                w_nxt = issue(nxt, q + 1);
+                it_next(nxt);
+            }
+            if (cur.j == 0) {
+                acc_init(a);
+                acc_init(b);
+                cnt = 0;
+                s = shifts[cur.c];
+                mbar_wait(bar_yfull + 8u * (cur.i & 1), (cur.i >> 1) & 1);
+            }
+            mbar_wait(my_bar + 8u * (q & 1u), (q >> 1) & 1u);
+            {
+                const double2* xb = reinterpret_cast<const double2*>(my_buf + (q & 1u) * FT_SUB) + lane * 16;
+                const double2* yb =
+                    reinterpret_cast<const double2*>(ybuf + (cur.i & 1) * FT_SUPER + cur.j * FT_SUB) + lane * 16;
+                cnt += __popc(w_cur);
+                const unsigned wr = __funnelshift_r(w_cur, w_cur, 2 * lane);  // bits 2k, 2k+1 <-> pair (k + lane) % 16
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const int p = (k + lane) & 15;
+                    const double2 x = xb[p];
+                    const double2 y = yb[p];
+                    acc_add_lean(a, (wr >> (2 * k)) & 1u, x.x, s, y.x - sy);
+                    acc_add_lean(b, (wr >> (2 * k + 1)) & 1u, x.y, s, y.y - sy);
+                }
+            }
+            __syncwarp();
+            if (cur.j == cur.nfull - 1) {
+                const double sd = warp_sum(a.sd + b.sd);
+                const double sdd = warp_sum(a.sdd + b.sdd);
+                const double sde = warp_sum(a.sde + b.sde);
+                const double se = warp_sum(a.se + b.se);
+                const double mn = warp_min(fmin(a.mn, b.mn));
+                const double mx = warp_max(fmax(a.mx, b.mx));
+                const unsigned total = __reduce_add_sync(FULL, cnt);
+                if (lane == 0) {
+                    double* qa = acc + cur.c * NS;
+                    double* kc = comp + cur.c * 4;
+                    qa[0] += (double)total;
+                    kahan_add(qa[1], kc[0], sd);
+                    kahan_add(qa[2], kc[1], sdd);
+                    kahan_add(qa[3], kc[2], sde);
+                    kahan_add(qa[4], kc[3], se);
+                    qa[5] = fmin(qa[5], mn);
+                    qa[6] = fmax(qa[6], mx);
+                    mbar_arrive(bar_yempty + 8u * (cur.i & 1));
+                }
+            }
+            it_next(cur);
+            w_cur = w_nxt;
+            ++q;
+        }
+        // rows past the last full sub-tile: read directly, by the last CTA
+        if (blockIdx.x == gridDim.x - 1 && rows_full < n) {
+            for (int c = warp; c <= ncols; c += FT_WARPS) {
+                const bool is_label = (c == ncols);
+                const double* col = is_label ? label : values + (int64_t)c * ld;
+                const uint64_t* vcol = (is_label || valid == nullptr) ? nullptr : valid + (int64_t)c * ldv;
+                const double sc = shifts[c];
+                acc_init(a);
+                unsigned tc = 0;
+                for (int64_t r = rows_full + lane; r < n; r += 32) {
+                    const bool v = vcol ? ((vcol[r >> 6] >> (r & 63)) & 1ull) != 0 : true;
+                    tc += v;
+                    acc_add(a, v, col[r], sc, label[r] - sy);
+                }
+                const double sd = warp_sum(a.sd), sdd = warp_sum(a.sdd), sde = warp_sum(a.sde), se = warp_sum(a.se);
+                const double mn = warp_min(a.mn), mx = warp_max(a.mx);
+                const unsigned total = __reduce_add_sync(FULL, tc);
+                if (lane == 0) {
+                    double* qa = acc + c * NS;
+                    double* kc = comp + c * 4;
+                    qa[0] += (double)total;
+                    kahan_add(qa[1], kc[0], sd);
+                    kahan_add(qa[2], kc[1], sdd);
+                    kahan_add(qa[3], kc[2], sde);
+                    kahan_add(qa[4], kc[3], se);
+                    qa[5] = fmin(qa[5], mn);
+                    qa[6] = fmax(qa[6], mx);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    double* out = scratch + (int64_t)blockIdx.x * nacc;
+    for (int i = tid; i < nacc; i += FT_THREADS) {
+        const int st = i % NS;
+        double v = acc[i];
+        if (st >= 1 && st <= 4) v -= comp[(i / NS) * 4 + (st - 1)];
+        out[i] = v;
+    }
+}
+
+static size_t fit_tma_smem_bytes(int ncols) {
+    return sizeof(double) * ((size_t)FT_WARPS * FT_STAGES * FT_SUB + 2 * FT_SUPER + (size_t)(ncols + 1) * (NS + 4)) +
+           8 * (size_t)FT_NBAR;
+}
+
 // Reduce the per-CTA partials in a fixed order (deterministic for a given grid): one warp per column.
 __global__ void __launch_bounds__(32)
 real_fit_reduce_kernel(const double* __restrict__ scratch, int nblocks, int ncols, int64_t n,
@@ -503,16 +763,29 @@ extern "C" int tmog_real_fit_partials_dev(const double* values, int64_t ld, cons
         set_error("scratch too small: %zu bytes given, %zu needed (tmog_real_fit_scratch_bytes)", scratch_bytes, need);
         return TMOG_ENOMEM;
     }
-    const size_t smem = fit_smem_bytes(ncols);
-    TMOG_REQUIRE(smem <= 200 * 1024, "too many columns for one fit call (%d): split the column block", ncols);
-    if (smem > 48 * 1024) {
-        TMOG_CUDA(cudaFuncSetAttribute(real_fit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    }
     cudaStream_t st = (cudaStream_t)stream;
-    real_fit_kernel<<<grid, FIT_THREADS, smem, st>>>(values, ld, valid, ldv, label, n, ncols, shifts,
-                                                     static_cast<double*>(scratch));
+    int nblocks = grid;
+    const size_t smem_tma = fit_tma_smem_bytes(ncols);
+    if (smem_tma <= 227 * 1024) {
+        // one CTA per SM, columns streamed through shared memory by the bulk-copy engine
+        nblocks = sm_count();
+        TMOG_CUDA(cudaFuncSetAttribute(real_fit_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem_tma));
+        real_fit_tma_kernel<<<nblocks, FT_THREADS, smem_tma, st>>>(values, ld, valid, ldv, label, n, ncols, shifts,
+                                                                   static_cast<double*>(scratch));
+    } else {
+        // very wide blocks: the register-streaming kernel, whose shared memory holds only the accumulators
+        const size_t smem = fit_smem_bytes(ncols);
+        TMOG_REQUIRE(smem <= 200 * 1024, "too many columns for one fit call (%d): split the column block", ncols);
+        if (smem > 48 * 1024) {
+            TMOG_CUDA(cudaFuncSetAttribute(real_fit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        }
+        real_fit_kernel<<<grid, FIT_THREADS, smem, st>>>(values, ld, valid, ldv, label, n, ncols, shifts,
+                                                         static_cast<double*>(scratch));
+    }
     TMOG_LAUNCH_CHECK();
-    real_fit_reduce_kernel<<<ncols + 1, 32, 0, st>>>(static_cast<const double*>(scratch), grid, ncols, n, partials);
+    real_fit_reduce_kernel<<<ncols + 1, 32, 0, st>>>(static_cast<const double*>(scratch), nblocks, ncols, n,
+                                                     partials);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }
