@@ -104,7 +104,8 @@ def test_real_fit_transform_matches_oracle(n, ncols):
 
 
 @pytest.mark.parametrize("n,ncols,nulls", [(148 * 4096 * 2 + 4096 * 5 + 2 * 1024 + 77, 11, True),
-                                           (4096 * 300 + 1024, 3, True), (1024 * 7, 17, False), (1023, 9, True)])
+                                           (4096 * 300 + 1024, 3, True), (1024 * 7, 17, False), (1023, 9, True),
+                                           (5000, 400, True)])   # 400 columns: the register-streaming kernel
 def test_real_fit_partials_over_many_super_tiles(n, ncols, nulls):
     """Raw partials of the fit scan when every CTA walks several super-tiles (the label ring wraps, both column
     buffers of a warp are reused) plus a ragged tail, against numpy on the same shifted sums."""
