@@ -104,6 +104,15 @@ struct StopEntry {
     char w[STOP_MAXLEN];
 };
 __constant__ StopEntry c_stop[STOP_SLOTS];
+// stop-word pre-filter: entry (first letter, second character class) holds a bit per word length, so that the two-slot
+// probe runs only for the few tokens that share first letter, second character and length with a stop word.
+// Second character classes: 0..25 letters, 26 the apostrophe, 27 anything else / past the end of the token.
+constexpr int STOP_PRE = 26 * 28;
+__constant__ unsigned short c_stop_pre[STOP_PRE];
+__host__ __device__ inline int stop_pre_index(unsigned c0, unsigned c1) {   // c0 must be 'a' .. 'z'
+    const unsigned k1 = (c1 - 'a') < 26u ? c1 - 'a' : (c1 == '\'' ? 26u : 27u);
+    return (int)((c0 - 'a') * 28u + k1);
+}
 
 // ------------------------------------------------------------------------------------------------------------------
 // column descriptors
@@ -324,6 +333,9 @@ constexpr int TH_PREFIX = 16;        // bytes reserved for "<nameHash>_"
 constexpr int TH_COLCACHE = 64;      // columns whose murmur3 prefix state is cached in shared memory
 constexpr int TH_GRAB = 4;           // rows taken from the counter at once
 constexpr int TH_MAX_TOKEN = 255;    // StandardAnalyzer.DEFAULT_MAX_TOKEN_LENGTH
+constexpr int TH_STOP_PRE_BYTES = (26 * 28 * 2 + 15) / 16 * 16;
+// shared memory in front of the per-warp regions: stop-word table, cached prefix states, stop-word pre-filter
+constexpr int TH_FIXED_SMEM = 512 * 16 + TH_COLCACHE * 12 + TH_STOP_PRE_BYTES;
 
 struct TextHashParams {
     int num_features;      // hash buckets per space
@@ -504,9 +516,10 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
     extern __shared__ __align__(16) unsigned char th_smem[];
     StopSlot* stop = reinterpret_cast<StopSlot*>(th_smem);                                   // [STOP_SLOTS]
     unsigned* colstate = reinterpret_cast<unsigned*>(th_smem + STOP_SLOTS * sizeof(StopSlot));  // [TH_COLCACHE][3]
+    unsigned short* stop_pre = reinterpret_cast<unsigned short*>(th_smem + TH_FIXED_SMEM - TH_STOP_PRE_BYTES);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     static_assert(L::BYTES % 16 == 0 && (TH_COLCACHE * 12) % 16 == 0, "per-warp regions must stay 16-byte aligned");
-    unsigned char* wbase = th_smem + STOP_SLOTS * sizeof(StopSlot) + TH_COLCACHE * 12 + (size_t)warp * L::BYTES;
+    unsigned char* wbase = th_smem + TH_FIXED_SMEM + (size_t)warp * L::BYTES;
     unsigned char* buf = wbase + L::BUF + 16;                      // text; buf[-16 ..) and (.. TB + 32) are slack
     const unsigned* bufw = reinterpret_cast<const unsigned*>(wbase + L::BUF);
     unsigned* mask = reinterpret_cast<unsigned*>(wbase + L::MASK);
@@ -528,6 +541,7 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
         }
         stop[i] = sl;
     }
+    for (int i = tid; i < STOP_PRE; i += WARPS * 32) stop_pre[i] = c_stop_pre[i];
     for (int j = tid; j < min(ncols, TH_COLCACHE); j += WARPS * 32) {
         Murmur pm;
         pm.init();
@@ -699,26 +713,32 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                         for (int w = 0; w < nwin; ++w) {
                             const unsigned* bp = bufw + 4 + (w << 5) + lane;
                             const unsigned W = bp[0];
-                            const unsigned plast = bp[-1] >> 24, nfirst = bp[1] & 0xffu;
                             const unsigned h7 = W & 0x7f7f7f7fu, ascii = ~W & 0x80808080u;
                             // bit 7 of (h7 + (0x80 - x) * 0x01010101) is set iff the byte is >= x
                             const unsigned fl = (h7 + 0x1f1f1f1fu) & ~(h7 + 0x05050505u) & ascii;     // 'a' .. 'z'
                             const unsigned fd = (h7 + 0x50505050u) & ~(h7 + 0x46464646u) & ascii;     // '0' .. '9'
                             // bit 7 of ((h7 ^ c) + 0x7f) is set iff the byte differs from c
                             const unsigned ne_us = (h7 ^ 0x5f5f5f5fu) + 0x7f7f7f7fu;
-                            const unsigned ne_dot = (h7 ^ 0x2e2e2e2eu) + 0x7f7f7f7fu;
-                            const unsigned ne_apo = (h7 ^ 0x27272727u) + 0x7f7f7f7fu;
-                            const unsigned ne_col = (h7 ^ 0x3a3a3a3au) + 0x7f7f7f7fu;
-                            const unsigned ne_com = (h7 ^ 0x2c2c2c2cu) + 0x7f7f7f7fu;
-                            const unsigned ne_sem = (h7 ^ 0x3b3b3b3bu) + 0x7f7f7f7fu;
-                            const unsigned mid_l = ~(ne_dot & ne_apo & ne_col);              // MidLetter | MidNumLet | '
-                            const unsigned mid_n = ~(ne_dot & ne_apo & ne_com & ne_sem);     // MidNum | MidNumLet | '
-                            const unsigned pl = (plast - 'a') < 26u ? 0x80u : 0u, pd = (plast - '0') < 10u ? 0x80u : 0u;
-                            const unsigned nl = (nfirst - 'a') < 26u ? 0x80000000u : 0u;
-                            const unsigned nd = (nfirst - '0') < 10u ? 0x80000000u : 0u;
-                            const unsigned joined = (mid_l & ((fl << 8) | pl) & ((fl >> 8) | nl)) |
-                                                    (mid_n & ((fd << 8) | pd) & ((fd >> 8) | nd));
-                            unsigned tcf = (fl | fd | ((~ne_us | joined) & ascii)) & 0x80808080u;
+                            unsigned tcf = (fl | fd | (~ne_us & ascii)) & 0x80808080u;
+                            // the Mid* characters . ' : , ; all lie in 0x27 .. 0x3b: windows without a non-digit byte
+                            // of that range (most of them) skip the neighbour tests
+                            const unsigned rng = (h7 + 0x59595959u) & ~(h7 + 0x44444444u) & ~fd & ascii;
+                            if (__any_sync(FULL, rng != 0u)) {
+                                const unsigned plast = bp[-1] >> 24, nfirst = bp[1] & 0xffu;
+                                const unsigned ne_dot = (h7 ^ 0x2e2e2e2eu) + 0x7f7f7f7fu;
+                                const unsigned ne_apo = (h7 ^ 0x27272727u) + 0x7f7f7f7fu;
+                                const unsigned ne_col = (h7 ^ 0x3a3a3a3au) + 0x7f7f7f7fu;
+                                const unsigned ne_com = (h7 ^ 0x2c2c2c2cu) + 0x7f7f7f7fu;
+                                const unsigned ne_sem = (h7 ^ 0x3b3b3b3bu) + 0x7f7f7f7fu;
+                                const unsigned mid_l = ~(ne_dot & ne_apo & ne_col);          // MidLetter | MidNumLet | '
+                                const unsigned mid_n = ~(ne_dot & ne_apo & ne_com & ne_sem); // MidNum | MidNumLet | '
+                                const unsigned pl = (plast - 'a') < 26u ? 0x80u : 0u, pd = (plast - '0') < 10u ? 0x80u : 0u;
+                                const unsigned nl = (nfirst - 'a') < 26u ? 0x80000000u : 0u;
+                                const unsigned nd = (nfirst - '0') < 10u ? 0x80000000u : 0u;
+                                const unsigned joined = (mid_l & ((fl << 8) | pl) & ((fl >> 8) | nl)) |
+                                                        (mid_n & ((fd << 8) | pd) & ((fd >> 8) | nd));
+                                tcf |= joined & ascii & 0x80808080u;
+                            }
                             if ((((w << 5) + lane) << 2) >= fill) tcf = 0u;
                             // bits 7, 15, 23, 31 -> a nibble, placed by lane; eight lanes make a mask word
                             const unsigned nib = (((tcf >> 7) * 0x00204081u) >> 21) & 0xfu;
@@ -801,11 +821,16 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                                 rec = (unsigned)s;
                             } else if (len >= p.min_token_length) {
                                 bool keep = true;
-                                if (buf[s] == '_') {          // a run of '_' only is not a token
+                                const unsigned c0 = buf[s];
+                                if (c0 == '_') {              // a run of '_' only is not a token
                                     keep = false;
                                     for (int q = s; q < e; ++q) keep |= buf[q] != '_';
                                 }
-                                if (keep && len <= STOP_MAXLEN) keep = !th_is_stop(stop, bufw, s, len);
+                                // stop words start with a letter; the pre-filter knows (first letter, second
+                                // character, length) of every one of them
+                                if (keep && len <= STOP_MAXLEN && (c0 - 'a') < 26u &&
+                                    ((stop_pre[stop_pre_index(c0, len > 1 ? buf[s + 1] : 0u)] >> len) & 1u))
+                                    keep = !th_is_stop(stop, bufw, s, len);
                                 if (keep) {
                                     kind = 1;
                                     rec = (unsigned)s | ((unsigned)(len - 1) << SB);
@@ -1174,6 +1199,15 @@ static int upload_stop_words() {
         TMOG_REQUIRE(placed, "stop-word table: cuckoo insertion failed");
     }
     TMOG_CUDA(cudaMemcpyToSymbol(c_stop, table, sizeof(table)));
+    static unsigned short pre[STOP_PRE];
+    memset(pre, 0, sizeof(pre));
+    for (int i = 0; i < nwords; ++i) {
+        const char* w = kStopWords[i];
+        const size_t len = strlen(w);
+        TMOG_REQUIRE(len >= 1 && len <= STOP_MAXLEN && w[0] >= 'a' && w[0] <= 'z', "stop word '%s' breaks the pre-filter", w);
+        pre[stop_pre_index((unsigned char)w[0], len > 1 ? (unsigned char)w[1] : 0u)] |= (unsigned short)(1u << len);
+    }
+    TMOG_CUDA(cudaMemcpyToSymbol(c_stop_pre, pre, sizeof(pre)));
     if (dev >= 0 && dev < 64) done[dev] = true;
     return TMOG_OK;
 }
@@ -1287,7 +1321,7 @@ struct ThArgs {
 template <typename Slot, int T, int TB, int WARPS, bool SPARSE_OUT>
 static int th_launch(const ThArgs& a, int level, int max_token_bound) {
     auto kernel = text_hash_kernel<Slot, T, TB, WARPS, SPARSE_OUT>;
-    const size_t smem = STOP_SLOTS * sizeof(StopSlot) + TH_COLCACHE * 12 + 32 + (size_t)WARPS * ThLayout<Slot, T, TB>::BYTES;
+    const size_t smem = TH_FIXED_SMEM + 32 + (size_t)WARPS * ThLayout<Slot, T, TB>::BYTES;
     TMOG_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, WARPS * 32, smem));
