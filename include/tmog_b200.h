@@ -168,6 +168,19 @@ int tmog_pivot_column_finish(const uint8_t* dict_data, const int64_t* dict_offse
                              int32_t* code_to_out, int64_t* out_class_counts, uint8_t* top_data, int64_t top_capacity,
                              int64_t* top_offsets);
 
+/* The same finish in two halves, so that the half that needs no counts -- cleaning every dictionary entry
+ * (TextUtils.cleanString, U/text/TextUtils.scala:39-47) and grouping the entries that clean alike (the key-wise sum of
+ * the Algebird map monoid in OpOneHotVectorizer.fitFn, OpOneHotVectorizer.scala:95-97) -- runs on host threads while
+ * the count kernel is still busy on the GPU.  prepare() returns an opaque handle (thread-safe, one per column);
+ * finish() takes the counts and produces what tmog_pivot_column_finish does; free() releases the handle. */
+typedef struct tmog_pivot_dict tmog_pivot_dict;
+int tmog_pivot_dict_prepare(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes, int clean_text,
+                            tmog_pivot_dict** out);
+int tmog_pivot_dict_finish(const tmog_pivot_dict* dict, const int64_t* raw_counts, int nclasses, int top_k,
+                           int64_t min_support, int* n_top, int32_t* code_to_out, int64_t* out_class_counts,
+                           uint8_t* top_data, int64_t top_capacity, int64_t* top_offsets);
+int tmog_pivot_dict_free(tmog_pivot_dict* dict);
+
 /* code_to_out for a dictionary other than the fitted one (transform of new data): position of each entry's cleaned
  * value in the fitted vocabulary, or n_top (OTHER) -- OneHotModelFun.pivotFn :420-427. */
 int tmog_pivot_column_map(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes, int clean_text,
@@ -232,12 +245,20 @@ int tmog_text_stats_layout(int ncols, int slots, int nclasses, size_t* head_byte
 int tmog_text_stats_table_bytes(int slots, int nclasses, size_t* bytes);
 int tmog_text_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* class_ids, int nclasses,
                         int clean_text, int slots, int max_distinct, void* tables, int32_t* flags, void* stream);
+/* The same scan without the length sums of columns that are past the cardinality cap: lengthCounts only feed
+ * `lengthStdDev < minLengthStdDev` (SmartTextVectorizer.scala:113), which never holds at the default minLengthStdDev = 0,
+ * so such a column needs nothing further from its cells and they are not read: non-ASCII bytes in them are reported
+ * by whichever call vectorizes the column afterwards (tmog_text_hash_*_dev, tmog_text_codes_dev: flags[0]).  len_sum
+ * then covers the cells seen before the cap only. */
+int tmog_text_stats_values_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* class_ids, int nclasses,
+                        int clean_text, int slots, int max_distinct, void* tables, int32_t* flags, void* stream);
 
 /* Dictionary codes for the text columns SmartTextVectorizer pivots: codes[k][r] = table slot of row r's cleaned value
  * in column col_index[k] (-1 null), which tmog_pivot_count_dev / tmog_pivot_transform_dev then consume
- * (SmartTextVectorizerModel.transformFn's categoricalPivotFn, SmartTextVectorizer.scala:333-345). */
+ * (SmartTextVectorizerModel.transformFn's categoricalPivotFn, SmartTextVectorizer.scala:333-345).  flags (or NULL):
+ * flags[0] is set when clean_text != 0 and a cell holds a non-ASCII byte (its cleaning is then not the reference's). */
 int tmog_text_codes_dev(const int64_t* col_desc, const int32_t* col_index, int nsel, int64_t n, int clean_text,
-                        int slots, const void* tables, int32_t* codes, int64_t ld, void* stream);
+                        int slots, const void* tables, int32_t* codes, int64_t ld, int32_t* flags, void* stream);
 
 /* ---- OpSetVectorizer (MultiPickList) ------------------------------------------------------------------------------
  * Set columns in Arrow List<dictionary> layout (device): int64 offsets [n + 1], int32 codes [offsets[n]]; row r holds

@@ -281,3 +281,50 @@ def test_hash_many_columns_wide_keys_and_count_overflow():
     rep = [" ".join(["repeat"] * 700 + ["other"] * 3), "repeat once", " ".join(["w%d" % (i % 7) for i in range(2000)])]
     got = _hash_case([rep], ["rep"], 1 << 23, "Shared")
     assert got[0].data.max() == 700
+
+
+def test_text_stats_values_entry_point_matches_the_full_scan():
+    """tmog_text_stats_values_dev (no lengths past the cardinality cap) against tmog_text_stats_dev: identical value
+    tables, distinct counts and non-null counts; the length sums agree for a column that stays under the cap and,
+    for a capped one, cover at most what the full scan covers."""
+    import ctypes as C
+    from transmogrifai_b200 import _lib as L
+    from transmogrifai_b200.stages.smart_text import _col_desc
+    rng = np.random.default_rng(5)
+    n = 20000
+    low = [None if rng.random() < 0.1 else f"Val-{rng.integers(0, 12)}!" for _ in range(n)]     # 12 distinct values
+    high = [None if rng.random() < 0.1 else f"free text {i} with, punctuation." for i in range(n)]
+    dev = _batch({"low": ("Text", low), "high": ("Text", high)}, device="cuda").texts(["low", "high"])
+    slots, cap = 128, 30
+    head, per = C.c_size_t(), C.c_size_t()
+    L.call("tmog_text_stats_layout", 2, slots, 1, C.byref(head), C.byref(per))
+    desc = _col_desc(dev)
+    out = {}
+    for name in ("tmog_text_stats_dev", "tmog_text_stats_values_dev"):
+        tables = torch.zeros(head.value + per.value * 2, dtype=torch.uint8, device="cuda")
+        flags = torch.zeros(4, dtype=torch.int32, device="cuda")
+        L.call(name, desc.data_ptr(), 2, n, None, 1, 1, slots, cap, tables.data_ptr(), flags.data_ptr(),
+               torch.cuda.current_stream().cuda_stream)
+        assert int(flags[0].item()) == 0
+        out[name] = tables[head.value:].cpu().numpy().reshape(2, per.value)
+    full, vals = out["tmog_text_stats_dev"], out["tmog_text_stats_values_dev"]
+    tail = 16 * slots + ((4 * slots + 7) & ~7)
+    assert np.array_equal(full[0], vals[0])                                   # under the cap: everything agrees
+    nd = [int(t[1, tail:tail + 4].view(np.int32)[0]) for t in (full, vals)]
+    assert nd[0] > cap and nd[1] > cap
+    assert np.array_equal(full[1, tail + 24:tail + 32], vals[1, tail + 24:tail + 32])       # non-null cells
+    ls_full, ls_vals = full[1, tail + 8:tail + 24].view(np.uint64), vals[1, tail + 8:tail + 24].view(np.uint64)
+    assert (ls_vals <= ls_full).all() and ls_full[0] > 0
+
+
+def test_non_ascii_text_in_a_capped_column_is_still_refused():
+    """A column past the cardinality cap is no longer read by the TextStats scan; the hashing pass must then be the one
+    that refuses non-ASCII text (the tokenizer is restated for ASCII only)."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    col = [f"distinct value number {i}" for i in range(300)] + ["café au lait"]
+    batch = _batch({"t": (F.TEXT, col)}, device="cuda")
+    est = SmartTextVectorizer().setMaxCardinality(30).setNumFeatures(128).setInput(*_feats(["t"]))
+    with pytest.raises(ValueError, match="non-ASCII"):
+        model = est.fit(batch)
+        model.transform(batch).vectors[est.getOutput().name].to_scipy()

@@ -52,6 +52,9 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_dedupe_strings": [_p, _p, _i64, _p, _p],
     "tmog_pivot_topk": [_p, _p, _p, _i64, _int, _i64, _p, _p],
     "tmog_pivot_column_finish": [_p, _p, _i64, _int, _p, _int, _int, _i64, _p, _p, _p, _p, _i64, _p],
+    "tmog_pivot_dict_prepare": [_p, _p, _i64, _int, _p],
+    "tmog_pivot_dict_finish": [_p, _p, _int, _int, _i64, _p, _p, _p, _p, _i64, _p],
+    "tmog_pivot_dict_free": [_p],
     "tmog_pivot_column_map": [_p, _p, _i64, _int, _p, _p, _int, _p],
     "tmog_pivot_count_dev": [_p, _i64, _i64, _int, _p, _int, _p, _p, _i64, _p, _p, _p],
     "tmog_binary_codes_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _i64, _p],
@@ -63,7 +66,8 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_text_stats_layout": [_int, _int, _int, C.POINTER(_sz), C.POINTER(_sz)],
     "tmog_text_stats_table_bytes": [_int, _int, C.POINTER(_sz)],
     "tmog_text_stats_dev": [_p, _int, _i64, _p, _int, _int, _int, _int, _p, _p, _p],
-    "tmog_text_codes_dev": [_p, _p, _int, _i64, _int, _int, _p, _p, _i64, _p],
+    "tmog_text_stats_values_dev": [_p, _int, _i64, _p, _int, _int, _int, _int, _p, _p, _p],
+    "tmog_text_codes_dev": [_p, _p, _int, _i64, _int, _int, _p, _p, _i64, _p, _p],
     "tmog_text_hash_scratch_bytes": [_i64, C.POINTER(_sz)],
     "tmog_text_hash_stats_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _dbl, _p, _p, _p, _sz, _p],
     "tmog_text_hash_transform_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _p, _p, _sz, _p],

@@ -4,6 +4,8 @@
 #include <string.h>
 
 #include <algorithm>
+#include <memory>
+#include <new>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -228,24 +230,48 @@ int64_t group_strings(const std::string& pool, const std::vector<int64_t>& off, 
 
 }  // namespace
 
-extern "C" int tmog_pivot_column_finish(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes,
-                                        int clean_text, const int64_t* raw_counts, int nclasses, int top_k,
-                                        int64_t min_support, int* n_top, int32_t* code_to_out,
-                                        int64_t* out_class_counts, uint8_t* top_data, int64_t top_capacity,
-                                        int64_t* top_offsets) {
-    TMOG_REQUIRE(ncodes >= 0 && dict_offsets && raw_counts && n_top && code_to_out && out_class_counts && top_offsets,
-                 "NULL argument");
-    TMOG_REQUIRE(top_k > 0 && nclasses >= 1, "requirement failed: topK must be positive");
-    std::string pool;
+// The counts-independent half of the finish (cleaning + grouping of the dictionary entries), so that a caller can run
+// it while the count kernel is still busy on the GPU.
+struct tmog_pivot_dict {
+    std::string pool;               // cleaned entries back to back
     std::vector<int64_t> off;
+    std::vector<int32_t> ids;       // cleaned-value id of every dictionary entry
+    std::vector<int32_t> first;     // first entry of every cleaned value
+    int64_t ncodes = 0;
+};
+
+extern "C" int tmog_pivot_dict_prepare(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes,
+                                       int clean_text, tmog_pivot_dict** out) {
+    TMOG_REQUIRE(ncodes >= 0 && dict_offsets && out, "NULL argument");
+    std::unique_ptr<tmog_pivot_dict> d(new (std::nothrow) tmog_pivot_dict());
+    TMOG_REQUIRE(d != nullptr, "out of host memory");
     int64_t bad = -1;
-    if (!clean_dictionary(dict_data, dict_offsets, ncodes, clean_text != 0, pool, off, &bad)) {
+    if (!clean_dictionary(dict_data, dict_offsets, ncodes, clean_text != 0, d->pool, d->off, &bad)) {
         set_error("cleanString: dictionary entry %lld holds non-ASCII text; Java's Unicode case mapping is not restated "
                   "on this path (set cleanText = false)", (long long)bad);
         return TMOG_EINVAL;
     }
-    std::vector<int32_t> ids, first;
-    const int64_t nd = group_strings(pool, off, ids, first);
+    group_strings(d->pool, d->off, d->ids, d->first);
+    d->ncodes = ncodes;
+    *out = d.release();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_pivot_dict_free(tmog_pivot_dict* d) {
+    delete d;
+    return TMOG_OK;
+}
+
+extern "C" int tmog_pivot_dict_finish(const tmog_pivot_dict* d, const int64_t* raw_counts, int nclasses, int top_k,
+                                      int64_t min_support, int* n_top, int32_t* code_to_out,
+                                      int64_t* out_class_counts, uint8_t* top_data, int64_t top_capacity,
+                                      int64_t* top_offsets) {
+    TMOG_REQUIRE(d && raw_counts && n_top && code_to_out && out_class_counts && top_offsets, "NULL argument");
+    TMOG_REQUIRE(top_k > 0 && nclasses >= 1, "requirement failed: topK must be positive");
+    const std::string& pool = d->pool;
+    const std::vector<int64_t>& off = d->off;
+    const std::vector<int32_t>&ids = d->ids, &first = d->first;
+    const int64_t ncodes = d->ncodes, nd = (int64_t)first.size();
     // merged counts per cleaned value and class (raw_counts row 0 is the null bin, row 1 + code the raw code)
     std::vector<int64_t> merged((size_t)nd * nclasses, 0), total((size_t)nd, 0);
     for (int64_t i = 0; i < ncodes; ++i)
@@ -290,6 +316,22 @@ extern "C" int tmog_pivot_column_finish(const uint8_t* dict_data, const int64_t*
         for (int c = 0; c < nclasses; ++c) out_class_counts[(size_t)pos[v] * nclasses + c] += merged[(size_t)v * nclasses + c];
     for (int c = 0; c < nclasses; ++c) out_class_counts[(k + 1) * nclasses + c] = raw_counts[c];
     return TMOG_OK;
+}
+
+extern "C" int tmog_pivot_column_finish(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes,
+                                        int clean_text, const int64_t* raw_counts, int nclasses, int top_k,
+                                        int64_t min_support, int* n_top, int32_t* code_to_out,
+                                        int64_t* out_class_counts, uint8_t* top_data, int64_t top_capacity,
+                                        int64_t* top_offsets) {
+    TMOG_REQUIRE(ncodes >= 0 && dict_offsets && raw_counts && n_top && code_to_out && out_class_counts && top_offsets,
+                 "NULL argument");
+    TMOG_REQUIRE(top_k > 0 && nclasses >= 1, "requirement failed: topK must be positive");
+    tmog_pivot_dict* d = nullptr;
+    if (int rc = tmog_pivot_dict_prepare(dict_data, dict_offsets, ncodes, clean_text, &d)) return rc;
+    const int rc = tmog_pivot_dict_finish(d, raw_counts, nclasses, top_k, min_support, n_top, code_to_out,
+                                          out_class_counts, top_data, top_capacity, top_offsets);
+    tmog_pivot_dict_free(d);
+    return rc;
 }
 
 // code_to_out[i] = position of dictionary entry i's cleaned value in the fitted vocabulary `top` (n_top strings), or

@@ -240,8 +240,8 @@ __device__ __forceinline__ int ts_insert(const TextStatsTable& t, int slots, int
 // one thread per cell (cells are short strings; consecutive threads take consecutive rows of one column)
 __global__ void __launch_bounds__(256)
 text_stats_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, const uint8_t* __restrict__ class_ids,
-                  int nclasses, int clean, int slots, int max_distinct, const TextStatsTable* __restrict__ tables,
-                  int* __restrict__ flags) {
+                  int nclasses, int clean, int want_lengths, int slots, int max_distinct,
+                  const TextStatsTable* __restrict__ tables, int* __restrict__ flags) {
     const int c = blockIdx.y;
     const TextColumn tc = cols[c];
     const TextStatsTable t = tables[c];
@@ -252,8 +252,11 @@ text_stats_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
         const int64_t a = tc.offsets[r], b = tc.offsets[r + 1];
         int m;
         if (*t.ndistinct > max_distinct) {
-            // past the cardinality cap nothing more is recorded for the column but the lengths
-            m = clean_length_cell(tc.data + a, b - a, clean != 0, non_ascii);
+            // past the cardinality cap nothing more is recorded for the column but the lengths, and those only
+            // matter to a positive minLengthStdDev (SmartTextVectorizer.scala:113)
+            // -- and without it the cell is not read at all: whoever vectorizes the column reads every cell anyway
+            // and reports non-ASCII bytes then (tmog_text_hash_*_dev, tmog_text_codes_dev)
+            m = want_lengths ? clean_length_cell(tc.data + a, b - a, clean != 0, non_ascii) : 0;
         } else {
             unsigned long long h;
             clean_hash_cell(tc.data + a, b - a, clean != 0, h, m, non_ascii);
@@ -281,7 +284,8 @@ text_stats_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
 // table, which cannot happen for a column whose cardinality stayed under the cap)
 __global__ void __launch_bounds__(256)
 text_code_kernel(const TextColumn* __restrict__ cols, const int* __restrict__ col_index, int nsel, int64_t n, int clean,
-                 int slots, const TextStatsTable* __restrict__ tables, int32_t* __restrict__ codes, int64_t ld) {
+                 int slots, const TextStatsTable* __restrict__ tables, int32_t* __restrict__ codes, int64_t ld,
+                 int* __restrict__ flags) {
     const int k = blockIdx.y;
     const int c = col_index[k];
     const TextColumn tc = cols[c];
@@ -294,6 +298,7 @@ text_code_kernel(const TextColumn* __restrict__ cols, const int* __restrict__ co
             int m;
             bool na = false;
             clean_hash_cell(tc.data + a, b - a, clean != 0, h, m, na);
+            if (na && clean && flags) flags[0] = 1;
             if (h == TS_EMPTY) h = 0x1234567ull;
             code = -2;
             unsigned s = (unsigned)(h >> 20) & (unsigned)(slots - 1);
@@ -1219,9 +1224,9 @@ extern "C" int tmog_text_stats_table_bytes(int slots, int nclasses, size_t* byte
     return TMOG_OK;
 }
 
-extern "C" int tmog_text_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* class_ids, int nclasses,
-                                   int clean_text, int slots, int max_distinct, void* tables, int32_t* flags,
-                                   void* stream) {
+static int text_stats_launch(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* class_ids, int nclasses,
+                             int clean_text, int want_lengths, int slots, int max_distinct, void* tables,
+                             int32_t* flags, void* stream) {
     TMOG_REQUIRE(ncols >= 0 && n >= 0 && nclasses >= 1 && nclasses <= 255, "bad shape");
     TMOG_REQUIRE(slots >= 64 && (slots & (slots - 1)) == 0, "slots must be a power of two >= 64");
     TMOG_REQUIRE(max_distinct >= 0 && max_distinct + 1 < slots / 2, "max_distinct %d too large for %d slots", max_distinct,
@@ -1254,10 +1259,24 @@ extern "C" int tmog_text_stats_dev(const int64_t* col_desc, int ncols, int64_t n
     if (n == 0) return TMOG_OK;
     const int gx = (int)std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 4);
     text_stats_kernel<<<dim3(gx, ncols), 256, 0, st>>>(reinterpret_cast<const TextColumn*>(col_desc), ncols, n, class_ids,
-                                                       nclasses, clean_text, slots, max_distinct,
+                                                       nclasses, clean_text, want_lengths, slots, max_distinct,
                                                        static_cast<const TextStatsTable*>(tables), flags);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
+}
+
+extern "C" int tmog_text_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* class_ids, int nclasses,
+                                   int clean_text, int slots, int max_distinct, void* tables, int32_t* flags,
+                                   void* stream) {
+    return text_stats_launch(col_desc, ncols, n, class_ids, nclasses, clean_text, 1, slots, max_distinct, tables, flags,
+                             stream);
+}
+
+extern "C" int tmog_text_stats_values_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* class_ids,
+                                          int nclasses, int clean_text, int slots, int max_distinct, void* tables,
+                                          int32_t* flags, void* stream) {
+    return text_stats_launch(col_desc, ncols, n, class_ids, nclasses, clean_text, 0, slots, max_distinct, tables, flags,
+                             stream);
 }
 
 extern "C" int tmog_text_stats_layout(int ncols, int slots, int nclasses, size_t* head_bytes, size_t* per_column_bytes) {
@@ -1268,14 +1287,14 @@ extern "C" int tmog_text_stats_layout(int ncols, int slots, int nclasses, size_t
 
 extern "C" int tmog_text_codes_dev(const int64_t* col_desc, const int32_t* col_index, int nsel, int64_t n,
                                    int clean_text, int slots, const void* tables, int32_t* codes, int64_t ld,
-                                   void* stream) {
+                                   int32_t* flags, void* stream) {
     TMOG_REQUIRE(nsel >= 0 && n >= 0 && ld >= n, "bad shape");
     if (nsel == 0 || n == 0) return TMOG_OK;
     TMOG_REQUIRE(col_desc && col_index && tables && codes, "NULL argument");
     const int gx = (int)std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 4);
     text_code_kernel<<<dim3(gx, nsel), 256, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const TextColumn*>(col_desc), col_index, nsel, n, clean_text, slots,
-        static_cast<const TextStatsTable*>(tables), codes, ld);
+        static_cast<const TextStatsTable*>(tables), codes, ld, flags);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }

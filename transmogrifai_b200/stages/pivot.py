@@ -149,12 +149,27 @@ class OpTextPivotVectorizer(OpEstimator):
         n, ncols = batch.n, len(names)
         label_name = batch.response
         classes = counts_per_class = ids = None
+        ncodes = np.array([len(d) for d in block.dicts], dtype=np.int64)
+        clean = int(self.cleanText)
+
+        def prepare(data, offs, nc):
+            """The counts-independent half of a column's finish (clean + group its dictionary), on a pool thread."""
+            h = C.c_void_p()
+            L.call("tmog_pivot_dict_prepare", data.ctypes.data, offs.ctypes.data, nc, clean, C.byref(h))
+            return h, (data, offs)                          # the arrays stay alive with the handle
+
+        # One process: the dictionaries are final, so their cleaning starts now, largest first, and runs on host
+        # threads while the label classes and the count kernel are on the GPU.
+        early = None
+        if D.world()[1] == 1 and ncols > 0:
+            order = sorted(range(ncols), key=lambda c: -int(ncodes[c]))
+            futs = {c: _pool().submit(prepare, *block.dict_arrays(c), int(ncodes[c])) for c in order}
+            early = futs
         if label_name:
             y = batch.label()
             y = y if y.is_cuda else y.cuda()
             classes, counts_per_class, ids = label_info_dev(batch, y, label_name)
         ncls = len(classes) if classes is not None else 1
-        ncodes = np.array([len(d) for d in block.dicts], dtype=np.int64)
         nids = ncodes + 1                                   # raw codes + the null id 0
         zeros = np.zeros(ncols, dtype=np.int64)
         count_offset = np.concatenate([[0], np.cumsum(nids * ncls)[:-1]]).astype(np.int64) if ncols else zeros
@@ -190,22 +205,25 @@ class OpTextPivotVectorizer(OpEstimator):
         counts = D.allreduce_sum(counts)
 
         def finish(c: int):
-            if g_maps[c] is None:
-                data, offs = block.dict_arrays(c)
-            else:
-                data, offs = encode_strings(g_dicts[c])
             nc = int(g_ncodes[c])
-            raw = np.ascontiguousarray(counts[g_offset[c]:g_offset[c] + (nc + 1) * ncls])
-            k = self.topK
-            n_top = C.c_int(0)
-            code_to_out = np.zeros(max(nc, 1), dtype=np.int32)
-            per_class = np.zeros((k + 2) * ncls, dtype=np.int64)
-            top_data = np.zeros(max(len(data), 1), dtype=np.uint8)
-            top_offs = np.zeros(k + 1, dtype=np.int64)
-            L.call("tmog_pivot_column_finish", data.ctypes.data, offs.ctypes.data, nc,
-                   int(self.cleanText), raw.ctypes.data, ncls, k, self.minSupport, C.byref(n_top),
-                   code_to_out.ctypes.data, per_class.ctypes.data, top_data.ctypes.data, len(top_data),
-                   top_offs.ctypes.data)
+            if early is not None:
+                handle, _keep = early[c].result()
+            else:
+                handle, _keep = prepare(*(block.dict_arrays(c) if g_maps[c] is None else encode_strings(g_dicts[c])),
+                                        nc)
+            try:
+                raw = np.ascontiguousarray(counts[g_offset[c]:g_offset[c] + (nc + 1) * ncls])
+                k = self.topK
+                n_top = C.c_int(0)
+                code_to_out = np.zeros(max(nc, 1), dtype=np.int32)
+                per_class = np.zeros((k + 2) * ncls, dtype=np.int64)
+                top_data = np.zeros(max(int(_keep[1][-1]) if len(_keep[1]) else 0, 1), dtype=np.uint8)
+                top_offs = np.zeros(k + 1, dtype=np.int64)
+                L.call("tmog_pivot_dict_finish", handle, raw.ctypes.data, ncls, k, self.minSupport, C.byref(n_top),
+                       code_to_out.ctypes.data, per_class.ctypes.data, top_data.ctypes.data, len(top_data),
+                       top_offs.ctypes.data)
+            finally:
+                L.call("tmog_pivot_dict_free", handle)
             t = n_top.value
             top = decode_strings(top_data, top_offs[:t + 1])
             rows = per_class.reshape(k + 2, ncls)[:t + 2]
@@ -214,12 +232,21 @@ class OpTextPivotVectorizer(OpEstimator):
             local = code_to_out[:nc] if g_maps[c] is None else code_to_out[:nc][g_maps[c]]
             return top, local, rows.astype(np.float64)
 
-        if ncols > 1:                  # the largest dictionaries first: they are the critical path
-            order = sorted(range(ncols), key=lambda c: -int(g_ncodes[c]))
-            done = dict(zip(order, _pool().map(finish, order)))
-            results = [done[c] for c in range(ncols)]
-        else:
-            results = [finish(c) for c in range(ncols)]
+        try:
+            if ncols > 1:                  # the largest dictionaries first: they are the critical path
+                order = sorted(range(ncols), key=lambda c: -int(g_ncodes[c]))
+                done = dict(zip(order, _pool().map(finish, order)))
+                results = [done[c] for c in range(ncols)]
+            else:
+                results = [finish(c) for c in range(ncols)]
+        except Exception:
+            if early is not None:          # handles of columns whose finish never ran
+                for f in early.values():
+                    try:
+                        L.call("tmog_pivot_dict_free", f.result()[0])
+                    except Exception:
+                        pass
+            raise
         tops = [r[0] for r in results]
         self._metadata = self._metadata_for(tops)
         stats = None

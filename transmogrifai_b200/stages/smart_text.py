@@ -253,7 +253,8 @@ class SmartTextVectorizer(OpEstimator):
         tables = torch.zeros(head.value + per.value * ncols, dtype=torch.uint8, device="cuda")
         flags = torch.zeros(4, dtype=torch.int32, device="cuda")
         desc = _col_desc(dev)
-        L.call("tmog_text_stats_dev", desc.data_ptr(), ncols, n, None, 1, int(self.cleanText), slots,
+        # lengths of capped columns matter to minLengthStdDev > 0 only (which this path does not take)
+        L.call("tmog_text_stats_values_dev", desc.data_ptr(), ncols, n, None, 1, int(self.cleanText), slots,
                self.maxCardinality, tables.data_ptr(), flags.data_ptr(), R.stream())
         if int(flags[0].item()) and self.cleanText:
             raise ValueError("non-ASCII text met with cleanText = true: Java's Unicode case mapping is not restated on "
@@ -452,8 +453,12 @@ class SmartTextVectorizerModel(OpModel):
         codes = torch.empty((max(k, 1), ld), dtype=torch.int32, device="cuda")
         sel = torch.tensor(self.pivot_idx or [0], dtype=torch.int32, device="cuda")
         desc = _col_desc(dev)
+        flags = torch.zeros(4, dtype=torch.int32, device="cuda")
         L.call("tmog_text_codes_dev", desc.data_ptr(), sel.data_ptr(), k, n, int(self.shouldCleanText), slots,
-               tables.data_ptr(), codes.data_ptr(), ld, R.stream())
+               tables.data_ptr(), codes.data_ptr(), ld, flags.data_ptr(), R.stream())
+        if k and self.shouldCleanText and int(flags[0].item()):
+            raise ValueError("non-ASCII text met with cleanText = true: Java's Unicode case mapping is not restated on "
+                             "this path")
         return codes, ld, slots, slot_of
 
     def _pivot_pos_tables(self, slots: int, slot_of, newpos: np.ndarray):
