@@ -38,6 +38,11 @@ def _worker(rank, size, port, q):
         for p in parts[1:]:
             L.call("tmog_real_partials_merge", ref.ctypes.data, p.reshape(-1).copy().ctypes.data, 3)
         np.testing.assert_allclose(merged, ref, rtol=1e-15)
+        # 1b. the fused exchange: partials merged in rank order + count tables summed, one all-gather
+        tabs = [np.arange(6, dtype=np.int64).reshape(2, 3) * (rank + 1), np.array([rank + 5], dtype=np.int64)]
+        merged2, sums = D.gather_fit_results(parts[rank].reshape(-1).copy(), tabs)
+        assert np.array_equal(merged2, ref)
+        assert np.array_equal(sums[0], np.arange(6).reshape(2, 3) * 3) and sums[1].tolist() == [11]
         # 2. shifts come from rank 0
         sh = D.broadcast(np.full(5, float(rank + 1)))
         assert np.array_equal(sh, np.full(5, 1.0))

@@ -309,3 +309,65 @@ def test_transmogrify_all_types_continuous_label_matches_oracle():
     import scipy.sparse as sp
     exp = sp.csr_matrix(xo)[:, ref.indices_to_keep]
     assert got.shape == exp.shape and abs(got - exp).max() < 1e-12
+
+
+def test_min_variance_filter_reference_drop_set():
+    # MinVarianceFilterTest.scala:73-124: minVariance 0.1 drops age, gender and testFeatNegCor, keeps the two heights
+    from transmogrifai_b200.stages.min_variance import MinVarianceFilter
+    batch, _label, fv, x, _y = _sc_batch()
+    checked = fv.filterMinVariance(minVariance=0.1, removeBadFeatures=True)
+    est = checked.origin_stage
+    assert isinstance(est, MinVarianceFilter)
+    model = est.fit(batch)
+    assert est.summary.dropped == ["age_0", "gender_3", "testFeatNegCor_4"]
+    assert model.indicesToKeep == [1, 2]
+    out = model.transform(batch).vectors[checked.name]
+    assert np.array_equal(out.to_numpy(), x[:, [1, 2]])
+    assert out.metadata.columnNames() == ["height_0", "height_null_1"]
+    st = S.col_stats(x)
+    assert est.summary.count == 6
+    np.testing.assert_allclose(est.summary.mean, st.mean, rtol=1e-12)
+    np.testing.assert_allclose(est.summary.variance, st.variance, rtol=1e-9, atol=1e-18)
+    assert np.array_equal(est.summary.min, st.min) and np.array_equal(est.summary.max, st.max)
+    # defaults (MinVarianceFilter.scala:155-158): nothing is removed, the vector passes through
+    dflt = MinVarianceFilter().setInput(fv)
+    assert dflt.minVariance == 1e-5 and dflt.removeBadFeatures is False
+    m2 = dflt.fit(batch)
+    assert m2.indicesToKeep == [0, 1, 2, 3, 4] and dflt.summary.dropped == []
+    assert np.array_equal(m2.transform(batch).vectors[dflt.getOutput().name].to_numpy(), x)
+    with pytest.raises(ValueError, match="dropped all of your features"):
+        MinVarianceFilter().setInput(fv).setMinVariance(10.0).setRemoveBadFeatures(True).fit(batch)
+
+
+@pytest.mark.parametrize("with_label", [True, False])
+def test_min_variance_filter_after_transmogrify(with_label):
+    """On the output of transmogrify(): with a response in the batch the statistics come from the fused vectorizer
+    scans, without one from the dense statistics kernel; both must agree with the oracle's colStats and variance rule."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+    rng = np.random.default_rng(11)
+    n = 5000
+    cols = {}
+    for j in range(6):
+        v = rng.normal(j, 1.0 + j, n)
+        if j == 2:
+            v[:] = 3.25                                     # constant: variance 0
+        if j == 4:
+            v = rng.normal(0.0, 1e-3, n)                    # variance 1e-6 <= 1e-5
+        cols[f"r{j}"] = (F.REAL, [None if rng.random() < 0.1 else float(t) for t in v])
+    cols["y"] = (F.REALNN, [float(rng.random() < 0.4) for _ in range(n)])
+    batch = _batch(cols, response="y" if with_label else None).to("cuda")
+    feats = [F.FeatureBuilder.Real(f"r{j}").asPredictor() for j in range(6)]
+    checked = transmogrify(feats).filterMinVariance(removeBadFeatures=True)
+    out, fitted = fit_and_transform(batch, checked)
+    est = checked.origin_stage
+    raw = [cols[f"r{j}"][1] for j in range(6)]
+    fills = V.real_vectorizer_fit(raw)
+    exp = V.real_vectorizer_transform(raw, fills, True)
+    st = S.col_stats(exp)
+    np.testing.assert_allclose(est.summary.mean, st.mean, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(est.summary.variance, st.variance, rtol=1e-9, atol=1e-18)
+    keep = [i for i in range(exp.shape[1]) if not st.variance[i] <= 1e-5]
+    assert fitted[-1].indicesToKeep == keep and 4 not in keep and 8 not in keep
+    got = out.vectors[checked.name].to_numpy()
+    np.testing.assert_allclose(got, exp[:, keep], rtol=1e-12, atol=0)

@@ -2,6 +2,7 @@
 //   contingency statistics (Cramer's V, mutual information, rule confidence / support) and the removeBadFeatures
 //   decision.  Reference file:line for each function is given in include/tmog_b200.h.
 #include <math.h>
+#include <string.h>
 
 #include <algorithm>
 #include <map>
@@ -134,23 +135,42 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
     for (int i = 0; i < d; ++i) max_group = std::max(max_group, group_id[i]);
     const double none = nan("");
     std::vector<double> corr_parent((size_t)max_parent + 1, none), cramers_parent((size_t)max_parent + 1, none);
-    for (int i = 0; i < d; ++i) {
-        if (corr_pos[i] >= 0 && corr_label) {
-            const double c = corr_label[corr_pos[i]];
-            const double ac = isnan(c) ? 0.0 : fabs(c);
-            for (int k = parent_offsets[i]; k < parent_offsets[i + 1]; ++k) {
-                double& slot = corr_parent[parent_ids[k]];
-                slot = isnan(slot) ? ac : std::max(slot, ac);
+    // Columns of a hashed block all carry the same parent list (a shared hash space: every text feature), so the walk
+    // over the parents is done once per run of identical lists, not once per column.
+    auto same_parents = [&](int a, int b) {
+        const int la = parent_offsets[a + 1] - parent_offsets[a], lb = parent_offsets[b + 1] - parent_offsets[b];
+        return la == lb && (la == 0 || memcmp(parent_ids + parent_offsets[a], parent_ids + parent_offsets[b],
+                                              sizeof(int32_t) * (size_t)la) == 0);
+    };
+    std::vector<int32_t> run_of((size_t)d, 0);      // first column of the run a column belongs to
+    for (int i0 = 0; i0 < d;) {
+        int i1 = i0 + 1;
+        while (i1 < d && same_parents(i0, i1)) ++i1;
+        bool any = false;
+        double run_max = 0.0;
+        for (int i = i0; i < i1; ++i) {
+            run_of[i] = i0;
+            if (corr_pos[i] >= 0 && corr_label) {
+                const double c = corr_label[corr_pos[i]];
+                const double ac = isnan(c) ? 0.0 : fabs(c);
+                run_max = any ? std::max(run_max, ac) : ac;
+                any = true;
+            }
+            // a column is in cramersVMap iff it belongs to a categorical group (rule_count >= 0); its V may be NaN.
+            // parentMap (.toMap) keeps the LAST parent of a multi-parent column.
+            if (rule_count[i] >= 0 && parent_offsets[i + 1] > parent_offsets[i]) {
+                const int last = parent_ids[parent_offsets[i + 1] - 1];
+                const double av = isnan(cramers_v[i]) ? 0.0 : fabs(cramers_v[i]);
+                double& slot = cramers_parent[last];
+                slot = isnan(slot) ? av : std::max(slot, av);
             }
         }
-        // a column is in cramersVMap iff it belongs to a categorical group (rule_count >= 0); its V may be NaN.
-        // parentMap (.toMap) keeps the LAST parent of a multi-parent column.
-        if (rule_count[i] >= 0 && parent_offsets[i + 1] > parent_offsets[i]) {
-            const int last = parent_ids[parent_offsets[i + 1] - 1];
-            const double av = isnan(cramers_v[i]) ? 0.0 : fabs(cramers_v[i]);
-            double& slot = cramers_parent[last];
-            slot = isnan(slot) ? av : std::max(slot, av);
-        }
+        if (any)
+            for (int k = parent_offsets[i0]; k < parent_offsets[i0 + 1]; ++k) {
+                double& slot = corr_parent[parent_ids[k]];
+                slot = isnan(slot) ? run_max : std::max(slot, run_max);
+            }
+        i0 = i1;
     }
     // getFeaturesToDrop: groups flagged by the association-rule check
     std::vector<char> group_flagged((size_t)max_group + 1, 0);
@@ -162,6 +182,7 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
                 break;
             }
     }
+    double run_pc = nan(""), run_pv = nan("");
     for (int i = 0; i < d; ++i) {
         uint32_t r = 0;
         if (variance[i] <= min_variance) r |= 1u;
@@ -185,13 +206,16 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
                 break;
             }
         if (group_id[i] >= 0 && group_flagged[group_id[i]]) r |= 64u;
-        // parent-level values: max over the column's parents that have an entry
-        double pc = nan(""), pv = nan("");
-        for (int k = parent_offsets[i]; k < parent_offsets[i + 1]; ++k) {
-            const double a = corr_parent[parent_ids[k]], b = cramers_parent[parent_ids[k]];
-            if (!isnan(a)) pc = isnan(pc) ? a : std::max(pc, a);
-            if (!isnan(b)) pv = isnan(pv) ? b : std::max(pv, b);
+        // parent-level values: max over the column's parents that have an entry (once per run of equal parent lists)
+        if (run_of[i] == i) {
+            run_pc = run_pv = nan("");
+            for (int k = parent_offsets[i]; k < parent_offsets[i + 1]; ++k) {
+                const double a = corr_parent[parent_ids[k]], b = cramers_parent[parent_ids[k]];
+                if (!isnan(a)) run_pc = isnan(run_pc) ? a : std::max(run_pc, a);
+                if (!isnan(b)) run_pv = isnan(run_pv) ? b : std::max(run_pv, b);
+            }
         }
+        const double pc = run_pc, pv = run_pv;
         if (parent_corr_out) parent_corr_out[i] = pc;
         if (parent_cramers_out) parent_cramers_out[i] = pv;
         if (remove_feature_group && (!text_shared_hash[i] || !protect_text_shared_hash)) {

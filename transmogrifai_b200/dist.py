@@ -41,6 +41,37 @@ def allreduce_real_partials(partials: np.ndarray) -> np.ndarray:
     return p.cpu().numpy().reshape(-1)
 
 
+def gather_fit_results(partials, tables=()):
+    """Everything one fit scan leaves behind, merged over the ranks in ONE exchange: the [(ncols+1) * NSTAT] partial
+    block (device tensor or numpy; merged in rank order by tmog_real_partials_merge, so the result does not depend on
+    the reduction tree) and any number of int64 count tables (summed).  The blocks travel as raw bytes in a single
+    all-gather followed by a single device-to-host copy.  -> (partials, [tables]) as numpy arrays."""
+    from . import _lib as L
+    as_t = lambda a: a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))  # noqa: E731
+    p = as_t(partials).reshape(-1)
+    ts = [as_t(t) for t in tables]
+    shapes = [tuple(t.shape) for t in ts]
+    if world()[1] == 1:
+        return p.cpu().numpy(), [t.cpu().numpy() for t in ts]
+    dev = _device()
+    flat = torch.cat([p.to(dev)] + [t.to(dev).contiguous().reshape(-1).view(torch.float64) for t in ts])
+    out = torch.empty(world()[1] * flat.numel(), dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(out, flat)
+    host = out.cpu().numpy().reshape(world()[1], flat.numel())
+    npart = p.numel()
+    ncols = npart // REAL_NSTAT - 1
+    merged = host[0, :npart].copy()
+    for r in range(1, world()[1]):
+        other = np.ascontiguousarray(host[r, :npart])
+        L.call("tmog_real_partials_merge", merged.ctypes.data, other.ctypes.data, ncols)
+    outs, at = [], npart
+    for shp in shapes:
+        k = int(np.prod(shp)) if len(shp) else 1
+        outs.append(np.ascontiguousarray(host[:, at:at + k]).view(np.int64).sum(axis=0).reshape(shp))
+        at += k
+    return merged, outs
+
+
 def broadcast(a: np.ndarray, src: int = 0) -> np.ndarray:
     if world()[1] == 1:
         return a
@@ -92,11 +123,10 @@ def union_classes(local: Optional[np.ndarray], cap: int = 255) -> Optional[np.nd
     if k > 0:
         buf[1:1 + k] = local
     t = torch.from_numpy(buf).to(_device())
-    out = [torch.empty_like(t) for _ in range(world()[1])]
-    dist.all_gather(out, t)
+    out = torch.empty(world()[1] * t.numel(), dtype=t.dtype, device=t.device)
+    dist.all_gather_into_tensor(out, t)
     vals = []
-    for o in out:
-        o = o.cpu().numpy()
+    for o in out.cpu().numpy().reshape(world()[1], -1):      # one device-to-host copy for all ranks
         kk = int(o[0])
         if kk < 0:
             return None

@@ -48,6 +48,12 @@ class Feature:
         from .dsl import sanity_check
         return sanity_check(self, feature_vector, **kwargs)
 
+    def filterMinVariance(self, minVariance: float = 1e-5, removeBadFeatures: bool = False) -> "Feature":  # noqa: N802,N803
+        """RichVectorFeature.filterMinVariance (core/src/main/scala/com/salesforce/op/dsl/RichVectorFeature.scala:153-163)"""
+        from .stages.min_variance import MinVarianceFilter
+        return MinVarianceFilter().setInput(self).setMinVariance(minVariance) \
+            .setRemoveBadFeatures(removeBadFeatures).getOutput()
+
 
 class _Builder:
     def __init__(self, name: str, type_name: str):

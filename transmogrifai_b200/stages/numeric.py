@@ -190,9 +190,11 @@ class RealVectorizer(OpEstimator):
                                MAX_LABEL_CLASSES, 0, d_nc.data_ptr(), R.stream())
 
                 classes, counts, ids = label_info_dev(batch, y, label_name, after_launch=count_nulls)
-                if classes is not None and d_nc is not None:
-                    null_counts = D.allreduce_sum(d_nc[:, :len(classes)].cpu().numpy())
-            partials = D.allreduce_real_partials(d_part.cpu().numpy())
+            # partial sums and null counts of all ranks in one exchange and one device-to-host copy
+            want_nc = label_name and classes is not None and d_nc is not None
+            partials, tabs = D.gather_fit_results(d_part, [d_nc[:, :len(classes)]] if want_nc else [])
+            if want_nc:
+                null_counts = tabs[0]
             shifts = d_shifts.cpu().numpy()
         else:
             y = batch.label() if label_name else torch.zeros(max(n, 2), dtype=torch.float64)

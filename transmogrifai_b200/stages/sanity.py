@@ -287,7 +287,14 @@ class SanityChecker(OpEstimator):
     def _plan(meta: OpVectorMetadata) -> "_MetaPlan":
         plan = meta.__dict__.get("_sanity_plan")
         if plan is None:
-            plan = _MetaPlan(meta)
+            # the plan depends on the column descriptions only: vectors with equal metadata (a refit on the next
+            # batch, the folds of a cross-validation) share it
+            key = tuple(meta.runs)
+            plan = _PLAN_CACHE.get(key)
+            if plan is None:
+                if len(_PLAN_CACHE) >= 64:
+                    _PLAN_CACHE.clear()
+                plan = _PLAN_CACHE[key] = _MetaPlan(meta)
             meta.__dict__["_sanity_plan"] = plan
         return plan
 
@@ -383,6 +390,7 @@ class SanityChecker(OpEstimator):
 
 
 _RUN_INFO: Dict[OpVectorColumnMetadata, tuple] = {}
+_PLAN_CACHE: Dict[tuple, "_MetaPlan"] = {}
 
 
 class _MetaPlan:
@@ -474,8 +482,14 @@ class SanityCheckerModel(OpModel):
     def __init__(self, parent: SanityChecker, indicesToKeep: List[int], removeBadFeatures: bool):  # noqa: N803
         super().__init__(parent)
         self._keep = np.asarray(indicesToKeep, dtype=np.int64)
-        self.indicesToKeep = self._keep.tolist()
+        self._keep_list: Optional[List[int]] = None
         self.removeBadFeatures = removeBadFeatures
+
+    @property
+    def indicesToKeep(self) -> List[int]:  # noqa: N802 -- a Python list on demand (262 k entries for a hashed block)
+        if self._keep_list is None:
+            self._keep_list = self._keep.tolist()
+        return self._keep_list
 
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
         vec = batch.vectors[self.inN[1].name]
