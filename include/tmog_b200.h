@@ -102,6 +102,11 @@ int tmog_real_finish(const double* partials, const double* shifts, int ncols, in
                      int track_nulls, double* fills /* [ncols] */, double* mean, double* variance, double* min,
                      double* max, double* cov_label, double* label_stats /* [5] */,
                      double* null_label_sum /* [ncols] */);
+/* The same finish with the fill value of every column given (fill_values [ncols]): the statistics of columns filled
+ * with their mode (IntegralVectorizer) or any other per-column constant. */
+int tmog_real_finish_with_fills(const double* partials, const double* shifts, int ncols, const double* fill_values,
+                                int track_nulls, double* mean, double* variance, double* mn, double* mx,
+                                double* cov_label, double* label_stats, double* null_label_sum);
 
 /* Replaces RealVectorizerModel.transformFn  C/stages/impl/feature/RealVectorizer.scala:112-123  (track_nulls: the
  * interleaved [x or fill, isNull] dense layout) and RealNNVectorizer.transformFn  RealNNVectorizer.scala:52-55
@@ -377,6 +382,39 @@ int tmog_label_class_ids_dev(const double* label, int64_t n, const double* class
  * accumulate != 0 adds to counts (row chunks), else counts is overwritten. */
 int tmog_null_class_counts_dev(const uint64_t* valid, int64_t ldv, const uint8_t* class_ids, int64_t n, int ncols,
                                int nclasses, int accumulate, uint64_t* counts, void* stream);
+
+/* ---- IntegralVectorizer (Integral features: int64 values + validity bitmap, device) ---------------------------------
+ * Replaces IntegralVectorizer.fitFn / IntegralVectorizerModel.transformFn
+ * (C/stages/impl/feature/IntegralVectorizer.scala:47-117) and SequenceAggregators.ModeSeqNullInt
+ * (U/spark/SequenceAggregators.scala:100-131): per column the map value -> count over the non-null rows; the mode is
+ * the most frequent value, the smallest one among equally frequent values, 0 for a column without values.
+ *
+ * tmog_integral_mode_dev counts into one open-addressing table per column (cap slots, a power of two >= 64) laid out in
+ * `scratch` (tmog_integral_mode_scratch_bytes; tmog_integral_mode_layout gives the byte offsets of keys [ncols][cap]
+ * u64, counts [ncols][cap] u64, min_count [ncols] u64 (rows holding INT64_MIN, whose bit pattern marks a free slot),
+ * ndistinct [ncols] i32, overflow [ncols] i32 for callers that merge the maps of several GPUs).  A column with more
+ * than 3/4 cap distinct values sets overflow[c]: call again with a larger cap.  modes [ncols], mode_counts [ncols]. */
+int tmog_integral_mode_scratch_bytes(int ncols, int64_t cap, size_t* bytes);
+int tmog_integral_mode_layout(int ncols, int64_t cap, size_t* offsets5);
+int tmog_integral_mode_dev(const int64_t* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n, int ncols,
+                           int64_t cap, void* scratch, size_t scratch_bytes, int64_t* modes, uint64_t* mode_counts,
+                           void* stream);
+
+/* The fused statistics scan and the transform of tmog_real_* over int64 columns (`i.value.getOrElse(m).toDouble`,
+ * IntegralVectorizer.scala:103-113): values are converted to double as they are read.  Same arguments, scratch
+ * (tmog_real_fit_scratch_bytes) and partials layout; finish with tmog_real_finish_with_fills (fills = the modes, or
+ * the constant of setFillWithConstant). */
+int tmog_integral_pilot_shift_dev(const int64_t* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                  const double* label, int64_t n, int ncols, double* shifts, void* stream);
+int tmog_integral_fit_partials_dev(const int64_t* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                   const double* label, int64_t n, int ncols, const double* shifts, void* scratch,
+                                   size_t scratch_bytes, double* partials, void* stream);
+int tmog_integral_transform_dev(const int64_t* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n,
+                                int ncols, const double* fills, int track_nulls, double* out, int64_t out_ld,
+                                int64_t out_col0, void* stream);
+int tmog_integral_transform_select_dev(const int64_t* values, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n,
+                                       int ncols, const double* fills, int track_nulls, const uint64_t* keep_mask,
+                                       int nkeep, double* out, int64_t out_ld, int64_t out_col0, void* stream);
 
 /* ------------------------------------------------------------------------------------------------------------------
  * SanityChecker over a materialised dense OPVector block (row-major f64, row stride ld, d feature columns)

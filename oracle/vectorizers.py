@@ -83,6 +83,33 @@ def real_vectorizer_transform(columns: Sequence[Sequence[Optional[float]]], fill
     return out
 
 
+def mode_seq_null_int(columns: Sequence[Sequence[Optional[int]]]) -> List[int]:
+    """SequenceAggregators.ModeSeqNullInt (utils/src/main/scala/com/salesforce/op/utils/spark/SequenceAggregators.scala
+    :100-131): per column the value -> count map of the non-null rows; finish = minBy(-count, value), 0 if empty."""
+    out = []
+    for col in columns:
+        m: Dict[int, int] = {}
+        for v in col:
+            if v is not None:
+                m[int(v)] = m.get(int(v), 0) + 1
+        out.append(min(m.items(), key=lambda kv: (-kv[1], kv[0]))[0] if m else 0)
+    return out
+
+
+def integral_vectorizer_fit(columns: Sequence[Sequence[Optional[int]]], fill_with_mode: bool = False,
+                            fill_value: int = 0) -> List[int]:
+    """IntegralVectorizer.fitFn (core/src/main/scala/com/salesforce/op/stages/impl/feature/IntegralVectorizer.scala
+    :81-90): withConstant defaults to true."""
+    return mode_seq_null_int(columns) if fill_with_mode else [int(fill_value)] * len(columns)
+
+
+def integral_vectorizer_transform(columns: Sequence[Sequence[Optional[int]]], fill_values: Sequence[int],
+                                  track_nulls: bool = True) -> np.ndarray:
+    """IntegralVectorizerModel.transformFn :103-113: value-or-fill .toDouble, [v, isNull] interleaved."""
+    cols = [[None if v is None else float(int(v)) for v in c] for c in columns]
+    return real_vectorizer_transform(cols, [float(int(m)) for m in fill_values], track_nulls)
+
+
 def numeric_metadata(names: Sequence[str], type_name: str, track_nulls: bool) -> List[ColumnMeta]:
     """VectorizerDefaults.vectorMetadata, Transmogrifier.scala:378-384"""
     cols: List[ColumnMeta] = []

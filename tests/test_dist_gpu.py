@@ -38,7 +38,10 @@ def _make_data(n):
           for i in range(n)]
     # "the the ..." in every row: a hashed bucket met twice or more in all rows (column minimum 2)
     t2 = ["zq zq " * int(rng.integers(1, 3)) + words[int(rng.integers(150))] for _ in y]
-    return {"b0": (F.BINARY, b0), "p0": (F.PICKLIST, p0), "r0": (F.REAL, r0), "nn": (F.REALNN, nn), "t0": (F.TEXT, t0),
+    # an Integral column whose mode differs between the two shards (5 on the first rows, 2 on the rest; 2 overall)
+    i0 = [opt(int(5 if (i < n // 3 and rng.random() < 0.6) else rng.integers(0, 4) if rng.random() < 0.5 else 2), 0.1)
+          for i in range(n)]
+    return {"i0": (F.INTEGRAL, i0), "b0": (F.BINARY, b0), "p0": (F.PICKLIST, p0), "r0": (F.REAL, r0), "nn": (F.REALNN, nn), "t0": (F.TEXT, t0),
             "t1": (F.TEXT, t1), "t2": (F.TEXT, t2), "y": (F.REALNN, y.tolist())}, y
 
 
@@ -62,7 +65,7 @@ def _worker(rank, size, port, q):
         FB = F.FeatureBuilder
         feats = [FB.Text("t0").asPredictor(), FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(),
                  FB.RealNN("nn").asPredictor(), FB.PickList("p0").asPredictor(), FB.Text("t1").asPredictor(),
-                 FB.Text("t2").asPredictor()]
+                 FB.Text("t2").asPredictor(), FB.Integral("i0").asPredictor()]
         label = FB.RealNN("y").asResponse()
         checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
                                     sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
@@ -71,6 +74,8 @@ def _worker(rank, size, port, q):
         # oracle on the whole dataset
         col = lambda k: data[k][1]   # noqa: E731
         xb = V.binary_vectorizer_transform([col("b0")])
+        modes = V.integral_vectorizer_fit([col("i0")], fill_with_mode=True)
+        xi = V.integral_vectorizer_transform([col("i0")], modes, True)
         tops = V.pivot_fit([col("p0")], 20, 10, True)
         xp = V.pivot_transform([col("p0")], tops, True, True)
         fills = V.real_vectorizer_fit([col("r0")])
@@ -81,8 +86,9 @@ def _worker(rank, size, port, q):
         assert methods == ["Hash", "Pivot", "Hash"]
         xt = V.smart_text_transform(tcols, tnames, methods, ttops, num_features=512)
         xo, metas = V.combine(
-            [xb, xp, xr, xn, xt],
-            [V.numeric_metadata(["b0"], "Binary", True), V.pivot_metadata(["p0"], "PickList", tops, True),
+            [xb, xi, xp, xr, xn, xt],
+            [V.numeric_metadata(["b0"], "Binary", True), V.numeric_metadata(["i0"], "Integral", True),
+             V.pivot_metadata(["p0"], "PickList", tops, True),
              V.numeric_metadata(["r0"], "Real", True), V.numeric_metadata(["nn"], "RealNN", False),
              V.smart_text_metadata(tnames, "Text", methods, ttops, 512, True)])
         p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,

@@ -338,3 +338,21 @@ def test_fraction():
     p = S.SanityParams()
     assert S.fraction(p, 500) == 1.0 and S.fraction(p, 10_000_000) == 0.1
     assert S.fraction(S.SanityParams(check_sample=0.5), 100_000) == 0.5
+
+
+def test_integral_vectorizer_golden():
+    # IntegralVectorizerTest.scala:48-56 (data), :93-118 (constant fill 3), :120-149 (mode: 4, 2, 1 -- the tie between
+    # 1 and 2 in inC goes to the smaller value -- and 0 for the all-null inD)
+    a, b, c, d = [4, 4, 2, None, None], [2, None, 4, 2, None], [2, 1, 1, 2, None], [None] * 5
+    assert V.mode_seq_null_int([a, b, c, d]) == [4, 2, 1, 0]
+    const = V.integral_vectorizer_fit([a, b, c, d], fill_with_mode=False, fill_value=3)
+    got = V.integral_vectorizer_transform([a, b, c, d], const, track_nulls=False)
+    assert got.tolist() == [[4.0, 2.0, 2.0, 3.0], [4.0, 3.0, 1.0, 3.0], [2.0, 4.0, 1.0, 3.0], [3.0, 2.0, 2.0, 3.0],
+                            [3.0, 3.0, 3.0, 3.0]]
+    mode = V.integral_vectorizer_fit([a, b, c, d], fill_with_mode=True)
+    got = V.integral_vectorizer_transform([a, b, c, d], mode, track_nulls=False)
+    assert got.tolist() == [[4.0, 2.0, 2.0, 0.0], [4.0, 2.0, 1.0, 0.0], [2.0, 4.0, 1.0, 0.0], [4.0, 2.0, 2.0, 0.0],
+                            [4.0, 2.0, 1.0, 0.0]]
+    # with null tracking: [value, isNull] interleaved (IntegralVectorizerTest.scala:151-180)
+    got = V.integral_vectorizer_transform([a, b], [4, 2], track_nulls=True)
+    assert got[3].tolist() == [4.0, 1.0, 2.0, 0.0] and got[4].tolist() == [4.0, 1.0, 2.0, 1.0]

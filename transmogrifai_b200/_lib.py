@@ -91,6 +91,14 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_pearson_from_cov": [_int, _dbl, _p, _p, _dbl, _p],
     "tmog_sanity_decide": [_int, _p, _p, _p, _int, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "tmog_real_transform_select_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _int, _p, _int, _p, _i64, _i64, _p],
+    "tmog_real_finish_with_fills": [_p, _p, _int, _p, _int, _p, _p, _p, _p, _p, _p, _p],
+    "tmog_integral_mode_scratch_bytes": [_int, _i64, _p],
+    "tmog_integral_mode_layout": [_int, _i64, _p],
+    "tmog_integral_mode_dev": [_p, _i64, _p, _i64, _i64, _int, _i64, _p, _sz, _p, _p, _p],
+    "tmog_integral_pilot_shift_dev": [_p, _i64, _p, _i64, _p, _i64, _int, _p, _p],
+    "tmog_integral_fit_partials_dev": [_p, _i64, _p, _i64, _p, _i64, _int, _p, _p, _sz, _p, _p],
+    "tmog_integral_transform_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _int, _p, _i64, _i64, _p],
+    "tmog_integral_transform_select_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _int, _p, _int, _p, _i64, _i64, _p],
     "tmog_binary_transform_select_dev": [_p, _i64, _p, _i64, _i64, _int, _int, _int, _p, _int, _p, _i64, _i64, _p],
     "tmog_ctx_create": [_int, C.POINTER(_p)],
     "tmog_ctx_destroy": [_p],

@@ -77,7 +77,7 @@ def to_host(tensors, piece_bytes: Optional[int] = None) -> list:
 class NumericBlock:
     names: List[str]
     type_name: str
-    values: torch.Tensor                 # [ncols, ld] float64 (Real, RealNN) or uint8 (Binary)
+    values: torch.Tensor                 # [ncols, ld] float64 (Real, RealNN), uint8 (Binary) or int64 (Integral)
     valid: Optional[torch.Tensor]        # [ncols, ldv] int64 bitmap words, or None (no nulls)
     n: int
 
@@ -113,9 +113,9 @@ class NumericBlock:
     def from_lists(names: Sequence[str], type_name: str, columns: Sequence[Sequence], pin: bool = True
                    ) -> "NumericBlock":
         n = len(columns[0]) if columns else 0
-        binary = type_name == F.BINARY
+        binary, integral = type_name == F.BINARY, type_name == F.INTEGRAL
         ld = round_up(max(n, 1), 16 if binary else 2)
-        vals = np.zeros((len(columns), ld), dtype=np.uint8 if binary else np.float64)
+        vals = np.zeros((len(columns), ld), dtype=np.uint8 if binary else np.int64 if integral else np.float64)
         ok = np.zeros((len(columns), n), dtype=bool)
         for j, col in enumerate(columns):
             if len(col) != n:
@@ -123,7 +123,7 @@ class NumericBlock:
             for i, v in enumerate(col):
                 if v is not None:
                     ok[j, i] = True
-                    vals[j, i] = (1 if v else 0) if binary else float(v)
+                    vals[j, i] = (1 if v else 0) if binary else int(v) if integral else float(v)
         if type_name == F.REALNN and not ok.all():
             raise ValueError("None.get: a RealNN feature holds a null")   # RealNNVectorizer.scala:53
         valid = None if ok.all() else torch.from_numpy(pack_validity(ok))

@@ -209,7 +209,8 @@ struct FitChunkIt {  // the sub-tiles of one consumer warp, in the order it work
     int nfull;       // sub-tiles of this super-tile
 };
 
-template <int FT_SUB, int FT_SUBS, int FT_WARPS, int FT_STAGES>
+// INT64: the value columns hold int64 (Integral features), converted to double as they are read; the label is f64.
+template <int FT_SUB, int FT_SUBS, int FT_WARPS, int FT_STAGES, bool INT64>
 __global__ void __launch_bounds__((FT_WARPS + 1) * 32, 1)
 real_fit_tma_kernel(const double* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid, int64_t ldv,
                     const double* __restrict__ label, int64_t n, int ncols, const double* __restrict__ shifts,
@@ -372,8 +373,12 @@ real_fit_tma_kernel(const double* __restrict__ values, int64_t ld, const uint64_
 #pragma unroll
                 for (int k = 0; k < PAIRS; ++k) {
                     const int p = (k + lane) & (PAIRS - 1);
-                    const double2 x = xb[p];
+                    double2 x = xb[p];
                     const double2 y = yb[p];
+                    if (INT64 && cur.c < ncols) {
+                        x.x = (double)__double_as_longlong(x.x);
+                        x.y = (double)__double_as_longlong(x.y);
+                    }
                     acc_add_lean(a, (wr >> (2 * k)) & 1u, x.x, s, y.x);
                     acc_add_lean(b, (wr >> (2 * k + 1)) & 1u, x.y, s, y.y);
                 }
@@ -417,7 +422,8 @@ real_fit_tma_kernel(const double* __restrict__ values, int64_t ld, const uint64_
                 for (int64_t r = rows_full + lane; r < n; r += 32) {
                     const bool v = vcol ? ((vcol[r >> 6] >> (r & 63)) & 1ull) != 0 : true;
                     tc += v;
-                    acc_add(a, v, col[r], sc, label[r] - sy);
+                    const double xv = (INT64 && !is_label) ? (double)__double_as_longlong(col[r]) : col[r];
+                    acc_add(a, v, xv, sc, label[r] - sy);
                 }
                 const double sd = warp_sum(a.sd), sdd = warp_sum(a.sdd), sde = warp_sum(a.sde), se = warp_sum(a.se);
                 const double mn = warp_min(a.mn), mx = warp_max(a.mx);
@@ -446,7 +452,7 @@ real_fit_tma_kernel(const double* __restrict__ values, int64_t ld, const uint64_
     }
 }
 
-template <int SUB, int SUBS, int WARPS, int STAGES>
+template <int SUB, int SUBS, int WARPS, int STAGES, bool INT64>
 static int launch_fit_tma(const double* values, int64_t ld, const uint64_t* valid, int64_t ldv, const double* label,
                           int64_t n, int ncols, const double* shifts, double* scratch, int nblocks, cudaStream_t st,
                           bool* fits) {
@@ -455,7 +461,7 @@ static int launch_fit_tma(const double* values, int64_t ld, const uint64_t* vali
         8 * (size_t)(WARPS * STAGES + 6);
     *fits = smem <= 227 * 1024;
     if (!*fits) return TMOG_OK;
-    auto kern = real_fit_tma_kernel<SUB, SUBS, WARPS, STAGES>;
+    auto kern = real_fit_tma_kernel<SUB, SUBS, WARPS, STAGES, INT64>;
     TMOG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<nblocks, (WARPS + 1) * 32, smem, st>>>(values, ld, valid, ldv, label, n, ncols, shifts, scratch);
     return TMOG_OK;
@@ -492,7 +498,8 @@ real_fit_reduce_kernel(const double* __restrict__ scratch, int nblocks, int ncol
 
 __global__ void __launch_bounds__(128)
 real_pilot_shift_kernel(const double* __restrict__ values, int64_t ld, const uint64_t* __restrict__ valid, int64_t ldv,
-                        const double* __restrict__ label, int64_t n, int ncols, double* __restrict__ shifts) {
+                        const double* __restrict__ label, int64_t n, int ncols, double* __restrict__ shifts,
+                        int values_are_int64) {
     __shared__ double ssum[4];
     __shared__ unsigned scnt[4];
     const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -504,7 +511,7 @@ real_pilot_shift_kernel(const double* __restrict__ values, int64_t ld, const uin
     unsigned cnt = 0;
     for (int r = tid; r < rows; r += 128) {
         const bool v = vcol ? ((vcol[r >> 6] >> (r & 63)) & 1ull) != 0 : true;
-        const double x = col[r];
+        const double x = (values_are_int64 && !is_label) ? (double)__double_as_longlong(col[r]) : col[r];
         if (v && isfinite(x)) {
             s += x;
             ++cnt;
@@ -794,7 +801,7 @@ extern "C" int tmog_real_pilot_shift_dev(const double* values, int64_t ld, const
     if (int rc = check_columns(values, ld, valid, ldv, n, ncols, 8)) return rc;
     TMOG_REQUIRE(shifts != nullptr && (label != nullptr || n == 0), "shifts / label is NULL");
     real_pilot_shift_kernel<<<ncols + 1, 128, 0, (cudaStream_t)stream>>>(values, ld, valid, ldv, label, n, ncols,
-                                                                         shifts);
+                                                                         shifts, 0);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }
@@ -824,7 +831,7 @@ extern "C" int tmog_real_fit_partials_dev(const double* values, int64_t ld, cons
     // 8 KB buffers 1.45 ms, 12 warps x 3 buffers 1.39 ms, super-tiles of 2048 rows 1.37 ms.
     bool fits = false;
     int nblocks = sm_count();
-    if (int rc = launch_fit_tma<512, 8, 16, 2>(values, ld, valid, ldv, label, n, ncols, shifts,
+    if (int rc = launch_fit_tma<512, 8, 16, 2, false>(values, ld, valid, ldv, label, n, ncols, shifts,
                                                static_cast<double*>(scratch), nblocks, st, &fits))
         return rc;
     if (!fits) {
@@ -858,10 +865,10 @@ extern "C" int tmog_real_partials_merge(double* acc, const double* other, int nc
     return TMOG_OK;
 }
 
-extern "C" int tmog_real_finish(const double* partials, const double* shifts, int ncols, int fill_with_mean,
-                                double fill_const, int track_nulls, double* fills, double* mean, double* variance,
-                                double* mn, double* mx, double* cov_label, double* label_stats,
-                                double* null_label_sum) {
+static int real_finish(const double* partials, const double* shifts, int ncols, int fill_with_mean,
+                       double fill_const, const double* fill_in, int track_nulls, double* fills, double* mean,
+                       double* variance, double* mn, double* mx, double* cov_label, double* label_stats,
+                       double* null_label_sum) {
     TMOG_REQUIRE(partials != nullptr && shifts != nullptr && ncols >= 0, "bad arguments");
     const double* L = partials + ncols * NS;
     const double n = L[7];
@@ -884,7 +891,7 @@ extern "C" int tmog_real_finish(const double* partials, const double* shifts, in
         const double z = n - v;
         const double s = shifts[c];
         // SequenceAggregators.scala:84 -- s / c if c > 0 else s (= 0.0)
-        const double fill = fill_with_mean ? (v > 0 ? s + sd / v : 0.0) : fill_const;
+        const double fill = fill_in ? fill_in[c] : (fill_with_mean ? (v > 0 ? s + sd / v : 0.0) : fill_const);
         if (fills) fills[c] = fill;
         // filled column f = x (valid) | fill (null)
         const double mu = n > 0 ? (fill_with_mean ? fill : (v * s + sd + z * fill) / n) : 0.0;
@@ -909,6 +916,23 @@ extern "C" int tmog_real_finish(const double* partials, const double* shifts, in
         }
     }
     return TMOG_OK;
+}
+
+extern "C" int tmog_real_finish(const double* partials, const double* shifts, int ncols, int fill_with_mean,
+                                double fill_const, int track_nulls, double* fills, double* mean, double* variance,
+                                double* mn, double* mx, double* cov_label, double* label_stats,
+                                double* null_label_sum) {
+    return real_finish(partials, shifts, ncols, fill_with_mean, fill_const, nullptr, track_nulls, fills, mean, variance,
+                       mn, mx, cov_label, label_stats, null_label_sum);
+}
+
+extern "C" int tmog_real_finish_with_fills(const double* partials, const double* shifts, int ncols,
+                                           const double* fill_values, int track_nulls, double* mean, double* variance,
+                                           double* mn, double* mx, double* cov_label, double* label_stats,
+                                           double* null_label_sum) {
+    TMOG_REQUIRE(fill_values != nullptr || ncols == 0, "fill_values is NULL");
+    return real_finish(partials, shifts, ncols, 0, 0.0, fill_values, track_nulls, nullptr, mean, variance, mn, mx,
+                       cov_label, label_stats, null_label_sum);
 }
 
 template <typename T>
@@ -994,6 +1018,62 @@ extern "C" int tmog_binary_transform_select_dev(const uint8_t* values, int64_t l
     TMOG_REQUIRE(keep_mask != nullptr && nkeep >= 0, "keep_mask is NULL");
     return launch_transform<uint8_t>(values, ld, valid, ldv, n, ncols, nullptr, fill_value ? 1.0 : 0.0, track_nulls,
                                      out, out_ld, out_col0, stream, keep_mask, nkeep);
+}
+
+// ---- Integral columns (int64): the same kernels, values converted to double as they are read ---------------------
+extern "C" int tmog_integral_pilot_shift_dev(const int64_t* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                             const double* label, int64_t n, int ncols, double* shifts,
+                                             void* stream) {
+    if (int rc = check_columns(values, ld, valid, ldv, n, ncols, 8)) return rc;
+    TMOG_REQUIRE(shifts != nullptr && (label != nullptr || n == 0), "shifts / label is NULL");
+    real_pilot_shift_kernel<<<ncols + 1, 128, 0, (cudaStream_t)stream>>>(reinterpret_cast<const double*>(values), ld,
+                                                                         valid, ldv, label, n, ncols, shifts, 1);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_integral_fit_partials_dev(const int64_t* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                              const double* label, int64_t n, int ncols, const double* shifts,
+                                              void* scratch, size_t scratch_bytes, double* partials, void* stream) {
+    if (int rc = check_columns(values, ld, valid, ldv, n, ncols, 8)) return rc;
+    TMOG_REQUIRE(label != nullptr || n == 0, "label is NULL");
+    TMOG_REQUIRE(aligned16(label), "label must be 16-byte aligned");
+    TMOG_REQUIRE(shifts != nullptr && partials != nullptr, "shifts / partials is NULL");
+    const size_t need = sizeof(double) * (size_t)fit_grid() * (size_t)(ncols + 1) * NS;
+    if (scratch == nullptr || scratch_bytes < need) {
+        set_error("scratch too small: %zu bytes given, %zu needed (tmog_real_fit_scratch_bytes)", scratch_bytes, need);
+        return TMOG_ENOMEM;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    bool fits = false;
+    const int nblocks = sm_count();
+    if (int rc = launch_fit_tma<512, 8, 16, 2, true>(reinterpret_cast<const double*>(values), ld, valid, ldv, label, n,
+                                                     ncols, shifts, static_cast<double*>(scratch), nblocks, st, &fits))
+        return rc;
+    TMOG_REQUIRE(fits, "too many columns for one fit call (%d): split the column block", ncols);
+    TMOG_LAUNCH_CHECK();
+    real_fit_reduce_kernel<<<ncols + 1, 32, 0, st>>>(static_cast<const double*>(scratch), nblocks, ncols, n,
+                                                     partials);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_integral_transform_dev(const int64_t* values, int64_t ld, const uint64_t* valid, int64_t ldv,
+                                           int64_t n, int ncols, const double* fills, int track_nulls, double* out,
+                                           int64_t out_ld, int64_t out_col0, void* stream) {
+    TMOG_REQUIRE(fills != nullptr || valid == nullptr, "fills is NULL but the columns are nullable");
+    return launch_transform<long long>(reinterpret_cast<const long long*>(values), ld, valid, ldv, n, ncols, fills, 0.0,
+                                       track_nulls, out, out_ld, out_col0, stream);
+}
+
+extern "C" int tmog_integral_transform_select_dev(const int64_t* values, int64_t ld, const uint64_t* valid,
+                                                  int64_t ldv, int64_t n, int ncols, const double* fills,
+                                                  int track_nulls, const uint64_t* keep_mask, int nkeep, double* out,
+                                                  int64_t out_ld, int64_t out_col0, void* stream) {
+    TMOG_REQUIRE(fills != nullptr || valid == nullptr, "fills is NULL but the columns are nullable");
+    TMOG_REQUIRE(keep_mask != nullptr && nkeep >= 0, "keep_mask is NULL");
+    return launch_transform<long long>(reinterpret_cast<const long long*>(values), ld, valid, ldv, n, ncols, fills, 0.0,
+                                       track_nulls, out, out_ld, out_col0, stream, keep_mask, nkeep);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

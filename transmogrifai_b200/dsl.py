@@ -29,6 +29,7 @@ class TransmogrifierDefaults:
     CleanText = True
     BinaryFreq = False
     FillWithMean = True
+    FillWithMode = True
     TrackNulls = True
     TrackTextLen = False
     MaxCategoricalCardinality = 30
@@ -46,6 +47,11 @@ def _vectorizer_for(type_name: str, feats: List[F.Feature], d=TransmogrifierDefa
         return st.getOutput()
     if type_name == F.REALNN:
         return RealNNVectorizer().setInput(*feats).getOutput()
+    if type_name == F.INTEGRAL:                      # Transmogrifier.scala:258-262
+        from .stages.integral import IntegralVectorizer
+        st = IntegralVectorizer().setInput(*feats).setTrackNulls(d.TrackNulls)
+        st = st.setFillWithMode() if d.FillWithMode else st.setFillWithConstant(d.FillValue)
+        return st.getOutput()
     if type_name in (F.PICKLIST, F.MULTIPICKLIST, F.TEXT, F.TEXTAREA):
         from .stages.text import vectorizer_for_text_type
         return vectorizer_for_text_type(type_name, feats, d)

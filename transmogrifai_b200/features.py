@@ -10,14 +10,14 @@ import itertools
 from dataclasses import dataclass, field
 from typing import Optional, Tuple
 
-REAL, REALNN, BINARY = "Real", "RealNN", "Binary"
+REAL, REALNN, BINARY, INTEGRAL = "Real", "RealNN", "Binary", "Integral"
 PICKLIST, MULTIPICKLIST = "PickList", "MultiPickList"
 TEXT, TEXTAREA = "Text", "TextArea"
 OPVECTOR = "OPVector"
 
-NUMERIC_TYPES = (REAL, REALNN, BINARY)
+NUMERIC_TYPES = (REAL, REALNN, BINARY, INTEGRAL)
 TEXT_TYPES = (TEXT, TEXTAREA)
-ALL_TYPES = (REAL, REALNN, BINARY, PICKLIST, MULTIPICKLIST, TEXT, TEXTAREA, OPVECTOR)
+ALL_TYPES = (REAL, REALNN, BINARY, INTEGRAL, PICKLIST, MULTIPICKLIST, TEXT, TEXTAREA, OPVECTOR)
 
 _uid_counter = itertools.count(1)
 
@@ -78,6 +78,7 @@ class FeatureBuilder:
     Real = staticmethod(lambda name: _Builder(name, REAL))
     RealNN = staticmethod(lambda name: _Builder(name, REALNN))
     Binary = staticmethod(lambda name: _Builder(name, BINARY))
+    Integral = staticmethod(lambda name: _Builder(name, INTEGRAL))
     PickList = staticmethod(lambda name: _Builder(name, PICKLIST))
     MultiPickList = staticmethod(lambda name: _Builder(name, MULTIPICKLIST))
     Text = staticmethod(lambda name: _Builder(name, TEXT))

@@ -76,7 +76,9 @@ def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str, after_launc
                    MAX_LABEL_CLASSES, ids.data_ptr(), counts.data_ptr(), R.stream())
             if after_launch is not None:
                 after_launch(ids)
-            out = (union, D.allreduce_sum(counts[:len(union)].cpu().numpy()), ids)
+            g_counts = counts[:len(union)].clone()
+            torch.distributed.all_reduce(g_counts)            # summed on the device: one copy back instead of three
+            out = (union, g_counts.cpu().numpy(), ids)
     else:
         out = (local, counts[:k].cpu().numpy(), ids) if k > 0 else (None, None, ids)
     cache[name] = out
@@ -297,6 +299,7 @@ def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_n
     n, ncols = block.n, len(block.names)
     w_full = ncols * (2 if track_nulls else 1)
     binary = block.values.dtype == torch.uint8
+    integral = block.values.dtype == torch.int64
     kp = None
     w = w_full
     if keep is not None:
@@ -311,7 +314,16 @@ def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_n
             bits = np.zeros(round_up(w_full, 64), dtype=np.uint8)
             bits[kp] = 1
             d_keep = torch.from_numpy(np.packbits(bits, bitorder="little").view("<i8").copy()).cuda()
-        if binary:
+        if integral:
+            d_fills = None if fills is None else torch.from_numpy(np.asarray(fills, dtype=np.float64)).cuda()
+            if kp is None:
+                L.call("tmog_integral_transform_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
+                       n, ncols, R.ptr(d_fills), int(track_nulls), out.data_ptr(), out.shape[1], 0, R.stream())
+            else:
+                L.call("tmog_integral_transform_select_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid),
+                       block.ldv, n, ncols, R.ptr(d_fills), int(track_nulls), d_keep.data_ptr(), w, out.data_ptr(),
+                       out.shape[1], 0, R.stream())
+        elif binary:
             if kp is None:
                 L.call("tmog_binary_transform_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
                        n, ncols, int(fill_value), int(track_nulls), out.data_ptr(), out.shape[1], 0, R.stream())
@@ -329,7 +341,7 @@ def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_n
                        block.ldv, n, ncols, R.ptr(d_fills), int(track_nulls), d_keep.data_ptr(), w, out.data_ptr(),
                        out.shape[1], 0, R.stream())
         return out[:, :w]
-    if binary:
+    if binary or integral:
         dev = block.to("cuda")
         return _transform_numeric(dev, fills, track_nulls, chunk_rows, fill_value, keep).cpu()
     out = torch.empty((n, w), dtype=torch.float64, pin_memory=True)

@@ -209,7 +209,11 @@ class SanityChecker(OpEstimator):
     def fit(self, batch: ColumnarBatch) -> "SanityCheckerModel":
         label_f, vec_f = self.inN
         vec = batch.vectors[vec_f.name]
-        n = int(D.allreduce_sum(np.array([batch.n], dtype=np.int64))[0])    # rows over all ranks
+        sidecar = vec.stats
+        if sidecar is not None and sidecar.label.name == label_f.name:
+            n = int(sidecar.label.n)                                          # rows over all ranks, counted by the fit scans
+        else:
+            n = int(D.allreduce_sum(np.array([batch.n], dtype=np.int64))[0])
         if n <= 0:
             raise ValueError("requirement failed: Sample size cannot be zero")
         frac = self.fraction(n)
