@@ -592,7 +592,10 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
             int tbits = 6;
             while (tbits < 31 && (1ll << tbits) < 2 * bytes_bound && (1 << tbits) < T) ++tbits;
             const int tsize = 1 << tbits;
-            const int dist_limit = tsize - (tsize >> 2);        // the table never gets fuller than 3/4 (+ 32)
+            // the table never gets fuller than 7/8 (+ 32): linear probing stays short while it fills (about four
+            // probes per insert on average up to that load), and rows of ~850 distinct buckets still fit the
+            // 1024-slot table of the level that runs 24 warps per SM
+            const int dist_limit = tsize - (tsize >> 3);
             int ndist = 0;
             bool row_bad = false;
 
@@ -1361,8 +1364,8 @@ static int th_launch(const ThArgs& a, int level, int max_token_bound) {
     return TMOG_OK;
 }
 
-// Three launches, by the size of the row's table: rows whose text is short enough for about 768 distinct buckets run
-// with 24 warps per SM, rows up to about 1536 with 16 warps per SM, the rest (and whatever overflowed a smaller table)
+// Three launches, by the size of the row's table: rows whose text is short enough for about 900 distinct buckets run
+// with 24 warps per SM, rows up to about 1800 with 16 warps per SM, the rest (and whatever overflowed a smaller table)
 // with 64-bit slots in most of the shared memory of an SM.  Packed 32-bit slots need >= 8 bits left for the count.
 template <bool SPARSE_OUT>
 static int th_run(ThArgs& a) {
@@ -1372,12 +1375,12 @@ static int th_run(ThArgs& a) {
     while ((1ll << key_bits) - 1 <= max_key) ++key_bits;
     if (key_bits <= 24) {
         a.p.count_bits = 32 - key_bits;
-        if (int rc = th_launch<unsigned, 1024, 2048, 12, SPARSE_OUT>(a, 0, 3072)) return rc;
-        if (int rc = th_launch<unsigned, 2048, 2048, 8, SPARSE_OUT>(a, 1, 6144)) return rc;
+        if (int rc = th_launch<unsigned, 1024, 2048, 12, SPARSE_OUT>(a, 0, 3584)) return rc;
+        if (int rc = th_launch<unsigned, 2048, 2048, 8, SPARSE_OUT>(a, 1, 7168)) return rc;
     } else {
         a.p.count_bits = 32;
-        if (int rc = th_launch<unsigned long long, 512, 2048, 12, SPARSE_OUT>(a, 0, 1536)) return rc;
-        if (int rc = th_launch<unsigned long long, 1024, 2048, 8, SPARSE_OUT>(a, 1, 3072)) return rc;
+        if (int rc = th_launch<unsigned long long, 512, 2048, 12, SPARSE_OUT>(a, 0, 1792)) return rc;
+        if (int rc = th_launch<unsigned long long, 1024, 2048, 8, SPARSE_OUT>(a, 1, 3584)) return rc;
     }
     a.p.count_bits = 32;
     return th_launch<unsigned long long, 16384, 4096, 1, SPARSE_OUT>(a, 2, 0x7fffffff);
