@@ -254,7 +254,7 @@ int tmog_text_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uin
  * `lengthStdDev < minLengthStdDev` (SmartTextVectorizer.scala:113), which never holds at the default minLengthStdDev = 0,
  * so such a column needs nothing further from its cells and they are not read: non-ASCII bytes in them are reported
  * by whichever call vectorizes the column afterwards (tmog_text_hash_*_dev, tmog_text_codes_dev: flags[0]).  len_sum
- * then covers the cells seen before the cap only. */
+ * and nonnull then cover the cells seen before the cap only. */
 int tmog_text_stats_values_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* class_ids, int nclasses,
                         int clean_text, int slots, int max_distinct, void* tables, int32_t* flags, void* stream);
 

@@ -312,7 +312,8 @@ def test_text_stats_values_entry_point_matches_the_full_scan():
     assert np.array_equal(full[0], vals[0])                                   # under the cap: everything agrees
     nd = [int(t[1, tail:tail + 4].view(np.int32)[0]) for t in (full, vals)]
     assert nd[0] > cap and nd[1] > cap
-    assert np.array_equal(full[1, tail + 24:tail + 32], vals[1, tail + 24:tail + 32])       # non-null cells
+    nn_full, nn_vals = (int(t[1, tail + 24:tail + 32].view(np.uint64)[0]) for t in (full, vals))
+    assert 0 < nn_vals <= nn_full                                             # the capped column is not scanned on
     ls_full, ls_vals = full[1, tail + 8:tail + 24].view(np.uint64), vals[1, tail + 8:tail + 24].view(np.uint64)
     assert (ls_vals <= ls_full).all() and ls_full[0] > 0
 

@@ -248,15 +248,17 @@ text_stats_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
     unsigned long long lsum = 0, lsq = 0, nn = 0;
     bool non_ascii = false;
     for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        // Past the cardinality cap nothing more is recorded for the column but the lengths, and those only matter to
+        // a positive minLengthStdDev (SmartTextVectorizer.scala:113).  Without it the scan of the column ends here:
+        // whoever vectorizes the column reads every cell anyway and reports non-ASCII bytes then
+        // (tmog_text_hash_*_dev, tmog_text_codes_dev).
+        const bool capped = *t.ndistinct > max_distinct;
+        if (capped && !want_lengths) break;
         if (!cell_valid(tc, r)) continue;
         const int64_t a = tc.offsets[r], b = tc.offsets[r + 1];
         int m;
-        if (*t.ndistinct > max_distinct) {
-            // past the cardinality cap nothing more is recorded for the column but the lengths, and those only
-            // matter to a positive minLengthStdDev (SmartTextVectorizer.scala:113)
-            // -- and without it the cell is not read at all: whoever vectorizes the column reads every cell anyway
-            // and reports non-ASCII bytes then (tmog_text_hash_*_dev, tmog_text_codes_dev)
-            m = want_lengths ? clean_length_cell(tc.data + a, b - a, clean != 0, non_ascii) : 0;
+        if (capped) {
+            m = clean_length_cell(tc.data + a, b - a, clean != 0, non_ascii);
         } else {
             unsigned long long h;
             clean_hash_cell(tc.data + a, b - a, clean != 0, h, m, non_ascii);
@@ -1364,6 +1366,9 @@ static int th_launch(const ThArgs& a, int level, int max_token_bound) {
     return TMOG_OK;
 }
 
+// A row is sent to a level by an upper bound of its tokens (half its bytes).  The bound is loose -- ordinary text has
+// a token per 6 to 8 bytes and repeats words -- so a level takes rows whose bound is about five times the distinct
+// buckets its table holds; the few rows that do overflow are redone by the next level.
 // Three launches, by the size of the row's table: rows whose text is short enough for about 900 distinct buckets run
 // with 24 warps per SM, rows up to about 1800 with 16 warps per SM, the rest (and whatever overflowed a smaller table)
 // with 64-bit slots in most of the shared memory of an SM.  Packed 32-bit slots need >= 8 bits left for the count.
@@ -1375,12 +1380,12 @@ static int th_run(ThArgs& a) {
     while ((1ll << key_bits) - 1 <= max_key) ++key_bits;
     if (key_bits <= 24) {
         a.p.count_bits = 32 - key_bits;
-        if (int rc = th_launch<unsigned, 1024, 2048, 12, SPARSE_OUT>(a, 0, 3584)) return rc;
-        if (int rc = th_launch<unsigned, 2048, 2048, 8, SPARSE_OUT>(a, 1, 7168)) return rc;
+        if (int rc = th_launch<unsigned, 1024, 2048, 12, SPARSE_OUT>(a, 0, 4608)) return rc;
+        if (int rc = th_launch<unsigned, 2048, 2048, 8, SPARSE_OUT>(a, 1, 9216)) return rc;
     } else {
         a.p.count_bits = 32;
-        if (int rc = th_launch<unsigned long long, 512, 2048, 12, SPARSE_OUT>(a, 0, 1792)) return rc;
-        if (int rc = th_launch<unsigned long long, 1024, 2048, 8, SPARSE_OUT>(a, 1, 3584)) return rc;
+        if (int rc = th_launch<unsigned long long, 512, 2048, 12, SPARSE_OUT>(a, 0, 2304)) return rc;
+        if (int rc = th_launch<unsigned long long, 1024, 2048, 8, SPARSE_OUT>(a, 1, 4608)) return rc;
     }
     a.p.count_bits = 32;
     return th_launch<unsigned long long, 16384, 4096, 1, SPARSE_OUT>(a, 2, 0x7fffffff);
