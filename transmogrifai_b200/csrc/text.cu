@@ -532,7 +532,7 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
     unsigned* mask = reinterpret_cast<unsigned*>(wbase + L::MASK);
     using Tok = typename L::Tok;
     constexpr int SB = TB <= 2048 ? 11 : 12;            // bits of a buffer position in a token record
-    static_assert(TB == 2048 || TB == 4096, "token records are packed for these two buffer sizes");
+    static_assert(TB == 1024 || TB == 2048 || TB == 4096, "token records are packed for these buffer sizes");
     Tok* toks = reinterpret_cast<Tok*>(wbase + L::TOKS);
     unsigned char* wcell = wbase + L::WCELL;
     Slot* table = reinterpret_cast<Slot*>(wbase + L::TABLE);
@@ -1370,7 +1370,7 @@ static int th_launch(const ThArgs& a, int level, int max_token_bound) {
 // a token per 6 to 8 bytes and repeats words -- so a level takes rows whose bound is about five times the distinct
 // buckets its table holds; the few rows that do overflow are redone by the next level.
 // Three launches, by the size of the row's table: rows whose text is short enough for about 900 distinct buckets run
-// with 24 warps per SM, rows up to about 1800 with 16 warps per SM, the rest (and whatever overflowed a smaller table)
+// with 32 warps per SM (a 1 KB text buffer: cells are staged four or five at a time), rows up to about 1800 with 16 warps per SM, the rest (and whatever overflowed a smaller table)
 // with 64-bit slots in most of the shared memory of an SM.  Packed 32-bit slots need >= 8 bits left for the count.
 template <bool SPARSE_OUT>
 static int th_run(ThArgs& a) {
@@ -1380,7 +1380,7 @@ static int th_run(ThArgs& a) {
     while ((1ll << key_bits) - 1 <= max_key) ++key_bits;
     if (key_bits <= 24) {
         a.p.count_bits = 32 - key_bits;
-        if (int rc = th_launch<unsigned, 1024, 2048, 12, SPARSE_OUT>(a, 0, 4608)) return rc;
+        if (int rc = th_launch<unsigned, 1024, 1024, 16, SPARSE_OUT>(a, 0, 4608)) return rc;
         if (int rc = th_launch<unsigned, 2048, 2048, 8, SPARSE_OUT>(a, 1, 9216)) return rc;
     } else {
         a.p.count_bits = 32;
