@@ -239,15 +239,16 @@ __device__ __forceinline__ int ts_insert(const TextStatsTable& t, int slots, int
 
 // one thread per cell (cells are short strings; consecutive threads take consecutive rows of one column)
 __global__ void __launch_bounds__(256)
-text_stats_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, const uint8_t* __restrict__ class_ids,
-                  int nclasses, int clean, int want_lengths, int slots, int max_distinct,
-                  const TextStatsTable* __restrict__ tables, int* __restrict__ flags) {
+text_stats_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t r_begin, int64_t n,
+                  const uint8_t* __restrict__ class_ids, int nclasses, int clean, int want_lengths, int slots,
+                  int max_distinct, const TextStatsTable* __restrict__ tables, int* __restrict__ flags) {
     const int c = blockIdx.y;
     const TextColumn tc = cols[c];
     const TextStatsTable t = tables[c];
     unsigned long long lsum = 0, lsq = 0, nn = 0;
     bool non_ascii = false;
-    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+    for (int64_t r = r_begin + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n;
+         r += (int64_t)gridDim.x * blockDim.x) {
         // Past the cardinality cap nothing more is recorded for the column but the lengths, and those only matter to
         // a positive minLengthStdDev (SmartTextVectorizer.scala:113).  Without it the scan of the column ends here:
         // whoever vectorizes the column reads every cell anyway and reports non-ASCII bytes then
@@ -1262,11 +1263,21 @@ static int text_stats_launch(const int64_t* col_desc, int ncols, int64_t n, cons
     TMOG_CUDA(cudaMemcpyAsync(tables, host.data(), sizeof(TextStatsTable) * ncols, cudaMemcpyHostToDevice, st));
     TMOG_CUDA(cudaStreamSynchronize(st));  // `host` goes out of scope
     if (n == 0) return TMOG_OK;
-    const int gx = (int)std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 4);
-    text_stats_kernel<<<dim3(gx, ncols), 256, 0, st>>>(reinterpret_cast<const TextColumn*>(col_desc), ncols, n, class_ids,
-                                                       nclasses, clean_text, want_lengths, slots, max_distinct,
-                                                       static_cast<const TextStatsTable*>(tables), flags);
+    // The first rows go through a small launch of their own: a free-text column passes the cardinality cap within its
+    // first few hundred cells, and the threads of the main launch then see that at once -- instead of a whole wave of
+    // them hammering a table of a few hundred slots with their first cells.
+    const int64_t pilot = std::min<int64_t>(n, 4096);
+    text_stats_kernel<<<dim3((unsigned)((pilot + 255) / 256), ncols), 256, 0, st>>>(
+        reinterpret_cast<const TextColumn*>(col_desc), ncols, 0, pilot, class_ids, nclasses, clean_text, want_lengths,
+        slots, max_distinct, static_cast<const TextStatsTable*>(tables), flags);
     TMOG_LAUNCH_CHECK();
+    if (n > pilot) {
+        const int gx = (int)std::min<int64_t>((n - pilot + 255) / 256, (int64_t)sm_count() * 4);
+        text_stats_kernel<<<dim3(gx, ncols), 256, 0, st>>>(
+            reinterpret_cast<const TextColumn*>(col_desc), ncols, pilot, n, class_ids, nclasses, clean_text,
+            want_lengths, slots, max_distinct, static_cast<const TextStatsTable*>(tables), flags);
+        TMOG_LAUNCH_CHECK();
+    }
     return TMOG_OK;
 }
 
