@@ -161,7 +161,7 @@ def kernel_times(workload, batch, fitted, info, reps: int = 5):
                                         len(keep_local), dst.data_ptr(), len(keep_local), 0, st), reps)
             out.append({"kernel": "vec_transform_pack_kernel<double, true>", "ms": t_tr,
                         "bytes_per_row": ncols * 8 + ncols / 8 + len(keep_local) * 8})
-            out.append({"kernel": "real_fit_kernel", "ms": t_fit, "bytes_per_row": ncols * 8 + ncols / 8 + 8})
+            out.append({"kernel": "real_fit_tma_kernel", "ms": t_fit, "bytes_per_row": ncols * 8 + ncols / 8 + 8})
             del dst
         elif isinstance(blk, DictBlock):
             ncols = len(blk.names)
@@ -224,6 +224,17 @@ def kernel_times(workload, batch, fitted, info, reps: int = 5):
                         "note": "instruction-bound (tokenise + murmur3 + per-row table), reported against HBM anyway"})
             del oi, ov
     return sorted(out, key=lambda d: -d["ms"])
+
+
+# DRAM bytes per row of the config-2 kernels, from `ncu --set full` (profiles/r01_c2_full_raw.csv: 10 M rows, 199 of
+# 200 columns kept): pack transform 8.125 GB read + 15.862 GB written, fit scan 8.286 GB read + 0.004 GB written
+NCU_DRAM_BYTES_PER_ROW = {"vec_transform_pack_kernel<double, true>": 2398.8, "real_fit_tma_kernel": 829.0}
+
+
+def traffic_gb(workload: str, kernel: str, rows: int):
+    """Measured DRAM traffic of one launch of `kernel` in GB (None where no capture exists for the workload)."""
+    per_row = NCU_DRAM_BYTES_PER_ROW.get(kernel) if workload == "c2" else None
+    return None if per_row is None else per_row * rows / 1e9
 
 
 def cpu_reference_c2(rows: int, threads: int):
@@ -473,7 +484,10 @@ def main():
                        "kept_columns": len(fitted[-1].indicesToKeep), "dropped_columns": len(est.summary.dropped),
                        "algorithmic_bytes_per_row": {"fit": info["fit_bytes"], "transform": info["transform_bytes"]}},
             "roofline": {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved"], "peak": peak,
-                         "unit": "GB/s", "frac": top["frac"], "traffic": None, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": top["frac"], "traffic": traffic_gb(wl, top["kernel"], rows),
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full "
+                                           "capture at 10 M rows, scaled by rows (profiles/r01_c2_full_raw.csv)",
+                         "peak_source": peak_src,
                          "ms": top["ms"], "bytes_per_row": top["bytes_per_row"], "other": kt[1:]},
             "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches * steps, "clocks": clocks}))
     if world > 1:
