@@ -13,8 +13,6 @@ g = torch.Generator(device="cuda").manual_seed(1)
 x = torch.randn((ncols, n), dtype=torch.float64, device="cuda", generator=g)
 y = (torch.rand(n, device="cuda", generator=g) < 0.3).double()
 vw = torch.full((ncols, (n + 63) // 64), -1, dtype=torch.int64, device="cuda")
-for k in range(3):      # ~5 % nulls: and of three ~37 %-zero masks would be too many; clear bits sparsely instead
-    pass
 r = torch.randint(0, 2**62, (ncols, (n + 63) // 64, 3), dtype=torch.int64, device="cuda", generator=g)
 sparse = ~(r[..., 0] & r[..., 1] & r[..., 2]) | (r[..., 0] >> 1)      # mostly ones
 vw = sparse
