@@ -51,6 +51,22 @@ def _worker(rank, size, port, q):
         u = D.union_classes(local)
         assert u.tolist() == [0.0, 0.0, 1.0, 2.0] and np.signbit(u[0]) and not np.signbit(u[1])
         assert D.union_classes(None if rank == 1 else local) is None
+        # 3b. the same union from the device-side tensors in one exchange, with the per-class row counts when the
+        #     lists agree
+        def dev_lists(vals, cnts):
+            c = torch.zeros(256, dtype=torch.float64)
+            c[:len(vals)] = torch.tensor(vals, dtype=torch.float64)
+            k = torch.zeros(256, dtype=torch.int64)
+            k[:len(cnts)] = torch.tensor(cnts, dtype=torch.int64)
+            return torch.tensor([len(vals)], dtype=torch.int32), c, k
+        u, same, tot = D.gather_label_classes(*dev_lists([0.0, 1.0], [3 + rank, 7]))
+        assert u.tolist() == [0.0, 1.0] and same and tot.tolist() == [7, 14]
+        u, same, tot = D.gather_label_classes(*dev_lists([0.0, 2.0] if rank == 0 else [1.0, 2.0], [1, 1]))
+        assert u.tolist() == [0.0, 1.0, 2.0] and not same and tot is None
+        nc, c, k = dev_lists([0.0], [1])
+        if rank == 1:
+            nc[0] = -1                                # more classes than tracked on one rank: a continuous label
+        assert D.gather_label_classes(nc, c, k)[0] is None
         # 4. count tables add
         c = D.allreduce_sum(np.arange(6, dtype=np.int64).reshape(2, 3) * (rank + 1))
         assert np.array_equal(c, np.arange(6).reshape(2, 3) * 3)

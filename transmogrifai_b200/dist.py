@@ -140,6 +140,37 @@ def union_classes(local: Optional[np.ndarray], cap: int = 255) -> Optional[np.nd
     return None if len(u) > cap else u
 
 
+def gather_label_classes(ncls: torch.Tensor, classes: torch.Tensor, counts: torch.Tensor, cap: int = 255):
+    """Label classes of all ranks in one exchange.  ncls (int32 [1]: number of local classes, < 0 = more than the cap),
+    classes (f64 [256], sorted) and counts (int64 [256], rows per local class) are device tensors as
+    tmog_label_classes_dev leaves them.  -> (union, same, counts): the union of the class lists (None if any rank or
+    the union exceeds `cap`), whether every rank's own list already equals it (then the class ids each rank computed
+    against its own list are valid as they are), and in that case the rows per class summed over the ranks."""
+    size = world()[1]
+    dev = _device()
+    flat = torch.cat([ncls.to(dev).double(), classes.to(dev), counts.to(dev).view(torch.float64)])
+    out = torch.empty(size * flat.numel(), dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(out, flat)
+    host = out.cpu().numpy().reshape(size, flat.numel())
+    w = classes.numel()
+    ks = [int(h[0]) for h in host]
+    if any(k < 0 for k in ks):
+        return None, False, None
+    lists = [host[r, 1:1 + ks[r]] for r in range(size)]
+    allv = np.concatenate(lists) if lists else np.zeros(0)
+    # distinct by bit pattern (java.lang.Double.equals), ascending by value with -0.0 < 0.0 and NaN last
+    bits = np.unique(allv.view(np.int64))
+    key = np.where(bits < 0, ~bits.view(np.uint64), bits.view(np.uint64) | np.uint64(1 << 63))
+    union = bits.view(np.float64)[np.argsort(key, kind="stable")]
+    if len(union) > cap:
+        return None, False, None
+    same = all(len(v) == len(union) and np.array_equal(v.view(np.int64), union.view(np.int64)) for v in lists)
+    total = None
+    if same:
+        total = np.ascontiguousarray(host[:, 1 + w:1 + w + len(union)]).view(np.int64).sum(axis=0)
+    return union, same, total
+
+
 def shard_rows(n: int, rank: int, size: int, align: int = 2048) -> Tuple[int, int]:
     """Contiguous row range of `rank` (starts aligned so that bitmap words and 16-byte loads stay aligned)."""
     per = (n + size - 1) // size

@@ -59,16 +59,18 @@ def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str, after_launc
     ncls = torch.zeros(1, dtype=torch.int32, device="cuda")
     ids = torch.empty(max(n, 1), dtype=torch.uint8, device="cuda")
     L.call("tmog_label_classes_dev", y.data_ptr(), n, MAX_LABEL_CLASSES, classes.data_ptr(), ncls.data_ptr(),
-           None if distributed else ids.data_ptr(), None if distributed else counts.data_ptr(), scratch.data_ptr(),
-           scratch.numel(), R.stream())
-    if not distributed and after_launch is not None:
+           ids.data_ptr(), counts.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
+    if after_launch is not None:
         after_launch(ids)
-    k = int(ncls.item())
-    local = classes[:k].cpu().numpy() if k >= 0 else None
     if distributed:
-        union = D.union_classes(local, MAX_LABEL_CLASSES)
+        # Every rank maps its rows against its own class list right away (the kernels that consume the ids are queued
+        # behind it without waiting for the host); one exchange then tells whether all lists were the same -- the
+        # usual case -- and only otherwise are the rows mapped again, against the union.
+        union, same, g_counts = D.gather_label_classes(ncls, classes, counts, MAX_LABEL_CLASSES)
         if union is None or len(union) == 0:
             out = (None, None, ids)
+        elif same:
+            out = (union, g_counts, ids)
         else:
             classes[:len(union)] = torch.from_numpy(union).cuda()
             ncls.fill_(len(union))
@@ -77,9 +79,11 @@ def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str, after_launc
             if after_launch is not None:
                 after_launch(ids)
             g_counts = counts[:len(union)].clone()
-            torch.distributed.all_reduce(g_counts)            # summed on the device: one copy back instead of three
+            torch.distributed.all_reduce(g_counts)
             out = (union, g_counts.cpu().numpy(), ids)
     else:
+        k = int(ncls.item())
+        local = classes[:k].cpu().numpy() if k >= 0 else None
         out = (local, counts[:k].cpu().numpy(), ids) if k > 0 else (None, None, ids)
     cache[name] = out
     return out
