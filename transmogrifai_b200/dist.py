@@ -52,7 +52,16 @@ def gather_fit_results(partials, tables=()):
     ts = [as_t(t) for t in tables]
     shapes = [tuple(t.shape) for t in ts]
     if world()[1] == 1:
-        return p.cpu().numpy(), [t.cpu().numpy() for t in ts]
+        if not ts or not p.is_cuda:
+            return p.cpu().numpy(), [t.cpu().numpy() for t in ts]
+        # one device-to-host copy for all of it
+        flat = torch.cat([p] + [t.contiguous().reshape(-1).view(torch.float64) for t in ts]).cpu().numpy()
+        outs, at = [], p.numel()
+        for shp in shapes:
+            k = int(np.prod(shp)) if len(shp) else 1
+            outs.append(flat[at:at + k].view(np.int64).reshape(shp).copy())
+            at += k
+        return flat[:p.numel()].copy(), outs
     dev = _device()
     flat = torch.cat([p.to(dev)] + [t.to(dev).contiguous().reshape(-1).view(torch.float64) for t in ts])
     out = torch.empty(world()[1] * flat.numel(), dtype=torch.float64, device=dev)

@@ -82,9 +82,10 @@ def label_info_dev(batch: ColumnarBatch, y: torch.Tensor, name: str, after_launc
             torch.distributed.all_reduce(g_counts)
             out = (union, g_counts.cpu().numpy(), ids)
     else:
-        k = int(ncls.item())
-        local = classes[:k].cpu().numpy() if k >= 0 else None
-        out = (local, counts[:k].cpu().numpy(), ids) if k > 0 else (None, None, ids)
+        # one device-to-host copy: {number of classes, classes, rows per class}
+        host = torch.cat([ncls.double(), classes, counts.view(torch.float64)]).cpu().numpy()
+        k = int(host[0])
+        out = (host[1:1 + k].copy(), host[257:257 + k].view(np.int64).copy(), ids) if k > 0 else (None, None, ids)
     cache[name] = out
     return out
 
@@ -198,10 +199,17 @@ class RealVectorizer(OpEstimator):
                 classes, counts, ids = label_info_dev(batch, y, label_name, after_launch=count_nulls)
             # partial sums and null counts of all ranks in one exchange and one device-to-host copy
             want_nc = label_name and classes is not None and d_nc is not None
-            partials, tabs = D.gather_fit_results(d_part, [d_nc[:, :len(classes)]] if want_nc else [])
+            # (the shifts ride along as raw bits; every rank holds rank 0's, so their "sum" is not used)
+            extra = [d_shifts.view(torch.int64)] + ([d_nc[:, :len(classes)]] if want_nc else [])
+            if D.world()[1] == 1:
+                partials, tabs = D.gather_fit_results(d_part, extra)
+                shifts = tabs[0].view(np.float64)
+                tabs = tabs[1:]
+            else:
+                partials, tabs = D.gather_fit_results(d_part, extra[1:])
+                shifts = d_shifts.cpu().numpy()
             if want_nc:
                 null_counts = tabs[0]
-            shifts = d_shifts.cpu().numpy()
         else:
             y = batch.label() if label_name else torch.zeros(max(n, 2), dtype=torch.float64)
             cls = np.zeros(256)
