@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <functional>
 #include <memory>
 #include <new>
 #include <string>
@@ -167,60 +168,116 @@ struct StrRef {
     int64_t len;
 };
 
+// 64-bit string hash, eight bytes per step (murmur3-style mixing; only used to bucket strings -- equality is always
+// checked on the bytes)
 inline uint64_t fnv64(const char* p, int64_t len) {
-    uint64_t h = 1469598103934665603ull;
-    for (int64_t i = 0; i < len; ++i) h = (h ^ (unsigned char)p[i]) * 1099511628211ull;
-    return h ^ (h >> 29);
+    auto rotl = [](uint64_t x, int r) { return (x << r) | (x >> (64 - r)); };
+    uint64_t h = 0x9E3779B97F4A7C15ull ^ ((uint64_t)len * 0x87c37b91114253d5ull);
+    while (len > 0) {
+        uint64_t w = 0;
+        memcpy(&w, p, (size_t)(len >= 8 ? 8 : len));
+        w *= 0x87c37b91114253d5ull;
+        w = rotl(w, 31);
+        w *= 0x4cf5ad432745937full;
+        h ^= w;
+        h = rotl(h, 27) * 5 + 0x52dce729;
+        p += 8;
+        len -= 8;
+    }
+    h ^= h >> 33;
+    h *= 0xff51afd7ed558ccdull;
+    h ^= h >> 33;
+    h *= 0xc4ceb9fe1a85ec53ull;
+    h ^= h >> 33;
+    return h;
 }
 
-// cleaned strings of a dictionary, stored back to back; returns false on non-ASCII input when cleaning
+// cleaned strings of a dictionary, stored back to back; returns false on non-ASCII input when cleaning.  Cleaning never
+// lengthens a string, so the pool is sized once and written through a raw pointer.
 bool clean_dictionary(const uint8_t* data, const int64_t* offsets, int64_t count, bool clean, std::string& pool,
                       std::vector<int64_t>& pool_off, int64_t* bad_entry) {
-    pool.clear();
-    pool_off.assign(1, 0);
-    pool_off.reserve((size_t)count + 1);
-    std::string tmp;
+    pool_off.resize((size_t)count + 1);
+    pool_off[0] = 0;
+    const int64_t total = count > 0 ? offsets[count] - offsets[0] : 0;
+    pool.resize((size_t)total);
+    if (!clean) {
+        if (total > 0) memcpy(&pool[0], data + offsets[0], (size_t)total);
+        for (int64_t i = 0; i < count; ++i) pool_off[i + 1] = offsets[i + 1] - offsets[0];
+        return true;
+    }
+    // clean_ascii through byte tables: kind 0 = separator (space / punctuation), 1 = kept, 2 = non-ASCII;
+    // lower[c] the lower-cased byte, upper[c] the byte that starts a piece (capitalised lower-case letter)
+    static unsigned char kind[256], lower[256], upper[256];
+    static const bool tables_ready = [] {
+        for (int c = 0; c < 256; ++c) {
+            kind[c] = c >= 0x80 ? 2 : ((c == ' ' || is_ascii_punct((unsigned char)c)) ? 0 : 1);
+            const int lo = (c >= 'A' && c <= 'Z') ? c + 32 : c;
+            lower[c] = (unsigned char)lo;
+            upper[c] = (unsigned char)((lo >= 'a' && lo <= 'z') ? lo - 32 : lo);
+        }
+        return true;
+    }();
+    (void)tables_ready;
+    char* out = total > 0 ? &pool[0] : nullptr;
+    int64_t w = 0;
     for (int64_t i = 0; i < count; ++i) {
+        const uint8_t* s = data + offsets[i];
         const int64_t len = offsets[i + 1] - offsets[i];
-        if (clean) {
-            if (!clean_ascii(data + offsets[i], len, tmp)) {
+        bool start = true;
+        for (int64_t q = 0; q < len; ++q) {
+            const unsigned char c = s[q];
+            const unsigned char k = kind[c];
+            if (k == 1) {
+                out[w++] = (char)(start ? upper[c] : lower[c]);
+                start = false;
+            } else if (k == 0) {
+                start = true;
+            } else {
                 *bad_entry = i;
                 return false;
             }
-            pool.append(tmp);
-        } else {
-            pool.append((const char*)data + offsets[i], (size_t)len);
         }
-        pool_off.push_back((int64_t)pool.size());
+        pool_off[i + 1] = w;
     }
+    pool.resize((size_t)w);
     return true;
 }
 
-// ids[i] = dense id of cleaned string i (first-appearance order); open addressing over (hash, id)
+// ids[i] = dense id of cleaned string i (first-appearance order); open addressing over (hash, id): a slot keeps the
+// hash of its string, so the strings themselves are only compared when the hashes agree
 int64_t group_strings(const std::string& pool, const std::vector<int64_t>& off, std::vector<int32_t>& ids,
                       std::vector<int32_t>& first) {
     const int64_t count = (int64_t)off.size() - 1;
     size_t cap = 16;
     while (cap < (size_t)count * 2 + 2) cap <<= 1;
-    std::vector<int32_t> slot(cap, -1);
+    struct Slot {
+        uint64_t hash;
+        int32_t id;
+    };
+    std::vector<Slot> slot(cap, Slot{0, -1});
     ids.resize((size_t)count);
     first.clear();
+    first.reserve((size_t)count);
     for (int64_t i = 0; i < count; ++i) {
         const char* p = pool.data() + off[i];
         const int64_t len = off[i + 1] - off[i];
-        size_t s = (size_t)fnv64(p, len) & (cap - 1);
+        const uint64_t h = fnv64(p, len);
+        size_t s = (size_t)h & (cap - 1);
         for (;;) {
-            const int32_t id = slot[s];
-            if (id < 0) {
-                slot[s] = (int32_t)first.size();
-                ids[i] = (int32_t)first.size();
+            Slot& sl = slot[s];
+            if (sl.id < 0) {
+                sl.hash = h;
+                sl.id = (int32_t)first.size();
+                ids[i] = sl.id;
                 first.push_back((int32_t)i);
                 break;
             }
-            const int32_t j = first[id];
-            if (off[j + 1] - off[j] == len && memcmp(pool.data() + off[j], p, (size_t)len) == 0) {
-                ids[i] = id;
-                break;
+            if (sl.hash == h) {
+                const int32_t j = first[sl.id];
+                if (off[j + 1] - off[j] == len && memcmp(pool.data() + off[j], p, (size_t)len) == 0) {
+                    ids[i] = sl.id;
+                    break;
+                }
             }
             s = (s + 1) & (cap - 1);
         }
@@ -272,14 +329,13 @@ extern "C" int tmog_pivot_dict_finish(const tmog_pivot_dict* d, const int64_t* r
     const std::vector<int64_t>& off = d->off;
     const std::vector<int32_t>&ids = d->ids, &first = d->first;
     const int64_t ncodes = d->ncodes, nd = (int64_t)first.size();
-    // merged counts per cleaned value and class (raw_counts row 0 is the null bin, row 1 + code the raw code)
-    std::vector<int64_t> merged((size_t)nd * nclasses, 0), total((size_t)nd, 0);
-    for (int64_t i = 0; i < ncodes; ++i)
-        for (int k = 0; k < nclasses; ++k) {
-            const int64_t v = raw_counts[(i + 1) * nclasses + k];
-            merged[(size_t)ids[i] * nclasses + k] += v;
-            total[ids[i]] += v;
-        }
+    // rows per cleaned value (raw_counts row 0 is the null bin, row 1 + code the raw code)
+    std::vector<int64_t> total((size_t)nd, 0);
+    for (int64_t i = 0; i < ncodes; ++i) {
+        int64_t v = 0;
+        for (int k = 0; k < nclasses; ++k) v += raw_counts[(i + 1) * nclasses + k];
+        total[ids[i]] += v;
+    }
     // top-K: count >= minSupport (and > 0), sort by (-count, java string order)
     std::vector<int32_t> cand;
     for (int64_t v = 0; v < nd; ++v)
@@ -293,6 +349,18 @@ extern "C" int tmog_pivot_dict_finish(const tmog_pivot_dict* d, const int64_t* r
         return java_compare(str_of(a), str_of(b)) < 0;
     };
     const size_t k = std::min<size_t>((size_t)top_k, cand.size());
+    if (cand.size() > 4 * k && k > 0) {
+        // only values whose count reaches the k-th largest count can make the vocabulary: cut the candidates down
+        // with a selection on the counts alone before the (string-comparing) sort
+        std::vector<int64_t> cnts(cand.size());
+        for (size_t i = 0; i < cand.size(); ++i) cnts[i] = total[cand[i]];
+        std::nth_element(cnts.begin(), cnts.begin() + (k - 1), cnts.end(), std::greater<int64_t>());
+        const int64_t kth = cnts[k - 1];
+        size_t w2 = 0;
+        for (size_t i = 0; i < cand.size(); ++i)
+            if (total[cand[i]] >= kth) cand[w2++] = cand[i];
+        cand.resize(w2);
+    }
     std::partial_sort(cand.begin(), cand.begin() + k, cand.end(), less);
     std::vector<int32_t> pos((size_t)nd, (int32_t)k);  // OTHER = k
     int64_t w = 0;
@@ -312,8 +380,10 @@ extern "C" int tmog_pivot_dict_finish(const tmog_pivot_dict* d, const int64_t* r
     for (int64_t i = 0; i < ncodes; ++i) code_to_out[i] = pos[ids[i]];
     // emitted columns: k top values, OTHER, null
     for (size_t i = 0; i < (k + 2) * (size_t)nclasses; ++i) out_class_counts[i] = 0;
-    for (int64_t v = 0; v < nd; ++v)
-        for (int c = 0; c < nclasses; ++c) out_class_counts[(size_t)pos[v] * nclasses + c] += merged[(size_t)v * nclasses + c];
+    for (int64_t i = 0; i < ncodes; ++i) {
+        int64_t* o = out_class_counts + (size_t)pos[ids[i]] * nclasses;
+        for (int c = 0; c < nclasses; ++c) o[c] += raw_counts[(i + 1) * nclasses + c];
+    }
     for (int c = 0; c < nclasses; ++c) out_class_counts[(k + 1) * nclasses + c] = raw_counts[c];
     return TMOG_OK;
 }
