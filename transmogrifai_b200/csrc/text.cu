@@ -480,6 +480,10 @@ __device__ __forceinline__ void th_insert(Slot* table, int tbits, int cb, unsign
     const Slot cmask = (Slot(1) << cb) - Slot(1);
     const unsigned tmask = (1u << tbits) - 1u;
     unsigned slot = (key * 0x9E3779B1u) >> (32 - tbits);
+    // double hashing: an odd step visits every slot of the power-of-two table, and keys that collide on their first
+    // slot part ways afterwards -- at a load of 7/8 linear probing would build long runs that a few lanes of the warp
+    // walk while the others wait
+    const unsigned step = ((key * 0x85EBCA6Bu) >> (32 - tbits)) | 1u;
     for (unsigned probe = 0; probe <= tmask; ++probe) {
         Slot cur = table[slot];
         if (cur == EMPTY) {
@@ -494,7 +498,7 @@ __device__ __forceinline__ void th_insert(Slot* table, int tbits, int cb, unsign
             if ((old & cmask) == cmask) ovf = true;       // the count ran into the key
             return;
         }
-        slot = (slot + 1) & tmask;
+        slot = (slot + step) & tmask;
     }
     ovf = true;                                           // table full
 }
