@@ -1049,8 +1049,59 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                     if ((int64_t)base + kept > capacity) flags[3] = 1;
                 }
                 base = __shfl_sync(FULL, base, 0);
+                // Narrow outputs (separate hash spaces of a few hundred buckets per column): order by a bitmap over the
+                // new positions instead.  Per slice of BM_WORDS * 32 positions every entry sets its bit, a scan of the
+                // words gives the number of set bits before each word, and an entry's place in the row is that prefix
+                // plus the set bits below its own -- no displacement chains, every lane busy.
+                constexpr int BM_WORDS = 256;
+                static_assert(BM_WORDS * 6 <= L::MASK - L::BUF, "bitmap + word prefixes live in the text buffer");
+                bool placed = false;
+                if (kept > 0 && (long long)np_max - np_min < 8ll * BM_WORDS * 32) {
+                    unsigned* bm = reinterpret_cast<unsigned*>(wbase + L::BUF);
+                    unsigned short* pre = reinterpret_cast<unsigned short*>(bm + BM_WORDS);
+                    int done = 0;
+                    for (int lo_p = np_min; lo_p <= np_max; lo_p += BM_WORDS * 32) {
+                        for (int i = lane; i < BM_WORDS; i += 32) bm[i] = 0u;
+                        __syncwarp();
+                        for (int i = lane; i < kept; i += 32) {
+                            const unsigned q = (unsigned)((int)(table[i] >> cb) - lo_p);
+                            if (q < (unsigned)(BM_WORDS * 32)) atomicOr(&bm[q >> 5], 1u << (q & 31u));
+                        }
+                        __syncwarp();
+                        int run = 0;
+                        for (int w0 = 0; w0 < BM_WORDS; w0 += 32) {
+                            const int c = __popc(bm[w0 + lane]);
+                            int incl = c;
+#pragma unroll
+                            for (int o = 1; o < 32; o <<= 1) {
+                                const int up = __shfl_up_sync(FULL, incl, o);
+                                if (lane >= o) incl += up;
+                            }
+                            pre[w0 + lane] = (unsigned short)(run + incl - c);
+                            run += __shfl_sync(FULL, incl, 31);
+                        }
+                        __syncwarp();
+                        for (int i = lane; i < kept; i += 32) {
+                            const Slot x = table[i];
+                            const unsigned q = (unsigned)((int)(x >> cb) - lo_p);
+                            if (q < (unsigned)(BM_WORDS * 32)) {
+                                const unsigned w = q >> 5;
+                                const int64_t at = (int64_t)base + done + pre[w] +
+                                                   __popc(bm[w] & ((1u << (q & 31u)) - 1u));
+                                if (at < capacity) {
+                                    out_idx[at] = (int32_t)(x >> cb);
+                                    out_val[at] = (int32_t)(x & cmask);
+                                }
+                            }
+                        }
+                        done += run;
+                        __syncwarp();
+                    }
+                    for (int i = lane; i < kept; i += 32) table[i] = EMPTY;
+                    placed = true;
+                }
                 const int phases = max(1, (kept + T2 / 2 - 1) / (T2 / 2));
-                bool ordered = kept > 0 && phases <= 8;
+                bool ordered = !placed && kept > 0 && phases <= 8;
                 if (ordered) {
                     const unsigned long long span = (unsigned long long)(np_max - np_min) + 1ull;
                     int done = 0;
@@ -1098,7 +1149,7 @@ text_hash_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 }
                 __syncwarp();
                 if (lane < 4) reinterpret_cast<unsigned*>(wbase + L::BUF)[lane] = 0u;       // the slack before the text
-                if (!ordered) {
+                if (!ordered && !placed) {
                     int m = 32;
                     while (m < kept) m <<= 1;
                     for (int k2 = 2; k2 <= m; k2 <<= 1) {
