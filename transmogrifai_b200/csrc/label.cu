@@ -31,13 +31,18 @@ __global__ void label_init_kernel(unsigned long long* table) {
 
 __global__ void __launch_bounds__(256)
 label_distinct_kernel(const double* __restrict__ label, int64_t n, int max_classes, unsigned long long* table) {
-    unsigned long long last = LBL_EMPTY;
+    // the values this thread entered last: a label of a few classes then costs one load and two compares per row
+    unsigned long long last = LBL_EMPTY, last2 = LBL_EMPTY;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        const unsigned long long b = label_bits(label[i]);
-        if (b == last) continue;
+    auto enter = [&](unsigned long long b) {
+        if (b == last || b == last2) return;
+        last2 = last;
         last = b;
-        if (table[LBL_SLOTS] > (unsigned long long)max_classes) return;  // already "continuous": stop
+        // the lanes that meet a new value in the same step (all of them in the first one) agree on one lane per
+        // distinct value to carry it to the table: a few thousand table accesses instead of one per thread
+        const unsigned peers = __match_any_sync(__activemask(), b);
+        if ((int)(__ffs(peers) - 1) != (int)(threadIdx.x & 31)) return;
+        if (table[LBL_SLOTS] > (unsigned long long)max_classes) return;  // already "continuous"
         unsigned s = slot_of(b);
         for (int probe = 0; probe < LBL_SLOTS; ++probe) {
             const unsigned long long cur = table[s];
@@ -52,7 +57,16 @@ label_distinct_kernel(const double* __restrict__ label, int64_t n, int max_class
             }
             s = (s + 1) & (LBL_SLOTS - 1);
         }
+    };
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 7 * stride < n; i += 8 * stride) {      // eight independent loads in flight per thread
+        double y[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) y[u] = __ldcs(label + i + u * stride);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) enter(label_bits(y[u]));
     }
+    for (; i < n; i += stride) enter(label_bits(label[i]));
 }
 
 // one block: compact the table, rank-sort ascending by numeric value (NaN last, -0.0 before 0.0 as
@@ -118,36 +132,100 @@ label_class_id_kernel(const double* __restrict__ label, int64_t n, const double*
             if (hist[i]) atomicAdd(&class_counts[i], (unsigned long long)hist[i]);
 }
 
-// counts[c][k] += number of NULL rows of column c whose label class is k.  One warp per (column, 2048-row tile);
-// only null bits are visited, so the cost is the bitmap read plus one shared-memory atomic per null.
+// counts[c][k] += number of NULL rows of column c whose label class is k.  A CTA walks tiles of 2048 rows (32 bitmap
+// words per column).  Per tile the class ids become one 64-row bit mask per class and word (ballots; classes 0..7),
+// after which a column costs one coalesced load of its 32 validity words and, per class, a popcount of
+// nulls & mask summed over the warp -- no per-null work.  A tile that holds a class id >= 8 takes the general path
+// instead: every null bit is visited and counted in a per-warp shared-memory histogram.
+constexpr int NC_FAST = 8;
+
 __global__ void __launch_bounds__(256)
 null_class_count_kernel(const uint64_t* __restrict__ valid, int64_t ldv, const uint8_t* __restrict__ ids, int64_t n,
                         int ncols, int nclasses, unsigned long long* __restrict__ counts) {
-    extern __shared__ unsigned int hist[];  // [8 warps][nclasses]
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned int* h = hist + warp * nclasses;
+    extern __shared__ unsigned int nc_smem[];       // [ncols][NC_FAST] accumulators | [8 warps][nclasses] histograms
+    __shared__ unsigned int masks[NC_FAST][64];     // class k, 32-row half-word h of the tile
+    __shared__ int big;
+    unsigned int* acc = nc_smem;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned int* h = nc_smem + ncols * NC_FAST + warp * nclasses;
+    for (int i = tid; i < ncols * NC_FAST; i += 256) acc[i] = 0u;
     const int64_t ntiles = (n + 2047) / 2048;
-    const int64_t nwork = ntiles * ncols;
-    for (int64_t w = (int64_t)blockIdx.x * 8 + warp; w < nwork; w += (int64_t)gridDim.x * 8) {
-        const int c = (int)(w % ncols);
-        const int64_t tile = w / ncols;
-        for (int k = lane; k < nclasses; k += 32) h[k] = 0;
-        __syncwarp();
-        const int64_t word = tile * 32 + lane;
-        const int64_t r0 = word * 64;
-        if (r0 < n) {
-            unsigned long long nulls = ~valid[(int64_t)c * ldv + word];
-            if (n - r0 < 64) nulls &= (1ull << (n - r0)) - 1ull;
-            while (nulls) {
-                const int bit = __ffsll((long long)nulls) - 1;
-                nulls &= nulls - 1;
-                atomicAdd(&h[ids[r0 + bit]], 1u);
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        __syncthreads();                            // the previous tile's masks are no longer read
+        if (tid == 0) big = 0;
+        __syncthreads();
+        int idv[8];
+        int idmax = -1;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {               // the tile's ids: eight independent loads per thread
+            const int64_t row = tile * 2048 + it * 256 + tid;
+            idv[it] = row < n ? (int)ids[row] : -1;
+            idmax = max(idmax, idv[it]);
+        }
+        idmax = __reduce_max_sync(FULL, idmax);
+        if (lane == 0 && idmax > 0) atomicMax(&big, idmax);      // big = the largest class id of the tile
+        __syncthreads();
+        const int kc = min(big + 1, NC_FAST);                    // classes that can occur in this tile
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int id = idv[it];
+            for (int k = 0; k < kc; ++k) {
+                const unsigned b = __ballot_sync(FULL, id == k);
+                if (lane == 0) masks[k][it * 8 + warp] = b;
             }
         }
-        __syncwarp();
-        for (int k = lane; k < nclasses; k += 32)
-            if (h[k]) atomicAdd(&counts[(int64_t)c * nclasses + k], (unsigned long long)h[k]);
-        __syncwarp();
+        __syncthreads();
+        const int64_t word = tile * 32 + lane;
+        const int64_t r0 = word * 64;
+        if (big < NC_FAST) {
+            const unsigned long long* m64 = reinterpret_cast<const unsigned long long*>(&masks[0][0]);
+            unsigned long long mk[NC_FAST];
+#pragma unroll
+            for (int k = 0; k < NC_FAST; ++k) mk[k] = k < kc ? m64[k * 32 + lane] : 0ull;
+            const unsigned long long tail = (r0 < n) ? ((n - r0 < 64) ? (1ull << (n - r0)) - 1ull : ~0ull) : 0ull;
+            for (int c0 = warp; c0 < ncols; c0 += 8 * 8) {      // eight columns' words in flight per lane
+                unsigned long long nulls[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int c = c0 + 8 * u;
+                    nulls[u] = (c < ncols && tail) ? ~__ldcs(valid + (int64_t)c * ldv + word) & tail : 0ull;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const int c = c0 + 8 * u;
+                    if (c >= ncols || !__any_sync(FULL, nulls[u] != 0ull)) continue;
+#pragma unroll
+                    for (int k = 0; k < NC_FAST; ++k) {
+                        if (k >= kc) break;
+                        const unsigned cnt = __reduce_add_sync(FULL, (unsigned)__popcll(nulls[u] & mk[k]));
+                        if (lane == 0 && cnt) acc[c * NC_FAST + k] += cnt;     // column c belongs to this warp alone
+                    }
+                }
+            }
+        } else {
+            for (int c = warp; c < ncols; c += 8) {
+                for (int k = lane; k < nclasses; k += 32) h[k] = 0;
+                __syncwarp();
+                if (r0 < n) {
+                    unsigned long long nulls = ~valid[(int64_t)c * ldv + word];
+                    if (n - r0 < 64) nulls &= (1ull << (n - r0)) - 1ull;
+                    while (nulls) {
+                        const int bit = __ffsll((long long)nulls) - 1;
+                        nulls &= nulls - 1;
+                        atomicAdd(&h[ids[r0 + bit]], 1u);
+                    }
+                }
+                __syncwarp();
+                for (int k = lane; k < nclasses; k += 32)
+                    if (h[k]) atomicAdd(&counts[(int64_t)c * nclasses + k], (unsigned long long)h[k]);
+                __syncwarp();
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < ncols * NC_FAST; i += 256) {
+        const int c = i / NC_FAST, k = i % NC_FAST;
+        if (acc[i] && k < nclasses) atomicAdd(&counts[(int64_t)c * nclasses + k], (unsigned long long)acc[i]);
     }
 }
 
@@ -215,9 +293,13 @@ extern "C" int tmog_null_class_counts_dev(const uint64_t* valid, int64_t ldv, co
     if (!accumulate) TMOG_CUDA(cudaMemsetAsync(counts, 0, sizeof(uint64_t) * (size_t)ncols * nclasses, st));
     if (valid == nullptr || n == 0 || ncols == 0) return TMOG_OK;  // no nulls anywhere
     TMOG_REQUIRE(class_ids != nullptr && ldv >= (n + 63) / 64, "class_ids is NULL or ldv too small");
-    const int64_t nwork = ((n + 2047) / 2048) * ncols;
-    const int grid = (int)std::min<int64_t>((nwork + 7) / 8, (int64_t)sm_count() * 8);
-    null_class_count_kernel<<<grid, 256, sizeof(unsigned) * 8 * nclasses, st>>>(
+    const int64_t ntiles = (n + 2047) / 2048;
+    const size_t smem = sizeof(unsigned) * ((size_t)ncols * NC_FAST + 8 * (size_t)nclasses);
+    TMOG_REQUIRE(smem <= 160 * 1024, "too many columns for one null-count call (%d): split the column block", ncols);
+    if (smem > 40 * 1024)
+        TMOG_CUDA(cudaFuncSetAttribute(null_class_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int grid = (int)std::min<int64_t>(ntiles, (int64_t)sm_count() * 8);
+    null_class_count_kernel<<<grid, 256, smem, st>>>(
         valid, ldv, class_ids, n, ncols, nclasses, reinterpret_cast<unsigned long long*>(counts));
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
