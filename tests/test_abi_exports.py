@@ -45,3 +45,38 @@ def test_host_only_entry_points_work_without_gpu():
     assert nls[0] == 0.0
     rc = L.lib().tmog_real_partials_merge(None, None, 1)
     assert rc == -1 and b"bad arguments" in L.lib().tmog_last_error()
+
+
+def test_sanity_decide_wide_vector_matches_the_rules():
+    """tmog_sanity_decide on a vector wide enough for its threaded path (host code, no GPU): the variance and
+    correlation rules per column and the parent-level correlation rule, against numpy."""
+    import numpy as np
+    from transmogrifai_b200 import _lib as L
+    rng = np.random.default_rng(0)
+    d, nparents = 70_000, 700
+    variance = rng.random(d)
+    variance[rng.integers(0, d, 500)] = 0.0
+    corr = rng.uniform(-1, 1, d + 1)
+    corr[rng.integers(0, d, 300)] = np.nan
+    parent = (np.arange(d) // 100).astype(np.int32)               # runs of 100 columns share a parent
+    offs = np.arange(d + 1, dtype=np.int32)
+    pos = np.arange(d, dtype=np.int32)
+    gid = np.full(d, -1, dtype=np.int32)
+    tsh = np.zeros(d, dtype=np.uint8)
+    cv = np.full(d, np.nan)
+    rcount = np.full(d, -1, dtype=np.int32)
+    rconf, rsup = np.zeros(2 * d), np.zeros(2 * d)
+    params = np.array([1e-5, 0.1, 0.9, 0.99, 0.95, 1.0, 1.0, 1.0, 0.0])
+    drop = np.zeros(d, dtype=np.uint8)
+    reasons = np.zeros(d, dtype=np.uint32)
+    pc, pv = np.zeros(d), np.zeros(d)
+    L.call("tmog_sanity_decide", d, variance.ctypes.data, corr.ctypes.data, None, 0, pos.ctypes.data, offs.ctypes.data,
+           parent.ctypes.data, gid.ctypes.data, tsh.ctypes.data, cv.ctypes.data, rcount.ctypes.data, rconf.ctypes.data,
+           rsup.ctypes.data, params.ctypes.data, drop.ctypes.data, reasons.ctypes.data, pc.ctypes.data, pv.ctypes.data)
+    ac = np.where(np.isnan(corr[:d]), 0.0, np.abs(corr[:d]))
+    exp_pc = np.repeat(ac.reshape(nparents, 100).max(axis=1), 100)
+    assert np.array_equal(pc, exp_pc) and np.isnan(pv).all()
+    with np.errstate(invalid="ignore"):
+        exp = (variance <= 1e-5) * 1 | (np.abs(corr[:d]) < 0.1) * 2 | (np.abs(corr[:d]) > 0.9) * 4 | (exp_pc > 0.9) * 256
+    assert np.array_equal(reasons, exp.astype(np.uint32))
+    assert np.array_equal(drop, (exp != 0).astype(np.uint8))

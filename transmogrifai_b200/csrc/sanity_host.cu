@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <map>
+#include <thread>
 #include <vector>
 
 #include "common.cuh"
@@ -182,8 +183,12 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
                 break;
             }
     }
+    // the per-column rules are independent of each other: wide vectors (a hashed block has hundreds of thousands of
+    // columns) are split over a few threads
+    auto decide_range = [&](int lo, int hi) {
     double run_pc = nan(""), run_pv = nan("");
-    for (int i = 0; i < d; ++i) {
+    int cur_head = -1;
+    for (int i = lo; i < hi; ++i) {
         uint32_t r = 0;
         if (variance[i] <= min_variance) r |= 1u;
         const bool has_corr = corr_pos[i] >= 0 && corr_label != nullptr;
@@ -207,9 +212,10 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
             }
         if (group_id[i] >= 0 && group_flagged[group_id[i]]) r |= 64u;
         // parent-level values: max over the column's parents that have an entry (once per run of equal parent lists)
-        if (run_of[i] == i) {
+        if (run_of[i] != cur_head) {
+            cur_head = run_of[i];
             run_pc = run_pv = nan("");
-            for (int k = parent_offsets[i]; k < parent_offsets[i + 1]; ++k) {
+            for (int k = parent_offsets[cur_head]; k < parent_offsets[cur_head + 1]; ++k) {
                 const double a = corr_parent[parent_ids[k]], b = cramers_parent[parent_ids[k]];
                 if (!isnan(a)) run_pc = isnan(run_pc) ? a : std::max(run_pc, a);
                 if (!isnan(b)) run_pv = isnan(run_pv) ? b : std::max(run_pv, b);
@@ -224,6 +230,19 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
         }
         drop[i] = r != 0;
         if (reasons) reasons[i] = r;
+    }
+    };
+    const int nthreads = d >= (1 << 16) ? (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency())) : 1;
+    if (nthreads == 1) {
+        decide_range(0, d);
+    } else {
+        std::vector<std::thread> pool;
+        const int chunk = (d + nthreads - 1) / nthreads;
+        for (int t = 0; t < nthreads; ++t) {
+            const int lo = t * chunk, hi = std::min(d, lo + chunk);
+            if (lo < hi) pool.emplace_back(decide_range, lo, hi);
+        }
+        for (auto& th : pool) th.join();
     }
     return TMOG_OK;
 }
