@@ -371,3 +371,93 @@ def test_min_variance_filter_after_transmogrify(with_label):
     assert fitted[-1].indicesToKeep == keep and 4 not in keep and 8 not in keep
     got = out.vectors[checked.name].to_numpy()
     np.testing.assert_allclose(got, exp[:, keep], rtol=1e-12, atol=0)
+
+
+def test_sanity_checker_sampling_matches_oracle_on_the_same_rows():
+    """fraction() < 1 (SanityChecker.scala:356-387): the statistics, tests and the drop decision are those of the
+    sampled rows of the vector that the models fitted on ALL rows produce.  The sample itself is ours (seeded device
+    generator), so the oracle is given the same rows."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+    rng = np.random.default_rng(51)
+    n = 6000
+    y = (rng.random(n) < 0.3).astype(np.float64)
+    opt = lambda v, p: None if rng.random() < p else v   # noqa: E731
+    b0 = [opt(bool(rng.random() < 0.4 + 0.3 * yy), 0.1) for yy in y]
+    p0 = [opt(["x", "y", "z", "X ", "w"][int(rng.integers(5))], 0.08) for _ in y]
+    r0 = [opt(float(rng.normal(2 + yy, 1)), 0.1) for yy in y]
+    i0 = [opt(int(rng.integers(0, 6)), 0.1) for _ in y]
+    words = ["".join(rng.choice(list("abcdefgh"), size=rng.integers(3, 7))) for _ in range(150)]
+    t0 = [opt(" ".join(words[i] for i in rng.integers(0, 150, rng.poisson(8))), 0.06) for _ in y]
+    data = {"b0": (F.BINARY, b0), "p0": (F.PICKLIST, p0), "r0": (F.REAL, r0), "i0": (F.INTEGRAL, i0),
+            "t0": (F.TEXT, t0), "y": (F.REALNN, y.tolist())}
+    batch = _batch(data, response="y", device="cuda")
+    FB = F.FeatureBuilder
+    feats = [FB.Text("t0").asPredictor(), FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(),
+             FB.PickList("p0").asPredictor(), FB.Integral("i0").asPredictor()]
+    label = FB.RealNN("y").asResponse()
+    # reference defaults for the limits, scaled down: upper limit 2000 rows of 6000 -> fraction 1/3
+    checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, checkSample=1.0, sampleLowerLimit=100,
+                                sampleUpperLimit=2000, sampleSeed=7, featureFeatureCorrLevel="Computed")
+    est = checked.origin_stage
+    frac = est.fraction(n)
+    assert abs(frac - 2000 / 6000) < 1e-12
+    out_batch, fitted = fit_and_transform(batch, checked)
+    g = torch.Generator(device="cuda").manual_seed(7)
+    idx = (torch.rand(n, device="cuda", generator=g) < frac).nonzero().squeeze(1).cpu().numpy()
+    assert 1700 < len(idx) < 2300 and est.summary.count == len(idx) and est.summary.sampleFraction == frac
+    # the vector over all rows, from models fitted on all rows
+    xb = V.binary_vectorizer_transform([b0])
+    modes = V.integral_vectorizer_fit([i0], fill_with_mode=True)
+    xi = V.integral_vectorizer_transform([i0], modes, True)
+    tops = V.pivot_fit([p0], 20, 10, True)
+    xp = V.pivot_transform([p0], tops, True, True)
+    fills = V.real_vectorizer_fit([r0])
+    xr = V.real_vectorizer_transform([r0], fills, True)
+    methods, ttops = V.smart_text_fit([t0], max_cardinality=30, top_k=20, min_support=10)
+    xt = V.smart_text_transform([t0], ["t0"], methods, ttops, num_features=512)
+    xo, metas = V.combine(
+        [xb, xi, xp, xr, xt],
+        [V.numeric_metadata(["b0"], "Binary", True), V.numeric_metadata(["i0"], "Integral", True),
+         V.pivot_metadata(["p0"], "PickList", tops, True), V.numeric_metadata(["r0"], "Real", True),
+         V.smart_text_metadata(["t0"], "Text", methods, ttops, 512, True)])
+    p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                       feature_feature_corr_level="computed")
+    ref = S.sanity_fit(y[idx], xo.tocsr()[idx], metas, p, label_name="y")
+    assert est.summary.dropped == ref.dropped
+    assert fitted[-1].indicesToKeep == ref.indices_to_keep
+    np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+    np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                               equal_nan=True)
+    # the model still transforms every row
+    got = out_batch.vectors[checked.name].to_scipy()
+    exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
+    assert got.shape == exp.shape and abs(got - exp).max() < 1e-9
+
+
+def test_sanity_checker_default_limits_sample_a_large_batch():
+    """The reference's defaults (checkSample 1.0, sampleUpperLimit 1e6) on 1.2 M rows: five sixths of the rows are
+    sampled, nothing raises, and the sample statistics are close to those of all rows."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch, NumericBlock
+    from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+    n, ncols = 1_200_000, 3
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.randn((ncols, n), dtype=torch.float64, device="cuda", generator=g) * 2.0 + 5.0
+    y = (torch.rand(n, device="cuda", generator=g) < 0.3).double()
+    x[1] += y                                                    # a correlated column
+    names = [f"c{j}" for j in range(ncols)]
+    blocks = [NumericBlock(names, F.REAL, x, None, n), NumericBlock(["y"], F.REALNN, y.reshape(1, n), None, n)]
+    batch = ColumnarBatch(n, blocks, {}, "y")
+    feats = [F.FeatureBuilder.Real(nm).asPredictor() for nm in names]
+    label = F.FeatureBuilder.RealNN("y").asResponse()
+    checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True)        # every default
+    out, fitted = fit_and_transform(batch, checked)
+    est = checked.origin_stage
+    assert abs(est.summary.sampleFraction - 1e6 / n) < 1e-12
+    assert abs(est.summary.count - 1_000_000) < 3000
+    np.testing.assert_allclose(est.summary.mean[0:6:2], x.mean(dim=1).cpu().numpy(), rtol=5e-3)
+    corr = dict(zip(est.summary.names, est.summary.correlationsWithLabel))
+    assert corr["c1_2"] > 0.15 and abs(corr["c0_0"]) < 0.01
+    assert out.vectors[checked.name].n == n

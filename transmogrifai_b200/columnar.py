@@ -73,6 +73,30 @@ def to_host(tensors, piece_bytes: Optional[int] = None) -> list:
     return out
 
 
+def take_bitmap(valid: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """Arrow validity words [..., ldv] of the rows `idx` (int64, ascending or not), repacked: [..., ceil(m / 64)]."""
+    m = idx.numel()
+    nw = max((m + 63) // 64, 1)
+    bits = (valid.index_select(-1, idx >> 6) >> (idx & 63)) & 1
+    pad = torch.zeros(valid.shape[:-1] + (nw * 64 - m,), dtype=torch.int64, device=valid.device)
+    bits = torch.cat([bits, pad], dim=-1).reshape(valid.shape[:-1] + (nw, 64))
+    weights = torch.ones(64, dtype=torch.int64, device=valid.device) << torch.arange(64, device=valid.device)
+    return (bits * weights).sum(dim=-1)
+
+
+def take_ragged(data: torch.Tensor, offsets: torch.Tensor, idx: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Rows `idx` of a ragged column (Arrow offsets int64 [n + 1] into `data`): (data', offsets' [m + 1])."""
+    a = offsets.index_select(0, idx)
+    lens = offsets.index_select(0, idx + 1) - a
+    new_off = torch.zeros(idx.numel() + 1, dtype=torch.int64, device=offsets.device)
+    new_off[1:] = torch.cumsum(lens, 0)
+    total = int(new_off[-1].item())
+    if total == 0:
+        return torch.zeros(1, dtype=data.dtype, device=data.device), new_off
+    src = torch.repeat_interleave(a - new_off[:-1], lens) + torch.arange(total, device=data.device)
+    return data.index_select(0, src), new_off
+
+
 @dataclass
 class NumericBlock:
     names: List[str]
@@ -104,6 +128,15 @@ class NumericBlock:
             v = self.values.index_select(0, sel)
             m = None if self.valid is None else self.valid.index_select(0, sel)
         return NumericBlock([self.names[i] for i in idx], self.type_name, v, m, self.n)
+
+    def take_rows(self, idx: torch.Tensor) -> "NumericBlock":
+        """The rows `idx` (int64 tensor on the block's device) as a block of their own."""
+        m = idx.numel()
+        ld = round_up(max(m, 1), 16 if self.values.dtype == torch.uint8 else 2)
+        vals = torch.zeros((self.values.shape[0], ld), dtype=self.values.dtype, device=self.values.device)
+        vals[:, :m] = self.values.index_select(1, idx)
+        valid = None if self.valid is None else take_bitmap(self.valid, idx)
+        return NumericBlock(self.names, self.type_name, vals, valid, m)
 
     def to(self, device) -> "NumericBlock":
         return NumericBlock(self.names, self.type_name, self.values.to(device, non_blocking=True),
@@ -188,6 +221,13 @@ class DictBlock:
             c = self.codes.index_select(0, torch.as_tensor(idx, device=self.codes.device))
         return DictBlock([self.names[i] for i in idx], self.type_name, c, [self.dicts[i] for i in idx], self.n)
 
+    def take_rows(self, idx: torch.Tensor) -> "DictBlock":
+        m = idx.numel()
+        codes = torch.full((self.codes.shape[0], round_up(max(m, 1), 4)), -1, dtype=torch.int32,
+                           device=self.codes.device)
+        codes[:, :m] = self.codes.index_select(1, idx)
+        return DictBlock(self.names, self.type_name, codes, self.dicts, m)
+
     def to(self, device) -> "DictBlock":
         return DictBlock(self.names, self.type_name, self.codes.to(device, non_blocking=True), self.dicts, self.n)
 
@@ -237,6 +277,11 @@ class SetBlock:
         return SetBlock([self.names[i] for i in idx], self.type_name, [self.offsets[i] for i in idx],
                         [self.codes[i] for i in idx], [self.dicts[i] for i in idx], self.n)
 
+    def take_rows(self, idx: torch.Tensor) -> "SetBlock":
+        pairs = [take_ragged(c, o, idx) for c, o in zip(self.codes, self.offsets)]
+        return SetBlock(self.names, self.type_name, [p[1] for p in pairs], [p[0] for p in pairs], self.dicts,
+                        idx.numel())
+
     def to(self, device) -> "SetBlock":
         mv = lambda t: t.to(device, non_blocking=True)  # noqa: E731
         return SetBlock(self.names, self.type_name, [mv(t) for t in self.offsets], [mv(t) for t in self.codes],
@@ -283,6 +328,11 @@ class TextBlock:
         idx = list(idx)
         return TextBlock([self.names[i] for i in idx], self.type_name, [self.data[i] for i in idx],
                          [self.offsets[i] for i in idx], [self.valid[i] for i in idx], self.n)
+
+    def take_rows(self, idx: torch.Tensor) -> "TextBlock":
+        pairs = [take_ragged(d, o, idx) for d, o in zip(self.data, self.offsets)]
+        valid = [None if v is None else take_bitmap(v, idx) for v in self.valid]
+        return TextBlock(self.names, self.type_name, [p[0] for p in pairs], [p[1] for p in pairs], valid, idx.numel())
 
     def to(self, device) -> "TextBlock":
         mv = lambda t: None if t is None else t.to(device, non_blocking=True)  # noqa: E731
@@ -529,10 +579,23 @@ class VectorColumn:
     metadata: OpVectorMetadata
     parts: List[object]                  # DensePart | CsrPart, in output-column order
     stats: Optional[object] = None       # stages.sanity.VectorStats sidecar
+    producer: Optional[object] = field(default=None, compare=False, repr=False)   # the transformer that made it
 
     @property
     def width(self) -> int:
         return sum(p.width for p in self.parts)
+
+    def recompute(self, full: "ColumnarBatch", sub: "ColumnarBatch") -> "VectorColumn":
+        """This vector over another batch of raw columns (`sub`, e.g. a row sample of `full`): the transformer that
+        produced it is run again, after the vectors it takes as input have been recomputed the same way."""
+        if self.producer is None:
+            raise ValueError(f"vector '{self.name}' does not know the stage that produced it")
+        for f in self.producer.inN:
+            if f.name in full.vectors and f.name not in sub.vectors:
+                sub = sub.with_vector(full.vectors[f.name].recompute(full, sub))
+        out = self.producer.transformColumn(sub)
+        out.producer = self.producer
+        return out
 
     def to_scipy(self):
         import scipy.sparse as sp
@@ -637,6 +700,11 @@ class ColumnarBatch:
         out = ColumnarBatch(self.n, self.blocks, dict(self.vectors), self.response)
         out.vectors[v.name] = v
         return out
+
+    def take_rows(self, idx: torch.Tensor) -> "ColumnarBatch":
+        """The raw columns of the rows `idx` (int64 tensor on the blocks' device) as a batch of their own (what
+        Dataset.sample leaves); vector columns are not carried over."""
+        return ColumnarBatch(int(idx.numel()), [b.take_rows(idx) for b in self.blocks], {}, self.response)
 
     def to(self, device) -> "ColumnarBatch":
         return ColumnarBatch(self.n, [b.to(device) for b in self.blocks], dict(self.vectors), self.response)

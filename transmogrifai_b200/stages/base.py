@@ -94,7 +94,9 @@ class OpTransformer(OpPipelineStage):
         raise NotImplementedError
 
     def transform(self, batch: ColumnarBatch) -> ColumnarBatch:
-        return batch.with_vector(self.transformColumn(batch))
+        vec = self.transformColumn(batch)
+        vec.producer = self
+        return batch.with_vector(vec)
 
 
 class OpModel(OpTransformer):

@@ -218,9 +218,9 @@ class SanityChecker(OpEstimator):
             raise ValueError("requirement failed: Sample size cannot be zero")
         frac = self.fraction(n)
         if frac < 1.0:
-            raise NotImplementedError(
-                f"SanityChecker sampling (fraction {frac:.4g} < 1) is not on the GPU path: set checkSample = 1.0 and "
-                "sampleUpperLimit >= the row count (the reference default down-samples to 1e6 rows at random)")
+            batch, vec, n = self._sample(batch, vec, frac)
+            if n <= 0:
+                raise ValueError("requirement failed: Sample size cannot be zero")
         meta = vec.metadata
         d = vec.width
         if d <= 0:
@@ -286,6 +286,25 @@ class SanityChecker(OpEstimator):
             raise ValueError("requirement failed: The sanity checker has dropped all of your features, check your "
                              "input data quality")
         return SanityCheckerModel(self, keep, self.removeBadFeatures)
+
+    def _sample(self, batch: ColumnarBatch, vec, frac: float):
+        """data.sample(withReplacement = false, fraction, seed) (SanityChecker.scala:381-387): every row is kept with
+        probability `frac` (a counter-based generator on the device, seeded with sampleSeed -- Spark's per-partition
+        XORShift stream is not restated, so the sample is a different one with the same law).  The sampled raw rows
+        form a batch of their own, the upstream transformers run again on it, and the statistics are those of the
+        resulting vector (no statistics sidecar applies to a sample)."""
+        if D.world()[1] > 1:
+            raise NotImplementedError("SanityChecker sampling over several ranks: set checkSample = 1.0 and "
+                                      "sampleUpperLimit >= the row count")
+        dev = "cuda" if any(getattr(b, "is_cuda", False) for b in batch.blocks) else "cpu"
+        g = torch.Generator(device=dev).manual_seed(int(self.sampleSeed))
+        idx = (torch.rand(batch.n, device=dev, generator=g) < frac).nonzero().squeeze(1)
+        on_dev = lambda b: b if getattr(b, "is_cuda", dev == "cuda") == (dev == "cuda") else b.to(dev)  # noqa: E731
+        full = ColumnarBatch(batch.n, [on_dev(b) for b in batch.blocks], batch.vectors, batch.response)
+        sub = full.take_rows(idx)
+        svec = vec.recompute(batch, sub)
+        svec.stats = None
+        return sub.with_vector(svec), svec, int(idx.numel())
 
     @staticmethod
     def _plan(meta: OpVectorMetadata) -> "_MetaPlan":
