@@ -215,7 +215,7 @@ class SmartTextVectorizer(OpEstimator):
         over = [c for c in range(ncols) if values[c] is None]
         self._prefix = {}
         if over:                                  # one fetch and one cleaning call for all of them
-            rows0 = min(4 * (self.maxCardinality + 8), n)
+            rows0 = min(self._prefix_rows(), n)
             fetched = dev.prefix_cells_many(over, rows0)
             flat = [v for c in over for v in fetched[c] if v is not None]
             ids, distinct = clean_and_group(flat, self.cleanText)
@@ -310,11 +310,16 @@ class SmartTextVectorizer(OpEstimator):
             merged.append(acc)
         return merged
 
+    def _prefix_rows(self) -> int:
+        """Rows fetched at first for a column past the cap: free text shows maxCardinality + 1 distinct values within
+        about that many rows; a column that needs more is fetched again, four times as far."""
+        return 2 * (self.maxCardinality + 8)
+
     def _frozen_counts(self, dev: TextBlock, c: int, n: int, seed: Optional[Dict[str, int]] = None) -> Dict[str, int]:
         """TextStats of a column whose cardinality exceeds maxCardinality: the reference's left fold stops adding once
         its map holds more than maxCardinality keys (SmartTextVectorizer.scala:231-235), so only a prefix of the rows
         counts.  Emulated in row order on a prefix fetched to the host (`seed`: the map of the ranks before)."""
-        rows = 4 * (self.maxCardinality + 8)
+        rows = self._prefix_rows()
         first = True
         while True:
             rows = min(rows, n)
