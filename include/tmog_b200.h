@@ -178,6 +178,11 @@ int tmog_pivot_column_finish(const uint8_t* dict_data, const int64_t* dict_offse
  * the Algebird map monoid in OpOneHotVectorizer.fitFn, OpOneHotVectorizer.scala:95-97) -- runs on host threads while
  * the count kernel is still busy on the GPU.  prepare() returns an opaque handle (thread-safe, one per column);
  * finish() takes the counts and produces what tmog_pivot_column_finish does; free() releases the handle. */
+/* 64-bit digest of a byte range (host).  Ranks that exported their partitions separately compare the digests of their
+ * dictionaries (bytes and offsets, two seeds) to see whether the count tables can be summed as they are or must first
+ * be re-indexed against the union dictionary -- the bookkeeping Spark's map-monoid reduce does by key. */
+int tmog_hash_bytes(const uint8_t* data, int64_t nbytes, uint64_t seed, uint64_t* out);
+
 typedef struct tmog_pivot_dict tmog_pivot_dict;
 int tmog_pivot_dict_prepare(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes, int clean_text,
                             tmog_pivot_dict** out);

@@ -52,6 +52,7 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_dedupe_strings": [_p, _p, _i64, _p, _p],
     "tmog_pivot_topk": [_p, _p, _p, _i64, _int, _i64, _p, _p],
     "tmog_pivot_column_finish": [_p, _p, _i64, _int, _p, _int, _int, _i64, _p, _p, _p, _p, _i64, _p],
+    "tmog_hash_bytes": [_p, _i64, C.c_uint64, _p],
     "tmog_pivot_dict_prepare": [_p, _p, _i64, _int, _p],
     "tmog_pivot_dict_finish": [_p, _p, _int, _int, _i64, _p, _p, _p, _p, _i64, _p],
     "tmog_pivot_dict_free": [_p],

@@ -388,6 +388,50 @@ extern "C" int tmog_pivot_dict_finish(const tmog_pivot_dict* d, const int64_t* r
     return TMOG_OK;
 }
 
+// 64-bit digest of a byte range (eight bytes per step): what the ranks compare to find out whether they encoded their
+// rows against the same dictionary.
+extern "C" int tmog_hash_bytes(const uint8_t* data, int64_t nbytes, uint64_t seed, uint64_t* out) {
+    TMOG_REQUIRE(nbytes >= 0 && out != nullptr && (data != nullptr || nbytes == 0), "NULL argument");
+    auto rotl = [](uint64_t x, int r) { return (x << r) | (x >> (64 - r)); };
+    auto mix = [&](uint64_t h, uint64_t w) {
+        w *= 0x87c37b91114253d5ull;
+        w = rotl(w, 31);
+        w *= 0x4cf5ad432745937full;
+        h ^= w;
+        return rotl(h, 27) * 5 + 0x52dce729;
+    };
+    // four independent lanes (32 bytes per step) so that the multiplies overlap; the lanes are folded at the end
+    uint64_t h0 = seed ^ ((uint64_t)nbytes * 0x9E3779B97F4A7C15ull), h1 = h0 ^ 0x6a09e667f3bcc909ull,
+             h2 = h0 ^ 0xbb67ae8584caa73bull, h3 = h0 ^ 0x3c6ef372fe94f82bull;
+    const uint8_t* p = data;
+    int64_t left = nbytes;
+    while (left >= 32) {
+        uint64_t w[4];
+        memcpy(w, p, 32);
+        h0 = mix(h0, w[0]);
+        h1 = mix(h1, w[1]);
+        h2 = mix(h2, w[2]);
+        h3 = mix(h3, w[3]);
+        p += 32;
+        left -= 32;
+    }
+    while (left > 0) {
+        uint64_t w = 0;
+        memcpy(&w, p, (size_t)(left >= 8 ? 8 : left));
+        h0 = mix(h0, w);
+        p += 8;
+        left -= 8;
+    }
+    uint64_t h = mix(mix(mix(h0, h1), h2), h3);
+    h ^= h >> 33;
+    h *= 0xff51afd7ed558ccdull;
+    h ^= h >> 33;
+    h *= 0xc4ceb9fe1a85ec53ull;
+    h ^= h >> 33;
+    *out = h;
+    return TMOG_OK;
+}
+
 extern "C" int tmog_pivot_column_finish(const uint8_t* dict_data, const int64_t* dict_offsets, int64_t ncodes,
                                         int clean_text, const int64_t* raw_counts, int nclasses, int top_k,
                                         int64_t min_support, int* n_top, int32_t* code_to_out,

@@ -127,7 +127,8 @@ class OpTextPivotVectorizer(OpEstimator):
         ncols = len(block.dicts)
         if D.world()[1] == 1:
             return block.dicts, [None] * ncols
-        sigs = D.all_gather_object([_dict_signature(*block.dict_arrays(c)) for c in range(ncols)])
+        local = list(_pool().map(lambda c: _dict_signature(*block.dict_arrays(c)), range(ncols)))
+        sigs = D.all_gather_object(local)
         differ = [c for c in range(ncols) if any(s[c] != sigs[0][c] for s in sigs)]
         dicts, maps = list(block.dicts), [None] * ncols
         if differ:
@@ -160,8 +161,12 @@ class OpTextPivotVectorizer(OpEstimator):
 
         # One process: the dictionaries are final, so their cleaning starts now, largest first, and runs on host
         # threads while the label classes and the count kernel are on the GPU.
+        # Ranks may have encoded their rows against different dictionaries (one per exported partition): the count
+        # tables are then re-indexed against the union dictionary (rank order) before they are summed.  Where all ranks
+        # share their dictionaries (compared by digest) the cleaning can start at once as well.
+        g_dicts, g_maps = self._union_dictionaries(block)
         early = None
-        if D.world()[1] == 1 and ncols > 0:
+        if ncols > 0 and all(m is None for m in g_maps):
             order = sorted(range(ncols), key=lambda c: -int(ncodes[c]))
             futs = {c: _pool().submit(prepare, *block.dict_arrays(c), int(ncodes[c])) for c in order}
             early = futs
@@ -182,13 +187,20 @@ class OpTextPivotVectorizer(OpEstimator):
         L.call("tmog_pivot_count_dev", dev.codes.data_ptr(), dev.ld, n, ncols,
                ids.data_ptr() if classes is not None else None, ncls, d_desc.data_ptr(), None,
                int(nids.max()) if ncols else 1, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
-        counts = d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF
+        shared_dicts = all(m is None for m in g_maps)
+        if D.world()[1] > 1 and shared_dicts:
+            # every rank counted against the same dictionaries: the tables add up on the device, one copy back
+            g_dev = d_counts.to(torch.int64) & 0xFFFFFFFF
+            torch.distributed.all_reduce(g_dev)
+            counts = g_dev.cpu().numpy()
+        else:
+            counts = d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF
         if int(d_bad.item()):
             raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
-        n_global = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
-        # Ranks may have encoded their rows against different dictionaries (one per exported partition): the count
-        # tables are then re-indexed against the union dictionary (rank order) before they are summed.
-        g_dicts, g_maps = self._union_dictionaries(block)
+        if classes is not None:
+            n_global = int(np.asarray(counts_per_class).sum())          # rows of all ranks, from the label classes
+        else:
+            n_global = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
         g_ncodes = np.array([len(d) for d in g_dicts], dtype=np.int64)
         g_offset = np.concatenate([[0], np.cumsum((g_ncodes + 1) * ncls)[:-1]]).astype(np.int64) if ncols else zeros
         if any(m is not None for m in g_maps):
@@ -202,7 +214,8 @@ class OpTextPivotVectorizer(OpEstimator):
                     dst[0] = loc[0]                                   # the null id
                     dst[1 + g_maps[c]] = loc[1:]
             counts = g_counts
-        counts = D.allreduce_sum(counts)
+        if not (D.world()[1] > 1 and shared_dicts):
+            counts = D.allreduce_sum(counts)
 
         def finish(c: int):
             nc = int(g_ncodes[c])
@@ -287,10 +300,13 @@ _POOL = None
 
 def _dict_signature(data: np.ndarray, offs: np.ndarray) -> str:
     """Digest of a dictionary in Arrow utf8 layout."""
-    import hashlib
-    h = hashlib.sha1(data.tobytes())
-    h.update(offs.tobytes())
-    return h.hexdigest()
+    out = []
+    for arr, seed in ((data, 1), (offs, 2)):
+        h = C.c_uint64(0)
+        a = np.ascontiguousarray(arr)
+        L.call("tmog_hash_bytes", a.ctypes.data, a.nbytes, seed, C.byref(h))
+        out.append(h.value)
+    return "%016x%016x" % tuple(out)
 
 
 def _pool():

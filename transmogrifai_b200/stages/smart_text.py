@@ -206,6 +206,7 @@ class SmartTextVectorizer(OpEstimator):
         block = batch.texts(names)
         dev = block if block.is_cuda else block.to("cuda")
         n, ncols = batch.n, len(names)
+        self._prefix = {}                          # cleaned first rows of the columns past the cap, of THIS batch
         # 1. TextStats per column (merged over the ranks like the reference's reduce over partitions)
         values, totals = self._text_stats(dev, n)
         values = self._merge_text_stats(values, dev, n)
@@ -213,17 +214,8 @@ class SmartTextVectorizer(OpEstimator):
         # columns past the cardinality cap need the first rows on the host (the reference's fold freezes there): fetch
         # them for all such columns at once
         over = [c for c in range(ncols) if values[c] is None]
-        self._prefix = {}
-        if over:                                  # one fetch and one cleaning call for all of them
-            rows0 = min(self._prefix_rows(), n)
-            fetched = dev.prefix_cells_many(over, rows0)
-            flat = [v for c in over for v in fetched[c] if v is not None]
-            ids, distinct = clean_and_group(flat, self.cleanText)
-            at = 0
-            for c in over:
-                k = sum(v is not None for v in fetched[c])
-                self._prefix[c] = (rows0, [distinct[i] for i in ids[at:at + k]])
-                at += k
+        if over:
+            self._fetch_prefix(dev, over, n)
         for c in range(ncols):
             m, top = self._decide(values[c], totals[c], dev, c, n)
             methods.append(m)
@@ -292,23 +284,43 @@ class SmartTextVectorizer(OpEstimator):
         if size == 1:
             return values
         gathered = D.all_gather_object(values)
-        merged = []
+        merged, frozen_by = [], {}
         for c in range(len(values)):
             acc: Dict[str, int] = {}
-            freezer = None
             for r in range(size):
                 vc = gathered[r][c]
                 if vc is not None and len(set(acc) | set(vc)) <= self.maxCardinality:
                     for k, v in vc.items():
                         acc[k] = acc.get(k, 0) + v
                 else:
-                    freezer = r
+                    frozen_by[c] = r
                     break
-            if freezer is not None:
-                res = self._frozen_counts(dev, c, n, seed=acc) if rank == freezer else None
-                acc = D.broadcast_object(res, src=freezer)
             merged.append(acc)
+        if frozen_by:
+            # every rank continues the fold for the columns that freeze in its rows (their first rows fetched and
+            # cleaned in one go), then ONE exchange hands all the frozen maps round
+            mine = [c for c, r in frozen_by.items() if r == rank]
+            if mine:
+                self._fetch_prefix(dev, mine, n)
+            res = {c: self._frozen_counts(dev, c, n, seed=merged[c]) for c in mine}
+            for per_rank in D.all_gather_object(res):
+                for c, vc in per_rank.items():
+                    merged[c] = vc
         return merged
+
+    def _fetch_prefix(self, dev: TextBlock, cols: List[int], n: int) -> None:
+        """The cleaned values of the first rows of several columns with one fetch and one cleaning call."""
+        if not hasattr(self, "_prefix"):
+            self._prefix = {}
+        rows0 = min(self._prefix_rows(), n)
+        fetched = dev.prefix_cells_many(cols, rows0)
+        flat = [v for c in cols for v in fetched[c] if v is not None]
+        ids, distinct = clean_and_group(flat, self.cleanText)
+        at = 0
+        for c in cols:
+            k = sum(v is not None for v in fetched[c])
+            self._prefix[c] = (rows0, [distinct[i] for i in ids[at:at + k]])
+            at += k
 
     def _prefix_rows(self) -> int:
         """Rows fetched at first for a column past the cap: free text shows maxCardinality + 1 distinct values within
