@@ -348,7 +348,7 @@ def main():
     ap.add_argument("--workload", default="c2", choices=list(benchdata.WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="rows per GPU (0 = the workload's default)")
     ap.add_argument("--impl", default="tmog", choices=["tmog", "reference"])
-    ap.add_argument("--cpu-rows", type=int, default=1_000_000, help="rows of the bounded CPU-baseline sample (c2)")
+    ap.add_argument("--cpu-rows", type=int, default=4_000_000, help="rows of the bounded CPU-baseline sample (c2)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
