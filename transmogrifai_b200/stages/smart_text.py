@@ -621,9 +621,12 @@ class SmartTextVectorizerModel(OpModel):
                 cs, nz, ex, ax = cs[:lay.hash_width], nz[:lay.hash_width], ex[:lay.hash_width], ax[:lay.hash_width]
             self._hash_nnz = nz                      # of the local rows: sizes the sparse output of the same batch
             if D.world()[1] > 1:
-                cs, nz, ex = D.allreduce_sum(cs), D.allreduce_sum(nz), D.allreduce_sum(ex)
-                ax = np.stack([D.allreduce_max(ax[:, 0].copy()), D.allreduce_max(ax[:, 1].copy()),
-                               D.allreduce_sum(ax[:, 2].copy())], axis=1)
+                # two exchanges in all: everything that adds (counts below 2^53, exact in f64), everything that maxes
+                sums = D.allreduce_sum(np.concatenate([cs.reshape(-1), nz, ex, ax[:, 2].astype(np.float64)]))
+                maxs = D.allreduce_max(np.concatenate([ax[:, 0], ax[:, 1]]))
+                k, m = cs.size, len(nz)
+                cs, nz, ex = sums[:k].reshape(cs.shape), sums[k:k + m], sums[k + m:k + 2 * m]
+                ax = np.stack([maxs[:m], maxs[m:], sums[k + 2 * m:].astype(np.int64)], axis=1)
             if cont is None:
                 parts.append(_stats_from_bucket_sums(cs, nz, ex, ax, classes, class_counts, n_all, label_name,
                                                      lay.hash_width))
