@@ -136,3 +136,79 @@ def test_two_ranks_all_types_match_oracle():
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(0, "ok"), (1, "ok")], "\n".join(str(r[1]) for r in res)
+
+
+def _worker_sampled(rank, size, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=size)
+    try:
+        from oracle import sanity as S
+        from oracle import vectorizers as V
+        from transmogrifai_b200 import dist as D
+        from transmogrifai_b200 import features as F
+        from transmogrifai_b200.columnar import ColumnarBatch
+        from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+        n, seed = 8192, 11
+        data, y = _make_data(n)
+        keep = ("b0", "p0", "r0", "nn", "y")
+        lo, hi = D.shard_rows(n, rank, size)
+        shard = {k: (data[k][0], data[k][1][lo:hi]) for k in keep}
+        batch = ColumnarBatch.from_columns(shard, response="y").to("cuda")
+        FB = F.FeatureBuilder
+        feats = [FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(), FB.RealNN("nn").asPredictor(),
+                 FB.PickList("p0").asPredictor()]
+        label = FB.RealNN("y").asResponse()
+        checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, checkSample=0.5, sampleLowerLimit=0,
+                                    sampleUpperLimit=10 ** 9, sampleSeed=seed, featureFeatureCorrLevel="Computed")
+        out_batch, fitted = fit_and_transform(batch, checked)
+        est = checked.origin_stage
+        # the rows every rank sampled from its shard (its own stream: seed + rank), in global numbering
+        idx = []
+        for r in range(size):
+            a, b = D.shard_rows(n, r, size)
+            g = torch.Generator(device="cuda").manual_seed(seed + r)
+            idx.append(a + (torch.rand(b - a, device="cuda", generator=g) < 0.5).nonzero().squeeze(1).cpu().numpy())
+        idx = np.concatenate(idx)
+        col = lambda k: data[k][1]   # noqa: E731
+        xb = V.binary_vectorizer_transform([col("b0")])
+        tops = V.pivot_fit([col("p0")], 20, 10, True)
+        xp = V.pivot_transform([col("p0")], tops, True, True)
+        fills = V.real_vectorizer_fit([col("r0")])
+        xr = V.real_vectorizer_transform([col("r0")], fills, True)
+        xn = V.realnn_vectorizer_transform([col("nn")])
+        xo, metas = V.combine(
+            [xb, xp, xr, xn],
+            [V.numeric_metadata(["b0"], "Binary", True), V.pivot_metadata(["p0"], "PickList", tops, True),
+             V.numeric_metadata(["r0"], "Real", True), V.numeric_metadata(["nn"], "RealNN", False)])
+        p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                           feature_feature_corr_level="computed")
+        xs = xo.tocsr()[idx] if hasattr(xo, "tocsr") else xo[idx]
+        ref = S.sanity_fit(y[idx], xs, metas, p, label_name="y")
+        assert est.summary.count == len(idx)
+        assert est.summary.dropped == ref.dropped
+        assert fitted[-1].indicesToKeep == ref.indices_to_keep
+        np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300)
+        np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+        np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                                   equal_nan=True)
+        q.put((rank, "ok"))
+    except Exception:  # pragma: no cover
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_sampled_sanity_checker_matches_oracle():
+    """fraction() < 1 over two row shards: every rank samples its shard, the statistics of the samples are merged."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_sampled, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, "ok"), (1, "ok")], "\n".join(str(r[1]) for r in res)

@@ -10,6 +10,7 @@ import numpy as np
 import torch
 
 from .. import _lib as L
+from .. import dist as DD
 from .. import runtime as R
 from ..columnar import (ColumnarBatch, CsrPart, DensePart, LazyDensePart, LazyOneHotPart, LazyPart, OneHotPart,
                         VectorColumn)
@@ -76,10 +77,14 @@ def vector_stats(batch: ColumnarBatch, vec: VectorColumn, label_name: str) -> Ve
     ncls = 0 if classes is None else len(classes)
     class_sums = torch.zeros((max(ncls, 1), d), dtype=torch.float64, device="cuda") if ncls else None
     L.call("tmog_dense_pilot_shift_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), shifts.data_ptr(), R.stream())
+    if DD.world()[1] > 1:                                  # partials only merge under common shifts (rank 0's)
+        torch.distributed.broadcast(shifts, src=0)
     L.call("tmog_dense_stats_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), ids.data_ptr() if ncls else None,
            ncls, d_cat.data_ptr(), shifts.data_ptr(), scratch.data_ptr(), scratch.numel(), partials.data_ptr(),
            R.ptr(class_sums), R.stream())
-    p = partials.cpu().numpy()
+    p, _ = DD.gather_fit_results(partials)                 # rows of all ranks
+    if DD.world()[1] > 1 and class_sums is not None:
+        torch.distributed.all_reduce(class_sums)
     s = shifts.cpu().numpy()
     mean, var, mn, mx, cov = (np.zeros(d) for _ in range(5))
     lab = np.zeros(5)
@@ -89,7 +94,7 @@ def vector_stats(batch: ColumnarBatch, vec: VectorColumn, label_name: str) -> Ve
     if ncls:
         cs = class_sums.cpu().numpy()
         cs[:, cat == 0] = np.nan
-    st = VectorStats(LabelInfo(label_name, n, lab, classes, counts), mean, var, mn, mx, cov, cs)
+    st = VectorStats(LabelInfo(label_name, int(lab[0]), lab, classes, counts), mean, var, mn, mx, cov, cs)
     st._shifted_sums = (s, p.reshape(d + 1, L.REAL_NSTAT)[:, 1].copy())
     return st
 
@@ -112,8 +117,11 @@ def pearson_matrix(batch: ColumnarBatch, vec: VectorColumn, label_name: str, cor
     d = x.shape[1]
     y = _device_label(batch, label_name)
     D = d + 1
+    dist_world = DD.world()[1]
     shifts = torch.zeros(D, dtype=torch.float64, device="cuda")
     L.call("tmog_dense_pilot_shift_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), shifts.data_ptr(), R.stream())
+    if dist_world > 1:
+        torch.distributed.broadcast(shifts, src=0)
     nb = C.c_size_t()
     L.call("tmog_dense_stats_scratch_bytes", n, d, C.byref(nb))
     scratch = R.scratch("dense_stats", nb.value)
@@ -123,10 +131,15 @@ def pearson_matrix(batch: ColumnarBatch, vec: VectorColumn, label_name: str, cor
     gram = torch.zeros((D, D), dtype=torch.float64, device="cuda")
     L.call("tmog_dense_gram_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), shifts.data_ptr(), gram.data_ptr(),
            R.stream())
+    if dist_world > 1:                                     # Gramian and sums of the shifted rows add up over the ranks
+        torch.distributed.all_reduce(gram)
     g = gram.cpu().numpy()
-    sums = np.ascontiguousarray(partials.cpu().numpy().reshape(D, L.REAL_NSTAT)[:, 1])
+    merged, _ = DD.gather_fit_results(partials)
+    merged = merged.reshape(D, L.REAL_NSTAT)
+    sums = np.ascontiguousarray(merged[:, 1])
+    n_all = float(merged[D - 1, 7]) if dist_world > 1 else float(n)
     corr = np.zeros((D, D))
-    L.call("tmog_pearson_from_gram", D, float(n), g.ctypes.data, sums.ctypes.data, corr.ctypes.data)
+    L.call("tmog_pearson_from_gram", D, n_all, g.ctypes.data, sums.ctypes.data, corr.ctypes.data)
     return corr
 
 

@@ -293,18 +293,16 @@ class SanityChecker(OpEstimator):
         XORShift stream is not restated, so the sample is a different one with the same law).  The sampled raw rows
         form a batch of their own, the upstream transformers run again on it, and the statistics are those of the
         resulting vector (no statistics sidecar applies to a sample)."""
-        if D.world()[1] > 1:
-            raise NotImplementedError("SanityChecker sampling over several ranks: set checkSample = 1.0 and "
-                                      "sampleUpperLimit >= the row count")
         dev = "cuda" if any(getattr(b, "is_cuda", False) for b in batch.blocks) else "cpu"
-        g = torch.Generator(device=dev).manual_seed(int(self.sampleSeed))
+        g = torch.Generator(device=dev).manual_seed(int(self.sampleSeed) + D.world()[0])   # a stream per row shard
         idx = (torch.rand(batch.n, device=dev, generator=g) < frac).nonzero().squeeze(1)
         on_dev = lambda b: b if getattr(b, "is_cuda", dev == "cuda") == (dev == "cuda") else b.to(dev)  # noqa: E731
         full = ColumnarBatch(batch.n, [on_dev(b) for b in batch.blocks], batch.vectors, batch.response)
         sub = full.take_rows(idx)
         svec = vec.recompute(batch, sub)
         svec.stats = None
-        return sub.with_vector(svec), svec, int(idx.numel())
+        m = int(D.allreduce_sum(np.array([idx.numel()], dtype=np.int64))[0])      # sampled rows of all ranks
+        return sub.with_vector(svec), svec, m
 
     @staticmethod
     def _plan(meta: OpVectorMetadata) -> "_MetaPlan":
