@@ -54,6 +54,22 @@ def test_integral_vectorizer_reference_golden(device):
     assert [c.parentFeatureType for c in cols][0] == ("Integral",)
 
 
+@pytest.mark.parametrize("type_name", ["Date", "DateTime"])
+def test_integral_vectorizer_on_date_types(type_name):
+    # IntegralVectorizerTest.scala:57-74 (data), :240-305 (DateTime and Date columns vectorize like Integral ones)
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.integral import IntegralVectorizer
+    batch = _batch({n: (type_name, c) for n, c in zip(NAMES, [A, B, CC, DD])})
+    feats = [F.FeatureBuilder.of(type_name, nm).asPredictor() for nm in NAMES]
+    est = IntegralVectorizer().setInput(*feats)
+    m = est.setFillWithMode().setTrackNulls(False).fit(batch)
+    assert m.fillValues == [4, 2, 1, 0]
+    got = m.transform(batch).vectors[est.getOutput().name].to_numpy()
+    assert got.tolist() == [[4.0, 2.0, 2.0, 0.0], [4.0, 2.0, 1.0, 0.0], [2.0, 4.0, 1.0, 0.0], [4.0, 2.0, 2.0, 0.0],
+                            [4.0, 2.0, 1.0, 0.0]]
+    assert est.getMetadata().columns[0].parentFeatureType == (type_name,)
+
+
 def _random_columns(rng, n):
     cols = []
     cols.append([None if rng.random() < 0.1 else int(rng.integers(0, 7)) for _ in range(n)])           # few values

@@ -146,7 +146,7 @@ class NumericBlock:
     def from_lists(names: Sequence[str], type_name: str, columns: Sequence[Sequence], pin: bool = True
                    ) -> "NumericBlock":
         n = len(columns[0]) if columns else 0
-        binary, integral = type_name == F.BINARY, type_name == F.INTEGRAL
+        binary, integral = type_name == F.BINARY, type_name in F.INTEGRAL_TYPES
         ld = round_up(max(n, 1), 16 if binary else 2)
         vals = np.zeros((len(columns), ld), dtype=np.uint8 if binary else np.int64 if integral else np.float64)
         ok = np.zeros((len(columns), n), dtype=bool)

@@ -11,13 +11,15 @@ from dataclasses import dataclass, field
 from typing import Optional, Tuple
 
 REAL, REALNN, BINARY, INTEGRAL = "Real", "RealNN", "Binary", "Integral"
+DATE, DATETIME = "Date", "DateTime"                 # Integral subtypes (epoch milliseconds as int64)
+INTEGRAL_TYPES = (INTEGRAL, DATE, DATETIME)
 PICKLIST, MULTIPICKLIST = "PickList", "MultiPickList"
 TEXT, TEXTAREA = "Text", "TextArea"
 OPVECTOR = "OPVector"
 
-NUMERIC_TYPES = (REAL, REALNN, BINARY, INTEGRAL)
+NUMERIC_TYPES = (REAL, REALNN, BINARY, INTEGRAL, DATE, DATETIME)
 TEXT_TYPES = (TEXT, TEXTAREA)
-ALL_TYPES = (REAL, REALNN, BINARY, INTEGRAL, PICKLIST, MULTIPICKLIST, TEXT, TEXTAREA, OPVECTOR)
+ALL_TYPES = (REAL, REALNN, BINARY, INTEGRAL, DATE, DATETIME, PICKLIST, MULTIPICKLIST, TEXT, TEXTAREA, OPVECTOR)
 
 _uid_counter = itertools.count(1)
 
@@ -79,6 +81,8 @@ class FeatureBuilder:
     RealNN = staticmethod(lambda name: _Builder(name, REALNN))
     Binary = staticmethod(lambda name: _Builder(name, BINARY))
     Integral = staticmethod(lambda name: _Builder(name, INTEGRAL))
+    Date = staticmethod(lambda name: _Builder(name, DATE))
+    DateTime = staticmethod(lambda name: _Builder(name, DATETIME))
     PickList = staticmethod(lambda name: _Builder(name, PICKLIST))
     MultiPickList = staticmethod(lambda name: _Builder(name, MULTIPICKLIST))
     Text = staticmethod(lambda name: _Builder(name, TEXT))

@@ -85,7 +85,7 @@ def column_modes(dev: NumericBlock, n: int) -> List[int]:
 class IntegralVectorizer(OpEstimator):
     """Fill nulls with the mode (or a constant) and optionally emit a null indicator per input."""
 
-    input_types = (F.INTEGRAL,)
+    input_types = F.INTEGRAL_TYPES        # IntegralVectorizer[T <: Integral]: Integral, Date, DateTime
 
     def __init__(self, uid: Optional[str] = None):
         super().__init__("vecInt", uid)
