@@ -484,6 +484,14 @@ int tmog_contingency_stats_batch(int ngroups, const int32_t* rows, const int32_t
                                  double* mutual_info, double* pmi, double* max_conf, double* supports,
                                  int32_t* status);
 
+/* Statistics of hashed term-frequency columns (Statistics.colStats + the label covariance of OpStatistics.scala:86-90)
+ * from the per-bucket sums of tmog_text_hash_*_dev: class_sum [w][nclasses] (sum of tf per label class), nnz [w] rows
+ * holding the bucket, sq_extra [w] = sum (tf^2 - tf), aux [w][3] = {max tf, ~min tf among tf > 1, rows with tf > 1};
+ * classes [nclasses] the label values, n rows, mean_y the label mean.  Host arrays. */
+int tmog_bucket_stats(int64_t w, int nclasses, const double* class_sum, const double* nnz, const double* sq_extra,
+                      const int64_t* aux, const double* classes, double n, double mean_y, double* mean,
+                      double* variance, double* mn, double* mx, double* cov);
+
 /* corr_i = cov_i / (sqrt(var_i) sqrt(var_y) (n - 1)), 0/0 kept as NaN  (U/stats/OpStatistics.scala:92-94). */
 int tmog_pearson_from_cov(int d, double n, const double* cov_label, const double* variance, double label_variance,
                           double* corr);

@@ -90,6 +90,7 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_contingency_stats": [_p, _int, _int, _p, _p, _p, _p, _p, _p],
     "tmog_contingency_stats_batch": [_int, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "tmog_pearson_from_cov": [_int, _dbl, _p, _p, _dbl, _p],
+    "tmog_bucket_stats": [_i64, _int, _p, _p, _p, _p, _p, _dbl, _dbl, _p, _p, _p, _p, _p],
     "tmog_sanity_decide": [_int, _p, _p, _p, _int, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p],
     "tmog_real_transform_select_dev": [_p, _i64, _p, _i64, _i64, _int, _p, _int, _p, _int, _p, _i64, _i64, _p],
     "tmog_real_finish_with_fills": [_p, _p, _int, _p, _int, _p, _p, _p, _p, _p, _p, _p],

@@ -5,6 +5,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <functional>
 #include <map>
 #include <thread>
 #include <vector>
@@ -129,9 +130,15 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
     // makeColumnStatistics: max |corr| and max Cramer's V per parent feature, NaNs skipped, folded from 0.0.  Parent and
     // group ids are small dense integers, so the two maps are arrays (NaN = no entry).
     int max_parent = -1, max_group = -1;
-    for (int k = 0; k < parent_offsets[d]; ++k) {
-        TMOG_REQUIRE(parent_ids[k] >= 0, "negative parent id");
-        max_parent = std::max(max_parent, parent_ids[k]);
+    {
+        int32_t lo = 0, hi = -1;                       // plain min / max loop (vectorises; a hashed block brings millions)
+        const int64_t np_total = parent_offsets[d];
+        for (int64_t k = 0; k < np_total; ++k) {
+            lo = std::min(lo, parent_ids[k]);
+            hi = std::max(hi, parent_ids[k]);
+        }
+        TMOG_REQUIRE(lo >= 0, "negative parent id");
+        max_parent = hi;
     }
     for (int i = 0; i < d; ++i) max_group = std::max(max_group, group_id[i]);
     const double none = nan("");
@@ -144,34 +151,57 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
                                               sizeof(int32_t) * (size_t)la) == 0);
     };
     std::vector<int32_t> run_of((size_t)d, 0);      // first column of the run a column belongs to
-    for (int i0 = 0; i0 < d;) {
-        int i1 = i0 + 1;
-        while (i1 < d && same_parents(i0, i1)) ++i1;
-        bool any = false;
-        double run_max = 0.0;
-        for (int i = i0; i < i1; ++i) {
-            run_of[i] = i0;
-            if (corr_pos[i] >= 0 && corr_label) {
-                const double c = corr_label[corr_pos[i]];
-                const double ac = isnan(c) ? 0.0 : fabs(c);
-                run_max = any ? std::max(run_max, ac) : ac;
-                any = true;
+    // the pass over the columns of [lo, hi), with its own maxima per parent (a run that crosses a range boundary is
+    // simply treated as two runs)
+    auto scan_range = [&](int lo, int hi, std::vector<double>& cp, std::vector<double>& vp) {
+        for (int i0 = lo; i0 < hi;) {
+            int i1 = i0 + 1;
+            while (i1 < hi && same_parents(i0, i1)) ++i1;
+            bool any = false;
+            double run_max = 0.0;
+            for (int i = i0; i < i1; ++i) {
+                run_of[i] = i0;
+                if (corr_pos[i] >= 0 && corr_label) {
+                    const double c = corr_label[corr_pos[i]];
+                    const double ac = isnan(c) ? 0.0 : fabs(c);
+                    run_max = any ? std::max(run_max, ac) : ac;
+                    any = true;
+                }
+                // a column is in cramersVMap iff it belongs to a categorical group (rule_count >= 0); its V may be
+                // NaN.  parentMap (.toMap) keeps the LAST parent of a multi-parent column.
+                if (rule_count[i] >= 0 && parent_offsets[i + 1] > parent_offsets[i]) {
+                    const int last = parent_ids[parent_offsets[i + 1] - 1];
+                    const double av = isnan(cramers_v[i]) ? 0.0 : fabs(cramers_v[i]);
+                    double& slot = vp[last];
+                    slot = isnan(slot) ? av : std::max(slot, av);
+                }
             }
-            // a column is in cramersVMap iff it belongs to a categorical group (rule_count >= 0); its V may be NaN.
-            // parentMap (.toMap) keeps the LAST parent of a multi-parent column.
-            if (rule_count[i] >= 0 && parent_offsets[i + 1] > parent_offsets[i]) {
-                const int last = parent_ids[parent_offsets[i + 1] - 1];
-                const double av = isnan(cramers_v[i]) ? 0.0 : fabs(cramers_v[i]);
-                double& slot = cramers_parent[last];
-                slot = isnan(slot) ? av : std::max(slot, av);
-            }
+            if (any)
+                for (int k = parent_offsets[i0]; k < parent_offsets[i0 + 1]; ++k) {
+                    double& slot = cp[parent_ids[k]];
+                    slot = isnan(slot) ? run_max : std::max(slot, run_max);
+                }
+            i0 = i1;
         }
-        if (any)
-            for (int k = parent_offsets[i0]; k < parent_offsets[i0 + 1]; ++k) {
-                double& slot = corr_parent[parent_ids[k]];
-                slot = isnan(slot) ? run_max : std::max(slot, run_max);
+    };
+    const int nthreads = d >= (1 << 16) ? (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency())) : 1;
+    const int chunk = (d + nthreads - 1) / std::max(nthreads, 1);
+    if (nthreads == 1) {
+        scan_range(0, d, corr_parent, cramers_parent);
+    } else {
+        std::vector<std::vector<double>> cps((size_t)nthreads, corr_parent), vps((size_t)nthreads, cramers_parent);
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nthreads; ++t) {
+            const int lo = t * chunk, hi = std::min(d, lo + chunk);
+            if (lo < hi) pool.emplace_back(scan_range, lo, hi, std::ref(cps[t]), std::ref(vps[t]));
+        }
+        for (auto& th : pool) th.join();
+        for (int t = 0; t < nthreads; ++t)
+            for (size_t q = 0; q < corr_parent.size(); ++q) {
+                const double a = cps[t][q], v = vps[t][q];
+                if (!isnan(a)) corr_parent[q] = isnan(corr_parent[q]) ? a : std::max(corr_parent[q], a);
+                if (!isnan(v)) cramers_parent[q] = isnan(cramers_parent[q]) ? v : std::max(cramers_parent[q], v);
             }
-        i0 = i1;
     }
     // getFeaturesToDrop: groups flagged by the association-rule check
     std::vector<char> group_flagged((size_t)max_group + 1, 0);
@@ -186,13 +216,13 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
     // the per-column rules are independent of each other: wide vectors (a hashed block has hundreds of thousands of
     // columns) are split over a few threads
     auto decide_range = [&](int lo, int hi) {
-    double run_pc = nan(""), run_pv = nan("");
+    double run_pc = none, run_pv = none;
     int cur_head = -1;
     for (int i = lo; i < hi; ++i) {
         uint32_t r = 0;
         if (variance[i] <= min_variance) r |= 1u;
         const bool has_corr = corr_pos[i] >= 0 && corr_label != nullptr;
-        const double c = has_corr ? corr_label[corr_pos[i]] : nan("");
+        const double c = has_corr ? corr_label[corr_pos[i]] : none;      // (nan("") is a library call: hoisted)
         if (has_corr && fabs(c) < min_corr) r |= 2u;
         if (has_corr && fabs(c) > max_corr) r |= 4u;
         if (corr_matrix && corr_pos[i] >= 0) {
@@ -214,7 +244,7 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
         // parent-level values: max over the column's parents that have an entry (once per run of equal parent lists)
         if (run_of[i] != cur_head) {
             cur_head = run_of[i];
-            run_pc = run_pv = nan("");
+            run_pc = run_pv = none;
             for (int k = parent_offsets[cur_head]; k < parent_offsets[cur_head + 1]; ++k) {
                 const double a = corr_parent[parent_ids[k]], b = cramers_parent[parent_ids[k]];
                 if (!isnan(a)) run_pc = isnan(run_pc) ? a : std::max(run_pc, a);
@@ -232,17 +262,43 @@ extern "C" int tmog_sanity_decide(int d, const double* variance, const double* c
         if (reasons) reasons[i] = r;
     }
     };
-    const int nthreads = d >= (1 << 16) ? (int)std::min<unsigned>(8u, std::max(1u, std::thread::hardware_concurrency())) : 1;
     if (nthreads == 1) {
         decide_range(0, d);
     } else {
         std::vector<std::thread> pool;
-        const int chunk = (d + nthreads - 1) / nthreads;
         for (int t = 0; t < nthreads; ++t) {
             const int lo = t * chunk, hi = std::min(d, lo + chunk);
             if (lo < hi) pool.emplace_back(decide_range, lo, hi);
         }
         for (auto& th : pool) th.join();
+    }
+    return TMOG_OK;
+}
+
+// Column statistics of term-frequency columns from the per-bucket sums the text kernels take:
+// sum v = sum_c S_c, sum v^2 = sum v + extra, cov(v, y) = sum_c (y_c - mean_y) S_c; min / max from the rare tf > 1 words.
+extern "C" int tmog_bucket_stats(int64_t w, int nclasses, const double* class_sum, const double* nnz,
+                                 const double* sq_extra, const int64_t* aux, const double* classes, double n,
+                                 double mean_y, double* mean, double* variance, double* mn, double* mx, double* cov) {
+    TMOG_REQUIRE(w >= 0 && nclasses >= 1 && class_sum && nnz && sq_extra && aux && classes && mean && variance && mn &&
+                     mx && cov,
+                 "NULL argument");
+    for (int64_t i = 0; i < w; ++i) {
+        const double* cs = class_sum + i * nclasses;
+        double sv = 0.0, cv = 0.0;
+        for (int c = 0; c < nclasses; ++c) {
+            sv += cs[c];
+            cv += cs[c] * (classes[c] - mean_y);
+        }
+        const double sv2 = sv + sq_extra[i];
+        mean[i] = sv / n;
+        const double var = n > 1 ? (sv2 - sv * sv / n) / (n - 1) : 0.0;
+        variance[i] = var > 0.0 ? var : 0.0;
+        const int64_t a0 = aux[3 * i], a1 = aux[3 * i + 1], a2 = aux[3 * i + 2];
+        mx[i] = nnz[i] > 0 ? (double)(a0 > 1 ? a0 : 1) : 0.0;
+        const int64_t min_gt1 = (~a1) & 0xFFFFFFFFll;
+        mn[i] = nnz[i] >= n ? ((double)a2 >= nnz[i] ? (double)min_gt1 : 1.0) : 0.0;
+        cov[i] = cv;
     }
     return TMOG_OK;
 }

@@ -759,16 +759,16 @@ def _stats_from_bucket_sums(class_sum: np.ndarray, nnz: np.ndarray, sq_extra: np
     mean_y = float((classes * cc).sum() / n)
     var_y = float((cc * (classes - mean_y) ** 2).sum() / (n - 1)) if n > 1 else 0.0
     lab = np.array([n, mean_y, var_y, classes.min(), classes.max()])
-    sv = class_sum.sum(axis=1)
-    sv2 = sv + sq_extra
-    mean = sv / n
-    var = (sv2 - sv * sv / n) / (n - 1) if n > 1 else np.zeros_like(sv)
-    var = np.maximum(var, 0.0)
     # term frequencies are >= 1 where present; aux = [max tf, ~min tf among tf > 1, rows with tf > 1]
-    mx = np.where(nnz > 0, np.maximum(aux[:, 0], 1), 0).astype(np.float64)
-    min_gt1 = (~aux[:, 1]) & 0xFFFFFFFF
-    mn = np.where(nnz >= n, np.where(aux[:, 2] >= nnz, min_gt1, 1), 0).astype(np.float64)
-    cov = class_sum @ (classes - mean_y)
-    cs = np.full((len(classes), len(sv)), np.nan)
+    w = class_sum.shape[0]
+    cs64 = np.ascontiguousarray(class_sum, dtype=np.float64)
+    nz64, ex64 = np.ascontiguousarray(nnz, dtype=np.float64), np.ascontiguousarray(sq_extra, dtype=np.float64)
+    ax64 = np.ascontiguousarray(aux, dtype=np.int64)
+    cl64 = np.ascontiguousarray(classes, dtype=np.float64)
+    mean, var, mn, mx, cov = (np.empty(w) for _ in range(5))
+    L.call("tmog_bucket_stats", w, len(cl64), cs64.ctypes.data, nz64.ctypes.data, ex64.ctypes.data, ax64.ctypes.data,
+           cl64.ctypes.data, float(n), mean_y, mean.ctypes.data, var.ctypes.data, mn.ctypes.data, mx.ctypes.data,
+           cov.ctypes.data)
+    cs = np.full((len(classes), w), np.nan)
     cs[:, hash_width:] = class_sum[hash_width:].T          # null indicators are categorical columns
     return VectorStats(LabelInfo(label_name, n, lab, classes, class_counts), mean, var, mn, mx, cov, cs)
