@@ -612,11 +612,17 @@ class SmartTextVectorizerModel(OpModel):
             flags[3] = 0
             _check_hash_flags(flags)
             self._fit_rows = None if too_small else SparseRowsPart(row_start[:n], row_nnz[:n], idx, val, w)
-            cs = (class_sum.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(w, ncls).astype(np.float64)
+            # the four bucket arrays widened on the device and brought back in one copy (unsigned 32-bit words read
+            # as int64, the 64-bit extra sums as they are): a 262 144-wide block costs milliseconds of host casts
+            u32 = lambda t: t.view(torch.int32).to(torch.int64) & 0xFFFFFFFF   # noqa: E731
+            packed = torch.cat([u32(class_sum).reshape(-1), u32(dup).reshape(-1), extra.view(torch.int64).reshape(-1),
+                                u32(aux).reshape(-1)]).cpu().numpy()
+            k = w * ncls
+            cs = packed[:k].reshape(w, ncls).astype(np.float64)
             # rows holding an index = sum of its term frequencies - (tf - 1) of the rows with tf > 1
-            nz = cs.sum(axis=1) - (dup.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).astype(np.float64)
-            ex = extra.cpu().numpy().astype(np.float64)
-            ax = (aux.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(w, 3)
+            nz = cs.sum(axis=1) - packed[k:k + w].astype(np.float64)
+            ex = packed[k + w:k + 2 * w].astype(np.float64)
+            ax = packed[k + 2 * w:].reshape(w, 3)
             if not self.shouldTrackNulls:
                 cs, nz, ex, ax = cs[:lay.hash_width], nz[:lay.hash_width], ex[:lay.hash_width], ax[:lay.hash_width]
             self._hash_nnz = nz                      # of the local rows: sizes the sparse output of the same batch
