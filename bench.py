@@ -90,7 +90,7 @@ def run_step(batch, checked):
     """One step: fit every stage (fused vectorizer + SanityChecker scans, label classes, decision) and materialise
     the kept columns of the output vector.  Nothing is reused from a previous step."""
     from transmogrifai_b200.dsl import fit_and_transform
-    for k in ("_label_cache", "_label_dev", "_dict_cache"):
+    for k in ("_label_cache", "_label_dev", "_dict_cache", "_dev_cache"):
         batch.__dict__.pop(k, None)
     out, fitted = fit_and_transform(batch, checked)
     vec = out.vectors[checked.name]

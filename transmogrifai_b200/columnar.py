@@ -699,7 +699,24 @@ class ColumnarBatch:
     def with_vector(self, v: VectorColumn) -> "ColumnarBatch":
         out = ColumnarBatch(self.n, self.blocks, dict(self.vectors), self.response)
         out.vectors[v.name] = v
+        out.__dict__["_dev_cache"] = self.__dict__.setdefault("_dev_cache", {})   # same raw blocks, same copies
         return out
+
+    def on_device(self, kind: str, names: Sequence[str], block):
+        """`block` (what strings / sets / texts returned for `names`) in HBM: itself when it is there already, else
+        ONE host-to-device copy shared by every stage that works on these columns of this batch (an estimator's fit
+        and its model's transform read the same rows; a second copy over PCIe costs more than both kernels)."""
+        if block.is_cuda:
+            return block
+        cache = self.__dict__.setdefault("_dev_cache", {})
+        key = (kind, tuple(names))
+        if key not in cache:
+            cache[key] = block.to("cuda")
+        return cache[key]
+
+    def device_thunk(self, kind: str, names: Sequence[str], block):
+        """on_device, deferred to the first call (lazy parts move their input only when they are read)."""
+        return lambda: self.on_device(kind, names, block)
 
     def take_rows(self, idx: torch.Tensor) -> "ColumnarBatch":
         """The raw columns of the rows `idx` (int64 tensor on the blocks' device) as a batch of their own (what

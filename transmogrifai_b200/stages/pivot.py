@@ -146,7 +146,7 @@ class OpTextPivotVectorizer(OpEstimator):
         R.require_cuda()
         names = [f.name for f in self.inN]
         block = batch.strings(names)
-        dev = block if block.is_cuda else block.to("cuda")
+        dev = batch.on_device("strings", names, block)
         n, ncols = batch.n, len(names)
         label_name = batch.response
         classes = counts_per_class = ids = None
@@ -355,7 +355,8 @@ class OpTextPivotVectorizerModel(OpModel):
         names = [f.name for f in self.inN]
         block = batch.strings(names)
         width = sum(self._widths())
-        part = LazyOneHotPart(width, lambda keep: self._materialize(block, keep))
+        dev_of = batch.device_thunk("strings", names, block)
+        part = LazyOneHotPart(width, lambda keep: self._materialize(block, keep, dev_of))
         same = self._fit_key == (block.codes.data_ptr(), batch.n)
         return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part],
                             self._fit_stats if same else None)
@@ -373,8 +374,8 @@ class OpTextPivotVectorizerModel(OpModel):
                top_data.ctypes.data, top_offs.ctypes.data, len(self.topValues[c]), out.ctypes.data)
         return out[:len(d)]
 
-    def _materialize(self, block: DictBlock, keep: Optional[List[int]]) -> OneHotPart:
-        dev = block if block.is_cuda else block.to("cuda")
+    def _materialize(self, block: DictBlock, keep: Optional[List[int]], on_device=None) -> OneHotPart:
+        dev = on_device() if on_device is not None else (block if block.is_cuda else block.to("cuda"))
         n, ncols = block.n, len(block.names)
         widths = self._widths()
         width = sum(widths)

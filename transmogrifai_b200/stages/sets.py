@@ -39,7 +39,7 @@ class OpSetVectorizer(OpTextPivotVectorizer):
         R.require_cuda()
         names = [f.name for f in self.inN]
         block = batch.sets(names)
-        dev = block if block.is_cuda else block.to("cuda")
+        dev = batch.on_device("sets", names, block)
         n, ncols = batch.n, len(names)
         label_name = batch.response
         classes = class_counts = ids = None
@@ -80,7 +80,7 @@ class OpSetVectorizer(OpTextPivotVectorizer):
         self._metadata = self._metadata_for(tops)
         model = OpSetVectorizerModel(self, tops, self.cleanText, self.trackNulls)
         model._pos_cache = {id(block.dicts[c]): (block.dicts[c], pos_tables[c]) for c in range(ncols)}
-        model._fit_key = (dev.offsets[0].data_ptr(), n) if ncols else None
+        model._fit_key = (block.offsets[0].data_ptr(), n) if ncols else None
         if label_name:
             cont = None if classes is not None else label_moments_dev(batch, y, label_name) + (y,)
             model._fit_stats = model._sidecar(dev, n, n_all, classes, class_counts, ids, label_name, cont)
@@ -179,7 +179,8 @@ class OpSetVectorizerModel(OpModel):
         block = batch.sets(names)
         n = batch.n
         same = bool(names) and self._fit_key == (block.offsets[0].data_ptr(), n)
-        parts = [LazyPart(self.widths[c], (lambda keep, c=c: self._materialize(block, c, n, keep)))
+        dev_of = batch.device_thunk("sets", names, block)
+        parts = [LazyPart(self.widths[c], (lambda keep, c=c: self._materialize(dev_of(), c, n, keep)))
                  for c in range(len(names))]
         return VectorColumn(self.getOutput().name, n, self.getMetadata(), parts, self._fit_stats if same else None)
 

@@ -204,7 +204,7 @@ class SmartTextVectorizer(OpEstimator):
             raise ValueError("requirement failed: Input dataset cannot be empty")
         names = [f.name for f in self.inN]
         block = batch.texts(names)
-        dev = block if block.is_cuda else block.to("cuda")
+        dev = batch.on_device("texts", names, block)
         n, ncols = batch.n, len(names)
         self._prefix = {}                          # cleaned first rows of the columns past the cap, of THIS batch
         # 1. TextStats per column (merged over the ranks like the reference's reduce over partitions)
@@ -652,10 +652,11 @@ class SmartTextVectorizerModel(OpModel):
         n = batch.n
         parts = []
         same = self._fit_key == (block.offsets[0].data_ptr(), n)
+        dev_of = batch.device_thunk("texts", names, block)
         if self.pivot_idx:
-            parts.append(LazyPart(self.pivot_width, lambda keep: self._materialize_pivot(block, n, keep)))
+            parts.append(LazyPart(self.pivot_width, lambda keep: self._materialize_pivot(dev_of(), n, keep)))
         if self.layout.text_idx:
-            parts.append(LazyPart(self.layout.width, lambda keep: self._materialize_hash(block, n, keep, same)))
+            parts.append(LazyPart(self.layout.width, lambda keep: self._materialize_hash(dev_of(), n, keep, same)))
         return VectorColumn(self.getOutput().name, n, self.getMetadata(), parts, self._fit_stats if same else None)
 
     def _materialize_pivot(self, block: TextBlock, n: int, keep) -> OneHotPart:
