@@ -15,7 +15,7 @@ from .. import _lib as L
 from .. import dist as D
 from .. import features as F
 from .. import runtime as R
-from ..columnar import ColumnarBatch, DensePart, LazyDensePart, NumericBlock, VectorColumn, round_up
+from ..columnar import ColumnarBatch, DensePart, LazyDensePart, NumericBlock, VectorColumn, round_up, to_host
 from ..metadata import OpVectorMetadata, feature_column
 from ..stats import LabelInfo, VectorStats
 from .base import OpEstimator, OpModel, OpTransformer
@@ -355,7 +355,7 @@ def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_n
         return out[:, :w]
     if binary or integral:
         dev = block.to("cuda")
-        return _transform_numeric(dev, fills, track_nulls, chunk_rows, fill_value, keep).cpu()
+        return to_host([_transform_numeric(dev, fills, track_nulls, chunk_rows, fill_value, keep)])[0]   # pinned
     out = torch.empty((n, w), dtype=torch.float64, pin_memory=True)
     L.call("tmog_real_transform_host", R.ctx(), block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv, n,
            ncols, None if fills is None else fills.ctypes.data, int(track_nulls), chunk_rows,
