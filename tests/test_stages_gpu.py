@@ -461,3 +461,43 @@ def test_sanity_checker_default_limits_sample_a_large_batch():
     corr = dict(zip(est.summary.names, est.summary.correlationsWithLabel))
     assert corr["c1_2"] > 0.15 and abs(corr["c0_0"]) < 0.01
     assert out.vectors[checked.name].n == n
+
+
+def test_host_batch_raw_blocks_cross_the_link_once(monkeypatch):
+    """A host batch through fit + transform: every PickList / Text / MultiPickList block is copied to the GPU once (the
+    estimator's fit and its model's transform share the copy), and the result equals the device batch's."""
+    from transmogrifai_b200 import columnar as CB
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+    rng = np.random.default_rng(5)
+    n = 1500
+    y = (rng.random(n) < 0.4).astype(np.float64)
+    opt = lambda v, p: None if rng.random() < p else v   # noqa: E731
+    p0 = [opt("abcde"[int(rng.integers(5))], 0.1) for _ in y]
+    p1 = [opt("uvw"[int(rng.integers(3))], 0.05) for _ in y]
+    words = ["".join(rng.choice(list("abcdefgh"), size=rng.integers(3, 7))) for _ in range(120)]
+    t0 = [opt(" ".join(words[i] for i in rng.integers(0, 120, rng.poisson(6))), 0.05) for _ in y]
+    s0 = [set(rng.choice(list("klmn"), size=rng.integers(0, 3), replace=False).tolist()) for _ in y]
+    data = {"p0": (F.PICKLIST, p0), "p1": (F.PICKLIST, p1), "t0": (F.TEXT, t0), "s0": (F.MULTIPICKLIST, s0),
+            "y": (F.REALNN, y.tolist())}
+    FB = F.FeatureBuilder
+    feats = [FB.PickList("p0").asPredictor(), FB.PickList("p1").asPredictor(), FB.Text("t0").asPredictor(),
+             FB.MultiPickList("s0").asPredictor()]
+    label = FB.RealNN("y").asResponse()
+
+    def run(batch):
+        checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
+                                    sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
+        out, fitted = fit_and_transform(batch, checked)
+        return out.vectors[checked.name].to_scipy(), fitted[-1].indicesToKeep
+
+    copies = []
+    for cls in (CB.DictBlock, CB.TextBlock, CB.SetBlock):
+        orig = cls.to
+        monkeypatch.setattr(cls, "to", lambda self, device, _o=orig, _c=cls: (copies.append(_c.__name__),
+                                                                             _o(self, device))[1])
+    host = _batch(data, response="y")
+    got_h, keep_h = run(host)
+    assert sorted(copies) == ["DictBlock", "SetBlock", "TextBlock"]
+    got_d, keep_d = run(_batch(data, response="y", device="cuda"))
+    assert keep_h == keep_d and got_h.shape == got_d.shape and abs(got_h - got_d).max() == 0
