@@ -757,7 +757,9 @@ vec_transform_pack_kernel(const T* __restrict__ values, int64_t ld, const uint64
                          "r"(total * (int)sizeof(double))
                          : "memory");
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+            // the CTA may go once the engine has READ the image (its shared memory is free again then); the global
+            // writes complete by the end of the grid like any other store
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         }
         return;
     }
