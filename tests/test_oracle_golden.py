@@ -11,7 +11,7 @@ import pytest
 from oracle import sanity as S
 from oracle import text as T
 from oracle import vectorizers as V
-from oracle.metadata import ColumnMeta, NULL_STRING, OTHER_STRING
+from oracle.metadata import ColumnMeta, NULL_STRING, OTHER_STRING, TEXT_LEN_STRING
 
 
 def dense(m):
@@ -356,3 +356,43 @@ def test_integral_vectorizer_golden():
     # with null tracking: [value, isNull] interleaved (IntegralVectorizerTest.scala:151-180)
     got = V.integral_vectorizer_transform([a, b], [4, 2], track_nulls=True)
     assert got[3].tolist() == [4.0, 1.0, 2.0, 0.0] and got[4].tolist() == [4.0, 1.0, 2.0, 1.0]
+
+
+@pytest.mark.parametrize("tokens,min_std", [(True, 0.5), (False, 1.0)])
+def test_smart_text_ignore_route_layout(tokens, min_std):
+    """SmartTextVectorizerTest.scala:213-280 ("detect and ignore fields that looks like machine-generated IDs"), with
+    data of the same four shapes (:85-97): the country column is hashed, the small-domain column is pivoted although
+    its lengths are fixed (the categorical check comes first), the fixed-length id column is ignored, the free text is
+    hashed; vector = [pivot 3+2 | 2 x 5 hash buckets | 3 lengths | 3 null indicators] = 21 columns."""
+    rng = np.random.default_rng(11)
+    n = 1000
+    opt = lambda v: None if rng.random() < 0.2 else v   # noqa: E731
+    places = [" ".join("".join(rng.choice(list("abcdefghijklmnop"), size=rng.integers(3, 9))).capitalize()
+                       for _ in range(rng.integers(1, 4))) for _ in range(250)]
+    country = [opt(places[int(rng.integers(len(places)))]) for _ in range(n)]
+    categorical = [opt("ABCDEF"[int(rng.integers(6))]) for _ in range(n)]
+    text_id = [opt("%06d" % (40231 + int(rng.integers(1000)))) for _ in range(n)]
+    text = [opt("".join(rng.choice(list("abc xyz,. QRS"), size=rng.integers(0, 101)))) for _ in range(n)]
+    cols, names = [country, categorical, text_id, text], ["country", "categorical", "textId", "text"]
+    methods, tops = V.smart_text_fit(cols, max_cardinality=10, top_k=3, min_support=10, min_length_std_dev=min_std,
+                                     tokenize_for_lengths=tokens)
+    assert methods == [V.HASH, V.PIVOT, V.IGNORE, V.HASH]
+    x = V.smart_text_transform(cols, names, methods, tops, num_features=5, track_nulls=True, track_text_len=True,
+                               to_lowercase=False, min_token_length=1)
+    meta = V.smart_text_metadata(names, "Text", methods, tops, num_features=5, track_nulls=True, track_text_len=True)
+    assert x.shape == (n, 21) and len(meta) == 21
+    assert all(m.grouping == "categorical" for m in meta[0:5])
+    assert all(m.parent_names == ("country",) for m in meta[5:10])
+    assert all(m.parent_names == ("text",) for m in meta[10:15])
+    assert [m.parent_names[0] for m in meta[15:18]] == ["country", "text", "textId"]        # hashed, then ignored
+    assert all(m.descriptor == TEXT_LEN_STRING for m in meta[15:18])
+    assert all(m.indicator == NULL_STRING for m in meta[18:21])
+    dense = np.asarray(x.todense())
+    for r in (0, 1, 2, 500, 999):
+        toks = [T.tokenize(c[r], False, 1) for c in (country, text, text_id)]
+        assert dense[r, 15:18].tolist() == [float(sum(len(t) for t in tk)) for tk in toks]
+        assert dense[r, 18:21].tolist() == [0.0 if tk else 1.0 for tk in toks]
+    # the ignored column contributes nothing but its length and its null indicator
+    assert np.count_nonzero(dense[:, 5:15].sum(axis=1) == 0) <= sum(1 for a, b in zip(country, text)
+                                                                      if not T.tokenize(a, False, 1)
+                                                                      and not T.tokenize(b, False, 1))
