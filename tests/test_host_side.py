@@ -90,3 +90,47 @@ def test_pivot_dictionary_prepare_and_finish_match_the_one_call_form_and_the_ora
     assert top == V.top_values(merged, k, min_support)
     assert p2.reshape(k + 2, 2)[n2.value + 1].tolist() == counts[0].tolist()          # the null row
     assert p2.sum() == counts.sum()
+
+
+def test_large_dictionary_grouping_on_threads_matches_the_oracle():
+    """Dictionaries of 32768 entries and more are grouped by several host threads (strings_host.cu group_strings_mt):
+    same vocabulary, same code -> column table and the same per-class counts as a plain fold over the entries."""
+    from transmogrifai_b200 import _lib as L
+    from transmogrifai_b200.columnar import decode_strings, encode_strings
+    rng = np.random.default_rng(17)
+    nbase = 60000
+    raw = [f"v7_{i}" for i in range(nbase)]
+    raw += [f"V7 {i}!" for i in rng.integers(0, nbase, 9000)]            # clean to the value of an earlier entry
+    raw += [f"v7.{i}" for i in rng.integers(0, nbase, 9000)]
+    raw += ["", " ", "__"]                                               # clean to the empty string
+    order = rng.permutation(len(raw))
+    raw = [raw[i] for i in order]
+    counts = rng.integers(0, 6, size=(len(raw) + 1, 2)).astype(np.int64)
+    hot = rng.integers(0, len(raw), 40)
+    counts[1 + hot] += rng.integers(50, 500, size=(40, 2))
+    data, offs = encode_strings(raw)
+    flat = np.ascontiguousarray(counts.reshape(-1))
+    k, min_support = 25, 10
+    h = C.c_void_p()
+    L.call("tmog_pivot_dict_prepare", data.ctypes.data, offs.ctypes.data, len(raw), 1, C.byref(h))
+    n_top, code_to_out = C.c_int(0), np.zeros(len(raw), dtype=np.int32)
+    per_class = np.zeros((k + 2) * 2, dtype=np.int64)
+    top_data, top_offs = np.zeros(len(data) + 1, dtype=np.uint8), np.zeros(k + 1, dtype=np.int64)
+    L.call("tmog_pivot_dict_finish", h, flat.ctypes.data, 2, k, min_support, C.byref(n_top), code_to_out.ctypes.data,
+           per_class.ctypes.data, top_data.ctypes.data, len(top_data), top_offs.ctypes.data)
+    L.call("tmog_pivot_dict_free", h)
+    top = decode_strings(top_data, top_offs[:n_top.value + 1])
+    cleaned = [T.clean_string(s) for s in raw]
+    merged, per_value = {}, {}
+    for s, c in zip(cleaned, counts[1:]):
+        if c.sum() > 0:
+            merged[s] = merged.get(s, 0) + int(c.sum())
+        per_value[s] = per_value.get(s, np.zeros(2, dtype=np.int64)) + c
+    exp_top = V.top_values(merged, k, min_support)
+    assert top == exp_top and n_top.value == k
+    col_of = {v: i for i, v in enumerate(exp_top)}
+    assert code_to_out.tolist() == [col_of.get(s, k) for s in cleaned]                  # k = the OTHER column
+    rows = per_class.reshape(k + 2, 2)
+    for i, v in enumerate(exp_top):
+        assert rows[i].tolist() == per_value[v].tolist()
+    assert rows[k + 1].tolist() == counts[0].tolist() and rows.sum() == counts.sum()

@@ -8,6 +8,7 @@
 #include <memory>
 #include <new>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -285,6 +286,79 @@ int64_t group_strings(const std::string& pool, const std::vector<int64_t>& off, 
     return (int64_t)first.size();
 }
 
+// group_strings for a large dictionary on several host threads; same ids and first-entry list.  Hashes are taken in
+// index chunks; then thread t owns the strings whose hash falls in its share of the hash range and finds, in index
+// order, the first equal string of each of them (rep[i]); a sequential sweep numbers the groups by first appearance.
+int64_t group_strings_mt(const std::string& pool, const std::vector<int64_t>& off, std::vector<int32_t>& ids,
+                         std::vector<int32_t>& first, int nthreads) {
+    const int64_t count = (int64_t)off.size() - 1;
+    std::vector<uint64_t> hash((size_t)count);
+    std::vector<int32_t> rep((size_t)count);
+    auto run = [&](const std::function<void(int)>& body) {
+        std::vector<std::thread> th;
+        th.reserve((size_t)nthreads - 1);
+        for (int t = 1; t < nthreads; ++t) th.emplace_back(body, t);
+        body(0);
+        for (auto& x : th) x.join();
+    };
+    run([&](int t) {
+        const int64_t lo = count * t / nthreads, hi = count * (t + 1) / nthreads;
+        for (int64_t i = lo; i < hi; ++i) hash[(size_t)i] = fnv64(pool.data() + off[i], off[i + 1] - off[i]);
+    });
+    auto owner = [&](uint64_t h) { return (int)(((h >> 32) * (uint64_t)nthreads) >> 32); };   // by the high bits
+    run([&](int t) {
+        int64_t mine = 0;
+        for (int64_t i = 0; i < count; ++i) mine += owner(hash[(size_t)i]) == t;
+        size_t cap = 16;
+        while (cap < (size_t)mine * 2 + 2) cap <<= 1;
+        struct Slot {
+            uint64_t hash;
+            int32_t idx;
+        };
+        std::vector<Slot> slot(cap, Slot{0, -1});
+        for (int64_t i = 0; i < count; ++i) {
+            const uint64_t h = hash[(size_t)i];
+            if (owner(h) != t) continue;
+            const char* p = pool.data() + off[i];
+            const int64_t len = off[i + 1] - off[i];
+            size_t s = (size_t)h & (cap - 1);                                               // by the low bits
+            for (;;) {
+                Slot& sl = slot[s];
+                if (sl.idx < 0) {
+                    sl.hash = h;
+                    sl.idx = (int32_t)i;
+                    rep[(size_t)i] = (int32_t)i;
+                    break;
+                }
+                if (sl.hash == h) {
+                    const int32_t j = sl.idx;
+                    if (off[j + 1] - off[j] == len && memcmp(pool.data() + off[j], p, (size_t)len) == 0) {
+                        rep[(size_t)i] = j;
+                        break;
+                    }
+                }
+                s = (s + 1) & (cap - 1);
+            }
+        }
+    });
+    ids.resize((size_t)count);
+    first.clear();
+    first.reserve((size_t)count);
+    for (int64_t i = 0; i < count; ++i) {
+        if (rep[(size_t)i] == (int32_t)i) {
+            ids[(size_t)i] = (int32_t)first.size();
+            first.push_back((int32_t)i);
+        } else {
+            ids[(size_t)i] = ids[(size_t)rep[(size_t)i]];
+        }
+    }
+    return (int64_t)first.size();
+}
+
+// dictionaries from this size on are grouped by several threads (the largest dictionary of a vectorizer is the
+// critical path of its fit: the other columns' dictionaries are done long before it)
+constexpr int64_t GROUP_MT_MIN = 32768;
+
 }  // namespace
 
 // The counts-independent half of the finish (cleaning + grouping of the dictionary entries), so that a caller can run
@@ -308,7 +382,12 @@ extern "C" int tmog_pivot_dict_prepare(const uint8_t* dict_data, const int64_t* 
                   "on this path (set cleanText = false)", (long long)bad);
         return TMOG_EINVAL;
     }
-    group_strings(d->pool, d->off, d->ids, d->first);
+    const int hw = (int)std::thread::hardware_concurrency();
+    const int nthreads = (int)std::min<int64_t>(std::min(8, std::max(hw, 1)), ncodes / (GROUP_MT_MIN / 2));
+    if (ncodes >= GROUP_MT_MIN && nthreads >= 2)
+        group_strings_mt(d->pool, d->off, d->ids, d->first, nthreads);
+    else
+        group_strings(d->pool, d->off, d->ids, d->first);
     d->ncodes = ncodes;
     *out = d.release();
     return TMOG_OK;
