@@ -396,3 +396,55 @@ def test_smart_text_ignore_route_layout(tokens, min_std):
     assert np.count_nonzero(dense[:, 5:15].sum(axis=1) == 0) <= sum(1 for a, b in zip(country, text)
                                                                       if not T.tokenize(a, False, 1)
                                                                       and not T.tokenize(b, False, 1))
+
+
+def _country_column(seed=23):
+    """The shape of SmartTextVectorizerTest.scala:107-109 (`categoricalCountryData`): 1000 x "United States" shuffled
+    with 1000 draws (20 % empty) from a list of ~450 country names."""
+    rng = np.random.default_rng(seed)
+    names = sorted({" ".join("".join(rng.choice(list("abcdefghijklmnoprstuvw"), size=rng.integers(3, 9))).capitalize()
+                             for _ in range(rng.integers(1, 3))) for _ in range(470)})[:450]
+    draws = [None if rng.random() < 0.2 else names[int(rng.integers(len(names)))] for _ in range(1000)]
+    col = ["United States"] * 1000 + draws
+    return [col[i] for i in rng.permutation(len(col))]
+
+
+@pytest.mark.parametrize("case,kw,num_features,method,width", [
+    # SmartTextVectorizerTest.scala:283-290: coverage near 0 -> pivot, TopK + OTHER + null
+    ("coverage~0", dict(coverage_pct=1e-10, max_cardinality=100, min_support=1), 512, "Pivot", 20 + 2),
+    # :291-298: coverage near 1 -> hash, DefaultNumOfFeatures + length + null
+    ("coverage~1", dict(coverage_pct=1.0 - 1e-10, max_cardinality=100, min_support=1), 512, "Hash", 512 + 2),
+    # :300-312: high cardinality, pivoted through the coverage
+    ("coverage", dict(max_cardinality=100, top_k=10, min_support=1, coverage_pct=0.5, clean_text=False), 512,
+     "Pivot", 10 + 2),
+    # :314-328: a minimum support nothing reaches -> coverage 0 -> hash
+    ("minSupport 99999", dict(max_cardinality=100, top_k=10, min_support=99999, coverage_pct=0.5, clean_text=False),
+     5, "Hash", 5 + 2),
+    # :330-344: minimum support 100 leaves the one frequent value, which alone covers half the rows -> pivot of width 3
+    ("minSupport 100", dict(max_cardinality=100, top_k=10, min_support=100, coverage_pct=0.5, clean_text=False), 5,
+     "Pivot", 3),
+    # :346-359: cardinality <= topK -> the coverage rule does not apply -> hash
+    ("topK too high", dict(max_cardinality=100, top_k=1000000, coverage_pct=0.5, clean_text=False), 5, "Hash", 5 + 2),
+])
+def test_smart_text_coverage_decisions(case, kw, num_features, method, width):
+    col = _country_column()
+    assert len({v for v in col if v is not None}) > 100
+    methods, tops = V.smart_text_fit([col], **kw)
+    assert methods == [method], case
+    meta = V.smart_text_metadata(["rawCatCountry"], "Text", methods, tops, num_features=num_features, track_nulls=True,
+                                 track_text_len=True)
+    x = V.smart_text_transform([col[:50]], ["rawCatCountry"], methods, tops, num_features=num_features,
+                               clean_text=kw.get("clean_text", True), track_nulls=True, track_text_len=True)
+    assert len(meta) == width and x.shape == (50, width), case
+
+
+def test_smart_text_uniform_countries_stay_text_despite_the_coverage():
+    # SmartTextVectorizerTest.scala:361-373: no dominant value -> top-10 of the capped map covers less than half
+    col = [v for v in _country_column(4) if v != "United States"]
+    assert len({v for v in col if v is not None}) > 100
+    methods, tops = V.smart_text_fit([col], max_cardinality=100, top_k=10, min_support=1, coverage_pct=0.5,
+                                     clean_text=False)
+    assert methods == ["Hash"]
+    meta = V.smart_text_metadata(["country"], "Text", methods, tops, num_features=5, track_nulls=True,
+                                 track_text_len=True)
+    assert len(meta) == 5 + 2
