@@ -1,0 +1,176 @@
+"""A dataset streamed in row chunks (transmogrifai_b200/streaming.py) must give what one resident batch gives and what
+the oracle gives: the folds of FitStagesUtil.scala:212-290 / OpOneHotVectorizer.scala:95-97 /
+SmartTextVectorizer.scala:88-91,231-235 do not depend on how the rows are cut into partitions (the TextStats fold is
+taken in row order, as the oracle takes it)."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+from oracle import sanity as S
+from oracle import vectorizers as V
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+SIZES = [100, 700, 1, 999, 300, 650, 250]          # seven uneven chunks
+
+
+def _data(n, seed, continuous=False):
+    from transmogrifai_b200 import features as F
+    rng = np.random.default_rng(seed)
+    z = rng.normal(0, 1, n)
+    y = (100.0 + 3.0 * z + rng.normal(0, 0.5, n)) if continuous else (rng.random(n) < 0.3).astype(np.float64)
+    opt = lambda v, p: None if rng.random() < p else v   # noqa: E731
+    b0 = [opt(bool(rng.random() < 0.4 + 0.3 * (yy > y.mean())), 0.1) for yy in y]
+    b1 = [opt(bool(rng.random() < 0.5), 0.05) for _ in y]
+    p0 = [opt(["x", "y", "z", "X ", "w"][int(rng.integers(5))], 0.08) for _ in y]
+    # values that only show up late (other chunks, other dictionaries) and aliases that clean alike
+    p1 = [opt(f"v{int(rng.zipf(1.3)) % 60}" if i > 900 else ["a", "A.", "b"][int(rng.integers(3))], 0.05)
+          for i in range(n)]
+    r0 = [opt(float(rng.normal(2 + (yy > y.mean()), 1)), 0.1) for yy in y]
+    r1 = [opt(float(rng.normal(0, 3)), 0.02) for _ in y]
+    nn = [float(v) for v in rng.normal(5, 2, n)]
+    words = ["".join(rng.choice(list("abcdefgh"), size=rng.integers(3, 7))) for _ in range(150)]
+    t0 = [opt(" ".join(words[i] for i in rng.integers(0, 150, rng.poisson(8))), 0.06) for _ in y]
+    t1 = [opt(["red", "Green", "blue", "blue!"][int(rng.integers(4))], 0.05) for _ in y]
+    # 25 distinct values at first; from row 1300 on (inside the fourth chunk) new ones appear and the map passes the
+    # cap of 30 there: the fold freezes in the middle of a chunk
+    t2 = [opt(f"k{int(rng.integers(25))}" if i < 1300 else f"k{int(rng.integers(400))}", 0.04) for i in range(n)]
+    cols = {"b0": (F.BINARY, b0), "b1": (F.BINARY, b1), "p0": (F.PICKLIST, p0), "p1": (F.PICKLIST, p1),
+            "r0": (F.REAL, r0), "r1": (F.REAL, r1), "nn": (F.REALNN, nn), "t0": (F.TEXT, t0), "t1": (F.TEXT, t1),
+            "t2": (F.TEXT, t2), "y": (F.REALNN, y.tolist())}
+    return cols, y
+
+
+def _plan():
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.dsl import transmogrify
+    FB = F.FeatureBuilder
+    feats = [FB.Text("t0").asPredictor(), FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(),
+             FB.RealNN("nn").asPredictor(), FB.PickList("p0").asPredictor(), FB.Real("r1").asPredictor(),
+             FB.Binary("b1").asPredictor(), FB.Text("t1").asPredictor(), FB.PickList("p1").asPredictor(),
+             FB.Text("t2").asPredictor()]
+    label = FB.RealNN("y").asResponse()
+    return label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
+                             sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
+
+
+def _oracle(cols, y):
+    c = {k: v[1] for k, v in cols.items()}
+    xb = V.binary_vectorizer_transform([c["b0"], c["b1"]])
+    tops = V.pivot_fit([c["p0"], c["p1"]], 20, 10, True)
+    xp = V.pivot_transform([c["p0"], c["p1"]], tops, True, True)
+    fills = V.real_vectorizer_fit([c["r0"], c["r1"]])
+    xr = V.real_vectorizer_transform([c["r0"], c["r1"]], fills, True)
+    xn = V.realnn_vectorizer_transform([c["nn"]])
+    texts = [c["t0"], c["t1"], c["t2"]]
+    methods, ttops = V.smart_text_fit(texts, max_cardinality=30, top_k=20, min_support=10)
+    xt = V.smart_text_transform(texts, ["t0", "t1", "t2"], methods, ttops, num_features=512)
+    xo, metas = V.combine(
+        [xb, xp, xr, xn, xt],
+        [V.numeric_metadata(["b0", "b1"], "Binary", True), V.pivot_metadata(["p0", "p1"], "PickList", tops, True),
+         V.numeric_metadata(["r0", "r1"], "Real", True), V.numeric_metadata(["nn"], "RealNN", False),
+         V.smart_text_metadata(["t0", "t1", "t2"], "Text", methods, ttops, 512, True)])
+    p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                       feature_feature_corr_level="off")
+    return S.sanity_fit(y, sp.csr_matrix(xo), metas, p, label_name="y"), sp.csr_matrix(xo), metas, methods, tops
+
+
+def _chunks(cols, mode):
+    from transmogrifai_b200.columnar import ColumnarBatch
+    n = len(cols["y"][1])
+    bounds = np.concatenate([[0], np.cumsum(SIZES)])
+    assert bounds[-1] == n
+    if mode == "own_dictionaries_host":
+        # every chunk exported on its own: pinned host buffers, a dictionary per chunk (first-appearance order)
+        return [ColumnarBatch.from_columns({k: (t, v[a:b]) for k, (t, v) in cols.items()}, response="y")
+                for a, b in zip(bounds[:-1], bounds[1:])]
+    full = ColumnarBatch.from_columns(cols, response="y").to("cuda")        # shared dictionaries, rows on the device
+    return [full.take_rows(torch.arange(a, b, device="cuda")) for a, b in zip(bounds[:-1], bounds[1:])]
+
+
+def _check(est, keep, rows, ref, xo, metas):
+    assert est.summary.names[:-1] == [m.col_name() for m in metas]
+    assert est.summary.dropped == ref.dropped
+    assert list(keep) == ref.indices_to_keep
+    assert est.summary.count == xo.shape[0]
+    np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+    assert np.array_equal(est.summary.min, ref.col_stats.min) and np.array_equal(est.summary.max, ref.col_stats.max)
+    np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                               equal_nan=True)
+    got_g = {g.group: g for g in est.summary.categoricalStats}
+    assert got_g.keys() == {g.group for g in ref.cat_stats}
+    for g in ref.cat_stats:
+        assert np.array_equal(got_g[g.group].contingencyMatrix, g.contingency_matrix)
+        np.testing.assert_allclose(got_g[g.group].cramersV, g.cramers_v, rtol=1e-9, equal_nan=True)
+    exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
+    assert rows.shape == exp.shape and abs(rows - exp).max() < 1e-12
+
+
+@pytest.mark.parametrize("mode", ["shared_dictionaries_device", "own_dictionaries_host"])
+@pytest.mark.parametrize("continuous", [False, True])
+def test_seven_uneven_chunks_equal_one_batch_equal_oracle(mode, continuous):
+    from transmogrifai_b200.columnar import ColumnarBatch, VectorColumn
+    from transmogrifai_b200.dsl import fit_and_transform
+    from transmogrifai_b200.streaming import fit_and_transform_stream
+    cols, y = _data(sum(SIZES), 77, continuous)
+    ref, xo, metas, methods, tops = _oracle(cols, y)
+    assert methods[:2] == ["Hash", "Pivot"]
+    chunks = _chunks(cols, mode)
+    checked = _plan()
+    out = []
+
+    def sink(k, vec, parts):
+        out.append(VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy())
+
+    res = fit_and_transform_stream(chunks, checked, sink)
+    est = checked.origin_stage
+    assert res.rows == sum(SIZES) and res.chunks == len(SIZES) and len(out) == len(SIZES)
+    _check(est, res.fitted[-1].indicesToKeep, sp.vstack(out).tocsr(), ref, xo, metas)
+    streamed = (list(est.summary.dropped), est.summary.mean.copy(), est.summary.variance.copy(),
+                est.summary.correlationsWithLabel.copy())
+    # the same plan over one resident batch
+    checked1 = _plan()
+    batch = ColumnarBatch.from_columns(cols, response="y").to("cuda")
+    out_batch, fitted = fit_and_transform(batch, checked1)
+    est1 = checked1.origin_stage
+    assert streamed[0] == est1.summary.dropped
+    np.testing.assert_allclose(streamed[1], est1.summary.mean, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(streamed[2], est1.summary.variance, rtol=1e-9, atol=1e-18)
+    np.testing.assert_allclose(streamed[3], est1.summary.correlationsWithLabel, rtol=1e-9, atol=1e-12, equal_nan=True)
+    one = out_batch.vectors[checked1.name].to_scipy()
+    assert abs(one - sp.vstack(out).tocsr()).max() < 1e-12
+
+
+def test_stream_transform_of_other_rows_and_empty_input():
+    """The fitted stages of a streamed fit transform rows they were not fitted on; an empty stream is an error."""
+    from transmogrifai_b200.columnar import VectorColumn
+    from transmogrifai_b200.streaming import fit_stream, transform_stream
+    cols, y = _data(sum(SIZES), 78)
+    chunks = _chunks(cols, "own_dictionaries_host")
+    checked = _plan()
+    fit = fit_stream(chunks[:5], checked)
+    out = []
+    rows = transform_stream(chunks[5:], checked, fit, lambda k, vec, parts: out.append(
+        VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy()))
+    assert rows == sum(SIZES[5:])
+    # against the oracle fitted on the first five chunks' rows and applied to the last two
+    m = sum(SIZES[:5])
+    head = {k: (t, v[:m]) for k, (t, v) in cols.items()}
+    ref, _xo, _metas, methods, tops = _oracle(head, y[:m])
+    c = {k: v[1] for k, v in cols.items()}
+    hc = {k: v[1] for k, v in head.items()}
+    xb = V.binary_vectorizer_transform([c["b0"], c["b1"]])
+    xp = V.pivot_transform([c["p0"], c["p1"]], tops, True, True)
+    xr = V.real_vectorizer_transform([c["r0"], c["r1"]], V.real_vectorizer_fit([hc["r0"], hc["r1"]]), True)
+    xn = V.realnn_vectorizer_transform([c["nn"]])
+    texts = [c["t0"], c["t1"], c["t2"]]
+    _m, ttops = V.smart_text_fit([hc["t0"], hc["t1"], hc["t2"]], max_cardinality=30, top_k=20, min_support=10)
+    xt = V.smart_text_transform(texts, ["t0", "t1", "t2"], methods, ttops, num_features=512)
+    full = sp.hstack([sp.csr_matrix(x) for x in (xb, xp, xr, xn, xt)]).tocsr()
+    exp = full[m:][:, ref.indices_to_keep]
+    got = sp.vstack(out).tocsr()
+    assert got.shape == exp.shape and abs(got - exp).max() < 1e-12
+    with pytest.raises(ValueError):
+        fit_stream([], _plan())

@@ -10,6 +10,7 @@ torch tensors are the storage (CPU pinned or CUDA): plumbing only, every computa
 """
 from __future__ import annotations
 
+import itertools
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -572,6 +573,17 @@ class LazyPart:
         return self.materialize(None).to_scipy()
 
 
+class WidthPart:
+    """Stand-in for the parts of a vector that is never materialised as a whole (a dataset streamed in row chunks):
+    VectorsCombiner and SanityChecker only need its width, the statistics come from the sidecar."""
+
+    def __init__(self, width: int):
+        self.width = width
+
+    def materialize(self, keep=None):
+        raise ValueError("the vector of a streamed dataset exists chunk by chunk only")
+
+
 @dataclass
 class VectorColumn:
     name: str
@@ -607,12 +619,23 @@ class VectorColumn:
         return np.asarray(self.to_scipy().todense())
 
 
+_batch_tokens = itertools.count(1)
+
+
+def batch_key(batch: "ColumnarBatch", block=None) -> int:
+    """Identity of the raw rows a stage was fitted on: the batch's token (never reused, unlike a device address, which
+    the allocator hands out again once a batch is freed).  A batch is immutable once built; refilling its buffers in
+    place is not supported."""
+    return batch.token
+
+
 @dataclass
 class ColumnarBatch:
     n: int
     blocks: List[object] = field(default_factory=list)     # NumericBlock | DictBlock
     vectors: Dict[str, VectorColumn] = field(default_factory=dict)
     response: Optional[str] = None       # name of the response (label) column, a RealNN
+    token: int = field(default_factory=lambda: next(_batch_tokens), compare=False)   # unique per set of raw rows
 
     def find(self, name: str):
         index = self.__dict__.get("_name_index")
@@ -697,7 +720,7 @@ class ColumnarBatch:
         return b.values[i]
 
     def with_vector(self, v: VectorColumn) -> "ColumnarBatch":
-        out = ColumnarBatch(self.n, self.blocks, dict(self.vectors), self.response)
+        out = ColumnarBatch(self.n, self.blocks, dict(self.vectors), self.response, self.token)   # same raw rows
         out.vectors[v.name] = v
         out.__dict__["_dev_cache"] = self.__dict__.setdefault("_dev_cache", {})   # same raw blocks, same copies
         return out

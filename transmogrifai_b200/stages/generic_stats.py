@@ -13,7 +13,7 @@ from .. import _lib as L
 from .. import dist as DD
 from .. import runtime as R
 from ..columnar import (ColumnarBatch, CsrPart, DensePart, LazyDensePart, LazyOneHotPart, LazyPart, OneHotPart,
-                        VectorColumn)
+                        VectorColumn, WidthPart)
 from ..stats import LabelInfo, VectorStats
 from .numeric import label_info_dev
 
@@ -155,7 +155,9 @@ def select_columns(vec: VectorColumn, keep: List[int]) -> list:
         if len(local) == 0:
             continue
         whole = len(local) == p.width and bool((local == np.arange(p.width)).all())
-        if isinstance(p, LazyDensePart):
+        if isinstance(p, WidthPart):
+            out.append(WidthPart(len(local)))
+        elif isinstance(p, LazyDensePart):
             out.append(DensePart(p.materialize(local)))
         elif isinstance(p, DensePart):
             if whole:

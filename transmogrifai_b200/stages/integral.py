@@ -18,7 +18,7 @@ from .. import _lib as L
 from .. import dist as D
 from .. import features as F
 from .. import runtime as R
-from ..columnar import ColumnarBatch, LazyDensePart, NumericBlock, VectorColumn
+from ..columnar import batch_key, ColumnarBatch, LazyDensePart, NumericBlock, VectorColumn
 from ..stats import LabelInfo, VectorStats
 from .base import OpEstimator, OpModel
 from .numeric import MAX_LABEL_CLASSES, _numeric_metadata, _transform_numeric, label_info_dev
@@ -123,7 +123,7 @@ class IntegralVectorizer(OpEstimator):
         label_name = batch.response
         if label_name:
             model._fit_stats = self._sidecar(batch, dev, n, ncols, np.asarray(fills, dtype=np.float64), label_name)
-            model._fit_key = (block.values.data_ptr(), n)
+            model._fit_key = batch_key(batch)
         return model
 
     def _sidecar(self, batch: ColumnarBatch, dev: NumericBlock, n: int, ncols: int, fills: np.ndarray,
@@ -186,6 +186,6 @@ class IntegralVectorizerModel(OpModel):
         fills, track = np.asarray(self.fillValues, dtype=np.float64), self.trackNulls       # .toDouble (:107,:111)
         part = LazyDensePart(len(names) * (2 if track else 1),
                              lambda keep: _transform_numeric(block, fills, track, 1 << 20, keep=keep))
-        same = self._fit_key == (block.values.data_ptr(), batch.n)
+        same = self._fit_key is not None and self._fit_key == batch_key(batch)
         return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part],
                             self._fit_stats if same else None)

@@ -15,7 +15,7 @@ from .. import _lib as L
 from .. import dist as D
 from .. import features as F
 from .. import runtime as R
-from ..columnar import ColumnarBatch, DensePart, LazyDensePart, NumericBlock, VectorColumn, round_up, to_host
+from ..columnar import batch_key, ColumnarBatch, DensePart, LazyDensePart, NumericBlock, VectorColumn, round_up, to_host
 from ..metadata import OpVectorMetadata, feature_column
 from ..stats import LabelInfo, VectorStats
 from .base import OpEstimator, OpModel, OpTransformer
@@ -246,6 +246,13 @@ class RealVectorizer(OpEstimator):
                     null_counts = D.allreduce_sum(g_null) if self.trackNulls else None
                 else:
                     classes = counts = null_counts = None
+        model = self._finish(partials, shifts, classes, counts, null_counts, label_name)
+        model._fit_key = batch_key(batch, block)
+        return model
+
+    def _finish(self, partials, shifts, classes, counts, null_counts, label_name) -> "RealVectorizerModel":
+        """Fill values and the statistics sidecar from the merged partial sums (host)."""
+        ncols = len(self.inN)
         w = ncols * (2 if self.trackNulls else 1)
         fills = np.zeros(ncols)
         mean, var, mn, mx, cov = (np.zeros(w) for _ in range(5))
@@ -264,8 +271,66 @@ class RealVectorizer(OpEstimator):
                                 class_sums)
         model = RealVectorizerModel(self, fills.tolist(), self.trackNulls)
         model._fit_stats = stats
-        model._fit_key = (block.values.data_ptr(), n)
         return model
+
+    # -- row chunks (streaming.py): partial sums of every chunk under the first chunk's shifts, merged in chunk order
+    def stream_begin(self, label: Optional["StreamLabel"]):
+        if self.trackNulls:
+            self._metadata = _numeric_metadata(self, True)
+        return {"label": label, "shifts": None, "parts": [], "nc": None}
+
+    def stream_update(self, st, chunk: ColumnarBatch) -> None:
+        names = [f.name for f in self.inN]
+        block = chunk.numeric(names)
+        dev = chunk.on_device("numeric", names, block)
+        ncols, n = len(names), chunk.n
+        lab = st["label"]
+        y = lab.device_label(chunk) if lab is not None else torch.zeros(max(n, 2), dtype=torch.float64, device="cuda")
+        if st["shifts"] is None:
+            d_shifts = torch.zeros(ncols + 1, dtype=torch.float64, device="cuda")
+            L.call("tmog_real_pilot_shift_dev", dev.values.data_ptr(), dev.ld, R.ptr(dev.valid), dev.ldv,
+                   y.data_ptr(), n, ncols, d_shifts.data_ptr(), R.stream())
+            if D.world()[1] > 1:
+                torch.distributed.broadcast(d_shifts, src=0)
+            st["shifts"] = d_shifts
+            nb = C.c_size_t()
+            L.call("tmog_real_fit_scratch_bytes", ncols, C.byref(nb))
+            st["scratch"] = torch.empty(max(nb.value, 256), dtype=torch.uint8, device="cuda")
+        d_part = torch.empty((ncols + 1) * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
+        L.call("tmog_real_fit_partials_dev", dev.values.data_ptr(), dev.ld, R.ptr(dev.valid), dev.ldv, y.data_ptr(),
+               n, ncols, st["shifts"].data_ptr(), st["scratch"].data_ptr(), st["scratch"].numel(), d_part.data_ptr(),
+               R.stream())
+        st["parts"].append(d_part)
+        if lab is not None and lab.classes is not None and self.trackNulls and dev.valid is not None:
+            if st["nc"] is None:
+                st["nc"] = torch.zeros((ncols, MAX_LABEL_CLASSES), dtype=torch.int64, device="cuda")
+            ids = lab.class_ids(chunk)
+            L.call("tmog_null_class_counts_dev", dev.valid.data_ptr(), dev.ldv, ids.data_ptr(), n, ncols,
+                   MAX_LABEL_CLASSES, 1, st["nc"].data_ptr(), R.stream())
+
+    def stream_finish(self, st) -> "RealVectorizerModel":
+        lab = st["label"]
+        ncols = len(self.inN)
+        if st["shifts"] is None:
+            raise ValueError("requirement failed: Input dataset cannot be empty")
+        host = torch.stack(st["parts"]).cpu().numpy()                  # one copy for all chunks
+        merged = np.ascontiguousarray(host[0])
+        for k in range(1, host.shape[0]):
+            other = np.ascontiguousarray(host[k])
+            L.call("tmog_real_partials_merge", merged.ctypes.data, other.ctypes.data, ncols)
+        classes = counts = null_counts = None
+        extra = []
+        if lab is not None and lab.classes is not None:
+            classes, counts = lab.classes, lab.class_counts
+            if self.trackNulls:
+                nc = st["nc"] if st["nc"] is not None else torch.zeros((ncols, MAX_LABEL_CLASSES), dtype=torch.int64,
+                                                                       device="cuda")
+                extra = [nc[:, :len(classes)]]
+        partials, tabs = D.gather_fit_results(merged, extra)
+        if extra:
+            null_counts = tabs[0]
+        shifts = st["shifts"].cpu().numpy()
+        return self._finish(partials, shifts, classes, counts, null_counts, lab.name if lab is not None else None)
 
 
 def _host_pilot_shifts(block: NumericBlock, y: torch.Tensor, n: int, ncols: int) -> np.ndarray:
@@ -295,13 +360,37 @@ class RealVectorizerModel(OpModel):
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
         R.require_cuda()
         names = [f.name for f in self.inN]
-        block = batch.numeric(names)
+        block = _stream_block(batch, names)
         fills, track, chunk = np.asarray(self.fillValues), self.trackNulls, self.chunkRows
         part = LazyDensePart(len(names) * (2 if track else 1),
                              lambda keep: _transform_numeric(block, fills, track, chunk, keep=keep))
-        same = self._fit_key == (block.values.data_ptr(), batch.n)
+        same = self._fit_key is not None and self._fit_key == batch_key(batch)
         return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part],
                             self._fit_stats if same else None)
+
+
+def _stream_block(batch: ColumnarBatch, names) -> NumericBlock:
+    """The numeric block of these columns; for a row chunk of a streamed dataset, its device copy (the chunk's output
+    stays on the device and the caller's sink moves it)."""
+    block = batch.numeric(names)
+    if batch.__dict__.get("_stream") is not None and not block.is_cuda:
+        block = batch.on_device("numeric", names, block)
+    return block
+
+
+_DEV_CONST: dict = {}
+
+
+def _dev_const(kind: str, arr: np.ndarray) -> torch.Tensor:
+    """Small constant arrays of a transform (keep bit masks, fill values) on the device, uploaded once per content:
+    a model transforms many row chunks with the same ones, and a pageable upload per call stalls the stream."""
+    key = (kind, torch.cuda.current_device(), arr.dtype.str, arr.tobytes())
+    t = _DEV_CONST.get(key)
+    if t is None:
+        if len(_DEV_CONST) > 64:
+            _DEV_CONST.clear()
+        t = _DEV_CONST[key] = torch.from_numpy(arr.copy()).cuda()
+    return t
 
 
 def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_nulls: bool, chunk_rows: int,
@@ -325,9 +414,9 @@ def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_n
         if kp is not None:
             bits = np.zeros(round_up(w_full, 64), dtype=np.uint8)
             bits[kp] = 1
-            d_keep = torch.from_numpy(np.packbits(bits, bitorder="little").view("<i8").copy()).cuda()
+            d_keep = _dev_const("keep", np.packbits(bits, bitorder="little").view("<i8"))
         if integral:
-            d_fills = None if fills is None else torch.from_numpy(np.asarray(fills, dtype=np.float64)).cuda()
+            d_fills = None if fills is None else _dev_const("fills", np.asarray(fills, dtype=np.float64))
             if kp is None:
                 L.call("tmog_integral_transform_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
                        n, ncols, R.ptr(d_fills), int(track_nulls), out.data_ptr(), out.shape[1], 0, R.stream())
@@ -344,7 +433,7 @@ def _transform_numeric(block: NumericBlock, fills: Optional[np.ndarray], track_n
                        block.ldv, n, ncols, int(fill_value), int(track_nulls), d_keep.data_ptr(), w, out.data_ptr(),
                        out.shape[1], 0, R.stream())
         else:
-            d_fills = None if fills is None else torch.from_numpy(fills).cuda()
+            d_fills = None if fills is None else _dev_const("fills", np.asarray(fills, dtype=np.float64))
             if kp is None:
                 L.call("tmog_real_transform_dev", block.values.data_ptr(), block.ld, R.ptr(block.valid), block.ldv,
                        n, ncols, R.ptr(d_fills), int(track_nulls), out.data_ptr(), out.shape[1], 0, R.stream())
@@ -377,13 +466,31 @@ class RealNNVectorizer(OpTransformer):
 
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
         R.require_cuda()
-        block = batch.numeric([f.name for f in self.inN])
+        block = _stream_block(batch, [f.name for f in self.inN])
         if block.valid is not None:
             raise ValueError("None.get: a RealNN feature holds a null")
         chunk = self.chunkRows
         part = LazyDensePart(len(block.names), lambda keep: _transform_numeric(block, None, False, chunk, keep=keep))
         stats = _realnn_stats(batch, block) if batch.response else None
         return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part], stats)
+
+    # -- row chunks: the statistics sidecar of a dataset that arrives in chunks (the transformer itself has no fit)
+    def stream_begin(self, label):
+        return {"label": label, "shifts": None, "parts": []}
+
+    def stream_update(self, st, chunk: ColumnarBatch) -> None:
+        if st["label"] is None:
+            return
+        block = chunk.numeric([f.name for f in self.inN])
+        if block.valid is not None:
+            raise ValueError("None.get: a RealNN feature holds a null")
+        _realnn_scan(st, chunk, block, st["label"].device_label(chunk))
+
+    def stream_finish(self, st):
+        lab = st["label"]
+        if lab is None or not st["parts"]:
+            return None
+        return _realnn_finish(st, len(self.inN), lab.name, lab.classes, lab.class_counts)
 
 
 class BinaryVectorizer(OpTransformer):
@@ -413,35 +520,70 @@ class BinaryVectorizer(OpTransformer):
 
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
         R.require_cuda()
-        block = batch.numeric([f.name for f in self.inN])
+        block = _stream_block(batch, [f.name for f in self.inN])
         track, chunk, fv = self.trackNulls, self.chunkRows, self.fillValue
         part = LazyDensePart(len(block.names) * (2 if track else 1),
                              lambda keep: _transform_numeric(block, None, track, chunk, fv, keep=keep))
         stats = _binary_stats(batch, block, track, fv) if batch.response else None
         return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part], stats)
 
+    # -- row chunks
+    def stream_begin(self, label):
+        return {"label": label, "acc": {}, "n": 0}
+
+    def stream_update(self, st, chunk: ColumnarBatch) -> None:
+        lab = st["label"]
+        if lab is None:
+            return
+        block = chunk.numeric([f.name for f in self.inN])
+        ids = lab.class_ids(chunk) if lab.classes is not None else None
+        _binary_scan(st["acc"], chunk, block, lab.device_label(chunk), lab.classes, ids, lab.continuous())
+        st["n"] += chunk.n
+
+    def stream_finish(self, st):
+        lab = st["label"]
+        if lab is None or not st["acc"]:
+            return None
+        return _binary_finish(st["acc"], len(self.inN), self.trackNulls, self.fillValue, lab.name, lab.classes,
+                              lab.class_counts, lab.continuous(), st["n"])
+
 
 def _realnn_stats(batch: ColumnarBatch, block: NumericBlock) -> Optional[VectorStats]:
     """Statistics sidecar of a RealNN block: the fused fit scan without nulls (the vectorizer itself has no fit)."""
-    label_name = batch.response
-    dev = block if block.is_cuda else block.to("cuda")
-    y = batch.label()
+    st = {"shifts": None, "parts": []}
+    _realnn_scan(st, batch, block, batch.label())
+    classes, counts, _ids = label_info_dev(batch, st["y"], batch.response)
+    return _realnn_finish(st, len(block.names), batch.response, classes, counts)
+
+
+def _realnn_scan(st: dict, batch: ColumnarBatch, block: NumericBlock, y: torch.Tensor) -> None:
+    dev = block if block.is_cuda else batch.on_device("numeric", block.names, block)
     y = y if y.is_cuda else y.cuda()
+    st["y"] = y
     n, ncols = batch.n, len(block.names)
-    nb = C.c_size_t()
-    L.call("tmog_real_fit_scratch_bytes", ncols, C.byref(nb))
-    scratch = R.scratch("real_fit", nb.value)
-    d_shifts = torch.zeros(ncols + 1, dtype=torch.float64, device="cuda")
+    if st["shifts"] is None:
+        nb = C.c_size_t()
+        L.call("tmog_real_fit_scratch_bytes", ncols, C.byref(nb))
+        st["scratch"] = R.scratch("real_fit", nb.value)
+        st["shifts"] = torch.zeros(ncols + 1, dtype=torch.float64, device="cuda")
+        L.call("tmog_real_pilot_shift_dev", dev.values.data_ptr(), dev.ld, None, 0, y.data_ptr(), n, ncols,
+               st["shifts"].data_ptr(), R.stream())
+        if D.world()[1] > 1:
+            torch.distributed.broadcast(st["shifts"], src=0)
     d_part = torch.zeros((ncols + 1) * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
-    L.call("tmog_real_pilot_shift_dev", dev.values.data_ptr(), dev.ld, None, 0, y.data_ptr(), n, ncols,
-           d_shifts.data_ptr(), R.stream())
-    if D.world()[1] > 1:
-        torch.distributed.broadcast(d_shifts, src=0)
     L.call("tmog_real_fit_partials_dev", dev.values.data_ptr(), dev.ld, None, 0, y.data_ptr(), n, ncols,
-           d_shifts.data_ptr(), scratch.data_ptr(), scratch.numel(), d_part.data_ptr(), R.stream())
-    partials = D.allreduce_real_partials(d_part.cpu().numpy())
-    shifts = d_shifts.cpu().numpy()
-    classes, counts, _ids = label_info_dev(batch, y, label_name)
+           st["shifts"].data_ptr(), st["scratch"].data_ptr(), st["scratch"].numel(), d_part.data_ptr(), R.stream())
+    st["parts"].append(d_part)
+
+
+def _realnn_finish(st: dict, ncols: int, label_name: str, classes, counts) -> VectorStats:
+    host = torch.stack(st["parts"]).cpu().numpy()
+    merged = np.ascontiguousarray(host[0])
+    for k in range(1, host.shape[0]):
+        other = np.ascontiguousarray(host[k])
+        L.call("tmog_real_partials_merge", merged.ctypes.data, other.ctypes.data, ncols)
+    partials = D.allreduce_real_partials(merged)
+    shifts = st["shifts"].cpu().numpy()
     mean, var, mn, mx, cov = (np.zeros(ncols) for _ in range(5))
     lab = np.zeros(5)
     L.call("tmog_real_finish", partials.ctypes.data, shifts.ctypes.data, ncols, 1, 0.0, 0, None, mean.ctypes.data,
@@ -453,35 +595,52 @@ def _realnn_stats(batch: ColumnarBatch, block: NumericBlock) -> Optional[VectorS
 def _binary_stats(batch: ColumnarBatch, block: NumericBlock, track_nulls: bool, fill_value: bool
                   ) -> Optional[VectorStats]:
     """Statistics sidecar of BinaryVectorizer's [value, isNull] columns from count[{null, false, true}][label class]
-    (needs a categorical label; otherwise SanityChecker scans the materialised block)."""
-    from .pivot import _stats_from_class_counts
+    (a continuous label adds the label sums per {null, false, true})."""
     label_name = batch.response
-    dev = block if block.is_cuda else block.to("cuda")
     y = batch.label()
     y = y if y.is_cuda else y.cuda()
     classes, class_counts, ids = label_info_dev(batch, y, label_name)
+    cont = None if classes is not None else label_moments_dev(batch, y, label_name)
+    st: dict = {}
+    _binary_scan(st, batch, block, y, classes, ids, cont)
+    return _binary_finish(st, len(block.names), track_nulls, fill_value, label_name, classes, class_counts, cont,
+                          batch.n)
+
+
+def _binary_scan(st: dict, batch: ColumnarBatch, block: NumericBlock, y: torch.Tensor, classes, ids, cont) -> None:
+    """One batch / row chunk into the accumulators of `st` (count tables widened to int64 per call)."""
+    dev = block if block.is_cuda else batch.on_device("numeric", block.names, block)
     n, ncols, ncls = batch.n, len(block.names), (len(classes) if classes is not None else 1)
     ldc = round_up(max(n, 1), 4)
     codes = torch.empty((ncols, ldc), dtype=torch.int32, device="cuda")
     L.call("tmog_binary_codes_dev", dev.values.data_ptr(), dev.ld, R.ptr(dev.valid), dev.ldv, n, ncols,
            codes.data_ptr(), ldc, R.stream())
-    desc = np.zeros((ncols, 4), dtype=np.int64)
-    for c in range(ncols):
-        desc[c] = [3, 0, c * 3 * ncls, 2]          # ids: 0 null, 1 false, 2 true
-    d_desc = torch.from_numpy(desc).cuda()
+    if "desc" not in st:
+        desc = np.zeros((ncols, 4), dtype=np.int64)
+        for c in range(ncols):
+            desc[c] = [3, 0, c * 3 * ncls, 2]          # ids: 0 null, 1 false, 2 true
+        st["desc"] = torch.from_numpy(desc).cuda()
+        st["acc"] = torch.zeros(ncols * 3 * ncls, dtype=torch.int64, device="cuda")
+        st["bad"] = torch.zeros(1, dtype=torch.int32, device="cuda")
+        st["ws"] = torch.zeros(ncols * 3, dtype=torch.float64, device="cuda") if cont is not None else None
+        st["woff"] = torch.arange(0, ncols * 3, 3, dtype=torch.int64, device="cuda")
     d_counts = torch.zeros(ncols * 3 * ncls, dtype=torch.int32, device="cuda")
-    d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
     L.call("tmog_pivot_count_dev", codes.data_ptr(), ldc, n, ncols, ids.data_ptr() if classes is not None else None,
-           ncls, d_desc.data_ptr(), None, 3, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
-    cnt = D.allreduce_sum(d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(ncols, 3, ncls)
-    n_global = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
-    if classes is None:                              # continuous label: counts + label sums per {null, false, true}
-        lab, shift = label_moments_dev(batch, y, label_name)
-        d_ws = torch.zeros(ncols * 3, dtype=torch.float64, device="cuda")
-        d_off = torch.arange(0, ncols * 3, 3, dtype=torch.int64, device="cuda")
-        L.call("tmog_pivot_label_sum_dev", codes.data_ptr(), ldc, n, ncols, d_desc.data_ptr(), None, d_off.data_ptr(),
-               y.data_ptr(), shift, d_ws.data_ptr(), R.stream())
-        ws = D.allreduce_sum(d_ws.cpu().numpy()).reshape(ncols, 3)
+           ncls, st["desc"].data_ptr(), None, 3, d_counts.data_ptr(), st["bad"].data_ptr(), R.stream())
+    st["acc"] += d_counts.to(torch.int64) & 0xFFFFFFFF
+    if cont is not None:                             # continuous label: label sums per {null, false, true}
+        L.call("tmog_pivot_label_sum_dev", codes.data_ptr(), ldc, n, ncols, st["desc"].data_ptr(), None,
+               st["woff"].data_ptr(), y.data_ptr(), cont[1], st["ws"].data_ptr(), R.stream())
+
+
+def _binary_finish(st: dict, ncols: int, track_nulls: bool, fill_value: bool, label_name: str, classes,
+                   class_counts, cont, n_local: int) -> VectorStats:
+    from .pivot import _stats_from_class_counts
+    ncls = len(classes) if classes is not None else 1
+    cnt = D.allreduce_sum(st["acc"].cpu().numpy()).reshape(ncols, 3, ncls)
+    if classes is None:
+        lab, shift = cont
+        ws = D.allreduce_sum(st["ws"].cpu().numpy()).reshape(ncols, 3)
         c1, w1 = [], []
         for c in range(ncols):
             c1.append(cnt[c, 2, 0] + (cnt[c, 0, 0] if fill_value else 0))
@@ -492,16 +651,17 @@ def _binary_stats(batch: ColumnarBatch, block: NumericBlock, track_nulls: bool, 
         sv = np.asarray(c1, dtype=np.float64)
         ones = np.ones_like(sv)
         return stats_from_sums_continuous(sv, sv, sv, ones, ones, np.asarray(w1), lab, shift, label_name)
+    n_global = int(np.asarray(class_counts).sum())
     rows = []
     for c in range(ncols):
         ones = cnt[c, 2] + (cnt[c, 0] if fill_value else 0)
         rows.append(ones)
         if track_nulls:
             rows.append(cnt[c, 0])
-    st = _stats_from_class_counts(np.stack(rows).astype(np.float64), classes, class_counts, n_global, label_name)
-    if st.class_sums is not None:                    # only the null indicators are categorical columns
-        keep = np.zeros(st.width, dtype=bool)
+    stt = _stats_from_class_counts(np.stack(rows).astype(np.float64), classes, class_counts, n_global, label_name)
+    if stt.class_sums is not None:                    # only the null indicators are categorical columns
+        keep = np.zeros(stt.width, dtype=bool)
         if track_nulls:
             keep[1::2] = True
-        st.class_sums[:, ~keep] = np.nan
-    return st
+        stt.class_sums[:, ~keep] = np.nan
+    return stt

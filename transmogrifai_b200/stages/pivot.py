@@ -19,7 +19,7 @@ from .. import _lib as L
 from .. import dist as D
 from .. import features as F
 from .. import runtime as R
-from ..columnar import (ColumnarBatch, DictBlock, LazyOneHotPart, OneHotPart, VectorColumn, decode_strings,
+from ..columnar import (batch_key, ColumnarBatch, DictBlock, LazyOneHotPart, OneHotPart, VectorColumn, decode_strings,
                         encode_strings, round_up)
 from ..metadata import NullString, OpVectorColumnMetadata, OpVectorMetadata, OtherString
 from ..stats import LabelInfo, VectorStats
@@ -147,63 +147,119 @@ class OpTextPivotVectorizer(OpEstimator):
         names = [f.name for f in self.inN]
         block = batch.strings(names)
         dev = batch.on_device("strings", names, block)
-        n, ncols = batch.n, len(names)
+        n = batch.n
         label_name = batch.response
-        classes = counts_per_class = ids = None
-        ncodes = np.array([len(d) for d in block.dicts], dtype=np.int64)
-        clean = int(self.cleanText)
-
-        def prepare(data, offs, nc):
-            """The counts-independent half of a column's finish (clean + group its dictionary), on a pool thread."""
-            h = C.c_void_p()
-            L.call("tmog_pivot_dict_prepare", data.ctypes.data, offs.ctypes.data, nc, clean, C.byref(h))
-            return h, (data, offs)                          # the arrays stay alive with the handle
-
         # One process: the dictionaries are final, so their cleaning starts now, largest first, and runs on host
         # threads while the label classes and the count kernel are on the GPU.
         # Ranks may have encoded their rows against different dictionaries (one per exported partition): the count
         # tables are then re-indexed against the union dictionary (rank order) before they are summed.  Where all ranks
         # share their dictionaries (compared by digest) the cleaning can start at once as well.
         g_dicts, g_maps = self._union_dictionaries(block)
-        early = None
-        if ncols > 0 and all(m is None for m in g_maps):
-            order = sorted(range(ncols), key=lambda c: -int(ncodes[c]))
-            futs = {c: _pool().submit(prepare, *block.dict_arrays(c), int(ncodes[c])) for c in order}
-            early = futs
+        early = self._start_prepare(block, g_maps)
+        classes = counts_per_class = ids = y = cont = None
         if label_name:
             y = batch.label()
             y = y if y.is_cuda else y.cuda()
             classes, counts_per_class, ids = label_info_dev(batch, y, label_name)
-        ncls = len(classes) if classes is not None else 1
+            if classes is None:
+                cont = label_moments_dev(batch, y, label_name)
+        st = self._scan_begin(block.dicts, len(classes) if classes is not None else 1, cont is not None)
+        self._scan(st, dev, n, ids if classes is not None else None, y, cont)
+        model = self._finish_counts(block, g_dicts, g_maps, early, [st], classes, counts_per_class, n, label_name, cont)
+        model._fit_key = batch_key(batch)
+        return model
+
+    def _start_prepare(self, block, g_maps):
+        """The counts-independent half of every column's finish (clean + group its dictionary) on the pool threads,
+        largest dictionary first -- only when the dictionaries are final (no union across ranks pending)."""
+        ncols = len(block.dicts)
+        if ncols == 0 or not all(m is None for m in g_maps):
+            return None
+        clean = int(self.cleanText)
+        order = sorted(range(ncols), key=lambda c: -len(block.dicts[c]))
+        return {c: _pool().submit(_prepare_dict, *block.dict_arrays(c), len(block.dicts[c]), clean) for c in order}
+
+    @staticmethod
+    def _scan_begin(dicts, ncls: int, continuous: bool) -> dict:
+        """Accumulators of the count scan over one set of dictionaries (`dicts`: one list per column)."""
+        ncols = len(dicts)
+        ncodes = np.array([len(d) for d in dicts], dtype=np.int64)
         nids = ncodes + 1                                   # raw codes + the null id 0
         zeros = np.zeros(ncols, dtype=np.int64)
         count_offset = np.concatenate([[0], np.cumsum(nids * ncls)[:-1]]).astype(np.int64) if ncols else zeros
         desc = np.ascontiguousarray(np.stack([nids, zeros, count_offset, ncodes], axis=1)) if ncols else \
             np.zeros((0, 4), dtype=np.int64)
         total_bins = int((nids * ncls).sum())
-        d_desc = torch.from_numpy(desc).cuda()
-        d_counts = torch.zeros(max(total_bins, 1), dtype=torch.int32, device="cuda")     # uint32 bins
-        d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+        st = dict(dicts=list(dicts), ncls=ncls, ncodes=ncodes, nids=nids, count_offset=count_offset,
+                  d_desc=torch.from_numpy(desc).cuda(), total_bins=total_bins,
+                  acc=None, bad=torch.zeros(1, dtype=torch.int32, device="cuda"), ws=None, calls=0)
+        if continuous:
+            w_off = np.concatenate([[0], np.cumsum(nids)[:-1]]).astype(np.int64) if ncols else zeros
+            st["w_off"] = w_off
+            st["d_woff"] = torch.from_numpy(w_off).cuda()
+            st["ws"] = torch.zeros(max(int(nids.sum()), 1), dtype=torch.float64, device="cuda")
+        return st
+
+    @staticmethod
+    def _scan(st: dict, dev, n: int, ids, y, cont) -> None:
+        """count[code][class] of one batch / row chunk (uint32 bins per call, widened into the int64 accumulator)."""
+        ncols = len(st["dicts"])
+        d_counts = torch.zeros(max(st["total_bins"], 1), dtype=torch.int32, device="cuda")     # uint32 bins
         L.call("tmog_pivot_count_dev", dev.codes.data_ptr(), dev.ld, n, ncols,
-               ids.data_ptr() if classes is not None else None, ncls, d_desc.data_ptr(), None,
-               int(nids.max()) if ncols else 1, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
+               ids.data_ptr() if ids is not None else None, st["ncls"], st["d_desc"].data_ptr(), None,
+               int(st["nids"].max()) if ncols else 1, d_counts.data_ptr(), st["bad"].data_ptr(), R.stream())
+        wide = d_counts.to(torch.int64) & 0xFFFFFFFF
+        st["acc"] = wide if st["acc"] is None else st["acc"].add_(wide)
+        if cont is not None:
+            # continuous label: the label sums of every raw code next to the plain counts (one class)
+            L.call("tmog_pivot_label_sum_dev", dev.codes.data_ptr(), dev.ld, n, ncols, st["d_desc"].data_ptr(), None,
+                   st["d_woff"].data_ptr(), y.data_ptr(), cont[1], st["ws"].data_ptr(), R.stream())
+        st["calls"] += 1
+
+    def _finish_counts(self, block, g_dicts, g_maps, early, scans, classes, counts_per_class, n_local: int,
+                       label_name, cont) -> "OpTextPivotVectorizerModel":
+        """Everything after the count scans: `scans` = the accumulators of this rank, one per set of dictionaries its
+        rows were encoded against (scans[0] is the one `block`, `g_dicts` and `g_maps` describe; further ones come
+        with `maps`: per column the table of their codes in block.dicts)."""
+        ncols = len(block.dicts)
+        ncls = len(classes) if classes is not None else 1
+        zeros = np.zeros(ncols, dtype=np.int64)
+        st0 = scans[0]
+        nids, count_offset = st0["nids"], st0["count_offset"]
         shared_dicts = all(m is None for m in g_maps)
-        if D.world()[1] > 1 and shared_dicts:
+        if any(int(st["bad"].item()) for st in scans):
+            raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
+        if len(scans) == 1 and D.world()[1] > 1 and shared_dicts:
             # every rank counted against the same dictionaries: the tables add up on the device, one copy back
-            g_dev = d_counts.to(torch.int64) & 0xFFFFFFFF
+            g_dev = st0["acc"].clone()
             torch.distributed.all_reduce(g_dev)
             counts = g_dev.cpu().numpy()
+            summed = True
         else:
-            counts = d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF
-        if int(d_bad.item()):
-            raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
+            counts = st0["acc"].cpu().numpy().copy()
+            summed = False
+        ws = None if cont is None else st0["ws"].cpu().numpy().copy()
+        for st in scans[1:]:                                 # row chunks that came with other dictionaries
+            loc = st["acc"].cpu().numpy()
+            lws = None if cont is None else st["ws"].cpu().numpy()
+            for c in range(ncols):
+                m = st["maps"][c]
+                src = loc[st["count_offset"][c]:st["count_offset"][c] + st["nids"][c] * ncls].reshape(-1, ncls)
+                dst = counts[count_offset[c]:count_offset[c] + nids[c] * ncls].reshape(-1, ncls)
+                dst[0] += src[0]
+                np.add.at(dst, 1 + m, src[1:])
+                if ws is not None:
+                    ws[st0["w_off"][c]] += lws[st["w_off"][c]]
+                    np.add.at(ws, st0["w_off"][c] + 1 + m, lws[st["w_off"][c] + 1:st["w_off"][c] + st["nids"][c]])
         if classes is not None:
             n_global = int(np.asarray(counts_per_class).sum())          # rows of all ranks, from the label classes
+        elif cont is not None:
+            n_global = int(cont[0][0])
         else:
-            n_global = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
+            n_global = int(D.allreduce_sum(np.array([n_local], dtype=np.int64))[0])
         g_ncodes = np.array([len(d) for d in g_dicts], dtype=np.int64)
         g_offset = np.concatenate([[0], np.cumsum((g_ncodes + 1) * ncls)[:-1]]).astype(np.int64) if ncols else zeros
-        if any(m is not None for m in g_maps):
+        if not shared_dicts:
             g_counts = np.zeros(int(((g_ncodes + 1) * ncls).sum()), dtype=np.int64)
             for c in range(ncols):
                 loc = counts[count_offset[c]:count_offset[c] + nids[c] * ncls].reshape(int(nids[c]), ncls)
@@ -214,16 +270,17 @@ class OpTextPivotVectorizer(OpEstimator):
                     dst[0] = loc[0]                                   # the null id
                     dst[1 + g_maps[c]] = loc[1:]
             counts = g_counts
-        if not (D.world()[1] > 1 and shared_dicts):
+        if not summed:
             counts = D.allreduce_sum(counts)
+        clean = int(self.cleanText)
 
         def finish(c: int):
             nc = int(g_ncodes[c])
             if early is not None:
                 handle, _keep = early[c].result()
             else:
-                handle, _keep = prepare(*(block.dict_arrays(c) if g_maps[c] is None else encode_strings(g_dicts[c])),
-                                        nc)
+                handle, _keep = _prepare_dict(*(block.dict_arrays(c) if g_maps[c] is None
+                                                else encode_strings(g_dicts[c])), nc, clean)
             try:
                 raw = np.ascontiguousarray(counts[g_offset[c]:g_offset[c] + (nc + 1) * ncls])
                 k = self.topK
@@ -269,13 +326,8 @@ class OpTextPivotVectorizer(OpEstimator):
         elif label_name:
             # continuous label: the plain counts above (one class) + the label sums of every raw code, folded into the
             # emitted columns (top values, OTHER, null) with the code -> column table of the finish
-            lab, shift = label_moments_dev(batch, y, label_name)
-            w_off = np.concatenate([[0], np.cumsum(nids)[:-1]]).astype(np.int64) if ncols else zeros
-            d_ws = torch.zeros(max(int(nids.sum()), 1), dtype=torch.float64, device="cuda")
-            d_woff = torch.from_numpy(w_off).cuda()
-            L.call("tmog_pivot_label_sum_dev", dev.codes.data_ptr(), dev.ld, n, ncols, d_desc.data_ptr(), None,
-                   d_woff.data_ptr(), y.data_ptr(), shift, d_ws.data_ptr(), R.stream())
-            ws = d_ws.cpu().numpy()
+            lab, shift = cont
+            w_off = st0["w_off"]
             cnt_cols, ws_cols = [], []
             for c in range(ncols):
                 k = len(tops[c])
@@ -290,9 +342,91 @@ class OpTextPivotVectorizer(OpEstimator):
                                                shift, label_name)
         model = OpTextPivotVectorizerModel(self, tops, self.cleanText, self.trackNulls)
         model._fit_stats = stats
-        model._fit_key = (block.codes.data_ptr(), n)
         model._fit_tables = {id(block.dicts[c]): (block.dicts[c], results[c][1]) for c in range(ncols)}
+        for st in scans[1:]:               # the other dictionaries this rank met: their codes through block.dicts
+            for c in range(ncols):
+                model._fit_tables[id(st["dicts"][c])] = (st["dicts"][c], results[c][1][st["maps"][c]])
         return model
+
+    # -- row chunks (streaming.py): one accumulator per set of dictionaries the chunks were encoded against
+    def stream_begin(self, label):
+        return {"label": label, "groups": {}, "order": [], "n": 0}
+
+    def stream_update(self, st, chunk: ColumnarBatch) -> None:
+        names = [f.name for f in self.inN]
+        block = chunk.strings(names)
+        dev = chunk.on_device("strings", names, block)
+        lab = st["label"]
+        sig = tuple(id(d) for d in block.dicts)
+        g = st["groups"].get(sig)
+        if g is None:
+            ncls = len(lab.classes) if lab is not None and lab.classes is not None else 1
+            g = st["groups"][sig] = self._scan_begin(block.dicts, ncls, lab is not None and lab.classes is None)
+            st["order"].append(sig)
+            st["names"], st["type_name"] = list(block.names), block.type_name
+        ids = y = cont = None
+        if lab is not None:
+            if lab.classes is not None:
+                ids = lab.class_ids(chunk)
+            else:
+                y, cont = lab.device_label(chunk), lab.continuous()
+        self._scan(g, dev, chunk.n, ids, y, cont)
+        st["n"] += chunk.n
+
+    def stream_finish(self, st) -> "OpTextPivotVectorizerModel":
+        lab = st["label"]
+        scans = [st["groups"][sig] for sig in st["order"]]
+        if not scans:
+            raise ValueError("requirement failed: Input dataset cannot be empty")
+        ncols = len(scans[0]["dicts"])
+        # dictionary of this rank: the first set, extended by the values only later chunks brought (first-seen order)
+        dicts = [list(d) for d in scans[0]["dicts"]] if len(scans) > 1 else scans[0]["dicts"]
+        if len(scans) > 1:
+            index = [{v: i for i, v in enumerate(d)} for d in dicts]
+            for sc in scans[1:]:
+                sc["maps"] = []
+                for c in range(ncols):
+                    ix = index[c]
+                    for v in sc["dicts"][c]:
+                        if v not in ix:
+                            ix[v] = len(dicts[c])
+                            dicts[c].append(v)
+                    sc["maps"].append(np.array([ix[v] for v in sc["dicts"][c]], dtype=np.int64))
+            # the first accumulator is re-laid out for the extended dictionaries (its own codes keep their places)
+            ncls = scans[0]["ncls"]
+            first = scans[0]
+            wide = self._scan_begin(dicts, ncls, first["ws"] is not None)
+            acc = torch.zeros(max(wide["total_bins"], 1), dtype=torch.int64, device="cuda")
+            for c in range(ncols):
+                a, k = int(first["count_offset"][c]), int(first["nids"][c]) * ncls
+                b = int(wide["count_offset"][c])
+                acc[b:b + k] = first["acc"][a:a + k]
+                if first["ws"] is not None:
+                    wa, wb, kk = int(first["w_off"][c]), int(wide["w_off"][c]), int(first["nids"][c])
+                    wide["ws"][wb:wb + kk] = first["ws"][wa:wa + kk]
+            wide["acc"], wide["bad"] = acc, first["bad"]
+            first_tables = first["dicts"]
+            scans = [wide] + scans[1:]
+        block = DictBlock(st["names"], st["type_name"], torch.zeros((ncols, 4), dtype=torch.int32), dicts, 0)
+        g_dicts, g_maps = self._union_dictionaries(block)
+        early = self._start_prepare(block, g_maps)
+        classes = counts = cont = None
+        if lab is not None:
+            classes, counts, cont = lab.classes, lab.class_counts, lab.continuous()
+        model = self._finish_counts(block, g_dicts, g_maps, early, scans, classes, counts, st["n"],
+                                    lab.name if lab is not None else None, cont)
+        if len(st["order"]) > 1:           # codes of the first chunk's own dictionaries are a prefix of the extended ones
+            for c in range(ncols):
+                d0 = first_tables[c]
+                model._fit_tables[id(d0)] = (d0, model._fit_tables[id(dicts[c])][1][:len(d0)])
+        return model
+
+
+def _prepare_dict(data, offs, nc: int, clean: int):
+    """tmog_pivot_dict_prepare of one column's dictionary (Arrow utf8 arrays); the arrays stay alive with the handle."""
+    h = C.c_void_p()
+    L.call("tmog_pivot_dict_prepare", data.ctypes.data, offs.ctypes.data, nc, clean, C.byref(h))
+    return h, (data, offs)
 
 
 _POOL = None
@@ -357,7 +491,7 @@ class OpTextPivotVectorizerModel(OpModel):
         width = sum(self._widths())
         dev_of = batch.device_thunk("strings", names, block)
         part = LazyOneHotPart(width, lambda keep: self._materialize(block, keep, dev_of))
-        same = self._fit_key == (block.codes.data_ptr(), batch.n)
+        same = self._fit_key is not None and self._fit_key == batch_key(batch)
         return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part],
                             self._fit_stats if same else None)
 
@@ -377,6 +511,24 @@ class OpTextPivotVectorizerModel(OpModel):
     def _materialize(self, block: DictBlock, keep: Optional[List[int]], on_device=None) -> OneHotPart:
         dev = on_device() if on_device is not None else (block if block.is_cuda else block.to("cuda"))
         n, ncols = block.n, len(block.names)
+        # position tables depend on the dictionaries and the kept columns only: row chunks encoded against the same
+        # dictionaries share them
+        key = (torch.cuda.current_device(), tuple(id(d) for d in block.dicts),
+               None if keep is None else np.asarray(keep).tobytes())
+        plans = self.__dict__.setdefault("_plans", {})
+        plan = plans.get(key)
+        if plan is None or any(a is not b for a, b in zip(plan[3], block.dicts)):
+            if len(plans) > 8:
+                plans.clear()
+            plan = plans[key] = self._position_tables(block, keep) + (list(block.dicts),)
+        d_desc, d_pos, out_width, _dicts = plan
+        out = torch.empty((n, max(ncols, 1)), dtype=torch.int32, device="cuda")   # dense rows: no unwritten padding
+        L.call("tmog_pivot_transform_dev", dev.codes.data_ptr(), dev.ld, n, ncols, d_desc.data_ptr(),
+               d_pos.data_ptr(), out.data_ptr(), out.shape[1], 0, R.stream())
+        return OneHotPart(out[:, :ncols], out_width)
+
+    def _position_tables(self, block: DictBlock, keep):
+        ncols = len(block.names)
         widths = self._widths()
         width = sum(widths)
         newpos = np.arange(width, dtype=np.int32)
@@ -400,9 +552,4 @@ class OpTextPivotVectorizerModel(OpModel):
         ncodes = np.array([len(d) for d in block.dicts], dtype=np.int64)
         slot_off = np.concatenate([[0], np.cumsum(ncodes)[:-1]]).astype(np.int64) if ncols else ncodes
         desc = np.ascontiguousarray(np.stack([ncodes + 1, slot_off, np.zeros_like(ncodes), ncodes], axis=1))
-        d_desc = torch.from_numpy(desc).cuda()
-        d_pos = torch.from_numpy(pos).cuda()
-        out = torch.empty((n, max(ncols, 1)), dtype=torch.int32, device="cuda")   # dense rows: no unwritten padding
-        L.call("tmog_pivot_transform_dev", dev.codes.data_ptr(), dev.ld, n, ncols, d_desc.data_ptr(),
-               d_pos.data_ptr(), out.data_ptr(), out.shape[1], 0, R.stream())
-        return OneHotPart(out[:, :ncols], out_width)
+        return torch.from_numpy(desc).cuda(), torch.from_numpy(pos).cuda(), out_width

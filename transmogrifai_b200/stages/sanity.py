@@ -293,6 +293,9 @@ class SanityChecker(OpEstimator):
         XORShift stream is not restated, so the sample is a different one with the same law).  The sampled raw rows
         form a batch of their own, the upstream transformers run again on it, and the statistics are those of the
         resulting vector (no statistics sidecar applies to a sample)."""
+        if not batch.blocks:
+            raise NotImplementedError("SanityChecker sampling (fraction < 1) over a dataset streamed in row chunks: set "
+                                      "sampleUpperLimit >= the row count (statistics then come from the fused scans)")
         dev = "cuda" if any(getattr(b, "is_cuda", False) for b in batch.blocks) else "cpu"
         g = torch.Generator(device=dev).manual_seed(int(self.sampleSeed) + D.world()[0])   # a stream per row shard
         idx = (torch.rand(batch.n, device=dev, generator=g) < frac).nonzero().squeeze(1)

@@ -20,7 +20,7 @@ from .. import _lib as L
 from .. import dist as D
 from .. import features as F
 from .. import runtime as R
-from ..columnar import ColumnarBatch, LazyPart, SetBlock, SparseRowsPart, VectorColumn
+from ..columnar import batch_key, ColumnarBatch, LazyPart, SetBlock, SparseRowsPart, VectorColumn
 from ..stats import LabelInfo, VectorStats
 from .base import OpModel
 from .numeric import label_info_dev, label_moments_dev, stats_from_sums_continuous
@@ -80,7 +80,7 @@ class OpSetVectorizer(OpTextPivotVectorizer):
         self._metadata = self._metadata_for(tops)
         model = OpSetVectorizerModel(self, tops, self.cleanText, self.trackNulls)
         model._pos_cache = {id(block.dicts[c]): (block.dicts[c], pos_tables[c]) for c in range(ncols)}
-        model._fit_key = (block.offsets[0].data_ptr(), n) if ncols else None
+        model._fit_key = batch_key(batch)
         if label_name:
             cont = None if classes is not None else label_moments_dev(batch, y, label_name) + (y,)
             model._fit_stats = model._sidecar(dev, n, n_all, classes, class_counts, ids, label_name, cont)
@@ -178,7 +178,7 @@ class OpSetVectorizerModel(OpModel):
         names = [f.name for f in self.inN]
         block = batch.sets(names)
         n = batch.n
-        same = bool(names) and self._fit_key == (block.offsets[0].data_ptr(), n)
+        same = bool(names) and self._fit_key is not None and self._fit_key == batch_key(batch)
         dev_of = batch.device_thunk("sets", names, block)
         parts = [LazyPart(self.widths[c], (lambda keep, c=c: self._materialize(dev_of(), c, n, keep)))
                  for c in range(len(names))]

@@ -17,7 +17,7 @@ from .. import _lib as L
 from .. import dist as D
 from .. import features as F
 from .. import runtime as R
-from ..columnar import ColumnarBatch, LazyPart, OneHotPart, SparseRowsPart, TextBlock, VectorColumn, encode_strings
+from ..columnar import batch_key, ColumnarBatch, LazyPart, OneHotPart, SparseRowsPart, TextBlock, VectorColumn, encode_strings
 from ..metadata import NullString, OpVectorColumnMetadata, OpVectorMetadata, OtherString, feature_column
 from ..stats import LabelInfo, VectorStats
 from .base import OpEstimator, OpModel
@@ -25,6 +25,8 @@ from .numeric import label_info_dev, label_moments_dev, stats_from_sums_continuo
 from .pivot import _stats_from_class_counts, clean_and_group, top_k
 
 PIVOT, HASH, IGNORE = "Pivot", "Hash", "Ignore"
+NON_ASCII_CLEAN = ("non-ASCII text met with cleanText = true: Java's Unicode case mapping is not restated on "
+                   "this path")
 MAX_NUM_OF_FEATURES = 1 << 17     # TransmogrifierDefaults.MaxNumOfFeatures
 M64 = (1 << 64) - 1
 
@@ -80,23 +82,36 @@ def _col_desc(block: TextBlock) -> torch.Tensor:
 
 
 class _HashLayout:
-    """Geometry of the hash + null-indicator part of the output vector."""
+    """Geometry of the text part of the output vector: [hash block | text lengths | null indicators]
+    (SmartTextVectorizer.scala:154-186, :333-356).  The kernels index their statistics arrays by vector index inside
+    this part, with room for the null indicators of every text column whether or not they are emitted."""
 
     def __init__(self, names: Sequence[str], hash_idx: List[int], ignore_idx: List[int], num_features: int,
-                 num_inputs: int, strategy: str, prepend: bool, track_nulls: bool):
+                 num_inputs: int, strategy: str, prepend: bool, track_nulls: bool, track_len: bool = False):
         s = strategy.lower()
         self.shared = True if s == "shared" else False if s == "separate" else \
             num_features * num_inputs > MAX_NUM_OF_FEATURES          # isSharedHashSpace :191-199
         self.num_features = num_features
         self.hash_idx, self.ignore_idx = hash_idx, ignore_idx
-        self.text_idx = hash_idx + ignore_idx                       # null indicators: hash columns, then ignored
+        self.text_idx = hash_idx + ignore_idx                       # lengths / null indicators: hash columns, then ignored
         self.hash_width = 0 if not hash_idx else (num_features if self.shared else num_features * len(hash_idx))
+        self.len_width = len(self.text_idx) if track_len else 0
         self.null_width = len(self.text_idx) if track_nulls else 0
-        self.width = self.hash_width + self.null_width
+        self.len_base = self.hash_width
+        self.null_base = self.hash_width + self.len_width
+        self.kernel_width = self.null_base + len(self.text_idx)
+        self.width = self.hash_width + self.len_width + self.null_width
         # the reference zips the NON-PIVOT features (hash and ignore, input order) with the hash columns (:348,358-361)
         non_pivot = sorted(self.text_idx)
         self.prefix_names = [names[non_pivot[k]] for k in range(len(hash_idx))]
         self.prepend = prepend
+
+    def stats_columns(self, *arrays):
+        """The emitted columns of arrays indexed by kernel vector index (rows)."""
+        return tuple(a[:self.width] for a in arrays)
+
+    def stats_columns_1d(self, a):
+        return a[:self.width]
 
 
 class SmartTextVectorizer(OpEstimator):
@@ -230,8 +245,109 @@ class SmartTextVectorizer(OpEstimator):
             classes, class_counts, ids = label_info_dev(batch, y, label_name)
             n_all = int(D.allreduce_sum(np.array([n], dtype=np.int64))[0])
             cont = None if classes is not None else label_moments_dev(batch, y, label_name) + (y,)
-            model._fit_stats = model._sidecar(dev, n, n_all, classes, class_counts, ids, label_name, cont)
-        model._fit_key = (block.offsets[0].data_ptr(), n)
+            st = model._side_begin(classes, cont is not None)
+            model._side_scan(st, dev, n, ids, cont, fused_rows=True)
+            model._fit_stats = model._side_finish(st, n_all, classes, class_counts, label_name, cont)
+            # the sparse rows the fused pass wrote belong to this batch, not to the model: they are dropped with it
+            batch.__dict__.setdefault("_dev_cache", {})[("fit_rows", model.uid)] = (st.get("rows"), st.get("local_nnz"))
+        model._fit_key = batch_key(batch)
+        return model
+
+    # -- row chunks (streaming.py) ------------------------------------------------------------------------------------
+    # Pre-pass: TextStats of every column folded over the chunks in row order (the reference's reduce over partitions
+    # taken as one left fold, like _merge_text_stats does for ranks).  A column is done once its map has passed
+    # maxCardinality -- free text does so within its first rows, so the pre-pass usually ends with the first chunk.
+    def stream_pre_begin(self):
+        ncols = len(self.inN)
+        self._prefix = {}
+        return {"maps": [[] for _ in range(ncols)], "acc": [dict() for _ in range(ncols)],
+                "frozen": [False] * ncols, "k": 0}
+
+    def stream_pre_update(self, st, chunk: ColumnarBatch) -> bool:
+        """-> True when no column needs anything from later chunks"""
+        names = [f.name for f in self.inN]
+        live = [c for c in range(len(names)) if not st["frozen"][c]]
+        if live and chunk.n > 0:
+            sub_names = [names[c] for c in live]
+            block = chunk.texts(sub_names)
+            dev = chunk.on_device("texts", sub_names, block)
+            values, _totals = self._text_stats(dev, chunk.n)
+            for t, c in enumerate(live):
+                vc, acc = values[t], st["acc"][c]
+                st["maps"][c].append(vc)
+                if vc is not None and len(set(acc) | set(vc)) <= self.maxCardinality:
+                    for k, v in vc.items():
+                        acc[k] = acc.get(k, 0) + v
+                else:
+                    st["frozen"][c] = True
+        else:
+            for c in live:
+                st["maps"][c].append({})
+        st["k"] += 1
+        return all(st["frozen"])
+
+    def stream_pre_finish(self, st, chunks) -> "SmartTextVectorizerModel":
+        """Global fold (ranks in order, chunks in order within a rank), decisions, model without statistics."""
+        if st["k"] == 0:
+            raise ValueError("requirement failed: Input dataset cannot be empty")
+        names = [f.name for f in self.inN]
+        ncols = len(names)
+        rank, size = D.world()
+        local = [None if st["frozen"][c] else st["acc"][c] for c in range(ncols)]
+        gathered = D.all_gather_object(local)
+        merged, frozen_by = [], {}
+        for c in range(ncols):
+            acc: Dict[str, int] = {}
+            for r in range(size):
+                vc = gathered[r][c]
+                if vc is not None and len(set(acc) | set(vc)) <= self.maxCardinality:
+                    for k, v in vc.items():
+                        acc[k] = acc.get(k, 0) + v
+                else:
+                    frozen_by[c] = r
+                    break
+            merged.append(acc)
+        mine = [c for c, r in frozen_by.items() if r == rank]
+        res: Dict[int, Dict[str, int]] = {}
+        need: Dict[int, List[int]] = {}
+        for c in mine:                       # continue the fold over this rank's chunks from the ranks before
+            acc = dict(merged[c])
+            at = None
+            for k, vc in enumerate(st["maps"][c]):
+                if vc is not None and len(set(acc) | set(vc)) <= self.maxCardinality:
+                    for kk, v in vc.items():
+                        acc[kk] = acc.get(kk, 0) + v
+                else:
+                    at = k
+                    break
+            res[c] = acc
+            if at is not None:
+                need.setdefault(at, []).append(c)
+        if need:
+            last = max(need)
+            for k, chunk in enumerate(chunks):
+                if k in need:
+                    cols = need[k]
+                    sub_names = [names[c] for c in cols]
+                    block = chunk.texts(sub_names)
+                    dev = chunk.on_device("texts", sub_names, block)
+                    self._prefix = {}
+                    self._fetch_prefix(dev, list(range(len(cols))), chunk.n)
+                    for t, c in enumerate(cols):
+                        res[c] = self._frozen_counts(dev, t, chunk.n, seed=res[c])
+                    chunk.__dict__.pop("_dev_cache", None)
+                if k >= last:
+                    break
+        for per_rank in D.all_gather_object(res):
+            for c, vc in per_rank.items():
+                merged[c] = vc
+        methods, tops = [], []
+        for c in range(ncols):
+            m, top = self._decide(merged[c], 0, None, c, 0)
+            methods.append(m)
+            tops.append(top)
+        model = SmartTextVectorizerModel(self, methods, tops)
+        self._metadata = model._metadata = model._build_metadata()
         return model
 
     def _text_stats(self, dev: TextBlock, n: int):
@@ -398,8 +514,9 @@ class SmartTextVectorizerModel(OpModel):
         self.pivot_idx = [j for j, m in enumerate(self.vectorizationMethods) if m == PIVOT]
         hash_idx = [j for j, m in enumerate(self.vectorizationMethods) if m == HASH]
         ignore_idx = [j for j, m in enumerate(self.vectorizationMethods) if m == IGNORE]
+        self.shouldTrackLen = bool(getattr(p, "trackTextLen", False))
         self.layout = _HashLayout(names, hash_idx, ignore_idx, p.numFeatures, len(names), p.hashSpaceStrategy,
-                                  p.prependFeatureName, p.trackNulls)
+                                  p.prependFeatureName, p.trackNulls, self.shouldTrackLen)
         self.pivot_widths = [len(self.topValues[j]) + (2 if self.shouldTrackNulls else 1) for j in self.pivot_idx]
         self.pivot_width = sum(self.pivot_widths)
 
@@ -431,15 +548,16 @@ class SmartTextVectorizerModel(OpModel):
         return OpVectorMetadata(self.parent.getOutputFeatureName(), history=self.parent.history(), runs=runs)
 
     # -- device tables -------------------------------------------------------------------------------------------------
-    def _pivot_tables(self, dev: TextBlock, n: int):
-        """Small hash tables holding just the top values of every pivoted column, and the dictionary codes of all
-        rows against them (code -2 = a value outside the vocabulary -> OTHER)."""
-        k = len(self.pivot_idx)
+    def _pivot_table_build(self, ncols: int):
+        """Small hash tables holding just the top values of every pivoted column (built once per model and device)."""
+        key = (torch.cuda.current_device(), ncols)
+        hit = self.__dict__.get("_pt_cache")
+        if hit is not None and hit[0] == key:
+            return hit[1]
         slots = 64
         while slots < 4 * (max((len(self.topValues[j]) for j in self.pivot_idx), default=0) + 2):
             slots <<= 1
         head, per = C.c_size_t(), C.c_size_t()
-        ncols = len(dev.names)
         L.call("tmog_text_stats_layout", ncols, slots, 1, C.byref(head), C.byref(per))
         host = np.zeros(head.value + per.value * ncols, dtype=np.uint8)
         # struct TextStatsTable {hash*, first_row*, counts*, ndistinct*, len_sum*, nonnull*} per column
@@ -466,16 +584,26 @@ class SmartTextVectorizerModel(OpModel):
             slot_of.append(mapping)
         host[:ptrs.nbytes] = ptrs.view(np.uint8).reshape(-1)
         tables.copy_(torch.from_numpy(host))
+        sel = torch.tensor(self.pivot_idx or [0], dtype=torch.int32, device="cuda")
+        built = (tables, slots, slot_of, sel)
+        self.__dict__["_pt_cache"] = (key, built)
+        return built
+
+    def _pivot_tables(self, dev: TextBlock, n: int, flags: Optional[torch.Tensor] = None):
+        """The dictionary codes of all rows against the top-value tables (code -2 = a value outside the vocabulary ->
+        OTHER).  With `flags` given the non-ASCII check is left to the caller (row chunks: checked once at the end)."""
+        k = len(self.pivot_idx)
+        tables, slots, slot_of, sel = self._pivot_table_build(len(dev.names))
         ld = (n + 3) // 4 * 4
         codes = torch.empty((max(k, 1), ld), dtype=torch.int32, device="cuda")
-        sel = torch.tensor(self.pivot_idx or [0], dtype=torch.int32, device="cuda")
         desc = _col_desc(dev)
-        flags = torch.zeros(4, dtype=torch.int32, device="cuda")
+        own = flags is None
+        if own:
+            flags = torch.zeros(4, dtype=torch.int32, device="cuda")
         L.call("tmog_text_codes_dev", desc.data_ptr(), sel.data_ptr(), k, n, int(self.shouldCleanText), slots,
                tables.data_ptr(), codes.data_ptr(), ld, flags.data_ptr(), R.stream())
-        if k and self.shouldCleanText and int(flags[0].item()):
-            raise ValueError("non-ASCII text met with cleanText = true: Java's Unicode case mapping is not restated on "
-                             "this path")
+        if own and k and self.shouldCleanText and int(flags[0].item()):
+            raise ValueError(NON_ASCII_CLEAN)
         return codes, ld, slots, slot_of
 
     def _pivot_pos_tables(self, slots: int, slot_of, newpos: np.ndarray):
@@ -501,48 +629,150 @@ class SmartTextVectorizerModel(OpModel):
         lay = self.layout
         hp = self.hashingParams
         k = len(lay.hash_idx)
-        prefix = np.zeros((max(k, 1), 16), dtype=np.uint8)
-        plen = np.zeros(max(k, 1), dtype=np.int32)
-        for t in range(k):
-            s = f"{murmur3_index(lay.prefix_names[t], lay.num_features)}_".encode("ascii")
-            prefix[t, :len(s)] = np.frombuffer(s, dtype=np.uint8)
-            plen[t] = len(s)
-        sub = dev.rows(lay.hash_idx)
+        key = torch.cuda.current_device()
+        hit = self.__dict__.get("_ha_cache")
+        if hit is None or hit[0] != key:
+            prefix = np.zeros((max(k, 1), 16), dtype=np.uint8)
+            plen = np.zeros(max(k, 1), dtype=np.int32)
+            for t in range(k):
+                s = f"{murmur3_index(lay.prefix_names[t], lay.num_features)}_".encode("ascii")
+                prefix[t, :len(s)] = np.frombuffer(s, dtype=np.uint8)
+                plen[t] = len(s)
+            hit = self.__dict__["_ha_cache"] = (key, torch.from_numpy(prefix).cuda(), torch.from_numpy(plen).cuda())
+        sub = dev.rows(lay.hash_idx)      # (ignored columns would ride behind the hashed ones)
         params = np.array([lay.num_features, int(lay.shared), int(hp["binaryFreq"]), hp["minTokenLength"],
                            int(self.shouldTrackNulls), int(hp["prependFeatureName"]), lay.hash_width, 0],
                           dtype=np.int32)
-        return sub, torch.from_numpy(prefix).cuda(), torch.from_numpy(plen).cuda(), params
+        return sub, hit[1], hit[2], params
 
     # -- statistics sidecar --------------------------------------------------------------------------------------------
     def _sidecar(self, dev: TextBlock, n: int, n_all: int, classes, class_counts, ids, label_name: str,
                  cont=None) -> VectorStats:
         """n = local rows, n_all = rows of all ranks; the count tables and bucket sums are all-reduced.
         cont = (label moments, shift, label on the device) for a continuous label (then classes is None)."""
+        st = self._side_begin(classes, cont is not None)
+        self._side_scan(st, dev, n, ids, cont)
+        return self._side_finish(st, n_all, classes, class_counts, label_name, cont)
+
+    def _side_begin(self, classes, continuous: bool) -> dict:
+        """Accumulators of the statistics scans (one batch, or the row chunks of a dataset one after the other)."""
         ncls = len(classes) if classes is not None else 1
-        ids_ptr = ids.data_ptr() if classes is not None else None
-        parts = []
+        st: dict = {"ncls": ncls, "flags": torch.zeros(4, dtype=torch.int32, device="cuda"),
+                    "pflags": torch.zeros(4, dtype=torch.int32, device="cuda"), "chunk_nnz": [], "scans": 0}
         if self.pivot_idx:
-            codes, ld, slots, slot_of = self._pivot_tables(dev, n)
-            # count per slot code: remap -2 (unknown value) to slot index `slots` so that it lands in OTHER
-            codes = torch.where(codes == -2, torch.full_like(codes, slots), codes)
             k = len(self.pivot_idx)
+            _tables, slots, _slot_of, _sel = self._pivot_table_build(len(self.inN))
             nids = slots + 2
             desc = np.zeros((k, 4), dtype=np.int64)
             for t in range(k):
                 desc[t] = [nids, 0, t * nids * ncls, slots + 1]
-            d_desc = torch.from_numpy(desc).cuda()
-            d_counts = torch.zeros(k * nids * ncls, dtype=torch.int32, device="cuda")
-            d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
-            L.call("tmog_pivot_count_dev", codes.data_ptr(), ld, n, k, ids_ptr, ncls, d_desc.data_ptr(), None,
-                   nids, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
-            cnt = D.allreduce_sum(d_counts.cpu().numpy().astype(np.int64) & 0xFFFFFFFF).reshape(k, nids, ncls)
+            st.update(p_desc=torch.from_numpy(desc).cuda(), p_nids=nids,
+                      p_acc=torch.zeros(k * nids * ncls, dtype=torch.int64, device="cuda"),
+                      p_bad=torch.zeros(1, dtype=torch.int32, device="cuda"),
+                      p_ws=torch.zeros(k * nids, dtype=torch.float64, device="cuda") if continuous else None,
+                      p_woff=torch.arange(0, k * nids, nids, dtype=torch.int64, device="cuda"))
+        lay = self.layout
+        if lay.text_idx:
+            w = lay.kernel_width
+            st.update(w=w, class_sum=torch.zeros(w * ncls, dtype=torch.int64, device="cuda"),
+                      dup=torch.zeros(w, dtype=torch.int64, device="cuda"),
+                      extra=torch.zeros(w, dtype=torch.int64, device="cuda"),
+                      aux=torch.zeros((w, 3), dtype=torch.int64, device="cuda"),
+                      wsum=torch.zeros(w, dtype=torch.float64, device="cuda") if continuous else None)
+        return st
+
+    def _side_scan(self, st: dict, dev: TextBlock, n: int, ids, cont, fused_rows: bool = False) -> None:
+        """One batch / row chunk into the accumulators.  fused_rows: the same tokenise + hash pass also writes the sparse
+        rows of the batch (st["rows"]; a workflow transforms its training rows right after the fit)."""
+        ncls = st["ncls"]
+        ids_ptr = ids.data_ptr() if ids is not None else None
+        if self.pivot_idx:
+            codes, ld, slots, _slot_of = self._pivot_tables(dev, n, st["pflags"])
+            # count per slot code: remap -2 (unknown value) to slot index `slots` so that it lands in OTHER
+            codes = torch.where(codes == -2, torch.full_like(codes, slots), codes)
+            k = len(self.pivot_idx)
+            d_counts = torch.zeros(k * st["p_nids"] * ncls, dtype=torch.int32, device="cuda")
+            L.call("tmog_pivot_count_dev", codes.data_ptr(), ld, n, k, ids_ptr, ncls, st["p_desc"].data_ptr(), None,
+                   st["p_nids"], d_counts.data_ptr(), st["p_bad"].data_ptr(), R.stream())
+            st["p_acc"] += d_counts.to(torch.int64) & 0xFFFFFFFF
+            if cont is not None:
+                L.call("tmog_pivot_label_sum_dev", codes.data_ptr(), ld, n, k, st["p_desc"].data_ptr(), None,
+                       st["p_woff"].data_ptr(), cont[2].data_ptr(), cont[1], st["p_ws"].data_ptr(), R.stream())
+        lay = self.layout
+        if lay.text_idx:
+            sub, d_prefix, d_plen, params = self._hash_args(dev)
+            params[7] = ncls
+            params[6] = lay.null_base
+            w = st["w"]
+            class_sum = torch.zeros(w * ncls, dtype=torch.int32, device="cuda")
+            dup = torch.zeros(w, dtype=torch.int32, device="cuda")
+            aux = torch.zeros(3 * w, dtype=torch.int32, device="cuda")
+            extra = st["extra"]                       # 64-bit sums: accumulated in place
+            flags = st["flags"]
+            scratch = _hash_scratch(n, len(sub.names), lay, fused_rows)
+            desc = _col_desc(sub)
+            wsum = st["wsum"]
+            k = len(sub.names)
+            label_ptr = cont[2].data_ptr() if cont is not None else None
+            shift = cont[1] if cont is not None else 0.0
+            if not fused_rows:
+                L.call("tmog_text_hash_stats_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(), d_plen.data_ptr(),
+                       params.ctypes.data, ids_ptr, class_sum.data_ptr(), dup.data_ptr(), extra.data_ptr(),
+                       aux.data_ptr(), label_ptr, shift, R.ptr(wsum), flags.data_ptr(), scratch.data_ptr(),
+                       scratch.numel(), R.stream())
+            else:
+                # One pass over the text gives the statistics AND the sparse rows of this batch: the output is sized
+                # from a sample of the first rows; if the estimate turns out too small the rows are dropped and the
+                # transform tokenises again.
+                ident = torch.arange(w, dtype=torch.int32, device="cuda")
+                row_start = torch.empty(max(n, 1), dtype=torch.int64, device="cuda")
+                row_nnz = torch.empty(max(n, 1), dtype=torch.int32, device="cuda")
+                cursor = torch.zeros(1, dtype=torch.int64, device="cuda")
+                m = min(n, 16384)
+                params1 = params.copy()
+                params1[7] = 1
+                L.call("tmog_text_hash_transform_dev", desc.data_ptr(), k, m, d_prefix.data_ptr(), d_plen.data_ptr(),
+                       params1.ctypes.data, ident.data_ptr(), row_start.data_ptr(), row_nnz.data_ptr(), None, None,
+                       cursor.data_ptr(), 0, flags.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
+                capacity = int(int(cursor.item()) / max(m, 1) * n * 1.1) + 65536
+                cursor.zero_()
+                flags.zero_()
+                idx = torch.empty(capacity, dtype=torch.int32, device="cuda")
+                val = torch.empty(capacity, dtype=torch.int32, device="cuda")
+                L.call("tmog_text_hash_fit_transform_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(),
+                       d_plen.data_ptr(), params.ctypes.data, ids_ptr, class_sum.data_ptr(), dup.data_ptr(),
+                       extra.data_ptr(), aux.data_ptr(), label_ptr, shift, R.ptr(wsum), ident.data_ptr(),
+                       row_start.data_ptr(), row_nnz.data_ptr(), idx.data_ptr(), val.data_ptr(), cursor.data_ptr(),
+                       capacity, flags.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
+                too_small = int(flags[3].item()) != 0
+                flags[3] = 0
+                st["rows"] = None if too_small else SparseRowsPart(row_start[:n], row_nnz[:n], idx, val, w)
+            # unsigned 32-bit words of this scan widened into the 64-bit accumulators
+            u32 = lambda t: t.to(torch.int64) & 0xFFFFFFFF   # noqa: E731
+            cs64, dp64, ax64 = u32(class_sum), u32(dup), u32(aux).view(w, 3)
+            st["class_sum"] += cs64
+            st["dup"] += dp64
+            acc = st["aux"]
+            torch.maximum(acc[:, 0], ax64[:, 0], out=acc[:, 0])
+            torch.maximum(acc[:, 1], ax64[:, 1], out=acc[:, 1])
+            acc[:, 2] += ax64[:, 2]
+            # entries this scan would write as sparse rows (all columns): sizes the transform of the same chunk
+            st["chunk_nnz"].append(cs64.sum() - dp64.sum())
+        st["scans"] += 1
+
+    def _side_finish(self, st: dict, n_all: int, classes, class_counts, label_name: str, cont) -> VectorStats:
+        ncls = st["ncls"]
+        parts = []
+        if self.pivot_idx:
+            if self.shouldCleanText and int(st["pflags"][0].item()):
+                raise ValueError(NON_ASCII_CLEAN)
+            k = len(self.pivot_idx)
+            _tables, slots, slot_of, _sel = self._pivot_table_build(len(self.inN))
+            nids = st["p_nids"]
+            cnt = D.allreduce_sum(st["p_acc"].cpu().numpy()).reshape(k, nids, ncls)
             ws = None
             if cont is not None:
-                d_ws = torch.zeros(k * nids, dtype=torch.float64, device="cuda")
-                d_woff = torch.arange(0, k * nids, nids, dtype=torch.int64, device="cuda")
-                L.call("tmog_pivot_label_sum_dev", codes.data_ptr(), ld, n, k, d_desc.data_ptr(), None,
-                       d_woff.data_ptr(), cont[2].data_ptr(), cont[1], d_ws.data_ptr(), R.stream())
-                ws = D.allreduce_sum(d_ws.cpu().numpy()).reshape(k, nids)
+                ws = D.allreduce_sum(st["p_ws"].cpu().numpy()).reshape(k, nids)
             rows, wrows = [], []
             for t, j in enumerate(self.pivot_idx):
                 top = self.topValues[j]
@@ -570,62 +800,18 @@ class SmartTextVectorizerModel(OpModel):
                                                         label_name))
         lay = self.layout
         if lay.text_idx:
-            if lay.ignore_idx:
-                raise NotImplementedError("ignored text columns are not on the GPU path")
-            sub, d_prefix, d_plen, params = self._hash_args(dev)
-            params[7] = ncls
-            w = lay.hash_width + len(lay.hash_idx)
-            class_sum = torch.zeros(w * ncls, dtype=torch.int32, device="cuda")
-            dup = torch.zeros(w, dtype=torch.int32, device="cuda")
-            extra = torch.zeros(w, dtype=torch.int64, device="cuda")
-            scratch = _hash_scratch(n)
-            aux = torch.zeros(3 * w, dtype=torch.int32, device="cuda")
-            flags = torch.zeros(4, dtype=torch.int32, device="cuda")
-            desc = _col_desc(sub)
-            wsum = torch.zeros(w, dtype=torch.float64, device="cuda") if cont is not None else None
-            # One pass over the text gives the statistics AND the sparse rows of this batch (the workflow transforms
-            # its training rows right after the fit): the output is sized from a sample of the first rows; if the
-            # estimate turns out too small the rows are dropped and the transform tokenises again.
-            k = len(lay.hash_idx)
-            ident = torch.arange(w, dtype=torch.int32, device="cuda")
-            row_start = torch.empty(max(n, 1), dtype=torch.int64, device="cuda")
-            row_nnz = torch.empty(max(n, 1), dtype=torch.int32, device="cuda")
-            cursor = torch.zeros(1, dtype=torch.int64, device="cuda")
-            m = min(n, 16384)
-            params1 = params.copy()
-            params1[7] = 1
-            L.call("tmog_text_hash_transform_dev", desc.data_ptr(), k, m, d_prefix.data_ptr(), d_plen.data_ptr(),
-                   params1.ctypes.data, ident.data_ptr(), row_start.data_ptr(), row_nnz.data_ptr(), None, None,
-                   cursor.data_ptr(), 0, flags.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
-            capacity = int(int(cursor.item()) / max(m, 1) * n * 1.1) + 65536
-            cursor.zero_()
-            flags.zero_()
-            idx = torch.empty(capacity, dtype=torch.int32, device="cuda")
-            val = torch.empty(capacity, dtype=torch.int32, device="cuda")
-            L.call("tmog_text_hash_fit_transform_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(), d_plen.data_ptr(),
-                   params.ctypes.data, ids_ptr, class_sum.data_ptr(), dup.data_ptr(), extra.data_ptr(), aux.data_ptr(),
-                   cont[2].data_ptr() if cont is not None else None, cont[1] if cont is not None else 0.0,
-                   wsum.data_ptr() if cont is not None else None, ident.data_ptr(), row_start.data_ptr(),
-                   row_nnz.data_ptr(), idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), capacity, flags.data_ptr(),
-                   scratch.data_ptr(), scratch.numel(), R.stream())
-            too_small = int(flags[3].item()) != 0
-            flags[3] = 0
-            _check_hash_flags(flags)
-            self._fit_rows = None if too_small else SparseRowsPart(row_start[:n], row_nnz[:n], idx, val, w)
-            # the four bucket arrays widened on the device and brought back in one copy (unsigned 32-bit words read
-            # as int64, the 64-bit extra sums as they are): a 262 144-wide block costs milliseconds of host casts
-            u32 = lambda t: t.view(torch.int32).to(torch.int64) & 0xFFFFFFFF   # noqa: E731
-            packed = torch.cat([u32(class_sum).reshape(-1), u32(dup).reshape(-1), extra.view(torch.int64).reshape(-1),
-                                u32(aux).reshape(-1)]).cpu().numpy()
+            _check_hash_flags(st["flags"])
+            w = st["w"]
+            # the bucket arrays of all scans brought back in one copy
+            packed = torch.cat([st["class_sum"].reshape(-1), st["dup"].reshape(-1), st["extra"].reshape(-1),
+                                st["aux"].reshape(-1)]).cpu().numpy()
             k = w * ncls
             cs = packed[:k].reshape(w, ncls).astype(np.float64)
             # rows holding an index = sum of its term frequencies - (tf - 1) of the rows with tf > 1
             nz = cs.sum(axis=1) - packed[k:k + w].astype(np.float64)
             ex = packed[k + w:k + 2 * w].astype(np.float64)
             ax = packed[k + 2 * w:].reshape(w, 3)
-            if not self.shouldTrackNulls:
-                cs, nz, ex, ax = cs[:lay.hash_width], nz[:lay.hash_width], ex[:lay.hash_width], ax[:lay.hash_width]
-            self._hash_nnz = nz                      # of the local rows: sizes the sparse output of the same batch
+            st["local_nnz"] = nz                     # of the local rows: sizes the sparse output of the same batch
             if D.world()[1] > 1:
                 # two exchanges in all: everything that adds (counts below 2^53, exact in f64), everything that maxes
                 sums = D.allreduce_sum(np.concatenate([cs.reshape(-1), nz, ex, ax[:, 2].astype(np.float64)]))
@@ -633,16 +819,49 @@ class SmartTextVectorizerModel(OpModel):
                 k, m = cs.size, len(nz)
                 cs, nz, ex = sums[:k].reshape(cs.shape), sums[k:k + m], sums[k + m:k + 2 * m]
                 ax = np.stack([maxs[:m], maxs[m:], sums[k + 2 * m:].astype(np.int64)], axis=1)
+            stats = lay.stats_columns(cs, nz, ex, ax)
             if cont is None:
-                parts.append(_stats_from_bucket_sums(cs, nz, ex, ax, classes, class_counts, n_all, label_name,
-                                                     lay.hash_width))
+                parts.append(_stats_from_bucket_sums(*stats, classes, class_counts, n_all, label_name, lay))
             else:
-                wv = D.allreduce_sum(wsum.cpu().numpy()[:len(nz)])
+                cs, nz, ex, ax = stats
+                wv = lay.stats_columns_1d(D.allreduce_sum(st["wsum"].cpu().numpy()))
                 sv = cs[:, 0]
                 vmax = np.maximum(ax[:, 0], 1).astype(np.float64)
                 vmin = np.where(ax[:, 2] >= nz, ((~ax[:, 1]) & 0xFFFFFFFF), 1).astype(np.float64)
                 parts.append(stats_from_sums_continuous(sv, sv + ex, nz, vmax, vmin, wv, cont[0], cont[1], label_name))
         return VectorStats.concat(parts)
+
+    # -- row chunks (streaming.py): the statistics sidecar accumulated over the chunks
+    def stream_begin(self, label):
+        if label is None:
+            return {"label": None}
+        st = self._side_begin(label.classes, label.classes is None)
+        st["label"], st["n"] = label, 0
+        return st
+
+    def stream_update(self, st, chunk: ColumnarBatch) -> None:
+        lab = st["label"]
+        if lab is None:
+            return
+        names = [f.name for f in self.inN]
+        block = chunk.texts(names)
+        dev = chunk.on_device("texts", names, block)
+        ids = lab.class_ids(chunk) if lab.classes is not None else None
+        cont = None if lab.classes is not None else lab.continuous() + (lab.device_label(chunk),)
+        self._side_scan(st, dev, chunk.n, ids, cont)
+        st.setdefault("tokens", []).append(chunk.token)
+        st["n"] += chunk.n
+
+    def stream_finish(self, st):
+        lab = st["label"]
+        if lab is None:
+            return self
+        cont = None if lab.classes is not None else lab.continuous() + (None,)
+        self._fit_stats = self._side_finish(st, lab.n, lab.classes, lab.class_counts, lab.name, cont)
+        if st["chunk_nnz"]:             # sparse entries of every chunk's rows, by the chunk's token: sizes its transform
+            nnz = torch.stack(st["chunk_nnz"]).cpu().numpy().astype(np.int64)
+            self._stream_nnz = dict(zip(st.get("tokens", []), nnz.tolist()))
+        return self
 
     # -- transform -----------------------------------------------------------------------------------------------------
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
@@ -651,50 +870,71 @@ class SmartTextVectorizerModel(OpModel):
         block = batch.texts(names)
         n = batch.n
         parts = []
-        same = self._fit_key == (block.offsets[0].data_ptr(), n)
+        same = self._fit_key is not None and self._fit_key == batch_key(batch)
         dev_of = batch.device_thunk("texts", names, block)
+        # what the fit pass left on this very batch (sparse rows of all columns, entries per vector index)
+        fitted = batch.__dict__.get("_dev_cache", {}).get(("fit_rows", self.uid)) if same else None
+        stream = batch.__dict__.get("_stream")        # row chunk of a streamed dataset: (chunk index, shared flags)
         if self.pivot_idx:
-            parts.append(LazyPart(self.pivot_width, lambda keep: self._materialize_pivot(dev_of(), n, keep)))
+            parts.append(LazyPart(self.pivot_width, lambda keep: self._materialize_pivot(dev_of(), n, keep, stream)))
         if self.layout.text_idx:
-            parts.append(LazyPart(self.layout.width, lambda keep: self._materialize_hash(dev_of(), n, keep, same)))
+            parts.append(LazyPart(self.layout.width,
+                                  lambda keep: self._materialize_hash(dev_of(), n, keep, fitted, stream)))
         return VectorColumn(self.getOutput().name, n, self.getMetadata(), parts, self._fit_stats if same else None)
 
-    def _materialize_pivot(self, block: TextBlock, n: int, keep) -> OneHotPart:
+    def _plan(self, kind: str, keep, build):
+        """Device tables of a transform that depend on the kept columns only: built once per keep set."""
+        key = (kind, torch.cuda.current_device(), None if keep is None else np.asarray(keep).tobytes())
+        cache = self.__dict__.setdefault("_plans", {})
+        if key not in cache:
+            if len(cache) > 8:
+                cache.clear()
+            cache[key] = build()
+        return cache[key]
+
+    def _materialize_pivot(self, block: TextBlock, n: int, keep, stream=None) -> OneHotPart:
         dev = block if block.is_cuda else block.to("cuda")
         width = self.pivot_width
-        newpos = np.arange(width, dtype=np.int32)
-        out_width = width
-        if keep is not None:
-            newpos = np.full(width, -1, dtype=np.int32)
-            newpos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
-            out_width = len(keep)
-        codes, ld, slots, slot_of = self._pivot_tables(dev, n)
-        codes = torch.where(codes == -2, torch.full_like(codes, slots), codes)
-        pos, desc = self._pivot_pos_tables(slots, slot_of, newpos)
         k = len(self.pivot_idx)
+
+        def build():
+            newpos = np.arange(width, dtype=np.int32)
+            out_width = width
+            if keep is not None:
+                newpos = np.full(width, -1, dtype=np.int32)
+                newpos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
+                out_width = len(keep)
+            _tables, slots, slot_of, _sel = self._pivot_table_build(len(self.inN))
+            pos, desc = self._pivot_pos_tables(slots, slot_of, newpos)
+            return torch.from_numpy(desc).cuda(), torch.from_numpy(pos).cuda(), out_width
+
+        d_desc, d_pos, out_width = self._plan("pivot", keep, build)
+        codes, ld, slots, _slot_of = self._pivot_tables(dev, n, None if stream is None else stream["flags_clean"])
+        codes = torch.where(codes == -2, torch.full_like(codes, slots), codes)
         out = torch.empty((n, max(k, 1)), dtype=torch.int32, device="cuda")
-        d_desc, d_pos = torch.from_numpy(desc).cuda(), torch.from_numpy(pos).cuda()
         L.call("tmog_pivot_transform_dev", codes.data_ptr(), ld, n, k, d_desc.data_ptr(), d_pos.data_ptr(),
                out.data_ptr(), out.shape[1], 0, R.stream())
         return OneHotPart(out[:, :k], out_width)
 
-    def _materialize_hash(self, block: TextBlock, n: int, keep, same_batch: bool) -> SparseRowsPart:
+    def _materialize_hash(self, block: TextBlock, n: int, keep, fitted=None, stream=None) -> SparseRowsPart:
         dev = block if block.is_cuda else block.to("cuda")
         lay = self.layout
-        if lay.ignore_idx:
-            raise NotImplementedError("ignored text columns are not on the GPU path")
         width = lay.width
-        full = lay.hash_width + len(lay.hash_idx)
-        newpos = np.full(full, -1, dtype=np.int32)
-        if keep is None:
-            newpos[:width] = np.arange(width, dtype=np.int32)
-            out_width = width
-        else:
-            newpos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
-            out_width = len(keep)
-        d_newpos = torch.from_numpy(newpos).cuda()
-        rows = getattr(self, "_fit_rows", None)
-        if same_batch and rows is not None:
+        full = lay.kernel_width
+
+        def build():
+            newpos = np.full(full, -1, dtype=np.int32)
+            if keep is None:
+                newpos[:width] = np.arange(width, dtype=np.int32)
+                out_width = width
+            else:
+                newpos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
+                out_width = len(keep)
+            return newpos, torch.from_numpy(newpos).cuda(), out_width
+
+        newpos, d_newpos, out_width = self._plan("hash", keep, build)
+        rows, local_nnz = fitted if fitted is not None else (None, None)
+        if rows is not None:
             # the fit pass wrote the rows of this batch: keep the wanted columns of them
             if keep is None or (len(keep) == width and bool((np.asarray(keep) == np.arange(width)).all())):
                 return SparseRowsPart(rows.row_start, rows.row_nnz, rows.indices, rows.values, width)
@@ -712,34 +952,41 @@ class SmartTextVectorizerModel(OpModel):
             return SparseRowsPart(out_start[:n], out_nnz[:n], oi, ov, out_width)
         sub, d_prefix, d_plen, params = self._hash_args(dev)
         params[7] = 1
+        params[6] = lay.null_base
         desc = _col_desc(sub)
+        k = len(sub.names)
         row_start = torch.empty(n, dtype=torch.int64, device="cuda")
         row_nnz = torch.empty(n, dtype=torch.int32, device="cuda")
-        flags = torch.zeros(4, dtype=torch.int32, device="cuda")
+        own_flags = stream is None
+        flags = torch.zeros(4, dtype=torch.int32, device="cuda") if own_flags else stream["flags"]
         cursor = torch.zeros(1, dtype=torch.int64, device="cuda")
-        scratch = _hash_scratch(n)
-        nz = getattr(self, "_hash_nnz", None)
-        if same_batch and nz is not None:      # exact size known from the fit pass over the same rows
-            capacity = int(nz[newpos[:len(nz)] >= 0].sum())
+        scratch = _hash_scratch(n, k, lay, True)
+        chunk_nnz = getattr(self, "_stream_nnz", None)
+        if local_nnz is not None:              # exact size known from the fit pass over the same rows
+            capacity = int(local_nnz[newpos[:len(local_nnz)] >= 0].sum())
+        elif stream is not None and chunk_nnz is not None and stream.get("token") in chunk_nnz:
+            capacity = int(chunk_nnz[stream["token"]])     # entries of these very rows over all columns (fit pass)
         else:                                  # sizing pass
-            L.call("tmog_text_hash_transform_dev", desc.data_ptr(), len(lay.hash_idx), n, d_prefix.data_ptr(),
+            L.call("tmog_text_hash_transform_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(),
                    d_plen.data_ptr(), params.ctypes.data, d_newpos.data_ptr(), row_start.data_ptr(),
                    row_nnz.data_ptr(), None, None, cursor.data_ptr(), 0, flags.data_ptr(), scratch.data_ptr(),
                    scratch.numel(), R.stream())
             capacity = int(cursor.item())
             cursor.zero_()
-            flags.zero_()
+            flags[3] = 0
         idx = torch.empty(max(capacity, 1), dtype=torch.int32, device="cuda")
         val = torch.empty(max(capacity, 1), dtype=torch.int32, device="cuda")
-        L.call("tmog_text_hash_transform_dev", desc.data_ptr(), len(lay.hash_idx), n, d_prefix.data_ptr(),
+        L.call("tmog_text_hash_transform_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(),
                d_plen.data_ptr(), params.ctypes.data, d_newpos.data_ptr(), row_start.data_ptr(), row_nnz.data_ptr(),
                idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), capacity, flags.data_ptr(), scratch.data_ptr(),
                scratch.numel(), R.stream())
-        _check_hash_flags(flags)
+        if own_flags:
+            _check_hash_flags(flags)
         return SparseRowsPart(row_start, row_nnz, idx, val, out_width)
 
 
-def _hash_scratch(n: int) -> torch.Tensor:
+def _hash_scratch(n: int, ncols: int = 0, lay: Optional[_HashLayout] = None, sparse_out: bool = True) -> torch.Tensor:
+    """Device scratch of the tokenise + hash entry points for n rows of ncols text columns."""
     import ctypes
     need = ctypes.c_size_t(0)
     L.call("tmog_text_hash_scratch_bytes", n, ctypes.byref(need))
@@ -759,14 +1006,14 @@ def _check_hash_flags(flags: torch.Tensor) -> None:
 
 
 def _stats_from_bucket_sums(class_sum: np.ndarray, nnz: np.ndarray, sq_extra: np.ndarray, aux: np.ndarray, classes,
-                            class_counts, n: int, label_name: str, hash_width: int) -> VectorStats:
-    """Column statistics of term-frequency columns from per-class sums: sum v = sum_c S_c,
-    sum v^2 = sum v + extra, cov(v, y) = sum_c y_c S_c - mean_y sum v."""
+                            class_counts, n: int, label_name: str, lay: _HashLayout) -> VectorStats:
+    """Column statistics of term-frequency (and text-length) columns from per-class sums:
+    sum v = sum_c S_c, sum v^2 = sum v + extra, cov(v, y) = sum_c y_c S_c - mean_y sum v."""
     cc = class_counts.astype(np.float64)
     mean_y = float((classes * cc).sum() / n)
     var_y = float((cc * (classes - mean_y) ** 2).sum() / (n - 1)) if n > 1 else 0.0
     lab = np.array([n, mean_y, var_y, classes.min(), classes.max()])
-    # term frequencies are >= 1 where present; aux = [max tf, ~min tf among tf > 1, rows with tf > 1]
+    # values are >= 1 where present; aux = [max v, ~min v among v > 1, rows with v > 1]
     w = class_sum.shape[0]
     cs64 = np.ascontiguousarray(class_sum, dtype=np.float64)
     nz64, ex64 = np.ascontiguousarray(nnz, dtype=np.float64), np.ascontiguousarray(sq_extra, dtype=np.float64)
@@ -777,5 +1024,5 @@ def _stats_from_bucket_sums(class_sum: np.ndarray, nnz: np.ndarray, sq_extra: np
            cl64.ctypes.data, float(n), mean_y, mean.ctypes.data, var.ctypes.data, mn.ctypes.data, mx.ctypes.data,
            cov.ctypes.data)
     cs = np.full((len(classes), w), np.nan)
-    cs[:, hash_width:] = class_sum[hash_width:].T          # null indicators are categorical columns
+    cs[:, lay.null_base:] = class_sum[lay.null_base:].T     # only the null indicators are categorical columns
     return VectorStats(LabelInfo(label_name, n, lab, classes, class_counts), mean, var, mn, mx, cov, cs)

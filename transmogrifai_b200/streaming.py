@@ -1,0 +1,311 @@
+"""Fit + transform of a dataset that arrives in row chunks (a dataset larger than one GPU's HBM, or the exported
+partitions of a Spark DataFrame one after the other).
+
+Reference: OpWorkflow.train()'s fitAndTransformDAG (core/src/main/scala/com/salesforce/op/utils/stages/
+FitStagesUtil.scala:212-290): every estimator of a layer is fitted by a fold over the partitions
+(OpOneHotVectorizer.scala:95-97 RDD.fold of per-row maps, SmartTextVectorizer.scala:88-91 reduce(_ + _) of TextStats,
+SequenceAggregators.scala:76-88 for the means, SanityChecker.scala:397-412 treeAggregate / reduceByKey), then the
+layer's transformers map over the partitions again (:96-119).  Here the partitions are ColumnarBatch chunks:
+
+  pass 0   label only: distinct label values, rows per value, label moments (what SanityChecker keys everything on);
+           SmartTextVectorizer's TextStats fold rides along until every text column has passed the cardinality cap
+  pass 1   every vectorizer's fused fit + statistics scan, chunk by chunk, into accumulators that merge by addition
+           (partial sums under shared shifts, int64 count tables, per-bucket sums) -- the same merges dist.py uses
+           for ranks; with several ranks each rank streams its own chunks and the accumulators are all-reduced once
+  decide   VectorsCombiner / SanityChecker / MinVarianceFilter are fitted from the merged statistics sidecar alone
+  pass 2   the fitted models transform chunk by chunk; only the columns SanityChecker kept are written, and `sink`
+           receives every chunk's output (device parts) as soon as it is queued
+
+No vector of the whole dataset is ever held: a chunk's raw blocks are dropped from the device once the chunk is done.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Callable, Dict, Iterable, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from . import dist as D
+from . import features as F
+from . import runtime as R
+from .columnar import ColumnarBatch, VectorColumn, WidthPart, round_up
+from .dsl import stages_of
+from .stages.base import OpEstimator, OpPipelineStage
+from .stages.numeric import MAX_LABEL_CLASSES
+
+
+class StreamLabel:
+    """The response over all chunks and ranks: sorted distinct values and rows per value (None when there are more
+    than MAX_LABEL_CLASSES: a continuous label), count / mean / variance / min / max, and the shift the label-sum
+    kernels subtract.  Hands every chunk its label on the device and its class ids against the global class list."""
+
+    def __init__(self, name: str):
+        self.name = name
+        self.n = 0
+        self.classes: Optional[np.ndarray] = None
+        self.class_counts: Optional[np.ndarray] = None
+        self.stats = np.zeros(5)
+        self.shift = 0.0
+        self._d_classes = None
+        self._d_ncls = None
+        # pass 0 accumulators
+        self._found: List[torch.Tensor] = []
+        self._parts: List[torch.Tensor] = []
+        self._d_shift = None
+
+    # -- pass 0 ------------------------------------------------------------------------------------------------------
+    def device_label(self, chunk: ColumnarBatch) -> torch.Tensor:
+        cache = chunk.__dict__.setdefault("_label_dev", {})
+        y = cache.get(self.name)
+        if y is None:
+            y = chunk.label(self.name)
+            y = y if y.is_cuda else y.to("cuda", non_blocking=True)
+            cache[self.name] = y
+        return y
+
+    def scan(self, chunk: ColumnarBatch) -> None:
+        n = chunk.n
+        if n == 0:
+            return
+        y = self.device_label(chunk)
+        nb = C.c_size_t()
+        L.call("tmog_label_classes_scratch_bytes", C.byref(nb))
+        scratch = R.scratch("label", nb.value)
+        found = torch.zeros(1 + 256 + 256, dtype=torch.float64, device="cuda")    # {n classes, classes, rows per class}
+        ncls = torch.zeros(1, dtype=torch.int32, device="cuda")
+        L.call("tmog_label_classes_dev", y.data_ptr(), n, MAX_LABEL_CLASSES, found[1:].data_ptr(), ncls.data_ptr(), None,
+               found[257:].data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
+        found[0] = ncls[0]
+        self._found.append(found)
+        # moments: the fit scan with no feature columns, under the first chunk's pilot shift
+        ld = round_up(max(n, 1), 2)
+        if self._d_shift is None:
+            self._d_shift = torch.zeros(1, dtype=torch.float64, device="cuda")
+            L.call("tmog_real_pilot_shift_dev", None, ld, None, 0, y.data_ptr(), n, 0, self._d_shift.data_ptr(),
+                   R.stream())
+            if D.world()[1] > 1:
+                torch.distributed.broadcast(self._d_shift, src=0)
+        nb2 = C.c_size_t()
+        L.call("tmog_real_fit_scratch_bytes", 0, C.byref(nb2))
+        sc2 = R.scratch("real_fit", nb2.value)
+        part = torch.zeros(L.REAL_NSTAT, dtype=torch.float64, device="cuda")
+        L.call("tmog_real_fit_partials_dev", None, ld, None, 0, y.data_ptr(), n, 0, self._d_shift.data_ptr(),
+               sc2.data_ptr(), sc2.numel(), part.data_ptr(), R.stream())
+        self._parts.append(part)
+
+    def finish(self) -> None:
+        if not self._found:
+            raise ValueError("requirement failed: Sample size cannot be zero")
+        host = torch.stack(self._found).cpu().numpy()
+        lists, continuous = [], False
+        for h in host:
+            k = int(h[0])
+            if k < 0:
+                continuous = True
+                break
+            lists.append((h[1:1 + k].copy(), h[257:257 + k].view(np.int64).copy()))
+        local = None
+        if not continuous:
+            allv = np.concatenate([v for v, _ in lists])
+            bits = np.unique(allv.view(np.int64))                 # distinct by bit pattern (java.lang.Double.equals)
+            key = np.where(bits < 0, ~bits.view(np.uint64), bits.view(np.uint64) | np.uint64(1 << 63))
+            local = bits.view(np.float64)[np.argsort(key, kind="stable")]
+            if len(local) > MAX_LABEL_CLASSES:
+                local = None
+        union = D.union_classes(local, MAX_LABEL_CLASSES) if D.world()[1] > 1 else local
+        if union is not None and len(union) > 0:
+            counts = np.zeros(len(union), dtype=np.int64)
+            index = {int(b): i for i, b in enumerate(union.view(np.int64))}
+            for v, c in lists:
+                for b, cnt in zip(v.view(np.int64), c):
+                    counts[index[int(b)]] += int(cnt)
+            self.classes, self.class_counts = union, D.allreduce_sum(counts)
+            self._d_classes = torch.zeros(256, dtype=torch.float64, device="cuda")
+            self._d_classes[:len(union)] = torch.from_numpy(union).cuda()
+            self._d_ncls = torch.tensor([len(union)], dtype=torch.int32, device="cuda")
+        parts = torch.stack(self._parts).cpu().numpy()
+        merged = np.ascontiguousarray(parts[0])
+        for k in range(1, parts.shape[0]):
+            other = np.ascontiguousarray(parts[k])
+            L.call("tmog_real_partials_merge", merged.ctypes.data, other.ctypes.data, 0)
+        merged = D.allreduce_real_partials(merged)
+        shift = self._d_shift.cpu().numpy()
+        lab = np.zeros(5)
+        L.call("tmog_real_finish", merged.ctypes.data, shift.ctypes.data, 0, 1, 0.0, 0, None, None, None, None, None,
+               None, lab.ctypes.data, None)
+        self.stats, self.shift, self.n = lab, float(shift[0]), int(lab[0])
+        self._found, self._parts = [], []
+
+    # -- passes 1 / 2 ------------------------------------------------------------------------------------------------
+    def continuous(self):
+        """(label moments, shift) when the label is continuous, else None"""
+        return None if self.classes is not None else (self.stats, self.shift)
+
+    def class_ids(self, chunk: ColumnarBatch) -> torch.Tensor:
+        """One byte per row of the chunk: index of its label in the global class list (cached on the chunk)."""
+        cache = chunk.__dict__.setdefault("_label_cache", {})
+        hit = cache.get(self.name)
+        if hit is not None:
+            return hit[2]
+        y = self.device_label(chunk)
+        ids = torch.empty(max(chunk.n, 1), dtype=torch.uint8, device="cuda")
+        L.call("tmog_label_class_ids_dev", y.data_ptr(), chunk.n, self._d_classes.data_ptr(), self._d_ncls.data_ptr(),
+               MAX_LABEL_CLASSES, ids.data_ptr(), None, R.stream())
+        cache[self.name] = (self.classes, self.class_counts, ids)
+        return ids
+
+    def prime(self, chunk: ColumnarBatch) -> None:
+        """Make the stage code that asks a batch for its label classes / moments see the global ones."""
+        cache = chunk.__dict__.setdefault("_label_cache", {})
+        if self.classes is not None:
+            self.class_ids(chunk)
+        else:
+            cache[self.name] = (None, None, None)
+            cache[(self.name, "moments")] = (self.stats, self.shift)
+
+
+def _release(chunk: ColumnarBatch) -> None:
+    """Drop what a pass left on a chunk (device copies of host blocks, label, class ids)."""
+    for k in ("_dev_cache", "_label_dev", "_label_cache", "_dict_cache"):
+        chunk.__dict__.pop(k, None)
+
+
+def _is_raw_stage(st: OpPipelineStage) -> bool:
+    return all(f.type_name != F.OPVECTOR for f in st.inN)
+
+
+class StreamResult:
+    def __init__(self, fitted, label: Optional[StreamLabel], n_local: int, n_chunks: int, vectors: Dict[str, VectorColumn]):
+        self.fitted = fitted
+        self.label = label
+        self.rows, self.chunks = n_local, n_chunks
+        self.vectors = vectors              # the vectors of the whole dataset: metadata + statistics, no rows
+
+
+def fit_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, response: Optional[str] = None,
+               on_chunk: Optional[Callable[[int, int, ColumnarBatch], None]] = None) -> StreamResult:
+    """Passes 0 and 1 and the decisions: every stage of `result`'s DAG fitted over the chunks (`chunks` is iterated
+    several times and must yield the same chunks in the same order each time).  on_chunk(pass, index, chunk) is called
+    after a chunk has been queued (for callers that recycle staging buffers)."""
+    R.require_cuda()
+    layers = stages_of(result)
+    stages = [st for layer in layers for st in layer]
+    raw = [st for st in stages if _is_raw_stage(st)]
+    for st in raw:
+        if not (hasattr(st, "stream_begin") or hasattr(st, "stream_pre_begin")):
+            raise NotImplementedError(f"{type(st).__name__} cannot be fitted over row chunks yet")
+    label: Optional[StreamLabel] = None
+    pre = [(st, st.stream_pre_begin()) for st in raw if hasattr(st, "stream_pre_begin")]
+    pre_done = [False] * len(pre)
+    n_local = n_chunks = 0
+    # ---- pass 0
+    for k, chunk in enumerate(chunks):
+        name = response or chunk.response
+        if name and label is None:
+            label = StreamLabel(name)
+        if label is not None:
+            label.scan(chunk)
+        for i, (st, acc) in enumerate(pre):
+            if not pre_done[i]:
+                pre_done[i] = st.stream_pre_update(acc, chunk)
+        n_local += chunk.n
+        n_chunks += 1
+        if on_chunk is not None:
+            on_chunk(0, k, chunk)
+        _release(chunk)
+        if label is None and all(pre_done):
+            break
+    if n_chunks == 0:
+        raise ValueError("requirement failed: Input dataset cannot be empty")
+    if label is not None:
+        label.finish()
+    fitters: Dict[int, object] = {}
+    for st, acc in pre:
+        fitters[id(st)] = st.stream_pre_finish(acc, chunks)       # e.g. the SmartTextVectorizer model, no statistics yet
+    # ---- pass 1
+    accs = []
+    for st in raw:
+        worker = fitters.get(id(st), st)
+        accs.append((st, worker, worker.stream_begin(label)))
+    for k, chunk in enumerate(chunks):
+        if label is not None:
+            label.prime(chunk)
+        for _st, worker, acc in accs:
+            worker.stream_update(acc, chunk)
+        if on_chunk is not None:
+            on_chunk(1, k, chunk)
+        _release(chunk)
+    models: Dict[int, object] = {}
+    stats_of: Dict[int, object] = {}
+    for st, worker, acc in accs:
+        out = worker.stream_finish(acc)
+        if isinstance(st, OpEstimator):
+            models[id(st)] = out
+            stats_of[id(st)] = getattr(out, "_fit_stats", None)
+        else:                                   # a transformer: stream_finish returns its statistics sidecar
+            models[id(st)] = st
+            stats_of[id(st)] = out
+    # ---- decisions: the vector stages see a batch without rows whose vectors carry metadata + statistics
+    n_all = label.n if label is not None else int(D.allreduce_sum(np.array([n_local], dtype=np.int64))[0])
+    virtual = ColumnarBatch(n_all, [], {}, label.name if label is not None else None)
+    fitted = []
+    for st in stages:
+        if _is_raw_stage(st):
+            model = models[id(st)]
+            meta = model.getMetadata()
+            vec = VectorColumn(model.getOutput().name, n_all, meta, [WidthPart(meta.size)], stats_of[id(st)], model)
+            virtual = virtual.with_vector(vec)
+        else:
+            model = st.fit(virtual) if isinstance(st, OpEstimator) else st
+            vec = model.transformColumn(virtual) if not hasattr(model, "stream_transform_virtual") else \
+                model.stream_transform_virtual(virtual)
+            vec.producer = model
+            virtual = virtual.with_vector(vec)
+        fitted.append(model)
+    return StreamResult(fitted, label, n_local, n_chunks, virtual.vectors)
+
+
+def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: StreamResult,
+                     sink: Optional[Callable[[int, VectorColumn, list], None]] = None,
+                     on_chunk: Optional[Callable[[int, int, ColumnarBatch], None]] = None) -> int:
+    """Pass 2: the fitted stages applied chunk by chunk.  sink(index, vector, parts) receives the materialised parts of
+    `result`'s vector for every chunk (device tensors; they may be overwritten once sink returns only if the sink
+    copied or consumed them on the current stream).  -> rows transformed."""
+    R.require_cuda()
+    flags = torch.zeros(4, dtype=torch.int32, device="cuda")
+    flags_clean = torch.zeros(4, dtype=torch.int32, device="cuda")
+    rows = 0
+    for k, chunk in enumerate(chunks):
+        batch = ColumnarBatch(chunk.n, chunk.blocks, {}, None, chunk.token)          # no response: no statistics
+        batch.__dict__["_dev_cache"] = chunk.__dict__.setdefault("_dev_cache", {})
+        batch.__dict__["_stream"] = {"index": k, "token": chunk.token, "flags": flags, "flags_clean": flags_clean}
+        for model in fit.fitted:
+            nb = model.transform(batch)
+            nb.__dict__["_stream"] = batch.__dict__["_stream"]
+            batch = nb
+        vec = batch.vectors[result.name]
+        parts = [p.materialize(None) if hasattr(p, "materialize") else p for p in vec.parts]
+        for p in parts:
+            if hasattr(p, "data") and not hasattr(p, "materialize"):
+                _ = p.data
+        if sink is not None:
+            sink(k, vec, parts)
+        rows += chunk.n
+        if on_chunk is not None:
+            on_chunk(2, k, chunk)
+        _release(chunk)
+    from .stages.smart_text import NON_ASCII_CLEAN, _check_hash_flags
+    _check_hash_flags(flags)
+    if int(flags_clean[0].item()):
+        raise ValueError(NON_ASCII_CLEAN)
+    return rows
+
+
+def fit_and_transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, sink=None,
+                             response: Optional[str] = None, on_chunk=None) -> StreamResult:
+    """OpWorkflow.train() over row chunks: fit_stream, then transform_stream of the same chunks."""
+    fit = fit_stream(chunks, result, response, on_chunk)
+    transform_stream(chunks, result, fit, sink, on_chunk)
+    return fit
