@@ -147,5 +147,10 @@ def check(status: int) -> None:
         raise TmogError(status, msg)
 
 
+DEV_CALLS = [0]      # calls of *_dev entry points so far (each one queues at least one of the library's kernels)
+
+
 def call(name: str, *args) -> None:
+    if name.endswith("_dev"):
+        DEV_CALLS[0] += 1
     check(getattr(lib(), name)(*args))

@@ -57,3 +57,13 @@ def ptr(t) -> Optional[int]:
     if isinstance(t, np.ndarray):
         return t.ctypes.data
     return t.data_ptr()
+
+
+def clear_caches() -> None:
+    """Drop the content-keyed caches of the stage layer (metadata plans, column descriptions, small device constants).
+    They hold nothing that depends on row data; a caller that wants every fit to start from nothing calls this."""
+    from .stages import numeric, pivot, sanity
+    sanity._PLAN_CACHE.clear()
+    sanity._RUN_INFO.clear()
+    pivot._COLUMN_DESCRIPTIONS.clear()
+    numeric._DEV_CONST.clear()

@@ -166,6 +166,127 @@ class StreamLabel:
             cache[(self.name, "moments")] = (self.stats, self.shift)
 
 
+def _block_tensors(block):
+    for name in ("values", "valid", "codes"):
+        t = getattr(block, name, None)
+        if isinstance(t, torch.Tensor):
+            yield t
+    for name in ("data", "offsets", "valid", "codes"):
+        ts = getattr(block, name, None)
+        if isinstance(ts, (list, tuple)):
+            for t in ts:
+                if isinstance(t, torch.Tensor):
+                    yield t
+
+
+def device_chunks(chunks: Iterable[ColumnarBatch], depth: int = 1):
+    """The chunks in HBM, in order.  Chunks that are there already pass through; a chunk in (pinned) host memory is
+    copied on a side stream while the chunks before it are being worked on, `depth` chunks ahead -- partition k + 1
+    crosses the link under partition k's kernels.  At most depth + 2 uploaded chunks exist at a time: the copy of a
+    further chunk waits for the work on chunk k - 1 to finish.  The device copy keeps the host chunk's token."""
+    main = torch.cuda.current_stream()
+    copy = None
+    pending = []                       # [(device chunk, upload event)]
+    done: List[torch.cuda.Event] = []  # work on earlier yielded chunks finished
+
+    def upload(chunk: ColumnarBatch):
+        nonlocal copy
+        if all(getattr(b, "is_cuda", True) for b in chunk.blocks):
+            return chunk, None
+        if copy is None:
+            copy = torch.cuda.Stream()
+        if len(done) > depth + 1:
+            done[-(depth + 2)].synchronize()
+        with torch.cuda.stream(copy):
+            blocks = [b if b.is_cuda else b.to("cuda") for b in chunk.blocks]
+            ev = torch.cuda.Event()
+            ev.record(copy)
+        return ColumnarBatch(chunk.n, blocks, {}, chunk.response, chunk.token), ev
+
+    def hand_over(item):
+        dev, ev = item
+        if ev is not None:
+            main.wait_event(ev)
+            for b in dev.blocks:
+                for t in _block_tensors(b):
+                    t.record_stream(main)
+        return dev
+
+    for chunk in chunks:
+        pending.append(upload(chunk))
+        if len(pending) > depth:
+            yield hand_over(pending.pop(0))
+            ev = torch.cuda.Event()
+            ev.record(main)
+            done.append(ev)
+            del done[:-(depth + 3)]
+    while pending:
+        yield hand_over(pending.pop(0))
+
+
+class HostSink:
+    """A sink for transform_stream that moves every chunk's output to pinned host memory on a side stream, `depth`
+    chunks in flight (the device-to-host copy of chunk k runs under the kernels of chunk k + 1 and, over PCIe, beside
+    the upload of chunk k + 2).  consume(index, vector, host_tensors) is called once a chunk's copies have landed, in
+    order; the pinned buffers are reused after that."""
+
+    def __init__(self, depth: int = 2, consume=None):
+        self.depth, self.consume = depth, consume
+        self.stream = torch.cuda.Stream()
+        self.slots = [dict(bufs=[], ev=None, item=None) for _ in range(depth)]
+        self.bytes = 0
+        self.chunks = 0
+
+    @staticmethod
+    def _tensors(parts):
+        out = []
+        for p in parts:
+            for name in ("data", "indices", "values", "row_start", "row_nnz"):
+                t = getattr(p, name, None)
+                if isinstance(t, torch.Tensor):
+                    out.append(t)
+        return out
+
+    def _drain(self, slot):
+        if slot["ev"] is not None:
+            slot["ev"].synchronize()
+            if self.consume is not None:
+                k, vec, views = slot["item"]
+                self.consume(k, vec, views)
+            slot["ev"], slot["item"] = None, None
+
+    def __call__(self, k: int, vec: VectorColumn, parts) -> None:
+        slot = self.slots[k % self.depth]
+        self._drain(slot)
+        tensors = self._tensors(parts)
+        main = torch.cuda.current_stream()
+        self.stream.wait_stream(main)
+        views = []
+        with torch.cuda.stream(self.stream):
+            for i, t in enumerate(tensors):
+                nbytes = t.numel() * t.element_size()
+                if i >= len(slot["bufs"]):
+                    slot["bufs"].append(None)
+                buf = slot["bufs"][i]
+                if buf is None or buf.numel() < nbytes:
+                    buf = slot["bufs"][i] = torch.empty(max(int(nbytes * 1.05), 1), dtype=torch.uint8, pin_memory=True)
+                src = t if t.is_contiguous() else t.contiguous()
+                dst = buf[:nbytes].view(t.dtype).view(src.shape)
+                dst.copy_(src, non_blocking=True)
+                src.record_stream(self.stream)
+                views.append(dst)
+                self.bytes += nbytes
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        slot["ev"], slot["item"] = ev, (k, vec, views)
+        self.chunks += 1
+
+    def finish(self) -> None:
+        order = sorted((s for s in self.slots if s["item"] is not None), key=lambda s: s["item"][0])
+        for s in order:
+            self._drain(s)
+
+
 def _release(chunk: ColumnarBatch) -> None:
     """Drop what a pass left on a chunk (device copies of host blocks, label, class ids)."""
     for k in ("_dev_cache", "_label_dev", "_label_cache", "_dict_cache"):
@@ -229,7 +350,7 @@ def fit_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, response: Opt
     for st in raw:
         worker = fitters.get(id(st), st)
         accs.append((st, worker, worker.stream_begin(label)))
-    for k, chunk in enumerate(chunks):
+    for k, chunk in enumerate(device_chunks(chunks)):
         if label is not None:
             label.prime(chunk)
         for _st, worker, acc in accs:
@@ -277,7 +398,7 @@ def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: St
     flags = torch.zeros(4, dtype=torch.int32, device="cuda")
     flags_clean = torch.zeros(4, dtype=torch.int32, device="cuda")
     rows = 0
-    for k, chunk in enumerate(chunks):
+    for k, chunk in enumerate(device_chunks(chunks)):
         batch = ColumnarBatch(chunk.n, chunk.blocks, {}, None, chunk.token)          # no response: no statistics
         batch.__dict__["_dev_cache"] = chunk.__dict__.setdefault("_dev_cache", {})
         batch.__dict__["_stream"] = {"index": k, "token": chunk.token, "flags": flags, "flags_clean": flags_clean}
@@ -296,6 +417,8 @@ def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: St
         if on_chunk is not None:
             on_chunk(2, k, chunk)
         _release(chunk)
+    if hasattr(sink, "finish"):
+        sink.finish()
     from .stages.smart_text import NON_ASCII_CLEAN, _check_hash_flags
     _check_hash_flags(flags)
     if int(flags_clean[0].item()):
