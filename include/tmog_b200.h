@@ -304,8 +304,12 @@ int tmog_set_transform_dev(const int64_t* offsets, const int32_t* codes, int64_t
  * (C/stages/impl/feature/OPCollectionHashingVectorizer.scala:244-305; Spark 2.4.5 HashingTF: legacy murmur3_x86_32
  * seed 42, non-negative mod) + the null indicators of SmartTextVectorizerModel (SmartTextVectorizer.scala:363-371).
  *   prefix [ncols * 16] / prefix_len [ncols] (device): the bytes of "<hasher.indexOf(featureName)>_" per column;
- *   params [8] (HOST): numFeatures, sharedHashSpace, binaryFreq, minTokenLength, trackNulls, prependFeatureName,
- *                      null_base (vector index of the first null indicator; >= width of the hash block), nclasses.
+ *   params [12] (HOST): numFeatures, sharedHashSpace, binaryFreq, minTokenLength, trackNulls, prependFeatureName,
+ *                      null_base (vector index of the first null indicator; >= width of the hash block), nclasses,
+ *                      n_hashed (0 = all: columns [0, n_hashed) are hashed, the ones behind them are the columns
+ *                      SmartTextVectorizer ignores -- tokenised for their null indicator / text length only,
+ *                      SmartTextVectorizer.scala:342-354), len_base (0 = none: vector index of the first text-length
+ *                      column, trackTextLen :373-375; value = summed length of the surviving tokens), 0, 0.
  * Vector index of a hit: bucket (+ j * numFeatures for separate spaces); null indicator of column j: null_base + j.
  * text bytes are read with aligned 16-byte loads, so every column's `data` must lie in an allocation whose bounds are
  * 16-byte aligned (true of anything cudaMalloc returns).
@@ -329,6 +333,12 @@ int tmog_set_transform_dev(const int64_t* offsets, const int32_t* codes, int64_t
  *   SanityChecker); *cursor (device u64, zeroed by the caller) ends as the total number of entries; entries beyond
  *   `capacity` are counted but not written (flags[3]) -- call with capacity 0 to size the buffers. */
 int tmog_text_hash_scratch_bytes(int64_t n, size_t* bytes);
+/* Scratch that also lets the three calls below take the per-cell path (separate hash spaces of at most 512 buckets per
+ * column, the TransmogrifierDefaults layout): a lane tokenises one cell into a 512-bit bucket bitmap, statistics come
+ * from warp-transposed bitmaps, and the sparse rows are assembled from 128-byte cell records by an HBM-bound second
+ * kernel (sparse_out != 0 adds n * ncols * 128 bytes for the records).  With less scratch than this (but at least
+ * tmog_text_hash_scratch_bytes) the calls run the per-row table kernel; ignored columns and text lengths need this one. */
+int tmog_text_hash_scratch_bytes2(int64_t n, int ncols, const int32_t* params, int sparse_out, size_t* bytes);
 int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
                              const int32_t* prefix_len, const int32_t* params, const uint8_t* class_ids,
                              uint32_t* bucket_class_sum, uint32_t* bucket_dup, uint64_t* bucket_sq_extra,

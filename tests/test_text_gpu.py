@@ -265,7 +265,9 @@ def test_hash_long_cells_and_crowded_rows():
 
 def test_hash_token_run_longer_than_buffer_is_refused():
     with pytest.raises(ValueError, match="longer than"):
-        _hash_case([["ok text", "a" * 9000 + " tail"]], ["t"], 64, "Shared")
+        _hash_case([["ok text", "a" * 9000 + " tail"], ["x", "y"]], ["t", "u"], 64, "Shared")
+    # separate hash spaces of <= 512 buckets run the per-cell kernels, whose byte-wise slow path has no such limit
+    _hash_case([["ok text", "a" * 9000 + " tail"], ["x", "y"]], ["t", "u"], 64, "Separate")
 
 
 def test_hash_many_columns_wide_keys_and_count_overflow():

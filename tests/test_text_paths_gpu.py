@@ -1,0 +1,99 @@
+"""The two tokenise + hash implementations must agree bit for bit: the per-cell kernels (text_cells.cuh: separate hash
+spaces of <= 512 buckets), their byte-wise slow path for the cells the fast path sets aside, and the per-row table kernel
+(text_hash_kernel) -- on text of the bench generator's shape and on hand-made cells that hit every special case
+(TextTokenizer.scala:160-220, OPCollectionHashingVectorizer.scala:244-272)."""
+import os
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+SPECIAL = [
+    "What's up www.google.com 3.14 1,000 a,b foo_bar9 ___ _a_ x:y 10:30 I've don't. 'tis", None, "", "   ",
+    "the and of to a in is it you that",                                  # stop words only -> null indicator
+    "z" * 300 + " tail " + "q" * 255 + " " + "w" * 256,                   # tokens longer than maxTokenLength
+    "m" * 44 + " " + "n" * 45 + " " + "o" * 47 + " p" * 3,                # around the ring's reach
+    " ".join(f"w{i} w{i}" for i in range(40)),                            # 40 repeated buckets: more than a record holds
+    " ".join(["same"] * 500),                                             # one bucket 500 times
+    "ALL CAPS AND Mixed Case, with; punct: u.s.a. 1.2.3.4 a.1 1.a _._ a_.b",
+    "x" * 15 + " " + "y" * 16 + " " + "z" * 17 + " " + "a" * 31 + " " + "b" * 32 + " " + "c" * 33,
+    "tab\tsep\nnewline\rcr end", "trailing.", ".leading", "a", "ab", "9", "_",
+]
+
+
+def _model_outputs(batch, names, num_features, binary, min_len, track, label):
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    feats = [F.FeatureBuilder.Text(nm).asPredictor() for nm in names]
+    est = SmartTextVectorizer().setMaxCardinality(0).setNumFeatures(num_features).setHashSpaceStrategy("Separate") \
+        .setBinaryFreq(binary).setMinTokenLength(min_len).setTrackNulls(track).setInput(*feats)
+    for k in ("_label_cache", "_label_dev", "_dev_cache"):
+        batch.__dict__.pop(k, None)
+    model = est.fit(batch)
+    st = model._fit_stats
+    rows = model.transform(batch).vectors[est.getOutput().name].to_scipy()
+    # and the transform-only pass (no rows left over from the fit)
+    from transmogrifai_b200.columnar import ColumnarBatch
+    other = ColumnarBatch(batch.n, batch.blocks, {}, None)
+    rows2 = model.transform(other).vectors[est.getOutput().name].to_scipy()
+    return st, rows, rows2
+
+
+@pytest.mark.parametrize("num_features,binary,min_len,track", [(512, False, 1, True), (100, True, 2, False)])
+def test_cell_path_slow_path_and_row_table_path_agree(num_features, binary, min_len, track):
+    import benchdata
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch, NumericBlock, TextBlock
+    n = 40_000
+    g = torch.Generator(device="cuda").manual_seed(123)
+    y = (torch.rand(benchdata._ld(n), device="cuda", generator=g) < 0.3).double()
+    tb = benchdata.text_block(g, n, 5)
+    rng = np.random.default_rng(9)
+    special = [SPECIAL[i % len(SPECIAL)] if rng.random() < 0.5 else
+               " ".join(rng.choice(["alpha", "Beta", "the", "gamma9", "x_y", "it's", "3.5", "end."], size=rng.integers(0, 60)))
+               for i in range(n)]
+    sb = TextBlock.from_lists(["s0"], F.TEXT, [special]).to("cuda")
+    block = TextBlock(tb.names + sb.names, F.TEXT, tb.data + sb.data, tb.offsets + sb.offsets, tb.valid + sb.valid, n)
+    label = NumericBlock(["label"], F.REALNN, y.view(1, -1), None, n)
+    batch = ColumnarBatch(n, [block, label], {}, response="label")
+    names = block.names
+    out = {}
+    try:
+        for mode, env in (("cells", {}), ("slow", {"TMOG_TEXT_FORCE_SLOW": "1"}), ("rows", {"TMOG_TEXT_PATH": "rows"})):
+            for k in ("TMOG_TEXT_FORCE_SLOW", "TMOG_TEXT_PATH"):
+                os.environ.pop(k, None)
+            os.environ.update(env)
+            out[mode] = _model_outputs(batch, names, num_features, binary, min_len, track, y)
+    finally:
+        for k in ("TMOG_TEXT_FORCE_SLOW", "TMOG_TEXT_PATH"):
+            os.environ.pop(k, None)
+    ref_st, ref_rows, ref_rows2 = out["rows"]
+    assert abs(ref_rows - ref_rows2).max() == 0
+    for mode in ("cells", "slow"):
+        st, rows, rows2 = out[mode]
+        for k in ("mean", "variance", "min", "max", "cov_label"):
+            assert np.array_equal(getattr(st, k), getattr(ref_st, k)), (mode, k)
+        assert np.array_equal(np.nan_to_num(st.class_sums, nan=-1.0), np.nan_to_num(ref_st.class_sums, nan=-1.0)), mode
+        assert rows.shape == ref_rows.shape and abs(rows - ref_rows).max() == 0, mode
+        assert abs(rows2 - ref_rows).max() == 0, mode
+
+
+def test_cell_path_matches_oracle_on_special_cells():
+    from oracle import vectorizers as V
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    cols = [SPECIAL, list(reversed(SPECIAL))]
+    names = ["first_col", "second"]
+    batch = ColumnarBatch.from_columns({nm: (F.TEXT, c) for nm, c in zip(names, cols)}).to("cuda")
+    feats = [F.FeatureBuilder.Text(nm).asPredictor() for nm in names]
+    for nf in (512, 37):
+        est = SmartTextVectorizer().setMaxCardinality(0).setNumFeatures(nf).setHashSpaceStrategy("Separate") \
+            .setInput(*feats)
+        model = est.fit(batch)
+        got = model.transform(batch).vectors[est.getOutput().name].to_scipy()
+        exp = V.smart_text_transform(cols, names, ["Hash"] * 2, [[], []], num_features=nf, hash_space_strategy="Separate")
+        import scipy.sparse as sp
+        assert abs(got - sp.csr_matrix(exp)).max() == 0

@@ -70,6 +70,7 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_text_stats_values_dev": [_p, _int, _i64, _p, _int, _int, _int, _int, _p, _p, _p],
     "tmog_text_codes_dev": [_p, _p, _int, _i64, _int, _int, _p, _p, _i64, _p, _p],
     "tmog_text_hash_scratch_bytes": [_i64, C.POINTER(_sz)],
+    "tmog_text_hash_scratch_bytes2": [_i64, _int, _p, _int, C.POINTER(_sz)],
     "tmog_text_hash_stats_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _dbl, _p, _p, _p, _sz, _p],
     "tmog_text_hash_transform_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _p, _p, _sz, _p],
     "tmog_text_hash_fit_transform_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _dbl, _p, _p, _p, _p, _p, _p,

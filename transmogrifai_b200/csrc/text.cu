@@ -14,6 +14,7 @@
 //
 // The tokenise + hash kernel is instruction-bound, not HBM-bound; its design is described above the kernel and in
 // DESIGN.md.
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -1217,6 +1218,8 @@ sparse_rows_select_kernel(const int64_t* __restrict__ row_start, const int32_t* 
 
 }  // namespace tmog
 
+#include "text_cells.cuh"
+
 using namespace tmog;
 // Snowball english_stop.txt (174 words) as loaded by Lucene's StandardAnalyzer in the reference
 // (core/src/main/scala/com/salesforce/op/utils/text/LuceneTextAnalyzer.scala:159-161)
@@ -1404,6 +1407,9 @@ struct ThArgs {
     int64_t capacity;
     int32_t* flags;
     ThScratch* scratch;
+    size_t scratch_bytes;
+    int n_hashed;          // columns [0, n_hashed) are hashed; the rest only give null indicators / text lengths
+    int len_base;          // vector index of the first text-length column, or -1
     cudaStream_t stream;
 };
 
@@ -1474,13 +1480,24 @@ static int text_hash_common(const int64_t* col_desc, int ncols, int64_t n, const
     TMOG_REQUIRE(p.num_features > 0 && p.num_features <= 10000000,
                  "requirement failed: numFeatures must be in (0, 10000000], got %d", p.num_features);
     TMOG_REQUIRE(p.nclasses >= 1 && p.nclasses <= 255, "nclasses must be in [1, 255]");
-    const int64_t hw = p.shared ? p.num_features : (int64_t)p.num_features * ncols;
-    TMOG_REQUIRE(hw + ncols < 0x7fffffffLL, "hash block too wide");
+    const int nh = params[8] > 0 ? params[8] : ncols;
+    const int64_t hw = p.shared ? p.num_features : (int64_t)p.num_features * nh;
+    TMOG_REQUIRE(hw + 2 * (int64_t)ncols < 0x7fffffffLL, "hash block too wide");
     p.hash_width = (int)hw;
     TMOG_REQUIRE(p.null_base >= p.hash_width && (int64_t)p.null_base + ncols < 0x7fffffffLL,
                  "null_base must not overlap the hash block");
     p.pow2_mask = (p.num_features & (p.num_features - 1)) == 0 ? p.num_features - 1 : -1;
     p.count_bits = 32;
+    a->n_hashed = params[8] > 0 ? params[8] : ncols;
+    a->len_base = params[9] > 0 ? params[9] : -1;
+    TMOG_REQUIRE(a->n_hashed <= ncols, "n_hashed %d exceeds the %d columns", a->n_hashed, ncols);
+    if (a->n_hashed < ncols || a->len_base >= 0) {
+        const int64_t hw2 = p.shared ? p.num_features : (int64_t)p.num_features * a->n_hashed;
+        p.hash_width = (int)hw2;
+        TMOG_REQUIRE(a->len_base < 0 || a->len_base >= p.hash_width, "len_base must not overlap the hash block");
+        TMOG_REQUIRE(p.null_base >= p.hash_width + (a->len_base >= 0 ? ncols : 0), "null_base overlaps");
+    }
+    a->scratch_bytes = scratch_bytes;
     size_t need = 0;
     if (int rc = tmog_text_hash_scratch_bytes(n, &need)) return rc;
     TMOG_REQUIRE(scratch != nullptr && scratch_bytes >= need, "scratch too small: %zu bytes needed", need);
@@ -1492,6 +1509,108 @@ static int text_hash_common(const int64_t* col_desc, int ncols, int64_t n, const
     a->prefix_len = prefix_len;
     a->scratch = reinterpret_cast<ThScratch*>(scratch);
     return upload_stop_words();
+}
+
+// ---- the per-cell path (text_cells.cuh): separate hash spaces of at most 512 buckets ---------------------------------
+static bool tc_eligible(const TextHashParams& p, int ncols, int n_hashed) {
+    const char* force = getenv("TMOG_TEXT_PATH");
+    if (force && strcmp(force, "rows") == 0) return false;
+    if (ncols < 1 || p.num_features > TC_MAXF) return false;
+    return !p.shared || n_hashed <= 1;
+}
+
+static size_t tc_scratch_need(int64_t n, int ncols, int n_hashed, bool sparse_out) {
+    const size_t keepw = ((size_t)n_hashed * TC_FW * 4 + 255) & ~size_t(255);
+    const size_t bits = ((((size_t)n * ncols + 31) / 32) * 4 + 255) & ~size_t(255);
+    return 256 + keepw + bits + (sparse_out ? (size_t)n * ncols * TC_REC_WORDS * 4 : 0);
+}
+
+template <bool STATS, bool CELLS>
+static int tc_run(const ThArgs& a) {
+    TcParams p;
+    p.num_features = a.p.num_features;
+    p.binary_freq = a.p.binary_freq;
+    p.min_token_length = a.p.min_token_length;
+    p.track_nulls = a.p.track_nulls;
+    p.prepend = a.p.prepend;
+    p.null_base = a.p.null_base;
+    p.len_base = a.len_base;
+    p.n_hashed = a.n_hashed;
+    p.nclasses = a.p.nclasses;
+    p.pow2_mask = a.p.pow2_mask;
+    const char* slow = getenv("TMOG_TEXT_FORCE_SLOW");
+    p.force_defer = (slow && slow[0] == '1') ? 1 : 0;
+    uint8_t* base = reinterpret_cast<uint8_t*>(a.scratch);
+    TcScratch* sc = reinterpret_cast<TcScratch*>(base);
+    const size_t keepw_bytes = ((size_t)a.n_hashed * TC_FW * 4 + 255) & ~size_t(255);
+    const size_t bits_bytes = ((((size_t)a.n * a.ncols + 31) / 32) * 4 + 255) & ~size_t(255);
+    unsigned* keepw = reinterpret_cast<unsigned*>(base + 256);
+    unsigned* defer_bits = reinterpret_cast<unsigned*>(base + 256 + keepw_bytes);
+    unsigned* records = reinterpret_cast<unsigned*>(base + 256 + keepw_bytes + bits_bytes);
+    TMOG_CUDA(cudaMemsetAsync(base, 0, 256, a.stream));
+    TMOG_CUDA(cudaMemsetAsync(defer_bits, 0, bits_bytes, a.stream));
+    auto kernel = text_cells_kernel<STATS, CELLS>;
+    const size_t smem = STOP_SLOTS * sizeof(StopSlot) + TH_STOP_PRE_BYTES + 64 +
+                        (size_t)TC_WARPS * (TC_RING + TC_FW + TC_DUPS) * 32 * 4;
+    TMOG_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, TC_WARPS * 32, smem));
+    TMOG_REQUIRE(per_sm >= 1, "text cell kernel does not fit an SM");
+    const int64_t items = ((a.n + TC_ITEM_ROWS - 1) / TC_ITEM_ROWS) * a.ncols;
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)sm_count() * per_sm, items));
+    kernel<<<grid, TC_WARPS * 32, smem, a.stream>>>(a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, a.class_ids, sc,
+                                                    defer_bits, a.class_sum, a.dup, a.sq_extra, a.aux, a.label,
+                                                    a.label_shift, a.wsum, records, a.flags);
+    TMOG_LAUNCH_CHECK();
+    if (STATS) {
+        const int64_t words = ((int64_t)a.n * a.ncols + 31) / 32;
+        const int sgrid = (int)std::max<int64_t>(1, std::min<int64_t>((words + 127) / 128, (int64_t)sm_count() * 8));
+        text_cells_slow_kernel<<<sgrid, 128, 0, a.stream>>>(a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, a.class_ids,
+                                                            defer_bits, a.class_sum, a.dup, a.sq_extra, a.aux, a.label,
+                                                            a.label_shift, a.wsum, a.flags);
+        TMOG_LAUNCH_CHECK();
+    }
+    if (CELLS) {
+        const int nw = a.n_hashed * TC_FW;
+        if (nw > 0) {
+            tc_keep_words_kernel<<<(nw + 127) / 128, 128, 0, a.stream>>>(a.newpos, a.n_hashed, p.num_features, keepw);
+            TMOG_LAUNCH_CHECK();
+        }
+        const size_t per_warp = ((size_t)a.ncols * TC_FW * 2 + TC_MAXF * 2 + 15) & ~size_t(15);
+        const size_t rsmem = per_warp * 8;
+        TMOG_REQUIRE(rsmem <= 200 * 1024, "too many text columns for the row assembly (%d)", a.ncols);
+        TMOG_CUDA(cudaFuncSetAttribute(text_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem));
+        const int rgrid = (int)std::max<int64_t>(1, std::min<int64_t>((a.n + 7) / 8, (int64_t)sm_count() * 8));
+        text_rows_kernel<<<rgrid, 256, rsmem, a.stream>>>(a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, records, keepw,
+                                                          a.newpos, a.row_start, a.row_nnz, a.out_idx, a.out_val, a.cursor,
+                                                          a.capacity, a.flags);
+        TMOG_LAUNCH_CHECK();
+    }
+    return TMOG_OK;
+}
+
+// which path serves a call: the per-cell path when the layout allows it and the caller's scratch holds its records
+template <bool STATS, bool CELLS>
+static int text_hash_dispatch(ThArgs& a) {
+    if (tc_eligible(a.p, a.ncols, a.n_hashed) && a.scratch_bytes >= tc_scratch_need(a.n, a.ncols, a.n_hashed, CELLS))
+        return tc_run<STATS, CELLS>(a);
+    TMOG_REQUIRE(a.n_hashed == a.ncols && a.len_base < 0,
+                 "ignored text columns / text lengths need separate hash spaces of at most %d buckets per column and "
+                 "the scratch of tmog_text_hash_scratch_bytes2", TC_MAXF);
+    return CELLS ? th_run<true>(a) : th_run<false>(a);
+}
+
+extern "C" int tmog_text_hash_scratch_bytes2(int64_t n, int ncols, const int32_t* params, int sparse_out, size_t* bytes) {
+    TMOG_REQUIRE(bytes != nullptr && params != nullptr && n >= 0 && n < 0x7fffffffLL && ncols >= 0, "bad arguments");
+    size_t need = 0;
+    if (int rc = tmog_text_hash_scratch_bytes(n, &need)) return rc;
+    TextHashParams p = {};
+    p.num_features = params[0];
+    p.shared = params[1];
+    const int nh = params[8] > 0 ? params[8] : ncols;
+    if (tc_eligible(p, ncols, nh)) need = std::max(need, tc_scratch_need(n, ncols, nh, sparse_out != 0));
+    *bytes = need;
+    return TMOG_OK;
 }
 
 extern "C" int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
@@ -1516,7 +1635,7 @@ extern "C" int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int6
     a.wsum = bucket_wsum;
     a.flags = flags;
     a.stream = (cudaStream_t)stream;
-    return th_run<false>(a);
+    return text_hash_dispatch<true, false>(a);
 }
 
 extern "C" int tmog_text_hash_transform_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
@@ -1538,7 +1657,7 @@ extern "C" int tmog_text_hash_transform_dev(const int64_t* col_desc, int ncols, 
     a.capacity = capacity;
     a.flags = flags;
     a.stream = (cudaStream_t)stream;
-    return th_run<true>(a);
+    return text_hash_dispatch<false, true>(a);
 }
 
 extern "C" int tmog_text_hash_fit_transform_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
@@ -1574,7 +1693,7 @@ extern "C" int tmog_text_hash_fit_transform_dev(const int64_t* col_desc, int nco
     a.capacity = capacity;
     a.flags = flags;
     a.stream = (cudaStream_t)stream;
-    return th_run<true>(a);
+    return text_hash_dispatch<true, true>(a);
 }
 
 extern "C" int tmog_sparse_rows_select_dev(const int64_t* row_start, const int32_t* row_nnz, const int32_t* idx,

@@ -639,9 +639,10 @@ class SmartTextVectorizerModel(OpModel):
                 prefix[t, :len(s)] = np.frombuffer(s, dtype=np.uint8)
                 plen[t] = len(s)
             hit = self.__dict__["_ha_cache"] = (key, torch.from_numpy(prefix).cuda(), torch.from_numpy(plen).cuda())
-        sub = dev.rows(lay.hash_idx)      # (ignored columns would ride behind the hashed ones)
+        sub = dev.rows(lay.text_idx)      # the ignored columns ride behind the hashed ones
         params = np.array([lay.num_features, int(lay.shared), int(hp["binaryFreq"]), hp["minTokenLength"],
-                           int(self.shouldTrackNulls), int(hp["prependFeatureName"]), lay.hash_width, 0],
+                           int(self.shouldTrackNulls), int(hp["prependFeatureName"]), lay.null_base, 0,
+                           len(lay.hash_idx) if lay.ignore_idx else 0, lay.len_base if lay.len_width else 0, 0, 0],
                           dtype=np.int32)
         return sub, hit[1], hit[2], params
 
@@ -989,7 +990,12 @@ def _hash_scratch(n: int, ncols: int = 0, lay: Optional[_HashLayout] = None, spa
     """Device scratch of the tokenise + hash entry points for n rows of ncols text columns."""
     import ctypes
     need = ctypes.c_size_t(0)
-    L.call("tmog_text_hash_scratch_bytes", n, ctypes.byref(need))
+    if lay is None:
+        L.call("tmog_text_hash_scratch_bytes", n, ctypes.byref(need))
+    else:
+        params = np.array([lay.num_features, int(lay.shared), 0, 0, 0, 0, 0, 0,
+                           len(lay.hash_idx) if lay.ignore_idx else 0, 0, 0, 0], dtype=np.int32)
+        L.call("tmog_text_hash_scratch_bytes2", n, ncols, params.ctypes.data, int(sparse_out), ctypes.byref(need))
     return torch.empty(max(need.value, 8), dtype=torch.uint8, device="cuda")
 
 
