@@ -365,6 +365,8 @@ struct StopSlot {          // stop-word table in shared memory: length + the wor
     unsigned len, w0, w1, w2;
 };
 
+__constant__ StopSlot c_stop_packed[STOP_SLOTS];      // the same table, words packed (read by the per-cell kernels)
+
 // two slot choices per word (cuckoo hashing): a probe is two loads, no loop
 __host__ __device__ inline unsigned stop_slot_hash(unsigned w0, unsigned w1, unsigned w2) {
     return ((w0 * 0x9E3779B1u) ^ (w1 * 0x85EBCA6Bu) ^ (w2 * 0xC2B2AE35u)) >> 23;   // 9 bits: STOP_SLOTS == 512
@@ -1268,6 +1270,17 @@ static int upload_stop_words() {
         TMOG_REQUIRE(placed, "stop-word table: cuckoo insertion failed");
     }
     TMOG_CUDA(cudaMemcpyToSymbol(c_stop, table, sizeof(table)));
+    static StopSlot packed[STOP_SLOTS];
+    memset(packed, 0, sizeof(packed));
+    for (int i = 0; i < STOP_SLOTS; ++i) {
+        packed[i].len = table[i].len;
+        for (int q = 0; q < table[i].len; ++q) {
+            const unsigned c = (unsigned char)table[i].w[q];
+            unsigned& w = q < 4 ? packed[i].w0 : q < 8 ? packed[i].w1 : packed[i].w2;
+            w |= c << (8 * (q & 3));
+        }
+    }
+    TMOG_CUDA(cudaMemcpyToSymbol(c_stop_packed, packed, sizeof(packed)));
     static unsigned short pre[STOP_PRE];
     memset(pre, 0, sizeof(pre));
     for (int i = 0; i < nwords; ++i) {
@@ -1550,8 +1563,7 @@ static int tc_run(const ThArgs& a) {
     TMOG_CUDA(cudaMemsetAsync(base, 0, 256, a.stream));
     TMOG_CUDA(cudaMemsetAsync(defer_bits, 0, bits_bytes, a.stream));
     auto kernel = text_cells_kernel<STATS, CELLS>;
-    const size_t smem = STOP_SLOTS * sizeof(StopSlot) + TH_STOP_PRE_BYTES + 64 +
-                        (size_t)TC_WARPS * (TC_RING + TC_FW + TC_DUPS) * 32 * 4;
+    const size_t smem = TH_STOP_PRE_BYTES + 64 + (size_t)TC_WARPS * (TC_WARP_ROWS + (STATS ? TC_STAT_ROWS : 0)) * 32 * 4;
     TMOG_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, TC_WARPS * 32, smem));
@@ -1576,7 +1588,7 @@ static int tc_run(const ThArgs& a) {
             tc_keep_words_kernel<<<(nw + 127) / 128, 128, 0, a.stream>>>(a.newpos, a.n_hashed, p.num_features, keepw);
             TMOG_LAUNCH_CHECK();
         }
-        const size_t per_warp = ((size_t)a.ncols * TC_FW * 2 + TC_MAXF * 2 + 15) & ~size_t(15);
+        const size_t per_warp = ((size_t)a.ncols * TC_FW * 4 + TC_MAXF * 2 + (size_t)a.ncols * TC_FW * 2 + 15) & ~size_t(15);
         const size_t rsmem = per_warp * 8;
         TMOG_REQUIRE(rsmem <= 200 * 1024, "too many text columns for the row assembly (%d)", a.ncols);
         TMOG_CUDA(cudaFuncSetAttribute(text_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsmem));

@@ -25,10 +25,14 @@ namespace tmog {
 constexpr int TC_WARPS = 8;
 constexpr int TC_FW = 16;                 // bitmap words of a cell: numFeatures <= 512
 constexpr int TC_MAXF = TC_FW * 32;
-constexpr int TC_DUPS = 13;               // buckets with term frequency > 1 a cell record holds
+constexpr int TC_DUPS = 12;               // buckets with term frequency > 1 a cell record holds (13 slots)
 constexpr int TC_RING = 16;               // words of recent text a lane keeps (64 bytes)
+constexpr int TC_RING_ROWS = TC_RING + 5; // + the first five words again, behind the last (no wrap inside a token)
 constexpr int TC_BACK = 44;               // a token may start this many bytes before the chunk it ends in
 constexpr int TC_ITEM_ROWS = 8192;        // rows of one column a CTA takes at a time
+constexpr int TC_ROUND_LANES = 26;        // a round runs when this many lanes have a token waiting
+constexpr int TC_WARP_ROWS = TC_RING_ROWS + 4 + TC_FW + TC_DUPS;   // shared-memory rows (32 words) of a warp
+constexpr int TC_STAT_ROWS = TC_FW;       // + per-class bucket counts of the warp's column (u16 x 2 classes), fit only
 
 // record of one cell, 32 words: bitmap [16] | header | length sum | extra | dup [13] (bucket | count << 16)
 constexpr int TC_REC_WORDS = 32;
@@ -154,21 +158,25 @@ __device__ __forceinline__ unsigned tc_ring_byte(const unsigned* ring, int lane,
 }
 
 // stop-word probe of the token [ps, ps + plen) (plen <= STOP_MAXLEN) read from the lane's ring
-__device__ __forceinline__ bool tc_is_stop(const StopSlot* stop, const unsigned* ring, int lane, int ps, int plen) {
+__device__ __forceinline__ bool tc_is_stop(const unsigned* ring, int lane, int ps, int plen) {
     const int w0 = ps >> 2, sh = (ps & 3) * 8;
     const unsigned a = ring[((w0) & (TC_RING - 1)) * 32 + lane], b = ring[((w0 + 1) & (TC_RING - 1)) * 32 + lane];
     const unsigned c = ring[((w0 + 2) & (TC_RING - 1)) * 32 + lane], d = ring[((w0 + 3) & (TC_RING - 1)) * 32 + lane];
     const unsigned l0 = __funnelshift_r(a, b, sh) & byte_range_mask(0, plen);
     const unsigned l1 = __funnelshift_r(b, c, sh) & byte_range_mask(0, plen - 4);
     const unsigned l2 = __funnelshift_r(c, d, sh) & byte_range_mask(0, plen - 8);
-    const uint4 e1 = reinterpret_cast<const uint4*>(stop)[stop_slot_hash(l0, l1, l2)];
-    const uint4 e2 = reinterpret_cast<const uint4*>(stop)[stop_slot_hash2(l0, l1, l2)];
-    const unsigned d1 = (e1.x ^ (unsigned)plen) | (e1.y ^ l0) | (e1.z ^ l1) | (e1.w ^ l2);
-    const unsigned d2 = (e2.x ^ (unsigned)plen) | (e2.y ^ l0) | (e2.z ^ l1) | (e2.w ^ l2);
+    // few tokens get here (the pre-filter knows first letter, second character and length of every stop word), so the
+    // table stays in constant memory
+    const StopSlot e1 = c_stop_packed[stop_slot_hash(l0, l1, l2)];
+    const StopSlot e2 = c_stop_packed[stop_slot_hash2(l0, l1, l2)];
+    const unsigned d1 = (e1.len ^ (unsigned)plen) | (e1.w0 ^ l0) | (e1.w1 ^ l1) | (e1.w2 ^ l2);
+    const unsigned d2 = (e2.len ^ (unsigned)plen) | (e2.w0 ^ l0) | (e2.w1 ^ l1) | (e2.w2 ^ l2);
     return d1 == 0u || d2 == 0u;
 }
 
-// murmur3 of "<prefix><token>" continued from the state after the prefix; the token is read from the ring
+// murmur3 of "<prefix><token>" continued from the state after the prefix; the token is read from the ring (rows
+// 16 .. 20 repeat rows 0 .. 4).  Tokens of up to 15 bytes with the prefix remainder take a fixed number of steps, the
+// same for every lane; longer ones loop.
 __device__ __forceinline__ unsigned tc_hash_token(const unsigned* ring, int lane, int ps, int plen, unsigned ph,
                                                   unsigned pw, unsigned pn) {
     const int r = (int)(pn & 3u);
@@ -176,19 +184,37 @@ __device__ __forceinline__ unsigned tc_hash_token(const unsigned* ring, int lane
     const int tot = r + plen, nfull = tot >> 2, tail = tot & 3;
     const int q0 = ps - r, sh = (q0 & 3) * 8;
     const int w0 = q0 >> 2;                       // arithmetic shift: q0 may be slightly negative
-    unsigned h = ph, nxt = ring[(w0 & (TC_RING - 1)) * 32 + lane];
-    for (int q = 0; q < nfull; ++q) {
-        const unsigned cur = nxt;
-        nxt = ring[((w0 + q + 1) & (TC_RING - 1)) * 32 + lane];
-        unsigned wd = __funnelshift_r(cur, nxt, sh);
-        if (q == 0) wd = (wd & keep_hi) | pw;
-        h = mix_h1(h, mix_k1(wd));
+    unsigned h = ph, wd;
+    if (tot <= 15) {
+        const unsigned* rp = ring + (w0 & (TC_RING - 1)) * 32 + lane;
+        const unsigned a0 = rp[0], a1 = rp[32], a2 = rp[64], a3 = rp[96], a4 = rp[128];
+        const unsigned s0 = (__funnelshift_r(a0, a1, sh) & keep_hi) | pw, s1 = __funnelshift_r(a1, a2, sh);
+        const unsigned s2 = __funnelshift_r(a2, a3, sh), s3 = __funnelshift_r(a3, a4, sh);
+        unsigned t = mix_h1(h, mix_k1(s0));
+        h = nfull > 0 ? t : h;
+        t = mix_h1(h, mix_k1(s1));
+        h = nfull > 1 ? t : h;
+        t = mix_h1(h, mix_k1(s2));
+        h = nfull > 2 ? t : h;
+        wd = nfull == 0 ? s0 : nfull == 1 ? s1 : nfull == 2 ? s2 : s3;
+    } else {
+        unsigned nxt = ring[(w0 & (TC_RING - 1)) * 32 + lane];
+        for (int q = 0; q < nfull; ++q) {
+            const unsigned cur = nxt;
+            nxt = ring[((w0 + q + 1) & (TC_RING - 1)) * 32 + lane];
+            unsigned x = __funnelshift_r(cur, nxt, sh);
+            if (q == 0) x = (x & keep_hi) | pw;
+            h = mix_h1(h, mix_k1(x));
+        }
+        wd = __funnelshift_r(nxt, ring[((w0 + nfull + 1) & (TC_RING - 1)) * 32 + lane], sh);
     }
-    unsigned wd = __funnelshift_r(nxt, ring[((w0 + nfull + 1) & (TC_RING - 1)) * 32 + lane], sh);
-    if (nfull == 0) wd = (wd & keep_hi) | pw;
-    if (tail > 0) h = mix_h1(h, mix_k1((unsigned)(int)(signed char)(wd & 0xffu)));
-    if (tail > 1) h = mix_h1(h, mix_k1((unsigned)(int)(signed char)((wd >> 8) & 0xffu)));
-    if (tail > 2) h = mix_h1(h, mix_k1((unsigned)(int)(signed char)((wd >> 16) & 0xffu)));
+    // the (< 4) bytes left are mixed one by one, sign-extended (Spark's legacy hashUnsafeBytes)
+    unsigned t = mix_h1(h, mix_k1((unsigned)(int)(signed char)(wd & 0xffu)));
+    h = tail > 0 ? t : h;
+    t = mix_h1(h, mix_k1((unsigned)(int)(signed char)((wd >> 8) & 0xffu)));
+    h = tail > 1 ? t : h;
+    t = mix_h1(h, mix_k1((unsigned)(int)(signed char)((wd >> 16) & 0xffu)));
+    h = tail > 2 ? t : h;
     return fmix32(h, pn + (unsigned)plen);
 }
 
@@ -252,28 +278,18 @@ text_cells_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
                   const double* __restrict__ label, double label_shift, double* __restrict__ bucket_wsum,
                   unsigned* __restrict__ records, int* __restrict__ flags) {
     extern __shared__ __align__(16) unsigned char tc_smem[];
-    StopSlot* stop = reinterpret_cast<StopSlot*>(tc_smem);                                      // [STOP_SLOTS]
-    unsigned short* stop_pre = reinterpret_cast<unsigned short*>(tc_smem + STOP_SLOTS * sizeof(StopSlot));
-    unsigned* item_info = reinterpret_cast<unsigned*>(tc_smem + STOP_SLOTS * sizeof(StopSlot) + TH_STOP_PRE_BYTES);
+    unsigned short* stop_pre = reinterpret_cast<unsigned short*>(tc_smem);
+    unsigned* item_info = reinterpret_cast<unsigned*>(tc_smem + TH_STOP_PRE_BYTES);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int WARP_WORDS = (TC_RING + TC_FW + TC_DUPS) * 32;
-    unsigned* wbase = reinterpret_cast<unsigned*>(tc_smem + STOP_SLOTS * sizeof(StopSlot) + TH_STOP_PRE_BYTES + 64) +
-                      (size_t)warp * WARP_WORDS;
-    unsigned* ring = wbase;                         // [TC_RING][32]
-    unsigned* bm = ring + TC_RING * 32;             // [TC_FW][32]
+    constexpr int WARP_WORDS = (TC_WARP_ROWS + (STATS ? TC_STAT_ROWS : 0)) * 32;
+    unsigned* wbase = reinterpret_cast<unsigned*>(tc_smem + TH_STOP_PRE_BYTES + 64) + (size_t)warp * WARP_WORDS;
+    unsigned* ring = wbase;                         // [TC_RING_ROWS][32]
+    unsigned* masks = ring + TC_RING_ROWS * 32;     // [4][32] token end | start << 16 masks of the last chunks
+    unsigned* bm = masks + 4 * 32;                  // [TC_FW][32]
     unsigned* dups = bm + TC_FW * 32;               // [TC_DUPS][32]: bucket | count << 16
+    // fit: rows of each label class holding bucket 32 w + lane of the warp's column, [class][TC_FW][32] u16
+    unsigned short* hist = reinterpret_cast<unsigned short*>(dups + TC_DUPS * 32);
 
-    for (int i = tid; i < STOP_SLOTS; i += TC_WARPS * 32) {
-        const StopEntry e = c_stop[i];
-        StopSlot sl = {e.len, 0u, 0u, 0u};
-        for (int q = 0; q < e.len; ++q) {
-            const unsigned c = (unsigned char)e.w[q];
-            if (q < 4) sl.w0 |= c << (8 * q);
-            else if (q < 8) sl.w1 |= c << (8 * (q - 4));
-            else sl.w2 |= c << (8 * (q - 8));
-        }
-        stop[i] = sl;
-    }
     for (int i = tid; i < STOP_PRE; i += TC_WARPS * 32) stop_pre[i] = c_stop_pre[i];
     __syncthreads();
 
@@ -308,12 +324,12 @@ text_cells_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
         const unsigned ph = item_info[2], pw = item_info[3], pn = item_info[4];
         const TextColumn tc = cols[j];
         const bool hashed = j < p.n_hashed;
-        // statistics of this column's buckets, in registers: lane k holds bucket 32 w + k of word w, classes 0 / 1
-        unsigned acc0[TC_FW], acc1[TC_FW];
+        // statistics of this column's buckets: lane k holds bucket 32 w + k of word w, classes 0 / 1 (a warp sees at
+        // most TC_ITEM_ROWS / TC_WARPS cells of an item, so 16 bits hold a count)
         unsigned null0 = 0u, null1 = 0u;
         if (STATS) {
 #pragma unroll
-            for (int w = 0; w < TC_FW; ++w) acc0[w] = acc1[w] = 0u;
+            for (int w = 0; w < 2 * TC_FW; ++w) hist[w * 32 + lane] = 0;
         }
 
         for (int64_t g0 = r_lo + (int64_t)warp * 32; g0 < r_hi; g0 += TC_WARPS * 32) {
@@ -339,91 +355,97 @@ text_cells_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
             int tok_start = 0, ndup = 0;
             unsigned len_sum = 0u, cl = 0u, cd = 0u;
 
-            auto load = [&](int ci) -> uint4 {
-                uint4 v = make_uint4(0u, 0u, 0u, 0u);
-                const int lo = ci == 0 ? sh : 0, hi = min(16, end - 16 * ci);
-                if (hi > 0) {
-                    v = __ldg(reinterpret_cast<const uint4*>(base + 16 * (int64_t)ci));
-                    if (lo != 0 || hi != 16) {
-                        v.x &= byte_range_mask(lo, hi);
-                        v.y &= byte_range_mask(lo - 4, hi - 4);
-                        v.z &= byte_range_mask(lo - 8, hi - 8);
-                        v.w &= byte_range_mask(lo - 12, hi - 12);
-                    }
-                    v.x = lower4(v.x);
-                    v.y = lower4(v.y);
-                    v.z = lower4(v.z);
-                    v.w = lower4(v.w);
-                }
-                return v;
+            // the first chunk is masked at both ends; of the later ones only the chunk holding the cell's last byte
+            // needs a mask, prepared here once (chunks behind it are the zero terminator)
+            const int last_real = (end - 1) >> 4;
+            unsigned lm0 = ~0u, lm1 = ~0u, lm2 = ~0u, lm3 = ~0u;
+            {
+                const int hi = end - 16 * last_real;
+                lm0 = byte_range_mask(0, hi);
+                lm1 = byte_range_mask(0, hi - 4);
+                lm2 = byte_range_mask(0, hi - 8);
+                lm3 = byte_range_mask(0, hi - 12);
+            }
+            auto load0 = [&]() -> uint4 {
+                uint4 v = __ldg(reinterpret_cast<const uint4*>(base));
+                const int hi = min(16, end);
+                v.x &= byte_range_mask(sh, hi);
+                v.y &= byte_range_mask(sh - 4, hi - 4);
+                v.z &= byte_range_mask(sh - 8, hi - 8);
+                v.w &= byte_range_mask(sh - 12, hi - 12);
+                return make_uint4(lower4(v.x), lower4(v.y), lower4(v.z), lower4(v.w));
+            };
+            auto load = [&](int ci) -> uint4 {                     // ci >= 1
+                if (ci > last_real) return make_uint4(0u, 0u, 0u, 0u);
+                uint4 v = __ldg(reinterpret_cast<const uint4*>(base + 16 * (int64_t)ci));
+                const unsigned all = ci == last_real ? 0u : ~0u;
+                return make_uint4(lower4(v.x & (lm0 | all)), lower4(v.y & (lm1 | all)), lower4(v.z & (lm2 | all)),
+                                  lower4(v.w & (lm3 | all)));
             };
 
             const int nch_eff = deferred ? 0 : nch;
-            uint4 cur = nch_eff > 0 ? load(0) : make_uint4(0u, 0u, 0u, 0u);
+            uint4 cur = nch_eff > 0 ? load0() : make_uint4(0u, 0u, 0u, 0u);
             int max_ch = nch_eff;
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) max_ch = max(max_ch, __shfl_xor_sync(FULL, max_ch, o));
-            for (int ci = 0; ci < max_ch; ++ci) {
+            // Finding the tokens is cheap and stays with the chunk: two 16-bit masks per chunk (where a token ends,
+            // where one starts) wait in a four-deep FIFO beside the ring.  The expensive part -- stop-word probe,
+            // murmur3, bucket -- runs in ROUNDS in which every lane with a token waiting takes one, so that it
+            // executes with most lanes busy instead of once per lane and token end.
+            bool c_in = false;                   // classification side: a token is open at the end of the last chunk
+            int c_start = 0;
+            int hc = 0, p_start = 0, pend = 0;   // processing side: chunk of the next token end, open token, ends waiting
+            unsigned h_end = 0u, h_start = 0u;
+            bool p_carry = false;
+            unsigned* ringl = ring + lane;
+
+            for (int ci = 0;; ++ci) {
+                const bool last = ci >= max_ch;
                 const bool active = ci < nch_eff && !deferred;
-                uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
-                if (active && ci + 1 < nch_eff) nxt = load(ci + 1);
-                unsigned m = 0u;
-                if (active) {
-                    m = tc_classify(cur, cl, cd, nxt.x, non_ascii);
-                    const int slot = (ci & 3) * 4;
-                    ring[(slot + 0) * 32 + lane] = cur.x;
-                    ring[(slot + 1) * 32 + lane] = cur.y;
-                    ring[(slot + 2) * 32 + lane] = cur.z;
-                    ring[(slot + 3) * 32 + lane] = cur.w;
-                }
-                __syncwarp();
-                // ---- tokens that end in this chunk, one per iteration and lane
-                const int cbase = ci << 4;
-                unsigned rest = m;
-                int pos = 0;
-                bool more = active;
-                while (__any_sync(FULL, more)) {
-                    int t_end = -1;
-                    if (more) {
-                        if (!in_tok) {
-                            if (rest == 0u) {
-                                more = false;
-                            } else {
-                                const int s = __ffs(rest) - 1;
-                                pos += s;
-                                rest >>= s;
-                                in_tok = true;
-                                tok_start = cbase + pos;
+                // ---- rounds: tokens whose bytes chunk ci is about to overwrite must go first; otherwise a round
+                //      runs while most lanes have a token waiting
+                for (;;) {
+                    const bool must = pend > 0 && (last || (active && (p_carry ? (p_start >> 4) : hc) <= ci - 4));
+                    const unsigned have = __ballot_sync(FULL, pend > 0);
+                    if (!(__any_sync(FULL, must || pend >= 12) || __popc(have) >= TC_ROUND_LANES)) break;
+                    if (pend > 0) {
+                        while (h_end == 0u) {                      // on to the next chunk that holds a token end
+                            if (h_start) {
+                                p_start = (hc << 4) + __ffs(h_start) - 1;
+                                p_carry = true;
                             }
+                            ++hc;
+                            const unsigned w = masks[(hc & 3) * 32 + lane];
+                            h_end = w & 0xffffu;
+                            h_start = w >> 16;
                         }
-                        if (more) {
-                            const int run = __ffs(~rest) - 1;          // rest has no bits at or above 16 - pos
-                            pos += run;
-                            rest = run >= 32 ? 0u : rest >> run;
-                            if (pos >= 16) {
-                                more = false;                          // the token goes on in the next chunk
-                            } else {
-                                t_end = cbase + pos;
-                                in_tok = false;
-                            }
+                        const int pe = __ffs(h_end) - 1;
+                        h_end &= h_end - 1u;
+                        int ps;
+                        if (p_carry) {
+                            ps = p_start;
+                            p_carry = false;
+                        } else {
+                            ps = (hc << 4) + __ffs(h_start) - 1;
+                            h_start &= h_start - 1u;
                         }
-                    }
-                    if (t_end >= 0) {
-                        const int ps = tok_start, plen = t_end - tok_start;
-                        if (ps < cbase - TC_BACK || plen > TC_BACK) {
-                            deferred = true;                           // longer than the ring holds
-                            more = false;
+                        const int plen = (hc << 4) + pe - ps;
+                        --pend;
+                        if (plen > TC_BACK) {
+                            deferred = true;                       // longer than the ring holds
                         } else if (plen >= p.min_token_length) {
+                            const unsigned* rs = ringl + ((ps >> 2) & (TC_RING - 1)) * 32;
+                            const unsigned first4 = __funnelshift_r(rs[0], rs[32], (ps & 3) * 8);
+                            const unsigned c0 = first4 & 0xffu;
                             bool keep = true;
-                            const unsigned c0 = tc_ring_byte(ring, lane, ps);
-                            if (c0 == '_') {                           // a run of '_' only is not a token
+                            if (c0 == '_') {                       // a run of '_' only is not a token
                                 keep = false;
-                                for (int q = ps; q < t_end; ++q) keep |= tc_ring_byte(ring, lane, q) != '_';
+                                for (int q = ps; q < ps + plen; ++q) keep |= tc_ring_byte(ring, lane, q) != '_';
                             }
                             if (keep && plen <= STOP_MAXLEN && (c0 - 'a') < 26u) {
-                                const unsigned c1 = plen > 1 ? tc_ring_byte(ring, lane, ps + 1) : 0u;
+                                const unsigned c1 = plen > 1 ? (first4 >> 8) & 0xffu : 0u;
                                 if ((stop_pre[stop_pre_index(c0, c1)] >> plen) & 1u)
-                                    keep = !tc_is_stop(stop, ring, lane, ps, plen);
+                                    keep = !tc_is_stop(ring, lane, ps, plen);
                             }
                             if (keep) {
                                 nohit = false;
@@ -443,21 +465,59 @@ text_cells_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
                                         for (int q = 0; q < ndup; ++q)
                                             if ((dups[q * 32 + lane] & 0xffffu) == (unsigned)bucket) at = q;
                                         if (at >= 0) {
-                                            const unsigned e = dups[at * 32 + lane];
-                                            if ((e >> 16) == 0xffffu) deferred = true;
-                                            else dups[at * 32 + lane] = e + 0x10000u;
+                                            const unsigned d = dups[at * 32 + lane];
+                                            if ((d >> 16) == 0xffffu) deferred = true;
+                                            else dups[at * 32 + lane] = d + 0x10000u;
                                         } else if (ndup < TC_DUPS) {
                                             dups[ndup * 32 + lane] = (unsigned)bucket | (2u << 16);
                                             ++ndup;
                                         } else {
                                             deferred = true;
                                         }
-                                        if (deferred) more = false;
                                     }
                                 }
                             }
                         }
+                        if (deferred) pend = 0;                    // nothing of a cell that is set aside counts
                     }
+                }
+                if (last) break;
+                uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
+                if (active && ci + 1 < nch_eff) nxt = load(ci + 1);
+                if (active) {
+                    const unsigned m = tc_classify(cur, cl, cd, nxt.x, non_ascii);
+                    // the ring: chunk c lives in rows 4 (c & 3) ..; rows 16 .. 20 repeat rows 0 .. 4, so that a token
+                    // is read from consecutive rows whatever its position
+                    const int slot = (ci & 3) * 4;
+                    unsigned* rw = ringl + slot * 32;
+                    rw[0] = cur.x;
+                    rw[32] = cur.y;
+                    rw[64] = cur.z;
+                    rw[96] = cur.w;
+                    if (slot == 0) {
+                        ringl[16 * 32] = cur.x;
+                        ringl[17 * 32] = cur.y;
+                        ringl[18 * 32] = cur.z;
+                        ringl[19 * 32] = cur.w;
+                    } else if (slot == 4) {
+                        ringl[20 * 32] = cur.x;
+                    }
+                    // position p ends a token when byte p - 1 is a token byte (or a token was open at the chunk's
+                    // start, p = 0) and byte p is not; a token starts where a token byte follows a byte that is none
+                    const unsigned ext = (m << 1) | (c_in ? 1u : 0u);
+                    const unsigned endm = ext & ~m & 0xffffu, startm = m & ~ext & 0xffffu;
+                    if (pend == 0) {
+                        hc = ci;
+                        h_end = endm;
+                        h_start = startm;
+                        p_carry = c_in;
+                        p_start = c_start;
+                    } else {
+                        masks[(ci & 3) * 32 + lane] = endm | (startm << 16);
+                    }
+                    pend += __popc(endm);
+                    c_in = (m >> 15) & 1u;
+                    if (c_in && startm) c_start = (ci << 4) + 31 - __clz(startm);
                 }
                 cur = nxt;
             }
@@ -502,8 +562,8 @@ text_cells_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
 #pragma unroll
                     for (int w = 0; w < TC_FW; ++w) {
                         const unsigned x = tc_transpose32(bm[w * 32 + lane], lane);
-                        acc1[w] += __popc(x & c1);
-                        acc0[w] += __popc(x & ~c1);
+                        hist[(TC_FW + w) * 32 + lane] += (unsigned short)__popc(x & c1);
+                        hist[w * 32 + lane] += (unsigned short)__popc(x & ~c1);
                     }
                     if (label && counted) {
                         for (int w = 0; w < TC_FW; ++w) {
@@ -557,8 +617,9 @@ text_cells_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
                 const int bkt = w * 32 + lane;
                 if (bkt < F && hashed) {
                     const int64_t v = (int64_t)j * F + bkt;
-                    if (acc0[w]) atomicAdd(&bucket_class_sum[v * p.nclasses], acc0[w]);
-                    if (acc1[w]) atomicAdd(&bucket_class_sum[v * p.nclasses + 1], acc1[w]);
+                    const unsigned a0 = hist[w * 32 + lane], a1 = hist[(TC_FW + w) * 32 + lane];
+                    if (a0) atomicAdd(&bucket_class_sum[v * p.nclasses], a0);
+                    if (a1) atomicAdd(&bucket_class_sum[v * p.nclasses + 1], a1);
                 }
             }
             if (lane == 0) {
@@ -639,13 +700,14 @@ text_rows_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
     extern __shared__ __align__(16) unsigned char tr_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nwarps = blockDim.x >> 5;
-    // per warp: word offsets [n_hashed * TC_FW] u16 | counts of a set-aside cell [TC_MAXF] u16
-    const size_t per_warp = ((size_t)ncols * TC_FW * 2 + TC_MAXF * 2 + 15) & ~size_t(15);
-    unsigned short* woff = reinterpret_cast<unsigned short*>(tr_smem + per_warp * warp);
-    unsigned short* counts = woff + (size_t)ncols * TC_FW;
+    // per warp: kept bitmap words [ncols * TC_FW] u32 | counts of a set-aside cell [TC_MAXF] u16 | word offsets u16
+    const size_t per_warp = ((size_t)ncols * TC_FW * 4 + TC_MAXF * 2 + (size_t)ncols * TC_FW * 2 + 15) & ~size_t(15);
+    unsigned* kept_words = reinterpret_cast<unsigned*>(tr_smem + per_warp * warp);
+    unsigned short* counts = reinterpret_cast<unsigned short*>(kept_words + (size_t)ncols * TC_FW);
+    unsigned short* woff = counts + TC_MAXF;
+
     const int F = p.num_features;
     const unsigned lt = (1u << lane) - 1u;
-    const int nwords = p.n_hashed * TC_FW;
     for (int64_t row = (int64_t)blockIdx.x * nwarps + warp; row < n; row += (int64_t)gridDim.x * nwarps) {
         unsigned* rrow = records + (size_t)row * ncols * TC_REC_WORDS;
         // ---- cells the fast path set aside are tokenised here, by one lane, and the bitmap of their record rebuilt
@@ -687,22 +749,37 @@ text_rows_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 __syncwarp();
             }
         }
-        // ---- size of the row: kept bits of every bitmap word, kept text lengths, kept null indicators
-        int total = 0;
+        // ---- a lane per cell loads the record (vector loads) and leaves the kept bits of its bitmap in shared memory
+        for (int j0 = 0; j0 < p.n_hashed; j0 += 32) {
+            const int j = j0 + lane;
+            if (j < p.n_hashed) {
+                const uint4* r4 = reinterpret_cast<const uint4*>(rrow + j * TC_REC_WORDS);
+                const uint4* k4 = reinterpret_cast<const uint4*>(keepw + j * TC_FW);
+                uint4* o4 = reinterpret_cast<uint4*>(kept_words + j * TC_FW);
+#pragma unroll
+                for (int q = 0; q < TC_FW / 4; ++q) {
+                    const uint4 v = r4[q], kq = k4[q];
+                    o4[q] = make_uint4(v.x & kq.x, v.y & kq.y, v.z & kq.z, v.w & kq.w);
+                }
+            }
+        }
+        __syncwarp();
+        // ---- a lane per bitmap word: entries before every word (consecutive lanes then write consecutive entries)
+        const int nwords = p.n_hashed * TC_FW;
+        int hash_total = 0;
         for (int w0 = 0; w0 < nwords; w0 += 32) {
             const int w = w0 + lane;
-            int c = 0;
-            if (w < nwords) c = __popc(rrow[(w / TC_FW) * TC_REC_WORDS + (w % TC_FW)] & keepw[w]);
+            const int c = w < nwords ? __popc(kept_words[w]) : 0;
             int incl = c;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int up = __shfl_up_sync(FULL, incl, o);
                 if (lane >= o) incl += up;
             }
-            if (w < nwords) woff[w] = (unsigned short)(total + incl - c);
-            total += __shfl_sync(FULL, incl, 31);
+            if (w < nwords) woff[w] = (unsigned short)(hash_total + incl - c);
+            hash_total += __shfl_sync(FULL, incl, 31);
         }
-        const int hash_total = total;
+        int total = hash_total;
         for (int j0 = 0; j0 < ncols; j0 += 32) {
             const int j = j0 + lane;
             const bool has = j < ncols && p.len_base >= 0 && rrow[j * TC_REC_WORDS + TC_FW + 1] > 0u &&
@@ -725,14 +802,12 @@ text_rows_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
         base = __shfl_sync(FULL, base, 0);
         if ((int64_t)base + total > capacity) continue;      // sizing call (capacity 0) or too small: nothing written
         __syncwarp();
-        // ---- entries of the hash block, ascending
         for (int w0 = 0; w0 < nwords; w0 += 32) {
             const int w = w0 + lane;
             if (w < nwords) {
-                const int j = w / TC_FW, k = w % TC_FW;
-                unsigned x = rrow[j * TC_REC_WORDS + k] & keepw[w];
+                unsigned x = kept_words[w];
                 int64_t at = (int64_t)base + woff[w];
-                const int32_t* np = newpos + (int64_t)j * F + k * 32;
+                const int32_t* np = newpos + (int64_t)(w / TC_FW) * F + (w % TC_FW) * 32;
                 while (x) {
                     const int bq = __ffs(x) - 1;
                     x &= x - 1u;
@@ -743,43 +818,48 @@ text_rows_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
             }
         }
         __syncwarp();
-        // ---- term frequencies > 1: the lists of the records, or the counts of a set-aside cell (tokenised again)
+        // ---- term frequencies > 1, a lane per cell from the record's list (a set-aside cell is patched below)
         if (!p.binary_freq) {
-            for (int j = 0; j < p.n_hashed; ++j) {
-                const unsigned head = rrow[j * TC_REC_WORDS + TC_FW];
-                if (head & TC_H_DEFER) {
-                    for (int q = lane; q < TC_MAXF; q += 32) counts[q] = 0;
-                    __syncwarp();
-                    if (lane == 0) {
-                        const TextColumn tc = cols[j];
-                        const int64_t a = tc.offsets[row], b = tc.offsets[row + 1];
-                        bool na = false, ovf = false;
-                        unsigned ls = 0u;
-                        tc_scalar_cell(tc.data + a, b - a, p, prefix + j * TH_PREFIX, p.prepend ? prefix_len[j] : 0, true,
-                                       counts, ls, na, ovf);
-                    }
-                    __syncwarp();
-                    for (int bkt = lane; bkt < F; bkt += 32) {
-                        const unsigned cnt = counts[bkt];
-                        const int w = j * TC_FW + (bkt >> 5);
-                        if (cnt > 1u && ((keepw[w] >> (bkt & 31)) & 1u)) {
-                            const unsigned below = rrow[j * TC_REC_WORDS + (bkt >> 5)] & keepw[w] & ((1u << (bkt & 31)) - 1u);
-                            out_val[(int64_t)base + woff[w] + __popc(below)] = (int32_t)cnt;
-                        }
-                    }
-                    __syncwarp();
-                } else {
-                    const int nd = (int)(head & 0xffu);
-                    if (lane < nd) {
-                        const unsigned e = rrow[j * TC_REC_WORDS + TC_FW + 3 + lane];
-                        const int bkt = (int)(e & 0xffffu);
-                        const int w = j * TC_FW + (bkt >> 5);
-                        if ((keepw[w] >> (bkt & 31)) & 1u) {
-                            const unsigned below = rrow[j * TC_REC_WORDS + (bkt >> 5)] & keepw[w] & ((1u << (bkt & 31)) - 1u);
-                            out_val[(int64_t)base + woff[w] + __popc(below)] = (int32_t)(e >> 16);
-                        }
+            for (int j0 = 0; j0 < p.n_hashed; j0 += 32) {
+                const int j = j0 + lane;
+                if (j < p.n_hashed) {
+                    const unsigned head = rrow[j * TC_REC_WORDS + TC_FW];
+                    const int nd = (head & TC_H_DEFER) ? 0 : (int)(head & 0xffu);
+                    for (int d = 0; d < nd; ++d) {
+                        const unsigned e = rrow[j * TC_REC_WORDS + TC_FW + 3 + d];
+                        const int bkt = (int)(e & 0xffffu), w = j * TC_FW + (bkt >> 5);
+                        const unsigned wword = kept_words[w];
+                        if ((wword >> (bkt & 31)) & 1u)
+                            out_val[(int64_t)base + woff[w] + __popc(wword & ((1u << (bkt & 31)) - 1u))] = (int32_t)(e >> 16);
                     }
                 }
+            }
+        }
+        __syncwarp();
+        // ---- set-aside cells: their term frequencies > 1 need the counts (tokenised again; rare)
+        if (!p.binary_freq && any_deferred) {
+            for (int j = 0; j < p.n_hashed; ++j) {
+                const unsigned head = rrow[j * TC_REC_WORDS + TC_FW];
+                if (!(head & TC_H_DEFER)) continue;
+                for (int q = lane; q < TC_MAXF; q += 32) counts[q] = 0;
+                __syncwarp();
+                if (lane == 0) {
+                    const TextColumn tc = cols[j];
+                    const int64_t a = tc.offsets[row], b = tc.offsets[row + 1];
+                    bool na = false, ovf = false;
+                    unsigned ls = 0u;
+                    tc_scalar_cell(tc.data + a, b - a, p, prefix + j * TH_PREFIX, p.prepend ? prefix_len[j] : 0, true,
+                                   counts, ls, na, ovf);
+                }
+                __syncwarp();
+                for (int bkt = lane; bkt < F; bkt += 32) {
+                    const unsigned cnt = counts[bkt];
+                    const int w = j * TC_FW + (bkt >> 5);
+                    const unsigned wword = kept_words[w];
+                    if (cnt > 1u && ((wword >> (bkt & 31)) & 1u))
+                        out_val[(int64_t)base + woff[w] + __popc(wword & ((1u << (bkt & 31)) - 1u))] = (int32_t)cnt;
+                }
+                __syncwarp();
             }
         }
         // ---- text lengths, then null indicators
