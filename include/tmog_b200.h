@@ -263,6 +263,17 @@ int tmog_text_stats_dev(const int64_t* col_desc, int ncols, int64_t n, const uin
 int tmog_text_stats_values_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* class_ids, int nclasses,
                         int clean_text, int slots, int max_distinct, void* tables, int32_t* flags, void* stream);
 
+/* TextStats.lengthCounts (SmartTextVectorizer.scala:85,207-299; decides Hash against Ignore through lengthStdDev <
+ * minLengthStdDev, :113-115): hist [ncols * nbins] += cells (tokens == 0: by the length of the cleaned cell,
+ * TextLengthType.FullEntry) or surviving tokens (tokens != 0: by token length, TextLengthType.Tokens) of every length,
+ * lengths >= nbins - 1 in the last bin; first_row [ncols * nbins] = min(row_base + row) over the rows a length was met
+ * in (the caller starts it at all-ones).  Neither array is cleared here: row chunks add up.  The reference's fold
+ * stops adding to a map that holds more than maxCardinality keys; the caller finds the row where that happens from
+ * first_row and asks again for the rows up to it. */
+int tmog_text_length_hist_dev(const int64_t* col_desc, int ncols, int64_t n, int64_t row_base, int clean_text,
+                              int tokens, int min_token_length, int nbins, uint64_t* hist, uint64_t* first_row,
+                              int32_t* flags, void* stream);
+
 /* Dictionary codes for the text columns SmartTextVectorizer pivots: codes[k][r] = table slot of row r's cleaned value
  * in column col_index[k] (-1 null), which tmog_pivot_count_dev / tmog_pivot_transform_dev then consume
  * (SmartTextVectorizerModel.transformFn's categoricalPivotFn, SmartTextVectorizer.scala:333-345).  flags (or NULL):

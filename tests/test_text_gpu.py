@@ -331,3 +331,94 @@ def test_non_ascii_text_in_a_capped_column_is_still_refused():
     with pytest.raises(ValueError, match="non-ASCII"):
         model = est.fit(batch)
         model.transform(batch).vectors[est.getOutput().name].to_scipy()
+
+
+def _ignore_route_data(seed=11, n=1000):
+    rng = np.random.default_rng(seed)
+    opt = lambda v: None if rng.random() < 0.2 else v   # noqa: E731
+    places = [" ".join("".join(rng.choice(list("abcdefghijklmnop"), size=rng.integers(3, 9))).capitalize()
+                       for _ in range(rng.integers(1, 4))) for _ in range(250)]
+    country = [opt(places[int(rng.integers(len(places)))]) for _ in range(n)]
+    categorical = [opt("ABCDEF"[int(rng.integers(6))]) for _ in range(n)]
+    text_id = [opt("%06d" % (40231 + int(rng.integers(1000)))) for _ in range(n)]
+    text = [opt("".join(rng.choice(list("abc xyz,. QRS"), size=rng.integers(0, 101)))) for _ in range(n)]
+    return [country, categorical, text_id, text], ["country", "categorical", "textId", "text"]
+
+
+@pytest.mark.parametrize("tokens,min_std,max_card", [(False, 0.5, 10), (True, 0.5, 300), (False, 0.5, 60)])
+@pytest.mark.parametrize("chunked", [False, True])
+def test_smart_text_ignore_route_and_text_lengths(tokens, min_std, max_card, chunked):
+    """SmartTextVectorizerTest.scala:213-280: machine-generated ids (fixed length) are ignored -- tokenised for their
+    null indicator and text length only; layout [pivot | hash | lengths (hashed, then ignored) | nulls]; lengthCounts
+    under the maxCardinality cap of the reference's fold (:231-235) and with textLengthType = Tokens (:85)."""
+    import scipy.sparse as sp
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch, VectorColumn
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    cols, names = _ignore_route_data()
+    methods, tops = V.smart_text_fit(cols, max_cardinality=max_card, top_k=3, min_support=10,
+                                     min_length_std_dev=min_std, tokenize_for_lengths=tokens)
+    if max_card == 10:
+        assert methods == [V.HASH, V.PIVOT, V.IGNORE, V.HASH]
+    exp = V.smart_text_transform(cols, names, methods, tops, num_features=5, track_nulls=True, track_text_len=True)
+    meta = V.smart_text_metadata(names, "Text", methods, tops, num_features=5, track_nulls=True, track_text_len=True)
+    est = SmartTextVectorizer().setMaxCardinality(min(max_card, 3000)).setTopK(3).setMinSupport(10).setNumFeatures(5) \
+        .setMinLengthStdDev(min_std).setTextLengthType("Tokens" if tokens else "FullEntry").setTrackTextLen(True) \
+        .setInput(*_feats(names))
+    if not chunked:
+        batch = _batch({nm: (F.TEXT, c) for nm, c in zip(names, cols)}, device="cuda")
+        model = est.fit(batch)
+        got = model.transform(batch).vectors[est.getOutput().name].to_scipy()
+    else:
+        from transmogrifai_b200.streaming import fit_stream, transform_stream
+        bounds = [0, 37, 400, 401, 1000]
+        chunks = [ColumnarBatch.from_columns({nm: (F.TEXT, c[a:b]) for nm, c in zip(names, cols)})
+                  for a, b in zip(bounds[:-1], bounds[1:])]
+        fit = fit_stream(chunks, est.getOutput())
+        model = fit.fitted[-1]
+        out = []
+        transform_stream(chunks, est.getOutput(), fit, lambda k, vec, parts: out.append(
+            VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy()))
+        got = sp.vstack(out).tocsr()
+    assert model.vectorizationMethods == methods
+    assert [list(t) for t in model.topValues] == [list(t) for t in tops]
+    assert got.shape == exp.shape and abs(got - sp.csr_matrix(exp)).max() == 0
+    cm = model.getMetadata().columns
+    assert [(c.parentFeatureName, c.grouping, c.indicatorValue, c.descriptorValue) for c in cm] == \
+        [(m.parent_names, m.grouping, m.indicator, m.descriptor) for m in meta]
+
+
+def test_smart_text_lengths_and_ignored_columns_through_sanity_checker():
+    """The text-length columns and the null indicators of ignored columns carry SanityChecker statistics like any other
+    column (fused sidecar), against the oracle."""
+    import scipy.sparse as sp
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    cols, names = _ignore_route_data(seed=12)
+    rng = np.random.default_rng(3)
+    y = (rng.random(len(cols[0])) < 0.4).astype(np.float64)
+    methods, tops = V.smart_text_fit(cols, max_cardinality=10, top_k=3, min_support=10, min_length_std_dev=0.5)
+    xo = sp.csr_matrix(V.smart_text_transform(cols, names, methods, tops, num_features=5, track_text_len=True))
+    metas = V.smart_text_metadata(names, "Text", methods, tops, num_features=5, track_nulls=True, track_text_len=True)
+    p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                       feature_feature_corr_level="off")
+    ref = S.sanity_fit(y, xo, metas, p, label_name="y")
+    data = {nm: (F.TEXT, c) for nm, c in zip(names, cols)}
+    data["y"] = (F.REALNN, y.tolist())
+    batch = _batch(data, response="y", device="cuda")
+    est = SmartTextVectorizer().setMaxCardinality(10).setTopK(3).setMinSupport(10).setNumFeatures(5) \
+        .setMinLengthStdDev(0.5).setTrackTextLen(True).setInput(*_feats(names))
+    label = F.FeatureBuilder.RealNN("y").asResponse()
+    checked = label.sanityCheck(est.getOutput(), removeBadFeatures=True, sampleLowerLimit=0, sampleUpperLimit=10 ** 9,
+                                featureFeatureCorrLevel="Off")
+    from transmogrifai_b200.dsl import fit_and_transform
+    out, fitted = fit_and_transform(batch, checked)
+    sm = checked.origin_stage.summary
+    assert sm.dropped == ref.dropped
+    np.testing.assert_allclose(sm.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(sm.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+    assert np.array_equal(sm.min, ref.col_stats.min) and np.array_equal(sm.max, ref.col_stats.max)
+    np.testing.assert_allclose(sm.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12, equal_nan=True)
+    got = out.vectors[checked.name].to_scipy()
+    exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
+    assert got.shape == exp.shape and abs(got - exp).max() == 0

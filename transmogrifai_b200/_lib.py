@@ -68,6 +68,7 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_text_stats_table_bytes": [_int, _int, C.POINTER(_sz)],
     "tmog_text_stats_dev": [_p, _int, _i64, _p, _int, _int, _int, _int, _p, _p, _p],
     "tmog_text_stats_values_dev": [_p, _int, _i64, _p, _int, _int, _int, _int, _p, _p, _p],
+    "tmog_text_length_hist_dev": [_p, _int, _i64, _i64, _int, _int, _int, _int, _p, _p, _p, _p],
     "tmog_text_codes_dev": [_p, _p, _int, _i64, _int, _int, _p, _p, _i64, _p, _p],
     "tmog_text_hash_scratch_bytes": [_i64, C.POINTER(_sz)],
     "tmog_text_hash_scratch_bytes2": [_i64, _int, _p, _int, C.POINTER(_sz)],

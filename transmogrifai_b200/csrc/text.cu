@@ -1612,6 +1612,21 @@ static int text_hash_dispatch(ThArgs& a) {
     return CELLS ? th_run<true>(a) : th_run<false>(a);
 }
 
+extern "C" int tmog_text_length_hist_dev(const int64_t* col_desc, int ncols, int64_t n, int64_t row_base, int clean_text,
+                                         int tokens, int min_token_length, int nbins, uint64_t* hist,
+                                         uint64_t* first_row, int32_t* flags, void* stream) {
+    TMOG_REQUIRE(ncols >= 0 && n >= 0 && nbins >= 2 && row_base >= 0, "bad shape");
+    if (ncols == 0 || n == 0) return TMOG_OK;
+    TMOG_REQUIRE(col_desc && hist && first_row && flags, "NULL argument");
+    if (int rc = upload_stop_words()) return rc;
+    const int gx = (int)std::max<int64_t>(1, std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 8));
+    text_length_hist_kernel<<<dim3(gx, ncols), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const TextColumn*>(col_desc), ncols, n, row_base, clean_text, tokens, min_token_length, nbins,
+        reinterpret_cast<unsigned long long*>(hist), reinterpret_cast<unsigned long long*>(first_row), flags);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
 extern "C" int tmog_text_hash_scratch_bytes2(int64_t n, int ncols, const int32_t* params, int sparse_out, size_t* bytes) {
     TMOG_REQUIRE(bytes != nullptr && params != nullptr && n >= 0 && n < 0x7fffffffLL && ncols >= 0, "bad arguments");
     size_t need = 0;

@@ -676,6 +676,41 @@ text_cells_slow_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n
     }
 }
 
+// TextStats.lengthCounts (SmartTextVectorizer.scala:207-299): per column a histogram of the cell lengths -- the length of
+// the cleaned cell (TextLengthType.FullEntry) or the lengths of the cell's tokens (Tokens) -- and the first row every
+// length was met in (the reference's fold stops adding once the map holds more than maxCardinality lengths: the
+// caller finds that row from the first rows and asks again for the rows up to it).  Lengths >= nbins - 1 share the
+// last bin.  A thread per cell.
+__global__ void __launch_bounds__(256)
+text_length_hist_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, int64_t row_base, int clean, int tokens,
+                        int min_token_length, int nbins, unsigned long long* __restrict__ hist,
+                        unsigned long long* __restrict__ first_row, int* __restrict__ flags) {
+    const int c = blockIdx.y;
+    const TextColumn tc = cols[c];
+    unsigned long long* h = hist + (size_t)c * nbins;
+    unsigned long long* f = first_row + (size_t)c * nbins;
+    bool non_ascii = false;
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+        if (!cell_valid(tc, r)) continue;
+        const int64_t a = tc.offsets[r], b = tc.offsets[r + 1];
+        const uint8_t* s = tc.data + a;
+        if (!tokens) {
+            const int m = clean_length_cell(s, b - a, clean != 0, non_ascii);
+            const int bin = min(m, nbins - 1);
+            atomicAdd(&h[bin], 1ull);
+            atomicMin(&f[bin], (unsigned long long)(row_base + r));
+        } else {
+            tc_scalar_tokens(s, b - a, min_token_length, non_ascii, [&](int64_t k, int plen) {
+                if (tc_scalar_is_stop(s, k, plen)) return;
+                const int bin = min(plen, nbins - 1);
+                atomicAdd(&h[bin], 1ull);
+                atomicMin(&f[bin], (unsigned long long)(row_base + r));
+            });
+        }
+    }
+    if (non_ascii) flags[0] = 1;
+}
+
 // keepw [j * TC_FW + k]: the buckets of bitmap word k of column j whose vector column SanityChecker kept
 __global__ void tc_keep_words_kernel(const int32_t* __restrict__ newpos, int n_hashed, int F, unsigned* __restrict__ keepw) {
     const int w = blockIdx.x * blockDim.x + threadIdx.x;

@@ -18,7 +18,7 @@ from .. import dist as D
 from .. import features as F
 from .. import runtime as R
 from ..columnar import batch_key, ColumnarBatch, LazyPart, OneHotPart, SparseRowsPart, TextBlock, VectorColumn, encode_strings
-from ..metadata import NullString, OpVectorColumnMetadata, OpVectorMetadata, OtherString, feature_column
+from ..metadata import NullString, OpVectorColumnMetadata, OpVectorMetadata, OtherString, TextLenString, feature_column
 from ..stats import LabelInfo, VectorStats
 from .base import OpEstimator, OpModel
 from .numeric import label_info_dev, label_moments_dev, stats_from_sums_continuous
@@ -127,6 +127,7 @@ class SmartTextVectorizer(OpEstimator):
         self.cleanText = True
         self.trackNulls = True
         self.trackTextLen = False
+        self.textLengthType = "FullEntry"
         self.unseenName = OtherString
         self.numFeatures = 512
         self.hashSpaceStrategy = "Auto"
@@ -175,8 +176,13 @@ class SmartTextVectorizer(OpEstimator):
         return self
 
     def setTrackTextLen(self, v):  # noqa: N802
-        if v:
-            raise NotImplementedError("trackTextLen is not on the GPU path (default false)")
+        self.trackTextLen = bool(v)
+        return self
+
+    def setTextLengthType(self, v):  # noqa: N802  (TextLengthType: FullEntry | Tokens, SmartTextVectorizer.scala:410-417)
+        if str(v).lower() not in ("fullentry", "tokens"):
+            raise ValueError(f"requirement failed: textLengthType given invalid value {v}")
+        self.textLengthType = "Tokens" if str(v).lower() == "tokens" else "FullEntry"
         return self
 
     def setNumFeatures(self, v):  # noqa: N802
@@ -222,6 +228,7 @@ class SmartTextVectorizer(OpEstimator):
         dev = batch.on_device("texts", names, block)
         n, ncols = batch.n, len(names)
         self._prefix = {}                          # cleaned first rows of the columns past the cap, of THIS batch
+        self._length_sources = lambda: [(dev, n, D.world()[0] << 40)]
         # 1. TextStats per column (merged over the ranks like the reference's reduce over partitions)
         values, totals = self._text_stats(dev, n)
         values = self._merge_text_stats(values, dev, n)
@@ -341,6 +348,15 @@ class SmartTextVectorizer(OpEstimator):
         for per_rank in D.all_gather_object(res):
             for c, vc in per_rank.items():
                 merged[c] = vc
+        def sources():
+            key = rank << 40
+            for chunk in chunks:
+                block = chunk.texts(names)
+                yield chunk.on_device("texts", names, block), chunk.n, key
+                key += chunk.n
+                chunk.__dict__.pop("_dev_cache", None)
+
+        self._length_sources = sources
         methods, tops = [], []
         for c in range(ncols):
             m, top = self._decide(merged[c], 0, None, c, 0)
@@ -468,6 +484,55 @@ class SmartTextVectorizer(OpEstimator):
                 return vc
             rows *= 4
 
+    LENGTH_BINS = 4096
+
+    def _length_std_dev(self, c: int) -> float:
+        """TextStats.lengthStdDev of column c (population standard deviation of lengthCounts, :207-220) over the row
+        sources the current fit registered in self._length_sources: a callable yielding (device TextBlock, rows,
+        row key of its first row) in fold order."""
+        lengths = self._length_counts(c)
+        size = sum(lengths.values())
+        if size == 0:
+            return float("nan")
+        mean = sum(k * v for k, v in lengths.items()) / size
+        var = sum(v * (k - mean) * (k - mean) for k, v in lengths.items()) / size
+        return float(np.sqrt(var))
+
+    def _length_counts(self, c: int) -> Dict[int, int]:
+        nb = self.LENGTH_BINS
+        tokens = int(self.textLengthType == "Tokens")
+        big = 1 << 62
+
+        def scan(limit_key: Optional[int]):
+            hist = torch.zeros(nb, dtype=torch.int64, device="cuda")
+            first = torch.full((nb,), big, dtype=torch.int64, device="cuda")
+            flags = torch.zeros(4, dtype=torch.int32, device="cuda")
+            for dev, n, key0 in self._length_sources():
+                m = n if limit_key is None else max(0, min(n, limit_key - key0 + 1))
+                if m > 0:
+                    desc = _col_desc(dev.rows([c]))
+                    L.call("tmog_text_length_hist_dev", desc.data_ptr(), 1, m, key0, int(self.cleanText), tokens,
+                           int(self.minTokenLength), nb, hist.data_ptr(), first.data_ptr(), flags.data_ptr(), R.stream())
+                if limit_key is not None and key0 + n > limit_key:
+                    break
+            if int(flags[0].item()) and self.cleanText:
+                raise ValueError(NON_ASCII_CLEAN)
+            return D.allreduce_sum(hist.cpu().numpy()), -D.allreduce_max(-first.cpu().numpy())
+
+        h, f = scan(None)
+        if h[nb - 1] > 0:
+            raise NotImplementedError(f"text lengths of {nb - 1} and more with minLengthStdDev > 0")
+        used = np.nonzero(h)[0]
+        if len(used) > self.maxCardinality:
+            if tokens:
+                raise NotImplementedError("textLengthType = Tokens with more distinct token lengths than maxCardinality "
+                                          "(the reference's per-row fold is order dependent there)")
+            # the fold stops adding after the row that brought the map past maxCardinality lengths (:231-235)
+            r_star = int(np.sort(f[used])[self.maxCardinality])
+            h, _ = scan(r_star)
+            used = np.nonzero(h)[0]
+        return {int(k): int(h[k]) for k in used}
+
     def _decide(self, vc: Optional[Dict[str, int]], nonnull: int, dev: TextBlock, c: int, n: int
                 ) -> Tuple[str, List[str]]:
         """SmartTextVectorizer.fitFn :93-120"""
@@ -485,8 +550,8 @@ class SmartTextVectorizer(OpEstimator):
             method = PIVOT
         elif card <= self.maxCardinality:
             method = PIVOT
-        elif self.minLengthStdDev > 0:
-            raise NotImplementedError("minLengthStdDev > 0 (the Ignore route) is not on the GPU path")
+        elif self.minLengthStdDev > 0 and self._length_std_dev(c) < self.minLengthStdDev:
+            method = IGNORE                                     # reads like machine-generated ids (:113-115)
         else:
             method = HASH
         vals = list(filtered)
@@ -542,6 +607,9 @@ class SmartTextVectorizerModel(OpModel):
                                  lay.num_features))
                 else:
                     runs += [(feature_column(f.name, f.type_name), lay.num_features) for f in hf]
+            if self.shouldTrackLen:             # :168-172: lengths of the hashed columns, then of the ignored ones
+                runs += [(OpVectorColumnMetadata((feats[j].name,), (feats[j].type_name,), grouping=feats[j].name,
+                                                 descriptorValue=TextLenString), 1) for j in lay.text_idx]
             # the reference appends the null-indicator columns to the metadata whether or not nulls are tracked
             # (SmartTextVectorizer.scala:176-183); kept as is, SanityChecker then rejects the width mismatch
             runs += [(feature_column(feats[j].name, feats[j].type_name, is_null=True), 1) for j in lay.text_idx]
