@@ -45,10 +45,18 @@ def _make_data(n):
             "t1": (F.TEXT, t1), "t2": (F.TEXT, t2), "y": (F.REALNN, y.tolist())}, y
 
 
-def _worker(rank, size, port, q):
+def _init(rank, size, port, backend):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
-    dist.init_process_group("gloo", rank=rank, world_size=size)
+    if backend == "nccl":                       # a GPU per rank, the exchanges over NCCL
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=size, device_id=torch.device("cuda", rank))
+    else:
+        dist.init_process_group("gloo", rank=rank, world_size=size)
+
+
+def _worker(rank, size, port, q, backend="gloo"):
+    _init(rank, size, port, backend)
     try:
         from oracle import sanity as S
         from oracle import vectorizers as V
@@ -125,11 +133,11 @@ def _worker(rank, size, port, q):
         dist.destroy_process_group()
 
 
-def test_two_ranks_all_types_match_oracle():
+def _run(target, *extra):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=target, args=(r, 2, port, q) + extra) for r in range(2)]
     for p in procs:
         p.start()
     res = [q.get(timeout=600) for _ in procs]
@@ -138,10 +146,103 @@ def test_two_ranks_all_types_match_oracle():
     assert sorted(res) == [(0, "ok"), (1, "ok")], "\n".join(str(r[1]) for r in res)
 
 
+def test_two_ranks_all_types_match_oracle():
+    _run(_worker)
+
+
+needs_two_gpus = pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs (NCCL)")
+
+
+@needs_two_gpus
+def test_two_ranks_over_nccl_all_types_match_oracle():
+    """The same rank merges with a GPU per rank and NCCL as the transport (what bench.py --gpus N runs)."""
+    _run(_worker, "nccl")
+
+
+def _worker_streamed(rank, size, port, q, backend="gloo"):
+    """Every rank streams its row shard in three chunks (own dictionaries per chunk): passes 0 / 1 fold the chunks, the
+    accumulators are merged over the ranks once, pass 2 transforms chunk by chunk."""
+    _init(rank, size, port, backend)
+    try:
+        import scipy.sparse as sp
+        from oracle import sanity as S
+        from oracle import vectorizers as V
+        from transmogrifai_b200 import dist as D
+        from transmogrifai_b200 import features as F
+        from transmogrifai_b200.columnar import ColumnarBatch, VectorColumn
+        from transmogrifai_b200.dsl import transmogrify
+        from transmogrifai_b200.streaming import fit_and_transform_stream
+        n = 5000
+        data, y = _make_data(n)
+        data.pop("i0")
+        lo, hi = D.shard_rows(n, rank, size)
+        cuts = [lo, lo + (hi - lo) // 5, lo + (hi - lo) // 2, hi]
+        chunks = [ColumnarBatch.from_columns({k: (t, v[a:b]) for k, (t, v) in data.items()}, response="y")
+                  for a, b in zip(cuts[:-1], cuts[1:])]
+        FB = F.FeatureBuilder
+        feats = [FB.Text("t0").asPredictor(), FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(),
+                 FB.RealNN("nn").asPredictor(), FB.PickList("p0").asPredictor(), FB.Text("t1").asPredictor(),
+                 FB.Text("t2").asPredictor()]
+        label = FB.RealNN("y").asResponse()
+        checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
+                                    sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
+        out = []
+        res = fit_and_transform_stream(chunks, checked, lambda k, vec, parts: out.append(
+            VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy()))
+        est = checked.origin_stage
+        col = lambda k: data[k][1]   # noqa: E731
+        xb = V.binary_vectorizer_transform([col("b0")])
+        tops = V.pivot_fit([col("p0")], 20, 10, True)
+        xp = V.pivot_transform([col("p0")], tops, True, True)
+        fills = V.real_vectorizer_fit([col("r0")])
+        xr = V.real_vectorizer_transform([col("r0")], fills, True)
+        xn = V.realnn_vectorizer_transform([col("nn")])
+        tcols, tnames = [col("t0"), col("t1"), col("t2")], ["t0", "t1", "t2"]
+        methods, ttops = V.smart_text_fit(tcols, max_cardinality=30, top_k=20, min_support=10)
+        xt = V.smart_text_transform(tcols, tnames, methods, ttops, num_features=512)
+        xo, metas = V.combine(
+            [xb, xp, xr, xn, xt],
+            [V.numeric_metadata(["b0"], "Binary", True), V.pivot_metadata(["p0"], "PickList", tops, True),
+             V.numeric_metadata(["r0"], "Real", True), V.numeric_metadata(["nn"], "RealNN", False),
+             V.smart_text_metadata(tnames, "Text", methods, ttops, 512, True)])
+        p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                           feature_feature_corr_level="off")
+        ref = S.sanity_fit(y, sp.csr_matrix(xo), metas, p, label_name="y")
+        assert est.summary.count == n
+        assert est.summary.names[:-1] == [m.col_name() for m in metas]
+        assert est.summary.dropped == ref.dropped
+        assert res.fitted[-1].indicesToKeep == ref.indices_to_keep
+        np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300)
+        np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+        assert np.array_equal(est.summary.min, ref.col_stats.min) and np.array_equal(est.summary.max, ref.col_stats.max)
+        np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                                   equal_nan=True)
+        got_g = {g.group: g for g in est.summary.categoricalStats}
+        for g in ref.cat_stats:
+            assert np.array_equal(got_g[g.group].contingencyMatrix, g.contingency_matrix)
+            np.testing.assert_allclose(got_g[g.group].cramersV, g.cramers_v, rtol=1e-9, equal_nan=True)
+        got = sp.vstack(out).tocsr()
+        exp = sp.csr_matrix(xo)[lo:hi][:, ref.indices_to_keep]
+        assert got.shape == exp.shape and abs(got - exp).max() < 1e-12
+        q.put((rank, "ok"))
+    except Exception:  # pragma: no cover
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_streamed_chunks_match_oracle():
+    _run(_worker_streamed)
+
+
+@needs_two_gpus
+def test_two_ranks_over_nccl_streamed_chunks_match_oracle():
+    _run(_worker_streamed, "nccl")
+
+
 def _worker_sampled(rank, size, port, q):
-    os.environ["MASTER_ADDR"] = "127.0.0.1"
-    os.environ["MASTER_PORT"] = str(port)
-    dist.init_process_group("gloo", rank=rank, world_size=size)
+    _init(rank, size, port, "gloo")
     try:
         from oracle import sanity as S
         from oracle import vectorizers as V
@@ -202,13 +303,4 @@ def _worker_sampled(rank, size, port, q):
 
 def test_two_ranks_sampled_sanity_checker_matches_oracle():
     """fraction() < 1 over two row shards: every rank samples its shard, the statistics of the samples are merged."""
-    ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    port = _free_port()
-    procs = [ctx.Process(target=_worker_sampled, args=(r, 2, port, q)) for r in range(2)]
-    for p in procs:
-        p.start()
-    res = [q.get(timeout=600) for _ in procs]
-    for p in procs:
-        p.join(timeout=60)
-    assert sorted(res) == [(0, "ok"), (1, "ok")], "\n".join(str(r[1]) for r in res)
+    _run(_worker_sampled)

@@ -45,15 +45,27 @@ def _both(n, ncols, seed):
     L.call("tmog_real_fit_partials_noalloc_dev", x.data_ptr(), ld, vw.data_ptr(), nw, y.data_ptr(), n, ncols,
            shifts.data_ptr(), got.data_ptr(), st)
     torch.cuda.synchronize()
-    return got.cpu().numpy().reshape(-1, L.REAL_NSTAT), ref.cpu().numpy().reshape(-1, L.REAL_NSTAT)
+    # the same sums in numpy from the raw inputs, so that a fault shared by both entry points would show too
+    xs, ys, sh = x[:, :n].cpu().numpy(), y[:n].cpu().numpy(), shifts.cpu().numpy()
+    ok = np.unpackbits(vw.cpu().numpy().view(np.uint8), axis=1, bitorder="little")[:, :n].astype(bool)
+    e = ys - sh[ncols]
+    exp = np.zeros((ncols + 1, L.REAL_NSTAT))
+    for j in range(ncols):
+        d = xs[j][ok[j]] - sh[j]
+        exp[j] = [ok[j].sum(), d.sum(), (d * d).sum(), (d * e[ok[j]]).sum(), e[ok[j]].sum(),
+                  xs[j][ok[j]].min(), xs[j][ok[j]].max(), n]
+    exp[ncols] = [n, e.sum(), (e * e).sum(), (e * e).sum(), e.sum(), ys.min(), ys.max(), n]
+    return (got.cpu().numpy().reshape(-1, L.REAL_NSTAT), ref.cpu().numpy().reshape(-1, L.REAL_NSTAT), exp)
 
 
 def test_noalloc_fit_matches_the_scratch_taking_entry_point_twice_in_a_row():
     # second call: other shape and data, so stale scratch from the first call would show
     for n, ncols, seed in ((300_001, 40, 1), (70_000, 9, 2)):
-        got, ref = _both(n, ncols, seed)
+        got, ref, exp = _both(n, ncols, seed)
         assert np.array_equal(got[:, [0, 5, 6, 7]], ref[:, [0, 5, 6, 7]])          # counts, min, max, rows: exact
         np.testing.assert_allclose(got[:, 1:5], ref[:, 1:5], rtol=1e-9, atol=1e-6)  # sums: as test_real_gpu.py
+        assert np.array_equal(got[:, [0, 5, 6, 7]], exp[:, [0, 5, 6, 7]])          # and against numpy on the raw inputs
+        np.testing.assert_allclose(got[:, 1:5], exp[:, 1:5], rtol=1e-9, atol=1e-6)
 
 
 def test_noalloc_fit_rejects_blocks_beyond_its_built_in_scratch():

@@ -7,46 +7,9 @@
 
 #include "common.cuh"
 
-namespace tmog {
-
-struct DevBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    int ensure(size_t bytes) {
-        if (bytes <= cap) return TMOG_OK;
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-        TMOG_CUDA(cudaMalloc(&p, bytes));
-        cap = bytes;
-        return TMOG_OK;
-    }
-    void release() {
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-    }
-};
-
-}  // namespace tmog
+#include "host_ctx.cuh"
 
 using namespace tmog;
-
-struct tmog_ctx {
-    int device = 0;
-    cudaStream_t s_h2d = nullptr, s_cmp = nullptr, s_d2h = nullptr;
-    // resident copy of the last fitted real block (lets transform skip the second upload)
-    DevBuf r_values, r_valid, r_label, classes, class_ids, null_counts;
-    const void* r_key = nullptr;
-    int64_t r_n = 0, r_ld = 0, r_ldv = 0;
-    int r_ncols = 0;
-    bool r_has_valid = false;
-    // streaming buffers
-    DevBuf in_values[2], in_valid[2], out_block[2];
-    DevBuf scratch, shifts, partials, fills, pos;
-    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_cmp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
-    cudaEvent_t ev_lbl = nullptr;
-};
 
 static int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
 
@@ -96,6 +59,17 @@ extern "C" int tmog_ctx_destroy(tmog_ctx* c) {
     c->partials.release();
     c->fills.release();
     c->pos.release();
+    for (int i = 0; i < 2; ++i) {
+        c->s_in[i].release();
+        c->s_aux[i].release();
+        c->s_out[i].release();
+    }
+    c->s_counts.release();
+    c->s_desc.release();
+    c->s_pos.release();
+    c->s_flags.release();
+    c->s_records.release();
+    if (c->pinned) cudaFreeHost(c->pinned);
     if (c->s_h2d) cudaStreamDestroy(c->s_h2d);
     if (c->s_cmp) cudaStreamDestroy(c->s_cmp);
     if (c->s_d2h) cudaStreamDestroy(c->s_d2h);

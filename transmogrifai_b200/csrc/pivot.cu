@@ -6,7 +6,8 @@
 // alike share an id); value ids are 1..K_c and the null "value" has id 0, so that the usually frequent null bin
 // always sits in the shared-memory part of the histogram.
 //
-//   fit        counts[col][id][class] (u64) -- vocabulary, top-K, contingency matrix, Cramer's V, column moments and
+//   fit        counts[col][id][class] (u32 bins per call: at most 2^32 - 1 rows; callers widen them to int64 when they
+//              add up row chunks or ranks) -- vocabulary, top-K, contingency matrix, Cramer's V, column moments and
 //              label correlations of every one-hot column all derive from this one table
 //   transform  out[row][col] = output index of the row's value (top-K position, OTHER, or the null indicator),
 //              row-major int32 (one-hot: the value 1.0 is implicit), -1 where SanityChecker dropped the column

@@ -10,6 +10,8 @@
 // writes 16 bytes per (row, column) when null indicators are tracked.
 #include <math.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace tmog {
@@ -1093,7 +1095,9 @@ extern "C" int tmog_integral_transform_select_dev(const int64_t* values, int64_t
 //     (296 on a B200), i.e. at most 220 columns per call on a B200; wider blocks are rejected with TMOG_EINVAL and a
 //     message that names the limit -- split the block, partials of column sub-blocks are independent.
 //   * the first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
-//     current).  Make that first call outside any stream capture.
+//     current) and keeps it (an atomic per device: host threads may race on the first call, they store the same
+//     value).  Make that first call outside any stream capture.  cudaDeviceReset invalidates the kept address: a
+//     process that resets a device must not call this entry point on it afterwards.
 //   * every call on a device uses the same array.  Nothing in it has to start at zero (each CTA rewrites its whole
 //     slot before the reduce kernel reads it) and a call leaves its partials behind, but two calls that overlap on
 //     the GPU -- different streams, or different host threads on the same device -- race on it.  Serialise them.
@@ -1105,7 +1109,7 @@ static __device__ __align__(256) double g_noalloc_fit_scratch[TMOG_NOALLOC_SCRAT
 
 namespace {
 constexpr int NOALLOC_MAX_DEVICES = 64;
-double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+std::atomic<double*> g_noalloc_ptr[NOALLOC_MAX_DEVICES];
 
 // Device address of the scratch array on the CURRENT device.  In host code the symbol's name is only a stand-in;
 // the kernel must be given the address cudaGetSymbolAddress returns.
@@ -1113,13 +1117,15 @@ int noalloc_scratch(double** out) {
     int dev = 0;
     TMOG_CUDA(cudaGetDevice(&dev));
     TMOG_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "device index %d not supported", dev);
-    if (g_noalloc_ptr[dev] == nullptr) {
+    double* known = g_noalloc_ptr[dev].load(std::memory_order_relaxed);
+    if (known == nullptr) {
         void* p = nullptr;
         TMOG_CUDA(cudaGetSymbolAddress(&p, g_noalloc_fit_scratch));
         TMOG_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
-        g_noalloc_ptr[dev] = static_cast<double*>(p);   // idempotent: racing first calls store the same value
+        known = static_cast<double*>(p);
+        g_noalloc_ptr[dev].store(known, std::memory_order_relaxed);   // racing first calls store the same value
     }
-    *out = g_noalloc_ptr[dev];
+    *out = known;
     return TMOG_OK;
 }
 }  // namespace

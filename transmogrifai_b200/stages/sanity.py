@@ -355,7 +355,11 @@ class SanityChecker(OpEstimator):
             a, b = plan.row_offsets[g], plan.row_offsets[g] + plan.rows[g]
             m = mats[a:b]
             m = m[m.sum(axis=1) != 0.0]
-            m = m[:, m.sum(axis=0) != 0.0] if len(m) else m
+            if len(m) and not (m.sum(axis=0) != 0.0).all():
+                # filterEmpties drops the label column, and the reference then builds its 2 x numLabels matrices from
+                # rows that are too short: DenseMatrix's size check fails (OpStatistics.scala:352-357)
+                raise ValueError(f"requirement failed: The values array must have length {2 * m.shape[1]}: no row of "
+                                 f"the MultiPickList group '{plan.groups[g][0]}' holds one of the label values")
             best = None
             for row in m:
                 two = np.ascontiguousarray(np.stack([row, counts[:len(row)] - row]))
