@@ -580,6 +580,61 @@ int tmog_real_transform_host(tmog_ctx* ctx, const double* values, int64_t ld, co
                              int64_t n, int ncols, const double* fills, int track_nulls, int64_t chunk_rows,
                              const int32_t* keep, int nkeep, double* out, int64_t out_ld, int64_t out_col0);
 
+/* ---- string paths over host buffers ------------------------------------------------------------------------------
+ * One call per exported partition does what the reference's estimator does in fit(Dataset) and its model in
+ * transform(Dataset) (features/src/main/scala/com/salesforce/op/stages/base/sequence/SequenceEstimator.scala:91-106):
+ * rows are staged through the device in chunks (the copy of chunk k + 1 under the kernel of chunk k) and the driver-side
+ * finishing runs on host threads inside the library -- no allocation, table building or threading is left to the caller.
+ *
+ * tmog_pivot_fit_host replaces OpTextPivotVectorizer.fitFn (C/stages/impl/feature/OpOneHotVectorizer.scala:75-124,
+ * 219-225) fused with SanityChecker.categoricalTests' per-label sums (C/stages/impl/preparators/SanityChecker.scala:
+ * 265-272):
+ *   codes [ncols][ld] int32 (HOST, pinned for full speed; < 0 = null), per column its dictionary in Arrow utf8 layout
+ *   (dict_data[j], dict_offsets[j] int64 [ncodes[j] + 1]); label f64 [n] or NULL (then one class);
+ *   max_classes <= 255: labels with more distinct values are refused here (use the *_dev entry points).
+ * Outputs: *nclasses_out, classes_out [max_classes], class_counts_out [max_classes] (may be NULL);
+ *   per column j: n_top[j], the vocabulary in top_data + j * (top_capacity / ncols) with offsets
+ *   top_offsets + j * (top_k + 1) (count desc, then String.compareTo), code_to_out (concatenated, ncodes[j] entries per
+ *   column: top position or n_top[j] = OTHER) and out_class_counts + j * (top_k + 2) * nclasses (rows: top values,
+ *   OTHER, null) -- everything tmog_pivot_column_finish yields, for all columns, cleaned and ranked on host threads
+ *   while the count kernel runs. */
+int tmog_pivot_fit_host(tmog_ctx* ctx, const int32_t* codes, int64_t ld, int64_t n, int ncols,
+                        const uint8_t* const* dict_data, const int64_t* const* dict_offsets, const int64_t* ncodes,
+                        const double* label, int64_t chunk_rows, int clean_text, int top_k, int64_t min_support,
+                        int max_classes, int* nclasses_out, double* classes_out, uint64_t* class_counts_out, int* n_top,
+                        uint8_t* top_data, int64_t top_capacity, int64_t* top_offsets, int32_t* code_to_out,
+                        int64_t* out_class_counts);
+
+/* Replaces OneHotModelFun.pivotFn + reindex (OpOneHotVectorizer.scala:416-437, Transmogrifier.scala:437-449) over host
+ * codes: out [n][out_ld] int32 (HOST), columns [out_col0, out_col0 + ncols) = index of each column's 1.0 inside the
+ * pivot block (column blocks of n_top[j] + 1 (+ 1 with track_nulls) in order), mapped through newpos [block width]
+ * when given (SanityCheckerModel's removeFeatures: -1 = dropped).  The position tables are built here from code_to_out. */
+int tmog_pivot_transform_host(tmog_ctx* ctx, const int32_t* codes, int64_t ld, int64_t n, int ncols, const int64_t* ncodes,
+                              const int32_t* code_to_out, const int* n_top, int track_nulls, const int32_t* newpos,
+                              int64_t chunk_rows, int32_t* out, int64_t out_ld, int64_t out_col0);
+
+/* tmog_text_hash_stats_dev over host text columns (Arrow utf8 per column: data[j], offsets[j] int64 [n + 1] starting at
+ * 0, valid[j] bitmap or NULL): the SanityChecker sums of the hashed block and the null indicators of one partition
+ * (C/stages/impl/feature/SmartTextVectorizer.scala:333-371, OPCollectionHashingVectorizer.scala:244-272), returned in
+ * plain form per vector index (w = null_base + ncols entries): bucket_class_sum [w * nclasses] = sum of term
+ * frequencies per label class, bucket_rows [w] = rows holding the index, bucket_sq_sum [w] = sum of squared values,
+ * bucket_max / bucket_min [w] = largest / smallest value among the rows holding it.  params as in the _dev call. */
+int tmog_text_hash_stats_host(tmog_ctx* ctx, int ncols, int64_t n, const uint8_t* const* data,
+                              const int64_t* const* offsets, const uint64_t* const* valid, const uint8_t* prefix,
+                              const int32_t* prefix_len, const int32_t* params, const double* label, int max_classes,
+                              int* nclasses_out, double* classes_out, uint64_t* class_counts_out,
+                              int64_t* bucket_class_sum, int64_t* bucket_rows, int64_t* bucket_sq_sum,
+                              int32_t* bucket_max, int32_t* bucket_min);
+
+/* tmog_text_hash_transform_dev over host text columns: the sparse rows of the partition in ROW ORDER as CSR (indptr
+ * [n + 1], out_idx / out_val [capacity]; *nnz_out = entries) -- what OpTransformerN.transform's mapPartitions hands
+ * back as one sparse vector per row.  capacity 0 sizes the output (nothing written). */
+int tmog_text_hash_transform_host(tmog_ctx* ctx, int ncols, int64_t n, const uint8_t* const* data,
+                                  const int64_t* const* offsets, const uint64_t* const* valid, const uint8_t* prefix,
+                                  const int32_t* prefix_len, const int32_t* params, const int32_t* newpos,
+                                  int64_t* indptr, int32_t* out_idx, int32_t* out_val, int64_t capacity,
+                                  int64_t* nnz_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -108,6 +108,11 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_ctx_destroy": [_p],
     "tmog_pinned_alloc": [_sz, C.POINTER(_p)],
     "tmog_pinned_free": [_p],
+    "tmog_pivot_fit_host": [_p, _p, _i64, _i64, _int, _p, _p, _p, _p, _i64, _int, _int, _i64, _int, _p, _p, _p, _p, _p, _i64,
+                            _p, _p, _p],
+    "tmog_pivot_transform_host": [_p, _p, _i64, _i64, _int, _p, _p, _p, _int, _p, _i64, _p, _i64, _i64],
+    "tmog_text_hash_stats_host": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _int, _p, _p, _p, _p, _p, _p, _p, _p],
+    "tmog_text_hash_transform_host": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _p],
     "tmog_real_fit_host": [_p, _p, _i64, _p, _i64, _p, _i64, _int, _i64, _int, _p, _p, _p, _int, _p, _p, _p, _p],
     "tmog_real_transform_host": [_p, _p, _i64, _p, _i64, _i64, _int, _p, _int, _i64, _p, _int, _p, _i64, _i64],
 }
