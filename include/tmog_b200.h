@@ -635,6 +635,23 @@ int tmog_text_hash_transform_host(tmog_ctx* ctx, int ncols, int64_t n, const uin
                                   int64_t* indptr, int32_t* out_idx, int32_t* out_val, int64_t capacity,
                                   int64_t* nnz_out);
 
+/* ---- multi-GPU exchange ---------------------------------------------------------------------------------------------
+ * Rows shard across GPUs; only the small results of a fit cross NVLink.  Replaces the reduce side of the reference's
+ * aggregations: Aggregator.merge of SequenceAggregators (U/spark/SequenceAggregators.scala:83), the RDD.fold of
+ * OpOneHotVectorizer.fitFn (C/stages/impl/feature/OpOneHotVectorizer.scala:95-97), treeAggregate / reduceByKey of
+ * SanityChecker (C/stages/impl/preparators/SanityChecker.scala:265-272,407).  One tmog_comm per rank (process or thread
+ * with its own GPU): rank 0 makes the 128-byte id (tmog_comm_unique_id) and hands it to the others out of band (the
+ * Spark driver broadcasts it), every rank calls tmog_comm_init.  NCCL (libnccl.so.2) is loaded at run time.
+ * All-reduce in place of `count` 8-byte elements: dtype 0 = int64 (count tables), 1 = float64 (partial sums, which must
+ * share their shifts); op 0 = sum, 1 = max, 2 = min.  _dev: device buffer, asynchronous on `stream`; _host: host
+ * buffer, staged through the comm's own device buffer, returns when the result is in place. */
+typedef struct tmog_comm tmog_comm;
+int tmog_comm_unique_id(uint8_t* id128);
+int tmog_comm_init(const uint8_t* id128, int rank, int size, int device, tmog_comm** comm);
+int tmog_comm_destroy(tmog_comm* comm);
+int tmog_comm_allreduce_dev(tmog_comm* comm, void* buf, int64_t count, int dtype, int op, void* stream);
+int tmog_comm_allreduce_host(tmog_comm* comm, void* buf, int64_t count, int dtype, int op);
+
 #ifdef __cplusplus
 }
 #endif

@@ -304,3 +304,45 @@ def _worker_sampled(rank, size, port, q):
 def test_two_ranks_sampled_sanity_checker_matches_oracle():
     """fraction() < 1 over two row shards: every rank samples its shard, the statistics of the samples are merged."""
     _run(_worker_sampled)
+
+
+def _worker_comm(rank, size, port, q):
+    """tmog_comm_* through ctypes only (no torch.distributed): the NCCL id travels through a file, as a Spark driver
+    would broadcast it."""
+    try:
+        import ctypes as C
+        import time
+        from transmogrifai_b200 import _lib as L
+        path = f"/tmp/tmog_comm_id_{port}"
+        ident = (C.c_uint8 * 128)()
+        if rank == 0:
+            L.call("tmog_comm_unique_id", ident)
+            with open(path + ".tmp", "wb") as f:
+                f.write(bytes(ident))
+            os.replace(path + ".tmp", path)
+        else:
+            for _ in range(600):
+                if os.path.exists(path):
+                    break
+                time.sleep(0.05)
+            ident = (C.c_uint8 * 128).from_buffer_copy(open(path, "rb").read())
+        comm = C.c_void_p()
+        L.call("tmog_comm_init", ident, rank, size, rank, C.byref(comm))
+        counts = np.arange(1000, dtype=np.int64) * (rank + 1)
+        L.call("tmog_comm_allreduce_host", comm, counts.ctypes.data, len(counts), 0, 0)
+        assert np.array_equal(counts, np.arange(1000, dtype=np.int64) * 3)
+        sums = np.array([0.5 + rank, -2.0 * rank, 1e-3], dtype=np.float64)
+        mx = sums.copy()
+        L.call("tmog_comm_allreduce_host", comm, sums.ctypes.data, 3, 1, 0)
+        L.call("tmog_comm_allreduce_host", comm, mx.ctypes.data, 3, 1, 1)
+        assert np.allclose(sums, [2.0, -2.0, 2e-3]) and np.array_equal(mx, [1.5, 0.0, 1e-3])
+        L.call("tmog_comm_destroy", comm)
+        q.put((rank, "ok"))
+    except Exception:  # pragma: no cover
+        import traceback
+        q.put((rank, traceback.format_exc()))
+
+
+@needs_two_gpus
+def test_comm_entry_points_allreduce_over_nccl():
+    _run(_worker_comm)
