@@ -607,6 +607,9 @@ class VectorColumn:
                 sub = sub.with_vector(full.vectors[f.name].recompute(full, sub))
         out = self.producer.transformColumn(sub)
         out.producer = self.producer
+        if out.stats is None and sub.response and hasattr(self.producer, "stats_for"):
+            # the statistics sidecar of the new rows from the same fused scans that serve a fit (no dense vector)
+            out.stats = self.producer.stats_for(sub)
         return out
 
     def to_scipy(self):

@@ -27,17 +27,23 @@ def _device_label(batch: ColumnarBatch, label_name: str) -> torch.Tensor:
 
 
 DENSIFY_LIMIT_BYTES = 64 << 30
+GRAM_TILE_BYTES = 4 << 30          # a vector larger than this goes through the Gramian kernel in row tiles
 
 
-def _dense_block(vec: VectorColumn) -> torch.Tensor:
-    """All parts as one device row-major block: a view for a single dense part, else a copy in which sparse parts are
-    densified (what Spark's RowMatrix does for Statistics.corr)."""
+def _materialized(vec: VectorColumn) -> list:
+    return [p.materialize(None) if isinstance(p, (LazyPart, LazyOneHotPart)) else p for p in vec.parts]
+
+
+def _dense_block(vec: VectorColumn, parts: Optional[list] = None, a: int = 0, b: Optional[int] = None) -> torch.Tensor:
+    """Rows [a, b) of all parts as one device row-major block: a view for a single dense part, else a copy in which
+    sparse parts are densified (what Spark's RowMatrix does for Statistics.corr)."""
     from ..columnar import SparseRowsPart
-    parts = [p.materialize(None) if isinstance(p, (LazyPart, LazyOneHotPart)) else p for p in vec.parts]
+    parts = _materialized(vec) if parts is None else parts
+    b = vec.n if b is None else b
     if len(parts) == 1 and isinstance(parts[0], (DensePart, LazyDensePart)):
-        d = parts[0].data
+        d = parts[0].data[a:b]
         return d if d.is_cuda else d.cuda()
-    n, w = vec.n, sum(p.width for p in parts)
+    n, w = b - a, sum(p.width for p in parts)
     if n * w * 8 > DENSIFY_LIMIT_BYTES:
         raise ValueError(f"densifying a {n} x {w} vector needs {n * w * 8 >> 30} GiB: use featureFeatureCorrLevel = Off "
                          "for wide hashed / pivoted vectors (the reference cannot exceed 65535 columns either)")
@@ -45,14 +51,16 @@ def _dense_block(vec: VectorColumn) -> torch.Tensor:
     off = 0
     for p in parts:
         if isinstance(p, (DensePart, LazyDensePart)):
-            d = p.data
+            d = p.data[a:b]
             out[:, off:off + p.width] = d if d.is_cuda else d.cuda()
         elif isinstance(p, OneHotPart):
-            idx = p.indices if p.indices.is_cuda else p.indices.cuda()
+            idx = p.indices[a:b]
+            idx = idx if idx.is_cuda else idx.cuda()
             L.call("tmog_onehot_densify_dev", idx.data_ptr(), idx.stride(0), n, idx.shape[1], out.data_ptr(), w, off,
                    R.stream())
         elif isinstance(p, SparseRowsPart):
-            L.call("tmog_sparse_rows_densify_dev", p.row_start.data_ptr(), p.row_nnz.data_ptr(), p.indices.data_ptr(),
+            rs, rn = p.row_start[a:b], p.row_nnz[a:b]
+            L.call("tmog_sparse_rows_densify_dev", rs.data_ptr(), rn.data_ptr(), p.indices.data_ptr(),
                    p.values.data_ptr(), n, out.data_ptr(), w, off, R.stream())
         else:
             raise NotImplementedError(f"cannot densify a {type(p).__name__}")
@@ -101,45 +109,62 @@ def vector_stats(batch: ColumnarBatch, vec: VectorColumn, label_name: str) -> Ve
 
 def pearson_matrix(batch: ColumnarBatch, vec: VectorColumn, label_name: str, corr_indices: Sequence[int],
                    st: Optional[VectorStats]) -> np.ndarray:
-    """Statistics.corr(vectorRowsForCorr, "pearson") over the selected columns + label (SanityChecker.scala:467-470)."""
+    """Statistics.corr(vectorRowsForCorr, "pearson") over the selected columns + label (SanityChecker.scala:467-470).
+    A vector too large to densify at once goes through the Gramian kernel in row tiles (the kernel adds to the matrix),
+    so the limit is the (d + 1)^2 matrix itself -- the reference's 65535 columns -- not rows x columns."""
     R.require_cuda()
-    x = _dense_block(vec)
-    n, d_all = x.shape
+    parts = _materialized(vec)
+    n, d_all = vec.n, sum(p.width for p in parts)
     feat = [i for i in corr_indices if i < d_all]
     if len(feat) + 1 > 65535:
         raise ValueError(f"requirement failed: Argument with more than 65535 cols: {len(feat) + 1}")
-    if feat != list(range(d_all)):
-        idx = torch.tensor(feat, dtype=torch.int32, device="cuda")
-        sub = torch.empty((n, len(feat)), dtype=torch.float64, device="cuda")
-        L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), n, idx.data_ptr(), len(feat), sub.data_ptr(),
-               len(feat), R.stream())
-        x = sub
-    d = x.shape[1]
-    y = _device_label(batch, label_name)
+    select = None if feat == list(range(d_all)) else torch.tensor(feat, dtype=torch.int32, device="cuda")
+    d = len(feat)
     D = d + 1
+    y = _device_label(batch, label_name)
     dist_world = DD.world()[1]
+    tile = n if n * d_all * 8 <= GRAM_TILE_BYTES else max(1024, GRAM_TILE_BYTES // (d_all * 8) // 64 * 64)
+
+    def rows(a: int, b: int) -> torch.Tensor:
+        x = _dense_block(vec, parts, a, b)
+        if select is None:
+            return x
+        sub = torch.empty((b - a, d), dtype=torch.float64, device="cuda")
+        L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), b - a, select.data_ptr(), d, sub.data_ptr(), d,
+               R.stream())
+        return sub
+
     shifts = torch.zeros(D, dtype=torch.float64, device="cuda")
-    L.call("tmog_dense_pilot_shift_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), shifts.data_ptr(), R.stream())
-    if dist_world > 1:
-        torch.distributed.broadcast(shifts, src=0)
+    gram = torch.zeros((D, D), dtype=torch.float64, device="cuda")
+    sums = torch.zeros(D * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
     nb = C.c_size_t()
-    L.call("tmog_dense_stats_scratch_bytes", n, d, C.byref(nb))
+    L.call("tmog_dense_stats_scratch_bytes", min(tile, n), d, C.byref(nb))
     scratch = R.scratch("dense_stats", nb.value)
     partials = torch.zeros(D * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
-    L.call("tmog_dense_stats_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), None, 0, None, shifts.data_ptr(),
-           scratch.data_ptr(), scratch.numel(), partials.data_ptr(), None, R.stream())
-    gram = torch.zeros((D, D), dtype=torch.float64, device="cuda")
-    L.call("tmog_dense_gram_dev", x.data_ptr(), x.stride(0), n, d, y.data_ptr(), shifts.data_ptr(), gram.data_ptr(),
-           R.stream())
+    for a in range(0, max(n, 1), max(tile, 1)):
+        b = min(n, a + tile)
+        x = rows(a, b)
+        ya = y[a:]
+        if a == 0:
+            L.call("tmog_dense_pilot_shift_dev", x.data_ptr(), x.stride(0), b - a, d, ya.data_ptr(), shifts.data_ptr(),
+                   R.stream())
+            if dist_world > 1:
+                torch.distributed.broadcast(shifts, src=0)
+        L.call("tmog_dense_stats_dev", x.data_ptr(), x.stride(0), b - a, d, ya.data_ptr(), None, 0, None,
+               shifts.data_ptr(), scratch.data_ptr(), scratch.numel(), partials.data_ptr(), None, R.stream())
+        sums += partials                                   # only the shifted sums ([.][1]) and the row count are used
+        L.call("tmog_dense_gram_dev", x.data_ptr(), x.stride(0), b - a, d, ya.data_ptr(), shifts.data_ptr(),
+               gram.data_ptr(), R.stream())
+        del x
     if dist_world > 1:                                     # Gramian and sums of the shifted rows add up over the ranks
         torch.distributed.all_reduce(gram)
+        torch.distributed.all_reduce(sums)
     g = gram.cpu().numpy()
-    merged, _ = DD.gather_fit_results(partials)
-    merged = merged.reshape(D, L.REAL_NSTAT)
-    sums = np.ascontiguousarray(merged[:, 1])
-    n_all = float(merged[D - 1, 7]) if dist_world > 1 else float(n)
+    merged = sums.cpu().numpy().reshape(D, L.REAL_NSTAT)
+    col_sums = np.ascontiguousarray(merged[:, 1])
+    n_all = float(merged[D - 1, 7])
     corr = np.zeros((D, D))
-    L.call("tmog_pearson_from_gram", D, n_all, g.ctypes.data, sums.ctypes.data, corr.ctypes.data)
+    L.call("tmog_pearson_from_gram", D, n_all, g.ctypes.data, col_sums.ctypes.data, corr.ctypes.data)
     return corr
 
 

@@ -162,11 +162,19 @@ class RealVectorizer(OpEstimator):
 
     def fit(self, batch: ColumnarBatch) -> "RealVectorizerModel":
         R.require_cuda()
+        if self.trackNulls:
+            self._metadata = _numeric_metadata(self, True)
+        partials, shifts, classes, counts, null_counts, label_name = self._scan_batch(batch)
+        model = self._finish(partials, shifts, classes, counts, null_counts, label_name)
+        model._fit_key = batch_key(batch)
+        return model
+
+    def _scan_batch(self, batch: ColumnarBatch):
+        """The fused scan of one batch (all ranks): merged partial sums, their shifts, label classes and the per-class
+        null counts."""
         names = [f.name for f in self.inN]
         block = batch.numeric(names)
         ncols, n = len(names), batch.n
-        if self.trackNulls:
-            self._metadata = _numeric_metadata(self, True)
         label_name = batch.response
         NS = L.REAL_NSTAT
         partials = np.zeros((ncols + 1) * NS)
@@ -246,9 +254,7 @@ class RealVectorizer(OpEstimator):
                     null_counts = D.allreduce_sum(g_null) if self.trackNulls else None
                 else:
                     classes = counts = null_counts = None
-        model = self._finish(partials, shifts, classes, counts, null_counts, label_name)
-        model._fit_key = batch_key(batch, block)
-        return model
+        return partials, shifts, classes, counts, null_counts, label_name
 
     def _finish(self, partials, shifts, classes, counts, null_counts, label_name) -> "RealVectorizerModel":
         """Fill values and the statistics sidecar from the merged partial sums (host)."""
@@ -356,6 +362,27 @@ class RealVectorizerModel(OpModel):
         self.chunkRows = parent.chunkRows
         self._fit_stats: Optional[VectorStats] = None
         self._fit_key = None
+
+    def stats_for(self, batch: ColumnarBatch) -> Optional[VectorStats]:
+        """SanityChecker statistics of this model's columns over another batch (a row sample of the training data):
+        the same fused scan, finished with the model's fill values instead of the batch's own means."""
+        if not batch.response:
+            return None
+        partials, shifts, classes, counts, null_counts, label_name = self.parent._scan_batch(batch)
+        ncols = len(self.inN)
+        w = ncols * (2 if self.trackNulls else 1)
+        fills = np.asarray(self.fillValues, dtype=np.float64)
+        mean, var, mn, mx, cov = (np.zeros(w) for _ in range(5))
+        lab = np.zeros(5)
+        L.call("tmog_real_finish_with_fills", partials.ctypes.data, shifts.ctypes.data, ncols, fills.ctypes.data,
+               int(self.trackNulls), mean.ctypes.data, var.ctypes.data, mn.ctypes.data, mx.ctypes.data, cov.ctypes.data,
+               lab.ctypes.data, None)
+        class_sums = None
+        if classes is not None:
+            class_sums = np.full((len(classes), w), np.nan)
+            if self.trackNulls and null_counts is not None:
+                class_sums[:, 1::2] = null_counts.T
+        return VectorStats(LabelInfo(label_name, int(lab[0]), lab, classes, counts), mean, var, mn, mx, cov, class_sums)
 
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
         R.require_cuda()

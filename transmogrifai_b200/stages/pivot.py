@@ -495,6 +495,52 @@ class OpTextPivotVectorizerModel(OpModel):
         return VectorColumn(self.getOutput().name, batch.n, self.getMetadata(), [part],
                             self._fit_stats if same else None)
 
+    def stats_for(self, batch: ColumnarBatch) -> Optional[VectorStats]:
+        """SanityChecker statistics of this model's one-hot columns over another batch (a row sample): counts per raw
+        code, folded into the emitted columns with the model's vocabulary; every rank folds its own counts first, so
+        ranks with different dictionaries need no union."""
+        label_name = batch.response
+        if not label_name:
+            return None
+        est = self.parent
+        names = [f.name for f in self.inN]
+        block = batch.strings(names)
+        dev = batch.on_device("strings", names, block)
+        y = batch.label()
+        y = y if y.is_cuda else y.cuda()
+        classes, counts_per_class, ids = label_info_dev(batch, y, label_name)
+        cont = None if classes is not None else label_moments_dev(batch, y, label_name)
+        ncls = len(classes) if classes is not None else 1
+        st = est._scan_begin(block.dicts, ncls, cont is not None)
+        est._scan(st, dev, batch.n, ids if classes is not None else None, y, cont)
+        if int(st["bad"].item()):
+            raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
+        acc = st["acc"].cpu().numpy()
+        ws = None if cont is None else st["ws"].cpu().numpy()
+        rows, wrows = [], []
+        for c in range(len(names)):
+            k = len(self.topValues[c])
+            local = self._code_to_out(block, c).astype(np.int64)
+            tab = acc[st["count_offset"][c]:st["count_offset"][c] + st["nids"][c] * ncls].reshape(-1, ncls)
+            out = np.zeros((k + 2, ncls), dtype=np.int64)
+            np.add.at(out, local, tab[1:])
+            out[k + 1] = tab[0]
+            rows.append(out if self.shouldTrackNulls else out[:k + 1])
+            if ws is not None:
+                w = ws[st["w_off"][c]:st["w_off"][c] + st["nids"][c]]
+                wr = np.zeros(k + 2)
+                np.add.at(wr, local, w[1:])
+                wr[k + 1] = w[0]
+                wrows.append(wr if self.shouldTrackNulls else wr[:k + 1])
+        per_class = D.allreduce_sum(np.concatenate(rows, axis=0)).astype(np.float64)
+        if classes is not None:
+            return _stats_from_class_counts(per_class, classes, counts_per_class, int(np.asarray(counts_per_class).sum()),
+                                            label_name)
+        sv = per_class[:, 0]
+        ones = np.ones_like(sv)
+        return stats_from_sums_continuous(sv, sv, sv, ones, ones, D.allreduce_sum(np.concatenate(wrows)), cont[0], cont[1],
+                                          label_name)
+
     def _code_to_out(self, block: DictBlock, c: int) -> np.ndarray:
         """Emitted-column index (top position or OTHER) of every code of column c's dictionary."""
         d = block.dicts[c]

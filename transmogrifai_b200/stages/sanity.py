@@ -302,8 +302,7 @@ class SanityChecker(OpEstimator):
         on_dev = lambda b: b if getattr(b, "is_cuda", dev == "cuda") == (dev == "cuda") else b.to(dev)  # noqa: E731
         full = ColumnarBatch(batch.n, [on_dev(b) for b in batch.blocks], batch.vectors, batch.response)
         sub = full.take_rows(idx)
-        svec = vec.recompute(batch, sub)
-        svec.stats = None
+        svec = vec.recompute(batch, sub)          # with its statistics sidecar where the upstream stages provide one
         m = int(D.allreduce_sum(np.array([idx.numel()], dtype=np.int64))[0])      # sampled rows of all ranks
         return sub.with_vector(svec), svec, m
 

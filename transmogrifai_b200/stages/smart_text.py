@@ -900,6 +900,21 @@ class SmartTextVectorizerModel(OpModel):
                 parts.append(stats_from_sums_continuous(sv, sv + ex, nz, vmax, vmin, wv, cont[0], cont[1], label_name))
         return VectorStats.concat(parts)
 
+    def stats_for(self, batch: ColumnarBatch) -> Optional[VectorStats]:
+        """SanityChecker statistics of this model's columns over another batch (a row sample of the training data)."""
+        label_name = batch.response
+        if not label_name:
+            return None
+        names = [f.name for f in self.inN]
+        block = batch.texts(names)
+        dev = batch.on_device("texts", names, block)
+        y = batch.label()
+        y = y if y.is_cuda else y.cuda()
+        classes, class_counts, ids = label_info_dev(batch, y, label_name)
+        n_all = int(D.allreduce_sum(np.array([batch.n], dtype=np.int64))[0])
+        cont = None if classes is not None else label_moments_dev(batch, y, label_name) + (y,)
+        return self._sidecar(dev, batch.n, n_all, classes, class_counts, ids, label_name, cont)
+
     # -- row chunks (streaming.py): the statistics sidecar accumulated over the chunks
     def stream_begin(self, label):
         if label is None:
