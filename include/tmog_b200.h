@@ -580,6 +580,25 @@ int tmog_real_transform_host(tmog_ctx* ctx, const double* values, int64_t ld, co
                              int64_t n, int ncols, const double* fills, int track_nulls, int64_t chunk_rows,
                              const int32_t* keep, int nkeep, double* out, int64_t out_ld, int64_t out_col0);
 
+/* ---- OPVector -> VectorUDT ----------------------------------------------------------------------------------------
+ * The wire format a mapPartitions transform returns to Spark, columnar for the rows of a partition: the reference ends
+ * every vectorizer, combiner and SanityCheckerModel with `.compressed` (C/stages/impl/feature/Transmogrifier.scala:466-475,
+ * F/utils/spark/RichVector.scala:120-134, C/stages/impl/preparators/DerivedFeatureFilterUtils.scala:291-305): explicit
+ * zeros are dropped; a row is a SparseVector when 1.5 (nnz + 1) < size, else a DenseVector.  VectorUDT's struct is
+ * (type: byte 0 sparse / 1 dense, size: int, null for dense; indices: int[], null for dense; values: double[]).
+ * parts: device array of nparts descriptors, 9 x int64 each, in vector order: {kind, width, col0, ld, k, a, b, c, d}
+ *   kind 0 dense   a = f64 [n][ld]
+ *   kind 1 one-hot a = i32 [n][ld], k entries per row = index local to the part of a 1.0, -1 = none
+ *   kind 2 sparse  a = row_start i64 [n], b = row_nnz i32 [n], c = indices i32 (local to the part), d = values i32
+ * _count: type [n], size_out [n] (-1 = null), idx_len / val_len [n] = lengths of the row's two lists; the caller turns
+ * the lengths into offsets (exclusive prefix sums) and calls _write, which fills indices / values (ascending indices;
+ * dense rows: `size` values). */
+int tmog_vector_export_count_dev(const void* parts, int nparts, int64_t n, int size, uint8_t* type, int32_t* size_out,
+                                 int64_t* idx_len, int64_t* val_len, void* stream);
+int tmog_vector_export_write_dev(const void* parts, int nparts, int64_t n, int size, const uint8_t* type,
+                                 const int64_t* idx_off, const int64_t* val_off, int32_t* indices, double* values,
+                                 void* stream);
+
 /* ---- string paths over host buffers ------------------------------------------------------------------------------
  * One call per exported partition does what the reference's estimator does in fit(Dataset) and its model in
  * transform(Dataset) (features/src/main/scala/com/salesforce/op/stages/base/sequence/SequenceEstimator.scala:91-106):

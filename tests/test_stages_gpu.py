@@ -501,3 +501,49 @@ def test_host_batch_raw_blocks_cross_the_link_once(monkeypatch):
     assert sorted(copies) == ["DictBlock", "SetBlock", "TextBlock"]
     got_d, keep_d = run(_batch(data, response="y", device="cuda"))
     assert keep_h == keep_d and got_h.shape == got_d.shape and abs(got_h - got_d).max() == 0
+
+
+def test_vector_udt_export_matches_spark_compressed():
+    """OPVector -> VectorUDT arrays (wire.py): every row carries exactly its non-zeros, in ascending index order, as a
+    SparseVector when 1.5 (nnz + 1) < size and as a DenseVector otherwise (Spark's Vector.compressed, which the
+    reference applies at the end of every stage: Transmogrifier.scala:466-475, RichVector.scala:120-134)."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.dsl import fit_and_transform, transmogrify
+    from transmogrifai_b200.wire import to_vector_udt
+    rng = np.random.default_rng(5)
+    n = 1500
+    y = (rng.random(n) < 0.3).astype(np.float64)
+    opt = lambda v, p: None if rng.random() < p else v   # noqa: E731
+    words = ["".join(rng.choice(list("abcdefgh"), size=rng.integers(3, 7))) for _ in range(60)]
+    data = {"b0": (F.BINARY, [opt(bool(rng.random() < 0.5), 0.1) for _ in y]),
+            "p0": (F.PICKLIST, [opt(["x", "y", "z"][int(rng.integers(3))], 0.1) for _ in y]),
+            "r0": (F.REAL, [opt(float(rng.normal(0, 1)) if rng.random() < 0.7 else 0.0, 0.1) for _ in y]),
+            "t0": (F.TEXT, [opt(" ".join(words[i] for i in rng.integers(0, 60, rng.poisson(6))), 0.1) for _ in y]),
+            "y": (F.REALNN, y.tolist())}
+    batch = _batch(data, response="y", device="cuda")
+    FB = F.FeatureBuilder
+    feats = [FB.Text("t0").asPredictor(), FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(),
+             FB.PickList("p0").asPredictor()]
+    narrow = transmogrify(feats[1:3])                     # 4 columns: rows with two or more non-zeros come out dense
+    wide = FB.RealNN("y").asResponse().sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
+                                                   featureFeatureCorrLevel="Off")
+    for result in (narrow, wide):
+        out, _ = fit_and_transform(batch, result)
+        vec = out.vectors[result.name]
+        exp = np.asarray(vec.to_scipy().todense())
+        udt = to_vector_udt(vec)
+        assert udt.width == exp.shape[1]
+        types = udt.type.cpu().numpy()
+        nnz = (exp != 0).sum(axis=1)
+        assert np.array_equal(types == 0, 1.5 * (nnz + 1.0) < exp.shape[1])
+        if result is narrow:
+            assert (types == 1).any() and (types == 0).any()
+        for r in list(range(0, n, 37)) + [n - 1]:
+            tp, size, idx, val = udt.row(r)
+            if tp == 0:
+                assert size == exp.shape[1] and np.array_equal(idx, np.nonzero(exp[r])[0])
+                assert np.array_equal(val, exp[r][idx])
+            else:
+                assert size == -1 and len(idx) == 0 and np.array_equal(val, exp[r])
+        assert int(udt.idx_offsets[-1]) == int(nnz[types == 0].sum())
+        assert int(udt.val_offsets[-1]) == int(nnz[types == 0].sum() + (types == 1).sum() * exp.shape[1])

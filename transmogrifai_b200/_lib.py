@@ -113,6 +113,8 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_pivot_transform_host": [_p, _p, _i64, _i64, _int, _p, _p, _p, _int, _p, _i64, _p, _i64, _i64],
     "tmog_text_hash_stats_host": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _int, _p, _p, _p, _p, _p, _p, _p, _p],
     "tmog_text_hash_transform_host": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _p],
+    "tmog_vector_export_count_dev": [_p, _int, _i64, _int, _p, _p, _p, _p, _p],
+    "tmog_vector_export_write_dev": [_p, _int, _i64, _int, _p, _p, _p, _p, _p, _p],
     "tmog_comm_unique_id": [_p],
     "tmog_comm_init": [_p, _int, _int, _int, C.POINTER(_p)],
     "tmog_comm_destroy": [_p],

@@ -1,0 +1,148 @@
+// OPVector -> Spark ml.linalg VectorUDT, columnar: what a mapPartitions transform hands back to Spark for the rows of a
+// partition.  The reference ends every vectorizer / combiner / SanityCheckerModel with `.compressed`
+// (Transmogrifier.scala:466-475, RichVector.scala:120-134, DerivedFeatureFilterUtils.scala:291-305): explicit zeros are
+// dropped and a row becomes a SparseVector when 1.5 (nnz + 1) < size, a DenseVector otherwise (Spark 2.4.5
+// ml.linalg.Vector.compressed).  VectorUDT's struct is (type: byte 0 sparse / 1 dense, size: int -- null for dense,
+// indices: int[] -- null for dense, values: double[]); as Arrow arrays of a partition: type u8 [n], size i32 [n],
+// indices = offsets i64 [n + 1] + i32 [], values = offsets i64 [n + 1] + f64 [].
+//
+// Two HBM-bound kernels, a warp per row: count (non-zeros -> type and the two list lengths), then -- after a prefix sum
+// of the lengths -- write.  The parts of the vector are read where the vectorizers left them (dense blocks, one-hot
+// index blocks, sparse rows in 4-array form); nothing is densified.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace tmog {
+
+struct ExportPart {        // device struct, 64 bytes
+    int64_t kind;          // 0 dense f64 [n][ld], 1 one-hot i32 [n][ld] (k entries, -1 = none), 2 sparse rows
+    int64_t width;         // columns of the part
+    int64_t col0;          // first vector index of the part
+    int64_t ld;            // row stride (kind 0, 1); entries per row k (kind 1) in `k`
+    int64_t k;
+    const void* a;         // kind 0: values; kind 1: indices; kind 2: row_start (i64)
+    const void* b;         // kind 2: row_nnz (i32)
+    const void* c;         // kind 2: indices (i32)
+    const void* d;         // kind 2: values (i32)
+};
+
+template <bool WRITE>
+__global__ void __launch_bounds__(256)
+vector_export_kernel(const ExportPart* __restrict__ parts, int nparts, int64_t n, int size, uint8_t* __restrict__ type,
+                     int32_t* __restrict__ size_out, int64_t* __restrict__ idx_len, int64_t* __restrict__ val_len,
+                     const int64_t* __restrict__ idx_off, const int64_t* __restrict__ val_off,
+                     int32_t* __restrict__ indices, double* __restrict__ values) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    for (int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n; r += warps) {
+        bool sparse = false;
+        int64_t io = 0, vo = 0;
+        if (WRITE) {
+            sparse = type[r] == 0;
+            io = idx_off[r];
+            vo = val_off[r];
+            if (!sparse)
+                for (int q = lane; q < size; q += 32) values[vo + q] = 0.0;
+            __syncwarp();
+        }
+        int nnz = 0;
+        for (int p = 0; p < nparts; ++p) {
+            const ExportPart e = parts[p];
+            if (e.kind == 0) {
+                const double* x = static_cast<const double*>(e.a) + r * e.ld;
+                for (int64_t c0 = 0; c0 < e.width; c0 += 32) {
+                    const int64_t c = c0 + lane;
+                    const double v = c < e.width ? x[c] : 0.0;
+                    const unsigned nz = __ballot_sync(FULL, v != 0.0);
+                    if (WRITE && v != 0.0) {
+                        if (sparse) {
+                            const int64_t at = nnz + __popc(nz & lt);
+                            indices[io + at] = (int32_t)(e.col0 + c);
+                            values[vo + at] = v;
+                        } else {
+                            values[vo + e.col0 + c] = v;
+                        }
+                    }
+                    nnz += __popc(nz);
+                }
+            } else if (e.kind == 1) {
+                const int32_t* x = static_cast<const int32_t*>(e.a) + r * e.ld;
+                for (int64_t c0 = 0; c0 < e.k; c0 += 32) {
+                    const int64_t c = c0 + lane;
+                    const int32_t v = c < e.k ? x[c] : -1;
+                    const unsigned nz = __ballot_sync(FULL, v >= 0);
+                    if (WRITE && v >= 0) {
+                        if (sparse) {
+                            const int64_t at = nnz + __popc(nz & lt);
+                            indices[io + at] = (int32_t)(e.col0 + v);
+                            values[vo + at] = 1.0;
+                        } else {
+                            values[vo + e.col0 + v] = 1.0;
+                        }
+                    }
+                    nnz += __popc(nz);
+                }
+            } else {
+                const int64_t s = static_cast<const int64_t*>(e.a)[r];
+                const int m = static_cast<const int32_t*>(e.b)[r];
+                const int32_t* ix = static_cast<const int32_t*>(e.c) + s;
+                const int32_t* vx = static_cast<const int32_t*>(e.d) + s;
+                for (int c0 = 0; c0 < m; c0 += 32) {
+                    const int c = c0 + lane;
+                    const int32_t v = c < m ? vx[c] : 0;
+                    const unsigned nz = __ballot_sync(FULL, v != 0);
+                    if (WRITE && v != 0) {
+                        if (sparse) {
+                            const int64_t at = nnz + __popc(nz & lt);
+                            indices[io + at] = (int32_t)(e.col0 + ix[c]);
+                            values[vo + at] = (double)v;
+                        } else {
+                            values[vo + e.col0 + ix[c]] = (double)v;
+                        }
+                    }
+                    nnz += __popc(nz);
+                }
+            }
+        }
+        if (!WRITE && lane == 0) {
+            const bool sp = 1.5 * (nnz + 1.0) < (double)size;         // Vector.compressed
+            type[r] = sp ? 0 : 1;
+            size_out[r] = sp ? size : -1;                              // -1 = null (dense rows carry no size)
+            idx_len[r] = sp ? nnz : 0;
+            val_len[r] = sp ? nnz : size;
+        }
+    }
+}
+
+}  // namespace tmog
+
+using namespace tmog;
+
+extern "C" int tmog_vector_export_count_dev(const void* parts, int nparts, int64_t n, int size, uint8_t* type,
+                                            int32_t* size_out, int64_t* idx_len, int64_t* val_len, void* stream) {
+    TMOG_REQUIRE(nparts >= 0 && n >= 0 && size >= 0, "bad shape");
+    if (n == 0) return TMOG_OK;
+    TMOG_REQUIRE(parts && type && size_out && idx_len && val_len, "NULL argument");
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 7) / 8, (int64_t)sm_count() * 16));
+    vector_export_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(static_cast<const ExportPart*>(parts), nparts, n,
+                                                                        size, type, size_out, idx_len, val_len, nullptr,
+                                                                        nullptr, nullptr, nullptr);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_vector_export_write_dev(const void* parts, int nparts, int64_t n, int size, const uint8_t* type,
+                                            const int64_t* idx_off, const int64_t* val_off, int32_t* indices,
+                                            double* values, void* stream) {
+    TMOG_REQUIRE(nparts >= 0 && n >= 0 && size >= 0, "bad shape");
+    if (n == 0) return TMOG_OK;
+    TMOG_REQUIRE(parts && type && idx_off && val_off && indices && values, "NULL argument");
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 7) / 8, (int64_t)sm_count() * 16));
+    vector_export_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(
+        static_cast<const ExportPart*>(parts), nparts, n, size, const_cast<uint8_t*>(type), nullptr, nullptr, nullptr,
+        idx_off, val_off, indices, values);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
