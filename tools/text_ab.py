@@ -15,7 +15,7 @@ rows = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 batch, feats, label, info = benchdata.make_workload("c5", rows, 1)
 checked = bench.build_plan(feats, label, info)
 out, fitted = fit_and_transform(batch, checked)
-for mode in ("cells", "rows"):
+for mode in (("cells",) if os.environ.get("AB_CELLS_ONLY") else ("cells", "rows")):
     if mode == "rows":
         os.environ["TMOG_TEXT_PATH"] = "rows"
     kt = bench.kernel_times("c5", batch, fitted, info, reps=4, text_offset=bench._text_offset(fitted))

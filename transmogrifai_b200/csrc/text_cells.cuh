@@ -22,7 +22,16 @@
 
 namespace tmog {
 
-constexpr int TC_WARPS = 8;
+#ifndef TC_WARPS_V
+#define TC_WARPS_V 8
+#endif
+#ifndef TC_ROUND_LANES_V
+#define TC_ROUND_LANES_V 26
+#endif
+#ifndef TC_PEND_V
+#define TC_PEND_V 12
+#endif
+constexpr int TC_WARPS = TC_WARPS_V;
 constexpr int TC_FW = 16;                 // bitmap words of a cell: numFeatures <= 512
 constexpr int TC_MAXF = TC_FW * 32;
 constexpr int TC_DUPS = 12;               // buckets with term frequency > 1 a cell record holds (13 slots)
@@ -30,7 +39,7 @@ constexpr int TC_RING = 16;               // words of recent text a lane keeps (
 constexpr int TC_RING_ROWS = TC_RING + 5; // + the first five words again, behind the last (no wrap inside a token)
 constexpr int TC_BACK = 44;               // a token may start this many bytes before the chunk it ends in
 constexpr int TC_ITEM_ROWS = 8192;        // rows of one column a CTA takes at a time
-constexpr int TC_ROUND_LANES = 26;        // a round runs when this many lanes have a token waiting
+constexpr int TC_ROUND_LANES = TC_ROUND_LANES_V;        // a round runs when this many lanes have a token waiting
 constexpr int TC_WARP_ROWS = TC_RING_ROWS + 4 + TC_FW + TC_DUPS;   // shared-memory rows (32 words) of a warp
 constexpr int TC_STAT_ROWS = TC_FW;       // + per-class bucket counts of the warp's column (u16 x 2 classes), fit only
 
@@ -407,7 +416,7 @@ text_cells_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
                 for (;;) {
                     const bool must = pend > 0 && (last || (active && (p_carry ? (p_start >> 4) : hc) <= ci - 4));
                     const unsigned have = __ballot_sync(FULL, pend > 0);
-                    if (!(__any_sync(FULL, must || pend >= 12) || __popc(have) >= TC_ROUND_LANES)) break;
+                    if (!(__any_sync(FULL, must || pend >= TC_PEND_V) || __popc(have) >= TC_ROUND_LANES)) break;
                     if (pend > 0) {
                         while (h_end == 0u) {                      // on to the next chunk that holds a token end
                             if (h_start) {

@@ -208,8 +208,12 @@ class OpTextPivotVectorizer(OpEstimator):
         L.call("tmog_pivot_count_dev", dev.codes.data_ptr(), dev.ld, n, ncols,
                ids.data_ptr() if ids is not None else None, st["ncls"], st["d_desc"].data_ptr(), None,
                int(st["nids"].max()) if ncols else 1, d_counts.data_ptr(), st["bad"].data_ptr(), R.stream())
-        wide = d_counts.to(torch.int64) & 0xFFFFFFFF
-        st["acc"] = wide if st["acc"] is None else st["acc"].add_(wide)
+        if st["calls"] == 0:
+            st["first"] = d_counts                    # one batch: the uint32 table goes to the host as it is
+        else:
+            if st["acc"] is None:
+                st["acc"] = st.pop("first").to(torch.int64) & 0xFFFFFFFF
+            st["acc"].add_(d_counts.to(torch.int64) & 0xFFFFFFFF)
         if cont is not None:
             # continuous label: the label sums of every raw code next to the plain counts (one class)
             L.call("tmog_pivot_label_sum_dev", dev.codes.data_ptr(), dev.ld, n, ncols, st["d_desc"].data_ptr(), None,
@@ -227,20 +231,33 @@ class OpTextPivotVectorizer(OpEstimator):
         st0 = scans[0]
         nids, count_offset = st0["nids"], st0["count_offset"]
         shared_dicts = all(m is None for m in g_maps)
-        if any(int(st["bad"].item()) for st in scans):
-            raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
+        def host_counts(st) -> np.ndarray:
+            """int64 counts of one accumulator on the host (a single call's uint32 table through pinned memory)"""
+            if st.get("acc") is None:
+                d32 = st["first"]
+                pinned = torch.empty(d32.shape, dtype=torch.int32, pin_memory=True)
+                pinned.copy_(d32, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                return pinned.numpy().view(np.uint32).astype(np.int64)
+            return st["acc"].cpu().numpy().copy()
+
+        def device_counts(st) -> torch.Tensor:
+            return st["acc"] if st.get("acc") is not None else st["first"].to(torch.int64) & 0xFFFFFFFF
+
         if len(scans) == 1 and D.world()[1] > 1 and shared_dicts:
             # every rank counted against the same dictionaries: the tables add up on the device, one copy back
-            g_dev = st0["acc"].clone()
+            g_dev = device_counts(st0).clone()
             torch.distributed.all_reduce(g_dev)
             counts = g_dev.cpu().numpy()
             summed = True
         else:
-            counts = st0["acc"].cpu().numpy().copy()
+            counts = host_counts(st0)
             summed = False
+        if any(int(st["bad"].item()) for st in scans):
+            raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
         ws = None if cont is None else st0["ws"].cpu().numpy().copy()
         for st in scans[1:]:                                 # row chunks that came with other dictionaries
-            loc = st["acc"].cpu().numpy()
+            loc = host_counts(st)
             lws = None if cont is None else st["ws"].cpu().numpy()
             for c in range(ncols):
                 m = st["maps"][c]
@@ -397,14 +414,15 @@ class OpTextPivotVectorizer(OpEstimator):
             first = scans[0]
             wide = self._scan_begin(dicts, ncls, first["ws"] is not None)
             acc = torch.zeros(max(wide["total_bins"], 1), dtype=torch.int64, device="cuda")
+            first_acc = first["acc"] if first.get("acc") is not None else first["first"].to(torch.int64) & 0xFFFFFFFF
             for c in range(ncols):
                 a, k = int(first["count_offset"][c]), int(first["nids"][c]) * ncls
                 b = int(wide["count_offset"][c])
-                acc[b:b + k] = first["acc"][a:a + k]
+                acc[b:b + k] = first_acc[a:a + k]
                 if first["ws"] is not None:
                     wa, wb, kk = int(first["w_off"][c]), int(wide["w_off"][c]), int(first["nids"][c])
                     wide["ws"][wb:wb + kk] = first["ws"][wa:wa + kk]
-            wide["acc"], wide["bad"] = acc, first["bad"]
+            wide["acc"], wide["bad"], wide["calls"] = acc, first["bad"], max(first["calls"], 2)
             first_tables = first["dicts"]
             scans = [wide] + scans[1:]
         block = DictBlock(st["names"], st["type_name"], torch.zeros((ncols, 4), dtype=torch.int32), dicts, 0)
@@ -515,7 +533,7 @@ class OpTextPivotVectorizerModel(OpModel):
         est._scan(st, dev, batch.n, ids if classes is not None else None, y, cont)
         if int(st["bad"].item()):
             raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
-        acc = st["acc"].cpu().numpy()
+        acc = (st["acc"] if st.get("acc") is not None else st["first"].to(torch.int64) & 0xFFFFFFFF).cpu().numpy()
         ws = None if cont is None else st["ws"].cpu().numpy()
         rows, wrows = [], []
         for c in range(len(names)):
@@ -574,28 +592,38 @@ class OpTextPivotVectorizerModel(OpModel):
         return OneHotPart(out[:, :ncols], out_width)
 
     def _position_tables(self, block: DictBlock, keep):
+        """Per column the table code -> output position (top value, OTHER, null indicator; -1 = dropped by
+        SanityChecker): the column index of every code is laid out once per set of dictionaries, the kept-column
+        renumbering is a gather on the device."""
         ncols = len(block.names)
         widths = self._widths()
         width = sum(widths)
-        newpos = np.arange(width, dtype=np.int32)
-        out_width = width
-        if keep is not None:
-            newpos = np.full(width, -1, dtype=np.int32)
+        key = (torch.cuda.current_device(), tuple(id(d) for d in block.dicts))
+        flats = self.__dict__.setdefault("_flat_tables", {})
+        hit = flats.get(key)
+        if hit is None or any(a is not b for a, b in zip(hit[2], block.dicts)):
+            offs = np.concatenate([[0], np.cumsum(widths)[:-1]]).astype(np.int64) if ncols else np.zeros(0, np.int64)
+            pieces = []
+            for c in range(ncols):
+                local = self._code_to_out(block, c)
+                tab = np.empty(len(local) + 1, dtype=np.int64)
+                tab[:-1] = offs[c] + local
+                tab[-1] = offs[c] + len(self.topValues[c]) + 1 if self.shouldTrackNulls else width   # width = "nothing"
+                pieces.append(tab)
+            flat = np.concatenate(pieces) if pieces else np.zeros(1, dtype=np.int64)
+            ncodes = np.array([len(d) for d in block.dicts], dtype=np.int64)
+            slot_off = np.concatenate([[0], np.cumsum(ncodes)[:-1]]).astype(np.int64) if ncols else ncodes
+            desc = np.ascontiguousarray(np.stack([ncodes + 1, slot_off, np.zeros_like(ncodes), ncodes], axis=1))
+            if len(flats) > 4:
+                flats.clear()
+            hit = flats[key] = (torch.from_numpy(flat).cuda(), torch.from_numpy(desc).cuda(), list(block.dicts))
+        d_flat, d_desc, _dicts = hit
+        newpos = np.full(width + 1, -1, dtype=np.int32)
+        if keep is None:
+            newpos[:width] = np.arange(width, dtype=np.int32)
+            out_width = width
+        else:
             newpos[np.asarray(keep, dtype=np.int64)] = np.arange(len(keep), dtype=np.int32)
             out_width = len(keep)
-        offs = np.concatenate([[0], np.cumsum(widths)[:-1]]).astype(np.int64) if ncols else np.zeros(0, np.int64)
-
-        def table(c: int) -> np.ndarray:
-            local = self._code_to_out(block, c)
-            tab = np.empty(len(local) + 1, dtype=np.int32)
-            tab[:-1] = newpos[offs[c] + local]
-            top_n = len(self.topValues[c])
-            tab[-1] = newpos[offs[c] + top_n + 1] if self.shouldTrackNulls else -1   # null -> indicator (or nothing)
-            return tab
-
-        tables = list(_pool().map(table, range(ncols))) if ncols > 1 else [table(c) for c in range(ncols)]
-        pos = np.concatenate(tables) if tables else np.zeros(1, dtype=np.int32)
-        ncodes = np.array([len(d) for d in block.dicts], dtype=np.int64)
-        slot_off = np.concatenate([[0], np.cumsum(ncodes)[:-1]]).astype(np.int64) if ncols else ncodes
-        desc = np.ascontiguousarray(np.stack([ncodes + 1, slot_off, np.zeros_like(ncodes), ncodes], axis=1))
-        return torch.from_numpy(desc).cuda(), torch.from_numpy(pos).cuda(), out_width
+        d_pos = torch.from_numpy(newpos).cuda().index_select(0, d_flat)
+        return d_desc, d_pos, out_width
