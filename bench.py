@@ -80,13 +80,41 @@ class ClockSampler(threading.Thread):
 
 
 
-def build_plan(feats, label, info):
+ALL_CPUS = os.sched_getaffinity(0)
+
+
+def bind_to_gpu_cpus(index: int):
+    """Run this process on the CPUs NVML reports as local to its GPU (the NUMA node behind the GPU's PCIe root), so that
+    the pinned host buffers it allocates afterwards -- first touch -- and the threads that fill them sit on that node:
+    with several ranks on one box each GPU then pulls its chunks over its own root complex instead of all of them
+    through node 0.  -> the CPU list, or None when NVML gives none."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(index)
+        ncpu = os.cpu_count() or 1
+        words = nv.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = [64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1 and 64 * w + b < ncpu]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return allowed
+    except Exception:
+        pass
+    return None
+
+
+def build_plan(feats, label, info, reference_defaults: bool = False):
     from transmogrifai_b200.dsl import TransmogrifierDefaults, transmogrify
 
     class Defaults(TransmogrifierDefaults):
         DefaultNumOfFeatures = info["num_features"]
 
     vec = transmogrify(feats, defaults=Defaults)
+    if reference_defaults:
+        # every SanityChecker default of the reference (SanityChecker.scala:561-581): above 1 M rows a sample of 1 M rows
+        # is checked, and the full feature-feature Pearson matrix is computed (the Gramian on the fp64 tensor cores)
+        return label.sanityCheck(vec, removeBadFeatures=True, sampleSeed=SEED)
     return label.sanityCheck(vec, removeBadFeatures=True, checkSample=1.0, sampleLowerLimit=0,
                              sampleUpperLimit=2 ** 31 - 1, featureFeatureCorrLevel="Off")
 
@@ -511,13 +539,17 @@ def parity_check_stream(ring, feats, label, info, world: int):
 
 
 def bench_single(wl: str, rows: int, steps: int, warmup: int, rank: int, world: int, local_rank: int, barrier,
-                 max_over_ranks, peak: float):
+                 max_over_ranks, peak: float, reference_defaults: bool = False):
     """One resident batch per GPU (c2 / c3 / c4, or the c5 shape at a size that fits): weak scaling."""
     import torch
     import benchdata
     from transmogrifai_b200 import _lib as L
     batch, feats, label, info = benchdata.make_workload(wl, rows, SEED + rank)
-    checked = build_plan(feats, label, info)
+    checked = build_plan(feats, label, info, reference_defaults)
+    if reference_defaults:
+        info = dict(info, desc=info["desc"] + " -- with every SanityChecker default of the reference: a sample of 1e6 "
+                                              "rows is checked and featureFeatureCorrLevel = Computed (full Pearson "
+                                              "matrix, Gramian on the fp64 tensor cores)")
     for _ in range(warmup):
         vec, fitted, parts = run_step(batch, checked)
         del vec, parts
@@ -540,6 +572,22 @@ def bench_single(wl: str, rows: int, steps: int, warmup: int, rank: int, world: 
     for k in kt:
         k["achieved"] = rows * k["bytes_per_row"] / (k["ms"] * 1e-3) / 1e9
         k["frac"] = k["achieved"] / peak
+    if reference_defaults and wl == "c2":
+        # the Gramian of the checked sample (fp64 tensor cores): upper-triangle flops 2 * n * D (D + 1) / 2
+        from transmogrifai_b200 import runtime as R
+        ns, dcol = 1_000_000, 200
+        x = torch.randn((ns, dcol), dtype=torch.float64, device="cuda")
+        yy = torch.randn(ns, dtype=torch.float64, device="cuda")
+        sh = torch.zeros(dcol + 1, dtype=torch.float64, device="cuda")
+        gram = torch.zeros((dcol + 1, dcol + 1), dtype=torch.float64, device="cuda")
+        t_g = _time(lambda: L.call("tmog_dense_gram_dev", x.data_ptr(), dcol, ns, dcol, yy.data_ptr(), sh.data_ptr(),
+                                   gram.data_ptr(), R.stream()), 3)
+        flops = float(ns) * (dcol + 1) * (dcol + 2)
+        kt.append({"kernel": "dense_gram_dmma_kernel (1e6 sampled rows x 201, fp64 mma.sync m8n8k4)", "ms": t_g,
+                   "bound": "tensor (fp64)", "tflops_upper_triangle": flops / (t_g * 1e-3) / 1e12,
+                   "bytes_per_row": (dcol + 1) * 8.0, "achieved": ns * (dcol + 1) * 8.0 / (t_g * 1e-3) / 1e9,
+                   "frac": None})
+        del x, yy, gram
     est = checked.origin_stage
     line = {"workload": info["desc"], "rows_per_gpu": rows, "ms_per_step": ms, "value": rows * world / (ms * 1e-3),
             "unit": "rows/s", "steps": steps, "warmup": warmup,
@@ -616,6 +664,7 @@ def main():
 
     import torch
     import torch.distributed as dist
+    numa = bind_to_gpu_cpus(local_rank)      # before any pinned allocation: first touch decides the NUMA node
     torch.cuda.set_device(local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
@@ -675,6 +724,7 @@ def main():
             del hbatch, parts, host
         cpu = None
         if rank == 0 and world == 1 and not args.no_cpu:
+            os.sched_setaffinity(0, ALL_CPUS)      # the CPU baseline runs on every host core
             secs, srows, used, sample = cpu_baseline(wl, cores, args.cpu_rows)
             cpu = {"value": srows / secs, "unit": "rows/s", "cores": used, "kind": "port",
                    "sample": f"{sample}, {secs:.2f} s"}
@@ -778,16 +828,17 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
+        os.sched_setaffinity(0, ALL_CPUS)          # the CPU baseline runs on every host core
         secs, srows, used, sample = cpu_baseline("c5", cores, args.cpu_rows)
         cpu = {"value": srows / secs, "unit": "rows/s", "cores": used, "kind": "port",
                "sample": f"{sample}, {secs:.2f} s"}
 
     others = []
     if world == 1 and not args.no_others:
-        for owl, osteps in (("c2", 10), ("c3", 5), ("c4", 3)):
+        for owl, osteps, refdef in (("c2", 10, False), ("c2", 5, True), ("c3", 5, False), ("c4", 3, False)):
             torch.cuda.empty_cache()
             oline, ob, _c, _f, _fe, _l, _i = bench_single(owl, benchdata.DEFAULT_ROWS[owl], osteps, 3, rank, world,
-                                                           local_rank, barrier, max_over_ranks, peak)
+                                                           local_rank, barrier, max_over_ranks, peak, refdef)
             del ob, _c, _f
             others.append(oline)
 
@@ -807,6 +858,7 @@ def main():
                                        "~740 GB of raw columns); every chunk is read in pass 1 and again in pass 2",
                        "l2": "a chunk (~7 GB) exceeds the 126 MB L2 many times over; no flush needed",
                        "metadata_caches": METADATA_NOTE,
+                       "host_cpus": (f"{len(numa)} CPUs local to the GPU (NVML affinity)" if numa else "not bound"),
                        "output_bytes_per_step": int(out_bytes_step),
                        "algorithmic_bytes_per_row": {"fit": info["fit_bytes"], "transform": info["transform_bytes"]},
                        **summary},
