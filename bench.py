@@ -138,11 +138,11 @@ def run_step(batch, checked):
     return vec, fitted, parts
 
 
-def run_stream_step(chunks, feats, label, info, sink=None):
+def run_stream_step(chunks, feats, label, info, sink=None, cache_bytes=0):
     """One step over a chunked dataset: a fresh plan (new stage objects), passes 0 / 1, decision, pass 2."""
     from transmogrifai_b200.streaming import fit_and_transform_stream
     checked = build_plan(feats, label, info)
-    res = fit_and_transform_stream(chunks, checked, sink)
+    res = fit_and_transform_stream(chunks, checked, sink, cache_bytes=cache_bytes)
     return checked, res
 
 
@@ -813,15 +813,19 @@ def main():
         hs = HostSink(depth=2)
         run_stream_step(hchunks[:min(4, len(hchunks))], feats, label, info, hs)      # warm-up: allocator, pinned buffers
         hs.bytes = 0
+        torch.cuda.empty_cache()
+        budget = int(torch.cuda.mem_get_info()[0] * 0.5)       # uploaded chunks stay resident up to this many bytes
         barrier()
         t0 = time.perf_counter()
-        run_stream_step(hchunks, feats, label, info, hs)
+        _c, eres = run_stream_step(hchunks, feats, label, info, hs, cache_bytes=budget)
         barrier()
         dt = max_over_ranks(time.perf_counter() - t0)
-        h2d = sum(2 * in_bytes[i % n_host] + label_bytes for i in range(len(hchunks))) + in_bytes[0]
+        kept = int(getattr(eres, "cache_hits", 0))
+        h2d = sum((2 if i >= kept else 1) * in_bytes[i % n_host] + label_bytes for i in range(len(hchunks))) + in_bytes[0]
         e2e = {"value": rows_e2e * world / dt, "unit": "rows/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(hs.bytes), "ms_per_step": dt * 1e3, "steps": 1, "rows": rows_e2e * world,
-               "distinct_host_chunks": n_host,
+               "distinct_host_chunks": n_host, "chunks_kept_in_hbm_between_passes": kept,
+               "hbm_cache_budget_bytes": budget,
                "api": "fit_and_transform_stream(pinned host chunks, label.sanityCheck(transmogrify(features)), HostSink)"}
         del hring, hchunks, hs
         torch.cuda.empty_cache()

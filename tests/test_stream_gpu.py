@@ -124,9 +124,12 @@ def test_seven_uneven_chunks_equal_one_batch_equal_oracle(mode, continuous):
     def sink(k, vec, parts):
         out.append(VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy())
 
-    res = fit_and_transform_stream(chunks, checked, sink)
+    # host chunks stay resident in HBM between the fit and the transform when they fit (here: all seven)
+    host = mode == "own_dictionaries_host"
+    res = fit_and_transform_stream(chunks, checked, sink, cache_bytes=None if host else 0)
     est = checked.origin_stage
     assert res.rows == sum(SIZES) and res.chunks == len(SIZES) and len(out) == len(SIZES)
+    assert res.cache_hits == (len(SIZES) if host else 0)
     _check(est, res.fitted[-1].indicesToKeep, sp.vstack(out).tocsr(), ref, xo, metas)
     streamed = (list(est.summary.dropped), est.summary.mean.copy(), est.summary.variance.copy(),
                 est.summary.correlationsWithLabel.copy())

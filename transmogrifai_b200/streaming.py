@@ -179,7 +179,39 @@ def _block_tensors(block):
                     yield t
 
 
-def device_chunks(chunks: Iterable[ColumnarBatch], depth: int = 1):
+class ChunkCache:
+    """Uploaded chunks kept in HBM between pass 1 and pass 2 (by their position in the stream) as long as they fit a
+    byte budget: a partition that is still resident when the transform comes needs no second trip over PCIe -- the
+    streamed counterpart of ColumnarBatch.on_device sharing one upload between an estimator's fit and its model's
+    transform.  budget = None: half of the device memory that is free when the cache is made."""
+
+    def __init__(self, budget: Optional[int] = None):
+        if budget is None:
+            free, _total = torch.cuda.mem_get_info()
+            budget = free // 2
+        self.budget, self.used, self.hits = int(budget), 0, 0
+        self.items: Dict[int, ColumnarBatch] = {}
+
+    @staticmethod
+    def nbytes(chunk: ColumnarBatch) -> int:
+        return sum(t.numel() * t.element_size() for b in chunk.blocks for t in _block_tensors(b))
+
+    def offer(self, k: int, dev: ColumnarBatch) -> None:
+        nb = self.nbytes(dev)
+        if k not in self.items and self.used + nb <= self.budget:
+            self.items[k] = dev
+            self.used += nb
+
+    def take(self, k: int) -> Optional[ColumnarBatch]:
+        dev = self.items.pop(k, None)
+        if dev is not None:
+            self.used -= self.nbytes(dev)
+            self.hits += 1
+        return dev
+
+
+def device_chunks(chunks: Iterable[ColumnarBatch], depth: int = 1, cache: Optional[ChunkCache] = None,
+                  fill: bool = False):
     """The chunks in HBM, in order.  Chunks that are there already pass through; a chunk in (pinned) host memory is
     copied on a side stream while the chunks before it are being worked on, `depth` chunks ahead -- partition k + 1
     crosses the link under partition k's kernels.  At most depth + 2 uploaded chunks exist at a time: the copy of a
@@ -189,10 +221,18 @@ def device_chunks(chunks: Iterable[ColumnarBatch], depth: int = 1):
     pending = []                       # [(device chunk, upload event)]
     done: List[torch.cuda.Event] = []  # work on earlier yielded chunks finished
 
+    index = [0]
+
     def upload(chunk: ColumnarBatch):
         nonlocal copy
+        k = index[0]
+        index[0] += 1
         if all(getattr(b, "is_cuda", True) for b in chunk.blocks):
             return chunk, None
+        if cache is not None and not fill:
+            kept = cache.take(k)                      # still resident from pass 1
+            if kept is not None:
+                return kept, None
         if copy is None:
             copy = torch.cuda.Stream()
         if len(done) > depth + 1:
@@ -201,7 +241,10 @@ def device_chunks(chunks: Iterable[ColumnarBatch], depth: int = 1):
             blocks = [b if b.is_cuda else b.to("cuda") for b in chunk.blocks]
             ev = torch.cuda.Event()
             ev.record(copy)
-        return ColumnarBatch(chunk.n, blocks, {}, chunk.response, chunk.token), ev
+        dev = ColumnarBatch(chunk.n, blocks, {}, chunk.response, chunk.token)
+        if cache is not None and fill:
+            cache.offer(k, dev)
+        return dev, ev
 
     def hand_over(item):
         dev, ev = item
@@ -306,7 +349,8 @@ class StreamResult:
 
 
 def fit_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, response: Optional[str] = None,
-               on_chunk: Optional[Callable[[int, int, ColumnarBatch], None]] = None) -> StreamResult:
+               on_chunk: Optional[Callable[[int, int, ColumnarBatch], None]] = None,
+               cache: Optional[ChunkCache] = None) -> StreamResult:
     """Passes 0 and 1 and the decisions: every stage of `result`'s DAG fitted over the chunks (`chunks` is iterated
     several times and must yield the same chunks in the same order each time).  on_chunk(pass, index, chunk) is called
     after a chunk has been queued (for callers that recycle staging buffers)."""
@@ -350,7 +394,7 @@ def fit_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, response: Opt
     for st in raw:
         worker = fitters.get(id(st), st)
         accs.append((st, worker, worker.stream_begin(label)))
-    for k, chunk in enumerate(device_chunks(chunks)):
+    for k, chunk in enumerate(device_chunks(chunks, cache=cache, fill=True)):
         if label is not None:
             label.prime(chunk)
         for _st, worker, acc in accs:
@@ -390,7 +434,8 @@ def fit_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, response: Opt
 
 def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: StreamResult,
                      sink: Optional[Callable[[int, VectorColumn, list], None]] = None,
-                     on_chunk: Optional[Callable[[int, int, ColumnarBatch], None]] = None) -> int:
+                     on_chunk: Optional[Callable[[int, int, ColumnarBatch], None]] = None,
+                     cache: Optional[ChunkCache] = None) -> int:
     """Pass 2: the fitted stages applied chunk by chunk.  sink(index, vector, parts) receives the materialised parts of
     `result`'s vector for every chunk (device tensors; they may be overwritten once sink returns only if the sink
     copied or consumed them on the current stream).  -> rows transformed."""
@@ -398,7 +443,7 @@ def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: St
     flags = torch.zeros(4, dtype=torch.int32, device="cuda")
     flags_clean = torch.zeros(4, dtype=torch.int32, device="cuda")
     rows = 0
-    for k, chunk in enumerate(device_chunks(chunks)):
+    for k, chunk in enumerate(device_chunks(chunks, cache=cache)):
         batch = ColumnarBatch(chunk.n, chunk.blocks, {}, None, chunk.token)          # no response: no statistics
         batch.__dict__["_dev_cache"] = chunk.__dict__.setdefault("_dev_cache", {})
         batch.__dict__["_stream"] = {"index": k, "token": chunk.token, "flags": flags, "flags_clean": flags_clean}
@@ -427,8 +472,15 @@ def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: St
 
 
 def fit_and_transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, sink=None,
-                             response: Optional[str] = None, on_chunk=None) -> StreamResult:
-    """OpWorkflow.train() over row chunks: fit_stream, then transform_stream of the same chunks."""
-    fit = fit_stream(chunks, result, response, on_chunk)
-    transform_stream(chunks, result, fit, sink, on_chunk)
+                             response: Optional[str] = None, on_chunk=None, cache_bytes: Optional[int] = 0
+                             ) -> StreamResult:
+    """OpWorkflow.train() over row chunks: fit_stream, then transform_stream of the same chunks.  cache_bytes: HBM
+    budget for host chunks that stay resident between the two (0 = none, None = half of the free device memory)."""
+    cache = None if cache_bytes == 0 else ChunkCache(cache_bytes)
+    fit = fit_stream(chunks, result, response, on_chunk, cache)
+    fit.cache_hits = 0
+    transform_stream(chunks, result, fit, sink, on_chunk, cache)
+    if cache is not None:
+        fit.cache_hits = cache.hits
+        cache.items.clear()
     return fit
