@@ -61,7 +61,8 @@ def test_cell_path_slow_path_and_row_table_path_agree(num_features, binary, min_
     names = block.names
     out = {}
     try:
-        for mode, env in (("cells", {}), ("slow", {"TMOG_TEXT_FORCE_SLOW": "1"}), ("rows", {"TMOG_TEXT_PATH": "rows"})):
+        for mode, env in (("span", {}), ("cells", {"TMOG_TEXT_PATH": "cells"}), ("slow", {"TMOG_TEXT_FORCE_SLOW": "1"}),
+                          ("rows", {"TMOG_TEXT_PATH": "rows"})):
             for k in ("TMOG_TEXT_FORCE_SLOW", "TMOG_TEXT_PATH"):
                 os.environ.pop(k, None)
             os.environ.update(env)
@@ -71,7 +72,7 @@ def test_cell_path_slow_path_and_row_table_path_agree(num_features, binary, min_
             os.environ.pop(k, None)
     ref_st, ref_rows, ref_rows2 = out["rows"]
     assert abs(ref_rows - ref_rows2).max() == 0
-    for mode in ("cells", "slow"):
+    for mode in ("span", "cells", "slow"):
         st, rows, rows2 = out[mode]
         for k in ("mean", "variance", "min", "max", "cov_label"):
             assert np.array_equal(getattr(st, k), getattr(ref_st, k)), (mode, k)

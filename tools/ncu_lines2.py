@@ -18,7 +18,7 @@ for ln in dis.splitlines():
     m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
     if m:
         f = m.group(1).split("/")[-1]
-        if f in ("text.cu", "text_cells.cuh"):
+        if f in ("text.cu", "text_cells.cuh", "text_span.cuh"):
             cur = (f, int(m.group(2)))
         continue
     m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", ln)
@@ -44,7 +44,7 @@ for r in rows[hi + 1:]:
     ins[key] += float(r[ci]); smp[key] += float(r[si]); thr[key] += float(r[ti])
 tot, tots = sum(ins.values()), sum(smp.values())
 src = {}
-for f in ("text.cu", "text_cells.cuh"):
+for f in ("text.cu", "text_cells.cuh", "text_span.cuh"):
     try:
         src[f] = open("transmogrifai_b200/csrc/" + f).read().splitlines()
     except OSError:
@@ -58,7 +58,7 @@ if len(sys.argv) > 6:
     for spec in sys.argv[6].split(","):
         name, rng = spec.split(":")
         lo, hi = map(int, rng.split("-"))
-        f = "text.cu" if name.startswith("T_") else "text_cells.cuh"
+        f = "text.cu" if name.startswith("T_") else "text_span.cuh" if name.startswith("S_") else "text_cells.cuh"
         v = sum(x for k, x in ins.items() if k and k[0] == f and lo <= k[1] <= hi)
         t = sum(x for k, x in thr.items() if k and k[0] == f and lo <= k[1] <= hi)
         print(f"{name:24s} {100*v/tot:5.1f}% ins   lanes {t/max(v,1):4.1f}")

@@ -1,4 +1,5 @@
-"""A/B of the text passes of one config-5 chunk: per-cell kernels against the row-table kernel (TMOG_TEXT_PATH=rows)."""
+"""A/B of the text passes of one config-5 chunk: the span kernel (default), the lane-per-cell kernel
+(TMOG_TEXT_PATH=cells) and the row-table kernel (TMOG_TEXT_PATH=rows)."""
 import os
 import sys
 import time
@@ -15,8 +16,9 @@ rows = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
 batch, feats, label, info = benchdata.make_workload("c5", rows, 1)
 checked = bench.build_plan(feats, label, info)
 out, fitted = fit_and_transform(batch, checked)
-for mode in (("cells",) if os.environ.get("AB_CELLS_ONLY") else ("cells", "rows")):
-    if mode == "rows":
-        os.environ["TMOG_TEXT_PATH"] = "rows"
+for mode in os.environ.get("AB_MODES", "span,cells,rows").split(","):
+    os.environ.pop("TMOG_TEXT_PATH", None)
+    if mode != "span":
+        os.environ["TMOG_TEXT_PATH"] = mode
     kt = bench.kernel_times("c5", batch, fitted, info, reps=4, text_offset=bench._text_offset(fitted))
     print(mode, [(k["kernel"][:44], round(k["ms"], 2)) for k in kt if "text" in k["kernel"]], flush=True)

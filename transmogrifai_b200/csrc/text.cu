@@ -114,6 +114,12 @@ __host__ __device__ inline int stop_pre_index(unsigned c0, unsigned c1) {   // c
     const unsigned k1 = (c1 - 'a') < 26u ? c1 - 'a' : (c1 == '\'' ? 26u : 27u);
     return (int)((c0 - 'a') * 28u + k1);
 }
+// second filter (text_span_kernel): one bit per (first four bytes, length) of a stop word, 4096 bits
+constexpr int STOP_BLOOM_WORDS = 128;
+__constant__ unsigned c_stop_bloom[STOP_BLOOM_WORDS];
+__host__ __device__ inline unsigned stop_bloom_index(unsigned first4, unsigned len) {   // first4: bytes past len are 0
+    return ((first4 * 0x9E3779B1u) ^ (len * 0x85EBCA6Bu)) >> 20;
+}
 
 // ------------------------------------------------------------------------------------------------------------------
 // column descriptors
@@ -1221,6 +1227,7 @@ sparse_rows_select_kernel(const int64_t* __restrict__ row_start, const int32_t* 
 }  // namespace tmog
 
 #include "text_cells.cuh"
+#include "text_span.cuh"
 
 using namespace tmog;
 // Snowball english_stop.txt (174 words) as loaded by Lucene's StandardAnalyzer in the reference
@@ -1290,6 +1297,17 @@ static int upload_stop_words() {
         pre[stop_pre_index((unsigned char)w[0], len > 1 ? (unsigned char)w[1] : 0u)] |= (unsigned short)(1u << len);
     }
     TMOG_CUDA(cudaMemcpyToSymbol(c_stop_pre, pre, sizeof(pre)));
+    static unsigned bloom[STOP_BLOOM_WORDS];
+    memset(bloom, 0, sizeof(bloom));
+    for (int i = 0; i < nwords; ++i) {
+        const char* w = kStopWords[i];
+        const size_t len = strlen(w);
+        unsigned first4 = 0u;
+        for (size_t q = 0; q < len && q < 4; ++q) first4 |= (unsigned)(unsigned char)w[q] << (8 * q);
+        const unsigned b = stop_bloom_index(first4, (unsigned)len);
+        bloom[b >> 5] |= 1u << (b & 31);
+    }
+    TMOG_CUDA(cudaMemcpyToSymbol(c_stop_bloom, bloom, sizeof(bloom)));
     if (dev >= 0 && dev < 64) done[dev] = true;
     return TMOG_OK;
 }
@@ -1562,17 +1580,23 @@ static int tc_run(const ThArgs& a) {
     unsigned* records = reinterpret_cast<unsigned*>(base + 256 + keepw_bytes + bits_bytes);
     TMOG_CUDA(cudaMemsetAsync(base, 0, 256, a.stream));
     TMOG_CUDA(cudaMemsetAsync(defer_bits, 0, bits_bytes, a.stream));
-    auto kernel = text_cells_kernel<STATS, CELLS>;
-    const size_t smem = TH_STOP_PRE_BYTES + 64 + (size_t)TC_WARPS * (TC_WARP_ROWS + (STATS ? TC_STAT_ROWS : 0)) * 32 * 4;
+    // TMOG_TEXT_PATH=cells: the lane-per-cell kernel (kept for comparison); default: the span kernel
+    const char* path = getenv("TMOG_TEXT_PATH");
+    const bool lane_cells = path && strcmp(path, "cells") == 0;
+    auto kernel = lane_cells ? text_cells_kernel<STATS, CELLS> : text_span_kernel<STATS, CELLS>;
+    const int threads = lane_cells ? TC_WARPS * 32 : TS_WARPS * 32;
+    const size_t smem = lane_cells
+        ? TH_STOP_PRE_BYTES + 64 + (size_t)TC_WARPS * (TC_WARP_ROWS + (STATS ? TC_STAT_ROWS : 0)) * 32 * 4
+        : TS_FIXED_SMEM + (STATS ? 2 * TC_MAXF * 4 : 0) + (size_t)TS_WARPS * TS_WARP_BYTES;
     TMOG_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, TC_WARPS * 32, smem));
+    TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
     TMOG_REQUIRE(per_sm >= 1, "text cell kernel does not fit an SM");
     const int64_t items = ((a.n + TC_ITEM_ROWS - 1) / TC_ITEM_ROWS) * a.ncols;
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)sm_count() * per_sm, items));
-    kernel<<<grid, TC_WARPS * 32, smem, a.stream>>>(a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, a.class_ids, sc,
-                                                    defer_bits, a.class_sum, a.dup, a.sq_extra, a.aux, a.label,
-                                                    a.label_shift, a.wsum, records, a.flags);
+    kernel<<<grid, threads, smem, a.stream>>>(a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, a.class_ids, sc,
+                                              defer_bits, a.class_sum, a.dup, a.sq_extra, a.aux, a.label,
+                                              a.label_shift, a.wsum, records, a.flags);
     TMOG_LAUNCH_CHECK();
     if (STATS) {
         const int64_t words = ((int64_t)a.n * a.ncols + 31) / 32;
