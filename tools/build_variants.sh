@@ -19,5 +19,12 @@ for v in "$@"; do
     w4) build w4 -DTC_WARPS_V=4 ;;
     w12) build w12 -DTC_WARPS_V=12 ;;
     w16) build w16 -DTC_WARPS_V=16 ;;
+    ir8k) build ir8k -DTS_ITEM_ROWS_V=8192 ;;
+    ir4k) build ir4k -DTS_ITEM_ROWS_V=4096 ;;
+    ir1k) build ir1k -DTS_ITEM_ROWS_V=1024 ;;
+    sw4) build sw4 -DTS_WARPS_V=4 ;;
+    sw6) build sw6 -DTS_WARPS_V=6 ;;
+    sw12) build sw12 -DTS_WARPS_V=12 ;;
+    sw24) build sw24 -DTS_WARPS_V=24 ;;
   esac
 done

@@ -50,7 +50,7 @@ for f in ("text.cu", "text_cells.cuh", "text_span.cuh"):
     except OSError:
         src[f] = []
 print(f"total warp instructions {tot:.3e}, samples {tots:.0f}")
-for key, v in sorted(ins.items(), key=lambda kv: -kv[1])[:top]:
+for key, v in sorted(ins.items(), key=(lambda kv: -smp[kv[0]]) if __import__("os").environ.get("BY_SAMPLES") else (lambda kv: -kv[1]))[:top]:
     text = src[key[0]][key[1] - 1].strip()[:90] if key and key[1] - 1 < len(src.get(key[0], [])) else ""
     print(f"{100*v/tot:5.1f}% ins {100*smp[key]/max(tots,1):5.1f}% smp  lanes {thr[key]/max(v,1):4.1f}  {key}  {text}")
 if len(sys.argv) > 6:

@@ -1592,7 +1592,8 @@ static int tc_run(const ThArgs& a) {
     int per_sm = 0;
     TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
     TMOG_REQUIRE(per_sm >= 1, "text cell kernel does not fit an SM");
-    const int64_t items = ((a.n + TC_ITEM_ROWS - 1) / TC_ITEM_ROWS) * a.ncols;
+    const int item_rows = lane_cells ? TC_ITEM_ROWS : TS_ITEM_ROWS;
+    const int64_t items = ((a.n + item_rows - 1) / item_rows) * a.ncols;
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)sm_count() * per_sm, items));
     kernel<<<grid, threads, smem, a.stream>>>(a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, a.class_ids, sc,
                                               defer_bits, a.class_sum, a.dup, a.sq_extra, a.aux, a.label,

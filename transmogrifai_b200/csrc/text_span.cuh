@@ -21,7 +21,15 @@
 
 namespace tmog {
 
-constexpr int TS_WARPS = 8;
+#ifndef TS_WARPS_V
+#define TS_WARPS_V 8
+#endif
+#ifndef TS_ITEM_ROWS_V
+#define TS_ITEM_ROWS_V 2048
+#endif
+constexpr int TS_WARPS = TS_WARPS_V;
+constexpr int TS_MIN_CTAS = 24 / TS_WARPS;   // 24 warps per SM at 80 registers
+constexpr int TS_ITEM_ROWS = TS_ITEM_ROWS_V;   // rows of one column a CTA takes at a time
 constexpr int TS_SLAB = 512;               // bytes of a step
 constexpr int TS_RING_WORDS = 512;         // the last four slabs
 constexpr int TS_RING_PAD = 8;             // + the first words again behind the last (a token is read without a wrap)
@@ -105,7 +113,7 @@ __device__ __forceinline__ unsigned ts_compress(const unsigned (&t)[4]) {
 constexpr int TS_FIXED_SMEM = TH_STOP_PRE_BYTES + 64 + TS_BLOOM_WORDS * 4;
 
 template <bool STATS, bool CELLS>
-__global__ void __launch_bounds__(TS_WARPS * 32, 3)
+__global__ void __launch_bounds__(TS_WARPS * 32, TS_MIN_CTAS)
 text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, const uint8_t* __restrict__ prefix,
                  const int* __restrict__ prefix_len, TcParams p, const uint8_t* __restrict__ class_ids,
                  TcScratch* __restrict__ scratch, unsigned* __restrict__ defer_bits,
@@ -134,7 +142,7 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
     for (int i = tid; i < STOP_PRE; i += TS_WARPS * 32) stop_pre[i] = c_stop_pre[i];
     for (int i = tid; i < TS_BLOOM_WORDS; i += TS_WARPS * 32) bloom[i] = c_stop_bloom[i];
 
-    const int64_t items_per_col = (n + TC_ITEM_ROWS - 1) / TC_ITEM_ROWS;
+    const int64_t items_per_col = (n + TS_ITEM_ROWS - 1) / TS_ITEM_ROWS;
     const int64_t nitems = items_per_col * ncols;
     const int F = p.num_features;
     const bool two_classes = p.nclasses <= 2;
@@ -149,7 +157,7 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
             item_info[0] = (unsigned)(it & 0xffffffffu);
             item_info[1] = (unsigned)(it >> 32);
             if ((int64_t)it < nitems) {
-                const int j = (int)((int64_t)it / items_per_col);
+                const int j = (int)((int64_t)it % ncols);
                 Murmur pm;
                 pm.init();
                 const int plen = p.prepend ? prefix_len[j] : 0;
@@ -164,8 +172,10 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
         __syncthreads();
         const int64_t item = (int64_t)(((unsigned long long)item_info[1] << 32) | item_info[0]);
         if (item >= nitems) break;
-        const int j = (int)(item / items_per_col);
-        const int64_t r_lo = (item % items_per_col) * TC_ITEM_ROWS, r_hi = min(n, r_lo + TC_ITEM_ROWS);
+        // items run over the columns first: the CTAs at work at any time are spread over all columns, and so are their
+        // atomics on the columns' statistics
+        const int j = (int)(item % ncols);
+        const int64_t r_lo = (item / ncols) * TS_ITEM_ROWS, r_hi = min(n, r_lo + TS_ITEM_ROWS);
         const unsigned ph = item_info[2], pw = item_info[3], pn = item_info[4];
         const TextColumn tc = cols[j];
         const bool hashed = j < p.n_hashed;
@@ -444,20 +454,29 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
             int ndup = 0;
             const int na = (int)min(napp[lane], (unsigned)TS_APP);
             if (__any_sync(FULL, na > 0)) {
-                // the appended buckets collapse, in place, to (bucket | count << 9) of the distinct ones
+                // the appended buckets collapse, in place, to (bucket | count << 9) of the distinct ones.  Every appended
+                // bucket has its bit in the cell's bitmap: the first time it is met here the bit is cleared (and set
+                // again below), so that only a bucket met three times or more has to be looked up in the list
                 for (int q = 0; q < na; ++q) {
                     const unsigned b = app[q * 32 + lane];
-                    int at = -1;
-                    for (int r = 0; r < ndup; ++r)
-                        if ((app[r * 32 + lane] & 0x1ffu) == b) at = r;
-                    if (at >= 0) {
-                        app[at * 32 + lane] += 0x200u;
-                    } else if (ndup < TC_DUPS) {
-                        app[ndup * 32 + lane] = (unsigned short)(b | (2u << 9));
-                        ++ndup;
+                    const unsigned bit = 1u << (b & 31u);
+                    const unsigned w = mybm[b >> 5];
+                    if (w & bit) {
+                        if (ndup < TC_DUPS) {
+                            mybm[b >> 5] = w & ~bit;
+                            app[ndup * 32 + lane] = (unsigned short)(b | (2u << 9));
+                            ++ndup;
+                        } else {
+                            deferred = true;                         // more distinct repeated buckets than a record holds
+                        }
                     } else {
-                        deferred = true;
+                        for (int r = 0; r < ndup; ++r)
+                            if ((app[r * 32 + lane] & 0x1ffu) == b) app[r * 32 + lane] += 0x200u;
                     }
+                }
+                for (int q = 0; q < ndup; ++q) {
+                    const unsigned b = app[q * 32 + lane] & 0x1ffu;
+                    mybm[b >> 5] |= 1u << (b & 31u);
                 }
             }
             if (deferred && in_rows) {
