@@ -375,6 +375,29 @@ int tmog_text_hash_fit_transform_dev(const int64_t* col_desc, int ncols, int64_t
                                      int32_t* out_idx, int32_t* out_val, uint64_t* cursor, int64_t capacity,
                                      int32_t* flags, void* scratch, size_t scratch_bytes, void* stream);
 
+/* Packed cells: the statistics pass of a row chunk can keep what it found in every cell -- the cell's buckets and their
+ * term frequencies, ~2 bytes per distinct token -- so that the transform of the same rows, which a chunk-streamed
+ * fit-then-transform runs after all chunks have been fitted (FitStagesUtil.scala:212-290; the reference tokenises and
+ * hashes the rows again, SmartTextVectorizer.scala:333-356), reads ~1.5 KB per row instead of the text and tokenises
+ * nothing.  Separate hash spaces of at most 512 buckets per column only (tmog_text_hash_scratch_bytes2's layout).
+ *   arena: device memory shared by all chunks, arena_cursor (device u64, zeroed once) counts the u16 entries handed
+ *          out; pack_meta: per chunk, tmog_text_cells_pack_bytes bytes (track_len = the vector has text-length
+ *          columns, params[9] > 0); pack_flags[0] is set when the arena was too small for this chunk -- its packed
+ *          cells are then unusable and the chunk is transformed from its text (tmog_text_hash_transform_dev).
+ *   _stats_pack_dev = tmog_text_hash_stats_dev + the packed cells of the chunk;
+ *   _transform_packed_dev = tmog_text_hash_transform_dev's outputs (same entries, same order) from the packed cells. */
+int tmog_text_cells_pack_bytes(int64_t n, int ncols, int track_len, size_t* meta_bytes);
+int tmog_text_hash_stats_pack_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
+                                  const int32_t* prefix_len, const int32_t* params, const uint8_t* class_ids,
+                                  uint32_t* bucket_class_sum, uint32_t* bucket_dup, uint64_t* bucket_sq_extra,
+                                  uint32_t* bucket_aux, const double* label, double label_shift, double* bucket_wsum,
+                                  int32_t* flags, void* scratch, size_t scratch_bytes, void* pack_meta, void* arena,
+                                  uint64_t arena_bytes, uint64_t* arena_cursor, int32_t* pack_flags, void* stream);
+int tmog_text_hash_transform_packed_dev(int ncols, int64_t n, const int32_t* params, void* pack_meta, void* arena,
+                                        uint64_t arena_bytes, const int32_t* newpos, int64_t* row_start, int32_t* row_nnz,
+                                        int32_t* out_idx, int32_t* out_val, uint64_t* cursor, int64_t capacity,
+                                        int32_t* flags, void* stream);
+
 /* Replaces SanityCheckerModel.transformFn -> removeFeatures (C/stages/impl/preparators/DerivedFeatureFilterUtils.scala:
  * 291-305) on sparse rows in 4-array CSR form: row r keeps the entries whose newpos [index] >= 0, as (newpos, value),
  * in order.  Call once with out_start = NULL to get out_nnz [n], prefix-sum it into out_start [n], call again to write

@@ -109,8 +109,8 @@ def _check(est, keep, rows, ref, xo, metas):
 
 
 @pytest.mark.parametrize("mode", ["shared_dictionaries_device", "own_dictionaries_host"])
-@pytest.mark.parametrize("continuous", [False, True])
-def test_seven_uneven_chunks_equal_one_batch_equal_oracle(mode, continuous):
+@pytest.mark.parametrize("continuous,cells", [(False, 0), (True, 0), (False, 64 << 20), (True, 64 << 20)])
+def test_seven_uneven_chunks_equal_one_batch_equal_oracle(mode, continuous, cells):
     from transmogrifai_b200.columnar import ColumnarBatch, VectorColumn
     from transmogrifai_b200.dsl import fit_and_transform
     from transmogrifai_b200.streaming import fit_and_transform_stream
@@ -126,10 +126,13 @@ def test_seven_uneven_chunks_equal_one_batch_equal_oracle(mode, continuous):
 
     # host chunks stay resident in HBM between the fit and the transform when they fit (here: all seven)
     host = mode == "own_dictionaries_host"
-    res = fit_and_transform_stream(chunks, checked, sink, cache_bytes=None if host else 0)
+    # cells: the text cells of every chunk stay packed in HBM after pass 1 and pass 2 reads them instead of the text
+    res = fit_and_transform_stream(chunks, checked, sink, cache_bytes=None if host and not cells else 0,
+                                   cell_cache_bytes=cells)
     est = checked.origin_stage
     assert res.rows == sum(SIZES) and res.chunks == len(SIZES) and len(out) == len(SIZES)
-    assert res.cache_hits == (len(SIZES) if host else 0)
+    assert res.cache_hits == (len(SIZES) if host and not cells else 0)
+    assert res.cells_cached == (len(SIZES) if cells else 0)
     _check(est, res.fitted[-1].indicesToKeep, sp.vstack(out).tocsr(), ref, xo, metas)
     streamed = (list(est.summary.dropped), est.summary.mean.copy(), est.summary.variance.copy(),
                 est.summary.correlationsWithLabel.copy())
@@ -177,3 +180,53 @@ def test_stream_transform_of_other_rows_and_empty_input():
     assert got.shape == exp.shape and abs(got - exp).max() < 1e-12
     with pytest.raises(ValueError):
         fit_stream([], _plan())
+
+
+@pytest.mark.parametrize("arena,slow", [(32 << 20, False), (32 << 20, True), (300000, False)])
+def test_packed_cells_give_the_rows_the_text_gives(arena, slow, monkeypatch):
+    """Pass 2 from the packed cells of pass 1 (tmog_text_hash_transform_packed_dev) against pass 2 from the text: the
+    same sparse rows, entry for entry -- with text lengths, an ignored column and dropped columns; with every cell on
+    the slow path (slots); and with an arena that holds only the first chunks (the others fall back to their text)."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch, VectorColumn
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    from transmogrifai_b200.streaming import fit_and_transform_stream
+    from tests.test_text_paths_gpu import SPECIAL
+    rng = np.random.default_rng(11)
+    n = 6000
+    words = ["".join(rng.choice(list("abcdefghij"), size=rng.integers(2, 9))) for _ in range(400)] + ["the", "and", "it's"]
+    def cell(i):
+        u = rng.random()
+        if u < 0.05:
+            return None
+        if u < 0.08:
+            return SPECIAL[i % len(SPECIAL)]
+        return " ".join(words[k] for k in rng.zipf(1.2, size=rng.poisson(25)) % len(words))
+    cols = {f"t{j}": (F.TEXT, [cell(i) for i in range(n)]) for j in range(3)}
+    cols["id"] = (F.TEXT, [f"row {i}" for i in range(n)])                       # ignored: every value differs
+    y = (rng.random(n) < 0.4).astype(np.float64)
+    cols["y"] = (F.REALNN, y.tolist())
+    bounds = [0, 1000, 1001, 3500, 6000]
+    chunks = [ColumnarBatch.from_columns({k: (t, v[a:b]) for k, (t, v) in cols.items()}, response="y")
+              for a, b in zip(bounds[:-1], bounds[1:])]
+
+    def run(cell_bytes):
+        feats = [F.FeatureBuilder.Text(nm).asPredictor() for nm in ("t0", "t1", "t2", "id")]
+        label = F.FeatureBuilder.RealNN("y").asResponse()
+        vec = SmartTextVectorizer().setMaxCardinality(5).setNumFeatures(512).setTrackTextLen(True) \
+            .setMinLengthStdDev(0.5).setInput(*feats).getOutput()
+        checked = label.sanityCheck(vec, removeBadFeatures=True, sampleLowerLimit=0, sampleUpperLimit=10 ** 9,
+                                    featureFeatureCorrLevel="Off", minVariance=1e-3)
+        out = []
+        res = fit_and_transform_stream(chunks, checked, lambda k, v, parts: out.append(
+            VectorColumn(v.name, v.n, v.metadata, parts).to_scipy()), cell_cache_bytes=cell_bytes)
+        return sp.vstack(out).tocsr(), res, checked.origin_stage.summary.dropped
+
+    if slow:
+        monkeypatch.setenv("TMOG_TEXT_FORCE_SLOW", "1")
+    ref, res0, dropped0 = run(0)
+    got, res1, dropped1 = run(arena)
+    assert res0.cells_cached == 0 and dropped0 == dropped1 and len(dropped0) > 0
+    assert 0 < res1.cells_cached <= len(chunks) and (res1.cells_cached == len(chunks)) == (arena > (1 << 20))
+    assert got.shape == ref.shape and abs(got - ref).max() == 0
+    assert np.array_equal(got.indptr, ref.indptr) and np.array_equal(got.indices, ref.indices)

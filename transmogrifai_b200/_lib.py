@@ -37,6 +37,7 @@ _i64 = C.c_int64
 _int = C.c_int
 _dbl = C.c_double
 _sz = C.c_size_t
+_u64 = C.c_uint64
 
 # name -> argtypes; every function returns int except the two noted below
 _SIGNATURES: Dict[str, List] = {
@@ -76,6 +77,10 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_text_hash_transform_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _p, _p, _sz, _p],
     "tmog_text_hash_fit_transform_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _dbl, _p, _p, _p, _p, _p, _p,
                                          _p, _i64, _p, _p, _sz, _p],
+    "tmog_text_cells_pack_bytes": [_i64, _int, _int, C.POINTER(_sz)],
+    "tmog_text_hash_stats_pack_dev": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _dbl, _p, _p, _p, _sz, _p, _p,
+                                      _u64, _p, _p, _p],
+    "tmog_text_hash_transform_packed_dev": [_int, _i64, _p, _p, _p, _u64, _p, _p, _p, _p, _p, _p, _i64, _p, _p],
     "tmog_sparse_rows_select_dev": [_p, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p],
     "tmog_label_classes_scratch_bytes": [C.POINTER(_sz)],
     "tmog_label_classes_dev": [_p, _i64, _int, _p, _p, _p, _p, _p, _sz, _p],

@@ -1228,6 +1228,7 @@ sparse_rows_select_kernel(const int64_t* __restrict__ row_start, const int32_t* 
 
 #include "text_cells.cuh"
 #include "text_span.cuh"
+#include "text_packed.cuh"
 
 using namespace tmog;
 // Snowball english_stop.txt (174 words) as loaded by Lucene's StandardAnalyzer in the reference
@@ -1442,6 +1443,7 @@ struct ThArgs {
     int n_hashed;          // columns [0, n_hashed) are hashed; the rest only give null indicators / text lengths
     int len_base;          // vector index of the first text-length column, or -1
     cudaStream_t stream;
+    TsPack pack;           // arena == NULL: the cells are not kept
 };
 
 // level 0 reads all rows, level 1 the rows level 0 deferred, level 2 the rows level 1 deferred
@@ -1583,28 +1585,37 @@ static int tc_run(const ThArgs& a) {
     // TMOG_TEXT_PATH=cells: the lane-per-cell kernel (kept for comparison); default: the span kernel
     const char* path = getenv("TMOG_TEXT_PATH");
     const bool lane_cells = path && strcmp(path, "cells") == 0;
-    auto kernel = lane_cells ? text_cells_kernel<STATS, CELLS> : text_span_kernel<STATS, CELLS>;
+    const bool pack = a.pack.arena != nullptr;
+    TMOG_REQUIRE(!pack || (STATS && !CELLS && !lane_cells), "packed cells come from the statistics pass of the span kernel");
     const int threads = lane_cells ? TC_WARPS * 32 : TS_WARPS * 32;
     const size_t smem = lane_cells
         ? TH_STOP_PRE_BYTES + 64 + (size_t)TC_WARPS * (TC_WARP_ROWS + (STATS ? TC_STAT_ROWS : 0)) * 32 * 4
         : TS_FIXED_SMEM + (STATS ? 2 * TC_MAXF * 4 : 0) + (size_t)TS_WARPS * TS_WARP_BYTES;
-    TMOG_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 0;
-    TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
-    TMOG_REQUIRE(per_sm >= 1, "text cell kernel does not fit an SM");
     const int item_rows = lane_cells ? TC_ITEM_ROWS : TS_ITEM_ROWS;
     const int64_t items = ((a.n + item_rows - 1) / item_rows) * a.ncols;
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)sm_count() * per_sm, items));
-    kernel<<<grid, threads, smem, a.stream>>>(a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, a.class_ids, sc,
-                                              defer_bits, a.class_sum, a.dup, a.sq_extra, a.aux, a.label,
-                                              a.label_shift, a.wsum, records, a.flags);
+    auto launch = [&](auto kernel, auto... extra) -> int {
+        TMOG_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int per_sm = 0;
+        TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
+        TMOG_REQUIRE(per_sm >= 1, "text cell kernel does not fit an SM");
+        const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)sm_count() * per_sm, items));
+        kernel<<<grid, threads, smem, a.stream>>>(a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, a.class_ids, sc,
+                                                  defer_bits, a.class_sum, a.dup, a.sq_extra, a.aux, a.label,
+                                                  a.label_shift, a.wsum, records, a.flags, extra...);
+        return TMOG_OK;
+    };
+    int rc;
+    if (lane_cells) rc = launch(text_cells_kernel<STATS, CELLS>);
+    else if (STATS && !CELLS && pack) rc = launch(text_span_kernel<STATS, CELLS, STATS && !CELLS>, a.pack);
+    else rc = launch(text_span_kernel<STATS, CELLS, false>, TsPack{});
+    if (rc) return rc;
     TMOG_LAUNCH_CHECK();
     if (STATS) {
         const int64_t words = ((int64_t)a.n * a.ncols + 31) / 32;
         const int sgrid = (int)std::max<int64_t>(1, std::min<int64_t>((words + 127) / 128, (int64_t)sm_count() * 8));
         text_cells_slow_kernel<<<sgrid, 128, 0, a.stream>>>(a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, a.class_ids,
                                                             defer_bits, a.class_sum, a.dup, a.sq_extra, a.aux, a.label,
-                                                            a.label_shift, a.wsum, a.flags);
+                                                            a.label_shift, a.wsum, a.flags, a.pack);
         TMOG_LAUNCH_CHECK();
     }
     if (CELLS) {
@@ -1688,6 +1699,101 @@ extern "C" int tmog_text_hash_stats_dev(const int64_t* col_desc, int ncols, int6
     a.flags = flags;
     a.stream = (cudaStream_t)stream;
     return text_hash_dispatch<true, false>(a);
+}
+
+// ---- packed cells (text_cells.cuh TsPack, text_packed.cuh): the fit pass keeps every cell's buckets, the transform of the
+//      same rows reads them back instead of the text
+static size_t pack_align(size_t b) { return (b + 255) & ~size_t(255); }
+
+extern "C" int tmog_text_cells_pack_bytes(int64_t n, int ncols, int track_len, size_t* meta_bytes) {
+    TMOG_REQUIRE(meta_bytes != nullptr && n >= 0 && n < 0x7fffffffLL && ncols >= 0, "bad arguments");
+    const size_t groups = (size_t)((n + 31) / 32) * ncols, cells = (size_t)n * ncols;
+    *meta_bytes = pack_align(groups * sizeof(TsGroup)) + pack_align((cells + 1) * 2) + (track_len ? pack_align(cells * 4) : 0);
+    return TMOG_OK;
+}
+
+static int pack_view(void* meta, int64_t n, int ncols, bool track_len, void* arena, uint64_t arena_bytes, uint64_t* cursor,
+                     int32_t* pack_flags, TsPack* pk) {
+    TMOG_REQUIRE(meta && arena && cursor && pack_flags, "NULL packed-cell argument");
+    TMOG_REQUIRE((reinterpret_cast<uintptr_t>(meta) & 15u) == 0 && (reinterpret_cast<uintptr_t>(arena) & 15u) == 0,
+                 "packed-cell buffers must be 16-byte aligned");
+    const size_t groups = (size_t)((n + 31) / 32) * ncols, cells = (size_t)n * ncols;
+    uint8_t* m = static_cast<uint8_t*>(meta);
+    pk->grp = reinterpret_cast<TsGroup*>(m);
+    pk->rel = reinterpret_cast<unsigned short*>(m + pack_align(groups * sizeof(TsGroup)));
+    pk->lens = track_len ? reinterpret_cast<unsigned*>(m + pack_align(groups * sizeof(TsGroup)) + pack_align((cells + 1) * 2))
+                         : nullptr;
+    pk->arena = static_cast<unsigned short*>(arena);
+    pk->arena_entries = arena_bytes / 2;
+    pk->cursor = reinterpret_cast<unsigned long long*>(cursor);
+    pk->flags = pack_flags;
+    return TMOG_OK;
+}
+
+extern "C" int tmog_text_hash_stats_pack_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,
+                                             const int32_t* prefix_len, const int32_t* params, const uint8_t* class_ids,
+                                             uint32_t* bucket_class_sum, uint32_t* bucket_dup, uint64_t* bucket_sq_extra,
+                                             uint32_t* bucket_aux, const double* label, double label_shift,
+                                             double* bucket_wsum, int32_t* flags, void* scratch, size_t scratch_bytes,
+                                             void* pack_meta, void* arena, uint64_t arena_bytes, uint64_t* arena_cursor,
+                                             int32_t* pack_flags, void* stream) {
+    ThArgs a = {};
+    if (int rc = text_hash_common(col_desc, ncols, n, prefix, prefix_len, params, scratch, scratch_bytes, &a)) return rc;
+    TMOG_REQUIRE(bucket_class_sum && bucket_dup && bucket_sq_extra && bucket_aux && flags, "NULL output");
+    TMOG_REQUIRE(a.p.nclasses == 1 || class_ids != nullptr, "class_ids is NULL");
+    if (n == 0 || ncols == 0) return TMOG_OK;
+    const char* path = getenv("TMOG_TEXT_PATH");
+    TMOG_REQUIRE(tc_eligible(a.p, ncols, a.n_hashed) && !(path && strcmp(path, "cells") == 0) &&
+                     a.scratch_bytes >= tc_scratch_need(n, ncols, a.n_hashed, false),
+                 "packed cells need separate hash spaces of at most %d buckets per column", TC_MAXF);
+    if (int rc = pack_view(pack_meta, n, ncols, a.len_base >= 0, arena, arena_bytes, arena_cursor, pack_flags, &a.pack))
+        return rc;
+    a.class_ids = class_ids;
+    a.class_sum = bucket_class_sum;
+    a.dup = bucket_dup;
+    a.sq_extra = reinterpret_cast<unsigned long long*>(bucket_sq_extra);
+    a.aux = bucket_aux;
+    TMOG_REQUIRE((label == nullptr) == (bucket_wsum == nullptr), "label and bucket_wsum go together");
+    a.label = label;
+    a.label_shift = label_shift;
+    a.wsum = bucket_wsum;
+    a.flags = flags;
+    a.stream = (cudaStream_t)stream;
+    return tc_run<true, false>(a);
+}
+
+extern "C" int tmog_text_hash_transform_packed_dev(int ncols, int64_t n, const int32_t* params, void* pack_meta, void* arena,
+                                                   uint64_t arena_bytes, const int32_t* newpos, int64_t* row_start,
+                                                   int32_t* row_nnz, int32_t* out_idx, int32_t* out_val, uint64_t* cursor,
+                                                   int64_t capacity, int32_t* flags, void* stream) {
+    TMOG_REQUIRE(ncols >= 0 && n >= 0 && n < 0x7fffffffLL && params != nullptr, "bad arguments");
+    TMOG_REQUIRE(newpos && row_start && row_nnz && cursor && flags, "NULL argument");
+    TMOG_REQUIRE(capacity >= 0 && (capacity == 0 || (out_idx && out_val)), "NULL output");
+    if (n == 0 || ncols == 0) return TMOG_OK;
+    TcParams p = {};
+    p.num_features = params[0];
+    p.binary_freq = params[2];
+    p.track_nulls = params[4];
+    p.null_base = params[6];
+    p.n_hashed = params[8] > 0 ? params[8] : ncols;
+    p.len_base = params[9] > 0 ? params[9] : -1;
+    TMOG_REQUIRE(p.num_features > 0 && p.num_features <= TC_MAXF && !params[1] && p.n_hashed <= ncols,
+                 "packed cells need separate hash spaces of at most %d buckets per column", TC_MAXF);
+    TsPack pk = {};
+    uint64_t unused_cursor = 0;
+    if (int rc = pack_view(pack_meta, n, ncols, p.len_base >= 0, arena, arena_bytes, &unused_cursor, flags, &pk)) return rc;
+    pk.cursor = nullptr;
+    const size_t smem = (size_t)TP_WARPS * TP_WARP_BYTES;
+    TMOG_CUDA(cudaFuncSetAttribute(text_rows_packed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    TMOG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, text_rows_packed_kernel, TP_WARPS * 32, smem));
+    TMOG_REQUIRE(per_sm >= 1, "packed row kernel does not fit an SM");
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + TP_WARPS - 1) / TP_WARPS, (int64_t)sm_count() * per_sm));
+    text_rows_packed_kernel<<<grid, TP_WARPS * 32, smem, (cudaStream_t)stream>>>(
+        ncols, n, p, pk, newpos, row_start, row_nnz, out_idx, out_val, reinterpret_cast<unsigned long long*>(cursor),
+        capacity, flags);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
 }
 
 extern "C" int tmog_text_hash_transform_dev(const int64_t* col_desc, int ncols, int64_t n, const uint8_t* prefix,

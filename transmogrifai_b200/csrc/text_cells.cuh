@@ -68,6 +68,32 @@ struct TcScratch {
     unsigned long long pad[6];
 };
 
+// ---- packed cells: what the fit pass found in every cell (its buckets and their term frequencies), kept in HBM so that
+//      the transform of the same rows needs neither the text nor a second tokenise + hash pass (text_packed.cuh reads
+//      them).  A group = 32 consecutive rows of one column = one span of text_span_kernel (text_span.cuh):
+//        arena   u16 entries, bucket | (term frequency - 1) << 9, ascending buckets per cell, the cells of a group one
+//                after the other; a group's entries start at a multiple of 8 (16-byte copies).  A cell the fast path
+//                set aside holds four entries instead: the arena offset of its slot (TS_SLOT_ENTRIES entries: the term
+//                frequency of every bucket, the summed token length, the no-token flag), written by the slow kernel.
+//        grp     [ceil(n / 32)][ncols]: arena offset of the group's entries (~0: the arena was full), their number
+//        rel     [n][ncols] u16: where the cell's entries begin inside the group | no token survived << 14 | slot << 15
+//        lens    [n][ncols] u32 summed token lengths (only when the vector has text-length columns)
+constexpr int TS_SLOT_ENTRIES = TC_MAXF + 8;          // 512 term frequencies | length sum (2) | no-token flag | pad
+constexpr unsigned TS_REL_MASK = 0x3fffu, TS_REL_NOHIT = 0x4000u, TS_REL_SLOT = 0x8000u;
+struct TsGroup {
+    unsigned long long off;
+    unsigned total, pad;
+};
+struct TsPack {
+    unsigned short* arena;
+    unsigned long long arena_entries;
+    unsigned long long* cursor;            // entries handed out so far
+    TsGroup* grp;
+    unsigned short* rel;
+    unsigned* lens;                        // or NULL
+    int* flags;                            // [0] = 1: the arena was too small for this chunk
+};
+
 // ---- exact scalar tokeniser (the definition the fast path must agree with; oracle/text.py standard_tokenize) --------
 template <typename F>
 __device__ void tc_scalar_tokens(const uint8_t* s, int64_t len, int min_len, bool& non_ascii, F&& emit) {
@@ -648,7 +674,7 @@ text_cells_slow_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n
                        const unsigned* __restrict__ defer_bits, unsigned int* __restrict__ bucket_class_sum,
                        unsigned int* __restrict__ bucket_dup, unsigned long long* __restrict__ bucket_sq_extra,
                        unsigned int* __restrict__ bucket_aux, const double* __restrict__ label, double label_shift,
-                       double* __restrict__ bucket_wsum, int* __restrict__ flags) {
+                       double* __restrict__ bucket_wsum, int* __restrict__ flags, TsPack pk) {
     const int64_t ncells = n * ncols;
     for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w * 32 < ncells;
          w += (int64_t)gridDim.x * blockDim.x) {
@@ -669,6 +695,24 @@ text_cells_slow_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n
                                               p.prepend ? prefix_len[j] : 0, hashed, counts, len_sum, na, ovf);
             if (na) flags[0] = 1;
             if (ovf) flags[2] = 1;
+            if (pk.arena != nullptr) {
+                // packed cells: this cell gets a slot of its own; its four entries in the group point at it
+                const TsGroup g = pk.grp[(row >> 5) * ncols + j];
+                if (g.off != ~0ull) {
+                    const unsigned long long slot = atomicAdd(pk.cursor, (unsigned long long)TS_SLOT_ENTRIES);
+                    if (slot + TS_SLOT_ENTRIES > pk.arena_entries) {
+                        pk.flags[0] = 1;
+                    } else {
+                        unsigned short* sl = pk.arena + slot;
+                        for (int q = 0; q < TC_MAXF; ++q) sl[q] = hashed && q < p.num_features ? counts[q] : (unsigned short)0;
+                        sl[TC_MAXF] = (unsigned short)(len_sum & 0xffffu);
+                        sl[TC_MAXF + 1] = (unsigned short)(len_sum >> 16);
+                        sl[TC_MAXF + 2] = nohit ? 1 : 0;
+                        unsigned short* at = pk.arena + g.off + (pk.rel[row * ncols + j] & TS_REL_MASK);
+                        for (int q = 0; q < 4; ++q) at[q] = (unsigned short)((slot >> (16 * q)) & 0xffffull);
+                    }
+                }
+            }
             const int cls = (p.nclasses > 1 && class_ids) ? class_ids[row] : 0;
             const double e_row = label ? label[row] - label_shift : 0.0;
             auto add = [&](unsigned v, unsigned cnt) {

@@ -112,7 +112,7 @@ __device__ __forceinline__ unsigned ts_compress(const unsigned (&t)[4]) {
 
 constexpr int TS_FIXED_SMEM = TH_STOP_PRE_BYTES + 64 + TS_BLOOM_WORDS * 4;
 
-template <bool STATS, bool CELLS>
+template <bool STATS, bool CELLS, bool PACK>
 __global__ void __launch_bounds__(TS_WARPS * 32, TS_MIN_CTAS)
 text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, const uint8_t* __restrict__ prefix,
                  const int* __restrict__ prefix_len, TcParams p, const uint8_t* __restrict__ class_ids,
@@ -120,7 +120,7 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                  unsigned int* __restrict__ bucket_class_sum, unsigned int* __restrict__ bucket_dup,
                  unsigned long long* __restrict__ bucket_sq_extra, unsigned int* __restrict__ bucket_aux,
                  const double* __restrict__ label, double label_shift, double* __restrict__ bucket_wsum,
-                 unsigned* __restrict__ records, int* __restrict__ flags) {
+                 unsigned* __restrict__ records, int* __restrict__ flags, TsPack pk) {
     extern __shared__ __align__(16) unsigned char ts_smem[];
     unsigned short* stop_pre = reinterpret_cast<unsigned short*>(ts_smem);
     unsigned* item_info = reinterpret_cast<unsigned*>(ts_smem + TH_STOP_PRE_BYTES);
@@ -482,6 +482,78 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
             if (deferred && in_rows) {
                 const int64_t cell = row * ncols + j;
                 atomicOr(&defer_bits[cell >> 5], 1u << (cell & 31));
+            }
+            if (PACK) {
+                // ---- the cells of this span in packed form.  The ring and the queue are free now: the ring holds the
+                //      entries before every bitmap word of a cell, the queue stages the group's entries
+                unsigned* before = ring;                             // [TC_FW][32]
+                int cnt = 0;
+                if (in_rows && hashed && !deferred) {
+#pragma unroll
+                    for (int w = 0; w < TC_FW; ++w) {
+                        before[w * 32 + lane] = (unsigned)cnt;
+                        cnt += __popc(mybm[w]);
+                    }
+                }
+                if (in_rows && deferred) cnt = 4;
+                int incl = cnt;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int up = __shfl_up_sync(FULL, incl, o);
+                    if (lane >= o) incl += up;
+                }
+                const int excl = incl - cnt, total = __shfl_sync(FULL, incl, 31), alloc = (total + 7) & ~7;
+                unsigned long long off = 0ull;
+                if (lane == 0 && total > 0) {
+                    off = atomicAdd(pk.cursor, (unsigned long long)alloc);
+                    if (off + (unsigned long long)alloc > pk.arena_entries) {
+                        pk.flags[0] = 1;
+                        off = ~0ull;
+                    }
+                }
+                off = __shfl_sync(FULL, off, 0);
+                if (in_rows) {
+                    pk.rel[row * ncols + j] = (unsigned short)((unsigned)excl | (nohit ? TS_REL_NOHIT : 0u) |
+                                                               (deferred ? TS_REL_SLOT : 0u));
+                    if (pk.lens) pk.lens[row * ncols + j] = need_lens ? len_sum : 0u;
+                }
+                if (lane == 0) {
+                    TsGroup g;
+                    g.off = off;
+                    g.total = (unsigned)total;
+                    g.pad = 0u;
+                    pk.grp[(g0 >> 5) * ncols + j] = g;
+                }
+                if (total > 0 && off != ~0ull) {
+                    const bool staged = alloc <= TS_Q * 2;
+                    unsigned short* stage = reinterpret_cast<unsigned short*>(tq);
+                    unsigned short* dst = (staged ? stage : pk.arena + off) + excl;
+                    if (in_rows && deferred) {
+                        dst[0] = dst[1] = dst[2] = dst[3] = 0;                  // the slow kernel leaves the slot here
+                    } else if (cnt > 0) {
+                        int k = 0;
+                        for (int w = 0; w < TC_FW; ++w) {
+                            unsigned x = mybm[w];
+                            while (x) {
+                                dst[k++] = (unsigned short)(w * 32 + __ffs(x) - 1);
+                                x &= x - 1u;
+                            }
+                        }
+                        if (!p.binary_freq)
+                            for (int q = 0; q < ndup; ++q) {
+                                const unsigned e = app[q * 32 + lane], bkt = e & 0x1ffu;
+                                const int at = (int)before[(bkt >> 5) * 32 + lane] +
+                                               __popc(mybm[bkt >> 5] & ((1u << (bkt & 31u)) - 1u));
+                                dst[at] = (unsigned short)(bkt | (((e >> 9) - 1u) << 9));
+                            }
+                    }
+                    if (staged) {
+                        __syncwarp();
+                        for (int i = lane * 8; i < alloc; i += 256)
+                            *reinterpret_cast<uint4*>(pk.arena + off + i) = *reinterpret_cast<const uint4*>(stage + i);
+                    }
+                }
+                __syncwarp();
             }
             if (CELLS && in_rows) {
                 unsigned* rec = records + ((size_t)row * ncols + j) * TC_REC_WORDS;

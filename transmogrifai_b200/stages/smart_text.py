@@ -784,7 +784,23 @@ class SmartTextVectorizerModel(OpModel):
             k = len(sub.names)
             label_ptr = cont[2].data_ptr() if cont is not None else None
             shift = cont[1] if cont is not None else 0.0
-            if not fused_rows:
+            cells = getattr(self, "_cells", None) if st.get("pack_token") is not None else None
+            if not fused_rows and cells is not None and not cells.get("full"):
+                import ctypes
+                need = ctypes.c_size_t(0)
+                L.call("tmog_text_cells_pack_bytes", n, k, int(lay.len_width > 0), ctypes.byref(need))
+                meta = torch.empty(max(need.value, 16), dtype=torch.uint8, device="cuda")
+                pflag = torch.zeros(1, dtype=torch.int32, device="cuda")
+                L.call("tmog_text_hash_stats_pack_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(), d_plen.data_ptr(),
+                       params.ctypes.data, ids_ptr, class_sum.data_ptr(), dup.data_ptr(), extra.data_ptr(),
+                       aux.data_ptr(), label_ptr, shift, R.ptr(wsum), flags.data_ptr(), scratch.data_ptr(),
+                       scratch.numel(), meta.data_ptr(), cells["arena"].data_ptr(), cells["arena"].numel(),
+                       cells["cursor"].data_ptr(), pflag.data_ptr(), R.stream())
+                cells["pending"].append((st["pack_token"], meta, pflag, n, k))
+                # every 8 chunks: has the arena run full?  (one small read; chunks after that are not packed)
+                if len(cells["pending"]) % 8 == 0 and int(cells["cursor"].item()) * 2 >= cells["arena"].numel():
+                    cells["full"] = True
+            elif not fused_rows:
                 L.call("tmog_text_hash_stats_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(), d_plen.data_ptr(),
                        params.ctypes.data, ids_ptr, class_sum.data_ptr(), dup.data_ptr(), extra.data_ptr(),
                        aux.data_ptr(), label_ptr, shift, R.ptr(wsum), flags.data_ptr(), scratch.data_ptr(),
@@ -915,6 +931,27 @@ class SmartTextVectorizerModel(OpModel):
         cont = None if classes is not None else label_moments_dev(batch, y, label_name) + (y,)
         return self._sidecar(dev, batch.n, n_all, classes, class_counts, ids, label_name, cont)
 
+    # -- packed cells: what the statistics pass found in every cell of a chunk, kept in HBM for the chunk's transform
+    def enable_cell_cache(self, nbytes: int) -> bool:
+        """Give the streamed fit an arena of `nbytes` of device memory for the packed cells of the chunks
+        (tmog_text_hash_stats_pack_dev): the transform of a chunk whose cells fitted reads them instead of the text."""
+        lay = self.layout
+        self._cells = None
+        if nbytes < (1 << 16) or not lay.text_idx or lay.shared or lay.num_features > 512:
+            return False
+        nbytes -= nbytes % 256
+        self._cells = {"arena": torch.empty(nbytes, dtype=torch.uint8, device="cuda"),
+                       "cursor": torch.zeros(1, dtype=torch.int64, device="cuda"), "chunks": {}, "pending": []}
+        return True
+
+    def stream_cached(self, token) -> bool:
+        """The chunk with this token needs none of its text columns for the transform."""
+        cells = getattr(self, "_cells", None)
+        return bool(cells) and not self.pivot_idx and token in cells["chunks"]
+
+    def release_cell_cache(self) -> None:
+        self._cells = None
+
     # -- row chunks (streaming.py): the statistics sidecar accumulated over the chunks
     def stream_begin(self, label):
         if label is None:
@@ -932,7 +969,9 @@ class SmartTextVectorizerModel(OpModel):
         dev = chunk.on_device("texts", names, block)
         ids = lab.class_ids(chunk) if lab.classes is not None else None
         cont = None if lab.classes is not None else lab.continuous() + (lab.device_label(chunk),)
+        st["pack_token"] = chunk.token
         self._side_scan(st, dev, chunk.n, ids, cont)
+        st["pack_token"] = None
         st.setdefault("tokens", []).append(chunk.token)
         st["n"] += chunk.n
 
@@ -945,6 +984,13 @@ class SmartTextVectorizerModel(OpModel):
         if st["chunk_nnz"]:             # sparse entries of every chunk's rows, by the chunk's token: sizes its transform
             nnz = torch.stack(st["chunk_nnz"]).cpu().numpy().astype(np.int64)
             self._stream_nnz = dict(zip(st.get("tokens", []), nnz.tolist()))
+        cells = getattr(self, "_cells", None)
+        if cells and cells["pending"]:  # the chunks whose cells fitted the arena
+            bad = torch.cat([f for _t, _m, f, _n, _k in cells["pending"]]).cpu().numpy()
+            for (token, meta, _f, n, k), b in zip(cells["pending"], bad):
+                if not b:
+                    cells["chunks"][token] = (meta, n, k)
+            cells["pending"] = []
         return self
 
     # -- transform -----------------------------------------------------------------------------------------------------
@@ -963,7 +1009,7 @@ class SmartTextVectorizerModel(OpModel):
             parts.append(LazyPart(self.pivot_width, lambda keep: self._materialize_pivot(dev_of(), n, keep, stream)))
         if self.layout.text_idx:
             parts.append(LazyPart(self.layout.width,
-                                  lambda keep: self._materialize_hash(dev_of(), n, keep, fitted, stream)))
+                                  lambda keep: self._materialize_hash(dev_of, n, keep, fitted, stream)))
         return VectorColumn(self.getOutput().name, n, self.getMetadata(), parts, self._fit_stats if same else None)
 
     def _plan(self, kind: str, keep, build):
@@ -1000,8 +1046,8 @@ class SmartTextVectorizerModel(OpModel):
                out.data_ptr(), out.shape[1], 0, R.stream())
         return OneHotPart(out[:, :k], out_width)
 
-    def _materialize_hash(self, block: TextBlock, n: int, keep, fitted=None, stream=None) -> SparseRowsPart:
-        dev = block if block.is_cuda else block.to("cuda")
+    def _materialize_hash(self, block, n: int, keep, fitted=None, stream=None) -> SparseRowsPart:
+        """block: the text block, or a thunk that fetches it (not called when the chunk's packed cells are at hand)."""
         lay = self.layout
         width = lay.width
         full = lay.kernel_width
@@ -1017,6 +1063,13 @@ class SmartTextVectorizerModel(OpModel):
             return newpos, torch.from_numpy(newpos).cuda(), out_width
 
         newpos, d_newpos, out_width = self._plan("hash", keep, build)
+        cells = getattr(self, "_cells", None)
+        packed = cells["chunks"].get(stream.get("token")) if cells and stream is not None and fitted is None else None
+        if packed is not None and packed[1] == n:
+            return self._rows_from_cells(cells, packed, n, d_newpos, out_width, stream)
+        if callable(block):
+            block = block()
+        dev = block if block.is_cuda else block.to("cuda")
         rows, local_nnz = fitted if fitted is not None else (None, None)
         if rows is not None:
             # the fit pass wrote the rows of this batch: keep the wanted columns of them
@@ -1066,6 +1119,37 @@ class SmartTextVectorizerModel(OpModel):
                scratch.numel(), R.stream())
         if own_flags:
             _check_hash_flags(flags)
+        return SparseRowsPart(row_start, row_nnz, idx, val, out_width)
+
+
+    def _rows_from_cells(self, cells, packed, n: int, d_newpos, out_width: int, stream) -> SparseRowsPart:
+        """The sparse rows of a chunk from its packed cells (tmog_text_hash_transform_packed_dev)."""
+        meta, _n, k = packed
+        lay = self.layout
+        hp = self.hashingParams
+        params = np.array([lay.num_features, int(lay.shared), int(hp["binaryFreq"]), hp["minTokenLength"],
+                           int(self.shouldTrackNulls), int(hp["prependFeatureName"]), lay.null_base, 1,
+                           len(lay.hash_idx) if lay.ignore_idx else 0, lay.len_base if lay.len_width else 0, 0, 0],
+                          dtype=np.int32)
+        row_start = torch.empty(n, dtype=torch.int64, device="cuda")
+        row_nnz = torch.empty(n, dtype=torch.int32, device="cuda")
+        flags = stream["flags"]
+        cursor = torch.zeros(1, dtype=torch.int64, device="cuda")
+        chunk_nnz = getattr(self, "_stream_nnz", None) or {}
+        args = (k, n, params.ctypes.data, meta.data_ptr(), cells["arena"].data_ptr(), cells["arena"].numel(),
+                d_newpos.data_ptr(), row_start.data_ptr(), row_nnz.data_ptr())
+        if stream.get("token") in chunk_nnz:
+            capacity = int(chunk_nnz[stream["token"]])
+        else:
+            L.call("tmog_text_hash_transform_packed_dev", *args, None, None, cursor.data_ptr(), 0, flags.data_ptr(),
+                   R.stream())
+            capacity = int(cursor.item())
+            cursor.zero_()
+            flags[3] = 0
+        idx = torch.empty(max(capacity, 1), dtype=torch.int32, device="cuda")
+        val = torch.empty(max(capacity, 1), dtype=torch.int32, device="cuda")
+        L.call("tmog_text_hash_transform_packed_dev", *args, idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), capacity,
+               flags.data_ptr(), R.stream())
         return SparseRowsPart(row_start, row_nnz, idx, val, out_width)
 
 

@@ -211,11 +211,12 @@ class ChunkCache:
 
 
 def device_chunks(chunks: Iterable[ColumnarBatch], depth: int = 1, cache: Optional[ChunkCache] = None,
-                  fill: bool = False):
+                  fill: bool = False, needed: Optional[Callable[[ColumnarBatch, object], bool]] = None):
     """The chunks in HBM, in order.  Chunks that are there already pass through; a chunk in (pinned) host memory is
     copied on a side stream while the chunks before it are being worked on, `depth` chunks ahead -- partition k + 1
     crosses the link under partition k's kernels.  At most depth + 2 uploaded chunks exist at a time: the copy of a
-    further chunk waits for the work on chunk k - 1 to finish.  The device copy keeps the host chunk's token."""
+    further chunk waits for the work on chunk k - 1 to finish.  The device copy keeps the host chunk's token.
+    needed(chunk, block) -> False leaves a host block where it is (no stage will read it for this chunk)."""
     main = torch.cuda.current_stream()
     copy = None
     pending = []                       # [(device chunk, upload event)]
@@ -238,7 +239,8 @@ def device_chunks(chunks: Iterable[ColumnarBatch], depth: int = 1, cache: Option
         if len(done) > depth + 1:
             done[-(depth + 2)].synchronize()
         with torch.cuda.stream(copy):
-            blocks = [b if b.is_cuda else b.to("cuda") for b in chunk.blocks]
+            blocks = [b if b.is_cuda or (needed is not None and not needed(chunk, b)) else b.to("cuda")
+                      for b in chunk.blocks]
             ev = torch.cuda.Event()
             ev.record(copy)
         dev = ColumnarBatch(chunk.n, blocks, {}, chunk.response, chunk.token)
@@ -252,7 +254,8 @@ def device_chunks(chunks: Iterable[ColumnarBatch], depth: int = 1, cache: Option
             main.wait_event(ev)
             for b in dev.blocks:
                 for t in _block_tensors(b):
-                    t.record_stream(main)
+                    if t.is_cuda:
+                        t.record_stream(main)
         return dev
 
     for chunk in chunks:
@@ -350,10 +353,12 @@ class StreamResult:
 
 def fit_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, response: Optional[str] = None,
                on_chunk: Optional[Callable[[int, int, ColumnarBatch], None]] = None,
-               cache: Optional[ChunkCache] = None) -> StreamResult:
+               cache: Optional[ChunkCache] = None, cell_cache_bytes: int = 0) -> StreamResult:
     """Passes 0 and 1 and the decisions: every stage of `result`'s DAG fitted over the chunks (`chunks` is iterated
     several times and must yield the same chunks in the same order each time).  on_chunk(pass, index, chunk) is called
-    after a chunk has been queued (for callers that recycle staging buffers)."""
+    after a chunk has been queued (for callers that recycle staging buffers).  cell_cache_bytes: HBM that stages may
+    use to keep what pass 1 found in a chunk for the chunk's transform (SmartTextVectorizer: the packed cells, so that
+    pass 2 neither uploads nor tokenises the text again)."""
     R.require_cuda()
     layers = stages_of(result)
     stages = [st for layer in layers for st in layer]
@@ -391,6 +396,9 @@ def fit_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, response: Opt
         fitters[id(st)] = st.stream_pre_finish(acc, chunks)       # e.g. the SmartTextVectorizer model, no statistics yet
     # ---- pass 1
     accs = []
+    cachers = [w for w in (fitters.get(id(st), st) for st in raw) if hasattr(w, "enable_cell_cache")]
+    for w in cachers:
+        w.enable_cell_cache(int(cell_cache_bytes) // len(cachers) if cell_cache_bytes else 0)
     for st in raw:
         worker = fitters.get(id(st), st)
         accs.append((st, worker, worker.stream_begin(label)))
@@ -443,7 +451,21 @@ def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: St
     flags = torch.zeros(4, dtype=torch.int32, device="cuda")
     flags_clean = torch.zeros(4, dtype=torch.int32, device="cuda")
     rows = 0
-    for k, chunk in enumerate(device_chunks(chunks, cache=cache)):
+    # a host block is uploaded unless every stage that reads its columns has what it needs of this chunk already
+    readers: Dict[str, list] = {}
+    for model in fit.fitted:
+        for f in getattr(model, "inN", ()):
+            if f.type_name != F.OPVECTOR:
+                readers.setdefault(f.name, []).append(model)
+
+    def needed(chunk: ColumnarBatch, block) -> bool:
+        for name in getattr(block, "names", ()):
+            for model in readers.get(name, ()):
+                if not (hasattr(model, "stream_cached") and model.stream_cached(chunk.token)):
+                    return True
+        return False
+
+    for k, chunk in enumerate(device_chunks(chunks, cache=cache, needed=needed)):
         batch = ColumnarBatch(chunk.n, chunk.blocks, {}, None, chunk.token)          # no response: no statistics
         batch.__dict__["_dev_cache"] = chunk.__dict__.setdefault("_dev_cache", {})
         batch.__dict__["_stream"] = {"index": k, "token": chunk.token, "flags": flags, "flags_clean": flags_clean}
@@ -472,14 +494,22 @@ def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: St
 
 
 def fit_and_transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, sink=None,
-                             response: Optional[str] = None, on_chunk=None, cache_bytes: Optional[int] = 0
-                             ) -> StreamResult:
+                             response: Optional[str] = None, on_chunk=None, cache_bytes: Optional[int] = 0,
+                             cell_cache_bytes: int = 0) -> StreamResult:
     """OpWorkflow.train() over row chunks: fit_stream, then transform_stream of the same chunks.  cache_bytes: HBM
-    budget for host chunks that stay resident between the two (0 = none, None = half of the free device memory)."""
+    budget for host chunks that stay resident between the two (0 = none, None = half of the free device memory);
+    cell_cache_bytes: HBM budget for what pass 1 keeps of every chunk for pass 2 (fit_stream)."""
     cache = None if cache_bytes == 0 else ChunkCache(cache_bytes)
-    fit = fit_stream(chunks, result, response, on_chunk, cache)
+    fit = fit_stream(chunks, result, response, on_chunk, cache, cell_cache_bytes)
     fit.cache_hits = 0
-    transform_stream(chunks, result, fit, sink, on_chunk, cache)
+    try:
+        transform_stream(chunks, result, fit, sink, on_chunk, cache)
+    finally:
+        fit.cells_cached = 0
+        for model in fit.fitted:
+            if hasattr(model, "release_cell_cache"):
+                fit.cells_cached += len((getattr(model, "_cells", None) or {}).get("chunks", {}))
+                model.release_cell_cache()
     if cache is not None:
         fit.cache_hits = cache.hits
         cache.items.clear()
