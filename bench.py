@@ -138,12 +138,23 @@ def run_step(batch, checked):
     return vec, fitted, parts
 
 
-def run_stream_step(chunks, feats, label, info, sink=None, cache_bytes=0):
-    """One step over a chunked dataset: a fresh plan (new stage objects), passes 0 / 1, decision, pass 2."""
+def run_stream_step(chunks, feats, label, info, sink=None, cache_bytes=0, cell_cache_bytes=0):
+    """One step over a chunked dataset: a fresh plan (new stage objects), passes 0 / 1, decision, pass 2.
+    cell_cache_bytes: HBM in which pass 1 leaves the packed text cells of the chunks for pass 2 (allocated, filled and
+    released inside the step)."""
     from transmogrifai_b200.streaming import fit_and_transform_stream
     checked = build_plan(feats, label, info)
-    res = fit_and_transform_stream(chunks, checked, sink, cache_bytes=cache_bytes)
+    res = fit_and_transform_stream(chunks, checked, sink, cache_bytes=cache_bytes, cell_cache_bytes=cell_cache_bytes)
     return checked, res
+
+
+def cell_cache_budget(arg_gb: float, reserve_gb: float) -> int:
+    """Bytes of HBM for the packed cells: what is free now minus a reserve for the step's own buffers."""
+    import torch
+    if arg_gb >= 0:
+        return int(arg_gb * 2 ** 30)
+    torch.cuda.empty_cache()
+    return max(0, int(torch.cuda.mem_get_info()[0] - reserve_gb * 2 ** 30))
 
 
 class CountingSink:
@@ -268,6 +279,27 @@ def kernel_times(workload, batch, fitted, info, reps: int = 5, text_offset: int 
             out.append({"kernel": "text tokenise + hash: bucket statistics (pass 1)", "ms": t_s,
                         "bytes_per_row": bpr + k * 8 + k / 8 + 1,
                         "note": "instruction-bound, reported against HBM anyway"})
+            # the same two passes with packed cells: pass 1 also leaves every cell's buckets in HBM, pass 2 reads them
+            if model.enable_cell_cache(int(4 * 2 ** 30 * max(n, 1) / 1e6) + (64 << 20)):
+                cells = model._cells
+                sst["pack_token"] = (0, batch.token)
+
+                def scan_pack():
+                    cells["cursor"].zero_()
+                    cells["pending"].clear()
+                    model._side_scan(sst, dev, n, ids, None)
+                t_sp = _time(scan_pack, max(reps // 2, 1))
+                token, meta, pflag, _n, kk = cells["pending"][-1]
+                if int(pflag.item()) == 0:
+                    cells["chunks"][token] = (meta, n, kk)
+                    packed_bytes = int(cells["cursor"].item()) * 2 + meta.numel()
+                    t_tp = _time(tr, max(reps // 2, 1))
+                    out.append({"kernel": "text statistics + packed cells (pass 1 when the cells are kept)", "ms": t_sp,
+                                "bytes_per_row": bpr + k * 8 + k / 8 + 1 + packed_bytes / max(n, 1),
+                                "note": "instruction-bound, reported against HBM anyway"})
+                    out.append({"kernel": "text_rows_packed_kernel: sparse rows from packed cells (pass 2)", "ms": t_tp,
+                                "bytes_per_row": packed_bytes / max(n, 1) + 12 + 8.0 * nnz / max(n, 1)})
+                model.release_cell_cache()
             del holder
     return sorted(out, key=lambda d: -d["ms"])
 
@@ -623,6 +655,9 @@ def main():
     ap.add_argument("--distinct-chunks", type=int, default=8, help="distinct synthetic chunks resident in HBM (c5)")
     ap.add_argument("--impl", default="tmog", choices=["tmog", "reference"])
     ap.add_argument("--cpu-rows", type=int, default=4_000_000, help="rows of the bounded CPU-baseline sample (c2)")
+    ap.add_argument("--cell-cache-gb", type=float, default=-1.0,
+                    help="HBM for the packed text cells kept between pass 1 and pass 2 (c5); -1 = what is free minus a "
+                         "reserve, 0 = none")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-others", action="store_true", help="skip the c2 / c3 / c4 lines of the default run")
@@ -757,8 +792,10 @@ def main():
     ring, feats, label, info = make_ring(chunk_rows, args.distinct_chunks, SEED + 100003 * rank)
     chunks, rows_rank = rank_chunks(ring, total_rows, chunk_rows, rank, world)
     sink = CountingSink()
+    run_stream_step(chunks[:min(3, len(chunks))], feats, label, info, sink)     # allocator warm-up before sizing the arena
+    cells_budget = cell_cache_budget(args.cell_cache_gb, 36.0)
     for _ in range(warmup):
-        checked, res = run_stream_step(chunks, feats, label, info, sink)
+        checked, res = run_stream_step(chunks, feats, label, info, sink, cell_cache_bytes=cells_budget)
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -768,7 +805,7 @@ def main():
     sink.bytes = 0
     e0.record()
     for _ in range(steps):
-        checked, res = run_stream_step(chunks, feats, label, info, sink)
+        checked, res = run_stream_step(chunks, feats, label, info, sink, cell_cache_bytes=cells_budget)
     e1.record()
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1) / steps)
@@ -780,6 +817,8 @@ def main():
     fitted = res.fitted
     summary = {"vector_width": len(est.summary.names) - 1, "kept_columns": len(fitted[-1].indicesToKeep),
                "dropped_columns": len(est.summary.dropped)}
+    cells_cached = int(getattr(res, "cells_cached", 0))
+    peak_alloc = int(torch.cuda.max_memory_allocated())
 
     # the kernels of one chunk, timed live on the launch stream (CUDA events), slowest first
     one = ring[0]
@@ -814,18 +853,27 @@ def main():
         run_stream_step(hchunks[:min(4, len(hchunks))], feats, label, info, hs)      # warm-up: allocator, pinned buffers
         hs.bytes = 0
         torch.cuda.empty_cache()
-        budget = int(torch.cuda.mem_get_info()[0] * 0.5)       # uploaded chunks stay resident up to this many bytes
+        # HBM between the passes: the packed text cells of as many chunks as fit (their text is not uploaded again);
+        # without them, whole uploaded chunks up to half of the free memory
+        e_cells = cell_cache_budget(args.cell_cache_gb, 64.0)
+        budget = 0 if e_cells else int(torch.cuda.mem_get_info()[0] * 0.5)
+        text_bytes = [benchdata.text_bytes(h) for h in hring]
         barrier()
         t0 = time.perf_counter()
-        _c, eres = run_stream_step(hchunks, feats, label, info, hs, cache_bytes=budget)
+        _c, eres = run_stream_step(hchunks, feats, label, info, hs, cache_bytes=budget, cell_cache_bytes=e_cells)
         barrier()
         dt = max_over_ranks(time.perf_counter() - t0)
         kept = int(getattr(eres, "cache_hits", 0))
-        h2d = sum((2 if i >= kept else 1) * in_bytes[i % n_host] + label_bytes for i in range(len(hchunks))) + in_bytes[0]
+        packed = int(getattr(eres, "cells_cached", 0))
+        # pass 1 uploads every chunk; pass 2 uploads it again unless it stayed resident, and without its text when its
+        # cells are packed (the arena fills in chunk order)
+        h2d = sum(in_bytes[i % n_host] + label_bytes + (0 if i < kept else in_bytes[i % n_host] -
+                                                        (text_bytes[i % n_host] if i < packed else 0))
+                  for i in range(len(hchunks))) + in_bytes[0]
         e2e = {"value": rows_e2e * world / dt, "unit": "rows/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(hs.bytes), "ms_per_step": dt * 1e3, "steps": 1, "rows": rows_e2e * world,
                "distinct_host_chunks": n_host, "chunks_kept_in_hbm_between_passes": kept,
-               "hbm_cache_budget_bytes": budget,
+               "hbm_cache_budget_bytes": budget, "chunks_with_packed_cells": packed, "cell_cache_bytes": e_cells,
                "api": "fit_and_transform_stream(pinned host chunks, label.sanityCheck(transmogrify(features)), HostSink)"}
         del hring, hchunks, hs
         torch.cuda.empty_cache()
@@ -865,6 +913,12 @@ def main():
                        "host_cpus": (f"{len(numa)} CPUs local to the GPU (NVML affinity)" if numa else "not bound"),
                        "output_bytes_per_step": int(out_bytes_step),
                        "algorithmic_bytes_per_row": {"fit": info["fit_bytes"], "transform": info["transform_bytes"]},
+                       "hbm_peak_allocated_bytes": peak_alloc,
+                       "packed_cells": {"hbm_budget_bytes": int(cells_budget), "chunks_packed_per_gpu": cells_cached,
+                                        "note": "pass 1 keeps every text cell's buckets and term frequencies (~1.6 KB "
+                                                "per row) for as many chunks as the budget holds; pass 2 of those chunks "
+                                                "reads them instead of tokenising the text again; filled and released "
+                                                "inside every step"},
                        **summary},
             "roofline": {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved"], "peak": peak,
                          "unit": "GB/s", "frac": top["frac"], "traffic": None, "peak_source": peak_src,

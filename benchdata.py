@@ -228,6 +228,16 @@ def host_copy(batch: ColumnarBatch) -> ColumnarBatch:
     return ColumnarBatch(batch.n, out, {}, batch.response)
 
 
+def text_bytes(batch: ColumnarBatch) -> int:
+    """Bytes of the text blocks of a chunk (data, offsets, validity)."""
+    tot = 0
+    for b in batch.blocks:
+        if not isinstance(b, (NumericBlock, DictBlock)):
+            tot += sum(t.numel() for t in b.data) + sum(t.numel() * 8 for t in b.offsets) + \
+                sum(0 if t is None else t.numel() * 8 for t in b.valid)
+    return tot
+
+
 def input_bytes(batch: ColumnarBatch) -> int:
     tot = 0
     for b in batch.blocks:

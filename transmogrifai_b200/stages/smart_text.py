@@ -944,10 +944,10 @@ class SmartTextVectorizerModel(OpModel):
                        "cursor": torch.zeros(1, dtype=torch.int64, device="cuda"), "chunks": {}, "pending": []}
         return True
 
-    def stream_cached(self, token) -> bool:
-        """The chunk with this token needs none of its text columns for the transform."""
+    def stream_cached(self, index: int, token) -> bool:
+        """Chunk number `index` of the stream (with this token) needs none of its text columns for the transform."""
         cells = getattr(self, "_cells", None)
-        return bool(cells) and not self.pivot_idx and token in cells["chunks"]
+        return bool(cells) and not self.pivot_idx and (index, token) in cells["chunks"]
 
     def release_cell_cache(self) -> None:
         self._cells = None
@@ -969,7 +969,8 @@ class SmartTextVectorizerModel(OpModel):
         dev = chunk.on_device("texts", names, block)
         ids = lab.class_ids(chunk) if lab.classes is not None else None
         cont = None if lab.classes is not None else lab.continuous() + (lab.device_label(chunk),)
-        st["pack_token"] = chunk.token
+        st["pack_token"] = (st.get("stream_index", 0), chunk.token)      # the chunk's place in the stream and its token
+        st["stream_index"] = st.get("stream_index", 0) + 1
         self._side_scan(st, dev, chunk.n, ids, cont)
         st["pack_token"] = None
         st.setdefault("tokens", []).append(chunk.token)
@@ -1064,7 +1065,8 @@ class SmartTextVectorizerModel(OpModel):
 
         newpos, d_newpos, out_width = self._plan("hash", keep, build)
         cells = getattr(self, "_cells", None)
-        packed = cells["chunks"].get(stream.get("token")) if cells and stream is not None and fitted is None else None
+        packed = cells["chunks"].get((stream.get("index"), stream.get("token"))) \
+            if cells and stream is not None and fitted is None else None
         if packed is not None and packed[1] == n:
             return self._rows_from_cells(cells, packed, n, d_newpos, out_width, stream)
         if callable(block):

@@ -211,12 +211,12 @@ class ChunkCache:
 
 
 def device_chunks(chunks: Iterable[ColumnarBatch], depth: int = 1, cache: Optional[ChunkCache] = None,
-                  fill: bool = False, needed: Optional[Callable[[ColumnarBatch, object], bool]] = None):
+                  fill: bool = False, needed: Optional[Callable[[int, ColumnarBatch, object], bool]] = None):
     """The chunks in HBM, in order.  Chunks that are there already pass through; a chunk in (pinned) host memory is
     copied on a side stream while the chunks before it are being worked on, `depth` chunks ahead -- partition k + 1
     crosses the link under partition k's kernels.  At most depth + 2 uploaded chunks exist at a time: the copy of a
     further chunk waits for the work on chunk k - 1 to finish.  The device copy keeps the host chunk's token.
-    needed(chunk, block) -> False leaves a host block where it is (no stage will read it for this chunk)."""
+    needed(index, chunk, block) -> False leaves a host block where it is (no stage will read it for this chunk)."""
     main = torch.cuda.current_stream()
     copy = None
     pending = []                       # [(device chunk, upload event)]
@@ -239,7 +239,7 @@ def device_chunks(chunks: Iterable[ColumnarBatch], depth: int = 1, cache: Option
         if len(done) > depth + 1:
             done[-(depth + 2)].synchronize()
         with torch.cuda.stream(copy):
-            blocks = [b if b.is_cuda or (needed is not None and not needed(chunk, b)) else b.to("cuda")
+            blocks = [b if b.is_cuda or (needed is not None and not needed(k, chunk, b)) else b.to("cuda")
                       for b in chunk.blocks]
             ev = torch.cuda.Event()
             ev.record(copy)
@@ -458,10 +458,10 @@ def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: St
             if f.type_name != F.OPVECTOR:
                 readers.setdefault(f.name, []).append(model)
 
-    def needed(chunk: ColumnarBatch, block) -> bool:
+    def needed(index: int, chunk: ColumnarBatch, block) -> bool:
         for name in getattr(block, "names", ()):
             for model in readers.get(name, ()):
-                if not (hasattr(model, "stream_cached") and model.stream_cached(chunk.token)):
+                if not (hasattr(model, "stream_cached") and model.stream_cached(index, chunk.token)):
                     return True
         return False
 
