@@ -18,7 +18,7 @@ for ln in dis.splitlines():
     m = re.search(r'//## File "([^"]+)", line (\d+)', ln)
     if m:
         f = m.group(1).split("/")[-1]
-        if f in ("text.cu", "text_cells.cuh", "text_span.cuh"):
+        if f in ("text.cu", "text_cells.cuh", "text_span.cuh", "text_packed.cuh"):
             cur = (f, int(m.group(2)))
         continue
     m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", ln)
@@ -44,7 +44,7 @@ for r in rows[hi + 1:]:
     ins[key] += float(r[ci]); smp[key] += float(r[si]); thr[key] += float(r[ti])
 tot, tots = sum(ins.values()), sum(smp.values())
 src = {}
-for f in ("text.cu", "text_cells.cuh", "text_span.cuh"):
+for f in ("text.cu", "text_cells.cuh", "text_span.cuh", "text_packed.cuh"):
     try:
         src[f] = open("transmogrifai_b200/csrc/" + f).read().splitlines()
     except OSError:

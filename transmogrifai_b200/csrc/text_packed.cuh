@@ -57,10 +57,14 @@ __device__ __forceinline__ TpCell tp_cell(const TsPack& pk, int ncols, int64_t n
 template <typename F>
 __device__ __forceinline__ void tp_for_entries(const TsPack& pk, const TpCell& c, F&& f) {
     if (!c.slot) {
-        const unsigned short* e = pk.arena + c.off;
-        for (int k = 0; k < c.cnt; ++k) {
-            const unsigned v = e[k];
-            f(k, (int)(v & 0x1ffu), (int)(v >> 9) + 1);
+        const unsigned short* __restrict__ e = pk.arena + c.off;
+        for (int k0 = 0; k0 < c.cnt; k0 += 16) {                  // sixteen loads in flight, then their entries
+            unsigned v[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = k0 + i < c.cnt ? (unsigned)e[k0 + i] : 0u;
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                if (k0 + i < c.cnt) f(k0 + i, (int)(v[i] & 0x1ffu), (int)(v[i] >> 9) + 1);
         }
     } else {
         const unsigned short* sl = pk.arena + c.off;
@@ -117,8 +121,11 @@ text_rows_packed_kernel(int ncols, int64_t n, TcParams p, TsPack pk, const int32
             raw_total += __shfl_sync(FULL, incl, 31);
             if (j < ncols && j < p.n_hashed) {
                 const int32_t* np = newpos + (int64_t)j * F;
+                // a column none of whose buckets was dropped maps bucket b to (its first output column) + b
+                const int lo = np[0], hi = np[F - 1];
+                const bool whole = lo >= 0 && hi - lo == F - 1;
                 tp_for_entries(pk, c, [&](int k, int bucket, int tf) {
-                    const int v = np[bucket];
+                    const int v = whole ? lo + bucket : np[bucket];
                     kept += v >= 0;
                     if (so + k < TP_STAGE) {
                         sidx[so + k] = v;

@@ -531,13 +531,14 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                     if (in_rows && deferred) {
                         dst[0] = dst[1] = dst[2] = dst[3] = 0;                  // the slow kernel leaves the slot here
                     } else if (cnt > 0) {
-                        int k = 0;
-                        for (int w = 0; w < TC_FW; ++w) {
-                            unsigned x = mybm[w];
-                            while (x) {
-                                dst[k++] = (unsigned short)(w * 32 + __ffs(x) - 1);
-                                x &= x - 1u;
-                            }
+                        // one loop over the cell's buckets (not one per bitmap word: the lanes would wait for the
+                        // fullest word of the 32 cells sixteen times)
+                        int w = 0;
+                        unsigned x = mybm[0];
+                        for (int k = 0; k < cnt; ++k) {
+                            while (!x) x = mybm[++w];
+                            dst[k] = (unsigned short)(w * 32 + __ffs(x) - 1);
+                            x &= x - 1u;
                         }
                         if (!p.binary_freq)
                             for (int q = 0; q < ndup; ++q) {
