@@ -843,6 +843,7 @@ def main():
         hring = [benchdata.host_copy(b) for b in ring[:n_host]]
         for h, b in zip(hring, ring):
             h.token = b.token
+        del h, b
         in_bytes = [benchdata.input_bytes(h) for h in hring]
         label_bytes = 8 * chunk_rows
         del ring, chunks, one
@@ -855,6 +856,9 @@ def main():
         torch.cuda.empty_cache()
         # HBM between the passes: the packed text cells of as many chunks as fit (their text is not uploaded again);
         # without them, whole uploaded chunks up to half of the free memory
+        if os.environ.get("TMOG_BENCH_DEBUG"):
+            print(f"[e2e] allocated {torch.cuda.memory_allocated() / 2**30:.1f} GiB, free "
+                  f"{torch.cuda.mem_get_info()[0] / 2**30:.1f} GiB", file=sys.stderr)
         e_cells = cell_cache_budget(args.cell_cache_gb, 64.0)
         budget = 0 if e_cells else int(torch.cuda.mem_get_info()[0] * 0.5)
         text_bytes = [benchdata.text_bytes(h) for h in hring]

@@ -242,6 +242,7 @@ class SmartTextVectorizer(OpEstimator):
             m, top = self._decide(values[c], totals[c], dev, c, n)
             methods.append(m)
             tops.append(top)
+        self._length_sources = None                # the estimator does not hold on to the batch
         model = SmartTextVectorizerModel(self, methods, tops)
         self._metadata = model._metadata = model._build_metadata()
         # 2. statistics sidecar (needs a categorical label)
@@ -362,6 +363,7 @@ class SmartTextVectorizer(OpEstimator):
             m, top = self._decide(merged[c], 0, None, c, 0)
             methods.append(m)
             tops.append(top)
+        self._length_sources = None                # the estimator does not hold on to the chunks
         model = SmartTextVectorizerModel(self, methods, tops)
         self._metadata = model._metadata = model._build_metadata()
         return model
