@@ -658,6 +658,8 @@ def main():
     ap.add_argument("--cell-cache-gb", type=float, default=-1.0,
                     help="HBM for the packed text cells kept between pass 1 and pass 2 (c5); -1 = what is free minus a "
                          "reserve, 0 = none")
+    ap.add_argument("--full-width-return", action="store_true",
+                    help="end-to-end arm: copy the output back full width instead of the compact return format")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-others", action="store_true", help="skip the c2 / c3 / c4 lines of the default run")
@@ -850,7 +852,7 @@ def main():
         torch.cuda.empty_cache()
         hchunks = [hring[i % n_host] for i in range(rows_rank // chunk_rows)]
         rows_e2e = len(hchunks) * chunk_rows
-        hs = HostSink(depth=2)
+        hs = HostSink(depth=2, compact=not args.full_width_return)
         run_stream_step(hchunks[:min(4, len(hchunks))], feats, label, info, hs)      # warm-up: allocator, pinned buffers
         hs.bytes = 0
         torch.cuda.empty_cache()
@@ -878,6 +880,9 @@ def main():
                "d2h_bytes_per_step": int(hs.bytes), "ms_per_step": dt * 1e3, "steps": 1, "rows": rows_e2e * world,
                "distinct_host_chunks": n_host, "chunks_kept_in_hbm_between_passes": kept,
                "hbm_cache_budget_bytes": budget, "chunks_with_packed_cells": packed, "cell_cache_bytes": e_cells,
+               "return_format": ("full width: f64 dense blocks, int32 term frequencies" if args.full_width_return else
+                                 "compact (streaming.compact_parts): null indicators and Binary values as u8, term "
+                                 "frequencies as u8 with an overflow list; indices, offsets and Real values unchanged"),
                "api": "fit_and_transform_stream(pinned host chunks, label.sanityCheck(transmogrify(features)), HostSink)"}
         del hring, hchunks, hs
         torch.cuda.empty_cache()

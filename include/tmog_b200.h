@@ -622,6 +622,20 @@ int tmog_vector_export_write_dev(const void* parts, int nparts, int64_t n, int s
                                  const int64_t* idx_off, const int64_t* val_off, int32_t* indices, double* values,
                                  void* stream);
 
+/* Compact return of a transformed partition over PCIe (what the JNI shim copies back instead of full-width arrays; it
+ * widens them while it builds the Spark vectors, which it has to touch element by element anyway).
+ *   tmog_dense_split_dev: a dense f64 block [n][ld] -> values f64 [n][ldv] of the columns with dest[c] >= 0 (column
+ *     dest[c] of the output) and units u8 [n][ldu] of the columns with dest[c] < 0 (column ~dest[c]): the columns that
+ *     are 0.0 / 1.0 by construction -- null indicators (OpVectorColumnMetadata.isNullIndicator) and the values of
+ *     Binary features (BinaryVectorizer.scala).  flags[0] is set if such a column holds anything else.
+ *   tmog_values_narrow_dev: the int32 term frequencies of sparse rows (tmog_text_hash_transform_dev's out_val) as u8; a
+ *     value above 254 is written as 255 and listed in over_pos / over_val (over_count counts them, also beyond
+ *     over_cap). */
+int tmog_dense_split_dev(const double* data, int64_t ld, int64_t n, int ncols, const int32_t* dest, double* values,
+                         int64_t ldv, uint8_t* units, int64_t ldu, int32_t* flags, void* stream);
+int tmog_values_narrow_dev(const int32_t* values, int64_t n, uint8_t* out, int64_t* over_pos, int32_t* over_val,
+                           int over_cap, uint32_t* over_count, void* stream);
+
 /* ---- string paths over host buffers ------------------------------------------------------------------------------
  * One call per exported partition does what the reference's estimator does in fit(Dataset) and its model in
  * transform(Dataset) (features/src/main/scala/com/salesforce/op/stages/base/sequence/SequenceEstimator.scala:91-106):

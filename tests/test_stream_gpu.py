@@ -230,3 +230,38 @@ def test_packed_cells_give_the_rows_the_text_gives(arena, slow, monkeypatch):
     assert 0 < res1.cells_cached <= len(chunks) and (res1.cells_cached == len(chunks)) == (arena > (1 << 20))
     assert got.shape == ref.shape and abs(got - ref).max() == 0
     assert np.array_equal(got.indptr, ref.indptr) and np.array_equal(got.indices, ref.indices)
+
+
+def test_compact_return_format_round_trip():
+    """HostSink(compact=True): 0 / 1 columns of dense blocks and term frequencies cross PCIe as bytes; expand_compact
+    gives back exactly the vector the plain sink delivers (and the oracle's)."""
+    from transmogrifai_b200.columnar import VectorColumn
+    from transmogrifai_b200.streaming import HostSink, expand_compact, fit_and_transform_stream, part_widths
+    cols, y = _data(sum(SIZES), 79)
+    ref, xo, metas, _methods, _tops = _oracle(cols, y)
+    chunks = _chunks(cols, "own_dictionaries_host")
+    plain, widths = [], []
+
+    def sink(k, vec, parts):
+        plain.append(VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy())
+        widths.append(part_widths(parts))
+
+    fit_and_transform_stream(chunks, _plan(), sink)
+    got, nbytes = [], [0, 0]
+    order = []
+
+    def consume(k, vec, named):
+        order.append(k)
+        got.append(expand_compact(vec, widths[k], named, SIZES[k]))
+        nbytes[1] += sum(t.numel() * t.element_size() for _nm, t in named)
+
+    hs = HostSink(depth=2, consume=consume, compact=True)
+    fit_and_transform_stream(chunks, _plan(), hs, cell_cache_bytes=32 << 20)
+    hs0 = HostSink(depth=2)
+    fit_and_transform_stream(chunks, _plan(), hs0)
+    assert order == list(range(len(SIZES)))
+    a, b = sp.vstack(got).tocsr(), sp.vstack(plain).tocsr()
+    assert a.shape == b.shape and abs(a - b).max() == 0
+    exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
+    assert abs(a - exp).max() < 1e-12
+    assert hs.bytes == nbytes[1] and hs.bytes < 0.8 * hs0.bytes

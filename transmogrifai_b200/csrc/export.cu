@@ -116,6 +116,76 @@ vector_export_kernel(const ExportPart* __restrict__ parts, int nparts, int64_t n
     }
 }
 
+// ---- compact return of a chunk's vector over PCIe (streaming.HostSink(compact=True)): what the device-to-host copy of a
+//      transformed partition carries.  Half of a RealVectorizer / BinaryVectorizer block is null indicators (0.0 / 1.0 as
+//      f64, RealVectorizer.scala / OpScalarStandardScaler aside), and a hashed text entry's term frequency is a small
+//      integer; both travel as one byte.
+// dense f64 [n][ld] -> values f64 [n][nv] (columns with unit_col == 0, in order) + units u8 [n][nu] (columns with
+// unit_col == 1: 0 / 1 valued by construction); flags[0] |= 1 if a unit column holds anything else
+__global__ void __launch_bounds__(256)
+dense_split_kernel(const double* __restrict__ data, int64_t ld, int64_t n, int ncols, const int32_t* __restrict__ dest,
+                   double* __restrict__ values, int64_t ldv, uint8_t* __restrict__ units, int64_t ldu,
+                   int32_t* __restrict__ flags) {
+    // dest[c] >= 0: value column number dest[c]; dest[c] < 0: unit column number ~dest[c]
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    bool bad = false;
+    for (int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n; r += warps) {
+        const double* x = data + r * ld;
+        for (int c = lane; c < ncols; c += 32) {
+            const double v = x[c];
+            const int d = dest[c];
+            if (d >= 0) {
+                values[r * ldv + d] = v;
+            } else {
+                bad |= !(v == 0.0 || v == 1.0);
+                units[r * ldu + ~d] = v != 0.0 ? 1 : 0;
+            }
+        }
+    }
+    if (bad) flags[0] = 1;
+}
+
+// int32 values -> u8; a value above 254 becomes 255 and goes to the overflow list (position, value) as well
+__global__ void __launch_bounds__(256)
+values_narrow_kernel(const int32_t* __restrict__ values, int64_t n, uint8_t* __restrict__ out, int64_t* __restrict__ over_pos,
+                     int32_t* __restrict__ over_val, int over_cap, unsigned* __restrict__ over_count) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
+    for (int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i0 < n; i0 += stride) {
+        if (i0 + 4 <= n) {
+            const int4 v = *reinterpret_cast<const int4*>(values + i0);
+            const int w[4] = {v.x, v.y, v.z, v.w};
+            unsigned packed = 0u;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool big = w[q] > 254 || w[q] < 0;
+                packed |= (big ? 255u : (unsigned)w[q]) << (8 * q);
+                if (big) {
+                    const unsigned k = atomicAdd(over_count, 1u);
+                    if (k < (unsigned)over_cap) {
+                        over_pos[k] = i0 + q;
+                        over_val[k] = w[q];
+                    }
+                }
+            }
+            *reinterpret_cast<unsigned*>(out + i0) = packed;
+        } else {
+            for (int64_t i = i0; i < n; ++i) {
+                const int w = values[i];
+                const bool big = w > 254 || w < 0;
+                out[i] = big ? 255 : (uint8_t)w;
+                if (big) {
+                    const unsigned k = atomicAdd(over_count, 1u);
+                    if (k < (unsigned)over_cap) {
+                        over_pos[k] = i;
+                        over_val[k] = w;
+                    }
+                }
+            }
+        }
+    }
+}
+
 }  // namespace tmog
 
 using namespace tmog;
@@ -143,6 +213,30 @@ extern "C" int tmog_vector_export_write_dev(const void* parts, int nparts, int64
     vector_export_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(
         static_cast<const ExportPart*>(parts), nparts, n, size, const_cast<uint8_t*>(type), nullptr, nullptr, nullptr,
         idx_off, val_off, indices, values);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_dense_split_dev(const double* data, int64_t ld, int64_t n, int ncols, const int32_t* dest,
+                                    double* values, int64_t ldv, uint8_t* units, int64_t ldu, int32_t* flags, void* stream) {
+    TMOG_REQUIRE(n >= 0 && ncols >= 0 && ld >= ncols, "bad shape");
+    if (n == 0 || ncols == 0) return TMOG_OK;
+    TMOG_REQUIRE(data && dest && flags && (values || ldv == 0) && (units || ldu == 0), "NULL argument");
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n + 7) / 8, (int64_t)sm_count() * 16));
+    dense_split_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(data, ld, n, ncols, dest, values, ldv, units, ldu, flags);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_values_narrow_dev(const int32_t* values, int64_t n, uint8_t* out, int64_t* over_pos, int32_t* over_val,
+                                      int over_cap, uint32_t* over_count, void* stream) {
+    TMOG_REQUIRE(n >= 0 && over_cap >= 0, "bad shape");
+    if (n == 0) return TMOG_OK;
+    TMOG_REQUIRE(values && out && over_count && (over_cap == 0 || (over_pos && over_val)), "NULL argument");
+    TMOG_REQUIRE((reinterpret_cast<uintptr_t>(values) & 15u) == 0 && (reinterpret_cast<uintptr_t>(out) & 3u) == 0,
+                 "values must be 16-byte aligned, out 4-byte aligned");
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n / 4 + 255) / 256, (int64_t)sm_count() * 16));
+    values_narrow_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(values, n, out, over_pos, over_val, over_cap, over_count);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }

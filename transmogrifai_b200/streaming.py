@@ -276,12 +276,17 @@ class HostSink:
     the upload of chunk k + 2).  consume(index, vector, host_tensors) is called once a chunk's copies have landed, in
     order; the pinned buffers are reused after that."""
 
-    def __init__(self, depth: int = 2, consume=None):
-        self.depth, self.consume = depth, consume
+    def __init__(self, depth: int = 2, consume=None, compact: bool = False):
+        """compact: the chunk crosses PCIe in the compact return format (compact_parts): the 0 / 1 columns of dense
+        blocks and the term frequencies of sparse rows as bytes; consume then gets [(name, host tensor)] and
+        expand_compact() turns them back into the vector."""
+        self.depth, self.consume, self.compact = depth, consume, compact
         self.stream = torch.cuda.Stream()
         self.slots = [dict(bufs=[], ev=None, item=None) for _ in range(depth)]
         self.bytes = 0
         self.chunks = 0
+        self._dest: Dict[tuple, tuple] = {}
+        self._flags = None
 
     @staticmethod
     def _tensors(parts):
@@ -304,7 +309,14 @@ class HostSink:
     def __call__(self, k: int, vec: VectorColumn, parts) -> None:
         slot = self.slots[k % self.depth]
         self._drain(slot)
-        tensors = self._tensors(parts)
+        names = None
+        if self.compact:
+            if self._flags is None:
+                self._flags = torch.zeros(4, dtype=torch.int32, device="cuda")
+            named = compact_parts(vec, parts, self._dest, self._flags)
+            names, tensors = [nm for nm, _t in named], [t for _nm, t in named]
+        else:
+            tensors = self._tensors(parts)
         main = torch.cuda.current_stream()
         self.stream.wait_stream(main)
         views = []
@@ -324,13 +336,117 @@ class HostSink:
                 self.bytes += nbytes
             ev = torch.cuda.Event()
             ev.record(self.stream)
-        slot["ev"], slot["item"] = ev, (k, vec, views)
+        slot["ev"], slot["item"] = ev, (k, vec, views if names is None else list(zip(names, views)))
         self.chunks += 1
 
     def finish(self) -> None:
         order = sorted((s for s in self.slots if s["item"] is not None), key=lambda s: s["item"][0])
         for s in order:
             self._drain(s)
+        if self._flags is not None and int(self._flags[0].item()):
+            raise ValueError("a null-indicator / Binary column holds a value other than 0 and 1: use compact=False")
+
+
+def _unit_columns(vec: VectorColumn, col0: int, width: int) -> np.ndarray:
+    """Which columns [col0, col0 + width) of the vector are 0 / 1 by construction: null indicators and the values of
+    Binary features."""
+    cols = vec.metadata.columns[col0:col0 + width]
+    return np.array([bool(c.isNullIndicator) or (len(c.parentFeatureType) == 1 and c.parentFeatureType[0] == F.BINARY)
+                     for c in cols], dtype=bool)
+
+
+def compact_parts(vec: VectorColumn, parts, dest_cache: Optional[dict] = None, flags: Optional[torch.Tensor] = None):
+    """The materialised parts of a chunk's vector in the compact return format, as [(name, device tensor)]:
+      dense block p  ->  "p.values" f64 [n][nv] (its other columns, in order) + "p.units" u8 [n][nu] (its 0 / 1 columns,
+                         in order; _unit_columns says which they are -- the receiver applies the same rule to the
+                         metadata);
+      one-hot block  ->  "p.indices" int32 [n][k] as it is;
+      sparse rows    ->  "p.row_start", "p.row_nnz", "p.indices" as they are, "p.values" u8 (255 = look the entry up in
+                         "p.over_pos" / "p.over_val", "p.over_count" of them)."""
+    from . import _lib as L
+    dest_cache = {} if dest_cache is None else dest_cache
+    flags = torch.zeros(4, dtype=torch.int32, device="cuda") if flags is None else flags
+    out = []
+    col0 = 0
+    for i, p in enumerate(parts):
+        data = p if isinstance(p, torch.Tensor) else getattr(p, "data", None)
+        if isinstance(data, torch.Tensor) and data.dtype == torch.float64 and data.dim() == 2:
+            n, w = data.shape
+            key = (i, col0, w)
+            hit = dest_cache.get(key)
+            if hit is None:
+                unit = _unit_columns(vec, col0, w)
+                dest = np.where(unit, ~(np.cumsum(unit) - 1), np.cumsum(~unit) - 1).astype(np.int32)
+                hit = dest_cache[key] = (torch.from_numpy(dest).cuda(), int((~unit).sum()), int(unit.sum()))
+            d_dest, nv, nu = hit
+            values = torch.empty((n, nv), dtype=torch.float64, device="cuda")
+            units = torch.empty((n, nu), dtype=torch.uint8, device="cuda")
+            L.call("tmog_dense_split_dev", data.data_ptr(), data.stride(0), n, w, d_dest.data_ptr(), R.ptr(values), nv,
+                   R.ptr(units), nu, flags.data_ptr(), R.stream())
+            out += [(f"{i}.values", values), (f"{i}.units", units)]
+            col0 += w
+        elif hasattr(p, "row_start"):
+            nnz = p.values.numel()
+            v8 = torch.empty(max(nnz, 4), dtype=torch.uint8, device="cuda")
+            over_pos = torch.zeros(256, dtype=torch.int64, device="cuda")
+            over_val = torch.zeros(256, dtype=torch.int32, device="cuda")
+            over_count = torch.zeros(1, dtype=torch.int32, device="cuda")
+            L.call("tmog_values_narrow_dev", p.values.data_ptr(), nnz, v8.data_ptr(), over_pos.data_ptr(),
+                   over_val.data_ptr(), 256, over_count.data_ptr(), R.stream())
+            out += [(f"{i}.row_start", p.row_start), (f"{i}.row_nnz", p.row_nnz), (f"{i}.indices", p.indices),
+                    (f"{i}.values", v8[:nnz]), (f"{i}.over_pos", over_pos), (f"{i}.over_val", over_val),
+                    (f"{i}.over_count", over_count)]
+            col0 += p.width
+        else:
+            out.append((f"{i}.indices", p.indices))
+            col0 += p.width
+    return out
+
+
+def part_widths(parts) -> List[int]:
+    return [int(p.shape[1]) if isinstance(p, torch.Tensor) else int(p.width) for p in parts]
+
+
+def expand_compact(vec: VectorColumn, widths: Sequence[int], named, n: int):
+    """The scipy CSR matrix of a chunk from what HostSink(compact=True) delivered (what the receiving side does);
+    widths = part_widths(parts): the columns of every part, which the receiver knows from the vector's metadata."""
+    import scipy.sparse as sp
+    by: Dict[int, dict] = {}
+    for name, t in named:
+        i, field = name.split(".")
+        by.setdefault(int(i), {})[field] = t.cpu().numpy() if isinstance(t, torch.Tensor) else np.asarray(t)
+    mats = []
+    col0 = 0
+    for i, w in enumerate(widths):
+        f = by[i]
+        if "units" in f:
+            unit = _unit_columns(vec, col0, w)
+            dense = np.zeros((n, w))
+            dense[:, ~unit] = f["values"]
+            dense[:, unit] = f["units"]
+            mats.append(sp.csr_matrix(dense))
+        elif "row_start" in f:
+            val = f["values"].astype(np.float64)
+            cnt = int(f["over_count"][0])
+            if cnt > len(f["over_pos"]):
+                raise ValueError("more term frequencies above 254 than the overflow list holds")
+            val[f["over_pos"][:cnt]] = f["over_val"][:cnt]
+            nnz = f["row_nnz"].astype(np.int64)
+            indptr = np.zeros(n + 1, dtype=np.int64)
+            indptr[1:] = np.cumsum(nnz)
+            take = np.repeat(f["row_start"] - indptr[:-1], nnz) + np.arange(indptr[-1])
+            mats.append(sp.csr_matrix((val[take], f["indices"][take].astype(np.int64), indptr), shape=(n, w)))
+        else:
+            idx = f["indices"]
+            k = idx.shape[1]
+            flat = idx.reshape(-1)
+            ok = flat >= 0
+            m = sp.csr_matrix((np.ones(int(ok.sum())), (np.repeat(np.arange(n), k)[ok], flat[ok].astype(np.int64))),
+                              shape=(n, w))
+            m.sum_duplicates()
+            mats.append(m)
+        col0 += w
+    return sp.hstack(mats).tocsr()
 
 
 def _release(chunk: ColumnarBatch) -> None:
