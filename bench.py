@@ -876,8 +876,8 @@ def main():
         h2d = sum(in_bytes[i % n_host] + label_bytes + (0 if i < kept else in_bytes[i % n_host] -
                                                         (text_bytes[i % n_host] if i < packed else 0))
                   for i in range(len(hchunks))) + in_bytes[0]
-        e2e = {"value": rows_e2e * world / dt, "unit": "rows/s", "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(hs.bytes), "ms_per_step": dt * 1e3, "steps": 1, "rows": rows_e2e * world,
+        e2e = {"value": rows_e2e * world / dt, "unit": "rows/s", "h2d_bytes_per_step": int(h2d) * world,
+               "d2h_bytes_per_step": int(hs.bytes) * world,      # every rank moves its own (equal) share "ms_per_step": dt * 1e3, "steps": 1, "rows": rows_e2e * world,
                "distinct_host_chunks": n_host, "chunks_kept_in_hbm_between_passes": kept,
                "hbm_cache_budget_bytes": budget, "chunks_with_packed_cells": packed, "cell_cache_bytes": e_cells,
                "return_format": ("full width: f64 dense blocks, int32 term frequencies" if args.full_width_return else
