@@ -102,6 +102,31 @@ __device__ __forceinline__ unsigned ts_hash_token(const unsigned* ring, int ps, 
     return fmix32(h, pn + (unsigned)plen);
 }
 
+// the same for a token of at most 15 bytes with the prefix remainder, from the four words that follow the position
+// (token start - prefix remainder), already loaded and aligned: no loads, a fixed number of steps
+__device__ __forceinline__ unsigned ts_hash_words(unsigned s0r, unsigned s1, unsigned s2, unsigned s3, int plen, unsigned ph,
+                                                  unsigned pw, unsigned pn) {
+    const int r = (int)(pn & 3u);
+    const unsigned keep_hi = ~((1u << (8 * r)) - 1u);
+    const int tot = r + plen, nfull = tot >> 2, tail = tot & 3;
+    const unsigned s0 = (s0r & keep_hi) | pw;
+    unsigned h = ph;
+    unsigned t = mix_h1(h, mix_k1(s0));
+    h = nfull > 0 ? t : h;
+    t = mix_h1(h, mix_k1(s1));
+    h = nfull > 1 ? t : h;
+    t = mix_h1(h, mix_k1(s2));
+    h = nfull > 2 ? t : h;
+    const unsigned wd = nfull == 0 ? s0 : nfull == 1 ? s1 : nfull == 2 ? s2 : s3;
+    t = mix_h1(h, mix_k1((unsigned)(int)(signed char)(wd & 0xffu)));
+    h = tail > 0 ? t : h;
+    t = mix_h1(h, mix_k1((unsigned)(int)(signed char)((wd >> 8) & 0xffu)));
+    h = tail > 1 ? t : h;
+    t = mix_h1(h, mix_k1((unsigned)(int)(signed char)((wd >> 16) & 0xffu)));
+    h = tail > 2 ? t : h;
+    return fmix32(h, pn + (unsigned)plen);
+}
+
 // bits 7, 15, 23, 31 of four words -> 16 bits
 __device__ __forceinline__ unsigned ts_compress(const unsigned (&t)[4]) {
     unsigned m = 0u;
@@ -232,9 +257,15 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 const int plen = (int)(e >> 16), ps = (int)(e & (unsigned)TS_POS_MASK);
                 const int cell = (int)tbl[(e >> 11) & 31u];
                 bool keep = plen >= min_len && ((valid_mask >> cell) & 1u);       // plen == 0: no token
+                // the words that hold the token, from (start - prefix remainder) on: read once, for the stop-word filter
+                // and for murmur3
+                const int pr = (int)(pn & 3u), q0 = ps - pr, sh = (q0 & 3) * 8;
+                const unsigned* rp = ring + ((q0 >> 2) & (TS_RING_WORDS - 1));
+                const unsigned a0 = rp[0], a1 = rp[1], a2 = rp[2], a3 = rp[3], a4 = rp[4];
+                const unsigned s0r = __funnelshift_r(a0, a1, sh), s1 = __funnelshift_r(a1, a2, sh);
+                const unsigned s2 = __funnelshift_r(a2, a3, sh), s3 = __funnelshift_r(a3, a4, sh);
                 if (keep) {
-                    const unsigned* rs = ring + (ps >> 2);
-                    const unsigned first4 = __funnelshift_r(rs[0], rs[1], (ps & 3) * 8);
+                    const unsigned first4 = __funnelshift_r(s0r, s1, 8 * pr);
                     const unsigned c0 = first4 & 0xffu;
                     if (c0 == '_') {                                 // a run of '_' only is not a token
                         keep = false;
@@ -255,7 +286,8 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                     if (keep && lane == __ffs(grp) - 1) atomicAdd(&lens[cell], sum);
                 }
                 if (keep && hashed) {
-                    const unsigned hv = ts_hash_token(ring, ps, plen, ph, pw, pn);
+                    const unsigned hv = pr + plen <= 15 ? ts_hash_words(s0r, s1, s2, s3, plen, ph, pw, pn)
+                                                        : ts_hash_token(ring, ps, plen, ph, pw, pn);
                     const int bucket = p.pow2_mask >= 0 ? (int)(hv & (unsigned)p.pow2_mask) : non_negative_mod(hv, F);
                     const unsigned bit = 1u << (bucket & 31);
                     const unsigned old = atomicOr(&bm[cell * TS_BM_STRIDE + (bucket >> 5)], bit);
