@@ -841,7 +841,13 @@ def main():
     e2e = None
     if not args.no_e2e:
         from transmogrifai_b200.streaming import HostSink
-        n_host = min(len(ring), 4)
+        # pinned host memory: at most a third of what the box has free, shared by the ranks (distinct host chunks: up to 4)
+        try:
+            avail = next(int(ln.split()[1]) * 1024 for ln in open("/proc/meminfo") if ln.startswith("MemAvailable"))
+        except (OSError, StopIteration):
+            avail = 64 << 30
+        chunk_host_bytes = benchdata.input_bytes(ring[0]) + 8 * chunk_rows
+        n_host = int(max(1, min(len(ring), 4, (avail // 3 // world - 2 * chunk_host_bytes) // chunk_host_bytes)))
         hring = [benchdata.host_copy(b) for b in ring[:n_host]]
         for h, b in zip(hring, ring):
             h.token = b.token
