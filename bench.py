@@ -307,11 +307,21 @@ def kernel_times(workload, batch, fitted, info, reps: int = 5, text_offset: int 
 # DRAM bytes per row of the config-2 kernels, from `ncu --set full` (profiles/r01_c2_full_raw.csv: 10 M rows, 199 of
 # 200 columns kept): pack transform 8.125 GB read + 15.862 GB written, fit scan 8.286 GB read + 0.004 GB written
 NCU_DRAM_BYTES_PER_ROW = {"vec_transform_pack_kernel<double, true>": 2398.8, "real_fit_tma_kernel": 829.0}
+# config 5's text calls, from profiles/r02_c5_text_raw.csv (1 M rows x 30 text columns): span kernel 7.02 GB read +
+# 3.81 GB of records written, text_rows_kernel 3.91 GB read + 5.76 GB written; fit + pack 7.02 + 1.51 GB; packed rows
+# 2.98 + 5.76 GB; fit without packing 7.04 GB read (r02_span captures at 500 k rows)
+NCU_DRAM_BYTES_PER_ROW_C5 = {
+    "text tokenise + hash: sparse rows of the kept columns (pass 2)": 20503.0,
+    "text statistics + packed cells (pass 1 when the cells are kept)": 8533.0,
+    "text tokenise + hash: bucket statistics (pass 1)": 7050.0,
+    "text_rows_packed_kernel: sparse rows from packed cells (pass 2)": 8738.0,
+}
 
 
 def traffic_gb(workload: str, kernel: str, rows: int):
     """Measured DRAM traffic of one launch of `kernel` in GB (None where no capture exists for the workload)."""
-    per_row = NCU_DRAM_BYTES_PER_ROW.get(kernel) if workload == "c2" else None
+    per_row = NCU_DRAM_BYTES_PER_ROW.get(kernel) if workload == "c2" else \
+        NCU_DRAM_BYTES_PER_ROW_C5.get(kernel) if workload == "c5" else None
     return None if per_row is None else per_row * rows / 1e9
 
 
@@ -936,7 +946,12 @@ def main():
                                                 "inside every step"},
                        **summary},
             "roofline": {"bound": "hbm", "kernel": top["kernel"], "achieved": top["achieved"], "peak": peak,
-                         "unit": "GB/s", "frac": top["frac"], "traffic": None, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": top["frac"], "traffic": traffic_gb("c5", top["kernel"], chunk_rows),
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one ncu --set full capture at "
+                                           "1 M rows, scaled by rows (profiles/r02_c5_text_raw.csv); for the pass-2 call "
+                                           "it includes the 128-byte cell records written by one kernel and read by the "
+                                           "next (7.7 KB per row beyond the algorithmic bytes)",
+                         "peak_source": peak_src,
                          "ms": top["ms"], "bytes_per_row": top["bytes_per_row"], "rows_per_launch": chunk_rows,
                          "step_frac": step_frac, "other": kt[1:]},
             "parity_check": check, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
