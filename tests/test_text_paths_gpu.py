@@ -98,3 +98,100 @@ def test_cell_path_matches_oracle_on_special_cells():
         exp = V.smart_text_transform(cols, names, ["Hash"] * 2, [[], []], num_features=nf, hash_space_strategy="Separate")
         import scipy.sparse as sp
         assert abs(got - sp.csr_matrix(exp)).max() == 0
+
+
+def _fuzz_cells(rng, n, heavy_punct):
+    """Random ASCII cells: letters, digits, '_', the Mid* characters and separators in changing proportions, lengths
+    from 0 to a few thousand bytes, runs of token characters of every length around the fast path's limits."""
+    letters = "abcdefghijklmnopqrstuvwxyzABCDEFGHIJKLMNOPQRSTUVWXYZ"
+    alphabet = letters * 3 + "0123456789" * (3 if heavy_punct else 1) + "_" * (4 if heavy_punct else 1) + \
+        (".':,;" * 6 if heavy_punct else ".,") + "   \t\n-/()!?\"&" * (2 if heavy_punct else 4)
+    alphabet = np.frombuffer(alphabet.encode(), dtype=np.uint8)
+    out = []
+    for i in range(n):
+        u = rng.random()
+        if u < 0.04:
+            out.append(None)
+        elif u < 0.07:
+            out.append("")
+        else:
+            length = int(rng.choice([1, 2, 3, 15, 16, 17, 31, 32, 33, 47, 48, 63, 64, 65, 200, 511, 512, 513, 1500, 3000])
+                         if rng.random() < 0.3 else rng.integers(1, 400))
+            b = alphabet[rng.integers(0, len(alphabet), size=length)].copy()
+            if rng.random() < 0.1:                      # a long run of token characters somewhere
+                k = int(rng.integers(40, 60))
+                at = int(rng.integers(0, max(1, length - k)))
+                b[at:at + k] = ord("x")
+            out.append(b.tobytes().decode())
+    return out
+
+
+@pytest.mark.parametrize("heavy_punct,num_features,min_len", [(True, 512, 1), (False, 100, 2)])
+def test_fuzz_span_kernel_against_row_table_kernel_and_oracle(heavy_punct, num_features, min_len):
+    """Random cells (see _fuzz_cells): the span kernel, the lane-per-cell kernel and the per-row table kernel give the
+    same statistics and rows; a sample of the rows against the oracle."""
+    from oracle import vectorizers as V
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch, NumericBlock, TextBlock
+    rng = np.random.default_rng(2024 + int(heavy_punct))
+    n = 6011                                            # not a multiple of 32
+    cols = [_fuzz_cells(rng, n, heavy_punct) for _ in range(3)]
+    names = ["fz0", "fz1", "fz2"]
+    block = TextBlock.from_lists(names, F.TEXT, cols).to("cuda")
+    y = torch.from_numpy((rng.random(n) < 0.5).astype(np.float64)).cuda()
+    label = NumericBlock(["label"], F.REALNN, y.view(1, -1), None, n)
+    batch = ColumnarBatch(n, [block, label], {}, response="label")
+    out = {}
+    try:
+        for mode, env in (("span", {}), ("cells", {"TMOG_TEXT_PATH": "cells"}), ("rows", {"TMOG_TEXT_PATH": "rows"})):
+            for k in ("TMOG_TEXT_FORCE_SLOW", "TMOG_TEXT_PATH"):
+                os.environ.pop(k, None)
+            os.environ.update(env)
+            out[mode] = _model_outputs(batch, names, num_features, False, min_len, True, y)
+    finally:
+        for k in ("TMOG_TEXT_FORCE_SLOW", "TMOG_TEXT_PATH"):
+            os.environ.pop(k, None)
+    ref_st, ref_rows, _ = out["rows"]
+    for mode in ("span", "cells"):
+        st, rows, rows2 = out[mode]
+        for k in ("mean", "variance", "min", "max", "cov_label"):
+            assert np.array_equal(getattr(st, k), getattr(ref_st, k)), (mode, k)
+        assert abs(rows - ref_rows).max() == 0 and abs(rows2 - ref_rows).max() == 0, mode
+    take = 700
+    exp = V.smart_text_transform([c[:take] for c in cols], names, ["Hash"] * 3, [[], [], []], num_features=num_features,
+                                 hash_space_strategy="Separate", min_token_length=min_len)
+    import scipy.sparse as sp
+    assert abs(out["span"][1][:take] - sp.csr_matrix(exp)).max() == 0
+
+
+def test_packed_cells_with_more_than_32_text_columns():
+    """The packed row kernel walks the cells of a row 32 at a time: 40 hashed columns, against the rows from the text."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch, VectorColumn
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    from transmogrifai_b200.streaming import fit_and_transform_stream
+    import scipy.sparse as sp
+    rng = np.random.default_rng(5)
+    n, k = 700, 40
+    words = ["".join(rng.choice(list("abcdefgh"), size=rng.integers(2, 8))) for _ in range(200)]
+    cols = {f"c{j:02d}": (F.TEXT, [None if rng.random() < 0.1 else " ".join(words[i] for i in rng.integers(0, 200, rng.poisson(6)))
+                                   for _ in range(n)]) for j in range(k)}
+    cols["y"] = (F.REALNN, (rng.random(n) < 0.5).astype(np.float64).tolist())
+    chunks = [ColumnarBatch.from_columns({nm: (t, v[a:b]) for nm, (t, v) in cols.items()}, response="y")
+              for a, b in ((0, 333), (333, 700))]
+
+    def run(cell_bytes):
+        feats = [F.FeatureBuilder.Text(f"c{j:02d}").asPredictor() for j in range(k)]
+        label = F.FeatureBuilder.RealNN("y").asResponse()
+        vec = SmartTextVectorizer().setMaxCardinality(0).setNumFeatures(64).setInput(*feats).getOutput()
+        checked = label.sanityCheck(vec, removeBadFeatures=True, sampleLowerLimit=0, sampleUpperLimit=10 ** 9,
+                                    featureFeatureCorrLevel="Off", minVariance=2e-3)
+        out = []
+        res = fit_and_transform_stream(chunks, checked, lambda i, v, parts: out.append(
+            VectorColumn(v.name, v.n, v.metadata, parts).to_scipy()), cell_cache_bytes=cell_bytes)
+        return sp.vstack(out).tocsr(), res
+
+    ref, _r0 = run(0)
+    got, r1 = run(8 << 20)
+    assert r1.cells_cached == 2 and got.shape == ref.shape and got.shape[1] < k * 64 + k
+    assert abs(got - ref).max() == 0 and np.array_equal(got.indices, ref.indices)
