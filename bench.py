@@ -292,7 +292,7 @@ def kernel_times(workload, batch, fitted, info, reps: int = 5, text_offset: int 
                 token, meta, pflag, _n, kk = cells["pending"][-1]
                 if int(pflag.item()) == 0:
                     cells["chunks"][token] = (meta, n, kk)
-                    packed_bytes = int(cells["cursor"].item()) * 2 + meta.numel()
+                    packed_bytes = int(cells["cursor"].item()) + meta.numel()
                     t_tp = _time(tr, max(reps // 2, 1))
                     out.append({"kernel": "text statistics + packed cells (pass 1 when the cells are kept)", "ms": t_sp,
                                 "bytes_per_row": bpr + k * 8 + k / 8 + 1 + packed_bytes / max(n, 1),

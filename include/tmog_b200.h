@@ -376,9 +376,9 @@ int tmog_text_hash_fit_transform_dev(const int64_t* col_desc, int ncols, int64_t
                                      int32_t* flags, void* scratch, size_t scratch_bytes, void* stream);
 
 /* Packed cells: the statistics pass of a row chunk can keep what it found in every cell -- the cell's buckets and their
- * term frequencies, ~2 bytes per distinct token -- so that the transform of the same rows, which a chunk-streamed
+ * term frequencies, ~1.1 bytes per distinct token -- so that the transform of the same rows, which a chunk-streamed
  * fit-then-transform runs after all chunks have been fitted (FitStagesUtil.scala:212-290; the reference tokenises and
- * hashes the rows again, SmartTextVectorizer.scala:333-356), reads ~1.5 KB per row instead of the text and tokenises
+ * hashes the rows again, SmartTextVectorizer.scala:333-356), reads ~0.9 KB per row instead of the text and tokenises
  * nothing.  Separate hash spaces of at most 512 buckets per column only (tmog_text_hash_scratch_bytes2's layout).
  *   arena: device memory shared by all chunks, arena_cursor (device u64, zeroed once) counts the u16 entries handed
  *          out; pack_meta: per chunk, tmog_text_cells_pack_bytes bytes (track_len = the vector has text-length

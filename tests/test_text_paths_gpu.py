@@ -20,6 +20,8 @@ SPECIAL = [
     "ALL CAPS AND Mixed Case, with; punct: u.s.a. 1.2.3.4 a.1 1.a _._ a_.b",
     "x" * 15 + " " + "y" * 16 + " " + "z" * 17 + " " + "a" * 31 + " " + "b" * 32 + " " + "c" * 33,
     "tab\tsep\nnewline\rcr end", "trailing.", ".leading", "a", "ab", "9", "_",
+    # term frequencies 4, 5, 6 and 1 in one cell (the packed cells' trailer), and two of them in a row
+    "aa aa aa aa bb bb bb bb bb cc cc cc cc cc cc dd", "qq qq qq qq qq qq qq qq qq rr rr rr rr", "solo",
 ]
 
 

@@ -1723,8 +1723,8 @@ static int pack_view(void* meta, int64_t n, int ncols, bool track_len, void* are
     pk->rel = reinterpret_cast<unsigned short*>(m + pack_align(groups * sizeof(TsGroup)));
     pk->lens = track_len ? reinterpret_cast<unsigned*>(m + pack_align(groups * sizeof(TsGroup)) + pack_align((cells + 1) * 2))
                          : nullptr;
-    pk->arena = static_cast<unsigned short*>(arena);
-    pk->arena_entries = arena_bytes / 2;
+    pk->arena = static_cast<unsigned char*>(arena);
+    pk->arena_bytes = arena_bytes;
     pk->cursor = reinterpret_cast<unsigned long long*>(cursor);
     pk->flags = pack_flags;
     return TMOG_OK;

@@ -71,12 +71,15 @@ struct TcScratch {
 // ---- packed cells: what the fit pass found in every cell (its buckets and their term frequencies), kept in HBM so that
 //      the transform of the same rows needs neither the text nor a second tokenise + hash pass (text_packed.cuh reads
 //      them).  A group = 32 consecutive rows of one column = one span of text_span_kernel (text_span.cuh):
-//        arena   u16 entries, bucket | (term frequency - 1) << 9, ascending buckets per cell, the cells of a group one
-//                after the other; a group's entries start at a multiple of 8 (16-byte copies).  A cell the fast path
-//                set aside holds four entries instead: the arena offset of its slot (TS_SLOT_ENTRIES entries: the term
+//        arena   bytes.  A cell is a stream of entries in ascending bucket order: one byte (gap << 2 | tf code) where
+//                gap = buckets skipped since the entry before (0 .. 62) and tf code 0 .. 2 = term frequency 1 .. 3, code 3
+//                = the term frequency (- 4) is the next byte of the cell's trailer, which is read backwards from the
+//                cell's last byte; gap 63 (byte >= 0xFC) = the bucket follows as two bytes.  ~1.1 bytes per distinct
+//                token.  The cells of a group follow one another; a group starts at a multiple of 16.  A cell the fast
+//                path set aside holds eight bytes instead: the arena offset of its slot (TS_SLOT_ENTRIES u16: the term
 //                frequency of every bucket, the summed token length, the no-token flag), written by the slow kernel.
-//        grp     [ceil(n / 32)][ncols]: arena offset of the group's entries (~0: the arena was full), their number
-//        rel     [n][ncols] u16: where the cell's entries begin inside the group | no token survived << 14 | slot << 15
+//        grp     [ceil(n / 32)][ncols]: arena offset of the group's bytes (~0: the arena was full), their number
+//        rel     [n][ncols] u16: where the cell's bytes begin inside the group | no token survived << 14 | slot << 15
 //        lens    [n][ncols] u32 summed token lengths (only when the vector has text-length columns)
 constexpr int TS_SLOT_ENTRIES = TC_MAXF + 8;          // 512 term frequencies | length sum (2) | no-token flag | pad
 constexpr unsigned TS_REL_MASK = 0x3fffu, TS_REL_NOHIT = 0x4000u, TS_REL_SLOT = 0x8000u;
@@ -85,9 +88,9 @@ struct TsGroup {
     unsigned total, pad;
 };
 struct TsPack {
-    unsigned short* arena;
-    unsigned long long arena_entries;
-    unsigned long long* cursor;            // entries handed out so far
+    unsigned char* arena;
+    unsigned long long arena_bytes;
+    unsigned long long* cursor;            // bytes handed out so far
     TsGroup* grp;
     unsigned short* rel;
     unsigned* lens;                        // or NULL
@@ -699,17 +702,17 @@ text_cells_slow_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n
                 // packed cells: this cell gets a slot of its own; its four entries in the group point at it
                 const TsGroup g = pk.grp[(row >> 5) * ncols + j];
                 if (g.off != ~0ull) {
-                    const unsigned long long slot = atomicAdd(pk.cursor, (unsigned long long)TS_SLOT_ENTRIES);
-                    if (slot + TS_SLOT_ENTRIES > pk.arena_entries) {
+                    const unsigned long long slot = atomicAdd(pk.cursor, (unsigned long long)TS_SLOT_ENTRIES * 2);
+                    if (slot + TS_SLOT_ENTRIES * 2 > pk.arena_bytes) {
                         pk.flags[0] = 1;
                     } else {
-                        unsigned short* sl = pk.arena + slot;
+                        unsigned short* sl = reinterpret_cast<unsigned short*>(pk.arena + slot);
                         for (int q = 0; q < TC_MAXF; ++q) sl[q] = hashed && q < p.num_features ? counts[q] : (unsigned short)0;
                         sl[TC_MAXF] = (unsigned short)(len_sum & 0xffffu);
                         sl[TC_MAXF + 1] = (unsigned short)(len_sum >> 16);
                         sl[TC_MAXF + 2] = nohit ? 1 : 0;
-                        unsigned short* at = pk.arena + g.off + (pk.rel[row * ncols + j] & TS_REL_MASK);
-                        for (int q = 0; q < 4; ++q) at[q] = (unsigned short)((slot >> (16 * q)) & 0xffffull);
+                        unsigned char* at = pk.arena + g.off + (pk.rel[row * ncols + j] & TS_REL_MASK);
+                        for (int q = 0; q < 8; ++q) at[q] = (unsigned char)((slot >> (8 * q)) & 0xffull);
                     }
                 }
             }

@@ -1,6 +1,6 @@
 // The transform of rows whose cells the fit pass left in packed form (TsPack, text_cells.cuh): sorted sparse rows of the
 // kept columns without the text and without tokenising or hashing anything -- the second pass over a chunk-streamed
-// dataset (SmartTextVectorizer.scala:333-356 applied to the rows it was fitted on) reads ~1.5 KB per row instead of ~7 KB
+// dataset (SmartTextVectorizer.scala:333-356 applied to the rows it was fitted on) reads ~0.9 KB per row instead of ~7 KB
 // of text.  Same output as text_cells_kernel / text_span_kernel + text_rows_kernel, entry for entry.
 //
 //   text_rows_packed_kernel   a warp per row, a lane per cell: the lane walks its cell's entries (ascending buckets),
@@ -19,13 +19,14 @@ constexpr int TP_STAGE = 1536;            // entries of a row the stage holds
 constexpr int TP_WARP_BYTES = TP_STAGE * 4 + TP_STAGE;
 
 struct TpCell {
-    unsigned long long off;               // arena offset of the cell's entries (of its slot when slot is set)
-    int cnt;                              // entries (buckets of the slot that hold something)
+    unsigned long long off;               // arena offset of the cell's bytes (of its slot when slot is set)
+    int cnt;                              // stage places the cell takes: its bytes (an upper bound of its entries), or
+                                          // for a slot the buckets that hold something
     bool slot, nohit;
     unsigned len_sum;
 };
 
-// the cell (row, j): where its entries are and how many
+// the cell (row, j): where its bytes are and how many
 __device__ __forceinline__ TpCell tp_cell(const TsPack& pk, int ncols, int64_t n, int64_t row, int j, bool want_len) {
     TpCell c;
     const unsigned r = pk.rel[row * ncols + j];
@@ -38,11 +39,11 @@ __device__ __forceinline__ TpCell tp_cell(const TsPack& pk, int ncols, int64_t n
     c.nohit = (r & TS_REL_NOHIT) != 0u;
     c.len_sum = (want_len && pk.lens) ? pk.lens[row * ncols + j] : 0u;
     if (c.slot) {
-        const unsigned short* at = pk.arena + c.off;
+        const unsigned char* at = pk.arena + c.off;
         unsigned long long s = 0ull;
-        for (int q = 0; q < 4; ++q) s |= (unsigned long long)at[q] << (16 * q);
+        for (int q = 0; q < 8; ++q) s |= (unsigned long long)at[q] << (8 * q);
         c.off = s;
-        const unsigned short* sl = pk.arena + s;
+        const unsigned short* sl = reinterpret_cast<const unsigned short*>(pk.arena + s);
         int m = 0;
         for (int q = 0; q < TC_MAXF; ++q) m += sl[q] != 0;
         c.cnt = m;
@@ -52,26 +53,52 @@ __device__ __forceinline__ TpCell tp_cell(const TsPack& pk, int ncols, int64_t n
     return c;
 }
 
-// entry k of a cell in ascending bucket order -> (bucket, term frequency); for a slot the k-th bucket that holds something
-// is found by walking (slots are rare)
+// the entries of a cell in ascending bucket order: f(k, bucket, term frequency) -> number of entries.  The bytes are
+// read sixteen at a time (loads in flight), then decoded in order (TsPack's format); for a slot the buckets that hold
+// something are found by walking (slots are rare)
 template <typename F>
-__device__ __forceinline__ void tp_for_entries(const TsPack& pk, const TpCell& c, F&& f) {
+__device__ __forceinline__ int tp_for_entries(const TsPack& pk, const TpCell& c, F&& f) {
+    int k = 0;
     if (!c.slot) {
-        const unsigned short* __restrict__ e = pk.arena + c.off;
-        for (int k0 = 0; k0 < c.cnt; k0 += 16) {                  // sixteen loads in flight, then their entries
+        const unsigned char* __restrict__ e = pk.arena + c.off;
+        const int nbytes = c.cnt;
+        int prev = -1, tused = 0, state = 0;
+        unsigned lo = 0u, code = 0u;
+        for (int k0 = 0; k0 < nbytes; k0 += 16) {
             unsigned v[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = k0 + i < c.cnt ? (unsigned)e[k0 + i] : 0u;
+            for (int i = 0; i < 16; ++i) v[i] = k0 + i < nbytes ? (unsigned)e[k0 + i] : 0u;
 #pragma unroll
-            for (int i = 0; i < 16; ++i)
-                if (k0 + i < c.cnt) f(k0 + i, (int)(v[i] & 0x1ffu), (int)(v[i] >> 9) + 1);
+            for (int i = 0; i < 16; ++i) {
+                if (k0 + i < nbytes - tused) {               // the trailer shrinks the stream from behind
+                    const unsigned b = v[i];
+                    int bucket = -1;
+                    if (state == 0) {
+                        code = b & 3u;
+                        if (b >= 0xFCu) state = 1;
+                        else bucket = prev + 1 + (int)(b >> 2);
+                    } else if (state == 1) {
+                        lo = b;
+                        state = 2;
+                    } else {
+                        bucket = (int)(lo | ((b & 1u) << 8));
+                        state = 0;
+                    }
+                    if (bucket >= 0) {
+                        int tf = (int)code + 1;
+                        if (code == 3u) tf = (int)e[nbytes - 1 - tused++] + 4;
+                        f(k++, bucket, tf);
+                        prev = bucket;
+                    }
+                }
+            }
         }
     } else {
-        const unsigned short* sl = pk.arena + c.off;
-        int k = 0;
+        const unsigned short* sl = reinterpret_cast<const unsigned short*>(pk.arena + c.off);
         for (int q = 0; q < TC_MAXF; ++q)
             if (sl[q]) f(k++, q, (int)sl[q]);
     }
+    return k;
 }
 
 __global__ void __launch_bounds__(TP_WARPS * 32)
@@ -124,7 +151,7 @@ text_rows_packed_kernel(int ncols, int64_t n, TcParams p, TsPack pk, const int32
                 // a column none of whose buckets was dropped maps bucket b to (its first output column) + b
                 const int lo = np[0], hi = np[F - 1];
                 const bool whole = lo >= 0 && hi - lo == F - 1;
-                tp_for_entries(pk, c, [&](int k, int bucket, int tf) {
+                const int used = tp_for_entries(pk, c, [&](int k, int bucket, int tf) {
                     const int v = whole ? lo + bucket : np[bucket];
                     kept += v >= 0;
                     if (so + k < TP_STAGE) {
@@ -132,6 +159,8 @@ text_rows_packed_kernel(int ncols, int64_t n, TcParams p, TsPack pk, const int32
                         sval[so + k] = (unsigned char)(p.binary_freq ? 1 : min(tf, 255));
                     }
                 });
+                for (int k = used; k < c.cnt; ++k)               // a cell has fewer entries than bytes: the rest is empty
+                    if (so + k < TP_STAGE) sidx[so + k] = -1;
             }
             const bool has_len = j < ncols && want_len && c.len_sum > 0u && newpos[p.len_base + j] >= 0;
             const bool has_null = j < ncols && p.track_nulls && c.nohit && newpos[p.null_base + j] >= 0;

@@ -516,36 +516,51 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 atomicOr(&defer_bits[cell >> 5], 1u << (cell & 31));
             }
             if (PACK) {
-                // ---- the cells of this span in packed form.  The ring and the queue are free now: the ring holds the
-                //      entries before every bitmap word of a cell, the queue stages the group's entries
-                unsigned* before = ring;                             // [TC_FW][32]
-                int cnt = 0;
-                if (in_rows && hashed && !deferred) {
+                // ---- the cells of this span in packed form (TsPack).  The ring and the queue are free now: the ring
+                //      holds, per bitmap word of a cell, the bytes of the cell's stream before it; the queue stages the
+                //      group's bytes
+                unsigned* before = ring;              // [TC_FW][32]: bytes before word w | its first bucket is far << 31
+                int nbytes = 0, cnt = 0, n4 = 0;
+                const bool plain = in_rows && hashed && !deferred;
+                if (plain) {
+                    int zrun = 0;                     // buckets skipped since the last one met
 #pragma unroll
                     for (int w = 0; w < TC_FW; ++w) {
-                        before[w * 32 + lane] = (unsigned)cnt;
-                        cnt += __popc(mybm[w]);
+                        const unsigned x = mybm[w];
+                        const bool far = x != 0u && zrun + __ffs(x) - 1 > 62;
+                        before[w * 32 + lane] = (unsigned)nbytes | (far ? 0x80000000u : 0u);
+                        if (x) {
+                            cnt += __popc(x);
+                            nbytes += __popc(x) + (far ? 2 : 0);
+                            zrun = __clz(x);
+                        } else {
+                            zrun += 32;
+                        }
                     }
+                    if (!p.binary_freq)
+                        for (int q = 0; q < ndup; ++q) n4 += (app[q * 32 + lane] >> 9) >= 4u;
+                    nbytes += n4;
                 }
-                if (in_rows && deferred) cnt = 4;
-                int incl = cnt;
+                if (in_rows && deferred) nbytes = 8;
+                int incl = nbytes;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
                     const int up = __shfl_up_sync(FULL, incl, o);
                     if (lane >= o) incl += up;
                 }
-                const int excl = incl - cnt, total = __shfl_sync(FULL, incl, 31), alloc = (total + 7) & ~7;
+                const int excl = incl - nbytes, total = __shfl_sync(FULL, incl, 31), alloc = (total + 15) & ~15;
                 unsigned long long off = 0ull;
                 if (lane == 0 && total > 0) {
                     off = atomicAdd(pk.cursor, (unsigned long long)alloc);
-                    if (off + (unsigned long long)alloc > pk.arena_entries) {
+                    // a cell's place inside its group has 14 bits: a group beyond that makes the chunk unusable
+                    if (off + (unsigned long long)alloc > pk.arena_bytes || total > (int)TS_REL_MASK) {
                         pk.flags[0] = 1;
                         off = ~0ull;
                     }
                 }
                 off = __shfl_sync(FULL, off, 0);
                 if (in_rows) {
-                    pk.rel[row * ncols + j] = (unsigned short)((unsigned)excl | (nohit ? TS_REL_NOHIT : 0u) |
+                    pk.rel[row * ncols + j] = (unsigned short)(((unsigned)excl & TS_REL_MASK) | (nohit ? TS_REL_NOHIT : 0u) |
                                                                (deferred ? TS_REL_SLOT : 0u));
                     if (pk.lens) pk.lens[row * ncols + j] = need_lens ? len_sum : 0u;
                 }
@@ -557,32 +572,51 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                     pk.grp[(g0 >> 5) * ncols + j] = g;
                 }
                 if (total > 0 && off != ~0ull) {
-                    const bool staged = alloc <= TS_Q * 2;
-                    unsigned short* stage = reinterpret_cast<unsigned short*>(tq);
-                    unsigned short* dst = (staged ? stage : pk.arena + off) + excl;
+                    const bool staged = alloc <= TS_Q * 4;
+                    unsigned char* stage = reinterpret_cast<unsigned char*>(tq);
+                    unsigned char* dst = (staged ? stage : pk.arena + off) + excl;
                     if (in_rows && deferred) {
-                        dst[0] = dst[1] = dst[2] = dst[3] = 0;                  // the slow kernel leaves the slot here
-                    } else if (cnt > 0) {
+                        for (int q = 0; q < 8; ++q) dst[q] = 0;                 // the slow kernel leaves the slot here
+                    } else if (plain && cnt > 0) {
                         // one loop over the cell's buckets (not one per bitmap word: the lanes would wait for the
                         // fullest word of the 32 cells sixteen times)
-                        int w = 0;
+                        int w = 0, prev = -1, k = 0;
                         unsigned x = mybm[0];
-                        for (int k = 0; k < cnt; ++k) {
+                        for (int i = 0; i < cnt; ++i) {
                             while (!x) x = mybm[++w];
-                            dst[k] = (unsigned short)(w * 32 + __ffs(x) - 1);
+                            const int bucket = w * 32 + __ffs(x) - 1, gap = bucket - prev - 1;
                             x &= x - 1u;
+                            prev = bucket;
+                            if (gap <= 62) {
+                                dst[k++] = (unsigned char)(gap << 2);
+                            } else {
+                                dst[k] = 0xFC;
+                                dst[k + 1] = (unsigned char)(bucket & 0xff);
+                                dst[k + 2] = (unsigned char)(bucket >> 8);
+                                k += 3;
+                            }
                         }
+                        // term frequencies above 1: the code goes into the entry's first byte, 4 and more to the trailer
                         if (!p.binary_freq)
                             for (int q = 0; q < ndup; ++q) {
-                                const unsigned e = app[q * 32 + lane], bkt = e & 0x1ffu;
-                                const int at = (int)before[(bkt >> 5) * 32 + lane] +
-                                               __popc(mybm[bkt >> 5] & ((1u << (bkt & 31u)) - 1u));
-                                dst[at] = (unsigned short)(bkt | (((e >> 9) - 1u) << 9));
+                                const unsigned e = app[q * 32 + lane], bkt = e & 0x1ffu, tf = e >> 9;
+                                const unsigned bw = before[(bkt >> 5) * 32 + lane];
+                                const unsigned below = mybm[bkt >> 5] & ((1u << (bkt & 31u)) - 1u);
+                                const int at = (int)(bw & 0x7fffffffu) + __popc(below) + ((bw >> 31) && below ? 2 : 0);
+                                dst[at] = (unsigned char)(dst[at] | (tf <= 3u ? tf - 1u : 3u));
+                                if (tf >= 4u) {
+                                    int order = 0;                   // its place among the trailer's entries: by bucket
+                                    for (int r = 0; r < ndup; ++r) {
+                                        const unsigned e2 = app[r * 32 + lane];
+                                        order += (e2 >> 9) >= 4u && (e2 & 0x1ffu) < bkt;
+                                    }
+                                    dst[nbytes - 1 - order] = (unsigned char)(tf - 4u);
+                                }
                             }
                     }
                     if (staged) {
                         __syncwarp();
-                        for (int i = lane * 8; i < alloc; i += 256)
+                        for (int i = lane * 16; i < alloc; i += 512)
                             *reinterpret_cast<uint4*>(pk.arena + off + i) = *reinterpret_cast<const uint4*>(stage + i);
                     }
                 }

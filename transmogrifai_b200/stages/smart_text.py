@@ -800,7 +800,7 @@ class SmartTextVectorizerModel(OpModel):
                        cells["cursor"].data_ptr(), pflag.data_ptr(), R.stream())
                 cells["pending"].append((st["pack_token"], meta, pflag, n, k))
                 # every 8 chunks: has the arena run full?  (one small read; chunks after that are not packed)
-                if len(cells["pending"]) % 8 == 0 and int(cells["cursor"].item()) * 2 >= cells["arena"].numel():
+                if len(cells["pending"]) % 8 == 0 and int(cells["cursor"].item()) >= cells["arena"].numel():
                     cells["full"] = True
             elif not fused_rows:
                 L.call("tmog_text_hash_stats_dev", desc.data_ptr(), k, n, d_prefix.data_ptr(), d_plen.data_ptr(),
