@@ -71,13 +71,13 @@ struct TcScratch {
 // ---- packed cells: what the fit pass found in every cell (its buckets and their term frequencies), kept in HBM so that
 //      the transform of the same rows needs neither the text nor a second tokenise + hash pass (text_packed.cuh reads
 //      them).  A group = 32 consecutive rows of one column = one span of text_span_kernel (text_span.cuh):
-//        arena   bytes.  A cell is a stream of entries in ascending bucket order: one byte (gap << 2 | tf code) where
-//                gap = buckets skipped since the entry before (0 .. 62) and tf code 0 .. 2 = term frequency 1 .. 3, code 3
-//                = the term frequency (- 4) is the next byte of the cell's trailer, which is read backwards from the
-//                cell's last byte; gap 63 (byte >= 0xFC) = the bucket follows as two bytes.  ~1.1 bytes per distinct
-//                token.  The cells of a group follow one another; a group starts at a multiple of 16.  A cell the fast
-//                path set aside holds eight bytes instead: the arena offset of its slot (TS_SLOT_ENTRIES u16: the term
-//                frequency of every bucket, the summed token length, the no-token flag), written by the slow kernel.
+//        arena   bytes.  A cell is a stream of bytes in ascending bucket order: (gap << 2 | tf code) with gap = buckets
+//                skipped since the entry before (0 .. 62) and tf code 0 .. 2 = term frequency 1 .. 3, code 3 = the term
+//                frequency (- 4) is the next byte of the cell's trailer, which is read backwards from the cell's last
+//                byte; gap 63 (byte >= 0xFC) is no entry: it skips 63 buckets.  ~1.1 bytes per distinct token.  The
+//                cells of a group follow one another; a group starts at a multiple of 16.  A cell the fast path set
+//                aside holds eight bytes instead: the arena offset of its slot (TS_SLOT_ENTRIES u16: the term frequency
+//                of every bucket, the summed token length, the no-token flag), written by the slow kernel.
 //        grp     [ceil(n / 32)][ncols]: arena offset of the group's bytes (~0: the arena was full), their number
 //        rel     [n][ncols] u16: where the cell's bytes begin inside the group | no token survived << 14 | slot << 15
 //        lens    [n][ncols] u32 summed token lengths (only when the vector has text-length columns)

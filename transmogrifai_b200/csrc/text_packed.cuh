@@ -62,34 +62,21 @@ __device__ __forceinline__ int tp_for_entries(const TsPack& pk, const TpCell& c,
     if (!c.slot) {
         const unsigned char* __restrict__ e = pk.arena + c.off;
         const int nbytes = c.cnt;
-        int prev = -1, tused = 0, state = 0;
-        unsigned lo = 0u, code = 0u;
+        int prev = -1, tused = 0;
         for (int k0 = 0; k0 < nbytes; k0 += 16) {
             unsigned v[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = k0 + i < nbytes ? (unsigned)e[k0 + i] : 0u;
+            for (int i = 0; i < 16; ++i) v[i] = k0 + i < nbytes ? (unsigned)e[k0 + i] : 0xFCu;
 #pragma unroll
             for (int i = 0; i < 16; ++i) {
-                if (k0 + i < nbytes - tused) {               // the trailer shrinks the stream from behind
-                    const unsigned b = v[i];
-                    int bucket = -1;
-                    if (state == 0) {
-                        code = b & 3u;
-                        if (b >= 0xFCu) state = 1;
-                        else bucket = prev + 1 + (int)(b >> 2);
-                    } else if (state == 1) {
-                        lo = b;
-                        state = 2;
-                    } else {
-                        bucket = (int)(lo | ((b & 1u) << 8));
-                        state = 0;
-                    }
-                    if (bucket >= 0) {
-                        int tf = (int)code + 1;
-                        if (code == 3u) tf = (int)e[nbytes - 1 - tused++] + 4;
-                        f(k++, bucket, tf);
-                        prev = bucket;
-                    }
+                const unsigned b = v[i], g = b >> 2;
+                // a byte past the stream (the trailer shrinks it from behind) is no entry; gap 63 skips 63 buckets
+                const bool entry = g != 63u && k0 + i < nbytes - tused;
+                prev += g == 63u ? 63 : (int)g + 1;
+                if (entry) {
+                    int tf = (int)(b & 3u) + 1;
+                    if (tf == 4) tf = (int)e[nbytes - 1 - tused++] + 4;
+                    f(k++, prev, tf);
                 }
             }
         }

@@ -519,7 +519,7 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 // ---- the cells of this span in packed form (TsPack).  The ring and the queue are free now: the ring
                 //      holds, per bitmap word of a cell, the bytes of the cell's stream before it; the queue stages the
                 //      group's bytes
-                unsigned* before = ring;              // [TC_FW][32]: bytes before word w | its first bucket is far << 31
+                unsigned* before = ring;              // [TC_FW][32]: bytes before word w's first entry byte
                 int nbytes = 0, cnt = 0, n4 = 0;
                 const bool plain = in_rows && hashed && !deferred;
                 if (plain) {
@@ -527,11 +527,11 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
 #pragma unroll
                     for (int w = 0; w < TC_FW; ++w) {
                         const unsigned x = mybm[w];
-                        const bool far = x != 0u && zrun + __ffs(x) - 1 > 62;
-                        before[w * 32 + lane] = (unsigned)nbytes | (far ? 0x80000000u : 0u);
                         if (x) {
+                            nbytes += (zrun + __ffs(x) - 1) / 63;     // "skip 63" bytes before the word's first entry
+                            before[w * 32 + lane] = (unsigned)nbytes;
                             cnt += __popc(x);
-                            nbytes += __popc(x) + (far ? 2 : 0);
+                            nbytes += __popc(x);
                             zrun = __clz(x);
                         } else {
                             zrun += 32;
@@ -584,25 +584,19 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                         unsigned x = mybm[0];
                         for (int i = 0; i < cnt; ++i) {
                             while (!x) x = mybm[++w];
-                            const int bucket = w * 32 + __ffs(x) - 1, gap = bucket - prev - 1;
+                            const int bucket = w * 32 + __ffs(x) - 1;
+                            int gap = bucket - prev - 1;
                             x &= x - 1u;
                             prev = bucket;
-                            if (gap <= 62) {
-                                dst[k++] = (unsigned char)(gap << 2);
-                            } else {
-                                dst[k] = 0xFC;
-                                dst[k + 1] = (unsigned char)(bucket & 0xff);
-                                dst[k + 2] = (unsigned char)(bucket >> 8);
-                                k += 3;
-                            }
+                            for (; gap > 62; gap -= 63) dst[k++] = 0xFC;          // skip 63 buckets
+                            dst[k++] = (unsigned char)(gap << 2);
                         }
-                        // term frequencies above 1: the code goes into the entry's first byte, 4 and more to the trailer
+                        // term frequencies above 1: the code goes into the entry's byte, 4 and more to the trailer
                         if (!p.binary_freq)
                             for (int q = 0; q < ndup; ++q) {
                                 const unsigned e = app[q * 32 + lane], bkt = e & 0x1ffu, tf = e >> 9;
-                                const unsigned bw = before[(bkt >> 5) * 32 + lane];
                                 const unsigned below = mybm[bkt >> 5] & ((1u << (bkt & 31u)) - 1u);
-                                const int at = (int)(bw & 0x7fffffffu) + __popc(below) + ((bw >> 31) && below ? 2 : 0);
+                                const int at = (int)before[(bkt >> 5) * 32 + lane] + __popc(below);
                                 dst[at] = (unsigned char)(dst[at] | (tf <= 3u ? tf - 1u : 3u));
                                 if (tf >= 4u) {
                                     int order = 0;                   // its place among the trailer's entries: by bucket
