@@ -521,6 +521,7 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 //      group's bytes
                 unsigned* before = ring;              // [TC_FW][32]: bytes before word w's first entry byte
                 int nbytes = 0, cnt = 0, n4 = 0;
+                unsigned words = 0u;                  // the bitmap words that hold a bucket
                 const bool plain = in_rows && hashed && !deferred;
                 if (plain) {
                     int zrun = 0;                     // buckets skipped since the last one met
@@ -528,6 +529,7 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                     for (int w = 0; w < TC_FW; ++w) {
                         const unsigned x = mybm[w];
                         if (x) {
+                            words |= 1u << w;
                             nbytes += (zrun + __ffs(x) - 1) / 63;     // "skip 63" bytes before the word's first entry
                             before[w * 32 + lane] = (unsigned)nbytes;
                             cnt += __popc(x);
@@ -581,15 +583,29 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                         // one loop over the cell's buckets (not one per bitmap word: the lanes would wait for the
                         // fullest word of the 32 cells sixteen times)
                         int w = 0, prev = -1, k = 0;
-                        unsigned x = mybm[0];
+                        unsigned x = 0u;
                         for (int i = 0; i < cnt; ++i) {
-                            while (!x) x = mybm[++w];
+                            if (!x) {                                // on to the next word that holds a bucket
+                                w = __ffs(words) - 1;
+                                words &= words - 1u;
+                                x = mybm[w];
+                            }
                             const int bucket = w * 32 + __ffs(x) - 1;
                             int gap = bucket - prev - 1;
                             x &= x - 1u;
                             prev = bucket;
-                            for (; gap > 62; gap -= 63) dst[k++] = 0xFC;          // skip 63 buckets
-                            dst[k++] = (unsigned char)(gap << 2);
+                            // one in twenty buckets is far (more than 62 skipped): a "skip 63" byte first -- written
+                            // without a branch, the lanes would take it in most rounds otherwise
+                            const bool far = gap > 62;
+                            gap -= far ? 63 : 0;
+                            if (gap > 62) {                          // further than 125: rare
+                                dst[k++] = 0xFC;
+                                for (; gap > 125; gap -= 63) dst[k++] = 0xFC;
+                                gap -= 63;
+                            }
+                            dst[k] = far ? (unsigned char)0xFC : (unsigned char)(gap << 2);
+                            if (far) dst[k + 1] = (unsigned char)(gap << 2);
+                            k += far ? 2 : 1;
                         }
                         // term frequencies above 1: the code goes into the entry's byte, 4 and more to the trailer
                         if (!p.binary_freq)
