@@ -347,7 +347,7 @@ text_cells_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, con
                 const int j = (int)((int64_t)it / items_per_col);
                 Murmur pm;
                 pm.init();
-                const int plen = p.prepend ? prefix_len[j] : 0;
+                const int plen = (p.prepend && j < p.n_hashed) ? prefix_len[j] : 0;   // ignored columns have no prefix
                 for (int q = 0; q < plen; ++q) pm.push(prefix[j * TH_PREFIX + q]);
                 item_info[2] = pm.h;
                 item_info[3] = pm.word;
@@ -695,7 +695,7 @@ text_cells_slow_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n
             bool na = false, ovf = false;
             const bool hashed = j < p.n_hashed;
             const bool nohit = tc_scalar_cell(tc.data + a, b - a, p, prefix + j * TH_PREFIX,
-                                              p.prepend ? prefix_len[j] : 0, hashed, counts, len_sum, na, ovf);
+                                              (p.prepend && hashed) ? prefix_len[j] : 0, hashed, counts, len_sum, na, ovf);
             if (na) flags[0] = 1;
             if (ovf) flags[2] = 1;
             if (pk.arena != nullptr) {
@@ -819,7 +819,8 @@ text_rows_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                     const TextColumn tc = cols[j];
                     const int64_t a = tc.offsets[row], b = tc.offsets[row + 1];
                     bool na = false, ovf = false;
-                    nohit = tc_scalar_cell(tc.data + a, b - a, p, prefix + j * TH_PREFIX, p.prepend ? prefix_len[j] : 0,
+                    nohit = tc_scalar_cell(tc.data + a, b - a, p, prefix + j * TH_PREFIX,
+                                           (p.prepend && j < p.n_hashed) ? prefix_len[j] : 0,
                                            j < p.n_hashed, counts, len_sum, na, ovf) ? 1u : 0u;
                     if (na) flags[0] = 1;
                     if (ovf) flags[2] = 1;

@@ -185,7 +185,7 @@ text_span_kernel(const TextColumn* __restrict__ cols, int ncols, int64_t n, cons
                 const int j = (int)((int64_t)it % ncols);
                 Murmur pm;
                 pm.init();
-                const int plen = p.prepend ? prefix_len[j] : 0;
+                const int plen = (p.prepend && j < p.n_hashed) ? prefix_len[j] : 0;   // ignored columns have no prefix
                 for (int q = 0; q < plen; ++q) pm.push(prefix[j * TH_PREFIX + q]);
                 item_info[2] = pm.h;
                 item_info[3] = pm.word;

@@ -702,8 +702,9 @@ class SmartTextVectorizerModel(OpModel):
         key = torch.cuda.current_device()
         hit = self.__dict__.get("_ha_cache")
         if hit is None or hit[0] != key:
-            prefix = np.zeros((max(k, 1), 16), dtype=np.uint8)
-            plen = np.zeros(max(k, 1), dtype=np.int32)
+            rows = max(len(lay.text_idx), k, 1)        # one row per column of the call; the ignored ones stay empty
+            prefix = np.zeros((rows, 16), dtype=np.uint8)
+            plen = np.zeros(rows, dtype=np.int32)
             for t in range(k):
                 s = f"{murmur3_index(lay.prefix_names[t], lay.num_features)}_".encode("ascii")
                 prefix[t, :len(s)] = np.frombuffer(s, dtype=np.uint8)
