@@ -893,7 +893,8 @@ def main():
                                                         (text_bytes[i % n_host] if i < packed else 0))
                   for i in range(len(hchunks))) + in_bytes[0]
         e2e = {"value": rows_e2e * world / dt, "unit": "rows/s", "h2d_bytes_per_step": int(h2d) * world,
-               "d2h_bytes_per_step": int(hs.bytes) * world,      # every rank moves its own (equal) share "ms_per_step": dt * 1e3, "steps": 1, "rows": rows_e2e * world,
+               "d2h_bytes_per_step": int(hs.bytes) * world,      # every rank moves its own (equal) share
+               "ms_per_step": dt * 1e3, "steps": 1, "rows": rows_e2e * world,
                "distinct_host_chunks": n_host, "chunks_kept_in_hbm_between_passes": kept,
                "hbm_cache_budget_bytes": budget, "chunks_with_packed_cells": packed, "cell_cache_bytes": e_cells,
                "return_format": ("full width: f64 dense blocks, int32 term frequencies" if args.full_width_return else
@@ -940,7 +941,7 @@ def main():
                        "algorithmic_bytes_per_row": {"fit": info["fit_bytes"], "transform": info["transform_bytes"]},
                        "hbm_peak_allocated_bytes": peak_alloc,
                        "packed_cells": {"hbm_budget_bytes": int(cells_budget), "chunks_packed_per_gpu": cells_cached,
-                                        "note": "pass 1 keeps every text cell's buckets and term frequencies (~1.6 KB "
+                                        "note": "pass 1 keeps every text cell's buckets and term frequencies (~0.9 KB "
                                                 "per row) for as many chunks as the budget holds; pass 2 of those chunks "
                                                 "reads them instead of tokenising the text again; filled and released "
                                                 "inside every step"},
