@@ -308,13 +308,13 @@ def kernel_times(workload, batch, fitted, info, reps: int = 5, text_offset: int 
 # 200 columns kept): pack transform 8.125 GB read + 15.862 GB written, fit scan 8.286 GB read + 0.004 GB written
 NCU_DRAM_BYTES_PER_ROW = {"vec_transform_pack_kernel<double, true>": 2398.8, "real_fit_tma_kernel": 829.0}
 # config 5's text calls, from profiles/r02_c5_text_raw.csv (1 M rows x 30 text columns): span kernel 7.02 GB read +
-# 3.81 GB of records written, text_rows_kernel 3.91 GB read + 5.76 GB written; fit + pack 7.02 + 1.51 GB; packed rows
-# 2.98 + 5.76 GB; fit without packing 7.04 GB read (r02_span captures at 500 k rows)
+# 3.81 GB of records written, text_rows_kernel 3.91 GB read + 5.76 GB written; fit + pack 7.02 + 0.84 GB; packed rows
+# 2.00 + 5.75 GB; fit without packing 7.04 GB read (r02_span captures at 500 k rows)
 NCU_DRAM_BYTES_PER_ROW_C5 = {
     "text tokenise + hash: sparse rows of the kept columns (pass 2)": 20503.0,
-    "text statistics + packed cells (pass 1 when the cells are kept)": 8533.0,
+    "text statistics + packed cells (pass 1 when the cells are kept)": 7860.0,
     "text tokenise + hash: bucket statistics (pass 1)": 7050.0,
-    "text_rows_packed_kernel: sparse rows from packed cells (pass 2)": 8738.0,
+    "text_rows_packed_kernel: sparse rows from packed cells (pass 2)": 7744.0,
 }
 
 
