@@ -805,7 +805,7 @@ def main():
     chunks, rows_rank = rank_chunks(ring, total_rows, chunk_rows, rank, world)
     sink = CountingSink()
     run_stream_step(chunks[:min(3, len(chunks))], feats, label, info, sink)     # allocator warm-up before sizing the arena
-    cells_budget = cell_cache_budget(args.cell_cache_gb, 40.0)
+    cells_budget = cell_cache_budget(args.cell_cache_gb, 36.0)
     for _ in range(warmup):
         checked, res = run_stream_step(chunks, feats, label, info, sink, cell_cache_bytes=cells_budget)
     barrier()

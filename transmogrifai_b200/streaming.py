@@ -600,6 +600,7 @@ def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: St
         if on_chunk is not None:
             on_chunk(2, k, chunk)
         _release(chunk)
+        parts = vec = batch = nb = p = _ = None   # the chunk's output is the sink's now: not kept alive under the next chunk
     if hasattr(sink, "finish"):
         sink.finish()
     from .stages.smart_text import NON_ASCII_CLEAN, _check_hash_flags
