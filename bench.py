@@ -480,15 +480,18 @@ def rank_chunks(ring, total_rows: int, chunk_rows: int, rank: int, world: int):
 
 def parity_check_stream(ring, feats, label, info, world: int):
     """Untimed self-check over the distinct chunks: the streamed fit against torch f64 reductions of the raw columns
-    (fills, null counts, class counts, PickList group totals), the sparse rows pass 2 writes against the per-column
-    sums pass 1 took (two different kernels over the same text), and the same dropped set on every rank."""
+    (fills, null counts, class counts, PickList group totals), the sparse rows pass 2 writes -- once from the packed
+    cells, once from the text -- against the per-column sums pass 1 took (different kernels over the same text), and
+    the same dropped set on every rank."""
     import torch
     from transmogrifai_b200.columnar import DictBlock, NumericBlock
     from transmogrifai_b200.streaming import fit_stream, transform_stream
     from transmogrifai_b200 import runtime as R
     R.clear_caches()
     checked = build_plan(feats, label, info)
-    fit = fit_stream(ring, checked)
+    # pass 1 also packs the text cells (as the timed step does): pass 2 is then checked twice, from the packed cells and
+    # from the text
+    fit = fit_stream(ring, checked, cell_cache_bytes=int(sum(b.n for b in ring) * 1400) + (64 << 20))
     est = checked.origin_stage
     sm = est.summary
     names = sm.meta.columnNames()
@@ -565,12 +568,34 @@ def parity_check_stream(ring, feats, label, info, world: int):
                 sums[off:off + p_.width] += p_.data.sum(dim=0)
             off += p_.width
 
-    transform_stream(ring, checked, fit, sink)
-    got = allsum(sums).cpu().numpy()
+    row_nnz = []
+    inner = sink
+
+    def sink_nnz(k, vec, parts):
+        row_nnz.append([p_.row_nnz.clone() for p_ in parts if hasattr(p_, "row_nnz")])
+        inner(k, vec, parts)
+
     exp = sm.mean[:-1][keep] * n_all
-    if not np.allclose(got, exp, rtol=1e-9, atol=1e-6):
-        bad = np.nonzero(~np.isclose(got, exp, rtol=1e-9, atol=1e-6))[0]
-        problems.append(f"pass-2 column sums differ from the pass-1 statistics in {len(bad)} columns (first {bad[:3]})")
+    packed_models = [m for m in fit.fitted if getattr(m, "_cells", None)]
+    n_packed = sum(len(m._cells["chunks"]) for m in packed_models)
+    for how in ("packed cells", "text"):
+        if how == "text":
+            if not packed_models:
+                break
+            for m in packed_models:
+                m.release_cell_cache()
+        elif n_packed != len(ring) * len(packed_models):
+            problems.append(f"only {n_packed} chunks were packed")
+        sums.zero_()
+        first_nnz, row_nnz = row_nnz, []
+        transform_stream(ring, checked, fit, sink_nnz)
+        got = allsum(sums.clone()).cpu().numpy()
+        if not np.allclose(got, exp, rtol=1e-9, atol=1e-6):
+            bad = np.nonzero(~np.isclose(got, exp, rtol=1e-9, atol=1e-6))[0]
+            problems.append(f"pass-2 column sums (from the {how}) differ from the pass-1 statistics in {len(bad)} "
+                            f"columns (first {bad[:3]})")
+        if how == "text" and not all(torch.equal(a, b) for x, y in zip(first_nnz, row_nnz) for a, b in zip(x, y)):
+            problems.append("rows from the packed cells and rows from the text differ in their lengths")
     if world > 1:
         import torch.distributed as dist
         box = [None] * world
