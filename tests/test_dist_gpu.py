@@ -187,8 +187,10 @@ def _worker_streamed(rank, size, port, q, backend="gloo"):
         checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
                                     sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
         out = []
+        # rank 0 keeps the packed text cells of its chunks for pass 2, rank 1 transforms from the text: same rows
         res = fit_and_transform_stream(chunks, checked, lambda k, vec, parts: out.append(
-            VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy()))
+            VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy()), cell_cache_bytes=(16 << 20) if rank == 0 else 0)
+        assert res.cells_cached == (len(chunks) if rank == 0 else 0)
         est = checked.origin_stage
         col = lambda k: data[k][1]   # noqa: E731
         xb = V.binary_vectorizer_transform([col("b0")])
