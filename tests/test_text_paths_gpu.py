@@ -166,8 +166,10 @@ def test_fuzz_span_kernel_against_row_table_kernel_and_oracle(heavy_punct, num_f
     assert abs(out["span"][1][:take] - sp.csr_matrix(exp)).max() == 0
 
 
-def test_packed_cells_with_more_than_32_text_columns():
-    """The packed row kernel walks the cells of a row 32 at a time: 40 hashed columns, against the rows from the text."""
+@pytest.mark.parametrize("binary_freq", [False, True])
+def test_packed_cells_with_more_than_32_text_columns(binary_freq):
+    """The packed row kernel walks the cells of a row 32 at a time: 40 hashed columns, against the rows from the text
+    (term frequencies, and binaryFreq = true)."""
     from transmogrifai_b200 import features as F
     from transmogrifai_b200.columnar import ColumnarBatch, VectorColumn
     from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
@@ -185,7 +187,8 @@ def test_packed_cells_with_more_than_32_text_columns():
     def run(cell_bytes):
         feats = [F.FeatureBuilder.Text(f"c{j:02d}").asPredictor() for j in range(k)]
         label = F.FeatureBuilder.RealNN("y").asResponse()
-        vec = SmartTextVectorizer().setMaxCardinality(0).setNumFeatures(64).setInput(*feats).getOutput()
+        vec = SmartTextVectorizer().setMaxCardinality(0).setNumFeatures(64).setBinaryFreq(binary_freq) \
+            .setInput(*feats).getOutput()
         checked = label.sanityCheck(vec, removeBadFeatures=True, sampleLowerLimit=0, sampleUpperLimit=10 ** 9,
                                     featureFeatureCorrLevel="Off", minVariance=2e-3)
         out = []
@@ -196,4 +199,46 @@ def test_packed_cells_with_more_than_32_text_columns():
     ref, _r0 = run(0)
     got, r1 = run(8 << 20)
     assert r1.cells_cached == 2 and got.shape == ref.shape and got.shape[1] < k * 64 + k
+    assert abs(got - ref).max() == 0 and np.array_equal(got.indices, ref.indices)
+
+
+def test_packed_cells_group_too_large_for_its_offsets_falls_back_to_the_text():
+    """32 consecutive cells that hold (nearly) every one of 512 buckets need more bytes than a cell's 14-bit offset inside
+    its group can address: the chunk is then not packed and its transform comes from the text -- same rows."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch, VectorColumn
+    from transmogrifai_b200.stages.smart_text import SmartTextVectorizer
+    from transmogrifai_b200.streaming import fit_and_transform_stream
+    import scipy.sparse as sp
+    from transmogrifai_b200.stages.smart_text import murmur3_index
+    rng = np.random.default_rng(8)
+    n = 96
+    # one token per bucket: a cell with all 512 buckets and no repeat stays on the fast path and takes 512 bytes
+    prefix = f"{murmur3_index('big', 512)}_"
+    by_bucket = {}
+    i = 0
+    while len(by_bucket) < 512:
+        by_bucket.setdefault(murmur3_index(prefix + f"w{i}", 512), f"w{i}")
+        i += 1
+    words = list(by_bucket.values())
+    big = [" ".join(words[k] for k in rng.permutation(512)) for _ in range(n)]
+    small = ["a few words here" for _ in range(n)]
+    y = (rng.random(n) < 0.5).astype(np.float64).tolist()
+    chunks = [ColumnarBatch.from_columns({"big": (F.TEXT, big), "small": (F.TEXT, small), "y": (F.REALNN, y)}, response="y"),
+              ColumnarBatch.from_columns({"big": (F.TEXT, small), "small": (F.TEXT, small), "y": (F.REALNN, y)}, response="y")]
+
+    def run(cell_bytes):
+        feats = [F.FeatureBuilder.Text("big").asPredictor(), F.FeatureBuilder.Text("small").asPredictor()]
+        label = F.FeatureBuilder.RealNN("y").asResponse()
+        vec = SmartTextVectorizer().setMaxCardinality(0).setNumFeatures(512).setInput(*feats).getOutput()
+        checked = label.sanityCheck(vec, removeBadFeatures=False, sampleLowerLimit=0, sampleUpperLimit=10 ** 9,
+                                    featureFeatureCorrLevel="Off")
+        out = []
+        res = fit_and_transform_stream(chunks, checked, lambda i, v, parts: out.append(
+            VectorColumn(v.name, v.n, v.metadata, parts).to_scipy()), cell_cache_bytes=cell_bytes)
+        return sp.vstack(out).tocsr(), res
+
+    ref, _r0 = run(0)
+    got, r1 = run(16 << 20)
+    assert r1.cells_cached == 1                       # the second chunk's cells are small
     assert abs(got - ref).max() == 0 and np.array_equal(got.indices, ref.indices)
