@@ -1612,7 +1612,9 @@ static int tc_run(const ThArgs& a) {
     TMOG_LAUNCH_CHECK();
     if (STATS) {
         const int64_t words = ((int64_t)a.n * a.ncols + 31) / 32;
-        const int sgrid = (int)std::max<int64_t>(1, std::min<int64_t>((words + 127) / 128, (int64_t)sm_count() * 8));
+        // a thread per 32 cells: the few cells that were set aside are spread over as many threads as possible (a thread
+        // tokenises its cells one after the other)
+        const int sgrid = (int)std::max<int64_t>(1, std::min<int64_t>((words + 127) / 128, (int64_t)1 << 20));
         text_cells_slow_kernel<<<sgrid, 128, 0, a.stream>>>(a.cols, a.ncols, a.n, a.prefix, a.prefix_len, p, a.class_ids,
                                                             defer_bits, a.class_sum, a.dup, a.sq_extra, a.aux, a.label,
                                                             a.label_shift, a.wsum, a.flags, a.pack);
