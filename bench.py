@@ -121,12 +121,10 @@ def build_plan(feats, label, info, reference_defaults: bool = False):
 
 def run_step(batch, checked):
     """One step over one resident batch: fit every stage (fused vectorizer + SanityChecker scans, label classes,
-    decision) and materialise the kept columns of the output vector.  Nothing is reused from a previous step: the
-    per-batch caches and the library's content-keyed metadata caches are dropped (the stage objects keep only
-    data-independent metadata of their own inputs)."""
-    from transmogrifai_b200 import runtime as R
+    decision) and materialise the kept columns of the output vector.  The per-batch caches are dropped; the library's
+    content-keyed, data-independent metadata caches survive steps (METADATA_NOTE, config.metadata_caches), as they do
+    in the chunk-streamed step."""
     from transmogrifai_b200.dsl import fit_and_transform
-    R.clear_caches()
     for k in ("_label_cache", "_label_dev", "_dict_cache", "_dev_cache"):
         batch.__dict__.pop(k, None)
     out, fitted = fit_and_transform(batch, checked)
