@@ -380,7 +380,7 @@ int tmog_text_hash_fit_transform_dev(const int64_t* col_desc, int ncols, int64_t
  * fit-then-transform runs after all chunks have been fitted (FitStagesUtil.scala:212-290; the reference tokenises and
  * hashes the rows again, SmartTextVectorizer.scala:333-356), reads ~0.9 KB per row instead of the text and tokenises
  * nothing.  Separate hash spaces of at most 512 buckets per column only (tmog_text_hash_scratch_bytes2's layout).
- *   arena: device memory shared by all chunks, arena_cursor (device u64, zeroed once) counts the u16 entries handed
+ *   arena: device memory shared by all chunks, arena_cursor (device u64, zeroed once) counts the bytes handed
  *          out; pack_meta: per chunk, tmog_text_cells_pack_bytes bytes (track_len = the vector has text-length
  *          columns, params[9] > 0); pack_flags[0] is set when the arena was too small for this chunk -- its packed
  *          cells are then unusable and the chunk is transformed from its text (tmog_text_hash_transform_dev).
