@@ -138,16 +138,20 @@ text_rows_packed_kernel(int ncols, int64_t n, TcParams p, TsPack pk, const int32
                 // a column none of whose buckets was dropped maps bucket b to (its first output column) + b
                 const int lo = np[0], hi = np[F - 1];
                 const bool whole = lo >= 0 && hi - lo == F - 1;
+                // (a cell that does not fit the stage means a row that does not: the stage is not used then)
+                const bool cell_fits = so + c.cnt <= TP_STAGE;
+                int* si = sidx + so;
+                unsigned char* sv = sval + so;
                 const int used = tp_for_entries(pk, c, [&](int k, int bucket, int tf) {
                     const int v = whole ? lo + bucket : np[bucket];
                     kept += v >= 0;
-                    if (so + k < TP_STAGE) {
-                        sidx[so + k] = v;
-                        sval[so + k] = (unsigned char)(p.binary_freq ? 1 : min(tf, 255));
+                    if (cell_fits) {
+                        si[k] = v;
+                        sv[k] = (unsigned char)(p.binary_freq ? 1 : min(tf, 255));
                     }
                 });
-                for (int k = used; k < c.cnt; ++k)               // a cell has fewer entries than bytes: the rest is empty
-                    if (so + k < TP_STAGE) sidx[so + k] = -1;
+                if (cell_fits)
+                    for (int k = used; k < c.cnt; ++k) si[k] = -1;   // fewer entries than bytes: the rest is empty
             }
             const bool has_len = j < ncols && want_len && c.len_sum > 0u && newpos[p.len_base + j] >= 0;
             const bool has_null = j < ncols && p.track_nulls && c.nohit && newpos[p.null_base + j] >= 0;
