@@ -932,7 +932,8 @@ def main():
                "hbm_cache_budget_bytes": budget, "chunks_with_packed_cells": packed, "cell_cache_bytes": e_cells,
                "return_format": ("full width: f64 dense blocks, int32 term frequencies" if args.full_width_return else
                                  "compact (streaming.compact_parts): null indicators and Binary values as u8, term "
-                                 "frequencies as u8 with an overflow list; indices, offsets and Real values unchanged"),
+                                 "frequencies as u8 with an overflow list, column indices of the text rows as u16; "
+                                 "row offsets, one-hot indices and Real values unchanged"),
                "api": "fit_and_transform_stream(pinned host chunks, label.sanityCheck(transmogrify(features)), HostSink)"}
         del hring, hchunks, hs
         torch.cuda.empty_cache()

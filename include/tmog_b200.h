@@ -630,11 +630,17 @@ int tmog_vector_export_write_dev(const void* parts, int nparts, int64_t n, int s
  *     Binary features (BinaryVectorizer.scala).  flags[0] is set if such a column holds anything else.
  *   tmog_values_narrow_dev: the int32 term frequencies of sparse rows (tmog_text_hash_transform_dev's out_val) as u8; a
  *     value above 254 is written as 255 and listed in over_pos / over_val (over_count counts them, also beyond
- *     over_cap). */
+ *     over_cap).
+ *   tmog_indices_narrow_dev: the int32 column indices of sparse rows whose block has at most 65 536 columns as u16;
+ *     flags[1] is set if an index does not fit.
+ *   used (device u64, or NULL): the number of entries actually written (the *cursor of the transform call); entries
+ *     behind it are not looked at. */
 int tmog_dense_split_dev(const double* data, int64_t ld, int64_t n, int ncols, const int32_t* dest, double* values,
                          int64_t ldv, uint8_t* units, int64_t ldu, int32_t* flags, void* stream);
-int tmog_values_narrow_dev(const int32_t* values, int64_t n, uint8_t* out, int64_t* over_pos, int32_t* over_val,
-                           int over_cap, uint32_t* over_count, void* stream);
+int tmog_indices_narrow_dev(const int32_t* indices, int64_t n, const uint64_t* used, uint16_t* out, int32_t* flags,
+                            void* stream);
+int tmog_values_narrow_dev(const int32_t* values, int64_t n, const uint64_t* used, uint8_t* out, int64_t* over_pos,
+                           int32_t* over_val, int over_cap, uint32_t* over_count, void* stream);
 
 /* ---- string paths over host buffers ------------------------------------------------------------------------------
  * One call per exported partition does what the reference's estimator does in fit(Dataset) and its model in

@@ -82,7 +82,8 @@ _SIGNATURES: Dict[str, List] = {
                                       _u64, _p, _p, _p],
     "tmog_text_hash_transform_packed_dev": [_int, _i64, _p, _p, _p, _u64, _p, _p, _p, _p, _p, _p, _i64, _p, _p],
     "tmog_dense_split_dev": [_p, _i64, _i64, _int, _p, _p, _i64, _p, _i64, _p, _p],
-    "tmog_values_narrow_dev": [_p, _i64, _p, _p, _p, _int, _p, _p],
+    "tmog_indices_narrow_dev": [_p, _i64, _p, _p, _p, _p],
+    "tmog_values_narrow_dev": [_p, _i64, _p, _p, _p, _p, _int, _p, _p],
     "tmog_sparse_rows_select_dev": [_p, _p, _p, _p, _i64, _p, _p, _p, _p, _p, _p],
     "tmog_label_classes_scratch_bytes": [C.POINTER(_sz)],
     "tmog_label_classes_dev": [_p, _i64, _int, _p, _p, _p, _p, _p, _sz, _p],

@@ -538,6 +538,7 @@ class SparseRowsPart:
     indices: torch.Tensor                # [nnz] int32
     values: torch.Tensor                 # [nnz] int32 (term frequencies)
     width: int
+    used: Optional[torch.Tensor] = None  # device int64 [1]: entries written (indices / values may be longer), or None
 
     def to_scipy(self):
         import scipy.sparse as sp

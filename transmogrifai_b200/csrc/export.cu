@@ -146,10 +146,39 @@ dense_split_kernel(const double* __restrict__ data, int64_t ld, int64_t n, int n
     if (bad) flags[0] = 1;
 }
 
+// int32 column indices of a block of at most 65 536 columns -> u16 (eight per thread and step)
+__global__ void __launch_bounds__(256)
+indices_narrow_kernel(const int32_t* __restrict__ idx, int64_t n, const unsigned long long* __restrict__ used,
+                      unsigned short* __restrict__ out, int32_t* __restrict__ flags) {
+    if (used) n = min(n, (int64_t)*used);          // entries behind the last one written are not looked at
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 8;
+    bool bad = false;
+    for (int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8; i0 < n; i0 += stride) {
+        if (i0 + 8 <= n) {
+            const int4 a = *reinterpret_cast<const int4*>(idx + i0), b = *reinterpret_cast<const int4*>(idx + i0 + 4);
+            bad |= ((unsigned)(a.x | a.y | a.z | a.w | b.x | b.y | b.z | b.w) >> 16) != 0u;
+            uint4 o;
+            o.x = (unsigned)(a.x & 0xffff) | ((unsigned)a.y << 16);
+            o.y = (unsigned)(a.z & 0xffff) | ((unsigned)a.w << 16);
+            o.z = (unsigned)(b.x & 0xffff) | ((unsigned)b.y << 16);
+            o.w = (unsigned)(b.z & 0xffff) | ((unsigned)b.w << 16);
+            *reinterpret_cast<uint4*>(out + i0) = o;
+        } else {
+            for (int64_t i = i0; i < n; ++i) {
+                bad |= ((unsigned)idx[i] >> 16) != 0u;
+                out[i] = (unsigned short)idx[i];
+            }
+        }
+    }
+    if (bad) flags[1] = 1;
+}
+
 // int32 values -> u8; a value above 254 becomes 255 and goes to the overflow list (position, value) as well
 __global__ void __launch_bounds__(256)
-values_narrow_kernel(const int32_t* __restrict__ values, int64_t n, uint8_t* __restrict__ out, int64_t* __restrict__ over_pos,
-                     int32_t* __restrict__ over_val, int over_cap, unsigned* __restrict__ over_count) {
+values_narrow_kernel(const int32_t* __restrict__ values, int64_t n, const unsigned long long* __restrict__ used,
+                     uint8_t* __restrict__ out, int64_t* __restrict__ over_pos, int32_t* __restrict__ over_val, int over_cap,
+                     unsigned* __restrict__ over_count) {
+    if (used) n = min(n, (int64_t)*used);
     const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
     for (int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i0 < n; i0 += stride) {
         if (i0 + 4 <= n) {
@@ -228,15 +257,30 @@ extern "C" int tmog_dense_split_dev(const double* data, int64_t ld, int64_t n, i
     return TMOG_OK;
 }
 
-extern "C" int tmog_values_narrow_dev(const int32_t* values, int64_t n, uint8_t* out, int64_t* over_pos, int32_t* over_val,
-                                      int over_cap, uint32_t* over_count, void* stream) {
+extern "C" int tmog_indices_narrow_dev(const int32_t* indices, int64_t n, const uint64_t* used, uint16_t* out, int32_t* flags,
+                                       void* stream) {
+    TMOG_REQUIRE(n >= 0, "bad shape");
+    if (n == 0) return TMOG_OK;
+    TMOG_REQUIRE(indices && out && flags, "NULL argument");
+    TMOG_REQUIRE((reinterpret_cast<uintptr_t>(indices) & 15u) == 0 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0,
+                 "indices and out must be 16-byte aligned");
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n / 8 + 255) / 256, (int64_t)sm_count() * 16));
+    indices_narrow_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(indices, n, reinterpret_cast<const unsigned long long*>(used), out,
+                                                                 flags);
+    TMOG_LAUNCH_CHECK();
+    return TMOG_OK;
+}
+
+extern "C" int tmog_values_narrow_dev(const int32_t* values, int64_t n, const uint64_t* used, uint8_t* out, int64_t* over_pos,
+                                      int32_t* over_val, int over_cap, uint32_t* over_count, void* stream) {
     TMOG_REQUIRE(n >= 0 && over_cap >= 0, "bad shape");
     if (n == 0) return TMOG_OK;
     TMOG_REQUIRE(values && out && over_count && (over_cap == 0 || (over_pos && over_val)), "NULL argument");
     TMOG_REQUIRE((reinterpret_cast<uintptr_t>(values) & 15u) == 0 && (reinterpret_cast<uintptr_t>(out) & 3u) == 0,
                  "values must be 16-byte aligned, out 4-byte aligned");
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n / 4 + 255) / 256, (int64_t)sm_count() * 16));
-    values_narrow_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(values, n, out, over_pos, over_val, over_cap, over_count);
+    values_narrow_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(values, n, reinterpret_cast<const unsigned long long*>(used), out,
+                                                                over_pos, over_val, over_cap, over_count);
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
 }

@@ -1124,7 +1124,7 @@ class SmartTextVectorizerModel(OpModel):
                scratch.numel(), R.stream())
         if own_flags:
             _check_hash_flags(flags)
-        return SparseRowsPart(row_start, row_nnz, idx, val, out_width)
+        return SparseRowsPart(row_start, row_nnz, idx, val, out_width, cursor)
 
 
     def _rows_from_cells(self, cells, packed, n: int, d_newpos, out_width: int, stream) -> SparseRowsPart:
@@ -1155,7 +1155,7 @@ class SmartTextVectorizerModel(OpModel):
         val = torch.empty(max(capacity, 1), dtype=torch.int32, device="cuda")
         L.call("tmog_text_hash_transform_packed_dev", *args, idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), capacity,
                flags.data_ptr(), R.stream())
-        return SparseRowsPart(row_start, row_nnz, idx, val, out_width)
+        return SparseRowsPart(row_start, row_nnz, idx, val, out_width, cursor)
 
 
 def _hash_scratch(n: int, ncols: int = 0, lay: Optional[_HashLayout] = None, sparse_out: bool = True) -> torch.Tensor:

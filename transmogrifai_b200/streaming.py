@@ -345,6 +345,8 @@ class HostSink:
             self._drain(s)
         if self._flags is not None and int(self._flags[0].item()):
             raise ValueError("a null-indicator / Binary column holds a value other than 0 and 1: use compact=False")
+        if self._flags is not None and int(self._flags[1].item()):
+            raise ValueError("a column index did not fit 16 bits: use compact=False")
 
 
 def _unit_columns(vec: VectorColumn, col0: int, width: int) -> np.ndarray:
@@ -361,8 +363,9 @@ def compact_parts(vec: VectorColumn, parts, dest_cache: Optional[dict] = None, f
                          in order; _unit_columns says which they are -- the receiver applies the same rule to the
                          metadata);
       one-hot block  ->  "p.indices" int32 [n][k] as it is;
-      sparse rows    ->  "p.row_start", "p.row_nnz", "p.indices" as they are, "p.values" u8 (255 = look the entry up in
-                         "p.over_pos" / "p.over_val", "p.over_count" of them)."""
+      sparse rows    ->  "p.row_start", "p.row_nnz" as they are, "p.indices" as uint16 (stored in an int16 tensor) when the
+                         block has at most 65 536 columns, "p.values" u8 (255 = look the entry up in "p.over_pos" /
+                         "p.over_val", "p.over_count" of them)."""
     from . import _lib as L
     dest_cache = {} if dest_cache is None else dest_cache
     flags = torch.zeros(4, dtype=torch.int32, device="cuda") if flags is None else flags
@@ -391,9 +394,16 @@ def compact_parts(vec: VectorColumn, parts, dest_cache: Optional[dict] = None, f
             over_pos = torch.zeros(256, dtype=torch.int64, device="cuda")
             over_val = torch.zeros(256, dtype=torch.int32, device="cuda")
             over_count = torch.zeros(1, dtype=torch.int32, device="cuda")
-            L.call("tmog_values_narrow_dev", p.values.data_ptr(), nnz, v8.data_ptr(), over_pos.data_ptr(),
+            used = getattr(p, "used", None)
+            L.call("tmog_values_narrow_dev", p.values.data_ptr(), nnz, R.ptr(used), v8.data_ptr(), over_pos.data_ptr(),
                    over_val.data_ptr(), 256, over_count.data_ptr(), R.stream())
-            out += [(f"{i}.row_start", p.row_start), (f"{i}.row_nnz", p.row_nnz), (f"{i}.indices", p.indices),
+            indices = p.indices
+            if p.width <= 65536 and nnz:           # the block's column numbers fit 16 bits
+                i16 = torch.empty(max(nnz, 8), dtype=torch.int16, device="cuda")
+                L.call("tmog_indices_narrow_dev", p.indices.data_ptr(), nnz, R.ptr(used), i16.data_ptr(), flags.data_ptr(),
+                       R.stream())
+                indices = i16[:nnz]
+            out += [(f"{i}.row_start", p.row_start), (f"{i}.row_nnz", p.row_nnz), (f"{i}.indices", indices),
                     (f"{i}.values", v8[:nnz]), (f"{i}.over_pos", over_pos), (f"{i}.over_val", over_val),
                     (f"{i}.over_count", over_count)]
             col0 += p.width
@@ -435,7 +445,9 @@ def expand_compact(vec: VectorColumn, widths: Sequence[int], named, n: int):
             indptr = np.zeros(n + 1, dtype=np.int64)
             indptr[1:] = np.cumsum(nnz)
             take = np.repeat(f["row_start"] - indptr[:-1], nnz) + np.arange(indptr[-1])
-            mats.append(sp.csr_matrix((val[take], f["indices"][take].astype(np.int64), indptr), shape=(n, w)))
+            idx = f["indices"]
+            idx = idx.view(np.uint16) if idx.dtype == np.int16 else idx
+            mats.append(sp.csr_matrix((val[take], idx[take].astype(np.int64), indptr), shape=(n, w)))
         else:
             idx = f["indices"]
             k = idx.shape[1]
