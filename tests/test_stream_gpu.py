@@ -265,3 +265,64 @@ def test_compact_return_format_round_trip():
     exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
     assert abs(a - exp).max() < 1e-12
     assert hs.bytes == nbytes[1] and hs.bytes < 0.8 * hs0.bytes
+
+
+@pytest.mark.parametrize("with_mode", [True, False])
+def test_integral_vectorizer_over_chunks(with_mode):
+    """IntegralVectorizer fitted over row chunks (IntegralVectorizer.scala:81-113, SequenceAggregators.scala:100-131): the
+    value -> count maps of the chunks add up key-wise (mode, ties to the smaller value), the statistics merge like
+    RealVectorizer's; against the oracle and against one resident batch."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch, VectorColumn
+    from transmogrifai_b200.dsl import fit_and_transform
+    from transmogrifai_b200.stages.integral import IntegralVectorizer
+    from transmogrifai_b200.streaming import fit_and_transform_stream
+    rng = np.random.default_rng(21)
+    n = sum(SIZES)
+    y = (rng.random(n) < 0.4).astype(np.float64)
+    # i0: the mode changes from chunk to chunk and ties at the end (7 and 3 equally often -> 3); i1: all null; i2: wide
+    i0 = [None if rng.random() < 0.1 else int(v) for v in rng.choice([3, 7, 11, -5], size=n, p=[0.3, 0.3, 0.25, 0.15])]
+    c3, c7 = sum(v == 3 for v in i0), sum(v == 7 for v in i0)
+    major, todo = (3, c3 - c7) if c3 > c7 else (7, c7 - c3)          # force the tie: surplus of the larger one -> 11
+    for k in range(n):
+        if todo and i0[k] == major:
+            i0[k] = 11
+            todo -= 1
+    assert sum(v == 3 for v in i0) == sum(v == 7 for v in i0) > sum(v == 11 for v in i0)
+    i1 = [None] * n
+    i2 = [None if rng.random() < 0.3 else int(v) for v in rng.integers(-10 ** 12, 10 ** 12, size=n)]
+    cols = {"i0": (F.INTEGRAL, i0), "i1": (F.INTEGRAL, i1), "i2": (F.INTEGRAL, i2), "y": (F.REALNN, y.tolist())}
+    fills = V.integral_vectorizer_fit([i0, i1, i2], fill_with_mode=with_mode)
+    if with_mode:
+        assert fills[0] == 3 and fills[1] == 0
+    exp = sp.csr_matrix(V.integral_vectorizer_transform([i0, i1, i2], fills, True))
+
+    def plan():
+        FB = F.FeatureBuilder
+        est = IntegralVectorizer().setInput(FB.Integral("i0").asPredictor(), FB.Integral("i1").asPredictor(),
+                                            FB.Integral("i2").asPredictor())
+        if with_mode:
+            est.setFillWithMode()
+        label = FB.RealNN("y").asResponse()
+        return est, label.sanityCheck(est.getOutput(), removeBadFeatures=False, sampleLowerLimit=0,
+                                      sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
+
+    bounds = np.concatenate([[0], np.cumsum(SIZES)])
+    chunks = [ColumnarBatch.from_columns({k_: (t, v[a:b]) for k_, (t, v) in cols.items()}, response="y")
+              for a, b in zip(bounds[:-1], bounds[1:])]
+    est, checked = plan()
+    out = []
+    res = fit_and_transform_stream(chunks, checked, lambda i, vec, parts: out.append(
+        VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy()))
+    got = sp.vstack(out).tocsr()
+    model = [m for m in res.fitted if hasattr(m, "fillValues")][0]
+    assert model.fillValues == [int(f) for f in fills]
+    assert got.shape == exp.shape and abs(got - exp).max() == 0
+    est1, checked1 = plan()
+    batch = ColumnarBatch.from_columns(cols, response="y").to("cuda")
+    fit_and_transform(batch, checked1)
+    s0, s1 = checked.origin_stage.summary, checked1.origin_stage.summary
+    np.testing.assert_allclose(s0.mean, s1.mean, rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(s0.variance, s1.variance, rtol=1e-9, atol=1e-18)
+    np.testing.assert_allclose(s0.correlationsWithLabel, s1.correlationsWithLabel, rtol=1e-9, atol=1e-12, equal_nan=True)
+    assert np.array_equal(s0.min, s1.min) and np.array_equal(s0.max, s1.max)

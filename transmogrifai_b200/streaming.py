@@ -30,7 +30,7 @@ from . import _lib as L
 from . import dist as D
 from . import features as F
 from . import runtime as R
-from .columnar import ColumnarBatch, VectorColumn, WidthPart, round_up
+from .columnar import ColumnarBatch, DensePart, VectorColumn, WidthPart, round_up
 from .dsl import stages_of
 from .stages.base import OpEstimator, OpPipelineStage
 from .stages.numeric import MAX_LABEL_CLASSES
@@ -603,6 +603,7 @@ def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: St
             batch = nb
         vec = batch.vectors[result.name]
         parts = [p.materialize(None) if hasattr(p, "materialize") else p for p in vec.parts]
+        parts = [DensePart(p) if isinstance(p, torch.Tensor) else p for p in parts]     # a dense block as a part
         for p in parts:
             if hasattr(p, "data") and not hasattr(p, "materialize"):
                 _ = p.data
