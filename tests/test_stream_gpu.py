@@ -326,3 +326,56 @@ def test_integral_vectorizer_over_chunks(with_mode):
     np.testing.assert_allclose(s0.variance, s1.variance, rtol=1e-9, atol=1e-18)
     np.testing.assert_allclose(s0.correlationsWithLabel, s1.correlationsWithLabel, rtol=1e-9, atol=1e-12, equal_nan=True)
     assert np.array_equal(s0.min, s1.min) and np.array_equal(s0.max, s1.max)
+
+
+@pytest.mark.parametrize("continuous", [False, True])
+def test_set_vectorizer_over_chunks(continuous):
+    """OpSetVectorizer fitted over row chunks with a dictionary per chunk (OpOneHotVectorizer.scala:75-124, :416-437): the
+    counts of pass 0 add up per cleaned value, the statistics of the multiplicity-valued columns come from pass 1;
+    against the oracle and against one resident batch."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import ColumnarBatch, VectorColumn
+    from transmogrifai_b200.dsl import fit_and_transform
+    from transmogrifai_b200.stages.sets import OpSetVectorizer
+    from transmogrifai_b200.streaming import fit_and_transform_stream
+    rng = np.random.default_rng(33)
+    n = sum(SIZES)
+    z = rng.normal(0, 1, n)
+    y = (100.0 + 3.0 * z + rng.normal(0, 0.5, n)) if continuous else (z > 0.2).astype(np.float64)
+    opt = lambda v, p: None if rng.random() < p else v   # noqa: E731
+    base = [["a", "A "], ["b"], ["a", "c", "d"], [], ["b", "B.", "b"]]
+    s0 = [opt(list(base[int(rng.integers(5))]) + (["hi"] if zz > 0 else []) + ([f"rare{i}"] if i > 2500 and i % 7 == 0 else []),
+              0.07) for i, zz in enumerate(z)]
+    s1 = [opt([f"v{int(k)}" for k in rng.zipf(1.4, size=rng.integers(0, 4)) % 30], 0.1) for _ in range(n)]
+    cols = {"s0": (F.MULTIPICKLIST, s0), "s1": (F.MULTIPICKLIST, s1), "y": (F.REALNN, y.tolist())}
+    tops = V.pivot_fit([s0, s1], 20, 10, True)
+    xo = sp.csr_matrix(V.pivot_transform([s0, s1], tops, True, True))
+    metas = V.pivot_metadata(["s0", "s1"], "MultiPickList", tops, True)
+    p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                       feature_feature_corr_level="off")
+    ref = S.sanity_fit(y, xo, metas, p, label_name="y")
+
+    def plan():
+        FB = F.FeatureBuilder
+        est = OpSetVectorizer().setTopK(20).setMinSupport(10).setInput(FB.MultiPickList("s0").asPredictor(),
+                                                                        FB.MultiPickList("s1").asPredictor())
+        label = FB.RealNN("y").asResponse()
+        return label.sanityCheck(est.getOutput(), removeBadFeatures=True, sampleLowerLimit=0, sampleUpperLimit=10 ** 9,
+                                 featureFeatureCorrLevel="Off")
+
+    bounds = np.concatenate([[0], np.cumsum(SIZES)])
+    chunks = [ColumnarBatch.from_columns({k_: (t, v[a:b]) for k_, (t, v) in cols.items()}, response="y")
+              for a, b in zip(bounds[:-1], bounds[1:])]
+    checked = plan()
+    out = []
+    res = fit_and_transform_stream(chunks, checked, lambda i, vec, parts: out.append(
+        VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy()))
+    est = checked.origin_stage
+    model = [m for m in res.fitted if hasattr(m, "topValues")][0]
+    assert [list(t) for t in model.topValues] == [list(t) for t in tops]
+    _check(est, res.fitted[-1].indicesToKeep, sp.vstack(out).tocsr(), ref, xo, metas)
+    checked1 = plan()
+    batch = ColumnarBatch.from_columns(cols, response="y").to("cuda")
+    out1, _f = fit_and_transform(batch, checked1)
+    assert checked1.origin_stage.summary.dropped == est.summary.dropped
+    assert abs(out1.vectors[checked1.name].to_scipy() - sp.vstack(out).tocsr()).max() == 0

@@ -87,6 +87,49 @@ class OpSetVectorizer(OpTextPivotVectorizer):
         return model
 
 
+    # -- row chunks (streaming.py).  The statistics of the emitted columns need the vocabulary (a column holds how many
+    #    of a row's values clean to its top value), so the counting is the pre-pass (pass 0, all chunks) and the
+    #    statistics are the model's pass 1.  Chunks may come with their own dictionaries: the counts are kept per
+    #    cleaned value.
+    def stream_pre_begin(self):
+        return {"counts": [dict() for _ in self.inN]}
+
+    def stream_pre_update(self, st, chunk: ColumnarBatch) -> bool:
+        names = [f.name for f in self.inN]
+        block = chunk.sets(names)
+        dev = chunk.on_device("sets", names, block)
+        d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+        for c in range(len(names)):
+            gid, distinct = clean_and_group(block.dicts[c], self.cleanText)
+            ngroups = len(distinct)
+            d_gid = torch.from_numpy(np.ascontiguousarray(gid, dtype=np.int32) if len(gid) else
+                                     np.zeros(1, dtype=np.int32)).cuda()
+            d_counts = torch.zeros(1 + ngroups, dtype=torch.int32, device="cuda")
+            L.call("tmog_set_count_dev", dev.offsets[c].data_ptr(), dev.codes[c].data_ptr(), chunk.n, d_gid.data_ptr(),
+                   len(block.dicts[c]), ngroups, None, 1, d_counts.data_ptr(), d_bad.data_ptr(), R.stream())
+            per_value = d_counts.cpu().numpy().astype(np.int64)[1:] & 0xFFFFFFFF
+            acc = st["counts"][c]
+            for g in np.nonzero(per_value)[0]:
+                acc[distinct[g]] = acc.get(distinct[g], 0) + int(per_value[g])
+        if int(d_bad.item()):
+            raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
+        return False                                   # every chunk counts
+
+    def stream_pre_finish(self, st, chunks) -> "OpSetVectorizerModel":
+        tops: List[List[str]] = []
+        for c, per_rank in enumerate(zip(*D.all_gather_object(st["counts"]))):
+            total: dict = {}
+            for d in per_rank:
+                for v, k in d.items():
+                    total[v] = total.get(v, 0) + k
+            values = list(total)
+            order = top_k(values, np.array([total[v] for v in values], dtype=np.int64), self.topK, self.minSupport) \
+                if values else []
+            tops.append([values[i] for i in order])
+        self._metadata = self._metadata_for(tops)
+        return OpSetVectorizerModel(self, tops, self.cleanText, self.trackNulls)
+
+
 class OpSetVectorizerModel(OpModel):
     def __init__(self, parent: OpSetVectorizer, topValues: List[List[str]], shouldCleanText: bool,  # noqa: N803
                  shouldTrackNulls: bool):  # noqa: N803
@@ -117,9 +160,23 @@ class OpSetVectorizerModel(OpModel):
     def _sidecar(self, dev: SetBlock, n: int, n_all: int, classes, class_counts, ids, label_name: str,
                  cont=None) -> VectorStats:
         """cont = (label moments, shift, label on the device) for a continuous label (then classes is None)."""
+        st = self._side_begin(classes, cont is not None)
+        self._side_scan(st, dev, n, ids, cont)
+        return self._side_finish(st, n_all, classes, class_counts, label_name, cont)
+
+    def _side_begin(self, classes, continuous: bool) -> dict:
+        """Accumulators of the statistics scans (one batch, or the row chunks of a dataset one after the other)."""
         ncls = len(classes) if classes is not None else 1
-        cs_all, pr_all, ex_all, ax_all, ws_all = [], [], [], [], []
-        d_bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+        ws_ = [len(t) + 2 for t in self.topValues]
+        return {"ncls": ncls, "bad": torch.zeros(1, dtype=torch.int32, device="cuda"),
+                "cs": [np.zeros((w, ncls), dtype=np.int64) for w in ws_],
+                "pr": [np.zeros((w, ncls), dtype=np.int64) for w in ws_],
+                "ex": [np.zeros(w, dtype=np.int64) for w in ws_],
+                "ax": [np.zeros((w, 3), dtype=np.int64) for w in ws_],
+                "ws": [np.zeros(w) for w in ws_] if continuous else None}
+
+    def _side_scan(self, st: dict, dev: SetBlock, n: int, ids, cont) -> None:
+        ncls = st["ncls"]
         for c in range(len(dev.names)):
             k = len(self.topValues[c])
             w = k + 2
@@ -130,32 +187,39 @@ class OpSetVectorizerModel(OpModel):
             ax = torch.zeros(3 * w, dtype=torch.int32, device="cuda")
             ws = torch.zeros(w, dtype=torch.float64, device="cuda") if cont is not None else None
             L.call("tmog_set_stats_dev", dev.offsets[c].data_ptr(), dev.codes[c].data_ptr(), n, pos.data_ptr(),
-                   len(dev.dicts[c]), k, int(self.shouldTrackNulls), ids.data_ptr() if classes is not None else None,
+                   len(dev.dicts[c]), k, int(self.shouldTrackNulls), ids.data_ptr() if ids is not None else None,
                    ncls, cs.data_ptr(), pr.data_ptr(), ex.data_ptr(), ax.data_ptr(),
                    cont[2].data_ptr() if cont is not None else None, cont[1] if cont is not None else 0.0,
-                   ws.data_ptr() if cont is not None else None, d_bad.data_ptr(), R.stream())
+                   ws.data_ptr() if cont is not None else None, st["bad"].data_ptr(), R.stream())
             u32 = lambda t: t.cpu().numpy().astype(np.int64) & 0xFFFFFFFF   # noqa: E731
-            keep = self.widths[c]                      # without the null slot when nulls are not tracked
-            cs_all.append(u32(cs).reshape(w, ncls)[:keep])
-            pr_all.append(u32(pr).reshape(w, ncls)[:keep])
-            ex_all.append(ex.cpu().numpy()[:keep])
-            ax_all.append(u32(ax).reshape(w, 3)[:keep])
+            st["cs"][c] += u32(cs).reshape(w, ncls)
+            st["pr"][c] += u32(pr).reshape(w, ncls)
+            st["ex"][c] += ex.cpu().numpy()
+            a = u32(ax).reshape(w, 3)
+            acc = st["ax"][c]
+            acc[:, 0] = np.maximum(acc[:, 0], a[:, 0])
+            acc[:, 1] = np.maximum(acc[:, 1], a[:, 1])
+            acc[:, 2] += a[:, 2]
             if cont is not None:
-                ws_all.append(ws.cpu().numpy()[:keep])
-        cs = D.allreduce_sum(np.concatenate(cs_all)).astype(np.float64)
-        pr = D.allreduce_sum(np.concatenate(pr_all)).astype(np.float64)
-        ex = D.allreduce_sum(np.concatenate(ex_all)).astype(np.float64)
-        ax = np.concatenate(ax_all)
+                st["ws"][c] += ws.cpu().numpy()
+
+    def _side_finish(self, st: dict, n_all: int, classes, class_counts, label_name: str, cont) -> VectorStats:
+        keep = self.widths                             # without the null slot when nulls are not tracked
+        cut = lambda arrs: np.concatenate([a[:keep[c]] for c, a in enumerate(arrs)])   # noqa: E731
+        cs = D.allreduce_sum(cut(st["cs"])).astype(np.float64)
+        pr = D.allreduce_sum(cut(st["pr"])).astype(np.float64)
+        ex = D.allreduce_sum(cut(st["ex"])).astype(np.float64)
+        ax = cut(st["ax"])
         if D.world()[1] > 1:
             ax = np.stack([D.allreduce_max(ax[:, 0].copy()), D.allreduce_max(ax[:, 1].copy()),
                            D.allreduce_sum(ax[:, 2].copy())], axis=1)
-        if int(d_bad.item()):
+        if int(st["bad"].item()):
             raise ValueError("a dictionary code outside its column's dictionary was found in the batch")
         if cont is not None:
             sv, nnz = cs[:, 0], pr[:, 0]
             vmax = np.maximum(ax[:, 0], 1).astype(np.float64)
             vmin = np.where(ax[:, 2] >= nnz, (~ax[:, 1]) & 0xFFFFFFFF, 1).astype(np.float64)
-            return stats_from_sums_continuous(sv, sv + ex, nnz, vmax, vmin, D.allreduce_sum(np.concatenate(ws_all)),
+            return stats_from_sums_continuous(sv, sv + ex, nnz, vmax, vmin, D.allreduce_sum(cut(st["ws"])),
                                               cont[0], cont[1], label_name)
         cc = class_counts.astype(np.float64)
         mean_y = float((classes * cc).sum() / n_all)
@@ -172,6 +236,32 @@ class OpSetVectorizerModel(OpModel):
         # the per-label sums SanityChecker's contingency tables use clip MultiPickList columns to <= 1 (:258-268)
         return VectorStats(LabelInfo(label_name, n_all, lab, classes, class_counts), mean, var, mn, mx, cov,
                            np.ascontiguousarray(pr.T))
+
+    # -- row chunks (streaming.py): the statistics sidecar accumulated over the chunks (pass 1)
+    def stream_begin(self, label):
+        if label is None:
+            return {"label": None}
+        st = self._side_begin(label.classes, label.classes is None)
+        st["label"] = label
+        return st
+
+    def stream_update(self, st, chunk: ColumnarBatch) -> None:
+        lab = st["label"]
+        if lab is None:
+            return
+        names = [f.name for f in self.inN]
+        block = chunk.sets(names)
+        dev = chunk.on_device("sets", names, block)
+        ids = lab.class_ids(chunk) if lab.classes is not None else None
+        cont = None if lab.classes is not None else lab.continuous() + (lab.device_label(chunk),)
+        self._side_scan(st, dev, chunk.n, ids, cont)
+
+    def stream_finish(self, st):
+        lab = st["label"]
+        if lab is not None:
+            cont = None if lab.classes is not None else lab.continuous() + (None,)
+            self._fit_stats = self._side_finish(st, lab.n, lab.classes, lab.class_counts, lab.name, cont)
+        return self
 
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
         R.require_cuda()
