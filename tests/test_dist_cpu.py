@@ -73,6 +73,28 @@ def _worker(rank, size, port, q):
         # 5. shards tile the rows, starts aligned
         lo, hi = D.shard_rows(10_000, rank, size)
         assert lo % 2048 == 0 and (lo, hi) == ((0, 6144) if rank == 0 else (6144, 10_000))
+        # 6. streamed fits over ranks: IntegralVectorizer's value -> count maps add key-wise (mode, ties to the smaller
+        #    value), OpSetVectorizer's counts per cleaned value add up before the top-K (host side of stream_*_finish)
+        from oracle import text as T
+        from oracle import vectorizers as V
+        from transmogrifai_b200 import features as F
+        from transmogrifai_b200.stages.integral import _merge_tables
+        from transmogrifai_b200.stages.sets import OpSetVectorizer
+        rng = np.random.default_rng(9)
+        col = [None if rng.random() < 0.2 else int(v) for v in rng.choice([4, 8, -1], size=400, p=[0.4, 0.4, 0.2])]
+        lo2, hi2 = (0, 150) if rank == 0 else (150, 400)
+        vals = np.array([v for v in col[lo2:hi2] if v is not None], dtype=np.int64)
+        k, w = np.unique(vals, return_counts=True)
+        assert _merge_tables(D.all_gather_object([(k, w.astype(np.int64))])) == V.mode_seq_null_int([col])
+        sets = [[["a", "A "], ["b"], ["a", "c"], [], ["b", "b"]][int(rng.integers(5))] for _ in range(400)]
+        est = OpSetVectorizer().setTopK(2).setMinSupport(5).setInput(F.FeatureBuilder.MultiPickList("s").asPredictor())
+        local = {}
+        for row in sets[lo2:hi2]:
+            for v in row:
+                cv = T.clean_string(v)
+                local[cv] = local.get(cv, 0) + 1
+        model = est.stream_pre_finish({"counts": [local]}, None)
+        assert [list(t) for t in model.topValues] == [list(t) for t in V.pivot_fit([sets], 2, 5, True)]
         q.put((rank, "ok"))
     except Exception as e:  # pragma: no cover
         q.put((rank, repr(e)))
