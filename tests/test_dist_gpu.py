@@ -159,7 +159,7 @@ def test_two_ranks_over_nccl_all_types_match_oracle():
     _run(_worker, "nccl")
 
 
-def _worker_streamed(rank, size, port, q, backend="gloo"):
+def _worker_streamed(rank, size, port, q, backend="gloo", sample=False):
     """Every rank streams its row shard in three chunks (own dictionaries per chunk): passes 0 / 1 fold the chunks, the
     accumulators are merged over the ranks once, pass 2 transforms chunk by chunk."""
     _init(rank, size, port, backend)
@@ -185,7 +185,8 @@ def _worker_streamed(rank, size, port, q, backend="gloo"):
                  FB.Text("t2").asPredictor()]
         label = FB.RealNN("y").asResponse()
         checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
-                                    sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
+                                    sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off",
+                                    checkSample=0.5 if sample else 1.0)
         out = []
         # rank 0 keeps the packed text cells of its chunks for pass 2, rank 1 transforms from the text: same rows
         res = fit_and_transform_stream(chunks, checked, lambda k, vec, parts: out.append(
@@ -209,12 +210,17 @@ def _worker_streamed(rank, size, port, q, backend="gloo"):
              V.smart_text_metadata(tnames, "Text", methods, ttops, 512, True)])
         p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
                            feature_feature_corr_level="off")
-        ref = S.sanity_fit(y, sp.csr_matrix(xo), metas, p, label_name="y")
-        assert est.summary.count == n
+        rows = np.arange(n)
+        if sample:          # SanityChecker looked at a row sample: every rank's sampled rows, gathered
+            mine = np.concatenate([r.cpu().numpy() + a for r, a in zip(res.sample_rows, cuts[:-1])])
+            rows = np.sort(np.concatenate(D.all_gather_object(mine)))
+            assert 0.4 * n < len(rows) < 0.6 * n
+        ref = S.sanity_fit(y[rows], sp.csr_matrix(xo)[rows], metas, p, label_name="y")
+        assert est.summary.count == len(rows)
         assert est.summary.names[:-1] == [m.col_name() for m in metas]
         assert est.summary.dropped == ref.dropped
         assert res.fitted[-1].indicesToKeep == ref.indices_to_keep
-        np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-12, atol=1e-300)
+        np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-10 if sample else 1e-12, atol=1e-300)
         np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
         assert np.array_equal(est.summary.min, ref.col_stats.min) and np.array_equal(est.summary.max, ref.col_stats.max)
         np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
@@ -241,6 +247,11 @@ def test_two_ranks_streamed_chunks_match_oracle():
 @needs_two_gpus
 def test_two_ranks_over_nccl_streamed_chunks_match_oracle():
     _run(_worker_streamed, "nccl")
+
+
+def test_two_ranks_streamed_chunks_sampled_sanity_checker_matches_oracle():
+    """fraction() < 1 over streamed chunks on two ranks: the ranks' sample statistics merge in rank order."""
+    _run(_worker_streamed, "gloo", True)
 
 
 def _worker_sampled(rank, size, port, q):

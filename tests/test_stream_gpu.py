@@ -379,3 +379,51 @@ def test_set_vectorizer_over_chunks(continuous):
     out1, _f = fit_and_transform(batch, checked1)
     assert checked1.origin_stage.summary.dropped == est.summary.dropped
     assert abs(out1.vectors[checked1.name].to_scipy() - sp.vstack(out).tocsr()).max() == 0
+
+
+def test_sanity_checker_sample_over_chunks():
+    """SanityChecker with fraction() < 1 over a chunk-streamed dataset (SanityChecker.scala:356-387): the statistics are
+    those of a row sample drawn chunk by chunk, taken by the fitted stages (fills and vocabularies of ALL rows) and merged;
+    against the oracle on exactly the sampled rows, and the transform of all rows with the kept columns."""
+    from transmogrifai_b200.columnar import VectorColumn
+    from transmogrifai_b200.streaming import fit_and_transform_stream
+    cols, y = _data(sum(SIZES), 91)
+    chunks = _chunks(cols, "own_dictionaries_host")
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.dsl import transmogrify
+    FB = F.FeatureBuilder
+    feats = [FB.Text("t0").asPredictor(), FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(),
+             FB.RealNN("nn").asPredictor(), FB.PickList("p0").asPredictor(), FB.Real("r1").asPredictor(),
+             FB.Binary("b1").asPredictor(), FB.Text("t1").asPredictor(), FB.PickList("p1").asPredictor(),
+             FB.Text("t2").asPredictor()]
+    label = FB.RealNN("y").asResponse()
+    checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, checkSample=0.4, sampleLowerLimit=0,
+                                sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off")
+    out = []
+    res = fit_and_transform_stream(chunks, checked, lambda k, vec, parts: out.append(
+        VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy()))
+    est = checked.origin_stage
+    assert res.sample_rows is not None and len(res.sample_rows) == len(SIZES)
+    bounds = np.concatenate([[0], np.cumsum(SIZES)])
+    rows = np.concatenate([r.cpu().numpy() + a for r, a in zip(res.sample_rows, bounds[:-1])])
+    assert 0.3 * sum(SIZES) < len(rows) < 0.5 * sum(SIZES) and est.summary.count == len(rows)
+    assert abs(est.summary.sampleFraction - 0.4) < 1e-12
+    # the oracle: vectorizers fitted on all rows, SanityChecker's statistics on the sampled ones
+    _ref_all, xo, metas, _methods, _tops = _oracle(cols, y)
+    p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                       feature_feature_corr_level="off")
+    ref = S.sanity_fit(y[rows], xo[rows], metas, p, label_name="y")
+    assert est.summary.dropped == ref.dropped
+    assert list(res.fitted[-1].indicesToKeep) == ref.indices_to_keep
+    np.testing.assert_allclose(est.summary.mean, ref.col_stats.mean, rtol=1e-10, atol=1e-300)
+    np.testing.assert_allclose(est.summary.variance, ref.col_stats.variance, rtol=1e-9, atol=1e-18)
+    assert np.array_equal(est.summary.min, ref.col_stats.min) and np.array_equal(est.summary.max, ref.col_stats.max)
+    np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                               equal_nan=True)
+    got_g = {g.group: g for g in est.summary.categoricalStats}
+    for g in ref.cat_stats:
+        assert np.array_equal(got_g[g.group].contingencyMatrix, g.contingency_matrix)
+        np.testing.assert_allclose(got_g[g.group].cramersV, g.cramers_v, rtol=1e-9, equal_nan=True)
+    exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
+    got = sp.vstack(out).tocsr()
+    assert got.shape == exp.shape and abs(got - exp).max() < 1e-12

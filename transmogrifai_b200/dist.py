@@ -15,10 +15,28 @@ import torch.distributed as dist
 from ._lib import REAL_NSTAT
 
 
+_LOCAL_ONLY = [0]
+
+
 def world() -> Tuple[int, int]:
+    if _LOCAL_ONLY[0]:
+        return 0, 1
     if dist.is_available() and dist.is_initialized():
         return dist.get_rank(), dist.get_world_size()
     return 0, 1
+
+
+class local_only:
+    """Inside this block the stage layer sees a single rank: fits and statistics cover this rank's rows only and make no
+    exchange (for work whose pieces are merged explicitly afterwards, e.g. the per-chunk statistics of a row sample)."""
+
+    def __enter__(self):
+        _LOCAL_ONLY[0] += 1
+        return self
+
+    def __exit__(self, *exc):
+        _LOCAL_ONLY[0] -= 1
+        return False
 
 
 def _device() -> torch.device:

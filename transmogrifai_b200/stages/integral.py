@@ -286,6 +286,16 @@ class IntegralVectorizerModel(OpModel):
         self._fit_stats: Optional[VectorStats] = None
         self._fit_key = None
 
+    def stats_for(self, batch: ColumnarBatch) -> Optional[VectorStats]:
+        """SanityChecker statistics of this model's columns over another batch (a row sample of the training data)."""
+        if not batch.response:
+            return None
+        names = [f.name for f in self.inN]
+        block = batch.numeric(names)
+        dev = batch.on_device("numeric", names, block)
+        return self.parent._sidecar(batch, dev, batch.n, len(names), np.asarray(self.fillValues, dtype=np.float64),
+                                    batch.response)
+
     def transformColumn(self, batch: ColumnarBatch) -> VectorColumn:  # noqa: N802
         R.require_cuda()
         names = [f.name for f in self.inN]

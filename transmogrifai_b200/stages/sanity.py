@@ -217,7 +217,12 @@ class SanityChecker(OpEstimator):
         if n <= 0:
             raise ValueError("requirement failed: Sample size cannot be zero")
         frac = self.fraction(n)
-        if frac < 1.0:
+        pre = batch.__dict__.get("_presampled")
+        if pre is not None:
+            # a chunk-streamed dataset: the sample has been drawn chunk by chunk and the sidecar is the sample's
+            # (streaming.fit_stream); batch.n is the row count of the whole dataset
+            frac = float(pre)
+        elif frac < 1.0:
             batch, vec, n = self._sample(batch, vec, frac)
             if n <= 0:
                 raise ValueError("requirement failed: Sample size cannot be zero")

@@ -237,6 +237,21 @@ class OpSetVectorizerModel(OpModel):
         return VectorStats(LabelInfo(label_name, n_all, lab, classes, class_counts), mean, var, mn, mx, cov,
                            np.ascontiguousarray(pr.T))
 
+    def stats_for(self, batch: ColumnarBatch) -> Optional[VectorStats]:
+        """SanityChecker statistics of this model's columns over another batch (a row sample of the training data)."""
+        label_name = batch.response
+        if not label_name:
+            return None
+        names = [f.name for f in self.inN]
+        block = batch.sets(names)
+        dev = batch.on_device("sets", names, block)
+        y = batch.label()
+        y = y if y.is_cuda else y.cuda()
+        classes, class_counts, ids = label_info_dev(batch, y, label_name)
+        n_all = int(D.allreduce_sum(np.array([batch.n], dtype=np.int64))[0])
+        cont = None if classes is not None else label_moments_dev(batch, y, label_name) + (y,)
+        return self._sidecar(dev, batch.n, n_all, classes, class_counts, ids, label_name, cont)
+
     # -- row chunks (streaming.py): the statistics sidecar accumulated over the chunks (pass 1)
     def stream_begin(self, label):
         if label is None:

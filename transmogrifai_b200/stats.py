@@ -21,6 +21,26 @@ class LabelInfo:
     def same_as(self, other: "LabelInfo") -> bool:
         return self.name == other.name and self.n == other.n
 
+    def merge(self, other: "LabelInfo") -> "LabelInfo":
+        """The label over the rows of both (disjoint row sets): moments by the pairwise update, classes united."""
+        na, nb = float(self.n), float(other.n)
+        n = na + nb
+        d = other.stats[1] - self.stats[1]
+        mean = self.stats[1] + d * nb / n
+        m2 = self.stats[2] * max(na - 1, 0) + other.stats[2] * max(nb - 1, 0) + d * d * na * nb / n
+        st = np.array([n, mean, m2 / (n - 1) if n > 1 else 0.0, min(self.stats[3], other.stats[3]),
+                       max(self.stats[4], other.stats[4])])
+        classes = counts = None
+        if self.classes is not None and other.classes is not None:
+            bits = np.union1d(self.classes.view(np.int64), other.classes.view(np.int64))
+            classes = np.sort(bits.view(np.float64))
+            key = {int(b): i for i, b in enumerate(classes.view(np.int64))}
+            counts = np.zeros(len(classes), dtype=np.int64)
+            for src in (self, other):
+                for b, k in zip(src.classes.view(np.int64), src.class_counts):
+                    counts[key[int(b)]] += int(k)
+        return LabelInfo(self.name, int(n), st, classes, counts)
+
 
 @dataclass
 class VectorStats:
@@ -47,6 +67,34 @@ class VectorStats:
             cs = np.concatenate([p.class_sums for p in parts], axis=1)
         cat = lambda k: np.concatenate([getattr(p, k) for p in parts])  # noqa: E731
         return VectorStats(first.label, cat("mean"), cat("variance"), cat("min"), cat("max"), cat("cov_label"), cs)
+
+    def merge(self, other: "VectorStats") -> "VectorStats":
+        """The statistics over the rows of both (two disjoint row sets of the same vector layout: the row chunks of a
+        sample): pairwise update of the moments and co-moments, per-class sums added class by class."""
+        na, nb = float(self.label.n), float(other.label.n)
+        if nb == 0:
+            return self
+        if na == 0:
+            return other
+        n = na + nb
+        lab = self.label.merge(other.label)
+        d = other.mean - self.mean
+        mean = self.mean + d * (nb / n)
+        m2 = self.variance * max(na - 1, 0) + other.variance * max(nb - 1, 0) + d * d * (na * nb / n)
+        var = m2 / (n - 1) if n > 1 else np.zeros_like(m2)
+        dy = other.label.stats[1] - self.label.stats[1]
+        cov = self.cov_label + other.cov_label + d * dy * (na * nb / n)
+        cs = None
+        if self.class_sums is not None and other.class_sums is not None and lab.classes is not None:
+            key = {int(b): i for i, b in enumerate(lab.classes.view(np.int64))}
+            cs = np.zeros((len(lab.classes), self.width))
+            nan = np.zeros(self.width, dtype=bool)
+            for src in (self, other):
+                nan |= np.isnan(src.class_sums).all(axis=0) if len(src.class_sums) else False
+                for b, row in zip(src.label.classes.view(np.int64), src.class_sums):
+                    cs[key[int(b)]] += np.nan_to_num(row, nan=0.0)
+            cs[:, nan] = np.nan                        # columns whose per-class sums are not tracked stay untracked
+        return VectorStats(lab, mean, var, np.minimum(self.min, other.min), np.maximum(self.max, other.max), cov, cs)
 
     def select(self, idx: List[int]) -> "VectorStats":
         idx = np.asarray(idx, dtype=np.int64)

@@ -551,6 +551,16 @@ def fit_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, response: Opt
     # ---- decisions: the vector stages see a batch without rows whose vectors carry metadata + statistics
     n_all = label.n if label is not None else int(D.allreduce_sum(np.array([n_local], dtype=np.int64))[0])
     virtual = ColumnarBatch(n_all, [], {}, label.name if label is not None else None)
+    # ---- pass 1s, only when a SanityChecker samples (fraction() < 1, its default above a million rows,
+    #      SanityChecker.scala:356-387): the statistics it reads are those of a row sample, taken by the fitted stages
+    #      over the sampled rows of every chunk (the same fused scans, finished with the fills / vocabularies of ALL rows)
+    #      and merged chunk by chunk
+    sample_rows = None
+    samplers = [st for st in stages if not _is_raw_stage(st) and hasattr(st, "fraction") and label is not None]
+    frac = min((st.fraction(n_all) for st in samplers), default=1.0)
+    if frac < 1.0:
+        seed = int(getattr(samplers[0], "sampleSeed", 42))
+        stats_of, sample_rows = _sampled_stats(chunks, [models[id(st)] for st in raw], raw, label.name, frac, seed)
     fitted = []
     for st in stages:
         if _is_raw_stage(st):
@@ -558,14 +568,52 @@ def fit_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, response: Opt
             meta = model.getMetadata()
             vec = VectorColumn(model.getOutput().name, n_all, meta, [WidthPart(meta.size)], stats_of[id(st)], model)
             virtual = virtual.with_vector(vec)
+            if frac < 1.0:
+                virtual.__dict__["_presampled"] = frac      # (a new batch object per vector)
         else:
             model = st.fit(virtual) if isinstance(st, OpEstimator) else st
             vec = model.transformColumn(virtual) if not hasattr(model, "stream_transform_virtual") else \
                 model.stream_transform_virtual(virtual)
             vec.producer = model
             virtual = virtual.with_vector(vec)
+            if frac < 1.0:
+                virtual.__dict__["_presampled"] = frac      # (a new batch object per vector)
         fitted.append(model)
-    return StreamResult(fitted, label, n_local, n_chunks, virtual.vectors)
+    res = StreamResult(fitted, label, n_local, n_chunks, virtual.vectors)
+    res.sample_rows = sample_rows            # per chunk: the rows a sampling SanityChecker looked at (None: all rows)
+    return res
+
+
+def _sampled_stats(chunks, models, raw, label_name: str, frac: float, seed: int):
+    """Statistics sidecars of every raw stage's vector over a Bernoulli(frac) sample of the rows of all chunks."""
+    rank = D.world()[0]
+    acc: Dict[int, object] = {}
+    picked = []
+    for k, chunk in enumerate(device_chunks(chunks)):
+        g = torch.Generator(device="cuda").manual_seed(seed + 7919 * k + 104729 * rank)
+        idx = (torch.rand(chunk.n, device="cuda", generator=g) < frac).nonzero().squeeze(1)
+        picked.append(idx)
+        if idx.numel():
+            sub = chunk.take_rows(idx)
+            sub.response = label_name
+            with D.local_only():              # this rank's rows only: the ranks' statistics are merged below
+                for st, model in zip(raw, models):
+                    vec = model.transformColumn(sub)
+                    stats = vec.stats if vec.stats is not None else model.stats_for(sub)
+                    if stats is None:
+                        raise NotImplementedError(f"{type(model).__name__} cannot give statistics of a row sample")
+                    acc[id(st)] = stats if id(st) not in acc else acc[id(st)].merge(stats)
+        _release(chunk)
+    if D.world()[1] > 1:                      # the ranks' samples merge like the chunks' do, in rank order
+        merged: Dict[int, object] = {}
+        for per_rank in D.all_gather_object([acc.get(id(st)) for st in raw]):
+            for st, stats in zip(raw, per_rank):
+                if stats is not None:
+                    merged[id(st)] = stats if id(st) not in merged else merged[id(st)].merge(stats)
+        acc = merged
+    if not acc:
+        raise ValueError("requirement failed: Sample size cannot be zero")
+    return acc, picked
 
 
 def transform_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, fit: StreamResult,
