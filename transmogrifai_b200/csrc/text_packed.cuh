@@ -15,7 +15,7 @@
 namespace tmog {
 
 constexpr int TP_WARPS = 8;
-constexpr int TP_STAGE = 1536;            // entries of a row the stage holds
+constexpr int TP_STAGE = 1152;            // entries of a row the stage holds (4 CTAs of 8 warps fit an SM)
 constexpr int TP_WARP_BYTES = TP_STAGE * 4 + TP_STAGE;
 
 struct TpCell {
