@@ -427,3 +427,52 @@ def test_sanity_checker_sample_over_chunks():
     exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
     got = sp.vstack(out).tocsr()
     assert got.shape == exp.shape and abs(got - exp).max() < 1e-12
+
+
+@pytest.mark.parametrize("sampled", [False, True])
+def test_feature_feature_correlations_over_chunks(sampled):
+    """CorrelationLevel.Computed (the reference's default, SanityChecker.scala:467-470) over a chunk-streamed dataset: one
+    more pass builds the checker's input vector chunk by chunk (of the sampled rows when the checker samples) and adds
+    every chunk's rows to one Gramian; the full Pearson matrix, the drop set and the kept columns against the oracle on
+    the same rows."""
+    from transmogrifai_b200 import features as F
+    from transmogrifai_b200.columnar import VectorColumn
+    from transmogrifai_b200.dsl import transmogrify
+    from transmogrifai_b200.streaming import fit_and_transform_stream
+    cols, y = _data(sum(SIZES), 58, continuous=True)
+    chunks = _chunks(cols, "own_dictionaries_host")
+    FB = F.FeatureBuilder
+    feats = [FB.Text("t0").asPredictor(), FB.Real("r0").asPredictor(), FB.Binary("b0").asPredictor(),
+             FB.RealNN("nn").asPredictor(), FB.PickList("p0").asPredictor(), FB.Real("r1").asPredictor(),
+             FB.Binary("b1").asPredictor(), FB.Text("t1").asPredictor(), FB.PickList("p1").asPredictor(),
+             FB.Text("t2").asPredictor()]
+    label = FB.RealNN("y").asResponse()
+    checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, checkSample=0.5 if sampled else 1.0,
+                                sampleLowerLimit=0, sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Computed")
+    out = []
+    res = fit_and_transform_stream(chunks, checked, lambda k, vec, parts: out.append(
+        VectorColumn(vec.name, vec.n, vec.metadata, parts).to_scipy()), cell_cache_bytes=64 << 20)
+    est = checked.origin_stage
+    n = sum(SIZES)
+    if sampled:
+        bounds = np.concatenate([[0], np.cumsum(SIZES)])
+        rows = np.concatenate([r.cpu().numpy() + a for r, a in zip(res.sample_rows, bounds[:-1])])
+        assert 0.4 * n < len(rows) < 0.6 * n
+    else:
+        assert res.sample_rows is None
+        rows = np.arange(n)
+    assert est.summary.count == len(rows)
+    _ref_all, xo, metas, _methods, _tops = _oracle(cols, y)
+    p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
+                       feature_feature_corr_level="computed")
+    ref = S.sanity_fit(y[rows], xo[rows], metas, p, label_name="y")
+    m = est.summary.featureFeatureCorr
+    assert m is not None and m.shape == ref.corr_matrix.shape == (xo.shape[1] + 1, xo.shape[1] + 1)
+    np.testing.assert_allclose(m, ref.corr_matrix, rtol=1e-9, atol=1e-12, equal_nan=True)
+    np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
+                               equal_nan=True)
+    assert est.summary.dropped == ref.dropped
+    assert list(res.fitted[-1].indicesToKeep) == ref.indices_to_keep
+    exp = xo.tocsc()[:, ref.indices_to_keep].tocsr()
+    got = sp.vstack(out).tocsr()
+    assert got.shape == exp.shape and abs(got - exp).max() < 1e-12

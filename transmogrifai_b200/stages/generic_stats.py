@@ -107,65 +107,90 @@ def vector_stats(batch: ColumnarBatch, vec: VectorColumn, label_name: str) -> Ve
     return st
 
 
+class PearsonAccumulator:
+    """Gramian and column sums of the shifted rows ([selected columns, label]) of one batch or of many: what
+    Statistics.corr(vectorRowsForCorr, "pearson") needs (SanityChecker.scala:467-470).  Rows go through the Gramian
+    kernel in tiles (the kernel adds to the matrix), so the limit is the (d + 1)^2 matrix itself -- the reference's
+    65535 columns -- not rows x columns.  `shifts` ([d + 1], common to every rank and batch: e.g. the column means
+    already known from the fit scans) conditions the sums; without it the first rows seen give a pilot shift."""
+
+    def __init__(self, d_all: int, corr_indices: Sequence[int], shifts: Optional[np.ndarray] = None):
+        R.require_cuda()
+        feat = [int(i) for i in corr_indices if i < d_all]
+        if len(feat) + 1 > 65535:
+            raise ValueError(f"requirement failed: Argument with more than 65535 cols: {len(feat) + 1}")
+        self.d_all, self.d, self.D = d_all, len(feat), len(feat) + 1
+        self.select = None if feat == list(range(d_all)) else torch.tensor(feat, dtype=torch.int32, device="cuda")
+        D = self.D
+        self.primed = shifts is not None
+        if shifts is None:
+            self.shifts = torch.zeros(D, dtype=torch.float64, device="cuda")
+        else:
+            s = np.nan_to_num(np.asarray(shifts, dtype=np.float64), nan=0.0, posinf=0.0, neginf=0.0)
+            if s.shape != (D,):
+                raise ValueError(f"shifts: expected {D} values, got {s.shape}")
+            self.shifts = torch.from_numpy(np.ascontiguousarray(s)).cuda()
+        self.gram = torch.zeros((D, D), dtype=torch.float64, device="cuda")
+        self.sums = torch.zeros(D * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
+        self.partials = torch.zeros(D * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
+
+    def update(self, batch: ColumnarBatch, vec: VectorColumn, label_name: str) -> None:
+        n, d_all, d = vec.n, self.d_all, self.d
+        if n <= 0:
+            return
+        parts = _materialized(vec)
+        if sum(p.width for p in parts) != d_all:
+            raise ValueError(f"the vector has {sum(p.width for p in parts)} columns, expected {d_all}")
+        y = _device_label(batch, label_name)
+        tile = n if n * d_all * 8 <= GRAM_TILE_BYTES else max(1024, GRAM_TILE_BYTES // (d_all * 8) // 64 * 64)
+        nb = C.c_size_t()
+        L.call("tmog_dense_stats_scratch_bytes", min(tile, n), d, C.byref(nb))
+        scratch = R.scratch("dense_stats", nb.value)
+        for a in range(0, n, tile):
+            b = min(n, a + tile)
+            x = _dense_block(vec, parts, a, b)
+            if self.select is not None:
+                sub = torch.empty((b - a, d), dtype=torch.float64, device="cuda")
+                L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), b - a, self.select.data_ptr(), d,
+                       sub.data_ptr(), d, R.stream())
+                x = sub
+            ya = y[a:]
+            if not self.primed:
+                L.call("tmog_dense_pilot_shift_dev", x.data_ptr(), x.stride(0), b - a, d, ya.data_ptr(),
+                       self.shifts.data_ptr(), R.stream())
+                if DD.world()[1] > 1:
+                    torch.distributed.broadcast(self.shifts, src=0)
+                self.primed = True
+            L.call("tmog_dense_stats_dev", x.data_ptr(), x.stride(0), b - a, d, ya.data_ptr(), None, 0, None,
+                   self.shifts.data_ptr(), scratch.data_ptr(), scratch.numel(), self.partials.data_ptr(), None,
+                   R.stream())
+            self.sums += self.partials                     # only the shifted sums ([.][1]) and the row count are used
+            L.call("tmog_dense_gram_dev", x.data_ptr(), x.stride(0), b - a, d, ya.data_ptr(), self.shifts.data_ptr(),
+                   self.gram.data_ptr(), R.stream())
+            del x
+
+    def finish(self) -> np.ndarray:
+        """-> the [d + 1, d + 1] Pearson matrix over the rows of every update of every rank."""
+        D = self.D
+        if DD.world()[1] > 1:                              # Gramian and sums of the shifted rows add up over the ranks
+            torch.distributed.all_reduce(self.gram)
+            torch.distributed.all_reduce(self.sums)
+        g = self.gram.cpu().numpy()
+        merged = self.sums.cpu().numpy().reshape(D, L.REAL_NSTAT)
+        col_sums = np.ascontiguousarray(merged[:, 1])
+        n_all = float(merged[D - 1, 7])
+        corr = np.zeros((D, D))
+        L.call("tmog_pearson_from_gram", D, n_all, g.ctypes.data, col_sums.ctypes.data, corr.ctypes.data)
+        return corr
+
+
 def pearson_matrix(batch: ColumnarBatch, vec: VectorColumn, label_name: str, corr_indices: Sequence[int],
                    st: Optional[VectorStats]) -> np.ndarray:
-    """Statistics.corr(vectorRowsForCorr, "pearson") over the selected columns + label (SanityChecker.scala:467-470).
-    A vector too large to densify at once goes through the Gramian kernel in row tiles (the kernel adds to the matrix),
-    so the limit is the (d + 1)^2 matrix itself -- the reference's 65535 columns -- not rows x columns."""
-    R.require_cuda()
-    parts = _materialized(vec)
-    n, d_all = vec.n, sum(p.width for p in parts)
-    feat = [i for i in corr_indices if i < d_all]
-    if len(feat) + 1 > 65535:
-        raise ValueError(f"requirement failed: Argument with more than 65535 cols: {len(feat) + 1}")
-    select = None if feat == list(range(d_all)) else torch.tensor(feat, dtype=torch.int32, device="cuda")
-    d = len(feat)
-    D = d + 1
-    y = _device_label(batch, label_name)
-    dist_world = DD.world()[1]
-    tile = n if n * d_all * 8 <= GRAM_TILE_BYTES else max(1024, GRAM_TILE_BYTES // (d_all * 8) // 64 * 64)
-
-    def rows(a: int, b: int) -> torch.Tensor:
-        x = _dense_block(vec, parts, a, b)
-        if select is None:
-            return x
-        sub = torch.empty((b - a, d), dtype=torch.float64, device="cuda")
-        L.call("tmog_dense_gather_dev", x.data_ptr(), x.stride(0), b - a, select.data_ptr(), d, sub.data_ptr(), d,
-               R.stream())
-        return sub
-
-    shifts = torch.zeros(D, dtype=torch.float64, device="cuda")
-    gram = torch.zeros((D, D), dtype=torch.float64, device="cuda")
-    sums = torch.zeros(D * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
-    nb = C.c_size_t()
-    L.call("tmog_dense_stats_scratch_bytes", min(tile, n), d, C.byref(nb))
-    scratch = R.scratch("dense_stats", nb.value)
-    partials = torch.zeros(D * L.REAL_NSTAT, dtype=torch.float64, device="cuda")
-    for a in range(0, max(n, 1), max(tile, 1)):
-        b = min(n, a + tile)
-        x = rows(a, b)
-        ya = y[a:]
-        if a == 0:
-            L.call("tmog_dense_pilot_shift_dev", x.data_ptr(), x.stride(0), b - a, d, ya.data_ptr(), shifts.data_ptr(),
-                   R.stream())
-            if dist_world > 1:
-                torch.distributed.broadcast(shifts, src=0)
-        L.call("tmog_dense_stats_dev", x.data_ptr(), x.stride(0), b - a, d, ya.data_ptr(), None, 0, None,
-               shifts.data_ptr(), scratch.data_ptr(), scratch.numel(), partials.data_ptr(), None, R.stream())
-        sums += partials                                   # only the shifted sums ([.][1]) and the row count are used
-        L.call("tmog_dense_gram_dev", x.data_ptr(), x.stride(0), b - a, d, ya.data_ptr(), shifts.data_ptr(),
-               gram.data_ptr(), R.stream())
-        del x
-    if dist_world > 1:                                     # Gramian and sums of the shifted rows add up over the ranks
-        torch.distributed.all_reduce(gram)
-        torch.distributed.all_reduce(sums)
-    g = gram.cpu().numpy()
-    merged = sums.cpu().numpy().reshape(D, L.REAL_NSTAT)
-    col_sums = np.ascontiguousarray(merged[:, 1])
-    n_all = float(merged[D - 1, 7])
-    corr = np.zeros((D, D))
-    L.call("tmog_pearson_from_gram", D, n_all, g.ctypes.data, col_sums.ctypes.data, corr.ctypes.data)
-    return corr
+    """Statistics.corr(vectorRowsForCorr, "pearson") over the selected columns + label of one resident batch
+    (SanityChecker.scala:467-470)."""
+    acc = PearsonAccumulator(sum(p.width for p in vec.parts), corr_indices)
+    acc.update(batch, vec, label_name)
+    return acc.finish()
 
 
 def select_columns(vec: VectorColumn, keep: List[int]) -> list:

@@ -257,8 +257,14 @@ class SanityChecker(OpEstimator):
         corr[-1] = 1.0 if lab.stats[2] > 0 else np.nan
         corr_matrix = None
         if self.featureFeatureCorrLevel == "Computed":
-            from .generic_stats import pearson_matrix
-            corr_matrix = pearson_matrix(batch, vec, label_f.name, [int(i) for i in corr_indices], st)
+            stream_corr = batch.__dict__.get("_stream_corr")
+            if stream_corr is not None:
+                # a chunk-streamed dataset: the rows are not in `batch`; one more pass over the chunks accumulates the
+                # Gramian (streaming.fit_stream)
+                corr_matrix = stream_corr(vec_f.name, label_f.name, [int(i) for i in corr_indices], st)
+            else:
+                from .generic_stats import pearson_matrix
+                corr_matrix = pearson_matrix(batch, vec, label_f.name, [int(i) for i in corr_indices], st)
             corr = corr_matrix[:, -1].copy()
         # categorical tests -------------------------------------------------------------------------------------
         cat_stats: List[CategoricalGroupStats] = []

@@ -562,26 +562,57 @@ def fit_stream(chunks: Iterable[ColumnarBatch], result: F.Feature, response: Opt
         seed = int(getattr(samplers[0], "sampleSeed", 42))
         stats_of, sample_rows = _sampled_stats(chunks, [models[id(st)] for st in raw], raw, label.name, frac, seed)
     fitted = []
+    marks = {"_stream_corr": _stream_corr(chunks, fitted, sample_rows)}    # re-applied: a new batch object per vector
+    if frac < 1.0:
+        marks["_presampled"] = frac
     for st in stages:
         if _is_raw_stage(st):
             model = models[id(st)]
             meta = model.getMetadata()
             vec = VectorColumn(model.getOutput().name, n_all, meta, [WidthPart(meta.size)], stats_of[id(st)], model)
             virtual = virtual.with_vector(vec)
-            if frac < 1.0:
-                virtual.__dict__["_presampled"] = frac      # (a new batch object per vector)
+            virtual.__dict__.update(marks)
         else:
             model = st.fit(virtual) if isinstance(st, OpEstimator) else st
             vec = model.transformColumn(virtual) if not hasattr(model, "stream_transform_virtual") else \
                 model.stream_transform_virtual(virtual)
             vec.producer = model
             virtual = virtual.with_vector(vec)
-            if frac < 1.0:
-                virtual.__dict__["_presampled"] = frac      # (a new batch object per vector)
+            virtual.__dict__.update(marks)
         fitted.append(model)
     res = StreamResult(fitted, label, n_local, n_chunks, virtual.vectors)
     res.sample_rows = sample_rows            # per chunk: the rows a sampling SanityChecker looked at (None: all rows)
     return res
+
+
+def _stream_corr(chunks, fitted: list, picked: Optional[list]):
+    """The SanityChecker's full Pearson matrix (CorrelationLevel.Computed, SanityChecker.scala:467-470) of a
+    chunk-streamed dataset: one more pass in which the stages fitted so far (`fitted`, read when the matrix is asked for)
+    produce the checker's input vector chunk by chunk -- of the sampled rows `picked[k]` when the checker samples -- and the
+    Gramian kernel adds each chunk's rows to one (d + 1)^2 matrix; the ranks' matrices add.  The shifts are the column
+    means the fit scans have found already (the same on every rank and chunk)."""
+    def matrix(vec_name: str, label_name: str, corr_indices, stats) -> np.ndarray:
+        from .stages.generic_stats import PearsonAccumulator
+        d_all = len(stats.mean)
+        feat = [int(i) for i in corr_indices if i < d_all]
+        shifts = np.append(np.asarray(stats.mean, dtype=np.float64)[feat], float(stats.label.stats[1]))
+        acc = PearsonAccumulator(d_all, corr_indices, shifts)
+        models = list(fitted)
+        for k, chunk in enumerate(device_chunks(chunks)):
+            rows = chunk
+            if picked is not None:
+                rows = chunk.take_rows(picked[k]) if picked[k].numel() else None
+            if rows is not None and rows.n:
+                batch = ColumnarBatch(rows.n, rows.blocks, {}, None)                   # no response: no statistics
+                with D.local_only():          # this rank's rows only: finish() adds the ranks' matrices
+                    for model in models:
+                        batch = model.transform(batch)
+                    acc.update(batch, batch.vectors[vec_name], label_name)
+                batch = None
+            rows = None
+            _release(chunk)
+        return acc.finish()
+    return matrix
 
 
 def _sampled_stats(chunks, models, raw, label_name: str, frac: float, seed: int):
