@@ -159,7 +159,7 @@ def test_two_ranks_over_nccl_all_types_match_oracle():
     _run(_worker, "nccl")
 
 
-def _worker_streamed(rank, size, port, q, backend="gloo", sample=False):
+def _worker_streamed(rank, size, port, q, backend="gloo", sample=False, corr="Off"):
     """Every rank streams its row shard in three chunks (own dictionaries per chunk): passes 0 / 1 fold the chunks, the
     accumulators are merged over the ranks once, pass 2 transforms chunk by chunk."""
     _init(rank, size, port, backend)
@@ -185,7 +185,7 @@ def _worker_streamed(rank, size, port, q, backend="gloo", sample=False):
                  FB.Text("t2").asPredictor()]
         label = FB.RealNN("y").asResponse()
         checked = label.sanityCheck(transmogrify(feats), removeBadFeatures=True, sampleLowerLimit=0,
-                                    sampleUpperLimit=10 ** 9, featureFeatureCorrLevel="Off",
+                                    sampleUpperLimit=10 ** 9, featureFeatureCorrLevel=corr,
                                     checkSample=0.5 if sample else 1.0)
         out = []
         # rank 0 keeps the packed text cells of its chunks for pass 2, rank 1 transforms from the text: same rows
@@ -209,7 +209,7 @@ def _worker_streamed(rank, size, port, q, backend="gloo", sample=False):
              V.numeric_metadata(["r0"], "Real", True), V.numeric_metadata(["nn"], "RealNN", False),
              V.smart_text_metadata(tnames, "Text", methods, ttops, 512, True)])
         p = S.SanityParams(remove_bad_features=True, sample_lower_limit=0, sample_upper_limit=10 ** 9,
-                           feature_feature_corr_level="off")
+                           feature_feature_corr_level=corr.lower())
         rows = np.arange(n)
         if sample:          # SanityChecker looked at a row sample: every rank's sampled rows, gathered
             mine = np.concatenate([r.cpu().numpy() + a for r, a in zip(res.sample_rows, cuts[:-1])])
@@ -225,6 +225,9 @@ def _worker_streamed(rank, size, port, q, backend="gloo", sample=False):
         assert np.array_equal(est.summary.min, ref.col_stats.min) and np.array_equal(est.summary.max, ref.col_stats.max)
         np.testing.assert_allclose(est.summary.correlationsWithLabel, ref.corrs_with_label, rtol=1e-9, atol=1e-12,
                                    equal_nan=True)
+        if corr == "Computed":      # every rank's chunks add to its Gramian, the ranks' Gramians add
+            np.testing.assert_allclose(est.summary.featureFeatureCorr, ref.corr_matrix, rtol=1e-9, atol=1e-12,
+                                       equal_nan=True)
         got_g = {g.group: g for g in est.summary.categoricalStats}
         for g in ref.cat_stats:
             assert np.array_equal(got_g[g.group].contingencyMatrix, g.contingency_matrix)
@@ -252,6 +255,12 @@ def test_two_ranks_over_nccl_streamed_chunks_match_oracle():
 def test_two_ranks_streamed_chunks_sampled_sanity_checker_matches_oracle():
     """fraction() < 1 over streamed chunks on two ranks: the ranks' sample statistics merge in rank order."""
     _run(_worker_streamed, "gloo", True)
+
+
+@pytest.mark.parametrize("sample", [False, True])
+def test_two_ranks_streamed_chunks_full_correlation_matrix_matches_oracle(sample):
+    """CorrelationLevel.Computed over streamed chunks on two ranks (all rows, and a row sample)."""
+    _run(_worker_streamed, "gloo", sample, "Computed")
 
 
 def _worker_sampled(rank, size, port, q):
