@@ -697,6 +697,54 @@ int tmog_text_hash_transform_host(tmog_ctx* ctx, int ncols, int64_t n, const uin
                                   int64_t* indptr, int32_t* out_idx, int32_t* out_val, int64_t capacity,
                                   int64_t* nnz_out);
 
+/* ---- RawFeatureFilter ---------------------------------------------------------------------------
+ * Replaces the row maps and reduces of RawFeatureFilter.computeFeatureStats (C/filters/RawFeatureFilter.scala:138-200)
+ * for numeric (Real, RealNN, Integral, Binary), Text / TextArea and PickList features, one HBM-bound scan each.
+ * Layouts: values [ncols][ld] (dtype 0 = f64, 1 = int64, 2 = uint8), valid = Arrow bitmap words [ncols][ldv] or NULL.
+ * Every output ACCUMULATES (row chunks and GPUs add); the caller initialises it.
+ *
+ * _numeric_summary_dev: Summary of every column (C/filters/Summary.scala:43-65, PreparedFeatures.scala:52-53):
+ *   out [ncols][5] = min, max, sum, count, NaN seen (initialise to +Inf, -Inf, 0, 0, 0; java Math.min / max make a
+ *   NaN value the min AND the max: the caller applies that).
+ * _numeric_hist_dev: FeatureDistribution.histValues for Right(values) (C/filters/FeatureDistribution.scala:328-350) with
+ *   NumericBucketizer.bucketize (C/stages/impl/feature/NumericBucketizer.scala:219-264; Inclusion.Left, trackInvalid):
+ *   mode [col] 0 = the (training) summary is empty: value_sum [col] += v; 1 = min < max: hist [col][b] += 1 with b the
+ *   bucket of v among splits [col][bins] (tmog_rff_numeric_splits), bins - 1 for NaN, +-Inf and values outside;
+ *   2 = otherwise: hist [col][0] += (v == same_value [col]), hist [col][1] += (v != same_value [col]).
+ *   nonnull [col] += valid rows.  hist u64 [ncols][bins].
+ * _rows_hist_dev: FeatureDistribution.histValues for Left(tokens) (:317-321: HashingTF(bins).transform(tokens)) from the
+ *   sparse rows tmog_text_hash_transform_dev wrote with separate hash spaces of `bins` buckets per column (index =
+ *   column * bins + bucket; larger indices are ignored): hist [column * bins + bucket] += weight * tf; tok [col][3] =
+ *   min / max tokens of a non-empty cell, non-empty cells (initialise to INT64_MAX, -1, 0) -- the text Summary
+ *   (Summary.scala:61).  valid_ptrs: device array of the columns' bitmap pointers (0 = no empty cell) or NULL;
+ *   weight [n] or NULL: rows a row stands for (the rows are a dictionary's entries, weight = tmog_rff_code_count_dev).
+ * _code_count_dev: counts [col_off[col] + code] += 1 over dictionary codes [ncols][ld] (< 0 = empty); *bad is set when
+ *   a code is >= ncodes [col]; with y (f64 [n]) given, null_y [col] += sum of (y - shift) over the column's empty rows
+ *   (what _null_label_sums_dev yields for columns with a bitmap).
+ * _null_label_sums_dev: PreparedFeatures.getNullLabelLeakageVector (:62-70) summed: out [c] += sum of (y - shift) over
+ *   the rows where column c is empty (c < ncols), out [ncols] += sum (y - shift), out [ncols + 1] += sum (y - shift)^2;
+ *   an empty response (y_valid bit 0) counts as 0.0.
+ * Host: _numeric_splits (FeatureDistribution.scala:333-334, no fused multiply-add), _js_divergence (:154-163),
+ * _null_label_corr (Statistics.corr of [response, null indicators], RawFeatureFilter.scala:184-191: min(|corr|, 1),
+ * NaN where a variance is <= 1e-12) from the sums above (n rows, null_count / null_y_sum [ncols]). */
+int tmog_rff_numeric_summary_dev(const void* values, int dtype, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n,
+                                 int ncols, double* out, void* stream);
+int tmog_rff_numeric_hist_dev(const void* values, int dtype, int64_t ld, const uint64_t* valid, int64_t ldv, int64_t n,
+                              int ncols, int bins, const double* splits, const int32_t* mode, const double* same_value,
+                              uint64_t* hist, double* value_sum, uint64_t* nonnull, void* stream);
+int tmog_rff_rows_hist_dev(const int64_t* row_start, const int32_t* row_nnz, const int32_t* idx, const int32_t* val,
+                           int64_t n, int ncols, int bins, const uint64_t* const* valid_ptrs, const uint64_t* weight,
+                           uint64_t* hist, int64_t* tok, void* stream);
+int tmog_rff_code_count_dev(const int32_t* codes, int64_t ld, int64_t n, int ncols, const int64_t* col_off,
+                            const int64_t* ncodes, uint64_t* counts, int32_t* bad, const double* y,
+                            const uint64_t* y_valid, double shift, double* null_y, void* stream);
+int tmog_rff_null_label_sums_dev(const uint64_t* const* valid_ptrs, int ncols, int64_t n, const double* y,
+                                 const uint64_t* y_valid, double shift, double* out, void* stream);
+int tmog_rff_numeric_splits(double min, double max, int bins, double* out);
+int tmog_rff_js_divergence(const double* a, const double* b, int n, double* out);
+int tmog_rff_null_label_corr(double n, double y_sum, double y_sq_sum, int ncols, const double* null_count,
+                             const double* null_y_sum, double* out);
+
 /* ---- multi-GPU exchange ---------------------------------------------------------------------------------------------
  * Rows shard across GPUs; only the small results of a fit cross NVLink.  Replaces the reduce side of the reference's
  * aggregations: Aggregator.merge of SequenceAggregators (U/spark/SequenceAggregators.scala:83), the RDD.fold of

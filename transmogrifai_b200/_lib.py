@@ -123,6 +123,14 @@ _SIGNATURES: Dict[str, List] = {
     "tmog_text_hash_transform_host": [_p, _int, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i64, _p],
     "tmog_vector_export_count_dev": [_p, _int, _i64, _int, _p, _p, _p, _p, _p],
     "tmog_vector_export_write_dev": [_p, _int, _i64, _int, _p, _p, _p, _p, _p, _p],
+    "tmog_rff_numeric_summary_dev": [_p, _int, _i64, _p, _i64, _i64, _int, _p, _p],
+    "tmog_rff_numeric_hist_dev": [_p, _int, _i64, _p, _i64, _i64, _int, _int, _p, _p, _p, _p, _p, _p, _p],
+    "tmog_rff_rows_hist_dev": [_p, _p, _p, _p, _i64, _int, _int, _p, _p, _p, _p, _p],
+    "tmog_rff_code_count_dev": [_p, _i64, _i64, _int, _p, _p, _p, _p, _p, _p, _dbl, _p, _p],
+    "tmog_rff_null_label_sums_dev": [_p, _int, _i64, _p, _p, _dbl, _p, _p],
+    "tmog_rff_numeric_splits": [_dbl, _dbl, _int, _p],
+    "tmog_rff_js_divergence": [_p, _p, _int, _p],
+    "tmog_rff_null_label_corr": [_dbl, _dbl, _dbl, _int, _p, _p, _p],
     "tmog_comm_unique_id": [_p],
     "tmog_comm_init": [_p, _int, _int, _int, C.POINTER(_p)],
     "tmog_comm_destroy": [_p],
