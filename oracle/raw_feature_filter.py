@@ -253,7 +253,8 @@ def compute_feature_stats(columns: Dict[str, Tuple[str, Sequence]], responses: S
                 seq = prepared[nm][r]
                 if seq is not None:                                 # an empty feature has no entry in the row's map
                     out[(nm, None)] = out[(nm, None)].plus(summary_of(seq)) if (nm, None) in out else summary_of(seq)
-        return out
+        # the reference's order is a Scala Map's iteration order (unspecified beyond four keys): feature order here
+        return {(nm, None): out[(nm, None)] for nm in group if (nm, None) in out}
 
     if info is not None:
         rs, ps = info.response_summaries, info.predictor_summaries

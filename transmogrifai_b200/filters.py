@@ -271,3 +271,375 @@ class RawFeatureFilter:
                 "maxCorrelation": self.maxCorrelation, "correlationType": self.correlationType,
                 "jsDivergenceProtectedFeatures": sorted(self.jsDivergenceProtectedFeatures),
                 "protectedFeatures": sorted(self.protectedFeatures)}
+
+    # -- the scans (csrc/rff.cu; every method below queues kernels on the current stream) --------------------------------
+    _device = "cuda"
+
+    @staticmethod
+    def _dtype_code(t) -> int:
+        import torch
+        return {torch.float64: 0, torch.int64: 1, torch.uint8: 2}[t.dtype]
+
+    def _k_summary(self, sub, n: int, out) -> None:
+        """out [ncols][5] += Summary of every column of the numeric block `sub` (device)."""
+        from . import runtime as R
+        L.call("tmog_rff_numeric_summary_dev", sub.values.data_ptr(), self._dtype_code(sub.values), sub.values.stride(0),
+               R.ptr(sub.valid), 0 if sub.valid is None else sub.valid.stride(0), n, len(sub.names), out.data_ptr(),
+               R.stream())
+
+    def _k_hist(self, sub, n: int, splits, mode, same, hist, vsum, nonnull) -> None:
+        from . import runtime as R
+        L.call("tmog_rff_numeric_hist_dev", sub.values.data_ptr(), self._dtype_code(sub.values), sub.values.stride(0),
+               R.ptr(sub.valid), 0 if sub.valid is None else sub.valid.stride(0), n, len(sub.names), self.bins,
+               splits.data_ptr(), mode.data_ptr(), same.data_ptr(), hist.data_ptr(), vsum.data_ptr(),
+               nonnull.data_ptr(), R.stream())
+
+    def _k_text_rows(self, sub, n: int):
+        """Tokenise + hash the text columns of `sub` (device TextBlock) into separate spaces of `bins` buckets
+        (TextTokenizer.Analyzer.analyze, PreparedFeatures.scala:201; HashingTF(bins), FeatureDistribution.scala:317-320)
+        -> sparse rows (row_start, row_nnz, idx, val) with index = column * bins + bucket."""
+        import torch
+        from . import runtime as R
+        from .stages.smart_text import _check_hash_flags, _col_desc
+        k, bins = len(sub.names), self.bins
+        params = np.array([bins, 0, 0, 1, 1, 0, k * bins, 1, 0, 0, 0, 0], dtype=np.int32)
+        prefix = torch.zeros((k, 16), dtype=torch.uint8, device="cuda")
+        plen = torch.zeros(k, dtype=torch.int32, device="cuda")
+        newpos = torch.from_numpy(np.concatenate([np.arange(k * bins), np.full(k, -1)]).astype(np.int32)).cuda()
+        desc = _col_desc(sub)
+        need = C.c_size_t(0)
+        if bins <= 512:
+            L.call("tmog_text_hash_scratch_bytes2", n, k, params.ctypes.data, 1, C.byref(need))
+        else:
+            L.call("tmog_text_hash_scratch_bytes", n, C.byref(need))
+        scratch = torch.empty(max(need.value, 8), dtype=torch.uint8, device="cuda")
+        row_start = torch.empty(max(n, 1), dtype=torch.int64, device="cuda")
+        row_nnz = torch.empty(max(n, 1), dtype=torch.int32, device="cuda")
+        cursor = torch.zeros(1, dtype=torch.int64, device="cuda")
+        flags = torch.zeros(4, dtype=torch.int32, device="cuda")
+        args = (desc.data_ptr(), k, n, prefix.data_ptr(), plen.data_ptr(), params.ctypes.data, newpos.data_ptr(),
+                row_start.data_ptr(), row_nnz.data_ptr())
+        L.call("tmog_text_hash_transform_dev", *args, None, None, cursor.data_ptr(), 0, flags.data_ptr(),
+               scratch.data_ptr(), scratch.numel(), R.stream())                      # sizing pass
+        capacity = int(cursor.item())
+        cursor.zero_()
+        flags[3] = 0
+        idx = torch.empty(max(capacity, 1), dtype=torch.int32, device="cuda")
+        val = torch.empty(max(capacity, 1), dtype=torch.int32, device="cuda")
+        L.call("tmog_text_hash_transform_dev", *args, idx.data_ptr(), val.data_ptr(), cursor.data_ptr(), capacity,
+               flags.data_ptr(), scratch.data_ptr(), scratch.numel(), R.stream())
+        _check_hash_flags(flags)
+        return row_start, row_nnz, idx, val
+
+    def _k_rows_hist(self, rows, n: int, ncols: int, valid_ptrs, weight, hist, tok) -> None:
+        from . import runtime as R
+        row_start, row_nnz, idx, val = rows
+        L.call("tmog_rff_rows_hist_dev", row_start.data_ptr(), row_nnz.data_ptr(), idx.data_ptr(), val.data_ptr(), n,
+               ncols, self.bins, R.ptr(valid_ptrs), R.ptr(weight), hist.data_ptr(), tok.data_ptr(), R.stream())
+
+    def _k_code_count(self, sub, n: int, col_off, ncodes, counts, bad, y, y_valid, shift: float, null_y) -> None:
+        from . import runtime as R
+        L.call("tmog_rff_code_count_dev", sub.codes.data_ptr(), sub.codes.stride(0), n, len(sub.names),
+               col_off.data_ptr(), ncodes.data_ptr(), counts.data_ptr(), bad.data_ptr(), R.ptr(y), R.ptr(y_valid),
+               float(shift), R.ptr(null_y), R.stream())
+
+    def _k_null_label(self, valid_ptrs, ncols: int, n: int, y, y_valid, shift: float, out) -> None:
+        from . import runtime as R
+        L.call("tmog_rff_null_label_sums_dev", R.ptr(valid_ptrs), ncols, n, y.data_ptr(), R.ptr(y_valid), float(shift),
+               out.data_ptr(), R.stream())
+
+    @staticmethod
+    def _groups(chunk, feats: Sequence[F.Feature]):
+        """The chunk's blocks that hold wanted features: [(block, columns inside the block, positions in `feats`)]."""
+        by_block: Dict[int, list] = {}
+        for i, f in enumerate(feats):
+            b, c = chunk.find(f.name)
+            by_block.setdefault(id(b), [b, [], []])
+            by_block[id(b)][1].append(c)
+            by_block[id(b)][2].append(i)
+        return [tuple(v) for v in by_block.values()]
+
+    def _dict_rows(self, cache: dict, block, col: int):
+        """The hashed rows of a dictionary's entries (every entry tokenised once per dictionary object)."""
+        import torch
+        from .columnar import TextBlock
+        d = block.dicts[col]
+        hit = cache.get(id(d))
+        if hit is None or hit[0] is not d:
+            data, offsets = block.dict_arrays(col)
+            buf = torch.zeros(len(data) + 16, dtype=torch.uint8, device=self._device)
+            if len(data):
+                buf[:len(data)] = torch.from_numpy(np.ascontiguousarray(data)).to(self._device)
+            entries = TextBlock(["dictionary"], F.TEXT, [buf],
+                                [torch.from_numpy(np.ascontiguousarray(offsets)).to(self._device)], [None], len(d))
+            hit = (d, self._k_text_rows(entries, len(d)) if len(d) else None)
+            cache[id(d)] = hit
+        return hit[1]
+
+    def computeFeatureStats(self, data, features: Sequence[F.Feature],  # noqa: N802
+                            featureDistributionType: str = "Training",  # noqa: N803
+                            allFeatureInfo: Optional[AllFeatureInformation] = None  # noqa: N803
+                            ) -> AllFeatureInformation:
+        """RawFeatureFilter.computeFeatureStats (:138-200).  data: a ColumnarBatch, or a list of row chunks (read twice
+        for training data: summaries, then distributions); with several ranks every rank passes its own rows."""
+        import torch
+        from . import dist as D
+        from . import runtime as R
+        from .columnar import ColumnarBatch, DictBlock, NumericBlock, TextBlock
+        R.require_cuda()
+        dev = self._device
+        chunks = [data] if isinstance(data, ColumnarBatch) else data
+        bins = self.bins
+        resp = [f for f in features if f.isResponse and f.type_name in F.NUMERIC_TYPES]      # :146-155
+        pred = [f for f in features if not f.isResponse]
+        feats = list(resp) + list(pred)
+        for f in feats:
+            if f.type_name not in F.NUMERIC_TYPES + F.TEXT_TYPES + (F.PICKLIST,):
+                raise RuntimeError(f"Feature type {f.type_name} is not supported in RawFeatureFilter")
+        k, nr = len(feats), len(resp)
+        training = allFeatureInfo is None
+        is_num = np.array([f.type_name in F.NUMERIC_TYPES for f in feats], dtype=bool)
+
+        def device_block(block):
+            return block if block.is_cuda else block.to(dev)
+
+        # ---- pass A: the numeric Summaries (training data only: scoring data are binned over the training summaries)
+        summ = np.tile(np.array([np.inf, -np.inf, 0.0, 0.0, 0.0]), (k, 1))
+        if training:
+            d_summ = torch.from_numpy(summ.copy()).to(dev)
+            for chunk in chunks:
+                for block, cols, at in self._groups(chunk, feats):
+                    if not isinstance(block, NumericBlock) or chunk.n == 0:
+                        continue
+                    sub = device_block(block).rows(cols)
+                    tmp = d_summ[at].contiguous()
+                    self._k_summary(sub, chunk.n, tmp)
+                    d_summ[at] = tmp
+            parts = D.all_gather_object(d_summ.cpu().numpy())
+            summ = parts[0].copy()
+            for p in parts[1:]:
+                summ[:, 0] = np.minimum(summ[:, 0], p[:, 0])
+                summ[:, 1] = np.maximum(summ[:, 1], p[:, 1])
+                summ[:, 2:4] += p[:, 2:4]
+                summ[:, 4] = np.maximum(summ[:, 4], p[:, 4])
+            nan = summ[:, 4] > 0                         # java Math.min / max: one NaN value makes both NaN
+            summ[nan, 0] = summ[nan, 1] = np.nan
+        else:
+            known = dict(allFeatureInfo.responseSummaries)
+            known.update(allFeatureInfo.predictorSummaries)
+            for i, f in enumerate(feats):
+                s = known.get((f.name, None))
+                if s is not None:
+                    summ[i, :4] = [s.min, s.max, s.sum, s.count]
+        # ---- how every numeric feature is binned (FeatureDistribution.scala:328-350)
+        splits = np.zeros((k, bins))
+        mode = np.full(k, 2, dtype=np.int32)
+        same = np.zeros(k)
+        for i in np.nonzero(is_num)[0]:
+            mn, mx = summ[i, 0], summ[i, 1]
+            if mn < mx:
+                mode[i] = 1
+                L.call("tmog_rff_numeric_splits", float(mn), float(mx), bins, splits[i].ctypes.data)
+            else:
+                same[i] = mx
+        d_splits, d_mode, d_same = (torch.from_numpy(a).to(dev) for a in (splits, mode, same))
+        # ---- pass B: distributions, empty cells, and (training) the response summed over every predictor's empty rows
+        hist = torch.zeros((k, bins), dtype=torch.int64, device=dev)
+        vsum = torch.zeros(k, dtype=torch.float64, device=dev)
+        nonnull = torch.zeros(k, dtype=torch.int64, device=dev)
+        tok = torch.tensor([[np.iinfo(np.int64).max, -1, 0]] * max(k, 1), dtype=torch.int64, device=dev)[:k]
+        bad = torch.zeros(1, dtype=torch.int32, device=dev)
+        shifts = [summ[i, 2] / summ[i, 3] if summ[i, 3] > 0 and np.isfinite(summ[i, 2]) else 0.0 for i in range(nr)]
+        nl = torch.zeros((max(nr, 1), k + 2), dtype=torch.float64, device=dev)
+        dict_cache: dict = {}
+        n_local = 0
+        for chunk in chunks:
+            n = chunk.n
+            n_local += n
+            if n == 0:
+                continue
+            groups = [(device_block(b), cols, at) for b, cols, at in self._groups(chunk, feats)]
+            ys = []
+            if training:
+                for f in resp:                            # the response as f64, an empty one counting as 0.0 (:63-66)
+                    b, c = chunk.find(f.name)
+                    b = device_block(b)
+                    ys.append((b.values[c].to(torch.float64), None if b.valid is None else b.valid[c].contiguous()))
+            vptr = np.zeros(k, dtype=np.int64)
+            for block, cols, at in groups:
+                m = len(cols)
+                if isinstance(block, NumericBlock):
+                    sub = block.rows(cols)
+                    h = torch.zeros((m, bins), dtype=torch.int64, device=dev)
+                    vs, nn = vsum[at].contiguous(), nonnull[at].contiguous()
+                    self._k_hist(sub, n, d_splits[at].contiguous(), d_mode[at].contiguous(), d_same[at].contiguous(), h,
+                                 vs, nn)
+                    hist[at] += h
+                    vsum[at], nonnull[at] = vs, nn
+                    if block.valid is not None:
+                        for c, i in zip(cols, at):
+                            vptr[i] = block.valid[c].data_ptr()
+                elif isinstance(block, TextBlock):
+                    sub = block.rows(cols)
+                    rows = self._k_text_rows(sub, n)
+                    ptrs = np.array([0 if v is None else v.data_ptr() for v in sub.valid], dtype=np.int64)
+                    d_ptrs = torch.from_numpy(ptrs).to(dev)
+                    h = torch.zeros(m * bins, dtype=torch.int64, device=dev)
+                    t = tok[at].contiguous()
+                    self._k_rows_hist(rows, n, m, d_ptrs, None, h, t)
+                    hist[at] += h.view(m, bins)
+                    tok[at] = t
+                    for p, i in zip(ptrs, at):
+                        vptr[i] = p
+                elif isinstance(block, DictBlock):
+                    sub = block.rows(cols)
+                    sizes = np.array([len(d) for d in sub.dicts], dtype=np.int64)
+                    offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+                    d_off, d_sizes = torch.from_numpy(offs[:-1].copy()).to(dev), torch.from_numpy(sizes).to(dev)
+                    counts = torch.zeros(max(int(offs[-1]), 1), dtype=torch.int64, device=dev)
+                    for r in range(max(len(ys), 1)):      # the codes are counted once; every response has its own sums
+                        y, yv = ys[r] if ys else (None, None)
+                        ny = torch.zeros(m, dtype=torch.float64, device=dev) if ys else None
+                        self._k_code_count(sub, n, d_off, d_sizes, counts if r == 0 else torch.zeros_like(counts), bad, y,
+                                           yv, shifts[r] if ys else 0.0, ny)
+                        if ys:
+                            nl[r, at] += ny
+                    for j, i in enumerate(at):
+                        if sizes[j] == 0:
+                            continue
+                        rows = self._dict_rows(dict_cache, sub, j)
+                        h = torch.zeros(bins, dtype=torch.int64, device=dev)
+                        t = tok[i:i + 1].contiguous()
+                        self._k_rows_hist(rows, int(sizes[j]), 1, None, counts[offs[j]:offs[j + 1]].contiguous(), h, t)
+                        hist[i] += h
+                        tok[i:i + 1] = t
+                else:
+                    raise RuntimeError(f"{type(block).__name__} columns are not supported in RawFeatureFilter")
+            if ys:
+                d_vptr = torch.from_numpy(vptr).to(dev)
+                for r, (y, yv) in enumerate(ys):
+                    out = torch.zeros(k + 2, dtype=torch.float64, device=dev)
+                    self._k_null_label(d_vptr, k, n, y, yv, shifts[r], out)
+                    nl[r] += out
+            del groups, ys
+        if int(bad.item()):
+            raise ValueError("a dictionary code beyond its dictionary")
+        # the text / PickList cells that hold a value: counted by the row kernel
+        is_tok = ~is_num
+        if is_tok.any():
+            sel = torch.from_numpy(np.nonzero(is_tok)[0]).to(dev)
+            nonnull[sel] = tok[sel, 2]
+        # ---- the ranks' sums add
+        n_all = int(D.allreduce_sum(np.array([n_local], dtype=np.int64))[0])
+        h_hist = D.allreduce_sum(hist.cpu().numpy())
+        h_nonnull = D.allreduce_sum(nonnull.cpu().numpy())
+        h_nl = D.allreduce_sum(nl.cpu().numpy())
+        h_tok = tok.cpu().numpy()
+        if D.world()[1] > 1:
+            parts = D.all_gather_object(h_tok)
+            h_tok = parts[0].copy()
+            for p in parts[1:]:
+                h_tok[:, 0] = np.minimum(h_tok[:, 0], p[:, 0])
+                h_tok[:, 1] = np.maximum(h_tok[:, 1], p[:, 1])
+        return self._assemble(feats, nr, is_num, summ, splits, mode, h_hist, h_nonnull, h_tok, h_nl, n_all,
+                              featureDistributionType, allFeatureInfo)
+
+    def _assemble(self, feats, nr: int, is_num, summ, splits, mode, hist, nonnull, tok, nl, n_all: int, type_: str,
+                  info: Optional[AllFeatureInformation]) -> AllFeatureInformation:
+        """What the reduce of the per-row FeatureDistributions leaves (FeatureDistribution.scala:107-122, :217-248):
+        a feature that is empty in every training row has no Summary and therefore no distribution at all."""
+        bins = self.bins
+        training = info is None
+        if training:
+            summaries: Dict[FeatureKey, Summary] = {}
+            for i, f in enumerate(feats):
+                if is_num[i]:
+                    if summ[i, 3] > 0:
+                        summaries[(f.name, None)] = Summary(*[float(v) for v in summ[i, :4]])
+                elif nonnull[i] > 0:
+                    summaries[(f.name, None)] = Summary(float(tok[i, 0]), float(tok[i, 1]), float(hist[i].sum()),
+                                                        float(nonnull[i]))
+        else:
+            summaries = dict(info.responseSummaries)
+            summaries.update(info.predictorSummaries)
+        dists: Dict[FeatureKey, FeatureDistribution] = {}
+        for i, f in enumerate(feats):
+            s = summaries.get((f.name, None))
+            if s is None:
+                continue
+            nulls = int(n_all - nonnull[i])
+            info4 = s.as_array()
+            dist = hist[i].astype(np.float64)
+            summary_info = info4
+            if is_num[i]:
+                if mode[i] == 1:
+                    # the rows' summaryInfo: the splits for a row with a value, [min, max, sum, count] for an empty
+                    # one; the reduce keeps the longer array (on a tie -- bins = 4 -- the later row's: the splits here)
+                    if nonnull[i] > 0 and (bins >= 4 or nulls == 0):
+                        summary_info = splits[i].copy()
+                else:
+                    # [same, other]: two entries, padded to `bins` by the array monoid once an empty row joins in
+                    dist = dist[:2] if nulls == 0 else dist
+            dists[(f.name, None)] = FeatureDistribution(f.name, None, n_all, nulls, dist, summary_info, type_)
+        rkeys = [(f.name, None) for f in feats[:nr] if (f.name, None) in dists]
+        pkeys = [(f.name, None) for f in feats[nr:] if (f.name, None) in dists]
+        if training:
+            at = {(f.name, None): i for i, f in enumerate(feats)}
+            corr_info: Dict[FeatureKey, Dict[FeatureKey, float]] = {}
+            for rk in rkeys:
+                r = at[rk]
+                cols = [at[pk] for pk in pkeys]
+                null_count = np.ascontiguousarray((n_all - nonnull[cols]).astype(np.float64))
+                null_y = np.ascontiguousarray(nl[r, cols].astype(np.float64))
+                out = np.zeros(len(cols))
+                L.call("tmog_rff_null_label_corr", float(n_all), float(nl[r, len(feats)]), float(nl[r, len(feats) + 1]),
+                       len(cols), null_count.ctypes.data, null_y.ctypes.data, out.ctypes.data)
+                corr_info[rk] = {pk: float(out[j]) for j, pk in enumerate(pkeys)}
+        else:
+            corr_info = info.correlationInfo
+        return AllFeatureInformation({k_: summaries[k_] for k_ in rkeys}, [dists[k_] for k_ in rkeys],
+                                     {k_: summaries[k_] for k_ in pkeys}, [dists[k_] for k_ in pkeys], corr_info)
+
+    def generateFilteredRaw(self, trainData, rawFeatures: Sequence[F.Feature], scoreData=None) -> FilteredRawData:  # noqa: N802,N803
+        """RawFeatureFilter.generateFilteredRaw (:482-566): the readers' data frames are the arguments here.  The
+        cleaned data are the training batch (or chunks) without the dropped features' columns."""
+        from . import dist as D
+        from .columnar import ColumnarBatch
+
+        def rows_of(data) -> int:
+            local = data.n if isinstance(data, ColumnarBatch) else sum(c.n for c in data)
+            return int(D.allreduce_sum(np.array([local], dtype=np.int64))[0])
+
+        if rows_of(trainData) <= 0:
+            raise ValueError("requirement failed: RawFeatureFilter cannot work with empty training data")
+        training = self.computeFeatureStats(trainData, rawFeatures, "Training")
+        scoring = None
+        if scoreData is not None and rows_of(scoreData) >= self.minScoringRows:
+            scoring = self.computeFeatureStats(scoreData, rawFeatures, "Scoring", training)
+        keep = lambda ds: [d for d in ds if d.name not in self.protectedFeatures]   # noqa: E731
+        metrics, reasons, to_drop, to_drop_keys = self.getFeaturesToExclude(
+            keep(training.predictorDistributions), keep(scoring.predictorDistributions) if scoring is not None else [],
+            training.correlationInfo)
+        features_to_drop = [f for f in rawFeatures if f.name in to_drop]
+        features_to_keep = [f for f in rawFeatures if f.name not in to_drop]
+        if not any(not f.isResponse for f in features_to_keep):
+            raise ValueError("requirement failed: The raw feature filter has dropped all of your features, check your "
+                             "input data quality")
+        dropped = set(to_drop)
+
+        def clean(batch: ColumnarBatch) -> ColumnarBatch:
+            blocks = []
+            for b in batch.blocks:
+                left = [i for i, nm in enumerate(b.names) if nm not in dropped]
+                if len(left) == len(b.names):
+                    blocks.append(b)
+                elif left:
+                    blocks.append(b.rows(left))
+            return ColumnarBatch(batch.n, blocks, {}, batch.response)
+
+        cleaned = clean(trainData) if isinstance(trainData, ColumnarBatch) else [clean(c) for c in trainData]
+        distributions = training.responseDistributions + training.predictorDistributions
+        if scoring is not None:
+            distributions = distributions + scoring.responseDistributions + scoring.predictorDistributions
+        results = RawFeatureFilterResults(self.config(), distributions, metrics, reasons)
+        return FilteredRawData(cleaned, features_to_drop, to_drop_keys, results)
