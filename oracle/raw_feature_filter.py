@@ -185,7 +185,7 @@ def hist_values(seq: ProcessedSeq, summary: Summary, bins: int, text_bins_formul
     if summary.is_empty():
         return [summary.min, summary.max], [float(x) for x in v]
     if summary.min < summary.max:
-        step = (summary.max - summary.min) / (bins - 2.0)
+        step = _div(summary.max - summary.min, bins - 2.0)            # bins = 2: x / 0.0 = Infinity on the JVM
         splits = [summary.min + step * b for b in range(bins)]
         hist = [0.0] * bins
         for x in v:

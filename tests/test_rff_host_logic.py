@@ -208,7 +208,7 @@ def check_info(got, exp, n):
             assert (np.isnan(e) and np.isnan(g)) or abs(g - e) < 1e-9, (rk, pk, g, e)
 
 
-@pytest.mark.parametrize("bins,sizes", [(10, [300]), (100, [100, 1, 150, 49]), (3, [120, 180])])
+@pytest.mark.parametrize("bins,sizes", [(10, [300]), (100, [100, 1, 150, 49]), (3, [120, 180]), (2, [90, 30])])
 def test_feature_stats_and_exclusions_match_the_oracle(monkeypatch, bins, sizes):
     from transmogrifai_b200.filters import RawFeatureFilter
     n = sum(sizes)
