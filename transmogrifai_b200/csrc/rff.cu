@@ -64,14 +64,28 @@ rff_numeric_summary_kernel(const void* __restrict__ values, int64_t ld, const un
     const T* x = static_cast<const T*>(values) + (int64_t)col * ld;
     const unsigned long long* v = valid ? valid + (int64_t)col * ldv : nullptr;
     double mn = INFINITY, mx = -INFINITY, sum = 0.0, cnt = 0.0, nan = 0.0;
-    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
-        if (!rff_valid(v, r)) continue;
-        const double d = (double)x[r];
-        if (d != d) nan = 1.0;
-        mn = fmin(mn, d);
-        mx = fmax(mx, d);
-        sum += d;
-        cnt += 1.0;
+    // a block's rows: a contiguous stretch; four loads in flight per thread (HBM latency x bandwidth needs ~40 KB per SM)
+    const int64_t per = (n + gridDim.x - 1) / gridDim.x;
+    const int64_t r0 = (int64_t)blockIdx.x * per, r1 = r0 + per < n ? r0 + per : n;
+    for (int64_t base = r0 + threadIdx.x; base < r1; base += 4 * RFF_THREADS) {
+        T raw[4];
+        bool ok[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t r = base + (int64_t)u * RFF_THREADS;
+            ok[u] = r < r1 && rff_valid(v, r);
+            raw[u] = ok[u] ? x[r] : T(0);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (!ok[u]) continue;
+            const double d = (double)raw[u];
+            if (d != d) nan = 1.0;
+            mn = fmin(mn, d);
+            mx = fmax(mx, d);
+            sum += d;
+            cnt += 1.0;
+        }
     }
     mn = warp_min(mn);
     mx = warp_max(mx);
@@ -136,26 +150,52 @@ rff_numeric_hist_kernel(const void* __restrict__ values, int64_t ld, const unsig
     // a block's rows: a contiguous stretch (at most 2^32 - 1 rows, so that the shared u32 counts cannot wrap)
     const int64_t per = (n + gridDim.x - 1) / gridDim.x;
     const int64_t r0 = (int64_t)blockIdx.x * per, r1 = r0 + per < n ? r0 + per : n;
-    for (int64_t r = r0 + threadIdx.x; r < r1; r += blockDim.x) {
-        if (!rff_valid(v, r)) continue;
-        const double d = (double)x[r];
-        ++cnt;
-        int b;
-        if (md == 1) {
-            int lo = 0, hi = bins;                     // first index with splits[i] > d (or not <= d: NaN)
-            while (lo < hi) {
-                const int mid = (lo + hi) >> 1;
-                if (lookup[mid] <= d) lo = mid + 1; else hi = mid;
-            }
-            b = lo - 1;
-            if (b < 0 || b >= bins - 1 || isinf(d)) b = bins - 1;
-        } else if (md == 2) {
-            b = d == same ? 0 : 1;
-        } else {
-            vsum += d;
-            continue;
+    // the bucket is guessed from (d - min) / step and corrected against the splits themselves (the splits decide, so
+    // the result is the reference's); a column whose step is not a positive finite number is searched instead
+    const double lo0 = lookup[0];
+    const double inv = md == 1 ? (double)(bins - 2) / (lookup[bins - 2 > 0 ? bins - 2 : 0] - lo0) : 0.0;
+    const bool guess = md == 1 && bins > 2 && inv > 0.0 && !isinf(inv) && !isinf(lo0) && lo0 == lo0;
+    for (int64_t base = r0 + threadIdx.x; base < r1; base += 4 * RFF_THREADS) {
+        T raw[4];
+        bool ok[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t r = base + (int64_t)u * RFF_THREADS;
+            ok[u] = r < r1 && rff_valid(v, r);
+            raw[u] = ok[u] ? x[r] : T(0);
         }
-        if (SMEM) atomicAdd(&s_hist[b], 1u); else atomicAdd(&gh[b], 1ull);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (!ok[u]) continue;
+            const double d = (double)raw[u];
+            ++cnt;
+            int b;
+            if (md == 1) {
+                if (d != d || isinf(d)) {
+                    b = bins - 1;
+                } else if (guess) {
+                    const double q = (d - lo0) * inv;
+                    int g = q > 0.0 ? (q < (double)(bins - 1) ? (int)q : bins - 1) : 0;
+                    while (g > 0 && d < lookup[g]) --g;
+                    while (g < bins - 1 && lookup[g + 1] <= d) ++g;
+                    b = (g >= bins - 1 || d < lookup[g]) ? bins - 1 : g;
+                } else {
+                    int lo = 0, hi = bins;                 // first index with splits[i] > d (or not <= d: NaN)
+                    while (lo < hi) {
+                        const int mid = (lo + hi) >> 1;
+                        if (lookup[mid] <= d) lo = mid + 1; else hi = mid;
+                    }
+                    b = lo - 1;
+                    if (b < 0 || b >= bins - 1) b = bins - 1;
+                }
+            } else if (md == 2) {
+                b = d == same ? 0 : 1;
+            } else {
+                vsum += d;
+                continue;
+            }
+            if (SMEM) atomicAdd(&s_hist[b], 1u); else atomicAdd(&gh[b], 1ull);
+        }
     }
     cnt = __reduce_add_sync(FULL, cnt);
     vsum = warp_sum(vsum);
@@ -325,8 +365,9 @@ rff_null_label_kernel(const unsigned long long* const* __restrict__ valid_ptrs, 
 }  // namespace
 
 static int rff_grid_x(int64_t n, int ncols, int per_thread) {
-    // enough blocks per column to fill the SMs a few times over, never more than the rows need
-    const int64_t want = std::max<int64_t>(1, ((int64_t)sm_count() * 8 + ncols - 1) / std::max(ncols, 1));
+    // one wave: as many blocks per column as fit the SMs' resident slots (8 blocks of 256 threads per SM) -- one block
+    // more per column would leave a second, nearly empty wave -- and never more than the rows need
+    const int64_t want = std::max<int64_t>(1, ((int64_t)sm_count() * 8) / std::max(ncols, 1));
     const int64_t need = std::max<int64_t>(1, (n + (int64_t)RFF_THREADS * per_thread - 1) / ((int64_t)RFF_THREADS * per_thread));
     return (int)std::min<int64_t>(std::min(want, need), 65535);
 }
