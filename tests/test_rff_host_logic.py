@@ -263,3 +263,63 @@ def test_too_few_scoring_rows_and_requirements(monkeypatch):
     only_sparse = {k: v for k, v in train.items() if k in ("y", "r0", "t1")}
     with pytest.raises(ValueError, match="dropped all of your features"):
         g.generateFilteredRaw(chunked(only_sparse, [200])[0], features_of(only_sparse))
+
+
+def _rank_worker(rank, size, port, q):
+    """Every rank passes its own rows (two chunks each); the summaries merge and the sums add (gloo, CPU)."""
+    import os
+    import types
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=size)
+    try:
+        from transmogrifai_b200 import runtime as R
+        from transmogrifai_b200.filters import RawFeatureFilter
+
+        class _Patch:
+            def setattr(self, obj, name, value):
+                setattr(obj, name, value)
+
+        n, bins = 400, 20
+        train, score = make_data(n, 13), make_data(n, 14, shift=True)
+        feats = features_of(train)
+        f = emulate(RawFeatureFilter(bins=bins, minFill=0.2, maxFillDifference=0.3, maxFillRatioDiff=2.0,
+                                     maxJSDivergence=0.5, maxCorrelation=0.6, minScoringRows=10), _Patch())
+        lo, hi = (0, 150) if rank == 0 else (150, n)
+        mine = lambda cols: chunked({k: (t, v[lo:hi]) for k, (t, v) in cols.items()},   # noqa: E731
+                                    [(hi - lo) // 3, (hi - lo) - (hi - lo) // 3])
+        got_t = f.computeFeatureStats(mine(train), feats, "Training")
+        exp_t = O.compute_feature_stats(train, ["y"], bins, "Training")
+        check_info(got_t, exp_t, n)
+        got_s = f.computeFeatureStats(mine(score), feats, "Scoring", got_t)
+        check_info(got_s, O.compute_feature_stats(score, ["y"], bins, "Scoring", exp_t), n)
+        out = f.generateFilteredRaw(mine(train), feats, mine(score))
+        p = O.FilterParams(bins=bins, min_fill=0.2, max_fill_difference=0.3, max_fill_ratio_diff=2.0,
+                           max_js_divergence=0.5, max_correlation=0.6, min_scoring_rows=10)
+        drop = O.generate_filtered_raw(train, score, ["y"], p)[4]
+        assert sorted(x.name for x in out.featuresToDrop) == sorted(drop)
+        q.put((rank, "ok"))
+    except Exception:  # pragma: no cover
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_add_up(tmp_path):
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_rank_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, "ok"), (1, "ok")], "\n".join(str(r[1]) for r in res)
