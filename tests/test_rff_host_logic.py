@@ -165,6 +165,8 @@ def make_data(n, seed, shift=False):
                         for _ in range(n)]),
         "t1": (F.TEXT, [opt(["red", "Green", "blue!", ""][int(rng.integers(4))], 0.5) for _ in range(n)]),
         "p0": (F.PICKLIST, [opt(["x", "y z", "Z", "w-w", ""][int(rng.integers(5))], 0.25) for _ in range(n)]),
+        "m0": (F.MULTIPICKLIST, [opt([["a b", "c", "D.", "e", "a b"][int(k)] for k in rng.integers(0, 5, rng.integers(0, 4))],
+                                     0.2) for _ in range(n)]),
     }
     return cols
 

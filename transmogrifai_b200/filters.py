@@ -12,7 +12,7 @@ null-indicator / response correlation.  What is left for the host is what the re
 exclusion reasons, the names to drop.
 
 Covered feature types: Real, RealNN, Integral (Date, DateTime as plain numbers: timePeriod = None), Binary, Text,
-TextArea, PickList.  Not covered (raise): maps, MultiPickList, lists, geolocations, vectors, a custom textBinsFormula,
+TextArea, PickList, MultiPickList.  Not covered (raise): maps, lists, geolocations, vectors, a custom textBinsFormula,
 timePeriod.  Not produced: FeatureDistribution.moments / cardEstimate (reported by the reference, read by no rule).
 Order of the distributions: responses, then predictors, in the order of `features` (the reference's is the iteration
 order of a Scala Map: unspecified beyond four features).
@@ -376,6 +376,20 @@ class RawFeatureFilter:
             cache[id(d)] = hit
         return hit[1]
 
+    def _set_dict_rows(self, cache: dict, d: list):
+        """One sparse row per dictionary value of a MultiPickList column: (HashingTF bucket of the whole value, 1)."""
+        import torch
+        from .stages.smart_text import murmur3_index
+        hit = cache.get(("set", id(d)))
+        if hit is None or hit[0] is not d:
+            m = len(d)
+            buckets = np.array([murmur3_index(v, self.bins) for v in d], dtype=np.int32)
+            mk = lambda a: torch.from_numpy(a).to(self._device)   # noqa: E731
+            hit = (d, (mk(np.arange(m, dtype=np.int64)), mk(np.ones(m, dtype=np.int32)), mk(buckets),
+                       mk(np.ones(m, dtype=np.int32))))
+            cache[("set", id(d))] = hit
+        return hit[1]
+
     def computeFeatureStats(self, data, features: Sequence[F.Feature],  # noqa: N802
                             featureDistributionType: str = "Training",  # noqa: N803
                             allFeatureInfo: Optional[AllFeatureInformation] = None  # noqa: N803
@@ -385,7 +399,7 @@ class RawFeatureFilter:
         import torch
         from . import dist as D
         from . import runtime as R
-        from .columnar import ColumnarBatch, DictBlock, NumericBlock, TextBlock
+        from .columnar import ColumnarBatch, DictBlock, NumericBlock, SetBlock, TextBlock
         R.require_cuda()
         dev = self._device
         chunks = [data] if isinstance(data, ColumnarBatch) else data
@@ -394,7 +408,7 @@ class RawFeatureFilter:
         pred = [f for f in features if not f.isResponse]
         feats = list(resp) + list(pred)
         for f in feats:
-            if f.type_name not in F.NUMERIC_TYPES + F.TEXT_TYPES + (F.PICKLIST,):
+            if f.type_name not in F.NUMERIC_TYPES + F.TEXT_TYPES + (F.PICKLIST, F.MULTIPICKLIST):
                 raise RuntimeError(f"Feature type {f.type_name} is not supported in RawFeatureFilter")
         k, nr = len(feats), len(resp)
         training = allFeatureInfo is None
@@ -513,6 +527,38 @@ class RawFeatureFilter:
                         self._k_rows_hist(rows, int(sizes[j]), 1, None, counts[offs[j]:offs[j + 1]].contiguous(), h, t)
                         hist[i] += h
                         tok[i:i + 1] = t
+                elif isinstance(block, SetBlock):
+                    # MultiPickList: Left(values), hashed whole (PreparedFeatures.scala:179); an empty set is an empty
+                    # feature.  Rows per dictionary code by the count kernel over the flat code list, then every
+                    # dictionary entry's bucket weighted by its count; set sizes are the "token" counts
+                    sub = block.rows(cols)
+                    totals = torch.stack([o[n] for o in sub.offsets]).cpu().numpy()
+                    big = int(np.iinfo(np.int64).max)
+                    for j, i in enumerate(at):
+                        d = sub.dicts[j]
+                        sizes = sub.offsets[j][1:n + 1] - sub.offsets[j][:n]
+                        filled = sizes > 0
+                        tok[i, 0] = torch.minimum(tok[i, 0], torch.where(filled, sizes, big).min())
+                        tok[i, 1] = torch.maximum(tok[i, 1], torch.where(filled, sizes, -1).max())
+                        tok[i, 2] += filled.sum()
+                        for r, (y, yv) in enumerate(ys):
+                            yy = y[:n]
+                            if yv is not None:
+                                rows_i = torch.arange(n, device=dev)
+                                yy = torch.where(((yv[rows_i >> 6] >> (rows_i & 63)) & 1) != 0, yy, torch.zeros_like(yy))
+                            nl[r, i] += ((yy - shifts[r]) * (~filled)).sum()
+                        total = int(totals[j])
+                        if total == 0 or len(d) == 0:
+                            continue
+                        flat = DictBlock([sub.names[j]], sub.type_name, sub.codes[j][:total].view(1, total), [d], total)
+                        counts = torch.zeros(len(d), dtype=torch.int64, device=dev)
+                        self._k_code_count(flat, total, torch.zeros(1, dtype=torch.int64, device=dev),
+                                           torch.tensor([len(d)], dtype=torch.int64, device=dev), counts, bad, None,
+                                           None, 0.0, None)
+                        h = torch.zeros(bins, dtype=torch.int64, device=dev)
+                        unused = torch.tensor([[big, -1, 0]], dtype=torch.int64, device=dev)
+                        self._k_rows_hist(self._set_dict_rows(dict_cache, d), len(d), 1, None, counts, h, unused)
+                        hist[i] += h
                 else:
                     raise RuntimeError(f"{type(block).__name__} columns are not supported in RawFeatureFilter")
             if ys:
