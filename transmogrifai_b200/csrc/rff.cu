@@ -54,6 +54,66 @@ __device__ __forceinline__ void atomic_max_f64(double* addr, double v) {
     }
 }
 
+// ---- staged reads -----------------------------------------------------------------------------------------------------
+// The plain kernels below leave it to the compiler how many loads are in flight, and it keeps one or two (it sinks
+// every load next to its use).  Here a thread copies RFF_UNROLL 16-byte pieces of its block's stretch into its own
+// shared-memory slots with cp.async (issued back to back, no register waits on them), waits for the group, and
+// consumes them: 64 bytes in flight per thread whatever the scheduler does.  Needs 16-byte aligned columns
+// (values % 16 == 0 and ld * sizeof(T) % 16 == 0: the package's layout); anything else takes the plain kernels.
+constexpr int RFF_UNROLL = 4;
+
+__device__ __forceinline__ void rff_cp_async16(void* smem, const void* gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void rff_cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+// A block's rows: a contiguous stretch whose start is a multiple of 64 (so that a 16-byte piece never straddles a
+// validity word and piece / word indices are 32-bit).  -> rows of this block (0 for blocks beyond the end)
+__device__ __forceinline__ int rff_stretch(int64_t n, int64_t* r0) {
+    const int64_t per = (((n + gridDim.x - 1) / gridDim.x) + 63) & ~(int64_t)63;
+    *r0 = (int64_t)blockIdx.x * per;
+    const int64_t left = n - *r0;
+    return left <= 0 ? 0 : (int)(left < per ? left : per);
+}
+
+// f(value as double) for every valid row of the block's stretch
+template <typename T, typename F>
+__device__ __forceinline__ void rff_for_each_valid(const T* __restrict__ x, const unsigned long long* __restrict__ v,
+                                                   int64_t n, F f) {
+    constexpr int EPC = 16 / (int)sizeof(T);                          // elements per 16-byte piece
+    __shared__ __align__(16) unsigned char stage[RFF_UNROLL][RFF_THREADS][16];
+    int64_t r0;
+    const int len = rff_stretch(n, &r0);
+    const unsigned char* xb = reinterpret_cast<const unsigned char*>(x + r0);
+    const unsigned long long* vb = v ? v + (r0 >> 6) : nullptr;
+    const int pieces = (len + EPC - 1) / EPC;      // the last piece may read past `len`: still inside the column (ld)
+    for (int p0 = 0; p0 < pieces; p0 += RFF_UNROLL * RFF_THREADS) {
+#pragma unroll
+        for (int u = 0; u < RFF_UNROLL; ++u) {
+            const int p = p0 + u * RFF_THREADS + threadIdx.x;
+            if (p < pieces) rff_cp_async16(&stage[u][threadIdx.x][0], xb + (size_t)p * 16);
+        }
+        rff_cp_async_wait_all();
+#pragma unroll
+        for (int u = 0; u < RFF_UNROLL; ++u) {
+            const int p = p0 + u * RFF_THREADS + threadIdx.x;
+            if (p >= pieces) continue;
+            const int i0 = p * EPC;
+            const unsigned long long w = vb ? vb[i0 >> 6] : ~0ull;
+            const T* e = reinterpret_cast<const T*>(&stage[u][threadIdx.x][0]);
+#pragma unroll
+            for (int k = 0; k < EPC; ++k) {
+                const int i = i0 + k;
+                if (i < len && ((w >> (i & 63)) & 1ull)) f((double)e[k]);
+            }
+        }
+    }
+}
+
 // out [ncols][5]: min, max, sum, count, NaN seen (Summary.monoid uses java Math.min / max: a NaN value makes both NaN)
 template <int DT>
 __global__ void __launch_bounds__(RFF_THREADS)
@@ -111,12 +171,52 @@ rff_numeric_summary_kernel(const void* __restrict__ values, int64_t ld, const un
     }
 }
 
+template <int DT>
+__global__ void __launch_bounds__(RFF_THREADS)
+rff_numeric_summary_staged_kernel(const void* __restrict__ values, int64_t ld, const unsigned long long* __restrict__ valid,
+                                  int64_t ldv, int64_t n, double* __restrict__ out) {
+    typedef typename RffValue<DT>::type T;
+    const int col = blockIdx.y;
+    const T* x = static_cast<const T*>(values) + (int64_t)col * ld;
+    const unsigned long long* v = valid ? valid + (int64_t)col * ldv : nullptr;
+    double mn = INFINITY, mx = -INFINITY, sum = 0.0, cnt = 0.0, nan = 0.0;
+    rff_for_each_valid<T>(x, v, n, [&](double d) {
+        if (d != d) nan = 1.0;
+        mn = fmin(mn, d);
+        mx = fmax(mx, d);
+        sum += d;
+        cnt += 1.0;
+    });
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    sum = warp_sum(sum);
+    cnt = warp_sum(cnt);
+    nan = warp_max(nan);
+    __shared__ double s[RFF_THREADS / 32][5];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { s[w][0] = mn; s[w][1] = mx; s[w][2] = sum; s[w][3] = cnt; s[w][4] = nan; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 1; i < RFF_THREADS / 32; ++i) {
+            mn = fmin(mn, s[i][0]); mx = fmax(mx, s[i][1]); sum += s[i][2]; cnt += s[i][3]; nan = fmax(nan, s[i][4]);
+        }
+        if (cnt > 0.0) {
+            double* o = out + (int64_t)col * 5;
+            atomic_min_f64(o + 0, mn);
+            atomic_max_f64(o + 1, mx);
+            atomicAdd(o + 2, sum);
+            atomicAdd(o + 3, cnt);
+            if (nan > 0.0) atomic_max_f64(o + 4, 1.0);
+        }
+    }
+}
+
 // mode [col]: 0 = the training summary is empty (FeatureDistribution.scala:329-330: the "distribution" of a row is its
 //   value: value_sum [col] += v), 1 = min < max (histogram over splits [col][bins]), 2 = otherwise (:345-348:
 //   hist [col][0] += (v == same_value [col]), hist [col][1] += (v != same_value [col])).
 // Bucket of v in mode 1 (NumericBucketizer.scala:231-258): the i with splits[i] <= v < splits[i + 1], i < bins - 1;
 //   none, NaN or +-Inf -> bins - 1.  The splits are non-decreasing, so i is the last split <= v (binary search).
-template <int DT, bool SMEM>
+template <int DT, bool SMEM, bool STAGED>
 __global__ void __launch_bounds__(RFF_THREADS)
 rff_numeric_hist_kernel(const void* __restrict__ values, int64_t ld, const unsigned long long* __restrict__ valid,
                         int64_t ldv, int64_t n, int bins, const double* __restrict__ splits,
@@ -155,46 +255,50 @@ rff_numeric_hist_kernel(const void* __restrict__ values, int64_t ld, const unsig
     const double lo0 = lookup[0];
     const double inv = md == 1 ? (double)(bins - 2) / (lookup[bins - 2 > 0 ? bins - 2 : 0] - lo0) : 0.0;
     const bool guess = md == 1 && bins > 2 && inv > 0.0 && !isinf(inv) && !isinf(lo0) && lo0 == lo0;
-    for (int64_t base = r0 + threadIdx.x; base < r1; base += 4 * RFF_THREADS) {
-        T raw[4];
-        bool ok[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int64_t r = base + (int64_t)u * RFF_THREADS;
-            ok[u] = r < r1 && rff_valid(v, r);
-            raw[u] = ok[u] ? x[r] : T(0);
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            if (!ok[u]) continue;
-            const double d = (double)raw[u];
-            ++cnt;
-            int b;
-            if (md == 1) {
-                if (d != d || isinf(d)) {
-                    b = bins - 1;
-                } else if (guess) {
-                    const double q = (d - lo0) * inv;
-                    int g = q > 0.0 ? (q < (double)(bins - 1) ? (int)q : bins - 1) : 0;
-                    while (g > 0 && d < lookup[g]) --g;
-                    while (g < bins - 1 && lookup[g + 1] <= d) ++g;
-                    b = (g >= bins - 1 || d < lookup[g]) ? bins - 1 : g;
-                } else {
-                    int lo = 0, hi = bins;                 // first index with splits[i] > d (or not <= d: NaN)
-                    while (lo < hi) {
-                        const int mid = (lo + hi) >> 1;
-                        if (lookup[mid] <= d) lo = mid + 1; else hi = mid;
-                    }
-                    b = lo - 1;
-                    if (b < 0 || b >= bins - 1) b = bins - 1;
-                }
-            } else if (md == 2) {
-                b = d == same ? 0 : 1;
+    auto count = [&](double d) {
+        ++cnt;
+        int b;
+        if (md == 1) {
+            if (d != d || isinf(d)) {
+                b = bins - 1;
+            } else if (guess) {
+                const double q = (d - lo0) * inv;
+                int g = q > 0.0 ? (q < (double)(bins - 1) ? (int)q : bins - 1) : 0;
+                while (g > 0 && d < lookup[g]) --g;
+                while (g < bins - 1 && lookup[g + 1] <= d) ++g;
+                b = (g >= bins - 1 || d < lookup[g]) ? bins - 1 : g;
             } else {
-                vsum += d;
-                continue;
+                int lo = 0, hi = bins;                     // first index with splits[i] > d (or not <= d: NaN)
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (lookup[mid] <= d) lo = mid + 1; else hi = mid;
+                }
+                b = lo - 1;
+                if (b < 0 || b >= bins - 1) b = bins - 1;
             }
-            if (SMEM) atomicAdd(&s_hist[b], 1u); else atomicAdd(&gh[b], 1ull);
+        } else if (md == 2) {
+            b = d == same ? 0 : 1;
+        } else {
+            vsum += d;
+            return;
+        }
+        if (SMEM) atomicAdd(&s_hist[b], 1u); else atomicAdd(&gh[b], 1ull);
+    };
+    if (STAGED) {
+        rff_for_each_valid<T>(x, v, n, count);
+    } else {
+        for (int64_t base = r0 + threadIdx.x; base < r1; base += 4 * RFF_THREADS) {
+            T raw[4];
+            bool ok[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t r = base + (int64_t)u * RFF_THREADS;
+                ok[u] = r < r1 && rff_valid(v, r);
+                raw[u] = ok[u] ? x[r] : T(0);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) count((double)raw[u]);
         }
     }
     cnt = __reduce_add_sync(FULL, cnt);
@@ -364,10 +468,10 @@ rff_null_label_kernel(const unsigned long long* const* __restrict__ valid_ptrs, 
 
 }  // namespace
 
-static int rff_grid_x(int64_t n, int ncols, int per_thread) {
+static int rff_grid_x(int64_t n, int ncols, int per_thread, int blocks_per_sm = 8) {
     // one wave: as many blocks per column as fit the SMs' resident slots (8 blocks of 256 threads per SM) -- one block
     // more per column would leave a second, nearly empty wave -- and never more than the rows need
-    const int64_t want = std::max<int64_t>(1, ((int64_t)sm_count() * 8) / std::max(ncols, 1));
+    const int64_t want = std::max<int64_t>(1, ((int64_t)sm_count() * blocks_per_sm) / std::max(ncols, 1));
     const int64_t need = std::max<int64_t>(1, (n + (int64_t)RFF_THREADS * per_thread - 1) / ((int64_t)RFF_THREADS * per_thread));
     return (int)std::min<int64_t>(std::min(want, need), 65535);
 }
@@ -385,7 +489,14 @@ extern "C" int tmog_rff_numeric_summary_dev(const void* values, int dtype, int64
     const dim3 grid(rff_grid_x(n, ncols, 8), ncols);
     const unsigned long long* v = reinterpret_cast<const unsigned long long*>(valid);
     cudaStream_t s = (cudaStream_t)stream;
-    if (dtype == 0) rff_numeric_summary_kernel<0><<<grid, RFF_THREADS, 0, s>>>(values, ld, v, ldv, n, out);
+    const size_t esz = dtype == 2 ? 1 : 8;
+    const bool staged = (reinterpret_cast<uintptr_t>(values) & 15u) == 0 && ((size_t)ld * esz) % 16 == 0 &&
+                        (n + grid.x - 1) / grid.x < (int64_t)0x7fffff00ll;
+    if (staged) {
+        if (dtype == 0) rff_numeric_summary_staged_kernel<0><<<grid, RFF_THREADS, 0, s>>>(values, ld, v, ldv, n, out);
+        else if (dtype == 1) rff_numeric_summary_staged_kernel<1><<<grid, RFF_THREADS, 0, s>>>(values, ld, v, ldv, n, out);
+        else rff_numeric_summary_staged_kernel<2><<<grid, RFF_THREADS, 0, s>>>(values, ld, v, ldv, n, out);
+    } else if (dtype == 0) rff_numeric_summary_kernel<0><<<grid, RFF_THREADS, 0, s>>>(values, ld, v, ldv, n, out);
     else if (dtype == 1) rff_numeric_summary_kernel<1><<<grid, RFF_THREADS, 0, s>>>(values, ld, v, ldv, n, out);
     else rff_numeric_summary_kernel<2><<<grid, RFF_THREADS, 0, s>>>(values, ld, v, ldv, n, out);
     TMOG_LAUNCH_CHECK();
@@ -402,26 +513,30 @@ extern "C" int tmog_rff_numeric_hist_dev(const void* values, int dtype, int64_t 
     if (n == 0 || ncols == 0) return TMOG_OK;
     TMOG_REQUIRE(values && splits && mode && same_value && hist && value_sum && nonnull && (!valid || ldv * 64 >= n),
                  "NULL argument or validity words too short");
-    const dim3 grid(rff_grid_x(n, ncols, 16), ncols);
-    TMOG_REQUIRE((n + grid.x - 1) / grid.x < (int64_t)0xffffffffll, "too many rows per call");
+    const dim3 grid(rff_grid_x(n, ncols, 16, 6), ncols);       // 38 registers: six blocks of 256 threads per SM
+    TMOG_REQUIRE((n + grid.x - 1) / grid.x < (int64_t)0x7fffff00ll, "too many rows per call");
     const unsigned long long* v = reinterpret_cast<const unsigned long long*>(valid);
     unsigned long long* h = reinterpret_cast<unsigned long long*>(hist);
     unsigned long long* nn = reinterpret_cast<unsigned long long*>(nonnull);
     cudaStream_t s = (cudaStream_t)stream;
     const bool smem = bins <= RFF_SMEM_BINS;
     const size_t sh = smem ? (size_t)bins * (sizeof(double) + sizeof(unsigned)) : 0;
+    const size_t esz = dtype == 2 ? 1 : 8;
+    const bool staged = (reinterpret_cast<uintptr_t>(values) & 15u) == 0 && ((size_t)ld * esz) % 16 == 0;
+#define RFF_HIST2(DT, SM, ST)                                                                                            \
+    rff_numeric_hist_kernel<DT, SM, ST><<<grid, RFF_THREADS, sh, s>>>(values, ld, v, ldv, n, bins, splits, mode,          \
+                                                                     same_value, h, value_sum, nn)
 #define RFF_HIST(DT)                                                                                                     \
     do {                                                                                                                 \
-        if (smem)                                                                                                        \
-            rff_numeric_hist_kernel<DT, true><<<grid, RFF_THREADS, sh, s>>>(values, ld, v, ldv, n, bins, splits, mode,   \
-                                                                            same_value, h, value_sum, nn);              \
-        else                                                                                                             \
-            rff_numeric_hist_kernel<DT, false><<<grid, RFF_THREADS, 0, s>>>(values, ld, v, ldv, n, bins, splits, mode,   \
-                                                                            same_value, h, value_sum, nn);              \
+        if (smem && staged) RFF_HIST2(DT, true, true);                                                                   \
+        else if (smem) RFF_HIST2(DT, true, false);                                                                       \
+        else if (staged) RFF_HIST2(DT, false, true);                                                                     \
+        else RFF_HIST2(DT, false, false);                                                                                \
     } while (0)
     if (dtype == 0) RFF_HIST(0);
     else if (dtype == 1) RFF_HIST(1);
     else RFF_HIST(2);
+#undef RFF_HIST2
 #undef RFF_HIST
     TMOG_LAUNCH_CHECK();
     return TMOG_OK;
