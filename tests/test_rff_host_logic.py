@@ -325,3 +325,32 @@ def test_two_ranks_add_up(tmp_path):
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(0, "ok"), (1, "ok")], "\n".join(str(r[1]) for r in res)
+
+
+def test_protected_features_and_js_protection(monkeypatch):
+    """RawFeatureFilterTest.scala:310-356: protected features never enter the checks; JS-protected ones skip only the
+    divergence rule.  Against the oracle with the same settings."""
+    from transmogrifai_b200.filters import RawFeatureFilter
+    n = 400
+    train, score = make_data(n, 3), make_data(n, 4, shift=True)
+    feats = features_of(train)
+    kw = dict(bins=10, minFill=0.0, maxFillDifference=1.0, maxFillRatioDiff=float("inf"), maxJSDivergence=0.0,
+              maxCorrelation=1.0, minScoringRows=0)
+    tr, sc = chunked(train, [n])[0], chunked(score, [n])[0]
+    base = emulate(RawFeatureFilter(**kw), monkeypatch).generateFilteredRaw(tr, feats, sc)
+    dropped = {f.name for f in base.featuresToDrop}
+    assert {"r0", "t0", "i0"} <= dropped                      # any drift at all exceeds maxJSDivergence = 0
+    prot = emulate(RawFeatureFilter(protectedFeatures={"r0"}, jsDivergenceProtectedFeatures={"t0"}, **kw), monkeypatch)
+    out = prot.generateFilteredRaw(tr, feats, sc)
+    got = {f.name for f in out.featuresToDrop}
+    assert got == dropped - {"r0", "t0"}
+    names = [m.name for m in out.rawFeatureFilterResults.rawFeatureFilterMetrics]
+    assert "r0" not in names and "t0" in names               # protected: not even measured; JS-protected: measured
+    t0 = [r for r in out.rawFeatureFilterResults.exclusionReasons if r.name == "t0"][0]
+    assert not t0.jsDivergenceMismatch and not t0.excluded
+    p = O.FilterParams(bins=10, min_fill=0.0, max_fill_difference=1.0, max_fill_ratio_diff=float("inf"),
+                       max_js_divergence=0.0, max_correlation=1.0, js_divergence_protected=["t0"], protected=["r0"],
+                       min_scoring_rows=0)
+    assert sorted(got) == sorted(O.generate_filtered_raw(train, score, ["y"], p)[4])
+    # the distributions of protected features are still reported (RawFeatureFilter.scala:547-549)
+    assert "r0" in [d.name for d in out.trainingFeatureDistributions]
