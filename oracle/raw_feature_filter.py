@@ -21,8 +21,8 @@ RawFeatureFilterTest.scala:156-268, FiltersTestData.scala:38-60).
 from __future__ import annotations
 
 import math
-from dataclasses import dataclass, field
-from typing import Dict, List, Optional, Sequence, Tuple, Union
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
 
 from . import text as T
 

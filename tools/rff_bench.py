@@ -15,7 +15,6 @@ import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
 import benchdata  # noqa: E402
-from transmogrifai_b200 import features as F  # noqa: E402
 from transmogrifai_b200.filters import RawFeatureFilter  # noqa: E402
 
 

@@ -21,7 +21,7 @@ from __future__ import annotations
 
 import ctypes as C
 from dataclasses import dataclass, field
-from typing import Dict, Iterable, List, Optional, Sequence, Tuple, Union
+from typing import Dict, Iterable, List, Optional, Sequence, Tuple
 
 import numpy as np
 
@@ -217,7 +217,8 @@ class RawFeatureFilter:
         else:
             # one entry per (distribution, response), flattened, then zipped with the distributions (:225-231): with a
             # single response -- the only case in which the reference lines them up -- entry i belongs to feature i
-            corrs = [per_response.get(d.featureKey) for d in trainingDistribs for per_response in correlationInfo.values()]
+            corrs = [per_response.get(d.featureKey) for d in trainingDistribs
+                     for per_response in correlationInfo.values()]
         if not scoringDistribs:
             sf = js = fd = fr = [None] * k
         else:
@@ -272,7 +273,7 @@ class RawFeatureFilter:
                 "jsDivergenceProtectedFeatures": sorted(self.jsDivergenceProtectedFeatures),
                 "protectedFeatures": sorted(self.protectedFeatures)}
 
-    # -- the scans (csrc/rff.cu; every method below queues kernels on the current stream) --------------------------------
+    # -- the scans (csrc/rff.cu; every method below queues kernels on the current stream) ---------------------------
     _device = "cuda"
 
     @staticmethod
@@ -283,7 +284,8 @@ class RawFeatureFilter:
     def _k_summary(self, sub, n: int, out) -> None:
         """out [ncols][5] += Summary of every column of the numeric block `sub` (device)."""
         from . import runtime as R
-        L.call("tmog_rff_numeric_summary_dev", sub.values.data_ptr(), self._dtype_code(sub.values), sub.values.stride(0),
+        L.call("tmog_rff_numeric_summary_dev", sub.values.data_ptr(), self._dtype_code(sub.values),
+               sub.values.stride(0),
                R.ptr(sub.valid), 0 if sub.valid is None else sub.valid.stride(0), n, len(sub.names), out.data_ptr(),
                R.stream())
 
@@ -514,8 +516,8 @@ class RawFeatureFilter:
                     for r in range(max(len(ys), 1)):      # the codes are counted once; every response has its own sums
                         y, yv = ys[r] if ys else (None, None)
                         ny = torch.zeros(m, dtype=torch.float64, device=dev) if ys else None
-                        self._k_code_count(sub, n, d_off, d_sizes, counts if r == 0 else torch.zeros_like(counts), bad, y,
-                                           yv, shifts[r] if ys else 0.0, ny)
+                        self._k_code_count(sub, n, d_off, d_sizes, counts if r == 0 else torch.zeros_like(counts),
+                                           bad, y, yv, shifts[r] if ys else 0.0, ny)
                         if ys:
                             nl[r, at] += ny
                     for j, i in enumerate(at):
@@ -545,7 +547,8 @@ class RawFeatureFilter:
                             yy = y[:n]
                             if yv is not None:
                                 rows_i = torch.arange(n, device=dev)
-                                yy = torch.where(((yv[rows_i >> 6] >> (rows_i & 63)) & 1) != 0, yy, torch.zeros_like(yy))
+                                held = ((yv[rows_i >> 6] >> (rows_i & 63)) & 1) != 0
+                                yy = torch.where(held, yy, torch.zeros_like(yy))
                             nl[r, i] += ((yy - shifts[r]) * (~filled)).sum()
                         total = int(totals[j])
                         if total == 0 or len(d) == 0:
@@ -646,7 +649,8 @@ class RawFeatureFilter:
         return AllFeatureInformation({k_: summaries[k_] for k_ in rkeys}, [dists[k_] for k_ in rkeys],
                                      {k_: summaries[k_] for k_ in pkeys}, [dists[k_] for k_ in pkeys], corr_info)
 
-    def generateFilteredRaw(self, trainData, rawFeatures: Sequence[F.Feature], scoreData=None) -> FilteredRawData:  # noqa: N802,N803
+    def generateFilteredRaw(self, trainData, rawFeatures: Sequence[F.Feature],  # noqa: N802,N803
+                            scoreData=None) -> FilteredRawData:  # noqa: N803
         """RawFeatureFilter.generateFilteredRaw (:482-566): the readers' data frames are the arguments here.  The
         cleaned data are the training batch (or chunks) without the dropped features' columns."""
         from . import dist as D
