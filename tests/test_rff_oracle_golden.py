@@ -225,3 +225,32 @@ def test_host_functions_of_the_library_match_the_oracle():
         e = exp[0][j + 1]
         e = e if math.isnan(e) else min(abs(e), 1.0)
         assert (math.isnan(e) and math.isnan(out[j])) or abs(out[j] - e) < 1e-9
+
+
+def test_js_divergence_properties():
+    """Size-independent properties of tmog_rff_js_divergence (FeatureDistribution.jsDivergence, :154-163): symmetric,
+    within [0, 1] (log base 2), 0 for proportional histograms, 1 for disjoint ones, blind to bins empty on both sides."""
+    import ctypes as C
+    from transmogrifai_b200 import _lib as L
+    rng = np.random.default_rng(23)
+
+    def js(a, b):
+        a, b = np.ascontiguousarray(a, dtype=np.float64), np.ascontiguousarray(b, dtype=np.float64)
+        out = C.c_double()
+        L.call("tmog_rff_js_divergence", a.ctypes.data, b.ctypes.data, len(a), C.byref(out))
+        return out.value
+
+    for _ in range(200):
+        k = int(rng.integers(2, 300))
+        a = rng.integers(0, 1000, k).astype(np.float64) * (rng.random(k) < 0.8)
+        b = rng.integers(0, 1000, k).astype(np.float64) * (rng.random(k) < 0.8)
+        if a.sum() == 0 or b.sum() == 0:
+            continue
+        d = js(a, b)
+        assert -1e-12 <= d <= 1.0 + 1e-12
+        assert abs(d - js(b, a)) < 1e-12
+        assert abs(js(a, 7.0 * a)) < 1e-12
+        pad = np.zeros(5)
+        assert abs(js(np.concatenate([a, pad]), np.concatenate([b, pad])) - d) < 1e-12
+        lo, hi = np.concatenate([a + 1, np.zeros(k)]), np.concatenate([np.zeros(k), b + 1])
+        assert abs(js(lo, hi) - 1.0) < 1e-12
